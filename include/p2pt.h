@@ -1,0 +1,186 @@
+/*
+ * p2pt.h -- C ABI of libp2ptunnel_b200.so: the batched, B200-resident form of the one byte path of
+ * michaelneale/p2p-llm-tunnel that every tunnelled response byte crosses:
+ *
+ *   TunnelMessage::encode / decode      /root/reference/tunnel/src/protocol.rs:148-154, :157-172
+ *   MessageType::from_u8                /root/reference/tunnel/src/protocol.rs:103-118
+ *   demux by stream_id                  /root/reference/tunnel/src/proxy.rs:105-172, serve.rs:103-139
+ *   CryptoGcm::encrypt / decrypt        webrtc-dtls 0.10.0 (un-vendored; Cargo.lock:2822-2824),
+ *                                       reached at every dc.send (serve.rs:274) / on_message (rtc.rs:88)
+ *
+ * Conventions
+ *   - Plain pointers and sizes only.  The caller owns every buffer it passes; the library keeps no
+ *     pointer past return.  A batch of n variable-length items is (base pointer, u64 off[n+1]):
+ *     item i occupies [off[i], off[i+1]) -- frames carry no length field (protocol.rs:157-172).
+ *     Offsets must be non-decreasing.
+ *   - Return value: 0 = the call ran; negative = the whole call failed (bad argument, CUDA error,
+ *     capacity).  p2pt_last_error() gives the text.  One bad item never fails a batch: it gets a
+ *     per-item status byte, mirroring the reference's warn!+continue (serve.rs:103-109,
+ *     proxy.rs:110-116).
+ *   - Entry points without a suffix take HOST pointers and do host->device copy, kernels,
+ *     device->host copy, synchronously.  *_device entry points take DEVICE pointers plus a
+ *     cudaStream_t (as void*) and only enqueue kernels; they allocate nothing.
+ *   - Re-entrant: any thread may call on any ctx; host-pointer calls on one ctx serialise on the
+ *     ctx's staging buffers.  One ctx per GPU.  There is no CPU fallback: without a CUDA device
+ *     p2pt_ctx_create fails.
+ */
+#ifndef P2PT_H
+#define P2PT_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define P2PT_ABI_VERSION 1
+
+/* whole-call return codes */
+#define P2PT_OK            0
+#define P2PT_ERR_ARG      -1
+#define P2PT_ERR_CUDA     -2
+#define P2PT_ERR_CAPACITY -3   /* an output array the caller sized is too small */
+#define P2PT_ERR_STATE    -4   /* e.g. seal/open before p2pt_sessions_load */
+
+/* per-item status bytes */
+#define P2PT_ST_OK                0
+#define P2PT_ST_TOO_SHORT         1  /* protocol.rs:158-160 "message too short: {len} bytes" */
+#define P2PT_ST_UNKNOWN_TYPE      2  /* protocol.rs:161-163 "unknown message type: {b}" */
+#define P2PT_ST_AUTH_FAIL         3  /* AEAD tag mismatch (aes-gcm decrypt_in_place Err) */
+#define P2PT_ST_NO_ROOM_FOR_NONCE 4  /* webrtc-dtls ErrNotEnoughRoomForNonce: len <= 13 + 8 */
+#define P2PT_ST_PASS_THROUGH      5  /* ChangeCipherSpec (type 20) record copied unmodified */
+#define P2PT_ST_BAD_HEADER        6  /* RecordLayerHeader::unmarshal failure: < 13 bytes or version */
+
+/* protocol.rs:9-12 */
+#define P2PT_MAX_FRAME_SIZE 65536u
+#define P2PT_MAX_BODY_CHUNK 65408u
+#define P2PT_FRAME_HEADER   5u
+/* DTLS record geometry (RFC 6347 4.1, RFC 5288 3) */
+#define P2PT_REC_HEADER     13u
+#define P2PT_REC_NONCE      8u
+#define P2PT_REC_TAG        16u
+#define P2PT_REC_OVERHEAD   24u   /* sealed = raw + 8 + 16 */
+
+typedef struct p2pt_ctx p2pt_ctx;
+
+/* Result of decoding one frame: the batched TunnelMessage (protocol.rs:139-144).  payload is the
+ * zero-copy slice [pay_off, pay_off + pay_len) of the input buffer, like Bytes::advance(5). */
+typedef struct {
+    uint64_t pay_off;
+    uint32_t pay_len;
+    uint32_t stream_id;
+    uint8_t  msg_type;
+    uint8_t  status;     /* P2PT_ST_OK / TOO_SHORT / UNKNOWN_TYPE */
+    uint8_t  pad[6];
+} p2pt_desc;             /* 24 bytes */
+
+/* ---- context ---------------------------------------------------------------------------- */
+int32_t     p2pt_abi_version(void);
+int32_t     p2pt_ctx_create(int device, p2pt_ctx** out);
+int32_t     p2pt_ctx_destroy(p2pt_ctx* ctx);
+const char* p2pt_last_error(p2pt_ctx* ctx);            /* ctx may be NULL: last create error */
+/* pinned host memory for callers that want full PCIe speed on the host-pointer entry points */
+void*       p2pt_host_alloc(size_t bytes);
+void        p2pt_host_free(void* p);
+/* number of kernels this ctx has launched so far (bench.py's gpu_launches evidence) */
+uint64_t    p2pt_launch_count(p2pt_ctx* ctx);
+/* tuning knobs.  "gcm_group_width": lanes that share one record in the seal/open kernels
+ * (4, 8, 16 or 32; 0 = choose from the batch's mean record length). */
+int32_t     p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value);
+
+/* ---- DTLS session keys: CryptoGcm::new(local_key, local_write_iv, remote_key, remote_write_iv)
+ *      (webrtc-dtls 0.10.0 crypto_gcm.rs).  n sessions; keys n x 16 bytes, ivs n x 4 bytes.
+ *      Expands AES-128 round keys, H = AES_K(0^128) and H^1..H^32 on the device.  Host pointers. */
+int32_t p2pt_sessions_load(p2pt_ctx* ctx, uint32_t n,
+                           const uint8_t* local_keys16, const uint8_t* local_ivs4,
+                           const uint8_t* remote_keys16, const uint8_t* remote_ivs4);
+
+/* ---- frame codec ------------------------------------------------------------------------- */
+/* TunnelMessage::encode (protocol.rs:148-154): out[out_off[i]..] = [types[i]][sids[i] BE][payload_i].
+ * Needs out_off[i+1] - out_off[i] >= 5 + payload length. */
+int32_t p2pt_frame_encode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* types, const uint32_t* sids,
+                                const uint8_t* payload, const uint64_t* pay_off,
+                                uint8_t* out, const uint64_t* out_off);
+/* TunnelMessage::decode (protocol.rs:157-172), check order as the reference. */
+int32_t p2pt_frame_decode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, const uint64_t* in_off,
+                                p2pt_desc* desc);
+/* Demux (proxy.rs:118-153, serve.rs:112-139): stable group-by stream_id of the status-OK frames.
+ * uniq_sid[k] ascending; csr[k+1] offsets into perm; perm[csr[k]] = frame indices in arrival
+ * order.  If gathered != NULL, body frames (ReqBody 11 / ResBody 21) are concatenated per stream
+ * into gathered and gathered_off[k+1] delimits streams (the Vec<u8> of serve.rs:120-124).
+ * max_streams sizes uniq_sid / csr / gathered_off; gathered_cap sizes gathered. */
+int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
+                               const uint8_t* in, uint64_t in_bytes,
+                               uint32_t max_streams, uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+                               uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
+                               uint64_t* gathered_off);
+
+/* ---- DTLS 1.2 AES-128-GCM record layer ------------------------------------------------------ */
+/* CryptoGcm::encrypt(pkt_rlh, raw): raw_i = hdr13 || plaintext; rec_i = hdr13' || nonce8 ||
+ * ciphertext || tag16 with the header length field rewritten to 8 + len + 16.  nonce8 (n x 8) is
+ * the explicit nonce the reference draws from rand::thread_rng(); it is an INPUT here so results
+ * are reproducible.  session[i] indexes the table given to p2pt_sessions_load (local key / iv).
+ * Needs rec_off[i+1] - rec_off[i] >= raw_len_i + 24.  status: OK or BAD_HEADER (raw_len < 13). */
+int32_t p2pt_dtls_gcm_seal_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                 const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
+                                 uint8_t* rec, const uint64_t* rec_off, uint8_t* status);
+/* CryptoGcm::decrypt(r): out_i = hdr13 (unchanged) || plaintext, out_len[i] its length.
+ * Uses the remote key / iv.  status: OK, AUTH_FAIL (output zeroed, out_len 0), NO_ROOM_FOR_NONCE,
+ * PASS_THROUGH (record copied), BAD_HEADER.  Needs out_off[i+1] - out_off[i] >= rec_len_i. */
+int32_t p2pt_dtls_gcm_open_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                 const uint8_t* rec, const uint64_t* rec_off,
+                                 uint8_t* out, const uint64_t* out_off,
+                                 uint32_t* out_len, uint8_t* status);
+
+/* ---- fused frame + record pipeline (one frame = one data-channel message = one record) ------- */
+/* encode -> seal in one pass: record i = hdr13 || nonce8 || E([type][sid BE][payload_i]) || tag.
+ * hdr13 = content_type 23, version fe fd, epoch[i], seq48[i], length.  (serve.rs:269-276 followed
+ * by dc.send.) */
+int32_t p2pt_pipeline_seal(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                           const uint16_t* epoch, const uint64_t* seq48, const uint8_t* nonce8,
+                           const uint8_t* types, const uint32_t* sids,
+                           const uint8_t* payload, const uint64_t* pay_off,
+                           uint8_t* rec, const uint64_t* rec_off, uint8_t* status);
+/* open -> decode in one pass: out_i = hdr13 || frame_i; desc[i] describes the frame inside out
+ * (pay_off relative to out).  desc[i].status carries the record status when the record did not
+ * open, else the frame decode status.  Follow with p2pt_frame_demux_batch on desc/out. */
+int32_t p2pt_pipeline_open(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                           const uint8_t* rec, const uint64_t* rec_off,
+                           uint8_t* out, const uint64_t* out_off, p2pt_desc* desc);
+
+/* ---- device-pointer variants: same arguments, all pointers are device pointers, `stream` is a
+ *      cudaStream_t.  They enqueue on `stream` and return without synchronising. -------------- */
+int32_t p2pt_frame_encode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* types, const uint32_t* sids,
+                                       const uint8_t* payload, const uint64_t* pay_off,
+                                       uint8_t* out, const uint64_t* out_off, void* stream);
+int32_t p2pt_frame_decode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, const uint64_t* in_off,
+                                       p2pt_desc* desc, void* stream);
+/* scratch: device memory of at least p2pt_frame_demux_scratch_bytes(n) bytes, 256-byte aligned.
+ * k_out is a device pointer to one u32. */
+uint64_t p2pt_frame_demux_scratch_bytes(uint64_t n);
+int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
+                                      const uint8_t* in,
+                                      uint32_t max_streams, uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+                                      uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
+                                      uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes,
+                                      void* stream);
+int32_t p2pt_dtls_gcm_seal_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                        const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
+                                        uint8_t* rec, const uint64_t* rec_off, uint8_t* status, void* stream);
+int32_t p2pt_dtls_gcm_open_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                        const uint8_t* rec, const uint64_t* rec_off,
+                                        uint8_t* out, const uint64_t* out_off,
+                                        uint32_t* out_len, uint8_t* status, void* stream);
+int32_t p2pt_pipeline_seal_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                  const uint16_t* epoch, const uint64_t* seq48, const uint8_t* nonce8,
+                                  const uint8_t* types, const uint32_t* sids,
+                                  const uint8_t* payload, const uint64_t* pay_off,
+                                  uint8_t* rec, const uint64_t* rec_off, uint8_t* status, void* stream);
+int32_t p2pt_pipeline_open_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                  const uint8_t* rec, const uint64_t* rec_off,
+                                  uint8_t* out, const uint64_t* out_off, p2pt_desc* desc, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* P2PT_H */

@@ -1,0 +1,96 @@
+/*
+ * p2pt_oracle.h -- CPU oracle for the tunnel frame codec + DTLS 1.2 AES-128-GCM record path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is part of the product: only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load it,
+ * and only as the checker or as the timed CPU baseline.  The product (libp2ptunnel_b200.so)
+ * never links or calls it.
+ *
+ * Parity pinning:
+ *   - frame codec: PINNED by the reference's own literal vectors and round-trip values
+ *     (/root/reference/tunnel/src/protocol.rs:392-460, :271-388) -> tests/golden/frames_kat.json.
+ *   - AES-128-GCM arithmetic: pinned by FIPS-197 App. B / C.1 and the GCM spec test cases 1-4,
+ *     and cross-checked against Python `cryptography` (OpenSSL) on every golden record.
+ *   - DTLS record LAYOUT (nonce / AAD / header length fix-up): "parity unpinned" against the
+ *     reference, because it lives in the un-vendored crate webrtc-dtls 0.10.0
+ *     (/root/reference/tunnel/Cargo.lock:2822-2824) whose source is not under /root/reference and
+ *     no reference test touches it.  The layout is restated from RFC 6347 4.1 / RFC 5288 3 as that
+ *     crate implements them and is isolated in orc_dtls_aad()/orc_dtls_seal()/orc_dtls_open().
+ */
+#ifndef P2PT_ORACLE_H
+#define P2PT_ORACLE_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* per-record status codes shared with include/p2pt.h */
+enum {
+    ORC_OK = 0,
+    ORC_TOO_SHORT = 1,        /* protocol.rs:158-160 "message too short" */
+    ORC_UNKNOWN_TYPE = 2,     /* protocol.rs:161-163 "unknown message type" */
+    ORC_AUTH_FAIL = 3,        /* aes-gcm decrypt_in_place Err */
+    ORC_NO_ROOM_FOR_NONCE = 4,/* webrtc-dtls ErrNotEnoughRoomForNonce */
+    ORC_PASS_THROUGH = 5,     /* ChangeCipherSpec record returned unmodified */
+    ORC_BAD_HEADER = 6        /* RecordLayerHeader::unmarshal failure (short / version) */
+};
+
+/* 24-byte frame descriptor, identical to p2pt_desc in include/p2pt.h */
+typedef struct {
+    uint64_t pay_off;   /* absolute byte offset of the payload inside the input buffer */
+    uint32_t pay_len;
+    uint32_t stream_id;
+    uint8_t  msg_type;
+    uint8_t  status;
+    uint8_t  pad[6];
+} orc_desc;
+
+/* ---- frame codec (protocol.rs) ---- */
+int  orc_msg_type_valid(uint8_t b);
+void orc_frame_encode_batch(uint64_t n, const uint8_t* types, const uint32_t* sids,
+                            const uint8_t* payload, const uint64_t* pay_off,
+                            uint8_t* out, const uint64_t* out_off);
+void orc_frame_decode_batch(uint64_t n, const uint8_t* in, const uint64_t* in_off, orc_desc* desc);
+/* stable group-by stream_id; returns number of streams k. Streams ascending by id. */
+uint32_t orc_frame_demux_batch(uint64_t n, const orc_desc* desc, const uint8_t* in,
+                               uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+                               uint8_t* gathered, uint64_t* gathered_off);
+
+/* ---- AES-128 / GHASH / GCM (FIPS-197, SP 800-38D) ---- */
+void orc_aes128_expand(const uint8_t key[16], uint8_t rk[176]);
+void orc_aes128_encrypt_block(const uint8_t rk[176], const uint8_t in[16], uint8_t out[16]);
+void orc_gf128_mul(const uint8_t x[16], const uint8_t y[16], uint8_t out[16]);
+void orc_ghash(const uint8_t h[16], const uint8_t* aad, size_t aad_len,
+               const uint8_t* c, size_t c_len, uint8_t out[16]);
+void orc_gcm_encrypt(const uint8_t key[16], const uint8_t iv12[12],
+                     const uint8_t* aad, size_t aad_len,
+                     const uint8_t* pt, size_t len, uint8_t* ct, uint8_t tag[16]);
+int  orc_gcm_decrypt(const uint8_t key[16], const uint8_t iv12[12],
+                     const uint8_t* aad, size_t aad_len,
+                     const uint8_t* ct, size_t len, const uint8_t tag[16], uint8_t* pt);
+
+/* ---- DTLS 1.2 record seal / open (webrtc-dtls 0.10.0 CryptoGcm, restated) ---- */
+void orc_dtls_aad(const uint8_t hdr13[13], uint16_t payload_len, uint8_t aad[13]);
+/* raw = hdr13 || plaintext; out gets hdr13' || nonce8 || ct || tag16 (raw_len + 24 bytes).
+ * returns status (ORC_OK or ORC_BAD_HEADER when raw_len < 13). */
+int  orc_dtls_seal(const uint8_t key[16], const uint8_t iv4[4], const uint8_t nonce8[8],
+                   const uint8_t* raw, uint64_t raw_len, uint8_t* out);
+/* rec = sealed record; out gets hdr13 || plaintext. *out_len set on OK / PASS_THROUGH. */
+int  orc_dtls_open(const uint8_t key[16], const uint8_t iv4[4],
+                   const uint8_t* rec, uint64_t rec_len, uint8_t* out, uint64_t* out_len);
+
+void orc_dtls_seal_batch(uint64_t n, const uint32_t* session,
+                         const uint8_t* keys16, const uint8_t* ivs4, const uint8_t* nonce8,
+                         const uint8_t* raw, const uint64_t* raw_off,
+                         uint8_t* rec, const uint64_t* rec_off, uint8_t* status);
+void orc_dtls_open_batch(uint64_t n, const uint32_t* session,
+                         const uint8_t* keys16, const uint8_t* ivs4,
+                         const uint8_t* rec, const uint64_t* rec_off,
+                         uint8_t* out, const uint64_t* out_off, uint32_t* out_len, uint8_t* status);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

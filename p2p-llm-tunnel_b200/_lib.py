@@ -1,0 +1,266 @@
+"""ctypes binding of libp2ptunnel_b200.so (include/p2pt.h).
+
+This is the stub a maintainer of the reference would write in Rust (`extern "C"` block, see
+INTEGRATION.md); here it is in Python because no Rust toolchain exists in this environment.
+The library is loaded lazily and loudly: a missing .so raises, nothing falls back to the CPU.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_NAME = "libp2ptunnel_b200.so"
+
+# whole-call return codes / per-item status bytes (include/p2pt.h)
+OK, ERR_ARG, ERR_CUDA, ERR_CAPACITY, ERR_STATE = 0, -1, -2, -3, -4
+ST_OK, ST_TOO_SHORT, ST_UNKNOWN_TYPE, ST_AUTH_FAIL, ST_NO_ROOM_FOR_NONCE, ST_PASS_THROUGH, ST_BAD_HEADER = range(7)
+
+DESC_DTYPE = np.dtype([("pay_off", "<u8"), ("pay_len", "<u4"), ("stream_id", "<u4"),
+                       ("msg_type", "u1"), ("status", "u1"), ("pad", "u1", (6,))])
+assert DESC_DTYPE.itemsize == 24
+
+_vp, _u64, _u32, _i32, _int = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32, C.c_int
+
+# name -> (restype, argtypes); every symbol include/p2pt.h declares
+SIGNATURES = {
+    "p2pt_abi_version": (_i32, []),
+    "p2pt_ctx_create": (_i32, [_int, C.POINTER(_vp)]),
+    "p2pt_ctx_destroy": (_i32, [_vp]),
+    "p2pt_last_error": (C.c_char_p, [_vp]),
+    "p2pt_host_alloc": (_vp, [C.c_size_t]),
+    "p2pt_host_free": (None, [_vp]),
+    "p2pt_launch_count": (_u64, [_vp]),
+    "p2pt_sessions_load": (_i32, [_vp, _u32, _vp, _vp, _vp, _vp]),
+    "p2pt_frame_encode_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_frame_decode_batch": (_i32, [_vp, _u64, _vp, _vp, _vp]),
+    "p2pt_frame_demux_batch": (_i32, [_vp, _u64, _vp, _vp, _u64, _u32, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
+    "p2pt_dtls_gcm_seal_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_dtls_gcm_open_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_pipeline_seal": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_pipeline_open": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_frame_encode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_frame_decode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp]),
+    "p2pt_frame_demux_scratch_bytes": (_u64, [_u64]),
+    "p2pt_frame_demux_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _u64, _vp]),
+    "p2pt_dtls_gcm_seal_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_dtls_gcm_open_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_pipeline_seal_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_pipeline_open_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_ctx_set_option": (_i32, [_vp, C.c_char_p, C.c_int64]),
+}
+
+
+class P2ptError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"p2pt error {code}: {msg}")
+        self.code = code
+
+
+def lib_path():
+    return os.path.join(_HERE, LIB_NAME)
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen the CUDA library and bind every symbol; raises if it was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise P2ptError(ERR_STATE, f"{path} not found: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                   "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the .so does not export it
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _ptr(x):
+    """numpy array / torch tensor / int / None -> address."""
+    if x is None:
+        return None
+    if isinstance(x, (int, np.integer)):
+        return int(x)
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data
+    if hasattr(x, "data_ptr"):
+        return x.data_ptr()
+    raise TypeError(f"cannot take the address of {type(x)}")
+
+
+def _as(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a
+
+
+class Context:
+    """One p2pt_ctx (one per GPU).  Host methods take/return numpy arrays; *_device methods take
+    raw device pointers (ints or torch tensors) and a CUDA stream handle."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        h = _vp()
+        rc = self.lib.p2pt_ctx_create(int(device), C.byref(h))
+        if rc != OK:
+            raise P2ptError(rc, (self.lib.p2pt_last_error(None) or b"").decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.p2pt_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != OK:
+            raise P2ptError(rc, (self.lib.p2pt_last_error(self.h) or b"").decode())
+
+    def call(self, name, *args):
+        """Raw call with pointer conversion; raises P2ptError on a negative return."""
+        fn = getattr(self.lib, name)
+        conv = [(_ptr(a) if not isinstance(a, (int, np.integer, bytes)) or a is None else a) for a in args]
+        self._check(fn(self.h, *conv))
+
+    def launch_count(self):
+        return int(self.lib.p2pt_launch_count(self.h))
+
+    def set_option(self, name, value):
+        self._check(self.lib.p2pt_ctx_set_option(self.h, name.encode(), int(value)))
+
+    # ---- sessions ------------------------------------------------------------------------------
+    def sessions_load(self, local_keys, local_ivs, remote_keys=None, remote_ivs=None):
+        lk = _as(local_keys, np.uint8).reshape(-1, 16)
+        li = _as(local_ivs, np.uint8).reshape(-1, 4)
+        rk = lk if remote_keys is None else _as(remote_keys, np.uint8).reshape(-1, 16)
+        ri = li if remote_ivs is None else _as(remote_ivs, np.uint8).reshape(-1, 4)
+        n = lk.shape[0]
+        assert li.shape[0] == n and rk.shape[0] == n and ri.shape[0] == n
+        self._check(self.lib.p2pt_sessions_load(self.h, n, lk.ctypes.data, li.ctypes.data, rk.ctypes.data, ri.ctypes.data))
+        self.n_sessions = n
+        self._session_owner = None
+
+    # ---- frame codec (host buffers) ------------------------------------------------------------------
+    def frame_encode(self, types, sids, payload, pay_off, out_off=None):
+        types = _as(types, np.uint8); sids = _as(sids, np.uint32)
+        payload = _as(payload, np.uint8); pay_off = _as(pay_off, np.uint64)
+        n = len(types)
+        if out_off is None:
+            lens = (pay_off[1:] - pay_off[:-1]) + np.uint64(5)
+            out_off = np.zeros(n + 1, np.uint64)
+            np.cumsum(lens, out=out_off[1:])
+        out_off = _as(out_off, np.uint64)
+        out = np.zeros(int(out_off[-1]) if n else 0, np.uint8)
+        self._check(self.lib.p2pt_frame_encode_batch(self.h, n, types.ctypes.data, sids.ctypes.data,
+                                                     payload.ctypes.data, pay_off.ctypes.data,
+                                                     out.ctypes.data, out_off.ctypes.data))
+        return out, out_off
+
+    def frame_decode(self, buf, in_off):
+        buf = _as(buf, np.uint8); in_off = _as(in_off, np.uint64)
+        n = len(in_off) - 1
+        desc = np.zeros(n, DESC_DTYPE)
+        self._check(self.lib.p2pt_frame_decode_batch(self.h, n, buf.ctypes.data, in_off.ctypes.data, desc.ctypes.data))
+        return desc
+
+    def frame_demux(self, desc, buf=None, max_streams=None, gather=True):
+        desc = np.ascontiguousarray(desc, dtype=DESC_DTYPE)
+        n = len(desc)
+        if max_streams is None:
+            max_streams = max(n, 1)
+        uniq = np.zeros(max_streams + 1, np.uint32)
+        csr = np.zeros(max_streams + 1, np.uint64)
+        perm = np.zeros(max(n, 1), np.uint32)
+        k = _u32(0)
+        gathered = goff = None
+        gcap = 0
+        if gather:
+            buf = _as(buf, np.uint8)
+            body = (desc["status"] == 0) & ((desc["msg_type"] == 11) | (desc["msg_type"] == 21))
+            gcap = int(desc["pay_len"][body].sum())
+            gathered = np.zeros(max(gcap, 1), np.uint8)
+            goff = np.zeros(max_streams + 1, np.uint64)
+        self._check(self.lib.p2pt_frame_demux_batch(
+            self.h, n, desc.ctypes.data, _ptr(buf) if gather else None, (buf.size if gather else 0),
+            max_streams, uniq.ctypes.data, csr.ctypes.data, perm.ctypes.data, C.addressof(k),
+            _ptr(gathered), gcap, _ptr(goff)))
+        kk = k.value
+        m = int(csr[kk])
+        res = {"k": kk, "uniq_sid": uniq[:kk].copy(), "csr": csr[:kk + 1].copy(), "perm": perm[:m].copy()}
+        if gather:
+            res["gathered_off"] = goff[:kk + 1].copy()
+            res["gathered"] = gathered[:int(goff[kk])].copy()
+        return res
+
+    # ---- DTLS record layer (host buffers) --------------------------------------------------------------
+    def dtls_seal(self, session, nonce8, raw, raw_off, rec_off=None):
+        session = _as(session, np.uint32); nonce8 = _as(nonce8, np.uint8)
+        raw = _as(raw, np.uint8); raw_off = _as(raw_off, np.uint64)
+        n = len(session)
+        if rec_off is None:
+            lens = (raw_off[1:] - raw_off[:-1]) + np.uint64(24)
+            rec_off = np.zeros(n + 1, np.uint64)
+            np.cumsum(lens, out=rec_off[1:])
+        rec_off = _as(rec_off, np.uint64)
+        rec = np.zeros(int(rec_off[-1]) if n else 0, np.uint8)
+        status = np.zeros(n, np.uint8)
+        self._check(self.lib.p2pt_dtls_gcm_seal_batch(self.h, n, session.ctypes.data, nonce8.ctypes.data,
+                                                      raw.ctypes.data, raw_off.ctypes.data,
+                                                      rec.ctypes.data, rec_off.ctypes.data, status.ctypes.data))
+        return rec, rec_off, status
+
+    def dtls_open(self, session, rec, rec_off, out_off=None):
+        session = _as(session, np.uint32); rec = _as(rec, np.uint8); rec_off = _as(rec_off, np.uint64)
+        n = len(session)
+        if out_off is None:
+            out_off = rec_off
+        out_off = _as(out_off, np.uint64)
+        out = np.zeros(int(out_off[-1]) if n else 0, np.uint8)
+        out_len = np.zeros(n, np.uint32)
+        status = np.zeros(n, np.uint8)
+        self._check(self.lib.p2pt_dtls_gcm_open_batch(self.h, n, session.ctypes.data, rec.ctypes.data,
+                                                      rec_off.ctypes.data, out.ctypes.data, out_off.ctypes.data,
+                                                      out_len.ctypes.data, status.ctypes.data))
+        return out, out_off, out_len, status
+
+    def pipeline_seal(self, session, epoch, seq48, nonce8, types, sids, payload, pay_off, rec_off=None):
+        session = _as(session, np.uint32); epoch = _as(epoch, np.uint16); seq48 = _as(seq48, np.uint64)
+        nonce8 = _as(nonce8, np.uint8); types = _as(types, np.uint8); sids = _as(sids, np.uint32)
+        payload = _as(payload, np.uint8); pay_off = _as(pay_off, np.uint64)
+        n = len(session)
+        if rec_off is None:
+            lens = (pay_off[1:] - pay_off[:-1]) + np.uint64(5 + 13 + 24)
+            rec_off = np.zeros(n + 1, np.uint64)
+            np.cumsum(lens, out=rec_off[1:])
+        rec_off = _as(rec_off, np.uint64)
+        rec = np.zeros(int(rec_off[-1]) if n else 0, np.uint8)
+        status = np.zeros(n, np.uint8)
+        self._check(self.lib.p2pt_pipeline_seal(self.h, n, session.ctypes.data, epoch.ctypes.data, seq48.ctypes.data,
+                                                nonce8.ctypes.data, types.ctypes.data, sids.ctypes.data,
+                                                payload.ctypes.data, pay_off.ctypes.data,
+                                                rec.ctypes.data, rec_off.ctypes.data, status.ctypes.data))
+        return rec, rec_off, status
+
+    def pipeline_open(self, session, rec, rec_off, out_off=None):
+        session = _as(session, np.uint32); rec = _as(rec, np.uint8); rec_off = _as(rec_off, np.uint64)
+        n = len(session)
+        if out_off is None:
+            out_off = rec_off
+        out_off = _as(out_off, np.uint64)
+        out = np.zeros(int(out_off[-1]) if n else 0, np.uint8)
+        desc = np.zeros(n, DESC_DTYPE)
+        self._check(self.lib.p2pt_pipeline_open(self.h, n, session.ctypes.data, rec.ctypes.data, rec_off.ctypes.data,
+                                                out.ctypes.data, out_off.ctypes.data, desc.ctypes.data))
+        return out, out_off, desc

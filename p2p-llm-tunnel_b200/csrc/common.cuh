@@ -1,0 +1,120 @@
+// common.cuh -- byte-stream helpers shared by the frame and record kernels (sm_100a).
+//
+// Frames and records are packed back to back at arbitrary byte offsets (a 5-byte frame header, a
+// 13-byte record header and an 8-byte nonce shift everything off 16-byte alignment), so every
+// kernel moves data as ALIGNED 16-byte vectors and re-aligns in registers with a byte funnel.
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+
+namespace p2pt {
+
+typedef unsigned long long u64;
+
+__device__ __forceinline__ uint4 ldg128(const void* p) {
+    return __ldg(reinterpret_cast<const uint4*>(p));
+}
+// streaming variants: data touched once, keep it out of L1
+__device__ __forceinline__ uint4 ldg128_stream(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void stg128(void* p, const uint4& v) {
+    *reinterpret_cast<uint4*>(p) = v;
+}
+
+// bytes [s, s+16) of the 32-byte string a || b, 0 <= s <= 15.
+__device__ __forceinline__ uint4 funnel16(const uint4& a, const uint4& b, unsigned s) {
+    uint32_t w0 = a.x, w1 = a.y, w2 = a.z, w3 = a.w, w4 = b.x, w5 = b.y, w6 = b.z, w7 = b.w;
+    if (s & 4) { w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; w5 = w6; w6 = w7; }
+    if (s & 8) { w0 = w2; w1 = w3; w2 = w4; w3 = w5; w4 = w6; }
+    const unsigned bs = (s & 3) * 8;
+    uint4 r;
+    r.x = __funnelshift_r(w0, w1, bs);
+    r.y = __funnelshift_r(w1, w2, bs);
+    r.z = __funnelshift_r(w2, w3, bs);
+    r.w = __funnelshift_r(w3, w4, bs);
+    return r;
+}
+
+// Load the 16 bytes at p (any alignment).  Bytes outside [lo, hi) read as zero and are never
+// touched in memory.  Fast path: two aligned 16-byte loads + funnel; edges: byte loads.
+__device__ __forceinline__ uint4 load16_bounded(const uint8_t* p, const uint8_t* lo, const uint8_t* hi) {
+    const unsigned s = (unsigned)((uintptr_t)p & 15);
+    const uint8_t* a = p - s;
+    if (a >= lo && a + 32 <= hi) {
+        uint4 v0 = ldg128(a);
+        uint4 v1 = ldg128(a + 16);
+        return funnel16(v0, v1, s);
+    }
+    if (s == 0 && p >= lo && p + 16 <= hi) return ldg128(p);
+    uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const uint8_t* q = p + i;
+        uint32_t b = (q >= lo && q < hi) ? (uint32_t)__ldg(q) : 0u;
+        w[i >> 2] |= b << (8 * (i & 3));
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+__device__ __forceinline__ uint32_t word_of(const uint4& v, int i) {
+    return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w;
+}
+
+// Store bytes [from, to) of the 16-byte block v to dst + from .. (byte stores; edges only).
+__device__ __forceinline__ void store_bytes(uint8_t* dst, const uint4& v, int from, int to) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        if (i >= from && i < to) dst[i] = (uint8_t)(word_of(v, i >> 2) >> (8 * (i & 3)));
+    }
+}
+
+// Warp-cooperative copy of len bytes, any alignment on either side.  All 32 lanes must call.
+__device__ __forceinline__ void warp_copy_bytes(uint8_t* dst, const uint8_t* src, u64 len, int lane) {
+    if (len < 64) {
+        for (u64 i = lane; i < len; i += 32) dst[i] = __ldg(src + i);
+        return;
+    }
+    const unsigned head = (unsigned)((16 - ((uintptr_t)dst & 15)) & 15);
+    if ((unsigned)lane < head) dst[lane] = __ldg(src + lane);
+    uint8_t* d2 = dst + head;
+    const uint8_t* s2 = src + head;
+    const u64 rem = len - head;
+    u64 nvec = rem >> 4;
+    const unsigned s = (unsigned)((uintptr_t)s2 & 15);
+    const uint8_t* sa = s2 - s;
+    if (s) {
+        // the second aligned source vector of the last few destination vectors may run past the
+        // end of the source: leave those to the byte tail
+        const uint8_t* send = src + len;
+        u64 safe = (send >= sa + 32) ? (u64)((send - (sa + 32)) >> 4) + 1 : 0;
+        if (nvec > safe) nvec = safe;
+    }
+    // Each aligned source vector is loaded exactly once: lane l holds vector base+l, gets its right
+    // neighbour by shuffle, and the prefetched next group supplies lane 31's neighbour.
+    const u64 nsrc = nvec + (s ? 1 : 0);
+    const uint4 zero = make_uint4(0, 0, 0, 0);
+    uint4 cur = ((u64)lane < nsrc && nvec) ? ldg128_stream(sa + 16 * (u64)lane) : zero;
+    for (u64 base = 0; base < nvec; base += 32) {
+        const u64 vn = base + 32 + lane;
+        uint4 nxt = (vn < nsrc) ? ldg128_stream(sa + 16 * vn) : zero;
+        uint4 out = cur;
+        if (s) {
+            uint4 nb, n0;
+            nb.x = __shfl_down_sync(0xffffffffu, cur.x, 1); n0.x = __shfl_sync(0xffffffffu, nxt.x, 0);
+            nb.y = __shfl_down_sync(0xffffffffu, cur.y, 1); n0.y = __shfl_sync(0xffffffffu, nxt.y, 0);
+            nb.z = __shfl_down_sync(0xffffffffu, cur.z, 1); n0.z = __shfl_sync(0xffffffffu, nxt.z, 0);
+            nb.w = __shfl_down_sync(0xffffffffu, cur.w, 1); n0.w = __shfl_sync(0xffffffffu, nxt.w, 0);
+            if (lane == 31) nb = n0;
+            out = funnel16(cur, nb, s);
+        }
+        if (base + lane < nvec) stg128(d2 + 16 * (base + lane), out);
+        cur = nxt;
+    }
+    for (u64 i = (nvec << 4) + lane; i < rem; i += 32) d2[i] = __ldg(s2 + i);
+}
+
+}  // namespace p2pt

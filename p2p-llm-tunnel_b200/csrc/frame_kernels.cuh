@@ -1,0 +1,418 @@
+// frame_kernels.cuh -- batched TunnelMessage encode / decode / demux for sm_100a.
+//
+// What the reference does one frame at a time:
+//   encode  /root/reference/tunnel/src/protocol.rs:148-154   [type u8][stream_id u32 BE][payload]
+//   decode  /root/reference/tunnel/src/protocol.rs:157-172   len<5 -> too short; tag set :103-118
+//   demux   /root/reference/tunnel/src/proxy.rs:118-153 (HashMap<u32,_> probe per frame) and
+//           /root/reference/tunnel/src/serve.rs:112-139 (ReqBody appended to a per-stream Vec<u8>)
+// All of it is HBM-bound byte work: the kernels move aligned 16-byte vectors (common.cuh), size
+// their grids in multiples of the SM count, and never touch a tensor core.
+#pragma once
+#include "common.cuh"
+#include "../../include/p2pt.h"
+
+namespace p2pt {
+
+// 256-bit membership mask of the 11 valid tags (protocol.rs:88-100): 1,2,3,4,10,11,12,20,21,22,99
+__device__ __forceinline__ bool msg_type_valid(uint32_t b) {
+    // bits 0..31: 1,2,3,4,10,11,12,20,21,22 ; bits 96..127: 99 -> bit 3 of word 3
+    const uint32_t w0 = (1u << 1) | (1u << 2) | (1u << 3) | (1u << 4) | (1u << 10) | (1u << 11) |
+                        (1u << 12) | (1u << 20) | (1u << 21) | (1u << 22);
+    if (b < 32) return (w0 >> b) & 1u;
+    return b == 99;
+}
+
+// ---- encode: one warp per frame ----------------------------------------------------------------
+__global__ void __launch_bounds__(256) frame_encode_kernel(
+    u64 n, const uint8_t* __restrict__ types, const uint32_t* __restrict__ sids,
+    const uint8_t* __restrict__ payload, const u64* __restrict__ pay_off,
+    uint8_t* __restrict__ out, const u64* __restrict__ out_off) {
+    const int lane = threadIdx.x & 31;
+    const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
+    for (u64 i = warp; i < n; i += nwarps) {
+        const u64 po = __ldg(pay_off + i), pe = __ldg(pay_off + i + 1);
+        uint8_t* o = out + __ldg(out_off + i);
+        if (lane < 5) {
+            const uint32_t sid = __ldg(sids + i);
+            uint32_t b = lane == 0 ? (uint32_t)__ldg(types + i) : (sid >> (8 * (4 - lane))) & 0xffu;
+            o[lane] = (uint8_t)b;
+        }
+        warp_copy_bytes(o + 5, payload + po, pe - po, lane);
+    }
+}
+
+// ---- decode: one thread per frame ----------------------------------------------------------------
+__global__ void __launch_bounds__(256) frame_decode_kernel(
+    u64 n, const uint8_t* __restrict__ in, const u64* __restrict__ in_off, p2pt_desc* __restrict__ desc) {
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const u64 o = __ldg(in_off + i), e = __ldg(in_off + i + 1);
+        const u64 len = e - o;
+        const uint8_t* f = in + o;
+        uint32_t type = 0, sid = 0, status, plen = 0;
+        u64 poff = o;
+        if (len < 5) {                                  // protocol.rs:158-160
+            status = P2PT_ST_TOO_SHORT;
+            if (len) type = __ldg(f);
+        } else {
+            type = __ldg(f);
+            if (!msg_type_valid(type)) {                // protocol.rs:161-163
+                status = P2PT_ST_UNKNOWN_TYPE;
+            } else {
+                status = P2PT_ST_OK;
+                sid = ((uint32_t)__ldg(f + 1) << 24) | ((uint32_t)__ldg(f + 2) << 16) |
+                      ((uint32_t)__ldg(f + 3) << 8) | (uint32_t)__ldg(f + 4);    // :165 get_u32 (BE)
+                poff = o + 5;
+                plen = (uint32_t)(len - 5);
+            }
+        }
+        // one 16-byte + one 8-byte store per descriptor
+        uint4 lo;
+        lo.x = (uint32_t)poff; lo.y = (uint32_t)(poff >> 32); lo.z = plen; lo.w = sid;
+        uint2 hi;
+        hi.x = type | (status << 8); hi.y = 0;
+        uint8_t* d = reinterpret_cast<uint8_t*>(desc + i);
+        *reinterpret_cast<uint2*>(d) = make_uint2(lo.x, lo.y);
+        *reinterpret_cast<uint2*>(d + 8) = make_uint2(lo.z, lo.w);
+        *reinterpret_cast<uint2*>(d + 16) = hi;
+    }
+}
+
+// ---- demux ----------------------------------------------------------------------------------------
+// Stable LSD radix sort of (key = stream_id, value = frame index) with a last pass on the "not
+// decodable" flag, so the status-OK frames end up first, grouped by stream_id ascending, arrival
+// order kept inside a stream.  Each pass = per-block digit histogram -> scan -> stable scatter with
+// warp match/ballot ranking.  A pass whose digit is the same for every key degenerates to a copy.
+//
+// Scratch layout (p2pt_frame_demux_scratch_bytes): two (key,idx) arrays for ping-pong, the
+// [digit][block] histogram matrix, and the block sums of the final (stream count, body bytes) scan.
+
+constexpr int kSortBlocks = 592;        // 4 x 148 SMs
+constexpr int kSortThreads = 256;
+constexpr int kRadix = 256;
+constexpr int kScanThreads = 1024;
+
+struct DemuxScratch {
+    uint2* pairs[2];       // (key, idx)
+    uint32_t* hist;        // kRadix * kSortBlocks
+    u64* blk_bytes;        // per scan block: body bytes
+    uint32_t* blk_heads;   // per scan block: stream heads
+    uint32_t* misc;        // [0] = number of valid frames m, [1] = or-mask, [2] = and-mask
+};
+
+__host__ __device__ inline u64 align256(u64 x) { return (x + 255) & ~(u64)255; }
+
+inline u64 demux_scan_blocks(u64 n) { return (n + kScanThreads - 1) / kScanThreads; }
+
+inline u64 demux_scratch_bytes(u64 n) {
+    u64 b = 0;
+    b += 2 * align256(n * sizeof(uint2));
+    b += align256((u64)kRadix * kSortBlocks * sizeof(uint32_t));
+    b += align256((demux_scan_blocks(n) + 1) * sizeof(u64));
+    b += align256((demux_scan_blocks(n) + 1) * sizeof(uint32_t));
+    b += 256;
+    return b;
+}
+
+inline DemuxScratch demux_carve(void* scratch, u64 n) {
+    uint8_t* p = (uint8_t*)scratch;
+    DemuxScratch s;
+    s.pairs[0] = (uint2*)p; p += align256(n * sizeof(uint2));
+    s.pairs[1] = (uint2*)p; p += align256(n * sizeof(uint2));
+    s.hist = (uint32_t*)p; p += align256((u64)kRadix * kSortBlocks * sizeof(uint32_t));
+    s.blk_bytes = (u64*)p; p += align256((demux_scan_blocks(n) + 1) * sizeof(u64));
+    s.blk_heads = (uint32_t*)p; p += align256((demux_scan_blocks(n) + 1) * sizeof(uint32_t));
+    s.misc = (uint32_t*)p;
+    return s;
+}
+
+// pass "4" sorts on the invalid flag; passes 0..3 on stream_id bytes
+__device__ __forceinline__ uint32_t demux_digit(const uint2& kv, int pass, const p2pt_desc* desc) {
+    if (pass < 4) return (kv.x >> (8 * pass)) & 0xffu;
+    return desc[kv.y].status != P2PT_ST_OK ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(256) demux_init_kernel(u64 n, const p2pt_desc* __restrict__ desc,
+                                                         uint2* __restrict__ pairs, uint32_t* __restrict__ misc) {
+    uint32_t vor = 0, vand = 0xffffffffu;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint32_t sid = desc[i].stream_id;
+        pairs[i] = make_uint2(sid, (uint32_t)i);
+        vor |= sid; vand &= sid;
+    }
+    vor = __reduce_or_sync(0xffffffffu, vor);
+    vand = __reduce_and_sync(0xffffffffu, vand);
+    if ((threadIdx.x & 31) == 0) { atomicOr(misc + 1, vor); atomicAnd(misc + 2, vand); }
+}
+
+__device__ __forceinline__ bool demux_pass_trivial(const uint32_t* misc, int pass) {
+    if (pass >= 4) return false;
+    return (((misc[1] ^ misc[2]) >> (8 * pass)) & 0xffu) == 0;
+}
+
+__device__ __forceinline__ void demux_tile(u64 n, u64& lo, u64& hi) {
+    const u64 per = (n + kSortBlocks - 1) / kSortBlocks;
+    const u64 per_r = (per + kSortThreads - 1) / kSortThreads * kSortThreads;
+    lo = (u64)blockIdx.x * per_r;
+    hi = lo + per_r;
+    if (lo > n) lo = n;
+    if (hi > n) hi = n;
+}
+
+__global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
+    u64 n, const uint2* __restrict__ src, const p2pt_desc* __restrict__ desc, int pass,
+    uint32_t* __restrict__ hist, const uint32_t* __restrict__ misc) {
+    if (demux_pass_trivial(misc, pass)) return;
+    __shared__ uint32_t h[kRadix];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    u64 lo, hi;
+    demux_tile(n, lo, hi);
+    for (u64 i = lo + threadIdx.x; i < hi; i += kSortThreads) {
+        const uint32_t d = demux_digit(src[i], pass, desc);
+        // warp-aggregated: one shared atomic per distinct digit in the warp
+        const uint32_t peers = __match_any_sync(__activemask(), d);
+        if ((__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&h[d], __popc(peers));
+    }
+    __syncthreads();
+    hist[(u64)threadIdx.x * kSortBlocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan of the digit-major [kRadix][kSortBlocks] matrix, one block of 1024 threads
+__global__ void __launch_bounds__(1024) demux_scan_hist_kernel(uint32_t* __restrict__ hist, int pass,
+                                                              uint32_t* __restrict__ misc) {
+    if (demux_pass_trivial(misc, pass)) return;
+    __shared__ uint32_t row_total[kRadix];
+    __shared__ uint32_t row_base[kRadix];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int r = warp; r < kRadix; r += 32) {
+        uint32_t* row = hist + (u64)r * kSortBlocks;
+        uint32_t carry = 0;
+        for (int b0 = 0; b0 < kSortBlocks; b0 += 32) {
+            const int b = b0 + lane;
+            uint32_t v = b < kSortBlocks ? row[b] : 0;
+            uint32_t incl = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            if (b < kSortBlocks) row[b] = carry + incl - v;
+            carry += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (lane == 0) row_total[r] = carry;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t carry = 0;
+        for (int r0 = 0; r0 < kRadix; r0 += 32) {
+            uint32_t v = row_total[r0 + lane], incl = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            row_base[r0 + lane] = carry + incl - v;
+            carry += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (pass == 4 && lane == 0) misc[0] = row_total[0];   // number of decodable frames
+    }
+    __syncthreads();
+    for (int r = warp; r < kRadix; r += 32) {
+        uint32_t* row = hist + (u64)r * kSortBlocks;
+        const uint32_t base = row_base[r];
+        for (int b = lane; b < kSortBlocks; b += 32) row[b] += base;
+    }
+}
+
+__global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
+    u64 n, const uint2* __restrict__ src, uint2* __restrict__ dst, const p2pt_desc* __restrict__ desc,
+    int pass, const uint32_t* __restrict__ hist, const uint32_t* __restrict__ misc) {
+    u64 lo, hi;
+    demux_tile(n, lo, hi);
+    if (demux_pass_trivial(misc, pass)) {
+        for (u64 i = lo + threadIdx.x; i < hi; i += kSortThreads) dst[i] = src[i];
+        return;
+    }
+    constexpr int W = kSortThreads / 32;
+    __shared__ uint32_t base[kRadix];          // running output position per digit for this block
+    __shared__ uint32_t wcount[W][kRadix];     // per-warp digit counts of the current chunk
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    base[threadIdx.x] = hist[(u64)threadIdx.x * kSortBlocks + blockIdx.x];
+    for (u64 c0 = lo; c0 < hi; c0 += kSortThreads) {
+#pragma unroll
+        for (int w = 0; w < W; w++) wcount[w][threadIdx.x] = 0;
+        __syncthreads();
+        const u64 i = c0 + threadIdx.x;
+        const bool live = i < hi;
+        uint2 kv = make_uint2(0, 0);
+        uint32_t d = 0, rank = 0;
+        if (live) {
+            kv = src[i];
+            d = demux_digit(kv, pass, desc);
+        }
+        // rank among equal digits inside the warp, in lane (= arrival) order
+        const uint32_t act = __ballot_sync(0xffffffffu, live);
+        if (live) {
+            const uint32_t peers = __match_any_sync(act, d);
+            rank = __popc(peers & ((1u << lane) - 1));
+            if (rank == 0) wcount[warp][d] = __popc(peers);
+        }
+        __syncthreads();
+        // exclusive prefix over warps for this thread's digit column, then advance the block base
+        {
+            uint32_t run = 0;
+            const int col = threadIdx.x;
+#pragma unroll
+            for (int w = 0; w < W; w++) { uint32_t t = wcount[w][col]; wcount[w][col] = run; run += t; }
+            // keep the chunk total in a register until every thread has read its offsets
+            __syncthreads();
+            if (live) dst[base[d] + wcount[warp][d] + rank] = kv;
+            __syncthreads();
+            base[col] += run;
+        }
+        __syncthreads();
+    }
+}
+
+// After the sort: flag stream heads, and scan (heads, body bytes) over the m decodable frames.
+struct HeadBytes { uint32_t heads; u64 bytes; };
+
+__device__ __forceinline__ HeadBytes demux_item(u64 j, u64 m, const uint2* sorted, const p2pt_desc* desc) {
+    HeadBytes r; r.heads = 0; r.bytes = 0;
+    if (j < m) {
+        const uint2 kv = sorted[j];
+        r.heads = (j == 0 || sorted[j - 1].x != kv.x) ? 1u : 0u;
+        const p2pt_desc d = desc[kv.y];
+        r.bytes = (d.msg_type == 11 || d.msg_type == 21) ? (u64)d.pay_len : 0;   // ReqBody / ResBody
+    }
+    return r;
+}
+
+__device__ __forceinline__ HeadBytes block_scan_excl(HeadBytes v, HeadBytes& total) {
+    __shared__ uint32_t sh[32];
+    __shared__ u64 sb[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t ih = v.heads; u64 ib = v.bytes;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t th = __shfl_up_sync(0xffffffffu, ih, o);
+        u64 tb = __shfl_up_sync(0xffffffffu, ib, o);
+        if (lane >= o) { ih += th; ib += tb; }
+    }
+    if (lane == 31) { sh[warp] = ih; sb[warp] = ib; }
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t wh = sh[lane]; u64 wb = sb[lane];
+        uint32_t xh = wh; u64 xb = wb;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t th = __shfl_up_sync(0xffffffffu, xh, o);
+            u64 tb = __shfl_up_sync(0xffffffffu, xb, o);
+            if (lane >= o) { xh += th; xb += tb; }
+        }
+        sh[lane] = xh - wh; sb[lane] = xb - wb;
+        if (lane == 31) { total.heads = xh; total.bytes = xb; }
+    }
+    __syncthreads();
+    HeadBytes r;
+    r.heads = sh[warp] + ih - v.heads;
+    r.bytes = sb[warp] + ib - v.bytes;
+    // broadcast total from warp 0 lane 31 through shared memory
+    __shared__ uint32_t th_; __shared__ u64 tb_;
+    if (threadIdx.x == 31) { th_ = total.heads; tb_ = total.bytes; }
+    __syncthreads();
+    total.heads = th_; total.bytes = tb_;
+    return r;
+}
+
+__global__ void __launch_bounds__(kScanThreads) demux_blocksum_kernel(
+    u64 n, const uint2* __restrict__ sorted, const p2pt_desc* __restrict__ desc,
+    const uint32_t* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes) {
+    const u64 m = misc[0];
+    const u64 j = (u64)blockIdx.x * kScanThreads + threadIdx.x;
+    HeadBytes tot;
+    (void)block_scan_excl(demux_item(j, m, sorted, desc), tot);
+    if (threadIdx.x == 0) { blk_heads[blockIdx.x] = tot.heads; blk_bytes[blockIdx.x] = tot.bytes; }
+}
+
+// single block: exclusive scan of the per-block sums, in place; element [nblk] receives the total
+__global__ void __launch_bounds__(kScanThreads) demux_scan_blocksums_kernel(
+    u64 nblk, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes) {
+    __shared__ uint32_t carry_h; __shared__ u64 carry_b;
+    if (threadIdx.x == 0) { carry_h = 0; carry_b = 0; }
+    __syncthreads();
+    for (u64 b0 = 0; b0 < nblk; b0 += kScanThreads) {
+        const u64 b = b0 + threadIdx.x;
+        HeadBytes v; v.heads = b < nblk ? blk_heads[b] : 0; v.bytes = b < nblk ? blk_bytes[b] : 0;
+        HeadBytes tot;
+        HeadBytes ex = block_scan_excl(v, tot);
+        const uint32_t ch = carry_h; const u64 cb = carry_b;
+        if (b < nblk) { blk_heads[b] = ch + ex.heads; blk_bytes[b] = cb + ex.bytes; }
+        __syncthreads();
+        if (threadIdx.x == 0) { carry_h = ch + tot.heads; carry_b = cb + tot.bytes; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { blk_heads[nblk] = carry_h; blk_bytes[nblk] = carry_b; }
+}
+
+// Emit perm / uniq_sid / csr / gathered_off and per-frame gather destinations.
+// dst_off[j] (in scratch, reusing the other pair buffer as u64) = byte offset of frame perm[j] in gathered.
+__global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
+    u64 n, const uint2* __restrict__ sorted, const p2pt_desc* __restrict__ desc,
+    const uint32_t* __restrict__ misc, const uint32_t* __restrict__ blk_heads, const u64* __restrict__ blk_bytes,
+    u64 nblk, uint32_t max_streams, uint32_t* __restrict__ uniq_sid, u64* __restrict__ csr,
+    uint32_t* __restrict__ perm, uint32_t* __restrict__ k_out, u64* __restrict__ gathered_off,
+    u64* __restrict__ dst_off) {
+    const u64 m = misc[0];
+    const u64 j = (u64)blockIdx.x * kScanThreads + threadIdx.x;
+    HeadBytes it = demux_item(j, m, sorted, desc);
+    HeadBytes tot;
+    HeadBytes ex = block_scan_excl(it, tot);
+    const uint32_t hbase = blk_heads[blockIdx.x];
+    const u64 bbase = blk_bytes[blockIdx.x];
+    if (j < m) {
+        const uint2 kv = sorted[j];
+        perm[j] = kv.y;
+        dst_off[j] = bbase + ex.bytes;
+        if (it.heads) {
+            const uint32_t k = hbase + ex.heads;
+            if (k < max_streams) {
+                uniq_sid[k] = kv.x;
+                csr[k] = j;
+                if (gathered_off) gathered_off[k] = bbase + ex.bytes;
+            }
+        }
+    }
+    if (j == 0) {
+        const uint32_t k = blk_heads[nblk];
+        *k_out = k;
+        if (k <= max_streams) {          // csr / gathered_off hold max_streams + 1 entries
+            csr[k] = m;
+            if (gathered_off) gathered_off[k] = blk_bytes[nblk];
+        }
+    }
+}
+
+// Gather: one warp per decodable frame, body frames only (serve.rs:120-124 extend_from_slice).
+__global__ void __launch_bounds__(256) demux_gather_kernel(
+    const uint32_t* __restrict__ misc, const uint32_t* __restrict__ perm, const u64* __restrict__ dst_off,
+    const p2pt_desc* __restrict__ desc, const uint8_t* __restrict__ in,
+    uint8_t* __restrict__ gathered, u64 gathered_cap, const uint32_t* __restrict__ k_out, uint32_t max_streams) {
+    const u64 m = misc[0];
+    if (*k_out > max_streams) return;
+    const int lane = threadIdx.x & 31;
+    const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
+    for (u64 j = warp; j < m; j += nwarps) {
+        const p2pt_desc d = desc[perm[j]];
+        if (!(d.msg_type == 11 || d.msg_type == 21) || d.pay_len == 0) continue;
+        const u64 o = dst_off[j];
+        if (o + d.pay_len > gathered_cap) continue;      // caller sees the overflow via gathered_off[k]
+        warp_copy_bytes(gathered + o, in + d.pay_off, d.pay_len, lane);
+    }
+}
+
+}  // namespace p2pt

@@ -1,0 +1,109 @@
+// gcm_math.cuh -- GF(2^128) arithmetic for GHASH without a carry-less multiply instruction.
+//
+// Everything here is __host__ __device__ so that the exact device arithmetic can be unit-tested on
+// the CPU (tests/test_gcm_math_host.py builds a tiny host harness around this header and compares
+// it with the oracle's SP 800-38D bitwise multiply).  It is NOT a CPU fallback: the library only
+// calls it from kernels.
+//
+// Representation ("reflected integer"): a 16-byte GHASH block is read as a big-endian 128-bit
+// integer X; w[3] holds bytes 0..3, w[0] bytes 12..15.  GHASH's coefficient of alpha^i is integer
+// bit 127-i.  In that domain the field product is  reduce((X (x) Y) << 1)  with (x) a plain
+// carry-less integer multiply (the layout used by every CLMUL implementation of GHASH, e.g.
+// ghash 0.5.1 / polyval 0.6.2 behind aes-gcm 0.10.3, /root/reference/tunnel/Cargo.lock:27-29,810,1542).
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define P2PT_HD __host__ __device__ __forceinline__
+#else
+#define P2PT_HD inline
+#endif
+
+namespace p2pt {
+
+struct U128 { uint32_t w[4]; };   // w[0] = least-significant 32 bits of the BE integer
+
+// Multiplier prepared once per (session, power): the 9 Karatsuba operands of Y, each split into
+// the four "bit i mod 4" classes used by the integer-multiply-with-holes carry-less product.
+struct GhashKey { uint32_t m[9][4]; };
+
+P2PT_HD void ghash_key_prepare(const U128& y, GhashKey& k) {
+    uint32_t o[9];
+    o[0] = y.w[0]; o[1] = y.w[1]; o[2] = y.w[0] ^ y.w[1];
+    o[3] = y.w[2]; o[4] = y.w[3]; o[5] = y.w[2] ^ y.w[3];
+    o[6] = y.w[0] ^ y.w[2]; o[7] = y.w[1] ^ y.w[3]; o[8] = o[6] ^ o[7];
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        k.m[i][0] = o[i] & 0x11111111u;
+        k.m[i][1] = o[i] & 0x22222222u;
+        k.m[i][2] = o[i] & 0x44444444u;
+        k.m[i][3] = o[i] & 0x88888888u;
+    }
+}
+
+// 32x32 -> 64 carry-less multiply from 16 integer multiplies.  Each operand class keeps every 4th
+// bit, so a product column sums at most 8 partial bits and never carries into the next kept
+// column (4 bits away); the kept column's low bit is the XOR we want.
+P2PT_HD uint64_t clmul32(uint32_t a, const uint32_t b[4]) {
+    const uint32_t a0 = a & 0x11111111u, a1 = a & 0x22222222u, a2 = a & 0x44444444u, a3 = a & 0x88888888u;
+    uint64_t z0 = ((uint64_t)a0 * b[0]) ^ ((uint64_t)a1 * b[3]) ^ ((uint64_t)a2 * b[2]) ^ ((uint64_t)a3 * b[1]);
+    uint64_t z1 = ((uint64_t)a0 * b[1]) ^ ((uint64_t)a1 * b[0]) ^ ((uint64_t)a2 * b[3]) ^ ((uint64_t)a3 * b[2]);
+    uint64_t z2 = ((uint64_t)a0 * b[2]) ^ ((uint64_t)a1 * b[1]) ^ ((uint64_t)a2 * b[0]) ^ ((uint64_t)a3 * b[3]);
+    uint64_t z3 = ((uint64_t)a0 * b[3]) ^ ((uint64_t)a1 * b[2]) ^ ((uint64_t)a2 * b[1]) ^ ((uint64_t)a3 * b[0]);
+    return (z0 & 0x1111111111111111ull) | (z1 & 0x2222222222222222ull) |
+           (z2 & 0x4444444444444444ull) | (z3 & 0x8888888888888888ull);
+}
+
+// 64x64 -> 128 Karatsuba from three clmul32; operands (lo, hi, lo^hi) and key rows (r, r+1, r+2).
+P2PT_HD void clmul64(uint32_t lo, uint32_t hi, uint32_t mid, const GhashKey& k, int r,
+                     uint64_t& out_lo, uint64_t& out_hi) {
+    uint64_t p = clmul32(lo, k.m[r]);
+    uint64_t q = clmul32(hi, k.m[r + 1]);
+    uint64_t m = clmul32(mid, k.m[r + 2]) ^ p ^ q;
+    out_lo = p ^ (m << 32);
+    out_hi = q ^ (m >> 32);
+}
+
+// Z = X * Y in GF(2^128) (GHASH convention), Y given prepared.
+P2PT_HD U128 gf128_mul(const U128& x, const GhashKey& k) {
+    const uint32_t x0 = x.w[0], x1 = x.w[1], x2 = x.w[2], x3 = x.w[3];
+    uint64_t pl, ph, ql, qh, rl, rh;
+    clmul64(x0, x1, x0 ^ x1, k, 0, pl, ph);                           // low  half x low  half
+    clmul64(x2, x3, x2 ^ x3, k, 3, ql, qh);                           // high half x high half
+    clmul64(x0 ^ x2, x1 ^ x3, x0 ^ x1 ^ x2 ^ x3, k, 6, rl, rh);       // (lo^hi) x (lo^hi)
+    rl ^= pl ^ ql;
+    rh ^= ph ^ qh;
+    // 256-bit carry-less product v3:v2:v1:v0
+    uint64_t v0 = pl, v1 = ph ^ rl, v2 = ql ^ rh, v3 = qh;
+    // reflected domain: the field product is the integer product shifted left by one bit
+    v3 = (v3 << 1) | (v2 >> 63);
+    v2 = (v2 << 1) | (v1 >> 63);
+    v1 = (v1 << 1) | (v0 >> 63);
+    v0 = (v0 << 1);
+    // fold the low 128 bits with x^128 = x^7 + x^2 + x + 1 (reflected: right shifts by 1, 2, 7)
+    v2 ^= v0 ^ (v0 >> 1) ^ (v0 >> 2) ^ (v0 >> 7);
+    v1 ^= (v0 << 63) ^ (v0 << 62) ^ (v0 << 57);
+    v3 ^= v1 ^ (v1 >> 1) ^ (v1 >> 2) ^ (v1 >> 7);
+    v2 ^= (v1 << 63) ^ (v1 << 62) ^ (v1 << 57);
+    U128 z;
+    z.w[0] = (uint32_t)v2; z.w[1] = (uint32_t)(v2 >> 32);
+    z.w[2] = (uint32_t)v3; z.w[3] = (uint32_t)(v3 >> 32);
+    return z;
+}
+
+P2PT_HD uint32_t bswap32(uint32_t v) {
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(v, 0, 0x0123);
+#else
+    return (v >> 24) | ((v >> 8) & 0xff00u) | ((v << 8) & 0xff0000u) | (v << 24);
+#endif
+}
+
+// 16 bytes held as four little-endian words (memory order) -> reflected integer, and back.
+P2PT_HD U128 block_to_u128(uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3) {
+    U128 r;
+    r.w[3] = bswap32(b0); r.w[2] = bswap32(b1); r.w[1] = bswap32(b2); r.w[0] = bswap32(b3);
+    return r;
+}
+
+}  // namespace p2pt

@@ -1,0 +1,753 @@
+// p2pt.cu -- the C ABI of libp2ptunnel_b200.so (include/p2pt.h): context, staging, launches.
+//
+// No CPU fallback lives here: every entry point either launches the sm_100a kernels or fails with
+// an error code.  Host-pointer entry points stage through a per-context device arena and a small
+// ring of streams so that host->device copies, kernels and device->host copies of successive
+// chunks overlap (PCIe Gen5 is what bounds these calls).
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <atomic>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/p2pt.h"
+#include "frame_kernels.cuh"
+#include "gcm_kernels.cuh"
+
+using namespace p2pt;
+
+static_assert(sizeof(p2pt_desc) == 24, "p2pt_desc must be 24 bytes");
+
+namespace {
+
+constexpr int kStreams = 4;
+
+struct Arena {
+    uint8_t* base = nullptr;
+    size_t cap = 0;
+    size_t used = 0;
+};
+
+}  // namespace
+
+struct p2pt_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t streams[kStreams] = {};
+    cudaEvent_t events[kStreams] = {};
+    std::mutex mu;                 // serialises host-pointer calls (they share the arena)
+    std::mutex err_mu;
+    std::string err;
+    SessionKey* keys_local = nullptr;
+    SessionKey* keys_remote = nullptr;
+    uint32_t n_sessions = 0;
+    Arena arena;
+    std::atomic<uint64_t> launches{0};
+    uint32_t lut_slack = 0;        // bytes needed in front of the T-tables to reach 64 KiB alignment
+    int gcm_g = 0;                 // forced group width (env P2PT_GCM_G), 0 = heuristic
+};
+
+static std::string g_create_err;
+static std::mutex g_create_mu;
+
+static int32_t set_err(p2pt_ctx* ctx, int32_t code, const std::string& msg) {
+    if (ctx) {
+        std::lock_guard<std::mutex> g(ctx->err_mu);
+        ctx->err = msg;
+    } else {
+        std::lock_guard<std::mutex> g(g_create_mu);
+        g_create_err = msg;
+    }
+    return code;
+}
+
+#define CUDA_TRY(ctx, expr)                                                                     \
+    do {                                                                                        \
+        cudaError_t e__ = (expr);                                                               \
+        if (e__ != cudaSuccess)                                                                 \
+            return set_err(ctx, P2PT_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__)); \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+// ---- Te0 table, computed from the S-box definition (FIPS-197 5.1.1) on the host ---------------------
+static uint8_t gf8_mul_h(uint8_t a, uint8_t b) {
+    uint8_t p = 0;
+    while (b) {
+        if (b & 1) p ^= a;
+        a = (uint8_t)((a << 1) ^ ((a & 0x80) ? 0x1b : 0));
+        b >>= 1;
+    }
+    return p;
+}
+static void build_te0(uint32_t te0[256]) {
+    // inverse via a^254, then the affine map
+    for (int x = 0; x < 256; x++) {
+        uint8_t inv = 0;
+        if (x) {
+            uint8_t r = 1, b = (uint8_t)x;
+            int e = 254;
+            while (e) { if (e & 1) r = gf8_mul_h(r, b); b = gf8_mul_h(b, b); e >>= 1; }
+            inv = r;
+        }
+        uint8_t s = inv ^ (uint8_t)((inv << 1) | (inv >> 7)) ^ (uint8_t)((inv << 2) | (inv >> 6)) ^
+                    (uint8_t)((inv << 3) | (inv >> 5)) ^ (uint8_t)((inv << 4) | (inv >> 4)) ^ 0x63;
+        uint8_t s2 = gf8_mul_h(s, 2), s3 = (uint8_t)(s2 ^ s);
+        te0[x] = (uint32_t)s2 | ((uint32_t)s << 8) | ((uint32_t)s << 16) | ((uint32_t)s3 << 24);
+    }
+}
+
+__global__ void smem_base_probe_kernel(uint32_t* out) {
+    extern __shared__ __align__(16) uint8_t dyn_smem[];
+    *out = shared_addr(dyn_smem);
+}
+
+// ---- arena -----------------------------------------------------------------------------------------
+static int32_t arena_reserve(p2pt_ctx* ctx, size_t bytes) {
+    ctx->arena.used = 0;
+    if (bytes <= ctx->arena.cap) return P2PT_OK;
+    if (ctx->arena.base) cudaFree(ctx->arena.base);
+    ctx->arena.base = nullptr;
+    ctx->arena.cap = 0;
+    size_t want = bytes + bytes / 8 + (1u << 20);
+    CUDA_TRY(ctx, cudaMalloc(&ctx->arena.base, want));
+    ctx->arena.cap = want;
+    return P2PT_OK;
+}
+template <class T>
+static T* arena_take(p2pt_ctx* ctx, size_t count) {
+    size_t bytes = (count * sizeof(T) + 255) & ~(size_t)255;
+    T* p = reinterpret_cast<T*>(ctx->arena.base + ctx->arena.used);
+    ctx->arena.used += bytes;
+    return p;
+}
+static size_t pad256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+// ---- launch helpers --------------------------------------------------------------------------------
+static inline void count_launch(p2pt_ctx* ctx, int k = 1) { ctx->launches.fetch_add((uint64_t)k, std::memory_order_relaxed); }
+
+static int pick_group(p2pt_ctx* ctx, uint64_t n, uint64_t body_bytes) {
+    if (ctx->gcm_g) return ctx->gcm_g;
+    const uint64_t avg = n ? body_bytes / n : 0;
+    const uint64_t slots = (avg + 15) / 16 + 2;
+    if (slots <= 6) return 4;
+    return 8;
+}
+
+template <int MODE>
+static int32_t launch_gcm(p2pt_ctx* ctx, const GcmArgs& a, int G, cudaStream_t st) {
+    if (a.n == 0) return P2PT_OK;
+    const uint32_t smem = kLutBytes + ctx->lut_slack;
+    const uint64_t groups_per_cta = kGcmThreads / G;
+    uint64_t grid = (a.n + groups_per_cta - 1) / groups_per_cta;
+    if (grid > (uint64_t)ctx->sm_count) grid = ctx->sm_count;      // persistent: one CTA per SM
+#define P2PT_LAUNCH_G(GG)                                                                              \
+    case GG: {                                                                                         \
+        static std::atomic<int> configured[16];                                                        \
+        if (!configured[ctx->device & 15].load()) {                                                    \
+            CUDA_TRY(ctx, cudaFuncSetAttribute(gcm_record_kernel<GG, MODE>,                            \
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            configured[ctx->device & 15].store(1);                                                     \
+        }                                                                                              \
+        gcm_record_kernel<GG, MODE><<<(unsigned)grid, kGcmThreads, smem, st>>>(a);                     \
+        break;                                                                                         \
+    }
+    switch (G) {
+        P2PT_LAUNCH_G(4)
+        P2PT_LAUNCH_G(8)
+        P2PT_LAUNCH_G(16)
+        P2PT_LAUNCH_G(32)
+        default: return set_err(ctx, P2PT_ERR_ARG, "group width must be 4, 8, 16 or 32");
+    }
+#undef P2PT_LAUNCH_G
+    count_launch(ctx);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+static unsigned grid_for(p2pt_ctx* ctx, uint64_t items, unsigned per_block, unsigned waves) {
+    uint64_t g = (items + per_block - 1) / per_block;
+    uint64_t cap = (uint64_t)ctx->sm_count * waves;
+    if (g > cap) g = cap;
+    if (g == 0) g = 1;
+    return (unsigned)g;
+}
+
+// ===================================================================================================
+extern "C" {
+
+int32_t p2pt_abi_version(void) { return P2PT_ABI_VERSION; }
+
+const char* p2pt_last_error(p2pt_ctx* ctx) {
+    if (ctx) {
+        std::lock_guard<std::mutex> g(ctx->err_mu);
+        static thread_local std::string copy;
+        copy = ctx->err;
+        return copy.c_str();
+    }
+    std::lock_guard<std::mutex> g(g_create_mu);
+    static thread_local std::string copy2;
+    copy2 = g_create_err;
+    return copy2.c_str();
+}
+
+int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
+    if (!out) return set_err(nullptr, P2PT_ERR_ARG, "out is null");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return set_err(nullptr, P2PT_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                                                   " (libp2ptunnel_b200 has no CPU fallback)");
+    if (device < 0 || device >= ndev) return set_err(nullptr, P2PT_ERR_ARG, "device index out of range");
+    DeviceGuard dg(device);
+    cudaDeviceProp prop;
+    CUDA_TRY(nullptr, cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return set_err(nullptr, P2PT_ERR_CUDA, "libp2ptunnel_b200 is built for sm_100a only");
+    p2pt_ctx* ctx = new p2pt_ctx();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    for (int i = 0; i < kStreams; i++) {
+        if (cudaStreamCreateWithFlags(&ctx->streams[i], cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ctx->events[i], cudaEventDisableTiming) != cudaSuccess) {
+            delete ctx;
+            return set_err(nullptr, P2PT_ERR_CUDA, "stream/event creation failed");
+        }
+    }
+    uint32_t te0[256];
+    build_te0(te0);
+    CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_te0, te0, sizeof te0));
+    // where does dynamic shared memory start?  The T-tables must sit on a 64 KiB boundary.
+    uint32_t* d_probe = nullptr;
+    CUDA_TRY(nullptr, cudaMalloc(&d_probe, 4));
+    smem_base_probe_kernel<<<1, 32, 16, ctx->streams[0]>>>(d_probe);
+    uint32_t sb = 0;
+    CUDA_TRY(nullptr, cudaMemcpyAsync(&sb, d_probe, 4, cudaMemcpyDeviceToHost, ctx->streams[0]));
+    CUDA_TRY(nullptr, cudaStreamSynchronize(ctx->streams[0]));
+    cudaFree(d_probe);
+    ctx->lut_slack = (0x10000u - (sb & 0xffffu)) & 0xffffu;
+    if (const char* g = getenv("P2PT_GCM_G")) {
+        int v = atoi(g);
+        if (v == 4 || v == 8 || v == 16 || v == 32) ctx->gcm_g = v;
+    }
+    *out = ctx;
+    return P2PT_OK;
+}
+
+int32_t p2pt_ctx_destroy(p2pt_ctx* ctx) {
+    if (!ctx) return P2PT_OK;
+    {
+        DeviceGuard dg(ctx->device);
+        cudaDeviceSynchronize();
+        for (int i = 0; i < kStreams; i++) {
+            if (ctx->streams[i]) cudaStreamDestroy(ctx->streams[i]);
+            if (ctx->events[i]) cudaEventDestroy(ctx->events[i]);
+        }
+        if (ctx->keys_local) cudaFree(ctx->keys_local);
+        if (ctx->keys_remote) cudaFree(ctx->keys_remote);
+        if (ctx->arena.base) cudaFree(ctx->arena.base);
+    }
+    delete ctx;
+    return P2PT_OK;
+}
+
+void* p2pt_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+    return p;
+}
+void p2pt_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+uint64_t p2pt_launch_count(p2pt_ctx* ctx) { return ctx ? ctx->launches.load() : 0; }
+
+int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
+    if (!ctx || !name) return P2PT_ERR_ARG;
+    if (strcmp(name, "gcm_group_width") == 0) {
+        if (!(value == 0 || value == 4 || value == 8 || value == 16 || value == 32))
+            return set_err(ctx, P2PT_ERR_ARG, "gcm_group_width must be 0, 4, 8, 16 or 32");
+        ctx->gcm_g = (int)value;
+        return P2PT_OK;
+    }
+    return set_err(ctx, P2PT_ERR_ARG, std::string("unknown option: ") + name);
+}
+
+// ---------------------------------------------------------------------------------------------------
+int32_t p2pt_sessions_load(p2pt_ctx* ctx, uint32_t n, const uint8_t* local_keys16, const uint8_t* local_ivs4,
+                           const uint8_t* remote_keys16, const uint8_t* remote_ivs4) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!n || !local_keys16 || !local_ivs4 || !remote_keys16 || !remote_ivs4)
+        return set_err(ctx, P2PT_ERR_ARG, "sessions_load: null key material or n == 0");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = ctx->streams[0];
+    if (ctx->keys_local) { cudaFree(ctx->keys_local); ctx->keys_local = nullptr; }
+    if (ctx->keys_remote) { cudaFree(ctx->keys_remote); ctx->keys_remote = nullptr; }
+    ctx->n_sessions = 0;
+    CUDA_TRY(ctx, cudaMalloc(&ctx->keys_local, (size_t)n * sizeof(SessionKey)));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->keys_remote, (size_t)n * sizeof(SessionKey)));
+    uint8_t *dk = nullptr, *di = nullptr;
+    CUDA_TRY(ctx, cudaMalloc(&dk, (size_t)n * 16));
+    CUDA_TRY(ctx, cudaMalloc(&di, (size_t)n * 4));
+    for (int dir = 0; dir < 2; dir++) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(dk, dir ? remote_keys16 : local_keys16, (size_t)n * 16, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(di, dir ? remote_ivs4 : local_ivs4, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+        session_expand_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, dk, di, dir ? ctx->keys_remote : ctx->keys_local);
+        count_launch(ctx);
+        CUDA_TRY(ctx, cudaGetLastError());
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    }
+    cudaFree(dk);
+    cudaFree(di);
+    ctx->n_sessions = n;
+    return P2PT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// device-pointer entry points
+// ---------------------------------------------------------------------------------------------------
+int32_t p2pt_frame_encode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* types, const uint32_t* sids,
+                                       const uint8_t* payload, const uint64_t* pay_off,
+                                       uint8_t* out, const uint64_t* out_off, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!types || !sids || !pay_off || !out || !out_off) return set_err(ctx, P2PT_ERR_ARG, "frame_encode: null argument");
+    DeviceGuard dg(ctx->device);
+    frame_encode_kernel<<<grid_for(ctx, n, 8, 16), 256, 0, (cudaStream_t)stream>>>(
+        n, types, sids, payload, (const u64*)pay_off, out, (const u64*)out_off);
+    count_launch(ctx);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+int32_t p2pt_frame_decode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, const uint64_t* in_off,
+                                       p2pt_desc* desc, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!in_off || !desc) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: null argument");
+    DeviceGuard dg(ctx->device);
+    frame_decode_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, (cudaStream_t)stream>>>(n, in, (const u64*)in_off, desc);
+    count_launch(ctx);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+uint64_t p2pt_frame_demux_scratch_bytes(uint64_t n) { return demux_scratch_bytes(n ? n : 1); }
+
+int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint8_t* in,
+                                      uint32_t max_streams, uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+                                      uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
+                                      uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!uniq_sid || !csr || !perm || !k_out) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null output");
+    if (n > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: n must fit in 32 bits");
+    if (gathered && (!gathered_off || !in)) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: gather needs in and gathered_off");
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        CUDA_TRY(ctx, cudaMemsetAsync(k_out, 0, 4, st));
+        CUDA_TRY(ctx, cudaMemsetAsync(csr, 0, 8, st));
+        if (gathered_off) CUDA_TRY(ctx, cudaMemsetAsync(gathered_off, 0, 8, st));
+        return P2PT_OK;
+    }
+    if (!desc || !scratch) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null desc or scratch");
+    if (scratch_bytes < demux_scratch_bytes(n)) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: scratch too small");
+    if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: scratch must be 256-byte aligned");
+    DemuxScratch s = demux_carve(scratch, n);
+    CUDA_TRY(ctx, cudaMemsetAsync(s.misc, 0, 16, st));
+    demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, s.pairs[0], s.misc);
+    int cur = 0;
+    for (int pass = 0; pass < 5; pass++) {
+        demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.pairs[cur], desc, pass, s.hist, s.misc);
+        demux_scan_hist_kernel<<<1, 1024, 0, st>>>(s.hist, pass, s.misc);
+        demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.pairs[cur], s.pairs[cur ^ 1], desc, pass, s.hist, s.misc);
+        cur ^= 1;
+    }
+    const uint2* sorted = s.pairs[cur];
+    u64* dst_off = reinterpret_cast<u64*>(s.pairs[cur ^ 1]);
+    const u64 nblk = demux_scan_blocks(n);
+    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, sorted, desc, s.misc, s.blk_heads, s.blk_bytes);
+    demux_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, s.blk_heads, s.blk_bytes);
+    demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, sorted, desc, s.misc, s.blk_heads, s.blk_bytes, nblk,
+                                                              max_streams, uniq_sid, (u64*)csr, perm, k_out,
+                                                              (u64*)gathered_off, dst_off);
+    count_launch(ctx, 1 + 15 + 3);
+    if (gathered) {
+        demux_gather_kernel<<<grid_for(ctx, n, 8, 16), 256, 0, st>>>(s.misc, perm, dst_off, desc, in, gathered,
+                                                                    gathered_cap, k_out, max_streams);
+        count_launch(ctx);
+    }
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+static int32_t check_sessions(p2pt_ctx* ctx) {
+    if (!ctx->n_sessions) return set_err(ctx, P2PT_ERR_STATE, "no sessions loaded: call p2pt_sessions_load first");
+    return P2PT_OK;
+}
+
+int32_t p2pt_dtls_gcm_seal_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                        const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
+                                        uint8_t* rec, const uint64_t* rec_off, uint8_t* status, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !nonce8 || !raw || !raw_off || !rec || !rec_off || !status)
+        return set_err(ctx, P2PT_ERR_ARG, "dtls_gcm_seal: null argument");
+    if (int32_t r = check_sessions(ctx)) return r;
+    DeviceGuard dg(ctx->device);
+    GcmArgs a = {};
+    a.n = n; a.session = session; a.keys = ctx->keys_local; a.n_sessions = ctx->n_sessions;
+    a.nonce8 = nonce8; a.in = raw; a.in_off = (const u64*)raw_off; a.out = rec; a.out_off = (const u64*)rec_off;
+    a.status = status;
+    return launch_gcm<kSeal>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 8, (cudaStream_t)stream);
+}
+
+int32_t p2pt_dtls_gcm_open_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                        const uint8_t* rec, const uint64_t* rec_off,
+                                        uint8_t* out, const uint64_t* out_off,
+                                        uint32_t* out_len, uint8_t* status, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !rec || !rec_off || !out || !out_off || !out_len || !status)
+        return set_err(ctx, P2PT_ERR_ARG, "dtls_gcm_open: null argument");
+    if (int32_t r = check_sessions(ctx)) return r;
+    DeviceGuard dg(ctx->device);
+    GcmArgs a = {};
+    a.n = n; a.session = session; a.keys = ctx->keys_remote; a.n_sessions = ctx->n_sessions;
+    a.in = rec; a.in_off = (const u64*)rec_off; a.out = out; a.out_off = (const u64*)out_off;
+    a.status = status; a.out_len = out_len;
+    return launch_gcm<kOpen>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 8, (cudaStream_t)stream);
+}
+
+int32_t p2pt_pipeline_seal_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                  const uint16_t* epoch, const uint64_t* seq48, const uint8_t* nonce8,
+                                  const uint8_t* types, const uint32_t* sids,
+                                  const uint8_t* payload, const uint64_t* pay_off,
+                                  uint8_t* rec, const uint64_t* rec_off, uint8_t* status, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !epoch || !seq48 || !nonce8 || !types || !sids || !pay_off || !rec || !rec_off || !status)
+        return set_err(ctx, P2PT_ERR_ARG, "pipeline_seal: null argument");
+    if (int32_t r = check_sessions(ctx)) return r;
+    DeviceGuard dg(ctx->device);
+    GcmArgs a = {};
+    a.n = n; a.session = session; a.keys = ctx->keys_local; a.n_sessions = ctx->n_sessions;
+    a.nonce8 = nonce8; a.in = payload; a.in_off = (const u64*)pay_off; a.out = rec; a.out_off = (const u64*)rec_off;
+    a.status = status; a.epoch = epoch; a.seq48 = (const u64*)seq48; a.types = types; a.sids = sids;
+    return launch_gcm<kPipeSeal>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 8, (cudaStream_t)stream);
+}
+
+int32_t p2pt_pipeline_open_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                  const uint8_t* rec, const uint64_t* rec_off,
+                                  uint8_t* out, const uint64_t* out_off, p2pt_desc* desc, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !rec || !rec_off || !out || !out_off || !desc)
+        return set_err(ctx, P2PT_ERR_ARG, "pipeline_open: null argument");
+    if (int32_t r = check_sessions(ctx)) return r;
+    DeviceGuard dg(ctx->device);
+    GcmArgs a = {};
+    a.n = n; a.session = session; a.keys = ctx->keys_remote; a.n_sessions = ctx->n_sessions;
+    a.in = rec; a.in_off = (const u64*)rec_off; a.out = out; a.out_off = (const u64*)out_off;
+    a.desc = desc;
+    return launch_gcm<kPipeOpen>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 8, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host-pointer entry points: stage, run, fetch
+// ---------------------------------------------------------------------------------------------------
+static bool offsets_monotonic(const uint64_t* off, uint64_t n) {
+    for (uint64_t i = 0; i < n; i++)
+        if (off[i + 1] < off[i]) return false;
+    return true;
+}
+
+int32_t p2pt_frame_encode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* types, const uint32_t* sids,
+                                const uint8_t* payload, const uint64_t* pay_off,
+                                uint8_t* out, const uint64_t* out_off) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!types || !sids || !pay_off || !out || !out_off) return set_err(ctx, P2PT_ERR_ARG, "frame_encode: null argument");
+    if (!offsets_monotonic(pay_off, n) || !offsets_monotonic(out_off, n))
+        return set_err(ctx, P2PT_ERR_ARG, "frame_encode: offsets must be non-decreasing");
+    for (uint64_t i = 0; i < n; i++)
+        if (out_off[i + 1] - out_off[i] < 5 + (pay_off[i + 1] - pay_off[i]))
+            return set_err(ctx, P2PT_ERR_CAPACITY, "frame_encode: output slot smaller than 5 + payload");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = ctx->streams[0];
+    const size_t pbytes = pay_off[n] - pay_off[0], obytes = out_off[n] - out_off[0];
+    if (pbytes && !payload) return set_err(ctx, P2PT_ERR_ARG, "frame_encode: null payload");
+    if (int32_t r = arena_reserve(ctx, pad256(n) + pad256(4 * n) + 2 * pad256(8 * (n + 1)) + pad256(pbytes) + pad256(obytes) + 4096)) return r;
+    uint8_t* d_types = arena_take<uint8_t>(ctx, n);
+    uint32_t* d_sids = arena_take<uint32_t>(ctx, n);
+    uint64_t* d_po = arena_take<uint64_t>(ctx, n + 1);
+    uint64_t* d_oo = arena_take<uint64_t>(ctx, n + 1);
+    uint8_t* d_pay = arena_take<uint8_t>(ctx, pbytes + 1);
+    uint8_t* d_out = arena_take<uint8_t>(ctx, obytes + 1);
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_types, types, n, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_sids, sids, 4 * n, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_po, pay_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_oo, out_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
+    if (pbytes) CUDA_TRY(ctx, cudaMemcpyAsync(d_pay, payload + pay_off[0], pbytes, cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_frame_encode_batch_device(ctx, n, d_types, d_sids, d_pay - pay_off[0], d_po,
+                                                   d_out - out_off[0], d_oo, st)) return r;
+    // only the bytes the frames cover are defined; gaps between slots keep the caller's contents
+    bool dense = true;
+    for (uint64_t i = 0; i < n && dense; i++) dense = (out_off[i + 1] - out_off[i] == 5 + (pay_off[i + 1] - pay_off[i]));
+    if (dense) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(out + out_off[0], d_out, obytes, cudaMemcpyDeviceToHost, st));
+    } else {
+        for (uint64_t i = 0; i < n; i++) {
+            const size_t len = 5 + (pay_off[i + 1] - pay_off[i]);
+            CUDA_TRY(ctx, cudaMemcpyAsync(out + out_off[i], d_out + (out_off[i] - out_off[0]), len, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return P2PT_OK;
+}
+
+int32_t p2pt_frame_decode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, const uint64_t* in_off, p2pt_desc* desc) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!in_off || !desc) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: null argument");
+    if (!offsets_monotonic(in_off, n)) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: offsets must be non-decreasing");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = ctx->streams[0];
+    const size_t ibytes = in_off[n] - in_off[0];
+    if (ibytes && !in) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: null input");
+    if (int32_t r = arena_reserve(ctx, pad256(8 * (n + 1)) + pad256(ibytes) + pad256(24 * n) + 4096)) return r;
+    uint64_t* d_io = arena_take<uint64_t>(ctx, n + 1);
+    uint8_t* d_in = arena_take<uint8_t>(ctx, ibytes + 1);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_io, in_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
+    if (ibytes) CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in + in_off[0], ibytes, cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_frame_decode_batch_device(ctx, n, d_in - in_off[0], d_io, d_desc, st)) return r;
+    CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return P2PT_OK;
+}
+
+int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint8_t* in, uint64_t in_bytes,
+                               uint32_t max_streams, uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+                               uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!uniq_sid || !csr || !perm || !k_out) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null output");
+    if (n == 0) { *k_out = 0; csr[0] = 0; if (gathered_off) gathered_off[0] = 0; return P2PT_OK; }
+    if (!desc) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null desc");
+    if (gathered && (!in || !gathered_off)) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: gather needs in and gathered_off");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = ctx->streams[0];
+    const uint64_t sbytes = demux_scratch_bytes(n);
+    const size_t gcap = gathered ? (size_t)gathered_cap : 0;
+    const size_t ib = gathered ? (size_t)in_bytes : 0;
+    if (int32_t r = arena_reserve(ctx, pad256(24 * n) + pad256(ib) + pad256(4 * (size_t)max_streams) +
+                                           2 * pad256(8 * ((size_t)max_streams + 1)) + pad256(4 * n) + 256 +
+                                           pad256(gcap) + pad256(sbytes) + 8192)) return r;
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
+    uint8_t* d_in = arena_take<uint8_t>(ctx, ib + 1);
+    uint32_t* d_uniq = arena_take<uint32_t>(ctx, max_streams + 1);
+    uint64_t* d_csr = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
+    uint64_t* d_goff = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
+    uint32_t* d_perm = arena_take<uint32_t>(ctx, n);
+    uint32_t* d_k = arena_take<uint32_t>(ctx, 1);
+    uint8_t* d_g = arena_take<uint8_t>(ctx, gcap + 1);
+    uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_desc, desc, 24 * n, cudaMemcpyHostToDevice, st));
+    if (ib) CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in, ib, cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_frame_demux_batch_device(ctx, n, d_desc, d_in, max_streams, d_uniq, d_csr, d_perm, d_k,
+                                                  gathered ? d_g : nullptr, gathered_cap,
+                                                  gathered_off ? d_goff : nullptr, d_scratch, sbytes, st)) return r;
+    uint32_t k = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&k, d_k, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    *k_out = k;
+    if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: more streams than max_streams");
+    CUDA_TRY(ctx, cudaMemcpyAsync(uniq_sid, d_uniq, 4 * (size_t)k, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(csr, d_csr, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const uint64_t m = csr[k];
+    if (m) CUDA_TRY(ctx, cudaMemcpyAsync(perm, d_perm, 4 * m, cudaMemcpyDeviceToHost, st));
+    if (gathered_off) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(gathered_off, d_goff, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        if (gathered) {
+            if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: gathered_cap too small");
+            if (gathered_off[k]) CUDA_TRY(ctx, cudaMemcpyAsync(gathered, d_g, gathered_off[k], cudaMemcpyDeviceToHost, st));
+        }
+    }
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return P2PT_OK;
+}
+
+// Shared staging for the four record entry points.  Records are processed in chunks round-robin
+// over kStreams streams so copies and kernels of neighbouring chunks overlap.
+namespace {
+struct RecordCall {
+    int mode;
+    uint64_t n;
+    const uint32_t* session;
+    const uint8_t* nonce8;
+    const uint8_t* in; const uint64_t* in_off;
+    uint8_t* out; const uint64_t* out_off;
+    uint8_t* status; uint32_t* out_len;
+    const uint16_t* epoch; const uint64_t* seq48; const uint8_t* types; const uint32_t* sids;
+    p2pt_desc* desc;
+};
+}  // namespace
+
+static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* what) {
+    const uint64_t n = c.n;
+    if (!offsets_monotonic(c.in_off, n) || !offsets_monotonic(c.out_off, n))
+        return set_err(ctx, P2PT_ERR_ARG, std::string(what) + ": offsets must be non-decreasing");
+    const bool seal = (c.mode == kSeal || c.mode == kPipeSeal);
+    for (uint64_t i = 0; i < n; i++) {
+        const uint64_t il = c.in_off[i + 1] - c.in_off[i], ol = c.out_off[i + 1] - c.out_off[i];
+        uint64_t need = c.mode == kSeal ? il + 24 : c.mode == kPipeSeal ? il + 5 + 13 + 24 : il;
+        if (c.mode == kSeal && il < 13) need = 0;
+        if (ol < need) return set_err(ctx, P2PT_ERR_CAPACITY, std::string(what) + ": output slot too small");
+    }
+    if (int32_t r = check_sessions(ctx)) return r;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    const size_t ibytes = c.in_off[n] - c.in_off[0], obytes = c.out_off[n] - c.out_off[0];
+    if (int32_t r = arena_reserve(ctx, pad256(4 * n) + pad256(8 * n) + 2 * pad256(8 * (n + 1)) + pad256(ibytes) +
+                                           pad256(obytes) + pad256(n) + pad256(4 * n) + pad256(2 * n) + pad256(8 * n) +
+                                           pad256(n) + pad256(4 * n) + pad256(24 * n) + 16384)) return r;
+    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
+    uint8_t* d_nonce = arena_take<uint8_t>(ctx, 8 * n);
+    uint64_t* d_io = arena_take<uint64_t>(ctx, n + 1);
+    uint64_t* d_oo = arena_take<uint64_t>(ctx, n + 1);
+    uint8_t* d_in = arena_take<uint8_t>(ctx, ibytes + 1);
+    uint8_t* d_out = arena_take<uint8_t>(ctx, obytes + 1);
+    uint8_t* d_status = arena_take<uint8_t>(ctx, n);
+    uint32_t* d_olen = arena_take<uint32_t>(ctx, n);
+    uint16_t* d_epoch = arena_take<uint16_t>(ctx, n);
+    uint64_t* d_seq = arena_take<uint64_t>(ctx, n);
+    uint8_t* d_types = arena_take<uint8_t>(ctx, n);
+    uint32_t* d_sids = arena_take<uint32_t>(ctx, n);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
+
+    cudaStream_t s0 = ctx->streams[0];
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_io, c.in_off, 8 * (n + 1), cudaMemcpyHostToDevice, s0));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_oo, c.out_off, 8 * (n + 1), cudaMemcpyHostToDevice, s0));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, c.session, 4 * n, cudaMemcpyHostToDevice, s0));
+    if (seal) CUDA_TRY(ctx, cudaMemcpyAsync(d_nonce, c.nonce8, 8 * n, cudaMemcpyHostToDevice, s0));
+    if (c.mode == kPipeSeal) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_epoch, c.epoch, 2 * n, cudaMemcpyHostToDevice, s0));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_seq, c.seq48, 8 * n, cudaMemcpyHostToDevice, s0));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_types, c.types, n, cudaMemcpyHostToDevice, s0));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_sids, c.sids, 4 * n, cudaMemcpyHostToDevice, s0));
+    }
+    CUDA_TRY(ctx, cudaEventRecord(ctx->events[0], s0));
+
+    const int G = pick_group(ctx, n, ibytes);
+    // chunk so that each chunk moves ~16 MiB of input
+    uint64_t chunk = n;
+    if (ibytes > (32u << 20)) {
+        const uint64_t avg = ibytes / n + 1;
+        chunk = (16u << 20) / avg;
+        if (chunk < 1024) chunk = 1024;
+    }
+    int si = 0;
+    for (uint64_t r0 = 0; r0 < n; r0 += chunk, si = (si + 1) % kStreams) {
+        const uint64_t r1 = r0 + chunk < n ? r0 + chunk : n, m = r1 - r0;
+        cudaStream_t st = ctx->streams[si];
+        if (si != 0 || r0 == 0) CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[0], 0));
+        const size_t ib0 = c.in_off[r0] - c.in_off[0], ib1 = c.in_off[r1] - c.in_off[0];
+        const size_t ob0 = c.out_off[r0] - c.out_off[0], ob1 = c.out_off[r1] - c.out_off[0];
+        if (ib1 > ib0) CUDA_TRY(ctx, cudaMemcpyAsync(d_in + ib0, c.in + c.in_off[r0], ib1 - ib0, cudaMemcpyHostToDevice, st));
+        GcmArgs a = {};
+        a.n = m; a.session = d_sess + r0; a.n_sessions = ctx->n_sessions;
+        a.keys = seal ? ctx->keys_local : ctx->keys_remote;
+        a.nonce8 = d_nonce + 8 * r0;
+        a.in = d_in - c.in_off[0]; a.in_off = (const u64*)(d_io + r0);
+        a.out = d_out - c.out_off[0]; a.out_off = (const u64*)(d_oo + r0);
+        a.status = d_status + r0; a.out_len = d_olen + r0;
+        a.epoch = d_epoch + r0; a.seq48 = (const u64*)(d_seq + r0); a.types = d_types + r0; a.sids = d_sids + r0;
+        a.desc = d_desc + r0;
+        int32_t r;
+        switch (c.mode) {
+            case kSeal: r = launch_gcm<kSeal>(ctx, a, G, st); break;
+            case kOpen: r = launch_gcm<kOpen>(ctx, a, G, st); break;
+            case kPipeSeal: r = launch_gcm<kPipeSeal>(ctx, a, G, st); break;
+            default: r = launch_gcm<kPipeOpen>(ctx, a, G, st); break;
+        }
+        if (r) return r;
+        if (ob1 > ob0) CUDA_TRY(ctx, cudaMemcpyAsync(c.out + c.out_off[r0], d_out + ob0, ob1 - ob0, cudaMemcpyDeviceToHost, st));
+        if (c.status) CUDA_TRY(ctx, cudaMemcpyAsync(c.status + r0, d_status + r0, m, cudaMemcpyDeviceToHost, st));
+        if (c.mode == kOpen) CUDA_TRY(ctx, cudaMemcpyAsync(c.out_len + r0, d_olen + r0, 4 * m, cudaMemcpyDeviceToHost, st));
+        if (c.mode == kPipeOpen) CUDA_TRY(ctx, cudaMemcpyAsync(c.desc + r0, d_desc + r0, 24 * m, cudaMemcpyDeviceToHost, st));
+    }
+    for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->streams[i]));
+    // pipe-open descriptors are relative to the caller's `out`, which is how the kernel wrote them
+    return P2PT_OK;
+}
+
+int32_t p2pt_dtls_gcm_seal_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                 const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
+                                 uint8_t* rec, const uint64_t* rec_off, uint8_t* status) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !nonce8 || !raw || !raw_off || !rec || !rec_off || !status)
+        return set_err(ctx, P2PT_ERR_ARG, "dtls_gcm_seal: null argument");
+    RecordCall c = {};
+    c.mode = kSeal; c.n = n; c.session = session; c.nonce8 = nonce8; c.in = raw; c.in_off = raw_off;
+    c.out = rec; c.out_off = rec_off; c.status = status;
+    return run_record_call(ctx, c, "dtls_gcm_seal");
+}
+
+int32_t p2pt_dtls_gcm_open_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                 const uint8_t* rec, const uint64_t* rec_off,
+                                 uint8_t* out, const uint64_t* out_off, uint32_t* out_len, uint8_t* status) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !rec || !rec_off || !out || !out_off || !out_len || !status)
+        return set_err(ctx, P2PT_ERR_ARG, "dtls_gcm_open: null argument");
+    RecordCall c = {};
+    c.mode = kOpen; c.n = n; c.session = session; c.in = rec; c.in_off = rec_off;
+    c.out = out; c.out_off = out_off; c.status = status; c.out_len = out_len;
+    return run_record_call(ctx, c, "dtls_gcm_open");
+}
+
+int32_t p2pt_pipeline_seal(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                           const uint16_t* epoch, const uint64_t* seq48, const uint8_t* nonce8,
+                           const uint8_t* types, const uint32_t* sids,
+                           const uint8_t* payload, const uint64_t* pay_off,
+                           uint8_t* rec, const uint64_t* rec_off, uint8_t* status) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !epoch || !seq48 || !nonce8 || !types || !sids || !pay_off || !rec || !rec_off || !status)
+        return set_err(ctx, P2PT_ERR_ARG, "pipeline_seal: null argument");
+    if (pay_off[n] > pay_off[0] && !payload) return set_err(ctx, P2PT_ERR_ARG, "pipeline_seal: null payload");
+    RecordCall c = {};
+    c.mode = kPipeSeal; c.n = n; c.session = session; c.nonce8 = nonce8; c.in = payload; c.in_off = pay_off;
+    c.out = rec; c.out_off = rec_off; c.status = status;
+    c.epoch = epoch; c.seq48 = seq48; c.types = types; c.sids = sids;
+    return run_record_call(ctx, c, "pipeline_seal");
+}
+
+int32_t p2pt_pipeline_open(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                           const uint8_t* rec, const uint64_t* rec_off,
+                           uint8_t* out, const uint64_t* out_off, p2pt_desc* desc) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !rec || !rec_off || !out || !out_off || !desc)
+        return set_err(ctx, P2PT_ERR_ARG, "pipeline_open: null argument");
+    RecordCall c = {};
+    c.mode = kPipeOpen; c.n = n; c.session = session; c.in = rec; c.in_off = rec_off;
+    c.out = out; c.out_off = out_off; c.desc = desc;
+    return run_record_call(ctx, c, "pipeline_open");
+}
+
+}  // extern "C"

@@ -1,0 +1,121 @@
+"""ctypes view of oracle/liboracle.so (the CPU oracle).  Test infrastructure only."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_LIB = os.path.join(ORACLE_DIR, "liboracle.so")
+
+DESC_DTYPE = np.dtype([("pay_off", "<u8"), ("pay_len", "<u4"), ("stream_id", "<u4"),
+                       ("msg_type", "u1"), ("status", "u1"), ("pad", "u1", (6,))])
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        src = os.path.join(ORACLE_DIR, "p2pt_oracle.c")
+        if not os.path.exists(ORACLE_LIB) or os.path.getmtime(ORACLE_LIB) < os.path.getmtime(src):
+            subprocess.check_call(["gcc", "-O2", "-shared", "-fPIC", "-o", ORACLE_LIB, src])
+        _lib = C.CDLL(ORACLE_LIB)
+        _lib.orc_frame_demux_batch.restype = C.c_uint32
+    return _lib
+
+
+def _p(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else None
+
+
+def _u8(a):
+    return np.ascontiguousarray(a, np.uint8)
+
+
+def frame_encode(types, sids, payload, pay_off, out_off=None):
+    types = _u8(types); sids = np.ascontiguousarray(sids, np.uint32)
+    payload = _u8(payload); pay_off = np.ascontiguousarray(pay_off, np.uint64)
+    n = len(types)
+    if out_off is None:
+        out_off = np.zeros(n + 1, np.uint64)
+        np.cumsum((pay_off[1:] - pay_off[:-1]) + np.uint64(5), out=out_off[1:])
+    out_off = np.ascontiguousarray(out_off, np.uint64)
+    out = np.zeros(int(out_off[-1]) if n else 0, np.uint8)
+    lib().orc_frame_encode_batch(C.c_uint64(n), _p(types), _p(sids), _p(payload), _p(pay_off), _p(out), _p(out_off))
+    return out, out_off
+
+
+def frame_decode(buf, in_off):
+    buf = _u8(buf); in_off = np.ascontiguousarray(in_off, np.uint64)
+    n = len(in_off) - 1
+    desc = np.zeros(n, DESC_DTYPE)
+    lib().orc_frame_decode_batch(C.c_uint64(n), _p(buf), _p(in_off), _p(desc))
+    return desc
+
+
+def frame_demux(desc, buf):
+    desc = np.ascontiguousarray(desc, DESC_DTYPE); buf = _u8(buf)
+    n = len(desc)
+    uniq = np.zeros(n + 1, np.uint32); csr = np.zeros(n + 1, np.uint64); perm = np.zeros(max(n, 1), np.uint32)
+    body = (desc["status"] == 0) & ((desc["msg_type"] == 11) | (desc["msg_type"] == 21))
+    gathered = np.zeros(max(int(desc["pay_len"][body].sum()), 1), np.uint8)
+    goff = np.zeros(n + 1, np.uint64)
+    k = lib().orc_frame_demux_batch(C.c_uint64(n), _p(desc), _p(buf), _p(uniq), _p(csr), _p(perm), _p(gathered), _p(goff))
+    m = int(csr[k])
+    return {"k": k, "uniq_sid": uniq[:k].copy(), "csr": csr[:k + 1].copy(), "perm": perm[:m].copy(),
+            "gathered_off": goff[:k + 1].copy(), "gathered": gathered[:int(goff[k])].copy()}
+
+
+def dtls_seal(session, keys, ivs, nonce8, raw, raw_off, rec_off=None):
+    session = np.ascontiguousarray(session, np.uint32); keys = _u8(keys); ivs = _u8(ivs)
+    nonce8 = _u8(nonce8); raw = _u8(raw); raw_off = np.ascontiguousarray(raw_off, np.uint64)
+    n = len(session)
+    if rec_off is None:
+        rec_off = np.zeros(n + 1, np.uint64)
+        np.cumsum((raw_off[1:] - raw_off[:-1]) + np.uint64(24), out=rec_off[1:])
+    rec_off = np.ascontiguousarray(rec_off, np.uint64)
+    rec = np.zeros(int(rec_off[-1]) if n else 0, np.uint8)
+    status = np.zeros(n, np.uint8)
+    lib().orc_dtls_seal_batch(C.c_uint64(n), _p(session), _p(keys), _p(ivs), _p(nonce8), _p(raw), _p(raw_off),
+                              _p(rec), _p(rec_off), _p(status))
+    return rec, rec_off, status
+
+
+def dtls_open(session, keys, ivs, rec, rec_off, out_off=None):
+    session = np.ascontiguousarray(session, np.uint32); keys = _u8(keys); ivs = _u8(ivs)
+    rec = _u8(rec); rec_off = np.ascontiguousarray(rec_off, np.uint64)
+    n = len(session)
+    if out_off is None:
+        out_off = rec_off
+    out_off = np.ascontiguousarray(out_off, np.uint64)
+    out = np.zeros(int(out_off[-1]) if n else 0, np.uint8)
+    out_len = np.zeros(n, np.uint32); status = np.zeros(n, np.uint8)
+    lib().orc_dtls_open_batch(C.c_uint64(n), _p(session), _p(keys), _p(ivs), _p(rec), _p(rec_off),
+                              _p(out), _p(out_off), _p(out_len), _p(status))
+    return out, out_off, out_len, status
+
+
+def pipeline_raw(w):
+    """frames -> raw records (hdr13 || frame) exactly as serve.rs:269-276 + the DTLS record layer
+    would build them: content type 23, version fe fd, epoch, seq48, length."""
+    frames, foff = frame_encode(w["types"], w["sids"], w["payload"], w["pay_off"])
+    n = w["n"]
+    flen = (foff[1:] - foff[:-1]).astype(np.uint64)
+    raw_off = np.zeros(n + 1, np.uint64)
+    np.cumsum(flen + np.uint64(13), out=raw_off[1:])
+    raw = np.zeros(int(raw_off[-1]), np.uint8)
+    for i in range(n):
+        o = int(raw_off[i]); L = int(flen[i])
+        raw[o:o + 13] = np.frombuffer(bytes([23, 0xFE, 0xFD]) + int(w["epoch"][i]).to_bytes(2, "big") +
+                                      int(w["seq48"][i]).to_bytes(6, "big") + (L & 0xFFFF).to_bytes(2, "big"), np.uint8)
+        raw[o + 13:o + 13 + L] = frames[int(foff[i]):int(foff[i + 1])]
+    return raw, raw_off
+
+
+def pipeline_seal(w, keys, ivs):
+    raw, raw_off = pipeline_raw(w)
+    rec, _, status = dtls_seal(w["session"], keys, ivs, w["nonce8"], raw, raw_off, w.get("rec_off"))
+    assert (status == 0).all()
+    return rec

@@ -1,0 +1,58 @@
+"""CPU: the C-ABI library builds for sm_100a, loads, and exports every symbol include/p2pt.h declares.
+No compute call is made (there is no GPU here and the library has no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "p2pt.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(p2pt_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_declares_the_expected_surface():
+    syms = declared_symbols()
+    for must in ("p2pt_ctx_create", "p2pt_frame_encode_batch", "p2pt_frame_decode_batch", "p2pt_frame_demux_batch",
+                 "p2pt_dtls_gcm_seal_batch", "p2pt_dtls_gcm_open_batch", "p2pt_pipeline_seal", "p2pt_pipeline_open",
+                 "p2pt_sessions_load", "p2pt_last_error"):
+        assert must in syms
+
+
+def test_library_exports_every_declared_symbol(built):
+    import p2p_llm_tunnel_b200 as p2pt
+    lib = C.CDLL(p2pt.lib_path())
+    for s in declared_symbols():
+        assert hasattr(lib, s), f"{s} declared in include/p2pt.h but not exported"
+    lib.p2pt_abi_version.restype = C.c_int32
+    assert lib.p2pt_abi_version() == 1
+
+
+def test_python_binding_covers_every_symbol(built):
+    from p2p_llm_tunnel_b200 import _lib
+    assert sorted(_lib.SIGNATURES) == declared_symbols()
+    _lib.load_library()
+
+
+def test_no_cpu_fallback_without_a_device(built):
+    """ctx_create must fail loudly (never fall back) when no CUDA device is present."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present; the failure path is exercised on the CPU box")
+    import p2p_llm_tunnel_b200 as p2pt
+    with pytest.raises(p2pt.P2ptError) as e:
+        p2pt.Context(0)
+    assert "no CUDA device" in str(e.value) or "CUDA" in str(e.value)
+
+
+def test_product_does_not_reference_the_oracle():
+    pkg = os.path.join(ROOT, "p2p-llm-tunnel_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "liboracle" not in text and "p2pt_oracle" not in text and "oracle_binding" not in text, f

@@ -1,0 +1,127 @@
+"""GPU: the host-side mirror of the reference interface (protocol.TunnelMessage, dtls.CryptoGcm) --
+these read like the reference's own tests (/root/reference/tunnel/src/protocol.rs:265-460) -- and the
+device-pointer entry points driven from torch tensors."""
+import json
+
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+
+pytestmark = pytest.mark.gpu
+
+
+def test_roundtrips_like_the_reference(ctx):
+    from p2p_llm_tunnel_b200.protocol import (Agree, Hello, MAX_BODY_CHUNK, MessageType, TunnelMessage)
+    d = TunnelMessage.decode(TunnelMessage.hello(Hello()).encode(ctx), ctx)
+    assert d.msg_type == MessageType.Hello and d.stream_id == 0 and json.loads(d.payload)["proto"] == "httptunnel"
+    d = TunnelMessage.decode(TunnelMessage.agree(Agree()).encode(ctx), ctx)
+    assert d.msg_type == MessageType.Agree and json.loads(d.payload)["features"] == ["sse"]
+    hdr = {"stream_id": 42, "method": "POST", "path": "/v1/chat/completions", "headers": {"content-type": "application/json"}}
+    d = TunnelMessage.decode(TunnelMessage.req_headers(hdr).encode(ctx), ctx)
+    assert d.msg_type == MessageType.ReqHeaders and d.stream_id == 42 and json.loads(d.payload)["method"] == "POST"
+    d = TunnelMessage.decode(TunnelMessage.req_body(7, b"hello world").encode(ctx), ctx)
+    assert (d.msg_type, d.stream_id, d.payload) == (MessageType.ReqBody, 7, b"hello world")
+    d = TunnelMessage.decode(TunnelMessage.req_end(7).encode(ctx), ctx)
+    assert (d.msg_type, d.stream_id, d.payload) == (MessageType.ReqEnd, 7, b"")
+    d = TunnelMessage.decode(TunnelMessage.res_headers({"stream_id": 99, "status": 200, "headers": {}}).encode(ctx), ctx)
+    assert d.msg_type == MessageType.ResHeaders and d.stream_id == 99
+    sse = b'data: {"token": "hello"}\n\n'
+    d = TunnelMessage.decode(TunnelMessage.res_body(99, sse).encode(ctx), ctx)
+    assert (d.msg_type, d.stream_id, d.payload) == (MessageType.ResBody, 99, sse)
+    d = TunnelMessage.decode(TunnelMessage.res_end(99).encode(ctx), ctx)
+    assert d.msg_type == MessageType.ResEnd and d.payload == b""
+    d = TunnelMessage.decode(TunnelMessage.error(5, "upstream timeout").encode(ctx), ctx)
+    assert (d.msg_type, d.stream_id, d.payload) == (MessageType.Error, 5, b"upstream timeout")
+    # negative / boundary cases
+    for bad, text in ((b"", "too short"), (bytes([1, 0, 0]), "too short"), (bytes([255, 0, 0, 0, 0]), "unknown message type")):
+        with pytest.raises(ValueError) as e:
+            TunnelMessage.decode(bad, ctx)
+        assert text in str(e.value)
+    d = TunnelMessage.decode(bytes([12, 0, 0, 0, 0]), ctx)
+    assert (d.msg_type, d.stream_id, d.payload) == (MessageType.ReqEnd, 0, b"")
+    assert TunnelMessage.decode(TunnelMessage.req_end(0xFFFFFFFF).encode(ctx), ctx).stream_id == 0xFFFFFFFF
+    big = bytes([0xAB]) * MAX_BODY_CHUNK
+    enc = TunnelMessage.res_body(1, big).encode(ctx)
+    assert len(enc) == 5 + MAX_BODY_CHUNK and TunnelMessage.decode(enc, ctx).payload == big
+    assert TunnelMessage.decode(TunnelMessage.res_body(1, b"").encode(ctx), ctx).payload == b""
+
+
+def test_chunker_and_demux_reassemble_a_body(ctx):
+    from p2p_llm_tunnel_b200.protocol import MAX_BODY_CHUNK, TunnelMessage, chunk_body, demux_batch, encode_batch
+    body_a = bytes((i * 7) & 0xFF for i in range(2 * MAX_BODY_CHUNK + 123))
+    body_b = b"short body"
+    msgs = chunk_body(1, body_a) + [TunnelMessage.res_body(2, body_b)]
+    msgs = [msgs[0], msgs[3], msgs[1], TunnelMessage.ping(), msgs[2], TunnelMessage.res_end(2), TunnelMessage.res_end(1)]
+    buf, off = encode_batch(msgs, ctx)
+    frames = [buf[int(off[i]):int(off[i + 1])].tobytes() for i in range(len(msgs))]
+    r = demux_batch(frames, ctx)
+    assert sorted(r) == [0, 1, 2]
+    assert r[1][1] == body_a and r[2][1] == body_b and r[0][1] == b""
+    assert [int(m.msg_type) for m in r[1][0]] == [21, 21, 21, 22]
+
+
+def test_crypto_gcm_mirror(ctx):
+    from cryptography.hazmat.primitives.ciphers.aead import AESGCM
+    from p2p_llm_tunnel_b200.dtls import CryptoGcm, ErrDecrypt, ErrNotEnoughRoomForNonce, record_header
+    lk, rk = bytes(range(16)), bytes(range(16, 32))
+    a = CryptoGcm(lk, b"\x01\x02\x03\x04", rk, b"\x05\x06\x07\x08", ctx=ctx)
+    payload = b"application data over the tunnel" * 10
+    raw = record_header(23, 1, 5, len(payload)) + payload
+    rec = a.encrypt(None, raw, nonce=bytes(8))
+    aad = raw[3:11] + raw[0:3] + len(payload).to_bytes(2, "big")
+    assert rec[21:] == AESGCM(lk).encrypt(b"\x01\x02\x03\x04" + bytes(8), payload, aad)
+    assert int.from_bytes(rec[11:13], "big") == 8 + len(payload) + 16
+    # the peer: its local key is our remote key
+    b = CryptoGcm(rk, b"\x05\x06\x07\x08", lk, b"\x01\x02\x03\x04", ctx=ctx)
+    out = b.decrypt(rec)
+    assert out == rec[:13] + payload
+    with pytest.raises(ErrDecrypt):
+        b.decrypt(rec[:-1] + bytes([rec[-1] ^ 1]))
+    with pytest.raises(ErrNotEnoughRoomForNonce):
+        b.decrypt(rec[:20])
+    # random nonce path: two seals differ, both open
+    r1, r2 = b.encrypt(None, raw), b.encrypt(None, raw)
+    assert r1 != r2
+    a2 = CryptoGcm(lk, b"\x01\x02\x03\x04", rk, b"\x05\x06\x07\x08", ctx=ctx)
+    assert a2.decrypt(r1) == a2.decrypt(r2) == r1[:13] + payload
+
+
+def test_device_pointer_entry_points(ctx):
+    import torch
+    from p2p_llm_tunnel_b200 import workload
+    dev = torch.device("cuda:0")
+    keys, ivs = workload.sessions_keys(32)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    w = workload.pipeline_workload(32, 8, 1200)
+    n = w["n"]
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
+    d = {k: t(w[k]) for k in ("session", "epoch", "seq48", "nonce8", "types", "sids", "payload", "pay_off", "rec_off")}
+    rec = torch.zeros(int(w["rec_off"][-1]), dtype=torch.uint8, device=dev)
+    status = torch.zeros(n, dtype=torch.uint8, device=dev)
+    s = torch.cuda.current_stream().cuda_stream
+    ctx.call("p2pt_pipeline_seal_device", n, d["session"], d["epoch"], d["seq48"], d["nonce8"], d["types"], d["sids"],
+             d["payload"], d["pay_off"], rec, d["rec_off"], status, s)
+    torch.cuda.synchronize()
+    assert int(status.sum()) == 0
+    assert np.array_equal(rec.cpu().numpy(), ob.pipeline_seal(w, keys, ivs))
+    out = torch.zeros_like(rec)
+    desc = torch.zeros(n * 24, dtype=torch.uint8, device=dev)
+    ctx.call("p2pt_pipeline_open_device", n, d["session"], rec, d["rec_off"], out, d["rec_off"], desc, s)
+    scratch_bytes = int(ctx.lib.p2pt_frame_demux_scratch_bytes(n))
+    scratch = torch.zeros(scratch_bytes, dtype=torch.uint8, device=dev)
+    uniq = torch.zeros(n + 1, dtype=torch.int32, device=dev); csr = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+    perm = torch.zeros(n, dtype=torch.int32, device=dev); k = torch.zeros(1, dtype=torch.int32, device=dev)
+    gathered = torch.zeros(n * 1200, dtype=torch.uint8, device=dev); goff = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+    ctx.call("p2pt_frame_demux_batch_device", n, desc, out, n, uniq, csr, perm, k, gathered, n * 1200, goff,
+             scratch, scratch_bytes, s)
+    torch.cuda.synchronize()
+    from p2p_llm_tunnel_b200._lib import DESC_DTYPE
+    dn = desc.cpu().numpy().view(DESC_DTYPE)
+    exp = ob.frame_demux(dn, out.cpu().numpy())
+    kk = int(k.item())
+    assert kk == exp["k"] == 4
+    assert np.array_equal(uniq.cpu().numpy()[:kk].astype(np.uint32), exp["uniq_sid"])
+    assert np.array_equal(csr.cpu().numpy()[:kk + 1].astype(np.uint64), exp["csr"])
+    assert np.array_equal(perm.cpu().numpy().astype(np.uint32), exp["perm"])
+    assert np.array_equal(gathered.cpu().numpy(), exp["gathered"])

@@ -1,0 +1,279 @@
+"""GPU parity: every C-ABI entry point against the CPU oracle and the golden fixtures, bit-exact."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), "golden")
+h = bytes.fromhex
+
+
+def load(name):
+    with open(os.path.join(G, name)) as f:
+        return json.load(f)
+
+
+def ragged(rng, n, lo, hi):
+    lens = rng.integers(lo, hi + 1, n).astype(np.uint64)
+    off = np.zeros(n + 1, np.uint64)
+    np.cumsum(lens, out=off[1:])
+    return lens, off
+
+
+VALID = np.array([1, 2, 3, 4, 10, 11, 12, 20, 21, 22, 99], np.uint8)
+
+
+# ---------------------------------------------------------------------------------------- frames
+def test_frame_golden_vectors(ctx):
+    k = load("frames_kat.json")
+    for v in k["ok"]:
+        p = h(v["payload_hex"]) if v["payload_hex"] is not None else bytes([v["payload_fill"][0]]) * v["payload_fill"][1]
+        out, off = ctx.frame_encode([v["type"]], [v["stream_id"]], np.frombuffer(p, np.uint8), [0, len(p)])
+        assert len(out) == v["frame_len"] and out[:32].tobytes().hex() == v["frame_head_hex"], v["name"]
+        assert out[5:].tobytes() == p
+        d = ctx.frame_decode(out, off)[0]
+        assert (d["status"], d["msg_type"], d["stream_id"], d["pay_off"], d["pay_len"]) == (0, v["type"], v["stream_id"], 5, len(p))
+    for v in k["bad"]:
+        f = h(v["frame_hex"])
+        d = ctx.frame_decode(np.frombuffer(f, np.uint8), [0, len(f)])[0]
+        assert d["status"] == v["status"], v["name"]
+
+
+@pytest.mark.parametrize("lo,hi,n", [(0, 40, 3000), (0, 300, 3000), (1100, 1300, 2000), (60000, 65408, 12)])
+def test_frame_encode_matches_oracle(ctx, lo, hi, n):
+    rng = np.random.default_rng(lo + hi)
+    lens, pay_off = ragged(rng, n, lo, hi)
+    payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+    types = VALID[rng.integers(0, len(VALID), n)]
+    sids = rng.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
+    got, off = ctx.frame_encode(types, sids, payload, pay_off)
+    exp, off2 = ob.frame_encode(types, sids, payload, pay_off)
+    assert np.array_equal(off, off2) and np.array_equal(got, exp)
+
+
+def test_frame_encode_with_gaps_and_unaligned_slots(ctx):
+    rng = np.random.default_rng(5)
+    n = 500
+    lens, pay_off = ragged(rng, n, 0, 700)
+    payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+    slot = lens + np.uint64(5) + rng.integers(0, 19, n).astype(np.uint64)
+    out_off = np.zeros(n + 1, np.uint64); np.cumsum(slot, out=out_off[1:]); out_off += np.uint64(3)
+    types = np.full(n, 21, np.uint8); sids = np.arange(n, dtype=np.uint32)
+    got, _ = ctx.frame_encode(types, sids, payload, pay_off, out_off)
+    exp, _ = ob.frame_encode(types, sids, payload, pay_off, out_off)
+    for i in range(n):
+        a, b = int(out_off[i]), int(out_off[i]) + 5 + int(lens[i])
+        assert np.array_equal(got[a:b], exp[a:b]), i
+
+
+def make_frames(rng, n, n_streams, corrupt=0.02, lo=0, hi=200):
+    lens, pay_off = ragged(rng, n, lo, hi)
+    payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+    types = rng.choice(np.array([10, 11, 12, 20, 21, 21, 21, 21, 22, 99, 3, 4], np.uint8), n)
+    sids = rng.integers(1, n_streams + 1, n).astype(np.uint32)
+    sids[(types == 3) | (types == 4)] = 0
+    buf, off = ob.frame_encode(types, sids, payload, pay_off)
+    buf = buf.copy()
+    bad = rng.random(n) < corrupt
+    for i in np.nonzero(bad)[0]:
+        buf[int(off[i])] = rng.choice([0, 5, 23, 98, 100, 255])       # unknown tag
+    return buf, off
+
+
+def test_frame_decode_matches_oracle_with_corruption(ctx):
+    rng = np.random.default_rng(11)
+    buf, off = make_frames(rng, 20000, 300, corrupt=0.05)
+    # splice in too-short frames by re-cutting offsets
+    cut = np.sort(np.concatenate([off, off[1:2000:7] - np.uint64(2)])).astype(np.uint64)
+    cut = np.unique(cut)
+    got = ctx.frame_decode(buf, cut)
+    exp = ob.frame_decode(buf, cut)
+    assert got.tobytes() == exp.tobytes()
+    assert set(np.unique(got["status"])) == {0, 1, 2}
+
+
+@pytest.mark.parametrize("n,streams", [(1, 1), (33, 3), (5000, 4096), (60000, 17), (50000, 4096)])
+def test_frame_demux_matches_oracle(ctx, n, streams):
+    rng = np.random.default_rng(n)
+    buf, off = make_frames(rng, n, streams)
+    d = ctx.frame_decode(buf, off)
+    got = ctx.frame_demux(d, buf)
+    exp = ob.frame_demux(d, buf)
+    assert got["k"] == exp["k"]
+    for key in ("uniq_sid", "csr", "perm", "gathered_off", "gathered"):
+        assert np.array_equal(got[key], exp[key]), key
+
+
+def test_frame_demux_wide_stream_ids_and_no_gather(ctx):
+    rng = np.random.default_rng(3)
+    n = 20000
+    ids = rng.integers(0, 2**32, 500, dtype=np.uint64).astype(np.uint32)
+    ids[:3] = [0, 0xFFFFFFFF, 0x80000000]
+    sids = ids[rng.integers(0, 500, n)]
+    types = np.full(n, 21, np.uint8)
+    lens, pay_off = ragged(rng, n, 0, 64)
+    payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+    buf, off = ob.frame_encode(types, sids, payload, pay_off)
+    d = ctx.frame_decode(buf, off)
+    got = ctx.frame_demux(d, None, gather=False)
+    exp = ob.frame_demux(d, buf)
+    for key in ("uniq_sid", "csr", "perm"):
+        assert np.array_equal(got[key], exp[key]), key
+
+
+def test_frame_demux_capacity_error(ctx):
+    import p2p_llm_tunnel_b200 as p2pt
+    rng = np.random.default_rng(4)
+    buf, off = make_frames(rng, 1000, 100, corrupt=0)
+    d = ctx.frame_decode(buf, off)
+    with pytest.raises(p2pt.P2ptError) as e:
+        ctx.frame_demux(d, buf, max_streams=10)
+    assert e.value.code == -3
+
+
+# ---------------------------------------------------------------------------------------- DTLS
+def test_dtls_golden_records(ctx):
+    for v in load("dtls_records_kat.json")["records"]:
+        raw, rec = h(v["raw"]), h(v["rec"])
+        key, iv = np.frombuffer(h(v["key"]), np.uint8), np.frombuffer(h(v["iv"]), np.uint8)
+        ctx.sessions_load(key, iv, key, iv)
+        for g in (4, 8, 16, 32):
+            ctx.set_option("gcm_group_width", g)
+            got, _, st = ctx.dtls_seal([0], np.frombuffer(h(v["nonce"]), np.uint8), np.frombuffer(raw, np.uint8), [0, len(raw)])
+            assert st[0] == 0 and got.tobytes() == rec, (v["name"], g)
+            out, _, olen, st = ctx.dtls_open([0], np.frombuffer(rec, np.uint8), [0, len(rec)])
+            assert st[0] == 0 and out[:int(olen[0])].tobytes() == rec[:13] + raw[13:], (v["name"], g)
+        ctx.set_option("gcm_group_width", 0)
+
+
+def make_raw(rng, n, lo, hi, n_sessions):
+    lens, _ = ragged(rng, n, lo, hi)
+    raw_off = np.zeros(n + 1, np.uint64); np.cumsum(lens + np.uint64(13), out=raw_off[1:])
+    raw = rng.integers(0, 256, int(raw_off[-1]), dtype=np.uint8)
+    for i in range(n):
+        o = int(raw_off[i])
+        raw[o] = rng.choice([21, 22, 23]); raw[o + 1] = 0xFE; raw[o + 2] = 0xFD
+        raw[o + 11] = (int(lens[i]) >> 8) & 0xFF; raw[o + 12] = int(lens[i]) & 0xFF
+    session = rng.integers(0, n_sessions, n).astype(np.uint32)
+    nonce = rng.integers(0, 256, 8 * n, dtype=np.uint8)
+    return session, nonce, raw, raw_off
+
+
+@pytest.mark.parametrize("g", [0, 4, 8, 16, 32])
+@pytest.mark.parametrize("lo,hi,n", [(0, 70, 1500), (1190, 1210, 600), (0, 2500, 300)])
+def test_dtls_seal_open_match_oracle(ctx, g, lo, hi, n):
+    rng = np.random.default_rng(1000 + lo + hi + g)
+    ns = 37
+    keys = rng.integers(0, 256, (ns, 16), dtype=np.uint8); ivs = rng.integers(0, 256, (ns, 4), dtype=np.uint8)
+    rkeys = rng.integers(0, 256, (ns, 16), dtype=np.uint8); rivs = rng.integers(0, 256, (ns, 4), dtype=np.uint8)
+    ctx.sessions_load(keys, ivs, rkeys, rivs)
+    ctx.set_option("gcm_group_width", g)
+    try:
+        session, nonce, raw, raw_off = make_raw(rng, n, lo, hi, ns)
+        rec, rec_off, st = ctx.dtls_seal(session, nonce, raw, raw_off)
+        erec, erec_off, est = ob.dtls_seal(session, keys, ivs, nonce, raw, raw_off)
+        assert np.array_equal(st, est) and np.array_equal(rec_off, erec_off)
+        assert np.array_equal(rec, erec)
+        # open uses the REMOTE key: seal with the oracle under the remote key, tamper a few, open on the GPU
+        rrec, _, _ = ob.dtls_seal(session, rkeys, rivs, nonce, raw, raw_off)
+        rrec = rrec.copy()
+        for i in range(0, n, 17):
+            a, b = int(rec_off[i]), int(rec_off[i + 1])
+            rrec[a + int(rng.integers(0, b - a))] ^= 1 << int(rng.integers(0, 8))
+        out, _, olen, st = ctx.dtls_open(session, rrec, rec_off)
+        eout, _, eolen, est = ob.dtls_open(session, rkeys, rivs, rrec, rec_off)
+        assert np.array_equal(st, est) and np.array_equal(olen, eolen)
+        for i in range(n):
+            a = int(rec_off[i])
+            ln = int(olen[i]) if st[i] in (0, 5) else int(rec_off[i + 1] - rec_off[i]) - 24
+            assert np.array_equal(out[a:a + ln], eout[a:a + ln]), (i, st[i])
+    finally:
+        ctx.set_option("gcm_group_width", 0)
+
+
+def test_dtls_unaligned_slots_and_error_statuses(ctx):
+    rng = np.random.default_rng(77)
+    keys = rng.integers(0, 256, (3, 16), dtype=np.uint8); ivs = rng.integers(0, 256, (3, 4), dtype=np.uint8)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    n = 400
+    session, nonce, raw, raw_off = make_raw(rng, n, 0, 400, 3)
+    lens = raw_off[1:] - raw_off[:-1]
+    slot = lens + np.uint64(24) + rng.integers(0, 23, n).astype(np.uint64)
+    rec_off = np.zeros(n + 1, np.uint64); np.cumsum(slot, out=rec_off[1:]); rec_off += np.uint64(5)
+    rec, _, st = ctx.dtls_seal(session, nonce, raw, raw_off, rec_off)
+    erec, _, est = ob.dtls_seal(session, keys, ivs, nonce, raw, raw_off, rec_off)
+    assert np.array_equal(st, est)
+    for i in range(n):
+        a, b = int(rec_off[i]), int(rec_off[i]) + int(lens[i]) + 24
+        assert np.array_equal(rec[a:b], erec[a:b]), i
+    # hand-made bad records through open
+    good = erec[int(rec_off[0]):int(rec_off[0]) + int(lens[0]) + 24].tobytes()
+    cases = [good[:12], good[:21], good[:30], bytes([20, 0xFE, 0xFD, 0, 0, 0, 0, 0, 0, 0, 5, 0, 1, 1]),
+             good[:2] + b"\xfc" + good[3:], good, b"", good[:13]]
+    buf = np.frombuffer(b"".join(cases), np.uint8)
+    off = np.concatenate([[0], np.cumsum([len(c) for c in cases])]).astype(np.uint64)
+    sess = np.full(len(cases), session[0], np.uint32)
+    out, _, olen, st = ctx.dtls_open(sess, buf, off)
+    eout, _, eolen, est = ob.dtls_open(sess, keys, ivs, buf, off)
+    assert list(st) == list(est) == [6, 4, 3, 5, 6, 0, 6, 4]
+    assert np.array_equal(olen, eolen)
+    for i in range(len(cases)):
+        a = int(off[i])
+        assert np.array_equal(out[a:a + int(olen[i])], eout[a:a + int(olen[i])])
+
+
+def test_seal_rejects_short_raw_and_bad_session(ctx):
+    keys = np.arange(16, dtype=np.uint8)[None]; ivs = np.arange(4, dtype=np.uint8)[None]
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    raw = np.zeros(40, np.uint8); raw[1] = 0xFE; raw[2] = 0xFD
+    off = np.array([0, 5, 40], np.uint64)
+    rec_off = np.array([0, 64, 128], np.uint64)
+    _, _, st = ctx.dtls_seal([0, 9], np.zeros(16, np.uint8), raw, off, rec_off)
+    assert list(st) == [6, 6]           # < 13 bytes ; session index out of range
+
+
+# ---------------------------------------------------------------------------------------- fused pipeline
+@pytest.mark.parametrize("plen", [0, 1, 11, 64, 1200, 4000])
+def test_pipeline_seal_open_match_oracle(ctx, plen):
+    from p2p_llm_tunnel_b200 import workload
+    keys, ivs = workload.sessions_keys(16, seed_shift=plen)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    w = workload.pipeline_workload(16, 9, plen, seed_shift=plen)
+    rec, rec_off, st = ctx.pipeline_seal(w["session"], w["epoch"], w["seq48"], w["nonce8"], w["types"], w["sids"],
+                                         w["payload"], w["pay_off"], w["rec_off"])
+    assert (st == 0).all()
+    assert np.array_equal(rec, ob.pipeline_seal(w, keys, ivs))
+    # tamper two records, then open + decode in one pass
+    rec = rec.copy(); rec[int(rec_off[3]) + 25 if plen else int(rec_off[3]) + 22] ^= 4; rec[int(rec_off[8]) + 7] ^= 1
+    out, out_off, desc = ctx.pipeline_open(w["session"], rec, rec_off)
+    eout, _, eolen, est = ob.dtls_open(w["session"], keys, ivs, rec, rec_off)
+    n = w["n"]
+    for i in range(n):
+        a = int(rec_off[i])
+        if est[i] == 0:
+            assert desc["status"][i] == 0 and desc["msg_type"][i] == 21 and desc["stream_id"][i] == w["sids"][i]
+            assert desc["pay_off"][i] == a + 18 and desc["pay_len"][i] == plen
+            assert np.array_equal(out[a:a + int(eolen[i])], eout[a:a + int(eolen[i])])
+        else:
+            assert desc["status"][i] == 3
+    assert sorted(np.nonzero(desc["status"])[0].tolist()) == [3, 8]
+
+
+def test_pipeline_ragged_with_short_frames(ctx):
+    """open->decode statuses: frames shorter than 5 bytes and unknown tags inside valid records."""
+    keys = np.arange(32, dtype=np.uint8).reshape(2, 16); ivs = np.arange(8, dtype=np.uint8).reshape(2, 4)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    frames = [b"", b"\x15", b"\x15\x00\x00\x00", b"\xff\x00\x00\x00\x01zz", b"\x0c\x00\x00\x00\x00", b"\x15\x00\x00\x01\x02" + bytes(50)]
+    raws = [bytes([23, 0xFE, 0xFD, 0, 1, 0, 0, 0, 0, 0, i]) + len(f).to_bytes(2, "big") + f for i, f in enumerate(frames)]
+    raw = np.frombuffer(b"".join(raws), np.uint8)
+    raw_off = np.concatenate([[0], np.cumsum([len(r) for r in raws])]).astype(np.uint64)
+    sess = np.array([0, 1, 0, 1, 0, 1], np.uint32)
+    rec, rec_off, _ = ob.dtls_seal(sess, keys, ivs, np.arange(48, dtype=np.uint8), raw, raw_off)
+    out, _, desc = ctx.pipeline_open(sess, rec, rec_off)
+    assert list(desc["status"]) == [1, 1, 1, 2, 0, 0]
+    assert list(desc["msg_type"]) == [0, 0x15, 0x15, 0xFF, 12, 0x15]
+    assert desc["stream_id"][5] == 0x102 and desc["pay_len"][5] == 50 and desc["pay_len"][4] == 0

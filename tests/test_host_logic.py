@@ -1,0 +1,78 @@
+"""CPU: host-side logic that needs no GPU -- workload generator determinism, the math header the
+kernels use (compiled for the host) against the oracle, message-type mirror, negotiation."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_splitmix64_known_values():
+    from p2p_llm_tunnel_b200 import workload
+    # reference values of splitmix64 with seed 0 (public test vector of the generator)
+    v = workload.splitmix64(0, 3)
+    assert [int(x) for x in v] == [0xE220A8397B1DCDAF, 0x6E789E6AA1B965F4, 0x06C45D188009454F]
+    a = workload.splitmix64(0x5EED0001, 10)
+    b = workload.splitmix64(0x5EED0001, 5, start=5)
+    assert np.array_equal(a[5:], b)
+
+
+def test_workloads_are_deterministic_and_shaped():
+    from p2p_llm_tunnel_b200 import workload
+    w1 = workload.frames_workload(1000, 1200)
+    w2 = workload.frames_workload(1000, 1200)
+    assert np.array_equal(w1["payload"], w2["payload"]) and np.array_equal(w1["sids"], w2["sids"])
+    assert w1["sids"].min() >= 1 and w1["sids"].max() <= 4096
+    assert w1["frame_off"][-1] == 1000 * 1205
+    r = workload.records_workload(100, 1200, n_sessions=7)
+    assert r["raw"].size == 100 * 1213 and r["raw"][0] == 23 and r["raw"][1] == 0xFE and r["raw"][2] == 0xFD
+    assert int.from_bytes(r["raw"][1213 * 15 + 5: 1213 * 15 + 11].tobytes(), "big") == 15 // 7
+    s = workload.frames_workload(10, 64, sse=True)
+    assert bytes(s["payload"][:6]) == b"data: "
+    p = workload.pipeline_workload(8, 16, 1200)
+    assert p["n"] == 128 and p["sids"].max() == 4 and p["seq48"][17] == 1
+
+
+def test_message_type_mirror():
+    from p2p_llm_tunnel_b200.protocol import MessageType, Agree, Hello
+    assert MessageType.from_u8(21) is MessageType.ResBody and MessageType.from_u8(255) is None
+    assert sorted(int(m) for m in MessageType) == [1, 2, 3, 4, 10, 11, 12, 20, 21, 22, 99]
+    # negotiation (protocol.rs:464-549)
+    a = Agree.from_hello(Hello(min_version=1, max_version=5, features=["sse", "zstd"]))
+    assert a.version == 1 and a.features == ["sse"]
+    with pytest.raises(ValueError):
+        Agree.from_hello(Hello(min_version=2, max_version=3))
+    with pytest.raises(ValueError):
+        Agree.from_hello(Hello(proto="other"))
+
+
+def test_device_gf128_math_on_host_matches_oracle(tmp_path):
+    """gcm_math.cuh is __host__ __device__: compile it for the host and compare the integer-multiply
+    carry-less GF(2^128) product with the oracle's SP 800-38D bitwise multiply."""
+    src = tmp_path / "t.cpp"
+    src.write_text(r'''
+#include "gcm_math.cuh"
+#include "p2pt_oracle.h"
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+using namespace p2pt;
+static U128 from_bytes(const uint8_t* b){ uint32_t w[4]; memcpy(w,b,16); return block_to_u128(w[0],w[1],w[2],w[3]); }
+static void to_bytes(const U128& x, uint8_t* b){ uint32_t w[4]={bswap32(x.w[3]),bswap32(x.w[2]),bswap32(x.w[1]),bswap32(x.w[0])}; memcpy(b,w,16);}
+int main(){ srand(7); int bad=0;
+ for(int it=0;it<5000;it++){ uint8_t x[16],y[16],z[16],z2[16];
+  for(int i=0;i<16;i++){x[i]=rand();y[i]=rand();}
+  if(it==0){memset(x,0xff,16);memset(y,0xff,16);} if(it==1){memset(x,0,16);x[0]=0x80;} if(it==2){memset(y,0,16);y[15]=1;}
+  if(it==3){memset(x,0,16);} if(it==4){memset(x,0xff,16);memset(y,0,16);y[0]=0x80;}
+  orc_gf128_mul(x,y,z); GhashKey k; ghash_key_prepare(from_bytes(y),k); to_bytes(gf128_mul(from_bytes(x),k),z2);
+  if(memcmp(z,z2,16)) bad++; }
+ printf("bad=%d\n",bad); return bad!=0; }
+''')
+    exe = tmp_path / "t"
+    subprocess.check_call(["g++", "-O2", "-I", os.path.join(ROOT, "p2p-llm-tunnel_b200", "csrc"), "-I",
+                           os.path.join(ROOT, "oracle"), "-x", "c++", str(src), os.path.join(ROOT, "oracle", "p2pt_oracle.c"),
+                           "-o", str(exe)])
+    out = subprocess.check_output([str(exe)]).decode()
+    assert "bad=0" in out
