@@ -1,0 +1,397 @@
+#!/usr/bin/env python
+"""bench.py -- framed + DTLS-GCM sealed GB/s and records/s on N B200s (BASELINE.json `metric`).
+
+Workload (BASELINE.json configs[4], "C5"): 65 536 tunnel sessions x 16 RES_BODY frames x 1200 B per
+GPU (weak scaling: every rank holds its own 65 536 sessions; global session id = local * N + rank,
+no data-path collective -- sessions share no state).  One step = the full pipeline over that batch:
+    provider side  frame encode -> DTLS-GCM seal            (serve.rs:269-276 + dc.send)
+    consumer side  DTLS-GCM open -> frame decode -> demux by (session, stream_id) -> body gather
+`value`  = payload bytes carried through that whole round trip per second, inputs resident in HBM.
+`e2e`    = the same step through the host-pointer C ABI with pinned host buffers (H2D/D2H inside).
+`--impl reference` times the reference's CPU path (AES-NI/PCLMULQDQ port, all host threads).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SESSIONS, RECS, PAYLOAD = 65536, 16, 1200
+METRIC = "framed+DTLS-GCM sealed GB/s (payload bytes through encode->seal->open->decode->demux)"
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_workload(rank, world, sessions=SESSIONS):
+    from p2p_llm_tunnel_b200 import workload
+    w = workload.pipeline_workload(sessions, RECS, PAYLOAD, seed_shift=rank, session_base=rank, session_stride=world)
+    keys, ivs = workload.sessions_keys(sessions, seed_shift=rank)
+    return w, keys, ivs
+
+
+# --------------------------------------------------------------------------------------- CPU reference arm
+def load_cpufast():
+    import __graft_entry__ as g
+    g.build_oracle()
+    lib = C.CDLL(g.CPUFAST_LIB)
+    if not lib.cpufast_supported():
+        raise RuntimeError("host CPU lacks AES-NI / PCLMULQDQ")
+    return lib
+
+
+def cpu_pipeline(lib, w, keys, ivs, rec, nthreads, reps=1):
+    """returns best (seal_s, open_s) over reps, and stats"""
+    p = lambda a: C.c_void_p(a.ctypes.data)
+    times = (C.c_double * 2)(); stats = (C.c_uint64 * 4)()
+    best = None
+    for _ in range(reps):
+        rc = lib.cpufast_pipeline(C.c_uint64(w["n"]), p(w["session"]), p(keys), p(ivs), C.c_uint32(len(keys)),
+                                  p(w["epoch"]), p(w["seq48"]), p(w["nonce8"]), p(w["types"]), p(w["sids"]),
+                                  p(w["payload"]), p(w["pay_off"]), p(rec), p(w["rec_off"]), None,
+                                  C.c_int(nthreads), C.c_int(3), times, stats)
+        if rc != 0:
+            raise RuntimeError("cpufast_pipeline failed")
+        t = (times[0], times[1])
+        if best is None or sum(t) < sum(best):
+            best = t
+    return best, [int(x) for x in stats]
+
+
+def run_reference(args):
+    rank = env_int("RANK", 0)
+    if rank != 0:
+        return
+    lib = load_cpufast()
+    cores = os.cpu_count() or 1
+    # bounded sample: 1/8 of the per-GPU batch (8192 sessions x 16 records x 1200 B = 157 MB payload)
+    sessions = SESSIONS // 8
+    w, keys, ivs = make_workload(0, 1, sessions)
+    rec = np.zeros(int(w["rec_off"][-1]), np.uint8)
+    for _ in range(max(args.warmup, 1)):
+        cpu_pipeline(lib, w, keys, ivs, rec, cores)
+    t0 = time.perf_counter()
+    tot_seal = tot_open = 0.0
+    for _ in range(args.steps):
+        (ts, to), stats = cpu_pipeline(lib, w, keys, ivs, rec, cores)
+        tot_seal += ts; tot_open += to
+    wall = time.perf_counter() - t0
+    assert stats[0] == 0 and stats[2] == w["n"] * PAYLOAD, stats
+    step_s = wall / args.steps
+    payload_bytes = w["n"] * PAYLOAD
+    gbs = payload_bytes / step_s / 1e9
+    line = {
+        "impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C5 full frame+seal/open pipeline, bounded sample", "sessions": sessions,
+                   "records_per_session": RECS, "payload_bytes": PAYLOAD, "records_per_step": w["n"]},
+        "records_per_s": w["n"] / step_s,
+        "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port",
+                         "sample": f"{sessions} sessions x {RECS} records x {PAYLOAD} B per step (1/8 of the GPU batch), "
+                                   f"AES-NI + PCLMULQDQ C port of the RustCrypto path, {cores} threads sharded by session",
+                         "seal_gbs": payload_bytes * args.steps / tot_seal / 1e9,
+                         "open_demux_gbs": payload_bytes * args.steps / tot_open / 1e9},
+        "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------------------- GPU arm
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import __graft_entry__ as g
+    if not os.path.exists(g.LIB):
+        g.build_cuda()
+    import p2p_llm_tunnel_b200 as p2pt
+    from p2p_llm_tunnel_b200._lib import DESC_DTYPE
+
+    ctx = p2pt.Context(local)
+    w, keys, ivs = make_workload(rank, world)
+    n = w["n"]
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    payload_bytes = n * PAYLOAD
+    rec_bytes = int(w["rec_off"][-1])
+    max_streams = SESSIONS * 4
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- device-resident arm ----------------
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
+    d = {k: t(w[k]) for k in ("session", "epoch", "seq48", "nonce8", "types", "sids", "payload", "pay_off", "rec_off")}
+    rec = torch.empty(rec_bytes, dtype=torch.uint8, device=dev)
+    out = torch.empty(rec_bytes, dtype=torch.uint8, device=dev)
+    status = torch.empty(n, dtype=torch.uint8, device=dev)
+    desc = torch.empty(n * 24, dtype=torch.uint8, device=dev)
+    sbytes = int(ctx.lib.p2pt_frame_demux_scratch_bytes(n))
+    scratch = torch.empty(sbytes, dtype=torch.uint8, device=dev)
+    uniq = torch.empty(max_streams + 1, dtype=torch.int32, device=dev)
+    usess = torch.empty(max_streams + 1, dtype=torch.int32, device=dev)
+    csr = torch.empty(max_streams + 1, dtype=torch.int64, device=dev)
+    goff = torch.empty(max_streams + 1, dtype=torch.int64, device=dev)
+    perm = torch.empty(n, dtype=torch.int32, device=dev)
+    kdev = torch.zeros(1, dtype=torch.int32, device=dev)
+    gathered = torch.empty(payload_bytes, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream()
+    s = stream.cuda_stream
+
+    def seal():
+        ctx.call("p2pt_pipeline_seal_device", n, d["session"], d["epoch"], d["seq48"], d["nonce8"], d["types"], d["sids"],
+                 d["payload"], d["pay_off"], rec, d["rec_off"], status, s)
+
+    def open_():
+        ctx.call("p2pt_pipeline_open_device", n, d["session"], rec, d["rec_off"], out, d["rec_off"], desc, s)
+
+    def demux():
+        ctx.call("p2pt_frame_demux_batch_device", n, desc, d["session"], out, max_streams, uniq, usess, csr, perm, kdev,
+                 gathered, payload_bytes, goff, scratch, sbytes, s)
+
+    def step():
+        seal(); open_(); demux()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    # correctness gate on what was just computed: round trip must reproduce the payload per stream
+    dn = desc.cpu().numpy().view(DESC_DTYPE)
+    assert int(status.sum()) == 0 and int(dn["status"].sum()) == 0, "pipeline produced failing records"
+    assert int(kdev.item()) == max_streams, int(kdev.item())
+    pm = perm[: 4096].cpu().numpy().astype(np.int64)
+    got = gathered[: 4096 * PAYLOAD].cpu().numpy().reshape(4096, PAYLOAD)
+    assert np.array_equal(got, w["payload"].reshape(n, PAYLOAD)[pm]), "round trip does not reproduce the payload"
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    marks = [[ev() for _ in range(4)] for _ in range(args.steps)]
+    launches0 = ctx.launch_count()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = ev(), ev()
+    e0.record(stream)
+    for k in range(args.steps):
+        marks[k][0].record(stream); seal()
+        marks[k][1].record(stream); open_()
+        marks[k][2].record(stream); demux()
+        marks[k][3].record(stream)
+    e1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = ctx.launch_count() - launches0
+    dev_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    seal_ms = float(np.mean([m[0].elapsed_time(m[1]) for m in marks]))
+    open_ms = float(np.mean([m[1].elapsed_time(m[2]) for m in marks]))
+    demux_ms = float(np.mean([m[2].elapsed_time(m[3]) for m in marks]))
+    value = world * payload_bytes / (dev_ms * 1e-3) / 1e9
+
+    # ---------------- end-to-end arm: host-pointer C ABI, pinned host buffers ----------------
+    def pinned(a):
+        tt = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory()
+        return tt
+    h = {k: pinned(w[k]) for k in ("session", "epoch", "seq48", "nonce8", "types", "sids", "payload", "pay_off", "rec_off")}
+    h_rec = torch.empty(rec_bytes, dtype=torch.uint8).pin_memory()
+    h_status = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h_desc = torch.empty(n * 24, dtype=torch.uint8).pin_memory()
+    h_uniq = torch.empty((max_streams + 1) * 4, dtype=torch.uint8).pin_memory()
+    h_usess = torch.empty((max_streams + 1) * 4, dtype=torch.uint8).pin_memory()
+    h_csr = torch.empty((max_streams + 1) * 8, dtype=torch.uint8).pin_memory()
+    h_goff = torch.empty((max_streams + 1) * 8, dtype=torch.uint8).pin_memory()
+    h_perm = torch.empty(n * 4, dtype=torch.uint8).pin_memory()
+    h_gath = torch.empty(payload_bytes, dtype=torch.uint8).pin_memory()
+    kk = C.c_uint32(0)
+
+    def e2e_step():
+        ctx.call("p2pt_pipeline_seal", n, h["session"], h["epoch"], h["seq48"], h["nonce8"], h["types"], h["sids"],
+                 h["payload"], h["pay_off"], h_rec, h["rec_off"], h_status)
+        ctx.call("p2pt_pipeline_open_demux", n, h["session"], h_rec, h["rec_off"], None, h_desc, max_streams, h_uniq,
+                 h_usess, h_csr, h_perm, C.addressof(kk), h_gath, payload_bytes, h_goff)
+
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(2):
+        e2e_step()
+    assert kk.value == max_streams
+    assert np.array_equal(h_gath[: 4096 * PAYLOAD].numpy().reshape(4096, PAYLOAD), got), "e2e result differs"
+    launches_e0 = ctx.launch_count()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
+    barrier()
+    launches_e2e = (ctx.launch_count() - launches_e0) // e2e_steps
+    meta = n * (4 + 2 + 8 + 8 + 1 + 4 + 8 + 8)
+    h2d = payload_bytes + meta + rec_bytes + n * (4 + 8)
+    d2h = rec_bytes + n + payload_bytes + n * 24 + n * 4 + (max_streams + 1) * (4 + 4 + 8 + 8)
+    e2e_val = world * payload_bytes / e2e_s / 1e9
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---------------- roofline of the dominant kernel ----------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    # algorithmic bytes per record, fused encode->seal: read P + 43, write P + 43
+    seal_bytes = 2 * PAYLOAD + 86
+    stages = {"seal_ms": seal_ms, "open_ms": open_ms, "demux_gather_ms": demux_ms,
+              "seal_gbs_payload": payload_bytes / seal_ms / 1e6, "open_gbs_payload": payload_bytes / open_ms / 1e6,
+              "demux_gather_gbs_hbm": n * (2 * PAYLOAD + 41) / demux_ms / 1e6}
+    dom = "gcm_record_kernel<8,kPipeSeal>" if seal_ms >= open_ms else "gcm_record_kernel<8,kPipeOpen>"
+    dom_ms = max(seal_ms, open_ms)
+    dom_bytes = seal_bytes if seal_ms >= open_ms else (2 * PAYLOAD + 91)
+    achieved = n * dom_bytes / dom_ms / 1e6
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_record": dom_bytes,
+                "note": "AES-GCM without AES/CLMUL instructions is bound by the integer ALU / shared-memory LSU "
+                        "pipes, not HBM; see DESIGN.md and profiles/ for pipe utilisation"}
+    prof = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get("traffic_bytes_per_launch")
+        except Exception:
+            pass
+
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu:
+        try:
+            lib = load_cpufast()
+            cores = os.cpu_count() or 1
+            hw = {k: w[k] for k in w}
+            crec = np.zeros(rec_bytes, np.uint8)
+            (ts, to), stats = cpu_pipeline(lib, hw, keys, ivs, crec, cores, reps=2)
+            assert stats[0] == 0 and stats[2] == payload_bytes
+            assert np.array_equal(crec[: 1 << 20], rec[: 1 << 20].cpu().numpy()), "CPU baseline and GPU records differ"
+            cpu_baseline = {"value": payload_bytes / (ts + to) / 1e9, "unit": "GB/s", "cores": cores, "kind": "port",
+                            "sample": f"the full per-GPU batch ({n} records x {PAYLOAD} B), best of 2, AES-NI + PCLMULQDQ "
+                                      f"C port of the RustCrypto path on {cores} host threads sharded by session",
+                            "seal_gbs": payload_bytes / ts / 1e9, "open_demux_gbs": payload_bytes / to / 1e9}
+        except Exception as e:  # the CPU arm must never take the GPU numbers down with it
+            cpu_baseline = {"value": None, "unit": "GB/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e}"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": "C5 full frame+seal/open pipeline: 65536 sessions x 16 RES_BODY frames x 1200 B per GPU, "
+                               "sessions sharded by connection (global id = local*N + rank), no collective",
+                   "records_per_step_per_gpu": n, "payload_bytes": PAYLOAD, "streams_per_session": 4,
+                   "l2_policy": "inputs (1.26 GB payload + 1.31 GB records per step) are larger than the 126 MB L2"},
+        "records_per_s": world * n / (dev_ms * 1e-3),
+        "stages": stages,
+        "roofline": roofline,
+        "cpu_baseline": cpu_baseline,
+        "e2e": {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": e2e_s * 1e3, "steps": e2e_steps, "launches_per_step": int(launches_e2e),
+                "pcie_note": "PCIe Gen5 x16 = 63 GB/s per direction theoretical; this step moves "
+                             f"{h2d / 1e9:.2f} GB up and {d2h / 1e9:.2f} GB down"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

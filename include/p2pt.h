@@ -105,13 +105,18 @@ int32_t p2pt_frame_encode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* types,
 int32_t p2pt_frame_decode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, const uint64_t* in_off,
                                 p2pt_desc* desc);
 /* Demux (proxy.rs:118-153, serve.rs:112-139): stable group-by stream_id of the status-OK frames.
- * uniq_sid[k] ascending; csr[k+1] offsets into perm; perm[csr[k]] = frame indices in arrival
- * order.  If gathered != NULL, body frames (ReqBody 11 / ResBody 21) are concatenated per stream
- * into gathered and gathered_off[k+1] delimits streams (the Vec<u8> of serve.rs:120-124).
- * max_streams sizes uniq_sid / csr / gathered_off; gathered_cap sizes gathered. */
-int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
+ * session (nullable, n entries): the tunnel session each frame arrived on; when given, streams are
+ * keyed by (session, stream_id) -- every connection has its own stream_id counter (proxy.rs:52) --
+ * and uniq_session (nullable) receives the session of each stream.
+ * Streams ascending by (session, stream_id); csr[k+1] offsets into perm; perm[csr[s]..csr[s+1]) =
+ * frame indices of stream s in arrival order.  If gathered != NULL, body frames (ReqBody 11 /
+ * ResBody 21) are concatenated per stream into gathered and gathered_off[k+1] delimits streams
+ * (the Vec<u8> of serve.rs:120-124).  max_streams sizes uniq_* / csr / gathered_off (csr and
+ * gathered_off need max_streams + 1 entries); gathered_cap sizes gathered. */
+int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
                                const uint8_t* in, uint64_t in_bytes,
-                               uint32_t max_streams, uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+                               uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                               uint64_t* csr, uint32_t* perm,
                                uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
                                uint64_t* gathered_off);
 
@@ -148,6 +153,17 @@ int32_t p2pt_pipeline_open(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
                            const uint8_t* rec, const uint64_t* rec_off,
                            uint8_t* out, const uint64_t* out_off, p2pt_desc* desc);
 
+/* The consumer-side reader loop in one call (proxy.rs:109-170 / serve.rs:82-156 batched):
+ * open -> decode -> demux -> gather.  The opened frames stay on the device unless `out` (nullable,
+ * sized like rec, with out_off = rec_off) is given; desc / uniq_* / csr / perm / gathered* are as in
+ * p2pt_pipeline_open and p2pt_frame_demux_batch (desc[i].pay_off is relative to `out`). */
+int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                 const uint8_t* rec, const uint64_t* rec_off,
+                                 uint8_t* out, p2pt_desc* desc,
+                                 uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                 uint64_t* csr, uint32_t* perm, uint32_t* k_out,
+                                 uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off);
+
 /* ---- device-pointer variants: same arguments, all pointers are device pointers, `stream` is a
  *      cudaStream_t.  They enqueue on `stream` and return without synchronising. -------------- */
 int32_t p2pt_frame_encode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* types, const uint32_t* sids,
@@ -158,9 +174,10 @@ int32_t p2pt_frame_decode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t*
 /* scratch: device memory of at least p2pt_frame_demux_scratch_bytes(n) bytes, 256-byte aligned.
  * k_out is a device pointer to one u32. */
 uint64_t p2pt_frame_demux_scratch_bytes(uint64_t n);
-int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
+int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
                                       const uint8_t* in,
-                                      uint32_t max_streams, uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+                                      uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                      uint64_t* csr, uint32_t* perm,
                                       uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
                                       uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes,
                                       void* stream);

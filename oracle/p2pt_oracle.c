@@ -82,7 +82,7 @@ void orc_frame_decode_batch(uint64_t n, const uint8_t* in, const uint64_t* in_of
  * Output: streams ascending by id; perm = frame indices grouped by stream, arrival order kept;
  * csr[k+1] offsets into perm; gathered = per-stream concatenation of the payloads of body frames
  * (ReqBody = 11, ResBody = 21); gathered_off[k+1]. */
-typedef struct { uint32_t sid; uint32_t idx; } orc_pair;
+typedef struct { uint64_t sid; uint32_t idx; } orc_pair;   /* sid = session << 32 | stream_id */
 
 static void orc_stable_sort_pairs(orc_pair* a, orc_pair* tmp, uint64_t n) {
     /* bottom-up merge sort: stable and deterministic; result always left in a */
@@ -99,14 +99,19 @@ static void orc_stable_sort_pairs(orc_pair* a, orc_pair* tmp, uint64_t n) {
     }
 }
 
-uint32_t orc_frame_demux_batch(uint64_t n, const orc_desc* desc, const uint8_t* in,
-                               uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+uint32_t orc_frame_demux_batch(uint64_t n, const orc_desc* desc, const uint32_t* session, const uint8_t* in,
+                               uint32_t* uniq_sid, uint32_t* uniq_session, uint64_t* csr, uint32_t* perm,
                                uint8_t* gathered, uint64_t* gathered_off) {
     orc_pair* a = (orc_pair*)malloc((n ? n : 1) * sizeof(orc_pair));
     orc_pair* b = (orc_pair*)malloc((n ? n : 1) * sizeof(orc_pair));
     uint64_t m = 0;
     for (uint64_t i = 0; i < n; i++)
-        if (desc[i].status == ORC_OK) { a[m].sid = desc[i].stream_id; a[m].idx = (uint32_t)i; m++; }
+        if (desc[i].status == ORC_OK) {
+            /* one stream_id namespace per tunnel session (proxy.rs:52) */
+            a[m].sid = desc[i].stream_id | (session ? (uint64_t)session[i] << 32 : 0);
+            a[m].idx = (uint32_t)i;
+            m++;
+        }
     orc_stable_sort_pairs(a, b, m);
     orc_pair* s = a;
 
@@ -114,7 +119,8 @@ uint32_t orc_frame_demux_batch(uint64_t n, const orc_desc* desc, const uint8_t* 
     uint64_t goff = 0;
     for (uint64_t j = 0; j < m; j++) {
         if (j == 0 || s[j].sid != s[j - 1].sid) {
-            uniq_sid[k] = s[j].sid;
+            uniq_sid[k] = (uint32_t)s[j].sid;
+            if (uniq_session) uniq_session[k] = (uint32_t)(s[j].sid >> 32);
             csr[k] = j;
             if (gathered_off) gathered_off[k] = goff;
             k++;

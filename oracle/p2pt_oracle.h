@@ -53,9 +53,10 @@ void orc_frame_encode_batch(uint64_t n, const uint8_t* types, const uint32_t* si
                             const uint8_t* payload, const uint64_t* pay_off,
                             uint8_t* out, const uint64_t* out_off);
 void orc_frame_decode_batch(uint64_t n, const uint8_t* in, const uint64_t* in_off, orc_desc* desc);
-/* stable group-by stream_id; returns number of streams k. Streams ascending by id. */
-uint32_t orc_frame_demux_batch(uint64_t n, const orc_desc* desc, const uint8_t* in,
-                               uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+/* stable group-by (session, stream_id); returns number of streams k. Streams ascending by key.
+ * session and uniq_session may be NULL (single-session batch). */
+uint32_t orc_frame_demux_batch(uint64_t n, const orc_desc* desc, const uint32_t* session, const uint8_t* in,
+                               uint32_t* uniq_sid, uint32_t* uniq_session, uint64_t* csr, uint32_t* perm,
                                uint8_t* gathered, uint64_t* gathered_off);
 
 /* ---- AES-128 / GHASH / GCM (FIPS-197, SP 800-38D) ---- */

@@ -34,15 +34,16 @@ SIGNATURES = {
     "p2pt_sessions_load": (_i32, [_vp, _u32, _vp, _vp, _vp, _vp]),
     "p2pt_frame_encode_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_frame_decode_batch": (_i32, [_vp, _u64, _vp, _vp, _vp]),
-    "p2pt_frame_demux_batch": (_i32, [_vp, _u64, _vp, _vp, _u64, _u32, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
+    "p2pt_frame_demux_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _u64, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_dtls_gcm_seal_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_dtls_gcm_open_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_pipeline_seal": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_pipeline_open": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2pt_pipeline_open_demux": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_frame_encode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_frame_decode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp]),
     "p2pt_frame_demux_scratch_bytes": (_u64, [_u64]),
-    "p2pt_frame_demux_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _u64, _vp]),
+    "p2pt_frame_demux_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _u64, _vp]),
     "p2pt_dtls_gcm_seal_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_dtls_gcm_open_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_pipeline_seal_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
@@ -175,9 +176,12 @@ class Context:
         self._check(self.lib.p2pt_frame_decode_batch(self.h, n, buf.ctypes.data, in_off.ctypes.data, desc.ctypes.data))
         return desc
 
-    def frame_demux(self, desc, buf=None, max_streams=None, gather=True):
+    def frame_demux(self, desc, buf=None, max_streams=None, gather=True, session=None):
         desc = np.ascontiguousarray(desc, dtype=DESC_DTYPE)
         n = len(desc)
+        if session is not None:
+            session = _as(session, np.uint32)
+        usess = np.zeros((max_streams if max_streams is not None else max(n, 1)) + 1, np.uint32)
         if max_streams is None:
             max_streams = max(n, 1)
         uniq = np.zeros(max_streams + 1, np.uint32)
@@ -193,12 +197,15 @@ class Context:
             gathered = np.zeros(max(gcap, 1), np.uint8)
             goff = np.zeros(max_streams + 1, np.uint64)
         self._check(self.lib.p2pt_frame_demux_batch(
-            self.h, n, desc.ctypes.data, _ptr(buf) if gather else None, (buf.size if gather else 0),
-            max_streams, uniq.ctypes.data, csr.ctypes.data, perm.ctypes.data, C.addressof(k),
+            self.h, n, desc.ctypes.data, _ptr(session), _ptr(buf) if gather else None, (buf.size if gather else 0),
+            max_streams, uniq.ctypes.data, usess.ctypes.data if session is not None else None,
+            csr.ctypes.data, perm.ctypes.data, C.addressof(k),
             _ptr(gathered), gcap, _ptr(goff)))
         kk = k.value
         m = int(csr[kk])
         res = {"k": kk, "uniq_sid": uniq[:kk].copy(), "csr": csr[:kk + 1].copy(), "perm": perm[:m].copy()}
+        if session is not None:
+            res["uniq_session"] = usess[:kk].copy()
         if gather:
             res["gathered_off"] = goff[:kk + 1].copy()
             res["gathered"] = gathered[:int(goff[kk])].copy()
@@ -264,3 +271,24 @@ class Context:
         self._check(self.lib.p2pt_pipeline_open(self.h, n, session.ctypes.data, rec.ctypes.data, rec_off.ctypes.data,
                                                 out.ctypes.data, out_off.ctypes.data, desc.ctypes.data))
         return out, out_off, desc
+
+    def pipeline_open_demux(self, session, rec, rec_off, max_streams, gathered_cap, want_out=False):
+        """open -> decode -> demux -> gather in one call; returns dict like frame_demux plus desc."""
+        session = _as(session, np.uint32); rec = _as(rec, np.uint8); rec_off = _as(rec_off, np.uint64)
+        n = len(session)
+        desc = np.zeros(n, DESC_DTYPE)
+        out = np.zeros(int(rec_off[-1]) if (n and want_out) else 0, np.uint8)
+        uniq = np.zeros(max_streams + 1, np.uint32); usess = np.zeros(max_streams + 1, np.uint32)
+        csr = np.zeros(max_streams + 1, np.uint64); goff = np.zeros(max_streams + 1, np.uint64)
+        perm = np.zeros(max(n, 1), np.uint32); gathered = np.zeros(max(gathered_cap, 1), np.uint8)
+        k = _u32(0)
+        self._check(self.lib.p2pt_pipeline_open_demux(
+            self.h, n, session.ctypes.data, rec.ctypes.data, rec_off.ctypes.data,
+            out.ctypes.data if want_out else None, desc.ctypes.data, max_streams, uniq.ctypes.data,
+            usess.ctypes.data, csr.ctypes.data, perm.ctypes.data, C.addressof(k),
+            gathered.ctypes.data, gathered_cap, goff.ctypes.data))
+        kk = k.value
+        m = int(csr[kk])
+        return {"k": kk, "desc": desc, "out": out, "uniq_sid": uniq[:kk].copy(), "uniq_session": usess[:kk].copy(),
+                "csr": csr[:kk + 1].copy(), "perm": perm[:m].copy(), "gathered_off": goff[:kk + 1].copy(),
+                "gathered": gathered[:int(goff[kk])].copy()}

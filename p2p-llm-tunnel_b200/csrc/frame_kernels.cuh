@@ -80,25 +80,30 @@ __global__ void __launch_bounds__(256) frame_decode_kernel(
 }
 
 // ---- demux ----------------------------------------------------------------------------------------
-// Stable LSD radix sort of (key = stream_id, value = frame index) with a last pass on the "not
-// decodable" flag, so the status-OK frames end up first, grouped by stream_id ascending, arrival
-// order kept inside a stream.  Each pass = per-block digit histogram -> scan -> stable scatter with
-// warp match/ballot ranking.  A pass whose digit is the same for every key degenerates to a copy.
+// Stable LSD radix sort of (key, frame index), key = stream_id or (session << 32 | stream_id) when the
+// batch spans several tunnel sessions (each session has its own stream_id namespace,
+// /root/reference/tunnel/src/proxy.rs:52), with a last pass on the "not decodable" flag, so the
+// status-OK frames end up first, grouped by key ascending, arrival order kept inside a stream.
+// Each pass = per-block digit histogram -> scan -> stable scatter with warp match/ballot ranking.
+// A pass whose digit is the same for every key degenerates to a copy.
 //
-// Scratch layout (p2pt_frame_demux_scratch_bytes): two (key,idx) arrays for ping-pong, the
+// Scratch layout (p2pt_frame_demux_scratch_bytes): two key and two index arrays for ping-pong, the
 // [digit][block] histogram matrix, and the block sums of the final (stream count, body bytes) scan.
 
 constexpr int kSortBlocks = 592;        // 4 x 148 SMs
 constexpr int kSortThreads = 256;
 constexpr int kRadix = 256;
 constexpr int kScanThreads = 1024;
+constexpr int kKeyPasses = 8;           // 8 key bytes, then the validity pass
+constexpr int kSortPasses = kKeyPasses + 1;
 
 struct DemuxScratch {
-    uint2* pairs[2];       // (key, idx)
+    u64* keys[2];
+    uint32_t* idx[2];
     uint32_t* hist;        // kRadix * kSortBlocks
     u64* blk_bytes;        // per scan block: body bytes
     uint32_t* blk_heads;   // per scan block: stream heads
-    uint32_t* misc;        // [0] = number of valid frames m, [1] = or-mask, [2] = and-mask
+    u64* misc;             // [0] = number of valid frames m, [1] = OR of keys, [2] = OR of ~keys
 };
 
 __host__ __device__ inline u64 align256(u64 x) { return (x + 255) & ~(u64)255; }
@@ -107,7 +112,8 @@ inline u64 demux_scan_blocks(u64 n) { return (n + kScanThreads - 1) / kScanThrea
 
 inline u64 demux_scratch_bytes(u64 n) {
     u64 b = 0;
-    b += 2 * align256(n * sizeof(uint2));
+    b += 2 * align256(n * sizeof(u64));
+    b += 2 * align256(n * sizeof(uint32_t));
     b += align256((u64)kRadix * kSortBlocks * sizeof(uint32_t));
     b += align256((demux_scan_blocks(n) + 1) * sizeof(u64));
     b += align256((demux_scan_blocks(n) + 1) * sizeof(uint32_t));
@@ -118,38 +124,47 @@ inline u64 demux_scratch_bytes(u64 n) {
 inline DemuxScratch demux_carve(void* scratch, u64 n) {
     uint8_t* p = (uint8_t*)scratch;
     DemuxScratch s;
-    s.pairs[0] = (uint2*)p; p += align256(n * sizeof(uint2));
-    s.pairs[1] = (uint2*)p; p += align256(n * sizeof(uint2));
+    s.keys[0] = (u64*)p; p += align256(n * sizeof(u64));
+    s.keys[1] = (u64*)p; p += align256(n * sizeof(u64));
+    s.idx[0] = (uint32_t*)p; p += align256(n * sizeof(uint32_t));
+    s.idx[1] = (uint32_t*)p; p += align256(n * sizeof(uint32_t));
     s.hist = (uint32_t*)p; p += align256((u64)kRadix * kSortBlocks * sizeof(uint32_t));
     s.blk_bytes = (u64*)p; p += align256((demux_scan_blocks(n) + 1) * sizeof(u64));
     s.blk_heads = (uint32_t*)p; p += align256((demux_scan_blocks(n) + 1) * sizeof(uint32_t));
-    s.misc = (uint32_t*)p;
+    s.misc = (u64*)p;
     return s;
 }
 
-// pass "4" sorts on the invalid flag; passes 0..3 on stream_id bytes
-__device__ __forceinline__ uint32_t demux_digit(const uint2& kv, int pass, const p2pt_desc* desc) {
-    if (pass < 4) return (kv.x >> (8 * pass)) & 0xffu;
-    return desc[kv.y].status != P2PT_ST_OK ? 1u : 0u;
+__device__ __forceinline__ uint32_t demux_digit(u64 key, uint32_t idx, int pass, const p2pt_desc* desc) {
+    if (pass < kKeyPasses) return (uint32_t)(key >> (8 * pass)) & 0xffu;
+    return desc[idx].status != P2PT_ST_OK ? 1u : 0u;
 }
 
 __global__ void __launch_bounds__(256) demux_init_kernel(u64 n, const p2pt_desc* __restrict__ desc,
-                                                         uint2* __restrict__ pairs, uint32_t* __restrict__ misc) {
-    uint32_t vor = 0, vand = 0xffffffffu;
+                                                         const uint32_t* __restrict__ session,
+                                                         u64* __restrict__ keys, uint32_t* __restrict__ idx,
+                                                         u64* __restrict__ misc) {
+    u64 vor = 0, vnor = 0;
     const u64 stride = (u64)gridDim.x * blockDim.x;
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint32_t sid = desc[i].stream_id;
-        pairs[i] = make_uint2(sid, (uint32_t)i);
-        vor |= sid; vand &= sid;
+        u64 k = desc[i].stream_id;
+        if (session) k |= (u64)session[i] << 32;
+        keys[i] = k;
+        idx[i] = (uint32_t)i;
+        vor |= k; vnor |= ~k;
     }
-    vor = __reduce_or_sync(0xffffffffu, vor);
-    vand = __reduce_and_sync(0xffffffffu, vand);
-    if ((threadIdx.x & 31) == 0) { atomicOr(misc + 1, vor); atomicAnd(misc + 2, vand); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        vor |= __shfl_xor_sync(0xffffffffu, vor, o);
+        vnor |= __shfl_xor_sync(0xffffffffu, vnor, o);
+    }
+    if ((threadIdx.x & 31) == 0) { atomicOr(misc + 1, vor); atomicOr(misc + 2, vnor); }
 }
 
-__device__ __forceinline__ bool demux_pass_trivial(const uint32_t* misc, int pass) {
-    if (pass >= 4) return false;
-    return (((misc[1] ^ misc[2]) >> (8 * pass)) & 0xffu) == 0;
+// a key byte that is identical in every key needs no sorting pass
+__device__ __forceinline__ bool demux_pass_trivial(const u64* misc, int pass) {
+    if (pass >= kKeyPasses) return false;
+    return (((misc[1] & misc[2]) >> (8 * pass)) & 0xffu) == 0;
 }
 
 __device__ __forceinline__ void demux_tile(u64 n, u64& lo, u64& hi) {
@@ -162,8 +177,8 @@ __device__ __forceinline__ void demux_tile(u64 n, u64& lo, u64& hi) {
 }
 
 __global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
-    u64 n, const uint2* __restrict__ src, const p2pt_desc* __restrict__ desc, int pass,
-    uint32_t* __restrict__ hist, const uint32_t* __restrict__ misc) {
+    u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx, const p2pt_desc* __restrict__ desc,
+    int pass, uint32_t* __restrict__ hist, const u64* __restrict__ misc) {
     if (demux_pass_trivial(misc, pass)) return;
     __shared__ uint32_t h[kRadix];
     h[threadIdx.x] = 0;
@@ -171,7 +186,7 @@ __global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
     u64 lo, hi;
     demux_tile(n, lo, hi);
     for (u64 i = lo + threadIdx.x; i < hi; i += kSortThreads) {
-        const uint32_t d = demux_digit(src[i], pass, desc);
+        const uint32_t d = demux_digit(keys[i], idx[i], pass, desc);
         // warp-aggregated: one shared atomic per distinct digit in the warp
         const uint32_t peers = __match_any_sync(__activemask(), d);
         if ((__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&h[d], __popc(peers));
@@ -182,7 +197,7 @@ __global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
 
 // exclusive scan of the digit-major [kRadix][kSortBlocks] matrix, one block of 1024 threads
 __global__ void __launch_bounds__(1024) demux_scan_hist_kernel(uint32_t* __restrict__ hist, int pass,
-                                                              uint32_t* __restrict__ misc) {
+                                                              u64* __restrict__ misc) {
     if (demux_pass_trivial(misc, pass)) return;
     __shared__ uint32_t row_total[kRadix];
     __shared__ uint32_t row_base[kRadix];
@@ -217,7 +232,7 @@ __global__ void __launch_bounds__(1024) demux_scan_hist_kernel(uint32_t* __restr
             row_base[r0 + lane] = carry + incl - v;
             carry += __shfl_sync(0xffffffffu, incl, 31);
         }
-        if (pass == 4 && lane == 0) misc[0] = row_total[0];   // number of decodable frames
+        if (pass == kKeyPasses && lane == 0) misc[0] = row_total[0];   // number of decodable frames
     }
     __syncthreads();
     for (int r = warp; r < kRadix; r += 32) {
@@ -228,12 +243,13 @@ __global__ void __launch_bounds__(1024) demux_scan_hist_kernel(uint32_t* __restr
 }
 
 __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
-    u64 n, const uint2* __restrict__ src, uint2* __restrict__ dst, const p2pt_desc* __restrict__ desc,
-    int pass, const uint32_t* __restrict__ hist, const uint32_t* __restrict__ misc) {
+    u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx,
+    u64* __restrict__ keys_out, uint32_t* __restrict__ idx_out, const p2pt_desc* __restrict__ desc,
+    int pass, const uint32_t* __restrict__ hist, const u64* __restrict__ misc) {
     u64 lo, hi;
     demux_tile(n, lo, hi);
     if (demux_pass_trivial(misc, pass)) {
-        for (u64 i = lo + threadIdx.x; i < hi; i += kSortThreads) dst[i] = src[i];
+        for (u64 i = lo + threadIdx.x; i < hi; i += kSortThreads) { keys_out[i] = keys[i]; idx_out[i] = idx[i]; }
         return;
     }
     constexpr int W = kSortThreads / 32;
@@ -247,11 +263,11 @@ __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
         __syncthreads();
         const u64 i = c0 + threadIdx.x;
         const bool live = i < hi;
-        uint2 kv = make_uint2(0, 0);
-        uint32_t d = 0, rank = 0;
+        u64 key = 0;
+        uint32_t ix = 0, d = 0, rank = 0;
         if (live) {
-            kv = src[i];
-            d = demux_digit(kv, pass, desc);
+            key = keys[i]; ix = idx[i];
+            d = demux_digit(key, ix, pass, desc);
         }
         // rank among equal digits inside the warp, in lane (= arrival) order
         const uint32_t act = __ballot_sync(0xffffffffu, live);
@@ -262,17 +278,17 @@ __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
         }
         __syncthreads();
         // exclusive prefix over warps for this thread's digit column, then advance the block base
-        {
-            uint32_t run = 0;
-            const int col = threadIdx.x;
+        uint32_t run = 0;
+        const int col = threadIdx.x;
 #pragma unroll
-            for (int w = 0; w < W; w++) { uint32_t t = wcount[w][col]; wcount[w][col] = run; run += t; }
-            // keep the chunk total in a register until every thread has read its offsets
-            __syncthreads();
-            if (live) dst[base[d] + wcount[warp][d] + rank] = kv;
-            __syncthreads();
-            base[col] += run;
+        for (int w = 0; w < W; w++) { uint32_t t = wcount[w][col]; wcount[w][col] = run; run += t; }
+        __syncthreads();
+        if (live) {
+            const uint32_t o = base[d] + wcount[warp][d] + rank;
+            keys_out[o] = key; idx_out[o] = ix;
         }
+        __syncthreads();
+        base[col] += run;
         __syncthreads();
     }
 }
@@ -280,12 +296,11 @@ __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
 // After the sort: flag stream heads, and scan (heads, body bytes) over the m decodable frames.
 struct HeadBytes { uint32_t heads; u64 bytes; };
 
-__device__ __forceinline__ HeadBytes demux_item(u64 j, u64 m, const uint2* sorted, const p2pt_desc* desc) {
+__device__ __forceinline__ HeadBytes demux_item(u64 j, u64 m, const u64* keys, const uint32_t* idx, const p2pt_desc* desc) {
     HeadBytes r; r.heads = 0; r.bytes = 0;
     if (j < m) {
-        const uint2 kv = sorted[j];
-        r.heads = (j == 0 || sorted[j - 1].x != kv.x) ? 1u : 0u;
-        const p2pt_desc d = desc[kv.y];
+        r.heads = (j == 0 || keys[j - 1] != keys[j]) ? 1u : 0u;
+        const p2pt_desc d = desc[idx[j]];
         r.bytes = (d.msg_type == 11 || d.msg_type == 21) ? (u64)d.pay_len : 0;   // ReqBody / ResBody
     }
     return r;
@@ -329,12 +344,12 @@ __device__ __forceinline__ HeadBytes block_scan_excl(HeadBytes v, HeadBytes& tot
 }
 
 __global__ void __launch_bounds__(kScanThreads) demux_blocksum_kernel(
-    u64 n, const uint2* __restrict__ sorted, const p2pt_desc* __restrict__ desc,
-    const uint32_t* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes) {
+    u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx, const p2pt_desc* __restrict__ desc,
+    const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes) {
     const u64 m = misc[0];
     const u64 j = (u64)blockIdx.x * kScanThreads + threadIdx.x;
     HeadBytes tot;
-    (void)block_scan_excl(demux_item(j, m, sorted, desc), tot);
+    (void)block_scan_excl(demux_item(j, m, keys, idx, desc), tot);
     if (threadIdx.x == 0) { blk_heads[blockIdx.x] = tot.heads; blk_bytes[blockIdx.x] = tot.bytes; }
 }
 
@@ -361,26 +376,27 @@ __global__ void __launch_bounds__(kScanThreads) demux_scan_blocksums_kernel(
 // Emit perm / uniq_sid / csr / gathered_off and per-frame gather destinations.
 // dst_off[j] (in scratch, reusing the other pair buffer as u64) = byte offset of frame perm[j] in gathered.
 __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
-    u64 n, const uint2* __restrict__ sorted, const p2pt_desc* __restrict__ desc,
-    const uint32_t* __restrict__ misc, const uint32_t* __restrict__ blk_heads, const u64* __restrict__ blk_bytes,
-    u64 nblk, uint32_t max_streams, uint32_t* __restrict__ uniq_sid, u64* __restrict__ csr,
-    uint32_t* __restrict__ perm, uint32_t* __restrict__ k_out, u64* __restrict__ gathered_off,
-    u64* __restrict__ dst_off) {
+    u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx, const p2pt_desc* __restrict__ desc,
+    const u64* __restrict__ misc, const uint32_t* __restrict__ blk_heads, const u64* __restrict__ blk_bytes,
+    u64 nblk, uint32_t max_streams, uint32_t* __restrict__ uniq_sid, uint32_t* __restrict__ uniq_session,
+    u64* __restrict__ csr, uint32_t* __restrict__ perm, uint32_t* __restrict__ k_out,
+    u64* __restrict__ gathered_off, u64* __restrict__ dst_off) {
     const u64 m = misc[0];
     const u64 j = (u64)blockIdx.x * kScanThreads + threadIdx.x;
-    HeadBytes it = demux_item(j, m, sorted, desc);
+    HeadBytes it = demux_item(j, m, keys, idx, desc);
     HeadBytes tot;
     HeadBytes ex = block_scan_excl(it, tot);
     const uint32_t hbase = blk_heads[blockIdx.x];
     const u64 bbase = blk_bytes[blockIdx.x];
     if (j < m) {
-        const uint2 kv = sorted[j];
-        perm[j] = kv.y;
+        const u64 key = keys[j];
+        perm[j] = idx[j];
         dst_off[j] = bbase + ex.bytes;
         if (it.heads) {
             const uint32_t k = hbase + ex.heads;
             if (k < max_streams) {
-                uniq_sid[k] = kv.x;
+                uniq_sid[k] = (uint32_t)key;
+                if (uniq_session) uniq_session[k] = (uint32_t)(key >> 32);
                 csr[k] = j;
                 if (gathered_off) gathered_off[k] = bbase + ex.bytes;
             }
@@ -398,7 +414,7 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
 
 // Gather: one warp per decodable frame, body frames only (serve.rs:120-124 extend_from_slice).
 __global__ void __launch_bounds__(256) demux_gather_kernel(
-    const uint32_t* __restrict__ misc, const uint32_t* __restrict__ perm, const u64* __restrict__ dst_off,
+    const u64* __restrict__ misc, const uint32_t* __restrict__ perm, const u64* __restrict__ dst_off,
     const p2pt_desc* __restrict__ desc, const uint8_t* __restrict__ in,
     uint8_t* __restrict__ gathered, u64 gathered_cap, const uint32_t* __restrict__ k_out, uint32_t max_streams) {
     const u64 m = misc[0];

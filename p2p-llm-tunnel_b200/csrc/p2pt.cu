@@ -342,8 +342,10 @@ int32_t p2pt_frame_decode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t*
 
 uint64_t p2pt_frame_demux_scratch_bytes(uint64_t n) { return demux_scratch_bytes(n ? n : 1); }
 
-int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint8_t* in,
-                                      uint32_t max_streams, uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
+                                      const uint8_t* in,
+                                      uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                      uint64_t* csr, uint32_t* perm,
                                       uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
                                       uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes, void* stream) {
     if (!ctx) return P2PT_ERR_ARG;
@@ -362,24 +364,26 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     if (scratch_bytes < demux_scratch_bytes(n)) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: scratch too small");
     if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: scratch must be 256-byte aligned");
     DemuxScratch s = demux_carve(scratch, n);
-    CUDA_TRY(ctx, cudaMemsetAsync(s.misc, 0, 16, st));
-    demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, s.pairs[0], s.misc);
+    CUDA_TRY(ctx, cudaMemsetAsync(s.misc, 0, 32, st));
+    demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc);
     int cur = 0;
-    for (int pass = 0; pass < 5; pass++) {
-        demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.pairs[cur], desc, pass, s.hist, s.misc);
+    for (int pass = 0; pass < kSortPasses; pass++) {
+        demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.keys[cur], s.idx[cur], desc, pass, s.hist, s.misc);
         demux_scan_hist_kernel<<<1, 1024, 0, st>>>(s.hist, pass, s.misc);
-        demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.pairs[cur], s.pairs[cur ^ 1], desc, pass, s.hist, s.misc);
+        demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.keys[cur], s.idx[cur], s.keys[cur ^ 1],
+                                                                  s.idx[cur ^ 1], desc, pass, s.hist, s.misc);
         cur ^= 1;
     }
-    const uint2* sorted = s.pairs[cur];
-    u64* dst_off = reinterpret_cast<u64*>(s.pairs[cur ^ 1]);
+    const u64* skeys = s.keys[cur];
+    const uint32_t* sidx = s.idx[cur];
+    u64* dst_off = s.keys[cur ^ 1];                 // the idle key buffer holds per-frame gather offsets
     const u64 nblk = demux_scan_blocks(n);
-    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, sorted, desc, s.misc, s.blk_heads, s.blk_bytes);
+    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, skeys, sidx, desc, s.misc, s.blk_heads, s.blk_bytes);
     demux_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, s.blk_heads, s.blk_bytes);
-    demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, sorted, desc, s.misc, s.blk_heads, s.blk_bytes, nblk,
-                                                              max_streams, uniq_sid, (u64*)csr, perm, k_out,
+    demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, skeys, sidx, desc, s.misc, s.blk_heads, s.blk_bytes, nblk,
+                                                              max_streams, uniq_sid, uniq_session, (u64*)csr, perm, k_out,
                                                               (u64*)gathered_off, dst_off);
-    count_launch(ctx, 1 + 15 + 3);
+    count_launch(ctx, 1 + 3 * kSortPasses + 3);
     if (gathered) {
         demux_gather_kernel<<<grid_for(ctx, n, 8, 16), 256, 0, st>>>(s.misc, perm, dst_off, desc, in, gathered,
                                                                     gathered_cap, k_out, max_streams);
@@ -537,8 +541,10 @@ int32_t p2pt_frame_decode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, co
     return P2PT_OK;
 }
 
-int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint8_t* in, uint64_t in_bytes,
-                               uint32_t max_streams, uint32_t* uniq_sid, uint64_t* csr, uint32_t* perm,
+int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
+                               const uint8_t* in, uint64_t in_bytes,
+                               uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                               uint64_t* csr, uint32_t* perm,
                                uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off) {
     if (!ctx) return P2PT_ERR_ARG;
     if (!uniq_sid || !csr || !perm || !k_out) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null output");
@@ -551,12 +557,14 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
     const uint64_t sbytes = demux_scratch_bytes(n);
     const size_t gcap = gathered ? (size_t)gathered_cap : 0;
     const size_t ib = gathered ? (size_t)in_bytes : 0;
-    if (int32_t r = arena_reserve(ctx, pad256(24 * n) + pad256(ib) + pad256(4 * (size_t)max_streams) +
+    if (int32_t r = arena_reserve(ctx, pad256(24 * n) + pad256(4 * n) + pad256(ib) + 2 * pad256(4 * ((size_t)max_streams + 1)) +
                                            2 * pad256(8 * ((size_t)max_streams + 1)) + pad256(4 * n) + 256 +
                                            pad256(gcap) + pad256(sbytes) + 8192)) return r;
     p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
+    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
     uint8_t* d_in = arena_take<uint8_t>(ctx, ib + 1);
     uint32_t* d_uniq = arena_take<uint32_t>(ctx, max_streams + 1);
+    uint32_t* d_usess = arena_take<uint32_t>(ctx, max_streams + 1);
     uint64_t* d_csr = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
     uint64_t* d_goff = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
     uint32_t* d_perm = arena_take<uint32_t>(ctx, n);
@@ -564,8 +572,10 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
     uint8_t* d_g = arena_take<uint8_t>(ctx, gcap + 1);
     uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
     CUDA_TRY(ctx, cudaMemcpyAsync(d_desc, desc, 24 * n, cudaMemcpyHostToDevice, st));
+    if (session) CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, st));
     if (ib) CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in, ib, cudaMemcpyHostToDevice, st));
-    if (int32_t r = p2pt_frame_demux_batch_device(ctx, n, d_desc, d_in, max_streams, d_uniq, d_csr, d_perm, d_k,
+    if (int32_t r = p2pt_frame_demux_batch_device(ctx, n, d_desc, session ? d_sess : nullptr, d_in, max_streams, d_uniq,
+                                                  uniq_session ? d_usess : nullptr, d_csr, d_perm, d_k,
                                                   gathered ? d_g : nullptr, gathered_cap,
                                                   gathered_off ? d_goff : nullptr, d_scratch, sbytes, st)) return r;
     uint32_t k = 0;
@@ -574,6 +584,7 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
     *k_out = k;
     if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: more streams than max_streams");
     CUDA_TRY(ctx, cudaMemcpyAsync(uniq_sid, d_uniq, 4 * (size_t)k, cudaMemcpyDeviceToHost, st));
+    if (uniq_session) CUDA_TRY(ctx, cudaMemcpyAsync(uniq_session, d_usess, 4 * (size_t)k, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(csr, d_csr, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     const uint64_t m = csr[k];
@@ -748,6 +759,106 @@ int32_t p2pt_pipeline_open(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
     c.mode = kPipeOpen; c.n = n; c.session = session; c.in = rec; c.in_off = rec_off;
     c.out = out; c.out_off = out_off; c.desc = desc;
     return run_record_call(ctx, c, "pipeline_open");
+}
+
+int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
+                                 const uint8_t* rec, const uint64_t* rec_off,
+                                 uint8_t* out, p2pt_desc* desc,
+                                 uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                 uint64_t* csr, uint32_t* perm, uint32_t* k_out,
+                                 uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!uniq_sid || !csr || !perm || !k_out) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: null output");
+    if (n == 0) { *k_out = 0; csr[0] = 0; if (gathered_off) gathered_off[0] = 0; return P2PT_OK; }
+    if (!session || !rec || !rec_off || !desc) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: null argument");
+    if (gathered && !gathered_off) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: gather needs gathered_off");
+    if (n > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: n must fit in 32 bits");
+    if (!offsets_monotonic(rec_off, n)) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: offsets must be non-decreasing");
+    if (int32_t r = check_sessions(ctx)) return r;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    const size_t ibytes = rec_off[n] - rec_off[0];
+    const uint64_t sbytes = demux_scratch_bytes(n);
+    const size_t gcap = gathered ? (size_t)gathered_cap : 0;
+    if (int32_t r = arena_reserve(ctx, pad256(4 * n) + pad256(8 * (n + 1)) + 2 * pad256(ibytes) + pad256(24 * n) +
+                                           2 * pad256(4 * ((size_t)max_streams + 1)) + 2 * pad256(8 * ((size_t)max_streams + 1)) +
+                                           pad256(4 * n) + 256 + pad256(gcap) + pad256(sbytes) + 16384)) return r;
+    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
+    uint64_t* d_io = arena_take<uint64_t>(ctx, n + 1);
+    uint8_t* d_in = arena_take<uint8_t>(ctx, ibytes + 1);
+    uint8_t* d_out = arena_take<uint8_t>(ctx, ibytes + 1);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
+    uint32_t* d_uniq = arena_take<uint32_t>(ctx, (size_t)max_streams + 1);
+    uint32_t* d_usess = arena_take<uint32_t>(ctx, (size_t)max_streams + 1);
+    uint64_t* d_csr = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
+    uint64_t* d_goff = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
+    uint32_t* d_perm = arena_take<uint32_t>(ctx, n);
+    uint32_t* d_k = arena_take<uint32_t>(ctx, 1);
+    uint8_t* d_g = arena_take<uint8_t>(ctx, gcap + 1);
+    uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
+
+    cudaStream_t s0 = ctx->streams[0];
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_io, rec_off, 8 * (n + 1), cudaMemcpyHostToDevice, s0));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, s0));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->events[0], s0));
+    const int G = pick_group(ctx, n, ibytes);
+    uint64_t chunk = n;
+    if (ibytes > (32u << 20)) {
+        chunk = (16u << 20) / (ibytes / n + 1);
+        if (chunk < 1024) chunk = 1024;
+    }
+    int si = 0;
+    for (uint64_t r0 = 0; r0 < n; r0 += chunk, si = (si + 1) % kStreams) {
+        const uint64_t r1 = r0 + chunk < n ? r0 + chunk : n;
+        cudaStream_t st = ctx->streams[si];
+        CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[0], 0));
+        const size_t b0 = rec_off[r0] - rec_off[0], b1 = rec_off[r1] - rec_off[0];
+        if (b1 > b0) CUDA_TRY(ctx, cudaMemcpyAsync(d_in + b0, rec + rec_off[r0], b1 - b0, cudaMemcpyHostToDevice, st));
+        GcmArgs a = {};
+        a.n = r1 - r0; a.session = d_sess + r0; a.n_sessions = ctx->n_sessions; a.keys = ctx->keys_remote;
+        a.in = d_in - rec_off[0]; a.in_off = (const u64*)(d_io + r0);
+        a.out = d_out - rec_off[0]; a.out_off = (const u64*)(d_io + r0);
+        a.desc = d_desc + r0;
+        if (int32_t r = launch_gcm<kPipeOpen>(ctx, a, G, st)) return r;
+        if (out && b1 > b0) CUDA_TRY(ctx, cudaMemcpyAsync(out + rec_off[r0], d_out + b0, b1 - b0, cudaMemcpyDeviceToHost, st));
+    }
+    for (int i = 1; i < kStreams; i++) {          // join the chunk streams into stream 0
+        CUDA_TRY(ctx, cudaEventRecord(ctx->events[i], ctx->streams[i]));
+        CUDA_TRY(ctx, cudaStreamWaitEvent(s0, ctx->events[i], 0));
+    }
+    CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, s0));
+    if (int32_t r = p2pt_frame_demux_batch_device(ctx, n, d_desc, d_sess, d_out - rec_off[0], max_streams, d_uniq,
+                                                  uniq_session ? d_usess : nullptr, d_csr, d_perm, d_k,
+                                                  gathered ? d_g : nullptr, gathered_cap,
+                                                  gathered_off ? d_goff : nullptr, d_scratch, sbytes, s0)) return r;
+    uint32_t k = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&k, d_k, 4, cudaMemcpyDeviceToHost, s0));
+    CUDA_TRY(ctx, cudaStreamSynchronize(s0));
+    *k_out = k;
+    if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "pipeline_open_demux: more streams than max_streams");
+    CUDA_TRY(ctx, cudaMemcpyAsync(uniq_sid, d_uniq, 4 * (size_t)k, cudaMemcpyDeviceToHost, s0));
+    if (uniq_session) CUDA_TRY(ctx, cudaMemcpyAsync(uniq_session, d_usess, 4 * (size_t)k, cudaMemcpyDeviceToHost, s0));
+    CUDA_TRY(ctx, cudaMemcpyAsync(csr, d_csr, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, s0));
+    if (gathered_off) CUDA_TRY(ctx, cudaMemcpyAsync(gathered_off, d_goff, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, s0));
+    CUDA_TRY(ctx, cudaStreamSynchronize(s0));
+    const uint64_t m = csr[k];
+    if (m) CUDA_TRY(ctx, cudaMemcpyAsync(perm, d_perm, 4 * m, cudaMemcpyDeviceToHost, s0));
+    if (gathered) {
+        if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "pipeline_open_demux: gathered_cap too small");
+        // split the big copy over the streams so both DMA engines stay busy
+        const uint64_t total = gathered_off[k];
+        const uint64_t piece = (total + kStreams - 1) / kStreams;
+        CUDA_TRY(ctx, cudaEventRecord(ctx->events[0], s0));
+        for (int i = 0; i < kStreams && piece; i++) {
+            const uint64_t o = (uint64_t)i * piece;
+            if (o >= total) break;
+            const uint64_t len = o + piece <= total ? piece : total - o;
+            CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->streams[i], ctx->events[0], 0));
+            CUDA_TRY(ctx, cudaMemcpyAsync(gathered + o, d_g + o, len, cudaMemcpyDeviceToHost, ctx->streams[i]));
+        }
+    }
+    for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->streams[i]));
+    return P2PT_OK;
 }
 
 }  // extern "C"

@@ -55,16 +55,20 @@ def frame_decode(buf, in_off):
     return desc
 
 
-def frame_demux(desc, buf):
+def frame_demux(desc, buf, session=None):
     desc = np.ascontiguousarray(desc, DESC_DTYPE); buf = _u8(buf)
     n = len(desc)
+    if session is not None:
+        session = np.ascontiguousarray(session, np.uint32)
+    usess = np.zeros(n + 1, np.uint32)
     uniq = np.zeros(n + 1, np.uint32); csr = np.zeros(n + 1, np.uint64); perm = np.zeros(max(n, 1), np.uint32)
     body = (desc["status"] == 0) & ((desc["msg_type"] == 11) | (desc["msg_type"] == 21))
     gathered = np.zeros(max(int(desc["pay_len"][body].sum()), 1), np.uint8)
     goff = np.zeros(n + 1, np.uint64)
-    k = lib().orc_frame_demux_batch(C.c_uint64(n), _p(desc), _p(buf), _p(uniq), _p(csr), _p(perm), _p(gathered), _p(goff))
+    k = lib().orc_frame_demux_batch(C.c_uint64(n), _p(desc), _p(session), _p(buf), _p(uniq), _p(usess), _p(csr),
+                                    _p(perm), _p(gathered), _p(goff))
     m = int(csr[k])
-    return {"k": k, "uniq_sid": uniq[:k].copy(), "csr": csr[:k + 1].copy(), "perm": perm[:m].copy(),
+    return {"k": k, "uniq_sid": uniq[:k].copy(), "uniq_session": usess[:k].copy(), "csr": csr[:k + 1].copy(), "perm": perm[:m].copy(),
             "gathered_off": goff[:k + 1].copy(), "gathered": gathered[:int(goff[k])].copy()}
 
 

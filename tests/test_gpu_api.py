@@ -113,14 +113,16 @@ def test_device_pointer_entry_points(ctx):
     uniq = torch.zeros(n + 1, dtype=torch.int32, device=dev); csr = torch.zeros(n + 1, dtype=torch.int64, device=dev)
     perm = torch.zeros(n, dtype=torch.int32, device=dev); k = torch.zeros(1, dtype=torch.int32, device=dev)
     gathered = torch.zeros(n * 1200, dtype=torch.uint8, device=dev); goff = torch.zeros(n + 1, dtype=torch.int64, device=dev)
-    ctx.call("p2pt_frame_demux_batch_device", n, desc, out, n, uniq, csr, perm, k, gathered, n * 1200, goff,
-             scratch, scratch_bytes, s)
+    usess = torch.zeros(n + 1, dtype=torch.int32, device=dev)
+    ctx.call("p2pt_frame_demux_batch_device", n, desc, d["session"], out, n, uniq, usess, csr, perm, k, gathered,
+             n * 1200, goff, scratch, scratch_bytes, s)
     torch.cuda.synchronize()
     from p2p_llm_tunnel_b200._lib import DESC_DTYPE
     dn = desc.cpu().numpy().view(DESC_DTYPE)
-    exp = ob.frame_demux(dn, out.cpu().numpy())
+    exp = ob.frame_demux(dn, out.cpu().numpy(), w["session"])
     kk = int(k.item())
-    assert kk == exp["k"] == 4
+    assert kk == exp["k"] == 32 * 4
+    assert np.array_equal(usess.cpu().numpy()[:kk].astype(np.uint32), exp["uniq_session"])
     assert np.array_equal(uniq.cpu().numpy()[:kk].astype(np.uint32), exp["uniq_sid"])
     assert np.array_equal(csr.cpu().numpy()[:kk + 1].astype(np.uint64), exp["csr"])
     assert np.array_equal(perm.cpu().numpy().astype(np.uint32), exp["perm"])

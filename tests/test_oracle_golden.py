@@ -125,3 +125,13 @@ def test_demux_semantics_small():
     assert list(r["perm"]) == [5, 1, 6, 0, 3, 4]
     assert list(r["gathered_off"]) == [0, 0, 1, 5]
     assert r["gathered"].tobytes() == b"baacc"
+
+
+def test_demux_session_namespaces():
+    frames = [bytes([21, 0, 0, 0, 1]) + b"a", bytes([21, 0, 0, 0, 1]) + b"b", bytes([21, 0, 0, 0, 1]) + b"c"]
+    buf = np.frombuffer(b"".join(frames), np.uint8)
+    off = np.array([0, 6, 12, 18], np.uint64)
+    d = ob.frame_decode(buf, off)
+    r = ob.frame_demux(d, buf, np.array([1, 0, 1], np.uint32))
+    assert list(r["uniq_session"]) == [0, 1] and list(r["uniq_sid"]) == [1, 1]
+    assert list(r["perm"]) == [1, 0, 2] and r["gathered"].tobytes() == b"bac"
