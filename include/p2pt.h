@@ -181,6 +181,30 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
                                       uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
                                       uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes,
                                       void* stream);
+/* No counterpart in the reference (it has no device memory to manage).
+ * Same work and same results as p2pt_frame_demux_batch_device, for callers that may not allocate
+ * device memory while they run and have nowhere to take `scratch` from: for example a reader task
+ * that was handed a fixed device-memory budget at start-up because an inference server on the same
+ * GPU owns the rest of HBM, or a per-connection loop that cannot afford cudaMalloc / cudaFree
+ * because those take the driver's allocator lock and synchronise the whole device, stalling every
+ * other session's stream.  The scratch lives in a static device array inside the library
+ * (about 6.9 MB, resident on every GPU that loads the library until the process exits), which
+ * bounds the batch: n <= P2PT_NOALLOC_MAX_FRAMES, larger batches are refused with
+ * P2PT_ERR_CAPACITY.  The call itself performs no cudaMalloc / cudaFree and uses no allocating
+ * library routine.
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress, which
+ * may make the driver load the module); make that first call during start-up, before any stream
+ * capture begins.  All calls on a device share the one array and it keeps the previous call's
+ * contents; the call clears the few words that must start at zero itself.  Two calls whose
+ * kernels can overlap on the GPU (different streams, or different contexts/threads on the same
+ * device) race on the array: serialise them. */
+#define P2PT_NOALLOC_MAX_FRAMES 262144u
+int32_t p2pt_frame_demux_batch_device_noalloc(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
+                                              const uint8_t* in,
+                                              uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                              uint64_t* csr, uint32_t* perm,
+                                              uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
+                                              uint64_t* gathered_off, void* stream);
 int32_t p2pt_dtls_gcm_seal_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
                                         const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
                                         uint8_t* rec, const uint64_t* rec_off, uint8_t* status, void* stream);

@@ -44,6 +44,7 @@ SIGNATURES = {
     "p2pt_frame_decode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp]),
     "p2pt_frame_demux_scratch_bytes": (_u64, [_u64]),
     "p2pt_frame_demux_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _u64, _vp]),
+    "p2pt_frame_demux_batch_device_noalloc": (_i32, [_vp, _u64, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp]),
     "p2pt_dtls_gcm_seal_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_dtls_gcm_open_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_pipeline_seal_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

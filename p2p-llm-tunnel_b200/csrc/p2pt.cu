@@ -393,6 +393,63 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     return P2PT_OK;
 }
 
+}  // extern "C" (reopened below)
+
+// ---- demux without any allocation ------------------------------------------------------------------
+// Scratch for up to P2PT_NOALLOC_MAX_FRAMES frames, laid out exactly as demux_carve() expects.  It is a
+// file-scope device array: in host code its name is only a handle, so the device address is looked up
+// once per device with cudaGetSymbolAddress (below) and that pointer is what the kernels receive.
+namespace {
+constexpr uint64_t na_align(uint64_t x) { return (x + 255) & ~(uint64_t)255; }
+constexpr uint64_t kNoAllocFrames = P2PT_NOALLOC_MAX_FRAMES;
+constexpr uint64_t kNoAllocBlocks = (kNoAllocFrames + kScanThreads - 1) / kScanThreads;
+constexpr uint64_t kNoAllocBytes =
+    2 * na_align(kNoAllocFrames * sizeof(uint64_t)) + 2 * na_align(kNoAllocFrames * sizeof(uint32_t)) +
+    na_align((uint64_t)kRadix * kSortBlocks * sizeof(uint32_t)) + na_align((kNoAllocBlocks + 1) * sizeof(uint64_t)) +
+    na_align((kNoAllocBlocks + 1) * sizeof(uint32_t)) + 256;
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_addr[kNoAllocMaxDevices] = {};
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_demux_static_scratch[kNoAllocBytes];
+
+extern "C" {
+
+int32_t p2pt_frame_demux_batch_device_noalloc(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
+                                              const uint8_t* in,
+                                              uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                              uint64_t* csr, uint32_t* perm,
+                                              uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
+                                              uint64_t* gathered_off, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n > kNoAllocFrames)
+        return set_err(ctx, P2PT_ERR_CAPACITY,
+                       "frame_demux (no-alloc): n = " + std::to_string(n) + " exceeds P2PT_NOALLOC_MAX_FRAMES (" +
+                           std::to_string(kNoAllocFrames) + "); split the batch or pass your own scratch to "
+                           "p2pt_frame_demux_batch_device");
+    if (ctx->device < 0 || ctx->device >= kNoAllocMaxDevices)
+        return set_err(ctx, P2PT_ERR_ARG, "frame_demux (no-alloc): device index beyond the per-device address table");
+    if (demux_scratch_bytes(n ? n : 1) > kNoAllocBytes)
+        return set_err(ctx, P2PT_ERR_STATE, "frame_demux (no-alloc): static scratch smaller than the layout needs");
+    DeviceGuard dg(ctx->device);                       // the symbol address is per device: look it up with ours current
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_addr[ctx->device]) {            // first call on this device: one-time set-up
+            void* p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress(&p, g_demux_static_scratch);
+            if (e != cudaSuccess || !p)
+                return set_err(ctx, P2PT_ERR_CUDA, std::string("cudaGetSymbolAddress(static demux scratch): ") + cudaGetErrorString(e));
+            g_noalloc_addr[ctx->device] = p;
+        }
+        scratch = g_noalloc_addr[ctx->device];
+    }
+    // same kernels, same order as the caller-scratch entry point; it zeroes its control words itself
+    return p2pt_frame_demux_batch_device(ctx, n, desc, session, in, max_streams, uniq_sid, uniq_session, csr, perm, k_out,
+                                         gathered, gathered_cap, gathered_off, scratch, kNoAllocBytes, stream);
+}
+
 static int32_t check_sessions(p2pt_ctx* ctx) {
     if (!ctx->n_sessions) return set_err(ctx, P2PT_ERR_STATE, "no sessions loaded: call p2pt_sessions_load first");
     return P2PT_OK;
