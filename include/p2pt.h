@@ -87,6 +87,8 @@ uint64_t    p2pt_launch_count(p2pt_ctx* ctx);
 /* tuning knobs.  "gcm_group_width": lanes that share one record in the seal/open kernels
  * (4, 8, 16 or 32; 0 = choose from the batch's mean record length). */
 int32_t     p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value);
+/* read-only facts: "sm_count", "lut_slack", "gcm_group_width", "n_sessions", "gcm_threads"; -1 if unknown */
+int64_t     p2pt_ctx_get_info(p2pt_ctx* ctx, const char* name);
 
 /* ---- DTLS session keys: CryptoGcm::new(local_key, local_write_iv, remote_key, remote_write_iv)
  *      (webrtc-dtls 0.10.0 crypto_gcm.rs).  n sessions; keys n x 16 bytes, ivs n x 4 bytes.

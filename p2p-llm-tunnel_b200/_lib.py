@@ -50,6 +50,7 @@ SIGNATURES = {
     "p2pt_pipeline_seal_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_pipeline_open_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_ctx_set_option": (_i32, [_vp, C.c_char_p, C.c_int64]),
+    "p2pt_ctx_get_info": (C.c_int64, [_vp, C.c_char_p]),
 }
 
 
@@ -138,6 +139,9 @@ class Context:
 
     def launch_count(self):
         return int(self.lib.p2pt_launch_count(self.h))
+
+    def get_info(self, name):
+        return int(self.lib.p2pt_ctx_get_info(self.h, name.encode()))
 
     def set_option(self, name, value):
         self._check(self.lib.p2pt_ctx_set_option(self.h, name.encode(), int(value)))

@@ -62,29 +62,90 @@ struct SmemLut {     // hot path: bank-replicated shared-memory tables
     }
 };
 
-template <class Lut>
-__device__ __forceinline__ void aes128_encrypt(const Lut& lut, const uint32_t (&rk)[44],
+// Round keys either in registers (set-up kernel) or in the group's shared-memory slot (hot path:
+// one LDS.128 per round, every lane of the group reads the same address -> broadcast).
+struct RegKeys {
+    const uint32_t (&rk)[44];
+    __device__ __forceinline__ uint4 get(int r) const { return make_uint4(rk[4 * r], rk[4 * r + 1], rk[4 * r + 2], rk[4 * r + 3]); }
+};
+struct SmemKeys {
+    uint32_t addr;     // shared address of 11 x 16 bytes
+    __device__ __forceinline__ uint4 get(int r) const {
+        uint4 v;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr + 16u * (uint32_t)r));
+        return v;
+    }
+};
+
+template <class Lut, class Keys>
+__device__ __forceinline__ void aes128_encrypt(const Lut& lut, const Keys& keys,
                                                uint32_t& s0, uint32_t& s1, uint32_t& s2, uint32_t& s3) {
-    s0 ^= rk[0]; s1 ^= rk[1]; s2 ^= rk[2]; s3 ^= rk[3];
+    {
+        const uint4 k = keys.get(0);
+        s0 ^= k.x; s1 ^= k.y; s2 ^= k.z; s3 ^= k.w;
+    }
 #pragma unroll
     for (int r = 1; r < 10; r++) {
-        uint32_t t0 = lut.template look<0, 0>(s0) ^ lut.template look<1, 1>(s1) ^ lut.template look<2, 2>(s2) ^ lut.template look<3, 3>(s3) ^ rk[4 * r + 0];
-        uint32_t t1 = lut.template look<0, 0>(s1) ^ lut.template look<1, 1>(s2) ^ lut.template look<2, 2>(s3) ^ lut.template look<3, 3>(s0) ^ rk[4 * r + 1];
-        uint32_t t2 = lut.template look<0, 0>(s2) ^ lut.template look<1, 1>(s3) ^ lut.template look<2, 2>(s0) ^ lut.template look<3, 3>(s1) ^ rk[4 * r + 2];
-        uint32_t t3 = lut.template look<0, 0>(s3) ^ lut.template look<1, 1>(s0) ^ lut.template look<2, 2>(s1) ^ lut.template look<3, 3>(s2) ^ rk[4 * r + 3];
+        const uint4 k = keys.get(r);
+        uint32_t t0 = lut.template look<0, 0>(s0) ^ lut.template look<1, 1>(s1) ^ lut.template look<2, 2>(s2) ^ lut.template look<3, 3>(s3) ^ k.x;
+        uint32_t t1 = lut.template look<0, 0>(s1) ^ lut.template look<1, 1>(s2) ^ lut.template look<2, 2>(s3) ^ lut.template look<3, 3>(s0) ^ k.y;
+        uint32_t t2 = lut.template look<0, 0>(s2) ^ lut.template look<1, 1>(s3) ^ lut.template look<2, 2>(s0) ^ lut.template look<3, 3>(s1) ^ k.z;
+        uint32_t t3 = lut.template look<0, 0>(s3) ^ lut.template look<1, 1>(s0) ^ lut.template look<2, 2>(s1) ^ lut.template look<3, 3>(s2) ^ k.w;
         s0 = t0; s1 = t1; s2 = t2; s3 = t3;
     }
     // last round: SubBytes + ShiftRows only.  S[x] sits in byte 0 of Te2, byte 1 of Te3, byte 2 of
     // Te0 and byte 3 of Te1, i.e. already in the byte lane it is needed in.
-#define P2PT_LAST(a, b, c, d, k)                                                             \
+    const uint4 k = keys.get(10);
+#define P2PT_LAST(a, b, c, d, kw)                                                            \
     (__byte_perm(__byte_perm(lut.template look<0, 2>(a), lut.template look<1, 3>(b), 0x0050), \
-                 __byte_perm(lut.template look<2, 0>(c), lut.template look<3, 1>(d), 0x7200), 0x7610) ^ rk[40 + k])
-    uint32_t o0 = P2PT_LAST(s0, s1, s2, s3, 0);
-    uint32_t o1 = P2PT_LAST(s1, s2, s3, s0, 1);
-    uint32_t o2 = P2PT_LAST(s2, s3, s0, s1, 2);
-    uint32_t o3 = P2PT_LAST(s3, s0, s1, s2, 3);
+                 __byte_perm(lut.template look<2, 0>(c), lut.template look<3, 1>(d), 0x7200), 0x7610) ^ kw)
+    uint32_t o0 = P2PT_LAST(s0, s1, s2, s3, k.x);
+    uint32_t o1 = P2PT_LAST(s1, s2, s3, s0, k.y);
+    uint32_t o2 = P2PT_LAST(s2, s3, s0, s1, k.z);
+    uint32_t o3 = P2PT_LAST(s3, s0, s1, s2, k.w);
 #undef P2PT_LAST
     s0 = o0; s1 = o1; s2 = o2; s3 = o3;
+}
+
+// GF(2^128) multiply with the prepared multiplier in shared memory (9 rows of 4 class masks):
+// same arithmetic as gf128_mul in gcm_math.cuh, one LDS.128 per 32x32 product instead of 36 registers.
+__device__ __forceinline__ uint64_t clmul32_s(uint32_t a, uint32_t key_addr, int row) {
+    uint32_t b[4];
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]) : "r"(key_addr + 16u * (uint32_t)row));
+    return clmul32(a, b);
+}
+__device__ __forceinline__ void clmul64_s(uint32_t lo, uint32_t hi, uint32_t mid, uint32_t key_addr, int r,
+                                          uint64_t& out_lo, uint64_t& out_hi) {
+    uint64_t p = clmul32_s(lo, key_addr, r);
+    uint64_t q = clmul32_s(hi, key_addr, r + 1);
+    uint64_t m = clmul32_s(mid, key_addr, r + 2) ^ p ^ q;
+    out_lo = p ^ (m << 32);
+    out_hi = q ^ (m >> 32);
+}
+__device__ __forceinline__ U128 gf128_reduce(uint64_t pl, uint64_t ph, uint64_t ql, uint64_t qh, uint64_t rl, uint64_t rh) {
+    rl ^= pl ^ ql;
+    rh ^= ph ^ qh;
+    uint64_t v0 = pl, v1 = ph ^ rl, v2 = ql ^ rh, v3 = qh;
+    v3 = (v3 << 1) | (v2 >> 63);
+    v2 = (v2 << 1) | (v1 >> 63);
+    v1 = (v1 << 1) | (v0 >> 63);
+    v0 = (v0 << 1);
+    v2 ^= v0 ^ (v0 >> 1) ^ (v0 >> 2) ^ (v0 >> 7);
+    v1 ^= (v0 << 63) ^ (v0 << 62) ^ (v0 << 57);
+    v3 ^= v1 ^ (v1 >> 1) ^ (v1 >> 2) ^ (v1 >> 7);
+    v2 ^= (v1 << 63) ^ (v1 << 62) ^ (v1 << 57);
+    U128 z;
+    z.w[0] = (uint32_t)v2; z.w[1] = (uint32_t)(v2 >> 32);
+    z.w[2] = (uint32_t)v3; z.w[3] = (uint32_t)(v3 >> 32);
+    return z;
+}
+__device__ __forceinline__ U128 gf128_mul_s(const U128& x, uint32_t key_addr) {
+    const uint32_t x0 = x.w[0], x1 = x.w[1], x2 = x.w[2], x3 = x.w[3];
+    uint64_t pl, ph, ql, qh, rl, rh;
+    clmul64_s(x0, x1, x0 ^ x1, key_addr, 0, pl, ph);
+    clmul64_s(x2, x3, x2 ^ x3, key_addr, 3, ql, qh);
+    clmul64_s(x0 ^ x2, x1 ^ x3, x0 ^ x1 ^ x2 ^ x3, key_addr, 6, rl, rh);
+    return gf128_reduce(pl, ph, ql, qh, rl, rh);
 }
 
 // ---- session set-up: key schedule, H, H^1..H^32 (one thread per key) ------------------------------
@@ -121,7 +182,8 @@ __global__ void __launch_bounds__(128) session_expand_kernel(uint32_t n, const u
     // H = AES_K(0^128)
     uint32_t h0 = 0, h1 = 0, h2 = 0, h3 = 0;
     GlobalLut lut;
-    aes128_encrypt(lut, rk, h0, h1, h2, h3);
+    RegKeys rkeys{rk};
+    aes128_encrypt(lut, rkeys, h0, h1, h2, h3);
     const U128 H = block_to_u128(h0, h1, h2, h3);
     GhashKey hk;
     ghash_key_prepare(H, hk);
@@ -154,10 +216,34 @@ struct GcmArgs {
     p2pt_desc* desc;              // pipe-open
 };
 
-constexpr int kGcmThreads = 512;
+constexpr int kGcmThreads = 1024;
+constexpr uint32_t kGroupSlotBytes = 336;   // 11 x 16 B round keys + 9 x 16 B GHASH multiplier rows, padded
+                                            // so that neighbouring groups' rows fall in different banks
+
+// Shared-memory map of the record kernel.  The T-tables must start on a 64 KiB boundary of the
+// shared window (PRMT addressing) and the window itself starts a little above 0 (the first KiB is
+// reserved by the system), so there is a gap of `slack` bytes below the tables: the per-group key
+// slots fill that gap first and continue after the tables.
+__host__ __device__ constexpr uint32_t gcm_smem_bytes(int G, uint32_t slack) {
+    const uint32_t groups = kGcmThreads / G, low = slack / kGroupSlotBytes;
+    return slack + kLutBytes + (groups > low ? (groups - low) * kGroupSlotBytes : 0u);
+}
 
 __device__ __forceinline__ uint32_t shared_addr(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// bytes beyond `nb` of a 16-byte block (four LE words) cleared
+__device__ __forceinline__ void mask_block(uint4& y, uint32_t nb) {
+    if (nb >= 16) return;
+    const uint32_t m0 = nb >= 4 ? 0xffffffffu : (nb ? (0xffffffffu >> (32 - 8 * nb)) : 0u);
+    const uint32_t m1 = nb >= 8 ? 0xffffffffu : (nb > 4 ? (0xffffffffu >> (32 - 8 * (nb - 4))) : 0u);
+    const uint32_t m2 = nb >= 12 ? 0xffffffffu : (nb > 8 ? (0xffffffffu >> (32 - 8 * (nb - 8))) : 0u);
+    const uint32_t m3 = nb > 12 ? (0xffffffffu >> (32 - 8 * (nb - 12))) : 0u;
+    y.x &= m0; y.y &= m1; y.z &= m2; y.w &= m3;
 }
 
 template <int G, int MODE>
@@ -165,6 +251,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
     extern __shared__ __align__(16) uint8_t dyn_smem[];
     constexpr bool SEAL = (MODE == kSeal || MODE == kPipeSeal);
     constexpr uint32_t GMASK_BASE = (G == 32) ? 0xffffffffu : ((1u << G) - 1u);
+    constexpr uint32_t PREFIX = SEAL ? 21u : 13u;
 
     const int lane = threadIdx.x & 31;
     const int j = lane & (G - 1);                        // lane inside the record group
@@ -187,6 +274,11 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
     __syncthreads();
     SmemLut lut;
     lut.lb = tbase + 4u * (uint32_t)lane;
+    // this group's key slot: round keys at +0, GHASH multiplier rows at +176
+    const uint32_t n_low = (tbase - sbase) / kGroupSlotBytes, gi = (uint32_t)(threadIdx.x / G);
+    const uint32_t slot = gi < n_low ? sbase + gi * kGroupSlotBytes : tbase + kLutBytes + (gi - n_low) * kGroupSlotBytes;
+    SmemKeys rkeys; rkeys.addr = slot;
+    const uint32_t gkey = slot + 176;
 
     const u64 groups_per_cta = kGcmThreads / G;
     const u64 group0 = (u64)blockIdx.x * groups_per_cta + (threadIdx.x / G);
@@ -250,19 +342,45 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
         }
 
         const uint32_t nc = (L + 15) >> 4;          // CTR / ciphertext blocks
+        const uint32_t nfull = L >> 4;              // of which complete
         const uint32_t slots = nc + 2;              // + J0/AAD slot + length slot
-        constexpr uint32_t PREFIX = SEAL ? 21u : 13u;
         uint8_t* ob0 = obase + PREFIX;              // output body byte 0
-        const unsigned so = (unsigned)((uintptr_t)ob0 & 15);
 
-        // ------------------------------------------------------------------ per-record key material
-        uint32_t rk[44];
+        // Input side: blocks whose five covering aligned words lie inside the body are loaded as
+        // 32-bit words + funnel shift; the others (record edges) go through the bounded byte path.
+        const unsigned ish = (unsigned)((uintptr_t)body0 & 3);
+        const uint8_t* ib4 = body0 - ish;           // word-aligned address of block 0's first covering word
+        int c_fast_lo = 0, c_fast_hi = -1;          // inclusive range of blocks on the fast input path
         {
-            const uint4* p = reinterpret_cast<const uint4*>(sk->rk);
+            // the covering words must stay inside this item's own input bytes [ibase, ibase + ilen):
+            // ib4 + 16c >= ibase  and  ib4 + 16c + (ish ? 20 : 16) <= ibase + ilen
+            const long long lo_gap = (long long)(ibase - ib4);
+            c_fast_lo = lo_gap > 0 ? (int)((lo_gap + 15) >> 4) : 0;
+            const long long room = (long long)((ibase + ilen) - ib4) - (ish ? 20 : 16);
+            c_fast_hi = room >= 0 ? (int)(room >> 4) : -1;
+            if (c_fast_hi > (int)nfull - 1) c_fast_hi = (int)nfull - 1;
+        }
+        // Output side: every complete block is stored as four aligned 32-bit words, each word
+        // funnel-shifted against the previous block's last word (from the neighbouring lane).
+        const unsigned osh = (unsigned)((uintptr_t)ob0 & 3);
+        uint8_t* ob4 = ob0 - osh;
+
+        // ------------------------------------------------------------------ per-record key material -> shared
+        __syncwarp(gmask);                                   // previous record's readers are done
+        {
+            const uint4* rp = reinterpret_cast<const uint4*>(sk->rk);
+            for (int q = j; q < 11; q += G) {
+                const uint4 v = __ldg(rp + q);
+                sts128(slot + 16u * q, v.x, v.y, v.z, v.w);
+            }
+            const uint4 hv = __ldg(reinterpret_cast<const uint4*>(sk->hpow[G - 1]));     // H^G
+            uint32_t o[9];
+            o[0] = hv.x; o[1] = hv.y; o[2] = hv.x ^ hv.y; o[3] = hv.z; o[4] = hv.w; o[5] = hv.z ^ hv.w;
+            o[6] = hv.x ^ hv.z; o[7] = hv.y ^ hv.w; o[8] = o[6] ^ o[7];
 #pragma unroll
-            for (int q = 0; q < 11; q++) {
-                uint4 v = __ldg(p + q);
-                rk[4 * q] = v.x; rk[4 * q + 1] = v.y; rk[4 * q + 2] = v.z; rk[4 * q + 3] = v.w;
+            for (int q = 0; q < 9; q++) {
+                if ((q % G) == j)
+                    sts128(gkey + 16u * q, o[q] & 0x11111111u, o[q] & 0x22222222u, o[q] & 0x44444444u, o[q] & 0x88888888u);
             }
         }
         const uint32_t ivw = __ldg(&sk->iv);
@@ -276,16 +394,11 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
             n1 = (uint32_t)__ldg(ibase + 17) | ((uint32_t)__ldg(ibase + 18) << 8) |
                  ((uint32_t)__ldg(ibase + 19) << 16) | ((uint32_t)__ldg(ibase + 20) << 24);
         }
-        GhashKey kG;
-        {
-            uint4 v = __ldg(reinterpret_cast<const uint4*>(sk->hpow[G - 1]));
-            U128 hg; hg.w[0] = v.x; hg.w[1] = v.y; hg.w[2] = v.z; hg.w[3] = v.w;
-            ghash_key_prepare(hg, kG);
-        }
+        __syncwarp(gmask);                                   // key slot visible to the whole group
 
         U128 acc; acc.w[0] = acc.w[1] = acc.w[2] = acc.w[3] = 0;
         uint4 ej0 = make_uint4(0, 0, 0, 0);                  // E_K(J0), valid in group lane 0
-        uint4 carry = make_uint4(0, 0, 0, 0);                // output block of lane G-1, previous round
+        uint32_t carry3 = 0;                                 // last word of lane G-1's block, previous round
         uint32_t fh0 = 0, fh1 = 0;                           // pipe-open: first 8 plaintext bytes (lane 1)
         uint32_t last_u = 0xffffffffu;
 
@@ -294,81 +407,91 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
             const uint32_t u = t * G + j;
             const int c = (int)u - 1;                        // body block index; -1 = J0/AAD slot
             const bool active = u < slots;
-            const bool is_j0 = (u == 0);
-            const bool is_len = (u == slots - 1);
-            const bool is_data = active && !is_j0 && !is_len;
 
             // ---- AES-CTR keystream for counter c + 2 (J0 = counter 1)
             uint32_t k0 = ivw, k1 = n0, k2 = n1, k3 = bswap32((uint32_t)(c + 2));
-            aes128_encrypt(lut, rk, k0, k1, k2, k3);
+            aes128_encrypt(lut, rkeys, k0, k1, k2, k3);
 
-            // ---- the slot's block
             uint4 oblk = make_uint4(0, 0, 0, 0);             // bytes this lane contributes to the output stream
-            int ovalid_lo = 0, ovalid_hi = 0;                // valid byte range of oblk
             U128 gin; gin.w[0] = gin.w[1] = gin.w[2] = gin.w[3] = 0;
-            if (is_data) {
-                const uint32_t pos = 16u * (uint32_t)c;
-                const uint32_t nb = (L - pos) < 16u ? (L - pos) : 16u;
-                uint4 x = load16_bounded(body0 + pos, body_lo, body_hi);
-                if (MODE == kPipeSeal && c == 0) {           // synthesise [type][sid BE] in front of the payload
-                    const uint32_t sid = __ldg(a.sids + i);
-                    x.x = (uint32_t)__ldg(a.types + i) | ((sid >> 24) << 8) | (((sid >> 16) & 0xff) << 16) | (((sid >> 8) & 0xff) << 24);
-                    x.y = (x.y & 0xffffff00u) | (sid & 0xff);
-                }
-                uint4 y = make_uint4(x.x ^ k0, x.y ^ k1, x.z ^ k2, x.w ^ k3);
-                if (nb < 16) {                               // zero the bytes past the end of the body
-                    const uint32_t m0 = nb >= 4 ? 0xffffffffu : (nb ? (0xffffffffu >> (32 - 8 * nb)) : 0u);
-                    const uint32_t m1 = nb >= 8 ? 0xffffffffu : (nb > 4 ? (0xffffffffu >> (32 - 8 * (nb - 4))) : 0u);
-                    const uint32_t m2 = nb >= 12 ? 0xffffffffu : (nb > 8 ? (0xffffffffu >> (32 - 8 * (nb - 8))) : 0u);
-                    const uint32_t m3 = nb > 12 ? (0xffffffffu >> (32 - 8 * (nb - 12))) : 0u;
-                    y.x &= m0; y.y &= m1; y.z &= m2; y.w &= m3;
-                }
-                const uint4 ct = SEAL ? y : x;               // GHASH always runs over the ciphertext
+            const bool fast_in = (c >= c_fast_lo && c <= c_fast_hi);
+            const bool full_blk = (c >= 0 && (uint32_t)c < nfull);
+            int ovalid_lo = 0, ovalid_hi = 0;                // valid byte range of oblk (edge slots)
+
+            if (fast_in) {
+                // -------- interior block: five aligned words, one funnel shift each
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(ib4 + 16 * (size_t)c);
+                const uint32_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2), w3 = __ldg(wp + 3);
+                const uint32_t w4 = ish ? __ldg(wp + 4) : 0u;
+                const unsigned sh = ish * 8;
+                uint4 x;
+                x.x = __funnelshift_r(w0, w1, sh); x.y = __funnelshift_r(w1, w2, sh);
+                x.z = __funnelshift_r(w2, w3, sh); x.w = __funnelshift_r(w3, w4, sh);
+                const uint4 y = make_uint4(x.x ^ k0, x.y ^ k1, x.z ^ k2, x.w ^ k3);
+                const uint4 ct = SEAL ? y : x;
                 gin = block_to_u128(ct.x, ct.y, ct.z, ct.w);
-                oblk = y; ovalid_lo = 0; ovalid_hi = (int)nb;
+                oblk = y; ovalid_hi = 16;
                 if (MODE == kPipeOpen && c == 0) { fh0 = y.x; fh1 = y.y; }
-            } else if (is_j0) {
-                ej0 = make_uint4(k0, k1, k2, k3);
-                // AAD = epoch(2) seq(6) type ver(2) len(2); record header = type ver(2) epoch(2) seq(6) len(2)
-                uint32_t e_hi, s_w0, s_w1;                   // header bytes 3..4, 5..8, 9..10 as BE numbers
-                if (MODE == kPipeSeal) {
-                    const uint32_t ep = __ldg(a.epoch + i);
-                    const u64 sq = __ldg(a.seq48 + i);
-                    e_hi = ep & 0xffff; s_w0 = (uint32_t)(sq >> 16); s_w1 = (uint32_t)(sq & 0xffff);
+            } else if (active) {
+                const bool is_j0 = (u == 0);
+                const bool is_len = (u == slots - 1);
+                if (!is_j0 && !is_len) {
+                    // -------- edge block: bounded byte loads, zero padding
+                    const uint32_t pos = 16u * (uint32_t)c;
+                    const uint32_t nb = (L - pos) < 16u ? (L - pos) : 16u;
+                    uint4 x = load16_bounded(body0 + pos, body_lo, body_hi);
+                    if (MODE == kPipeSeal && c == 0) {       // synthesise [type][sid BE] in front of the payload
+                        const uint32_t sid = __ldg(a.sids + i);
+                        x.x = (uint32_t)__ldg(a.types + i) | ((sid >> 24) << 8) | (((sid >> 16) & 0xff) << 16) | (((sid >> 8) & 0xff) << 24);
+                        x.y = (x.y & 0xffffff00u) | (sid & 0xff);
+                    }
+                    uint4 y = make_uint4(x.x ^ k0, x.y ^ k1, x.z ^ k2, x.w ^ k3);
+                    mask_block(y, nb);
+                    const uint4 ct = SEAL ? y : x;           // GHASH always runs over the ciphertext
+                    gin = block_to_u128(ct.x, ct.y, ct.z, ct.w);
+                    oblk = y; ovalid_hi = (int)nb;
+                    if (MODE == kPipeOpen && c == 0) { fh0 = y.x; fh1 = y.y; }
+                } else if (is_j0) {
+                    ej0 = make_uint4(k0, k1, k2, k3);
+                    // AAD = epoch(2) seq(6) type ver(2) len(2); record header = type ver(2) epoch(2) seq(6) len(2)
+                    uint32_t e_hi, s_w0, s_w1;               // header bytes 3..4, 5..8, 9..10 as BE numbers
+                    if (MODE == kPipeSeal) {
+                        const uint32_t ep = __ldg(a.epoch + i);
+                        const u64 sq = __ldg(a.seq48 + i);
+                        e_hi = ep & 0xffff; s_w0 = (uint32_t)(sq >> 16); s_w1 = (uint32_t)(sq & 0xffff);
+                    } else {
+                        if (MODE == kSeal) { hdr_type = __ldg(ibase); hdr_v0 = __ldg(ibase + 1); hdr_v1 = __ldg(ibase + 2); }
+                        e_hi = ((uint32_t)__ldg(ibase + 3) << 8) | __ldg(ibase + 4);
+                        s_w0 = ((uint32_t)__ldg(ibase + 5) << 24) | ((uint32_t)__ldg(ibase + 6) << 16) |
+                               ((uint32_t)__ldg(ibase + 7) << 8) | __ldg(ibase + 8);
+                        s_w1 = ((uint32_t)__ldg(ibase + 9) << 8) | __ldg(ibase + 10);
+                    }
+                    const uint32_t plen = L & 0xffff;        // `as u16` in the reference
+                    gin.w[3] = (e_hi << 16) | (s_w0 >> 16);
+                    gin.w[2] = (s_w0 << 16) | s_w1;
+                    gin.w[1] = (hdr_type << 24) | (hdr_v0 << 16) | (hdr_v1 << 8) | (plen >> 8);
+                    gin.w[0] = (plen & 0xff) << 24;
+                    // the 16 output bytes that precede the body
+                    if (SEAL) {
+                        const uint32_t rlen = (8 + L + 16) & 0xffff;
+                        obase[0] = (uint8_t)hdr_type; obase[1] = (uint8_t)hdr_v0; obase[2] = (uint8_t)hdr_v1;
+                        obase[3] = (uint8_t)(e_hi >> 8); obase[4] = (uint8_t)e_hi;
+                        oblk.x = bswap32(s_w0);
+                        oblk.y = ((s_w1 >> 8) & 0xff) | ((s_w1 & 0xff) << 8) | ((rlen >> 8) << 16) | ((rlen & 0xff) << 24);
+                        oblk.z = n0; oblk.w = n1;
+                        ovalid_lo = 0; ovalid_hi = 16;
+                    } else {
+                        const uint32_t l_w = ((uint32_t)__ldg(ibase + 11) << 8) | __ldg(ibase + 12);
+                        oblk.x = hdr_type << 24;
+                        oblk.y = hdr_v0 | (hdr_v1 << 8) | ((e_hi >> 8) << 16) | ((e_hi & 0xff) << 24);
+                        oblk.z = bswap32(s_w0);
+                        oblk.w = ((s_w1 >> 8) & 0xff) | ((s_w1 & 0xff) << 8) | ((l_w >> 8) << 16) | ((l_w & 0xff) << 24);
+                        ovalid_lo = 3; ovalid_hi = 16;
+                    }
                 } else {
-                    if (MODE == kSeal) { hdr_type = __ldg(ibase); hdr_v0 = __ldg(ibase + 1); hdr_v1 = __ldg(ibase + 2); }
-                    e_hi = ((uint32_t)__ldg(ibase + 3) << 8) | __ldg(ibase + 4);
-                    s_w0 = ((uint32_t)__ldg(ibase + 5) << 24) | ((uint32_t)__ldg(ibase + 6) << 16) |
-                           ((uint32_t)__ldg(ibase + 7) << 8) | __ldg(ibase + 8);
-                    s_w1 = ((uint32_t)__ldg(ibase + 9) << 8) | __ldg(ibase + 10);
+                    gin.w[2] = 13 * 8;                       // len(AAD) in bits
+                    gin.w[0] = L << 3;                       // len(C) in bits
                 }
-                const uint32_t plen = L & 0xffff;            // `as u16` in the reference
-                gin.w[3] = (e_hi << 16) | (s_w0 >> 16);
-                gin.w[2] = (s_w0 << 16) | s_w1;
-                gin.w[1] = (hdr_type << 24) | (hdr_v0 << 16) | (hdr_v1 << 8) | (plen >> 8);
-                gin.w[0] = (plen & 0xff) << 24;
-                // the 16 output bytes that precede the body
-                if (SEAL) {
-                    const uint32_t rlen = (8 + L + 16) & 0xffff;
-                    // record bytes 5..20: seq(6) len(2) nonce(8); bytes 0..4 are stored right here
-                    obase[0] = (uint8_t)hdr_type; obase[1] = (uint8_t)hdr_v0; obase[2] = (uint8_t)hdr_v1;
-                    obase[3] = (uint8_t)(e_hi >> 8); obase[4] = (uint8_t)e_hi;
-                    oblk.x = bswap32(s_w0);
-                    oblk.y = ((s_w1 >> 8) & 0xff) | ((s_w1 & 0xff) << 8) | ((rlen >> 8) << 16) | ((rlen & 0xff) << 24);
-                    oblk.z = n0; oblk.w = n1;
-                    ovalid_lo = 0; ovalid_hi = 16;
-                } else {
-                    // output bytes -3..12: (3 bytes not ours) then the 13 header bytes unchanged
-                    const uint32_t l_w = ((uint32_t)__ldg(ibase + 11) << 8) | __ldg(ibase + 12);
-                    oblk.x = hdr_type << 24;
-                    oblk.y = hdr_v0 | (hdr_v1 << 8) | ((e_hi >> 8) << 16) | ((e_hi & 0xff) << 24);
-                    oblk.z = bswap32(s_w0);
-                    oblk.w = ((s_w1 >> 8) & 0xff) | ((s_w1 & 0xff) << 8) | ((l_w >> 8) << 16) | ((l_w & 0xff) << 24);
-                    ovalid_lo = 3; ovalid_hi = 16;
-                }
-            } else if (is_len) {
-                gin.w[2] = 13 * 8;                           // len(AAD) in bits
-                gin.w[0] = L << 3;                           // len(C) in bits (L < 2^16)
             }
 
             // ---- GHASH: Horner in H^G; the lane's last block is multiplied after the loop
@@ -376,30 +499,28 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
                 acc.w[0] ^= gin.w[0]; acc.w[1] ^= gin.w[1]; acc.w[2] ^= gin.w[2]; acc.w[3] ^= gin.w[3];
                 last_u = u;
             }
-            if (u + G < slots) acc = gf128_mul(acc, kG);
+            if (u + G < slots) acc = gf128_mul_s(acc, gkey);
 
-            // ---- output stream: aligned vector V_c = tail of block c-1 || head of block c
-            uint4 prev;
-            prev.x = __shfl_up_sync(gmask, oblk.x, 1, G); prev.y = __shfl_up_sync(gmask, oblk.y, 1, G);
-            prev.z = __shfl_up_sync(gmask, oblk.z, 1, G); prev.w = __shfl_up_sync(gmask, oblk.w, 1, G);
-            if (j == 0) prev = carry;
-            carry.x = __shfl_sync(gmask, oblk.x, G - 1, G); carry.y = __shfl_sync(gmask, oblk.y, G - 1, G);
-            carry.z = __shfl_sync(gmask, oblk.z, G - 1, G); carry.w = __shfl_sync(gmask, oblk.w, G - 1, G);
-
-            // W(c): vector c is a full interior vector
-            auto vec_written = [&](int cc) -> bool {
-                if (cc < 0 || (uint32_t)(16 * cc + 16) > L) return false;
-                if (!SEAL && cc == 0 && so > 13) return false;   // would start before the output record
-                return true;
-            };
-            if (active && !is_len) {
-                const bool wc = vec_written(c), wn = vec_written(c + 1);
-                uint8_t* bp = ob0 + 16 * (int64_t)c;             // where this lane's block starts
-                if (wc) stg128(bp - so, so ? funnel16(prev, oblk, 16 - so) : oblk);
-                // bytes of my block no full vector covers
-                const int split = 16 - (int)so;                  // head [0,split) belongs to V_c, tail to V_c+1
-                if (!wc) store_bytes(bp, oblk, ovalid_lo, ovalid_hi < split ? ovalid_hi : split);
-                if (!wn && so) store_bytes(bp, oblk, ovalid_lo > split ? ovalid_lo : split, ovalid_hi);
+            // ---- output: the word that straddles into my block needs the previous block's last word
+            uint32_t prev3 = __shfl_up_sync(gmask, oblk.w, 1, G);
+            if (j == 0) prev3 = carry3;
+            carry3 = __shfl_sync(gmask, oblk.w, G - 1, G);
+            if (full_blk) {
+                uint32_t* op = reinterpret_cast<uint32_t*>(ob4 + 16 * (size_t)c);
+                const unsigned sh = osh * 8;
+                op[0] = __funnelshift_l(prev3, oblk.x, sh);
+                op[1] = __funnelshift_l(oblk.x, oblk.y, sh);
+                op[2] = __funnelshift_l(oblk.y, oblk.z, sh);
+                op[3] = __funnelshift_l(oblk.z, oblk.w, sh);
+                // my last `osh` bytes ride in the next block's first word; if there is no complete
+                // next block, store them here
+                if (osh && (uint32_t)(c + 1) >= nfull) store_bytes(ob0 + 16 * (size_t)c, oblk, 16 - (int)osh, 16);
+            } else if (active && ovalid_hi > ovalid_lo) {
+                // edge slots (prefix block, partial last block): byte stores; the prefix's last `osh`
+                // bytes are covered by block 0's first word when block 0 is complete
+                int hi = ovalid_hi;
+                if (c == -1 && nfull > 0 && osh) hi = 16 - (int)osh;
+                store_bytes(ob0 + 16 * (ptrdiff_t)c, oblk, ovalid_lo, hi);
             }
         }
 
@@ -408,8 +529,9 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
             const uint32_t fp = (last_u == 0xffffffffu) ? 1u : (slots - last_u);     // 1..G
             uint4 v = __ldg(reinterpret_cast<const uint4*>(sk->hpow[fp - 1]));
             U128 hf; hf.w[0] = v.x; hf.w[1] = v.y; hf.w[2] = v.z; hf.w[3] = v.w;
-            ghash_key_prepare(hf, kG);
-            acc = gf128_mul(acc, kG);                            // lanes that never ran hold 0
+            GhashKey kF;
+            ghash_key_prepare(hf, kF);
+            acc = gf128_mul(acc, kF);                            // lanes that never ran hold 0
         }
 #pragma unroll
         for (int o = G >> 1; o > 0; o >>= 1) {

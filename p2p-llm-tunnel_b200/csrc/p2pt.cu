@@ -145,7 +145,7 @@ static int pick_group(p2pt_ctx* ctx, uint64_t n, uint64_t body_bytes) {
 template <int MODE>
 static int32_t launch_gcm(p2pt_ctx* ctx, const GcmArgs& a, int G, cudaStream_t st) {
     if (a.n == 0) return P2PT_OK;
-    const uint32_t smem = kLutBytes + ctx->lut_slack;
+    const uint32_t smem = gcm_smem_bytes(G, ctx->lut_slack);
     const uint64_t groups_per_cta = kGcmThreads / G;
     uint64_t grid = (a.n + groups_per_cta - 1) / groups_per_cta;
     if (grid > (uint64_t)ctx->sm_count) grid = ctx->sm_count;      // persistent: one CTA per SM
@@ -268,6 +268,16 @@ void* p2pt_host_alloc(size_t bytes) {
 void p2pt_host_free(void* p) { if (p) cudaFreeHost(p); }
 
 uint64_t p2pt_launch_count(p2pt_ctx* ctx) { return ctx ? ctx->launches.load() : 0; }
+
+int64_t p2pt_ctx_get_info(p2pt_ctx* ctx, const char* name) {
+    if (!ctx || !name) return -1;
+    if (strcmp(name, "sm_count") == 0) return ctx->sm_count;
+    if (strcmp(name, "lut_slack") == 0) return ctx->lut_slack;
+    if (strcmp(name, "gcm_group_width") == 0) return ctx->gcm_g;
+    if (strcmp(name, "n_sessions") == 0) return ctx->n_sessions;
+    if (strcmp(name, "gcm_threads") == 0) return kGcmThreads;
+    return -1;
+}
 
 int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
     if (!ctx || !name) return P2PT_ERR_ARG;

@@ -33,6 +33,28 @@ csr = torch.empty(ms + 1, dtype=torch.int64, device=dev); goff = torch.empty(ms 
 perm = torch.empty(n, dtype=torch.int32, device=dev); k = torch.zeros(1, dtype=torch.int32, device=dev)
 gathered = torch.empty(n * 1200, dtype=torch.uint8, device=dev)
 s = torch.cuda.current_stream().cuda_stream
+print("lut_slack", ctx.get_info("lut_slack"), "threads", ctx.get_info("gcm_threads"))
+gs = [int(x) for x in os.environ.get("PROF_G", "0").split(",")]
+for g in gs:
+    ctx.set_option("gcm_group_width", g)
+    for _ in range(reps):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        ev[0].record()
+        ctx.call("p2pt_pipeline_seal_device", n, d["session"], d["epoch"], d["seq48"], d["nonce8"], d["types"], d["sids"],
+                 d["payload"], d["pay_off"], rec, d["rec_off"], status, s)
+        ev[1].record()
+        ctx.call("p2pt_pipeline_open_device", n, d["session"], rec, d["rec_off"], out, d["rec_off"], desc, s)
+        ev[2].record()
+        ctx.call("p2pt_frame_demux_batch_device", n, desc, d["session"], out, ms, uniq, usess, csr, perm, k, gathered,
+                 n * 1200, goff, scratch, sb, s)
+        ev[3].record()
+        torch.cuda.synchronize()
+    tt = [ev[i].elapsed_time(ev[i + 1]) for i in range(3)]
+    print(f"G={g}: seal {tt[0]:.3f} ms ({n * 1200 / tt[0] / 1e6:.1f} GB/s)  open {tt[1]:.3f} ms ({n * 1200 / tt[1] / 1e6:.1f} GB/s)  "
+          f"demux+gather {tt[2]:.3f} ms")
+assert int(status.sum()) == 0 and int(k.item()) == ms
+print("prof target ok", n, "records")
+sys.exit(0)
 for _ in range(reps):
     ctx.call("p2pt_pipeline_seal_device", n, d["session"], d["epoch"], d["seq48"], d["nonce8"], d["types"], d["sids"],
              d["payload"], d["pay_off"], rec, d["rec_off"], status, s)
