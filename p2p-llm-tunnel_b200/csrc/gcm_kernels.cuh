@@ -46,13 +46,36 @@ struct GlobalLut {   // setup kernels only (key expansion): plain global table
     }
 };
 
+// Measured on B200 (round 1): moving the byte-0 / byte-3 index arithmetic to the FMA pipe
+// (IMAD / IMAD.WIDE with run-time multipliers) took the ALU pipe from 630 to 550 instructions per
+// block but made the kernel 9 % SLOWER (3.89 -> 4.25 ms per 1 M records): the extra instructions
+// cost more issue slots than the ALU relief buys.  Kept behind a switch, off.
+#ifndef P2PT_FMA_EXTRACT
+#define P2PT_FMA_EXTRACT 0
+#endif
 constexpr uint32_t kLutBytes = 131072;   // 4 tables x 256 entries x 32 replicas x 4 B
 
 struct SmemLut {     // hot path: bank-replicated shared-memory tables
     uint32_t lb;     // 64 KiB-aligned shared address of the tables + 4 * lane
+    uint32_t m8, m16, m24;   // 1<<8, 1<<16, 1<<24 as RUN-TIME values (kernel arguments): multiplying by
+                             // them keeps the byte-0 / byte-3 index arithmetic on the FMA pipe (IMAD,
+                             // IMAD.HI); as literals ptxas would turn them back into ALU-pipe shifts
     template <int K, int T> __device__ __forceinline__ uint32_t look(uint32_t w) const {
-        // address = base | byte_K(w) << 8 | lane << 2, built by a single PRMT
-        const uint32_t idx = __byte_perm(w, lb, 0x7604 | (K << 4));
+        // address = base | byte_K(w) << 8 | lane << 2
+        uint32_t idx;
+#if P2PT_FMA_EXTRACT
+        if (K == 0) {            // ((w << 24) * 2^16 + (lb << 32)) >> 32 = (byte0 << 8) + lb, via IMAD + IMAD.WIDE
+            const uint32_t t = w * m24;
+            const unsigned long long r = (unsigned long long)t * m16 + ((unsigned long long)lb << 32);
+            idx = (uint32_t)(r >> 32);
+        } else if (K == 3) {     // (w * 2^8) >> 32 = byte3, via IMAD.WIDE + IMAD
+            const unsigned long long r = (unsigned long long)w * m8;
+            idx = (uint32_t)(r >> 32) * m8 + lb;
+        } else
+#endif
+        {
+            idx = __byte_perm(w, lb, 0x7604 | (K << 4));     // a single PRMT (ALU pipe)
+        }
         uint32_t v;
         if (T == 0)      asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(idx));
         else if (T == 1) asm("ld.shared.u32 %0, [%1+128];" : "=r"(v) : "r"(idx));
@@ -214,6 +237,7 @@ struct GcmArgs {
     const uint8_t* types;         // pipe-seal
     const uint32_t* sids;         // pipe-seal
     p2pt_desc* desc;              // pipe-open
+    uint32_t m8, m16, m24;        // 1<<8, 1<<16, 1<<24 (see SmemLut)
 };
 
 constexpr int kGcmThreads = 1024;
@@ -274,6 +298,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
     __syncthreads();
     SmemLut lut;
     lut.lb = tbase + 4u * (uint32_t)lane;
+    lut.m8 = a.m8; lut.m16 = a.m16; lut.m24 = a.m24;
     // this group's key slot: round keys at +0, GHASH multiplier rows at +176
     const uint32_t n_low = (tbase - sbase) / kGroupSlotBytes, gi = (uint32_t)(threadIdx.x / G);
     const uint32_t slot = gi < n_low ? sbase + gi * kGroupSlotBytes : tbase + kLutBytes + (gi - n_low) * kGroupSlotBytes;

@@ -135,16 +135,16 @@ static size_t pad256(size_t b) { return (b + 255) & ~(size_t)255; }
 static inline void count_launch(p2pt_ctx* ctx, int k = 1) { ctx->launches.fetch_add((uint64_t)k, std::memory_order_relaxed); }
 
 static int pick_group(p2pt_ctx* ctx, uint64_t n, uint64_t body_bytes) {
+    (void)n; (void)body_bytes;
     if (ctx->gcm_g) return ctx->gcm_g;
-    const uint64_t avg = n ? body_bytes / n : 0;
-    const uint64_t slots = (avg + 15) / 16 + 2;
-    if (slots <= 6) return 4;
-    return 8;
+    return 4;      // measured on B200 at 1200-byte records: G=4 323 GB/s, 8: 313, 16: 290, 32: 213
 }
 
 template <int MODE>
-static int32_t launch_gcm(p2pt_ctx* ctx, const GcmArgs& a, int G, cudaStream_t st) {
-    if (a.n == 0) return P2PT_OK;
+static int32_t launch_gcm(p2pt_ctx* ctx, const GcmArgs& a_in, int G, cudaStream_t st) {
+    if (a_in.n == 0) return P2PT_OK;
+    GcmArgs a = a_in;
+    a.m8 = 1u << 8; a.m16 = 1u << 16; a.m24 = 1u << 24;
     const uint32_t smem = gcm_smem_bytes(G, ctx->lut_slack);
     const uint64_t groups_per_cta = kGcmThreads / G;
     uint64_t grid = (a.n + groups_per_cta - 1) / groups_per_cta;
@@ -478,7 +478,7 @@ int32_t p2pt_dtls_gcm_seal_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_
     a.n = n; a.session = session; a.keys = ctx->keys_local; a.n_sessions = ctx->n_sessions;
     a.nonce8 = nonce8; a.in = raw; a.in_off = (const u64*)raw_off; a.out = rec; a.out_off = (const u64*)rec_off;
     a.status = status;
-    return launch_gcm<kSeal>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 8, (cudaStream_t)stream);
+    return launch_gcm<kSeal>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 4, (cudaStream_t)stream);
 }
 
 int32_t p2pt_dtls_gcm_open_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
@@ -495,7 +495,7 @@ int32_t p2pt_dtls_gcm_open_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_
     a.n = n; a.session = session; a.keys = ctx->keys_remote; a.n_sessions = ctx->n_sessions;
     a.in = rec; a.in_off = (const u64*)rec_off; a.out = out; a.out_off = (const u64*)out_off;
     a.status = status; a.out_len = out_len;
-    return launch_gcm<kOpen>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 8, (cudaStream_t)stream);
+    return launch_gcm<kOpen>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 4, (cudaStream_t)stream);
 }
 
 int32_t p2pt_pipeline_seal_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
@@ -513,7 +513,7 @@ int32_t p2pt_pipeline_seal_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* ses
     a.n = n; a.session = session; a.keys = ctx->keys_local; a.n_sessions = ctx->n_sessions;
     a.nonce8 = nonce8; a.in = payload; a.in_off = (const u64*)pay_off; a.out = rec; a.out_off = (const u64*)rec_off;
     a.status = status; a.epoch = epoch; a.seq48 = (const u64*)seq48; a.types = types; a.sids = sids;
-    return launch_gcm<kPipeSeal>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 8, (cudaStream_t)stream);
+    return launch_gcm<kPipeSeal>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 4, (cudaStream_t)stream);
 }
 
 int32_t p2pt_pipeline_open_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
@@ -529,7 +529,7 @@ int32_t p2pt_pipeline_open_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* ses
     a.n = n; a.session = session; a.keys = ctx->keys_remote; a.n_sessions = ctx->n_sessions;
     a.in = rec; a.in_off = (const u64*)rec_off; a.out = out; a.out_off = (const u64*)out_off;
     a.desc = desc;
-    return launch_gcm<kPipeOpen>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 8, (cudaStream_t)stream);
+    return launch_gcm<kPipeOpen>(ctx, a, ctx->gcm_g ? ctx->gcm_g : 4, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------------------
