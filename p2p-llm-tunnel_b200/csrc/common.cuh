@@ -93,26 +93,37 @@ __device__ __forceinline__ void warp_copy_bytes(uint8_t* dst, const uint8_t* src
         u64 safe = (send >= sa + 32) ? (u64)((send - (sa + 32)) >> 4) + 1 : 0;
         if (nvec > safe) nvec = safe;
     }
-    // Each aligned source vector is loaded exactly once: lane l holds vector base+l, gets its right
-    // neighbour by shuffle, and the prefetched next group supplies lane 31's neighbour.
+    // Each aligned source vector is loaded exactly once.  A lane keeps three vectors in flight
+    // (96 per warp pass); its right neighbour's vector comes by shuffle, the neighbour of lane 31
+    // is lane 0's vector of the next group.
     const u64 nsrc = nvec + (s ? 1 : 0);
     const uint4 zero = make_uint4(0, 0, 0, 0);
-    uint4 cur = ((u64)lane < nsrc && nvec) ? ldg128_stream(sa + 16 * (u64)lane) : zero;
-    for (u64 base = 0; base < nvec; base += 32) {
-        const u64 vn = base + 32 + lane;
-        uint4 nxt = (vn < nsrc) ? ldg128_stream(sa + 16 * vn) : zero;
-        uint4 out = cur;
-        if (s) {
-            uint4 nb, n0;
-            nb.x = __shfl_down_sync(0xffffffffu, cur.x, 1); n0.x = __shfl_sync(0xffffffffu, nxt.x, 0);
-            nb.y = __shfl_down_sync(0xffffffffu, cur.y, 1); n0.y = __shfl_sync(0xffffffffu, nxt.y, 0);
-            nb.z = __shfl_down_sync(0xffffffffu, cur.z, 1); n0.z = __shfl_sync(0xffffffffu, nxt.z, 0);
-            nb.w = __shfl_down_sync(0xffffffffu, cur.w, 1); n0.w = __shfl_sync(0xffffffffu, nxt.w, 0);
-            if (lane == 31) nb = n0;
-            out = funnel16(cur, nb, s);
+    for (u64 base = 0; base < nvec; base += 96) {
+        uint4 v[4];
+#pragma unroll
+        for (int g = 0; g < 3; g++) {
+            const u64 idx = base + 32 * g + lane;
+            v[g] = idx < nsrc ? ldg128_stream(sa + 16 * idx) : zero;
         }
-        if (base + lane < nvec) stg128(d2 + 16 * (base + lane), out);
-        cur = nxt;
+        {   // only lane 0's copy of the 4th group is ever used (as lane 31's neighbour in group 2)
+            const u64 idx = base + 96 + lane;
+            v[3] = (s && lane == 0 && idx < nsrc) ? ldg128_stream(sa + 16 * idx) : zero;
+        }
+#pragma unroll
+        for (int g = 0; g < 3; g++) {
+            const u64 idx = base + 32 * g + lane;
+            uint4 out = v[g];
+            if (s) {
+                uint4 nb, n0;
+                nb.x = __shfl_down_sync(0xffffffffu, v[g].x, 1); n0.x = __shfl_sync(0xffffffffu, v[g + 1].x, 0);
+                nb.y = __shfl_down_sync(0xffffffffu, v[g].y, 1); n0.y = __shfl_sync(0xffffffffu, v[g + 1].y, 0);
+                nb.z = __shfl_down_sync(0xffffffffu, v[g].z, 1); n0.z = __shfl_sync(0xffffffffu, v[g + 1].z, 0);
+                nb.w = __shfl_down_sync(0xffffffffu, v[g].w, 1); n0.w = __shfl_sync(0xffffffffu, v[g + 1].w, 0);
+                if (lane == 31) nb = n0;
+                out = funnel16(v[g], nb, s);
+            }
+            if (idx < nvec) stg128(d2 + 16 * idx, out);
+        }
     }
     for (u64 i = (nvec << 4) + lane; i < rem; i += 32) d2[i] = __ldg(s2 + i);
 }

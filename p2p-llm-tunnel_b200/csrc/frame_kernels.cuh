@@ -195,51 +195,48 @@ __global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
     hist[(u64)threadIdx.x * kSortBlocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// exclusive scan of the digit-major [kRadix][kSortBlocks] matrix, one block of 1024 threads
+// exclusive scan of the digit-major [kRadix][kSortBlocks] matrix, one block of 1024 threads:
+// four threads per digit row, each walks a quarter of the row (independent loads, a running sum
+// in a register), quarter sums and row totals are combined with shuffles / shared memory.
 __global__ void __launch_bounds__(1024) demux_scan_hist_kernel(uint32_t* __restrict__ hist, int pass,
                                                               u64* __restrict__ misc) {
     if (demux_pass_trivial(misc, pass)) return;
+    static_assert(kSortBlocks % 4 == 0 && kRadix * 4 == 1024, "scan layout");
+    constexpr int Q = kSortBlocks / 4;
     __shared__ uint32_t row_total[kRadix];
     __shared__ uint32_t row_base[kRadix];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int r = warp; r < kRadix; r += 32) {
-        uint32_t* row = hist + (u64)r * kSortBlocks;
-        uint32_t carry = 0;
-        for (int b0 = 0; b0 < kSortBlocks; b0 += 32) {
-            const int b = b0 + lane;
-            uint32_t v = b < kSortBlocks ? row[b] : 0;
-            uint32_t incl = v;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += t;
-            }
-            if (b < kSortBlocks) row[b] = carry + incl - v;
-            carry += __shfl_sync(0xffffffffu, incl, 31);
-        }
-        if (lane == 0) row_total[r] = carry;
-    }
+    const int row = threadIdx.x >> 2, part = threadIdx.x & 3, lane = threadIdx.x & 31;
+    uint32_t* seg = hist + (u64)row * kSortBlocks + part * Q;
+    uint32_t s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+    int k = 0;
+    for (; k + 4 <= Q; k += 4) { s0 += seg[k]; s1 += seg[k + 1]; s2 += seg[k + 2]; s3 += seg[k + 3]; }
+    for (; k < Q; k++) s0 += seg[k];
+    const uint32_t mine = s0 + s1 + s2 + s3;
+    // exclusive prefix over the four parts of the row (they sit in adjacent lanes)
+    uint32_t incl = mine;
+    uint32_t t = __shfl_up_sync(0xffffffffu, incl, 1, 4); if (part >= 1) incl += t;
+    t = __shfl_up_sync(0xffffffffu, incl, 2, 4); if (part >= 2) incl += t;
+    const uint32_t part_excl = incl - mine;
+    if (part == 3) row_total[row] = incl;
     __syncthreads();
-    if (warp == 0) {
+    if (threadIdx.x < 32) {
         uint32_t carry = 0;
         for (int r0 = 0; r0 < kRadix; r0 += 32) {
-            uint32_t v = row_total[r0 + lane], incl = v;
+            uint32_t v = row_total[r0 + lane], in2 = v;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
-                uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += t;
+                uint32_t u = __shfl_up_sync(0xffffffffu, in2, o);
+                if (lane >= o) in2 += u;
             }
-            row_base[r0 + lane] = carry + incl - v;
-            carry += __shfl_sync(0xffffffffu, incl, 31);
+            row_base[r0 + lane] = carry + in2 - v;
+            carry += __shfl_sync(0xffffffffu, in2, 31);
         }
         if (pass == kKeyPasses && lane == 0) misc[0] = row_total[0];   // number of decodable frames
     }
     __syncthreads();
-    for (int r = warp; r < kRadix; r += 32) {
-        uint32_t* row = hist + (u64)r * kSortBlocks;
-        const uint32_t base = row_base[r];
-        for (int b = lane; b < kSortBlocks; b += 32) row[b] += base;
-    }
+    uint32_t run = row_base[row] + part_excl;
+#pragma unroll 4
+    for (k = 0; k < Q; k++) { const uint32_t v = seg[k]; seg[k] = run; run += v; }
 }
 
 __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(

@@ -1,0 +1,128 @@
+"""GPU: BASELINE.json's full-size configurations through the C ABI, checked with size-independent
+properties (round trips, permutation / stability, checksums) plus sampled records against
+Python `cryptography`.  The oracle is too slow for these sizes; it covers the same code paths at
+small sizes in test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _check_demux_properties(r, sids, n_valid, session=None):
+    k = r["k"]
+    csr, perm = r["csr"].astype(np.int64), r["perm"].astype(np.int64)
+    assert csr[0] == 0 and csr[k] == n_valid and np.all(np.diff(csr) > 0)
+    assert np.array_equal(np.sort(perm), np.arange(n_valid))                 # a permutation of the valid frames
+    keys = sids[perm].astype(np.uint64)
+    if session is not None:
+        keys |= session[perm].astype(np.uint64) << np.uint64(32)
+    starts = np.zeros(n_valid, bool); starts[csr[:k]] = True
+    assert np.all(np.diff(keys.astype(np.int64))[~starts[1:]] == 0)          # one key per stream
+    assert np.all(np.diff(keys.astype(np.int64))[starts[1:]] > 0)            # streams ascending
+    assert np.all(np.diff(perm)[~starts[1:]] > 0)                            # arrival order kept inside a stream
+    assert np.array_equal(r["uniq_sid"], (keys[csr[:k]] & np.uint64(0xFFFFFFFF)).astype(np.uint32))
+
+
+def test_c2_one_million_frames_decode_demux(ctx):
+    """configs[1]: 1 M RES_BODY frames x 1200 B across 4096 stream ids, decode + demux + gather."""
+    from p2p_llm_tunnel_b200 import workload
+    n, P = 1_000_000, 1200
+    w = workload.frames_workload(n, P)
+    frames, off = ctx.frame_encode(w["types"], w["sids"], w["payload"], w["pay_off"])
+    assert np.array_equal(off, w["frame_off"])
+    f2 = frames.reshape(n, P + 5)
+    assert np.all(f2[:, 0] == 21)
+    assert np.array_equal(f2[:, 1:5].copy().view(">u4").reshape(-1), w["sids"])     # big-endian stream id
+    assert np.array_equal(f2[:, 5:].reshape(-1), w["payload"])
+    desc = ctx.frame_decode(frames, off)
+    assert not desc["status"].any() and np.all(desc["msg_type"] == 21) and np.all(desc["pay_len"] == P)
+    assert np.array_equal(desc["stream_id"], w["sids"]) and np.array_equal(desc["pay_off"], off[:-1] + np.uint64(5))
+    r = ctx.frame_demux(desc, frames, max_streams=4096)
+    assert r["k"] == 4096 and r["uniq_sid"][0] == 1 and r["uniq_sid"][-1] == 4096
+    _check_demux_properties(r, w["sids"], n)
+    assert np.array_equal(r["gathered_off"], r["csr"] * np.uint64(P))
+    assert np.array_equal(r["gathered"].reshape(n, P), w["payload"].reshape(n, P)[r["perm"]])
+
+
+def test_c2x_corrupt_frames_are_skipped(ctx):
+    from p2p_llm_tunnel_b200 import workload
+    n, P = 200_000, 1200
+    w = workload.frames_workload(n, P, seed_shift=9)
+    frames, off = ctx.frame_encode(w["types"], w["sids"], w["payload"], w["pay_off"])
+    frames = frames.copy()
+    bad = (workload.splitmix64(workload.SEED_CORRUPT, n) % np.uint64(1000)) == 0        # 0.1 %
+    frames[off[:-1][bad].astype(np.int64)] = 0xEE
+    desc = ctx.frame_decode(frames, off)
+    assert np.array_equal(desc["status"] != 0, bad) and np.all(desc["status"][bad] == 2)
+    r = ctx.frame_demux(desc, frames, max_streams=4096)
+    good = np.nonzero(~bad)[0]
+    assert np.array_equal(np.sort(r["perm"].astype(np.int64)), good)
+    assert np.array_equal(r["gathered"].reshape(-1, P), w["payload"].reshape(n, P)[r["perm"]])
+
+
+@pytest.mark.parametrize("n_sessions", [1, 4096])
+def test_c3_one_million_records_seal_open(ctx, n_sessions):
+    """configs[2]: 1 M records x 1200 B, fixed keys / injected nonces; seal -> open round trip, sampled
+    records against `cryptography`, 0.1 % tampered tags must fail and only those."""
+    from cryptography.hazmat.primitives.ciphers.aead import AESGCM
+    from p2p_llm_tunnel_b200 import workload
+    n, L = 1_000_000, 1200
+    keys, ivs = workload.sessions_keys(n_sessions, seed_shift=n_sessions)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    w = workload.records_workload(n, L, n_sessions=n_sessions)
+    rec, rec_off, st = ctx.dtls_seal(w["session"], w["nonce8"], w["raw"], w["raw_off"], w["rec_off"])
+    assert not st.any()
+    raw2, rec2 = w["raw"].reshape(n, 13 + L), rec.reshape(n, 37 + L)
+    assert np.array_equal(rec2[:, :11], raw2[:, :11]) and np.all(rec2[:, 11] == (L + 24) >> 8) and np.all(rec2[:, 12] == (L + 24) & 0xFF)
+    assert np.array_equal(rec2[:, 13:21].reshape(-1), w["nonce8"])
+    for i in [0, 1, 4095, 4096, 65537, 123456, 999_999] + list(range(500_000, 500_020)):
+        s = int(w["session"][i])
+        hdr = raw2[i, :13].tobytes()
+        aad = hdr[3:11] + hdr[0:3] + L.to_bytes(2, "big")
+        exp = AESGCM(keys[s].tobytes()).encrypt(ivs[s].tobytes() + w["nonce8"][8 * i:8 * i + 8].tobytes(), raw2[i, 13:].tobytes(), aad)
+        assert rec2[i, 21:].tobytes() == exp, i
+    bad = (workload.splitmix64(workload.SEED_CORRUPT + 1, n) % np.uint64(1000)) == 0
+    rec = rec.copy(); rec.reshape(n, 37 + L)[bad, -1] ^= 0x01
+    out, _, olen, st = ctx.dtls_open(w["session"], rec, rec_off)
+    assert np.array_equal(st != 0, bad) and np.all(st[bad] == 3) and np.all(olen[~bad] == 13 + L) and np.all(olen[bad] == 0)
+    out2 = out.reshape(n, 37 + L)
+    assert np.array_equal(out2[~bad, 13:13 + L], raw2[~bad, 13:])           # plaintext restored
+    assert np.array_equal(out2[~bad, :13], rec.reshape(n, 37 + L)[~bad, :13])  # header not rewritten on open
+    assert not out2[bad, :13 + L].any()                                     # failed records are zeroed
+
+
+def test_c4_ten_million_tiny_sse_frames(ctx):
+    """configs[3]: 10 M RES_BODY frames x 64 B (SSE chunk template), 4096 stream ids."""
+    from p2p_llm_tunnel_b200 import workload
+    n, P = 10_000_000, 64
+    w = workload.frames_workload(n, P, sse=True)
+    frames, off = ctx.frame_encode(w["types"], w["sids"], w["payload"], w["pay_off"])
+    f2 = frames.reshape(n, P + 5)
+    assert np.all(f2[:, 0] == 21) and np.array_equal(f2[:, 5:].reshape(-1), w["payload"])
+    desc = ctx.frame_decode(frames, off)
+    assert not desc["status"].any() and np.array_equal(desc["stream_id"], w["sids"])
+    r = ctx.frame_demux(desc, frames, max_streams=4096)
+    assert r["k"] == 4096
+    _check_demux_properties(r, w["sids"], n)
+    assert int(r["gathered"].astype(np.uint64).sum()) == int(w["payload"].astype(np.uint64).sum())
+    g = r["gathered"].reshape(n, P)
+    assert np.all(g[:, :6] == np.frombuffer(b"data: ", np.uint8))
+
+
+def test_c5_slice_full_pipeline_multi_session(ctx):
+    """configs[4] at 1/8 size (the full size runs in bench.py with its own correctness gate): 8192 sessions x
+    16 records, encode->seal, open->decode->demux->gather keyed by (session, stream id)."""
+    from p2p_llm_tunnel_b200 import workload
+    S, R, P = 8192, 16, 1200
+    keys, ivs = workload.sessions_keys(S, seed_shift=5)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    w = workload.pipeline_workload(S, R, P, seed_shift=5)
+    n = w["n"]
+    rec, rec_off, st = ctx.pipeline_seal(w["session"], w["epoch"], w["seq48"], w["nonce8"], w["types"], w["sids"],
+                                         w["payload"], w["pay_off"], w["rec_off"])
+    assert not st.any()
+    r = ctx.pipeline_open_demux(w["session"], rec, rec_off, max_streams=S * 4, gathered_cap=n * P)
+    assert not r["desc"]["status"].any() and r["k"] == S * 4
+    _check_demux_properties(r, w["sids"], n, w["session"])
+    assert np.array_equal(r["uniq_session"], np.repeat(np.arange(S, dtype=np.uint32), 4))
+    assert np.array_equal(r["gathered"].reshape(n, P), w["payload"].reshape(n, P)[r["perm"]])
