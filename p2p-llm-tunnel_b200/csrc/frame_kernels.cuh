@@ -104,20 +104,21 @@ struct DemuxScratch {
     u64* blk_bytes;        // per scan block: body bytes
     uint32_t* blk_heads;   // per scan block: stream heads
     u64* misc;             // [0] = number of valid frames m, [1] = OR of keys, [2] = OR of ~keys
+    uint32_t* row_total;   // kRadix digit totals of the current pass
 };
 
-__host__ __device__ inline u64 align256(u64 x) { return (x + 255) & ~(u64)255; }
+__host__ __device__ constexpr u64 align256(u64 x) { return (x + 255) & ~(u64)255; }
 
-inline u64 demux_scan_blocks(u64 n) { return (n + kScanThreads - 1) / kScanThreads; }
+constexpr u64 demux_scan_blocks(u64 n) { return (n + kScanThreads - 1) / kScanThreads; }
 
-inline u64 demux_scratch_bytes(u64 n) {
+constexpr u64 demux_scratch_bytes(u64 n) {
     u64 b = 0;
     b += 2 * align256(n * sizeof(u64));
     b += 2 * align256(n * sizeof(uint32_t));
     b += align256((u64)kRadix * kSortBlocks * sizeof(uint32_t));
     b += align256((demux_scan_blocks(n) + 1) * sizeof(u64));
     b += align256((demux_scan_blocks(n) + 1) * sizeof(uint32_t));
-    b += 256;
+    b += 256 + kRadix * sizeof(uint32_t);      // control words + row totals
     return b;
 }
 
@@ -131,7 +132,8 @@ inline DemuxScratch demux_carve(void* scratch, u64 n) {
     s.hist = (uint32_t*)p; p += align256((u64)kRadix * kSortBlocks * sizeof(uint32_t));
     s.blk_bytes = (u64*)p; p += align256((demux_scan_blocks(n) + 1) * sizeof(u64));
     s.blk_heads = (uint32_t*)p; p += align256((demux_scan_blocks(n) + 1) * sizeof(uint32_t));
-    s.misc = (u64*)p;
+    s.misc = (u64*)p; p += 256;
+    s.row_total = (uint32_t*)p;
     return s;
 }
 
@@ -195,65 +197,73 @@ __global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
     hist[(u64)threadIdx.x * kSortBlocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// exclusive scan of the digit-major [kRadix][kSortBlocks] matrix, one block of 1024 threads:
-// four threads per digit row, each walks a quarter of the row (independent loads, a running sum
-// in a register), quarter sums and row totals are combined with shuffles / shared memory.
-__global__ void __launch_bounds__(1024) demux_scan_hist_kernel(uint32_t* __restrict__ hist, int pass,
-                                                              u64* __restrict__ misc) {
+// Per digit row: exclusive scan over the kSortBlocks block counts (one warp per row, all loads of
+// the row issued up front) and the row total.  The scan ACROSS rows is redone by every scatter
+// block in shared memory (256 values), which is cheaper than a serial single-block pass.
+constexpr int kRowScanWarps = 4;
+__global__ void __launch_bounds__(32 * kRowScanWarps) demux_rowscan_kernel(uint32_t* __restrict__ hist, int pass,
+                                                                          u64* __restrict__ misc,
+                                                                          uint32_t* __restrict__ row_total) {
     if (demux_pass_trivial(misc, pass)) return;
-    static_assert(kSortBlocks % 4 == 0 && kRadix * 4 == 1024, "scan layout");
-    constexpr int Q = kSortBlocks / 4;
-    __shared__ uint32_t row_total[kRadix];
-    __shared__ uint32_t row_base[kRadix];
-    const int row = threadIdx.x >> 2, part = threadIdx.x & 3, lane = threadIdx.x & 31;
-    uint32_t* seg = hist + (u64)row * kSortBlocks + part * Q;
-    uint32_t s0 = 0, s1 = 0, s2 = 0, s3 = 0;
-    int k = 0;
-    for (; k + 4 <= Q; k += 4) { s0 += seg[k]; s1 += seg[k + 1]; s2 += seg[k + 2]; s3 += seg[k + 3]; }
-    for (; k < Q; k++) s0 += seg[k];
-    const uint32_t mine = s0 + s1 + s2 + s3;
-    // exclusive prefix over the four parts of the row (they sit in adjacent lanes)
-    uint32_t incl = mine;
-    uint32_t t = __shfl_up_sync(0xffffffffu, incl, 1, 4); if (part >= 1) incl += t;
-    t = __shfl_up_sync(0xffffffffu, incl, 2, 4); if (part >= 2) incl += t;
-    const uint32_t part_excl = incl - mine;
-    if (part == 3) row_total[row] = incl;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        uint32_t carry = 0;
-        for (int r0 = 0; r0 < kRadix; r0 += 32) {
-            uint32_t v = row_total[r0 + lane], in2 = v;
+    constexpr int CH = (kSortBlocks + 31) / 32;
+    const int row = blockIdx.x * kRowScanWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= kRadix) return;
+    uint32_t* r = hist + (u64)row * kSortBlocks;
+    uint32_t v[CH];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                uint32_t u = __shfl_up_sync(0xffffffffu, in2, o);
-                if (lane >= o) in2 += u;
-            }
-            row_base[r0 + lane] = carry + in2 - v;
-            carry += __shfl_sync(0xffffffffu, in2, 31);
+    for (int i = 0; i < CH; i++) { const int b = 32 * i + lane; v[i] = b < kSortBlocks ? r[b] : 0u; }
+    uint32_t carry = 0;
+#pragma unroll
+    for (int i = 0; i < CH; i++) {
+        uint32_t incl = v[i];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
         }
-        if (pass == kKeyPasses && lane == 0) misc[0] = row_total[0];   // number of decodable frames
+        const int b = 32 * i + lane;
+        if (b < kSortBlocks) r[b] = carry + incl - v[i];
+        carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    __syncthreads();
-    uint32_t run = row_base[row] + part_excl;
-#pragma unroll 4
-    for (k = 0; k < Q; k++) { const uint32_t v = seg[k]; seg[k] = run; run += v; }
+    if (lane == 0) {
+        row_total[row] = carry;
+        if (pass == kKeyPasses && row == 0) misc[0] = carry;      // number of decodable frames
+    }
 }
 
 __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
     u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx,
     u64* __restrict__ keys_out, uint32_t* __restrict__ idx_out, const p2pt_desc* __restrict__ desc,
-    int pass, const uint32_t* __restrict__ hist, const u64* __restrict__ misc) {
+    int pass, const uint32_t* __restrict__ hist, const u64* __restrict__ misc,
+    const uint32_t* __restrict__ row_total) {
     u64 lo, hi;
     demux_tile(n, lo, hi);
     if (demux_pass_trivial(misc, pass)) {
         for (u64 i = lo + threadIdx.x; i < hi; i += kSortThreads) { keys_out[i] = keys[i]; idx_out[i] = idx[i]; }
         return;
     }
+    static_assert(kSortThreads == kRadix, "one thread per digit");
     constexpr int W = kSortThreads / 32;
     __shared__ uint32_t base[kRadix];          // running output position per digit for this block
     __shared__ uint32_t wcount[W][kRadix];     // per-warp digit counts of the current chunk
+    __shared__ uint32_t wtot[W];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    base[threadIdx.x] = hist[(u64)threadIdx.x * kSortBlocks + blockIdx.x];
+    {
+        // exclusive scan of the 256 row totals -> where each digit's output range starts
+        const uint32_t v = row_total[threadIdx.x];
+        uint32_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) wtot[warp] = incl;
+        __syncthreads();
+        uint32_t wbase = 0;
+#pragma unroll
+        for (int w = 0; w < W; w++) wbase += (w < warp) ? wtot[w] : 0u;
+        base[threadIdx.x] = wbase + incl - v + hist[(u64)threadIdx.x * kSortBlocks + blockIdx.x];
+    }
     for (u64 c0 = lo; c0 < hi; c0 += kSortThreads) {
 #pragma unroll
         for (int w = 0; w < W; w++) wcount[w][threadIdx.x] = 0;

@@ -379,9 +379,9 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     int cur = 0;
     for (int pass = 0; pass < kSortPasses; pass++) {
         demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.keys[cur], s.idx[cur], desc, pass, s.hist, s.misc);
-        demux_scan_hist_kernel<<<1, 1024, 0, st>>>(s.hist, pass, s.misc);
+        demux_rowscan_kernel<<<kRadix / kRowScanWarps, 32 * kRowScanWarps, 0, st>>>(s.hist, pass, s.misc, s.row_total);
         demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.keys[cur], s.idx[cur], s.keys[cur ^ 1],
-                                                                  s.idx[cur ^ 1], desc, pass, s.hist, s.misc);
+                                                                  s.idx[cur ^ 1], desc, pass, s.hist, s.misc, s.row_total);
         cur ^= 1;
     }
     const u64* skeys = s.keys[cur];
@@ -410,13 +410,8 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
 // file-scope device array: in host code its name is only a handle, so the device address is looked up
 // once per device with cudaGetSymbolAddress (below) and that pointer is what the kernels receive.
 namespace {
-constexpr uint64_t na_align(uint64_t x) { return (x + 255) & ~(uint64_t)255; }
 constexpr uint64_t kNoAllocFrames = P2PT_NOALLOC_MAX_FRAMES;
-constexpr uint64_t kNoAllocBlocks = (kNoAllocFrames + kScanThreads - 1) / kScanThreads;
-constexpr uint64_t kNoAllocBytes =
-    2 * na_align(kNoAllocFrames * sizeof(uint64_t)) + 2 * na_align(kNoAllocFrames * sizeof(uint32_t)) +
-    na_align((uint64_t)kRadix * kSortBlocks * sizeof(uint32_t)) + na_align((kNoAllocBlocks + 1) * sizeof(uint64_t)) +
-    na_align((kNoAllocBlocks + 1) * sizeof(uint32_t)) + 256;
+constexpr uint64_t kNoAllocBytes = demux_scratch_bytes(kNoAllocFrames);      // same layout function the kernels use
 constexpr int kNoAllocMaxDevices = 64;
 std::mutex g_noalloc_mu;
 void* g_noalloc_addr[kNoAllocMaxDevices] = {};
