@@ -263,77 +263,141 @@ def run_gpu(args):
     value = world * payload_bytes / (dev_ms * 1e-3) / 1e9
 
     # ---------------- end-to-end arm: host-pointer C ABI, pinned host buffers ----------------
-    # Two contexts on this GPU, as a deployment has: the provider side seals (serve.rs:269-276 +
-    # dc.send) while the consumer side opens + demuxes (rtc.rs:88 + proxy.rs:109-170).  The two
-    # host-pointer calls run on two host threads, software-pipelined over batches (seal of batch k+1
-    # overlaps open of batch k) so that PCIe carries traffic in both directions at once.
-    import threading
-    ctx_b = p2pt.Context(local)
-    ctx_b.sessions_load(keys, ivs, keys, ivs)
+    # What a deployment does with one GPU: the batch is cut into sub-batches of whole sessions
+    # (sessions share nothing, so each sub-batch is an independent call), the provider side seals
+    # (serve.rs:269-276 + dc.send) while the consumer side opens + demuxes (rtc.rs:88 +
+    # proxy.rs:109-170).  Two seal workers and two open workers, each a host thread with its own
+    # p2pt_ctx, keep PCIe busy in both directions; every byte goes host -> device -> host inside the
+    # timed region, through the host-pointer C ABI only.
+    import queue
+    NB = 8                                   # sub-batches per step (8192 sessions = 131072 records each)
+    sub_n = n // NB
+    sub_streams = max_streams // NB
+    ctxs = [ctx] + [p2pt.Context(local) for _ in range(3)]
+    for c_ in ctxs[1:]:
+        c_.sessions_load(keys, ivs, keys, ivs)
 
     def pinned(a):
         return torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory()
     h = {k: pinned(w[k]) for k in ("session", "epoch", "seq48", "nonce8", "types", "sids", "payload", "pay_off", "rec_off")}
+    esz = {"session": 4, "epoch": 2, "seq48": 8, "nonce8": 8, "types": 1, "sids": 4, "pay_off": 8, "rec_off": 8}
+    hp = {k: h[k].data_ptr() for k in h}
     h_rec = [torch.empty(rec_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
     h_status = torch.empty(n, dtype=torch.uint8).pin_memory()
     h_desc = torch.empty(n * 24, dtype=torch.uint8).pin_memory()
-    h_uniq = torch.empty((max_streams + 1) * 4, dtype=torch.uint8).pin_memory()
-    h_usess = torch.empty((max_streams + 1) * 4, dtype=torch.uint8).pin_memory()
-    h_csr = torch.empty((max_streams + 1) * 8, dtype=torch.uint8).pin_memory()
-    h_goff = torch.empty((max_streams + 1) * 8, dtype=torch.uint8).pin_memory()
+    h_uniq = torch.empty(NB * (sub_streams + 1) * 4, dtype=torch.uint8).pin_memory()
+    h_usess = torch.empty(NB * (sub_streams + 1) * 4, dtype=torch.uint8).pin_memory()
+    h_csr = torch.empty(NB * (sub_streams + 1) * 8, dtype=torch.uint8).pin_memory()
+    h_goff = torch.empty(NB * (sub_streams + 1) * 8, dtype=torch.uint8).pin_memory()
     h_perm = torch.empty(n * 4, dtype=torch.uint8).pin_memory()
     h_gath = torch.empty(payload_bytes, dtype=torch.uint8).pin_memory()
-    kk = C.c_uint32(0)
+    kks = (C.c_uint32 * NB)()
     errs = []
 
-    def do_seal(buf):
-        try:
-            ctx.call("p2pt_pipeline_seal", n, h["session"], h["epoch"], h["seq48"], h["nonce8"], h["types"], h["sids"],
-                     h["payload"], h["pay_off"], h_rec[buf], h["rec_off"], h_status)
-        except Exception as e:   # surfaced after join
-            errs.append(e)
+    def at(name, r0):
+        return hp[name] + r0 * esz[name]
 
-    def do_open(buf):
-        try:
-            ctx_b.call("p2pt_pipeline_open_demux", n, h["session"], h_rec[buf], h["rec_off"], None, h_desc, max_streams,
-                       h_uniq, h_usess, h_csr, h_perm, C.addressof(kk), h_gath, payload_bytes, h_goff)
-        except Exception as e:
-            errs.append(e)
+    def do_seal(c_, buf, b):
+        r0 = b * sub_n
+        c_.call("p2pt_pipeline_seal", sub_n, at("session", r0), at("epoch", r0), at("seq48", r0), at("nonce8", r0),
+                at("types", r0), at("sids", r0), hp["payload"], at("pay_off", r0), h_rec[buf].data_ptr(),
+                at("rec_off", r0), h_status.data_ptr() + r0)
+
+    def do_open(c_, buf, b):
+        r0 = b * sub_n
+        so = b * (sub_streams + 1)
+        c_.call("p2pt_pipeline_open_demux", sub_n, at("session", r0), h_rec[buf].data_ptr(), at("rec_off", r0), None,
+                h_desc.data_ptr() + 24 * r0, sub_streams, h_uniq.data_ptr() + 4 * so, h_usess.data_ptr() + 4 * so,
+                h_csr.data_ptr() + 8 * so, h_perm.data_ptr() + 4 * r0, C.addressof(kks) + 4 * b,
+                h_gath.data_ptr() + r0 * PAYLOAD, sub_n * PAYLOAD, h_goff.data_ptr() + 8 * so)
 
     def e2e_run(steps):
-        """steps batches through seal -> open_demux, pipelined; steps + 1 iterations (fill + drain)."""
-        for it in range(steps + 1):
-            ts = []
-            if it < steps:
-                ts.append(threading.Thread(target=do_seal, args=(it & 1,)))
-            if it >= 1:
-                ts.append(threading.Thread(target=do_open, args=((it - 1) & 1,)))
-            for t_ in ts:
-                t_.start()
-            for t_ in ts:
-                t_.join()
-            if errs:
-                raise errs[0]
+        """steps x NB sub-batches, each sealed then opened+demuxed; 2 seal + 2 open worker threads."""
+        jobs = steps * NB
+        sealed = [threading.Event() for _ in range(jobs)]
+        opened = [threading.Event() for _ in range(jobs)]
+
+        def seal_worker(i):
+            try:
+                for q in range(i, jobs, 2):
+                    if q >= 2 * NB:
+                        opened[q - 2 * NB].wait()          # the record buffer of two steps ago is free again
+                    do_seal(ctxs[i], (q // NB) & 1, q % NB)
+                    sealed[q].set()
+            except Exception as e:
+                errs.append(e)
+                for ev_ in sealed + opened:
+                    ev_.set()
+
+        def open_worker(i):
+            try:
+                for q in range(i, jobs, 2):
+                    sealed[q].wait()
+                    do_open(ctxs[2 + i], (q // NB) & 1, q % NB)
+                    opened[q].set()
+            except Exception as e:
+                errs.append(e)
+                for ev_ in sealed + opened:
+                    ev_.set()
+        ts = [threading.Thread(target=seal_worker, args=(i,)) for i in range(2)] + \
+             [threading.Thread(target=open_worker, args=(i,)) for i in range(2)]
+        for t_ in ts:
+            t_.start()
+        for t_ in ts:
+            t_.join()
+        if errs:
+            raise errs[0]
 
     e2e_steps = max(1, min(args.steps, 6))
     e2e_run(2)
-    assert kk.value == max_streams
+    assert all(int(kks[b]) == sub_streams for b in range(NB)), list(kks)
+    assert int(h_status.sum()) == 0
     assert np.array_equal(h_gath[: 4096 * PAYLOAD].numpy().reshape(4096, PAYLOAD), got), "e2e result differs"
-    launches_e0 = ctx.launch_count() + ctx_b.launch_count()
+    tail = gathered[-4096 * PAYLOAD:].cpu().numpy()
+    assert np.array_equal(h_gath[-4096 * PAYLOAD:].numpy(), tail), "e2e result differs (tail)"
+    launches_e0 = sum(c_.launch_count() for c_ in ctxs)
     barrier()
     t0 = time.perf_counter()
     e2e_run(e2e_steps)
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
     barrier()
-    launches_e2e = (ctx.launch_count() + ctx_b.launch_count() - launches_e0) // e2e_steps
-    # un-pipelined latency of one batch through both calls, for reference
-    t0 = time.perf_counter(); do_seal(0); t_seal = time.perf_counter() - t0
-    t0 = time.perf_counter(); do_open(0); t_open = time.perf_counter() - t0
+    launches_e2e = (sum(c_.launch_count() for c_ in ctxs) - launches_e0) // e2e_steps
+    # latency of ONE sub-batch through both calls with nothing else running, for reference
+    t0 = time.perf_counter(); do_seal(ctxs[0], 0, 0); t_seal = time.perf_counter() - t0
+    t0 = time.perf_counter(); do_open(ctxs[2], 0, 0); t_open = time.perf_counter() - t0
     meta = n * (4 + 2 + 8 + 8 + 1 + 4 + 8 + 8)
     h2d = payload_bytes + meta + rec_bytes + n * (4 + 8)
-    d2h = rec_bytes + n + payload_bytes + n * 24 + n * 4 + (max_streams + 1) * (4 + 4 + 8 + 8)
+    d2h = rec_bytes + n + payload_bytes + n * 24 + n * 4 + NB * (sub_streams + 1) * (4 + 4 + 8 + 8)
     e2e_val = world * payload_bytes / e2e_s / 1e9
+
+    # single small frame, batch of 1, host buffers: launch + copies dominate; the CPU wins this one
+    from p2p_llm_tunnel_b200.protocol import TunnelMessage
+    lat = {}
+    try:
+        sse = b'data: {"token": "hello"}\n\n' + b" " * 37          # 64-byte SSE chunk
+        m1 = TunnelMessage.res_body(99, sse)
+        for _ in range(5):
+            f1 = m1.encode(ctxs[3]); TunnelMessage.decode(f1, ctxs[3])
+        t0 = time.perf_counter()
+        for _ in range(50):
+            f1 = m1.encode(ctxs[3])
+        lat["frame_encode_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
+        t0 = time.perf_counter()
+        for _ in range(50):
+            TunnelMessage.decode(f1, ctxs[3])
+        lat["frame_decode_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
+        one = {k: w[k][:1].copy() for k in ("session", "epoch", "seq48", "types", "sids")}
+        one_pay = np.frombuffer(sse, np.uint8); one_off = np.array([0, 64], np.uint64)
+        for _ in range(3):
+            ctxs[3].pipeline_seal(one["session"], one["epoch"], one["seq48"], w["nonce8"][:8], one["types"], one["sids"], one_pay, one_off)
+        t0 = time.perf_counter()
+        for _ in range(50):
+            r1 = ctxs[3].pipeline_seal(one["session"], one["epoch"], one["seq48"], w["nonce8"][:8], one["types"], one["sids"], one_pay, one_off)
+        lat["pipeline_seal_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
+        lat["note"] = "wall clock per call through the Python binding, one 64-byte RES_BODY frame, host buffers"
+    except Exception as e:
+        lat = {"error": str(e)}
 
     # PCIe as this box delivers it: pinned 1 GiB copies, each direction alone and both at once
     pcie = None
@@ -380,7 +444,7 @@ def run_gpu(args):
     stages = {"seal_ms": seal_ms, "open_ms": open_ms, "demux_gather_ms": demux_ms,
               "seal_gbs_payload": payload_bytes / seal_ms / 1e6, "open_gbs_payload": payload_bytes / open_ms / 1e6,
               "demux_gather_gbs_hbm": n * (2 * PAYLOAD + 41) / demux_ms / 1e6}
-    dom = "gcm_record_kernel<8,kPipeSeal>" if seal_ms >= open_ms else "gcm_record_kernel<8,kPipeOpen>"
+    dom = "gcm_record_kernel<4,kPipeSeal>" if seal_ms >= open_ms else "gcm_record_kernel<4,kPipeOpen>"
     dom_ms = max(seal_ms, open_ms)
     dom_bytes = seal_bytes if seal_ms >= open_ms else (2 * PAYLOAD + 91)
     achieved = n * dom_bytes / dom_ms / 1e6
@@ -426,13 +490,16 @@ def run_gpu(args):
         "cpu_baseline": cpu_baseline,
         "e2e": {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_s * 1e3, "steps": e2e_steps, "launches_per_step": int(launches_e2e),
-                "unpipelined_ms": {"pipeline_seal": t_seal * 1e3, "pipeline_open_demux": t_open * 1e3},
+                "one_subbatch_alone_ms": {"pipeline_seal": t_seal * 1e3, "pipeline_open_demux": t_open * 1e3,
+                                          "records": sub_n},
                 "pcie": pcie,
                 "frac_of_pcie": (max(h2d, d2h) / e2e_s / 1e9) / pcie["bidir_each_gbs"] if pcie and "bidir_each_gbs" in pcie else None,
-                "note": "two contexts / two host threads: seal of batch k+1 overlaps open+demux of batch k; "
-                        f"{e2e_steps} steps timed over {e2e_steps + 1} iterations (fill and drain included); "
+                "note": f"each step = the same {n}-record batch as {NB} sub-batches of whole sessions through "
+                        "p2pt_pipeline_seal then p2pt_pipeline_open_demux (host pointers, pinned memory); 2 seal + 2 open "
+                        "worker threads, one p2pt_ctx each; fill and drain of the worker pipeline are inside the timing; "
                         f"each step moves {h2d / 1e9:.2f} GB up and {d2h / 1e9:.2f} GB down over PCIe"},
         "gpu_launches": int(launches),
+        "single_frame_latency": lat,
         "clocks": clocks,
     }
     print(json.dumps(line))

@@ -85,7 +85,8 @@ void        p2pt_host_free(void* p);
 /* number of kernels this ctx has launched so far (bench.py's gpu_launches evidence) */
 uint64_t    p2pt_launch_count(p2pt_ctx* ctx);
 /* tuning knobs.  "gcm_group_width": lanes that share one record in the seal/open kernels
- * (4, 8, 16 or 32; 0 = choose from the batch's mean record length). */
+ * (4, 8, 16 or 32; 0 = library default).  "chunk_bytes": size of the pieces in which host-pointer
+ * calls overlap host->device copies, kernels and device->host copies (default 16 MiB). */
 int32_t     p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value);
 /* read-only facts: "sm_count", "lut_slack", "gcm_group_width", "n_sessions", "gcm_threads"; -1 if unknown */
 int64_t     p2pt_ctx_get_info(p2pt_ctx* ctx, const char* name);

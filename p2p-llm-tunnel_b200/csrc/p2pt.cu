@@ -47,6 +47,7 @@ struct p2pt_ctx {
     uint32_t n_sessions = 0;
     Arena arena;
     std::atomic<uint64_t> launches{0};
+    uint64_t chunk_bytes = 16u << 20;  // host-pointer calls move records in chunks of about this size
     uint32_t lut_slack = 0;        // bytes needed in front of the T-tables to reach 64 KiB alignment
     int gcm_g = 0;                 // forced group width (env P2PT_GCM_G), 0 = heuristic
 };
@@ -285,6 +286,11 @@ int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
         if (!(value == 0 || value == 4 || value == 8 || value == 16 || value == 32))
             return set_err(ctx, P2PT_ERR_ARG, "gcm_group_width must be 0, 4, 8, 16 or 32");
         ctx->gcm_g = (int)value;
+        return P2PT_OK;
+    }
+    if (strcmp(name, "chunk_bytes") == 0) {
+        if (value < (1 << 16)) return set_err(ctx, P2PT_ERR_ARG, "chunk_bytes must be at least 65536");
+        ctx->chunk_bytes = (uint64_t)value;
         return P2PT_OK;
     }
     return set_err(ctx, P2PT_ERR_ARG, std::string("unknown option: ") + name);
@@ -727,9 +733,9 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
     const int G = pick_group(ctx, n, ibytes);
     // chunk so that each chunk moves ~16 MiB of input
     uint64_t chunk = n;
-    if (ibytes > (32u << 20)) {
+    if (ibytes > 2 * ctx->chunk_bytes) {
         const uint64_t avg = ibytes / n + 1;
-        chunk = (16u << 20) / avg;
+        chunk = ctx->chunk_bytes / avg;
         if (chunk < 1024) chunk = 1024;
     }
     int si = 0;
@@ -865,8 +871,8 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
     CUDA_TRY(ctx, cudaEventRecord(ctx->events[0], s0));
     const int G = pick_group(ctx, n, ibytes);
     uint64_t chunk = n;
-    if (ibytes > (32u << 20)) {
-        chunk = (16u << 20) / (ibytes / n + 1);
+    if (ibytes > 2 * ctx->chunk_bytes) {
+        chunk = ctx->chunk_bytes / (ibytes / n + 1);
         if (chunk < 1024) chunk = 1024;
     }
     int si = 0;
