@@ -354,3 +354,63 @@ void cpufast_open_batch(uint64_t n, const uint32_t* session, const uint8_t* keys
         out_len[i] = (uint32_t)ol;
     }
 }
+
+/* ---- frame codec baseline (protocol.rs:148-172 + the reader loop's map append, serve.rs:112-139):
+ * nthreads threads each take a contiguous range of frames, as if each were one connection's
+ * reader task (proxy.rs:108-109).  phase 0 = encode, phase 1 = decode + demux append. ---- */
+typedef struct {
+    uint64_t r0, r1; const uint8_t* types; const uint32_t* sids; const uint8_t* payload; const uint64_t* pay_off;
+    uint8_t* frames; const uint64_t* frame_off; int phase; uint64_t bad, streams, body_bytes;
+} codec_job;
+
+static void* codec_worker(void* arg) {
+    codec_job* j = (codec_job*)arg;
+    if (j->phase == 0) {
+        for (uint64_t i = j->r0; i < j->r1; i++) {
+            uint8_t* o = j->frames + j->frame_off[i];
+            uint64_t len = j->pay_off[i + 1] - j->pay_off[i];
+            o[0] = j->types[i];
+            o[1] = (uint8_t)(j->sids[i] >> 24); o[2] = (uint8_t)(j->sids[i] >> 16);
+            o[3] = (uint8_t)(j->sids[i] >> 8); o[4] = (uint8_t)j->sids[i];
+            memcpy(o + 5, j->payload + j->pay_off[i], len);
+        }
+    } else {
+        stream_map m; map_init(&m, 1024);
+        for (uint64_t i = j->r0; i < j->r1; i++) {
+            const uint8_t* f = j->frames + j->frame_off[i];
+            uint64_t len = j->frame_off[i + 1] - j->frame_off[i];
+            if (len < 5 || !orc_msg_type_valid(f[0])) { j->bad++; continue; }
+            uint32_t sid = ((uint32_t)f[1] << 24) | ((uint32_t)f[2] << 16) | ((uint32_t)f[3] << 8) | f[4];
+            stream_slot* sl = map_get(&m, sid);
+            if (f[0] == 11 || f[0] == 21) map_append(sl, f + 5, len - 5);
+        }
+        j->streams = m.count;
+        for (uint64_t q = 0; q < m.nslots; q++) if (m.slots[q].used) j->body_bytes += m.slots[q].len;
+        map_free(&m);
+    }
+    return NULL;
+}
+
+int cpufast_codec(uint64_t n, const uint8_t* types, const uint32_t* sids, const uint8_t* payload, const uint64_t* pay_off,
+                  uint8_t* frames, const uint64_t* frame_off, int nthreads, double* times, uint64_t* stats) {
+    if (nthreads < 1) nthreads = 1;
+    codec_job* jobs = (codec_job*)calloc((size_t)nthreads, sizeof(codec_job));
+    pthread_t* th = (pthread_t*)calloc((size_t)nthreads, sizeof(pthread_t));
+    memset(stats, 0, 3 * sizeof(uint64_t));
+    for (int phase = 0; phase < 2; phase++) {
+        for (int t = 0; t < nthreads; t++) {
+            jobs[t].r0 = n * (uint64_t)t / (uint64_t)nthreads; jobs[t].r1 = n * (uint64_t)(t + 1) / (uint64_t)nthreads;
+            jobs[t].types = types; jobs[t].sids = sids; jobs[t].payload = payload; jobs[t].pay_off = pay_off;
+            jobs[t].frames = frames; jobs[t].frame_off = frame_off; jobs[t].phase = phase;
+            jobs[t].bad = jobs[t].streams = jobs[t].body_bytes = 0;
+        }
+        double t0 = now_s();
+        for (int t = 0; t < nthreads; t++) pthread_create(&th[t], NULL, codec_worker, &jobs[t]);
+        for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
+        times[phase] = now_s() - t0;
+        if (phase == 1)
+            for (int t = 0; t < nthreads; t++) { stats[0] += jobs[t].bad; stats[1] += jobs[t].streams; stats[2] += jobs[t].body_bytes; }
+    }
+    free(jobs); free(th);
+    return 0;
+}

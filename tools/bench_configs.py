@@ -1,0 +1,109 @@
+"""Per-config, per-kernel device-resident timings for BASELINE.json configs C2 / C3 / C4 with the CPU
+port beside them.  Prints one JSON object; bench.py (C5) stays the headline.
+usage: python tools/bench_configs.py > profiles/rNN_configs.json"""
+import ctypes as C
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as g  # noqa: E402
+import p2p_llm_tunnel_b200 as p2pt  # noqa: E402
+from p2p_llm_tunnel_b200 import workload  # noqa: E402
+
+dev = torch.device("cuda:0")
+ctx = p2pt.Context(0)
+pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+peak = json.load(open(pk)).get("hbm_gbs", 6650.0) if os.path.exists(pk) else 6650.0
+g.build_oracle()
+fast = C.CDLL(g.CPUFAST_LIB)
+cores = os.cpu_count() or 1
+s = torch.cuda.current_stream().cuda_stream
+t = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
+p = lambda a: C.c_void_p(a.ctypes.data)
+
+
+def timeit(fn, reps=5):
+    fn(); torch.cuda.synchronize()
+    best = 1e9
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return best
+
+
+def codec_config(n, P, sse):
+    w = workload.frames_workload(n, P, sse=sse)
+    d = {k: t(w[k]) for k in ("types", "sids", "payload", "pay_off", "frame_off")}
+    frames = torch.empty(n * (P + 5), dtype=torch.uint8, device=dev)
+    desc = torch.empty(n * 24, dtype=torch.uint8, device=dev)
+    sb = int(ctx.lib.p2pt_frame_demux_scratch_bytes(n))
+    scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
+    ms = 4096
+    uniq = torch.empty(ms + 1, dtype=torch.int32, device=dev); csr = torch.empty(ms + 1, dtype=torch.int64, device=dev)
+    goff = torch.empty(ms + 1, dtype=torch.int64, device=dev); perm = torch.empty(n, dtype=torch.int32, device=dev)
+    k = torch.zeros(1, dtype=torch.int32, device=dev); gathered = torch.empty(n * P, dtype=torch.uint8, device=dev)
+    enc = lambda: ctx.call("p2pt_frame_encode_batch_device", n, d["types"], d["sids"], d["payload"], d["pay_off"], frames, d["frame_off"], s)
+    dec = lambda: ctx.call("p2pt_frame_decode_batch_device", n, frames, d["frame_off"], desc, s)
+    dmx = lambda: ctx.call("p2pt_frame_demux_batch_device", n, desc, None, frames, ms, uniq, None, csr, perm, k, None, 0, None, scratch, sb, s)
+    dmg = lambda: ctx.call("p2pt_frame_demux_batch_device", n, desc, None, frames, ms, uniq, None, csr, perm, k, gathered, n * P, goff, scratch, sb, s)
+    t_enc, t_dec, t_dmx, t_dmg = timeit(enc), timeit(dec), timeit(dmx), timeit(dmg)
+    assert int(k.item()) == 4096
+    t_both = timeit(lambda: (dec(), dmg()))
+    hf = np.zeros(n * (P + 5), np.uint8)
+    res = {}
+    for nt in (1, cores):
+        times = (C.c_double * 2)(); stats = (C.c_uint64 * 3)()
+        best = [1e9, 1e9]
+        for _ in range(2):
+            fast.cpufast_codec(C.c_uint64(n), p(w["types"]), p(w["sids"]), p(w["payload"]), p(w["pay_off"]), p(hf), p(w["frame_off"]),
+                               C.c_int(nt), times, stats)
+            best = [min(best[0], times[0]), min(best[1], times[1])]
+        assert stats[0] == 0 and stats[2] == n * P
+        res[f"cpu_{nt}_threads"] = {"encode_gbs_payload": n * P / best[0] / 1e9, "decode_demux_gbs_payload": n * P / best[1] / 1e9,
+                                     "decode_demux_frames_per_s": n / best[1]}
+    assert np.array_equal(hf[: 1 << 20], frames[: 1 << 20].cpu().numpy())
+    out = {
+        "frames": n, "payload_bytes": P,
+        "encode": {"ms": t_enc, "alg_bytes_per_frame": 2 * P + 26, "hbm_gbs": n * (2 * P + 26) / t_enc / 1e6,
+                   "frac_of_hbm_peak": n * (2 * P + 26) / t_enc / 1e6 / peak, "payload_gbs": n * P / t_enc / 1e6},
+        "decode": {"ms": t_dec, "alg_bytes_per_frame": 37, "hbm_gbs": n * 37 / t_dec / 1e6, "frames_per_s": n / t_dec * 1e3},
+        "demux_no_gather": {"ms": t_dmx, "alg_bytes_per_frame": 45, "frames_per_s": n / t_dmx * 1e3},
+        "demux_gather": {"ms": t_dmg},
+        "decode_demux_gather": {"ms": t_both, "alg_bytes_per_frame": 2 * P + 41, "hbm_gbs": n * (2 * P + 41) / t_both / 1e6,
+                                "frac_of_hbm_peak": n * (2 * P + 41) / t_both / 1e6 / peak, "frames_per_s": n / t_both * 1e3,
+                                "payload_gbs": n * P / t_both / 1e6},
+    }
+    out.update(res)
+    return out
+
+
+def records_config(n, L, n_sessions):
+    keys, ivs = workload.sessions_keys(n_sessions, seed_shift=n_sessions)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    w = workload.records_workload(n, L, n_sessions=n_sessions)
+    d = {k: t(w[k]) for k in ("session", "nonce8", "raw", "raw_off", "rec_off")}
+    rec = torch.empty(n * (L + 37), dtype=torch.uint8, device=dev); out = torch.empty_like(rec)
+    status = torch.empty(n, dtype=torch.uint8, device=dev); olen = torch.empty(n, dtype=torch.int32, device=dev)
+    seal = lambda: ctx.call("p2pt_dtls_gcm_seal_batch_device", n, d["session"], d["nonce8"], d["raw"], d["raw_off"], rec, d["rec_off"], status, s)
+    opn = lambda: ctx.call("p2pt_dtls_gcm_open_batch_device", n, d["session"], rec, d["rec_off"], out, d["rec_off"], olen, status, s)
+    t_seal = timeit(seal); t_open = timeit(opn)
+    assert int(status.sum()) == 0
+    return {"records": n, "plaintext_bytes": L, "sessions": n_sessions,
+            "seal": {"ms": t_seal, "gbs_plaintext": n * L / t_seal / 1e6, "records_per_s": n / t_seal * 1e3,
+                     "alg_bytes_per_record": 2 * L + 79, "frac_of_hbm_peak": n * (2 * L + 79) / t_seal / 1e6 / peak},
+            "open": {"ms": t_open, "gbs_plaintext": n * L / t_open / 1e6, "records_per_s": n / t_open * 1e3,
+                     "alg_bytes_per_record": 2 * L + 74, "frac_of_hbm_peak": n * (2 * L + 74) / t_open / 1e6 / peak}}
+
+
+res = {"hbm_peak_gbs": peak, "host_cores": cores,
+       "C2_1M_frames_1200B_4096_streams": codec_config(1_000_000, 1200, False),
+       "C4_10M_frames_64B_sse": codec_config(10_000_000, 64, True),
+       "C3_1M_records_1200B_1_session": records_config(1_000_000, 1200, 1),
+       "C3_1M_records_1200B_4096_sessions": records_config(1_000_000, 1200, 4096)}
+print(json.dumps(res, indent=1))
