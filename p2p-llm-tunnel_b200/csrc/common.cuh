@@ -128,4 +128,31 @@ __device__ __forceinline__ void warp_copy_bytes(uint8_t* dst, const uint8_t* src
     for (u64 i = (nvec << 4) + lane; i < rem; i += 32) d2[i] = __ldg(s2 + i);
 }
 
+// Four lanes (q = 0..3) copy one short item (any alignment).  For frames of a few dozen to a few
+// hundred bytes (SSE token chunks) a whole warp per item wastes 7/8 of every load; eight items per
+// warp keeps the lanes busy.  All four lanes of the quad must call.
+__device__ __forceinline__ void quad_copy_bytes(uint8_t* dst, const uint8_t* src, uint32_t len, int q) {
+    uint32_t head = (uint32_t)((16 - ((uintptr_t)dst & 15)) & 15);
+    if (head > len) head = len;
+    for (uint32_t b = q; b < head; b += 4) dst[b] = __ldg(src + b);
+    dst += head; src += head; len -= head;
+    uint32_t nvec = len >> 4;
+    const unsigned s = (unsigned)((uintptr_t)src & 15);
+    const uint8_t* sa = src - s;
+    if (s) {   // the second aligned source vector must not run past the end of the item
+        const uint8_t* send = src + len;
+        const uint32_t safe = (send >= sa + 32) ? (uint32_t)((send - (sa + 32)) >> 4) + 1 : 0;
+        if (nvec > safe) nvec = safe;
+    }
+    for (uint32_t v = q; v < nvec; v += 4) {
+        const uint4 a = ldg128(sa + 16 * v);
+        uint4 o = a;
+        if (s) o = funnel16(a, ldg128(sa + 16 * v + 16), s);
+        stg128(dst + 16 * v, o);
+    }
+    for (uint32_t b = (nvec << 4) + q; b < len; b += 4) dst[b] = __ldg(src + b);
+}
+
+constexpr uint32_t kQuadCopyMax = 256;     // items up to this size take the 4-lane path
+
 }  // namespace p2pt

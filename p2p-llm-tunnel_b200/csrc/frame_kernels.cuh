@@ -22,23 +22,36 @@ __device__ __forceinline__ bool msg_type_valid(uint32_t b) {
     return b == 99;
 }
 
-// ---- encode: one warp per frame ----------------------------------------------------------------
+// ---- encode: a warp takes eight consecutive frames.  If all eight are short (<= 256 B, the SSE
+// token regime) each gets four lanes; otherwise the warp copies them one after another with all 32
+// lanes (aligned 16-byte vectors either way).
 __global__ void __launch_bounds__(256) frame_encode_kernel(
     u64 n, const uint8_t* __restrict__ types, const uint32_t* __restrict__ sids,
     const uint8_t* __restrict__ payload, const u64* __restrict__ pay_off,
     uint8_t* __restrict__ out, const u64* __restrict__ out_off) {
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, quad = lane >> 2, q = lane & 3;
     const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
-    for (u64 i = warp; i < n; i += nwarps) {
-        const u64 po = __ldg(pay_off + i), pe = __ldg(pay_off + i + 1);
-        uint8_t* o = out + __ldg(out_off + i);
-        if (lane < 5) {
+    for (u64 i0 = warp * 8; i0 < n; i0 += nwarps * 8) {
+        const u64 i = i0 + quad;
+        u64 po = 0, len = 0, oo = 0;
+        if (i < n) { po = __ldg(pay_off + i); len = __ldg(pay_off + i + 1) - po; oo = __ldg(out_off + i); }
+        if (i < n && q == 0) {                         // header: [type][stream_id BE]
             const uint32_t sid = __ldg(sids + i);
-            uint32_t b = lane == 0 ? (uint32_t)__ldg(types + i) : (sid >> (8 * (4 - lane))) & 0xffu;
-            o[lane] = (uint8_t)b;
+            uint8_t* o = out + oo;
+            o[0] = __ldg(types + i);
+            o[1] = (uint8_t)(sid >> 24); o[2] = (uint8_t)(sid >> 16); o[3] = (uint8_t)(sid >> 8); o[4] = (uint8_t)sid;
         }
-        warp_copy_bytes(o + 5, payload + po, pe - po, lane);
+        if (__all_sync(0xffffffffu, len <= kQuadCopyMax)) {
+            if (i < n) quad_copy_bytes(out + oo + 5, payload + po, (uint32_t)len, q);
+        } else {
+#pragma unroll 1
+            for (int f = 0; f < 8; f++) {
+                const u64 fpo = __shfl_sync(0xffffffffu, po, 4 * f), flen = __shfl_sync(0xffffffffu, len, 4 * f);
+                const u64 foo = __shfl_sync(0xffffffffu, oo, 4 * f);
+                if (i0 + f < n) warp_copy_bytes(out + foo + 5, payload + fpo, flen, lane);
+            }
+        }
     }
 }
 
@@ -103,7 +116,7 @@ struct DemuxScratch {
     uint32_t* hist;        // kRadix * kSortBlocks
     u64* blk_bytes;        // per scan block: body bytes
     uint32_t* blk_heads;   // per scan block: stream heads
-    u64* misc;             // [0] = number of valid frames m, [1] = OR of keys, [2] = OR of ~keys
+    u64* misc;             // [1] = OR of keys, [2] = OR of ~keys, [3] = number of undecodable frames
     uint32_t* row_total;   // kRadix digit totals of the current pass
 };
 
@@ -147,6 +160,7 @@ __global__ void __launch_bounds__(256) demux_init_kernel(u64 n, const p2pt_desc*
                                                          u64* __restrict__ keys, uint32_t* __restrict__ idx,
                                                          u64* __restrict__ misc) {
     u64 vor = 0, vnor = 0;
+    uint32_t bad = 0;
     const u64 stride = (u64)gridDim.x * blockDim.x;
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         u64 k = desc[i].stream_id;
@@ -154,7 +168,10 @@ __global__ void __launch_bounds__(256) demux_init_kernel(u64 n, const p2pt_desc*
         keys[i] = k;
         idx[i] = (uint32_t)i;
         vor |= k; vnor |= ~k;
+        bad += desc[i].status != P2PT_ST_OK;
     }
+    bad = __reduce_add_sync(0xffffffffu, bad);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(misc + 3, (u64)bad);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         vor |= __shfl_xor_sync(0xffffffffu, vor, o);
@@ -163,11 +180,13 @@ __global__ void __launch_bounds__(256) demux_init_kernel(u64 n, const p2pt_desc*
     if ((threadIdx.x & 31) == 0) { atomicOr(misc + 1, vor); atomicOr(misc + 2, vnor); }
 }
 
-// a key byte that is identical in every key needs no sorting pass
+// a key byte that is identical in every key needs no sorting pass; neither does the validity pass
+// when every frame decoded
 __device__ __forceinline__ bool demux_pass_trivial(const u64* misc, int pass) {
-    if (pass >= kKeyPasses) return false;
+    if (pass >= kKeyPasses) return misc[3] == 0;
     return (((misc[1] & misc[2]) >> (8 * pass)) & 0xffu) == 0;
 }
+__device__ __forceinline__ u64 demux_valid_count(u64 n, const u64* misc) { return n - misc[3]; }
 
 __device__ __forceinline__ void demux_tile(u64 n, u64& lo, u64& hi) {
     const u64 per = (n + kSortBlocks - 1) / kSortBlocks;
@@ -225,10 +244,7 @@ __global__ void __launch_bounds__(32 * kRowScanWarps) demux_rowscan_kernel(uint3
         if (b < kSortBlocks) r[b] = carry + incl - v[i];
         carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    if (lane == 0) {
-        row_total[row] = carry;
-        if (pass == kKeyPasses && row == 0) misc[0] = carry;      // number of decodable frames
-    }
+    if (lane == 0) row_total[row] = carry;
 }
 
 __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
@@ -353,7 +369,7 @@ __device__ __forceinline__ HeadBytes block_scan_excl(HeadBytes v, HeadBytes& tot
 __global__ void __launch_bounds__(kScanThreads) demux_blocksum_kernel(
     u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx, const p2pt_desc* __restrict__ desc,
     const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes) {
-    const u64 m = misc[0];
+    const u64 m = demux_valid_count(n, misc);
     const u64 j = (u64)blockIdx.x * kScanThreads + threadIdx.x;
     HeadBytes tot;
     (void)block_scan_excl(demux_item(j, m, keys, idx, desc), tot);
@@ -388,7 +404,7 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
     u64 nblk, uint32_t max_streams, uint32_t* __restrict__ uniq_sid, uint32_t* __restrict__ uniq_session,
     u64* __restrict__ csr, uint32_t* __restrict__ perm, uint32_t* __restrict__ k_out,
     u64* __restrict__ gathered_off, u64* __restrict__ dst_off) {
-    const u64 m = misc[0];
+    const u64 m = demux_valid_count(n, misc);
     const u64 j = (u64)blockIdx.x * kScanThreads + threadIdx.x;
     HeadBytes it = demux_item(j, m, keys, idx, desc);
     HeadBytes tot;
@@ -419,22 +435,38 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
     }
 }
 
-// Gather: one warp per decodable frame, body frames only (serve.rs:120-124 extend_from_slice).
+// Gather: body frames only (serve.rs:120-124 extend_from_slice).  Same eight-items-per-warp
+// scheme as the encoder: four lanes per short frame, the whole warp per long one.
 __global__ void __launch_bounds__(256) demux_gather_kernel(
-    const u64* __restrict__ misc, const uint32_t* __restrict__ perm, const u64* __restrict__ dst_off,
+    u64 n, const u64* __restrict__ misc, const uint32_t* __restrict__ perm, const u64* __restrict__ dst_off,
     const p2pt_desc* __restrict__ desc, const uint8_t* __restrict__ in,
     uint8_t* __restrict__ gathered, u64 gathered_cap, const uint32_t* __restrict__ k_out, uint32_t max_streams) {
-    const u64 m = misc[0];
+    const u64 m = demux_valid_count(n, misc);
     if (*k_out > max_streams) return;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, quad = lane >> 2, q = lane & 3;
     const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
-    for (u64 j = warp; j < m; j += nwarps) {
-        const p2pt_desc d = desc[perm[j]];
-        if (!(d.msg_type == 11 || d.msg_type == 21) || d.pay_len == 0) continue;
-        const u64 o = dst_off[j];
-        if (o + d.pay_len > gathered_cap) continue;      // caller sees the overflow via gathered_off[k]
-        warp_copy_bytes(gathered + o, in + d.pay_off, d.pay_len, lane);
+    for (u64 j0 = warp * 8; j0 < m; j0 += nwarps * 8) {
+        const u64 j = j0 + quad;
+        u64 so = 0, o = 0;
+        uint32_t len = 0;
+        if (j < m) {
+            const p2pt_desc d = desc[perm[j]];
+            if ((d.msg_type == 11 || d.msg_type == 21) && d.pay_len) {
+                o = dst_off[j];
+                if (o + d.pay_len <= gathered_cap) { len = d.pay_len; so = d.pay_off; }   // overflow: caller sees it in gathered_off[k]
+            }
+        }
+        if (__all_sync(0xffffffffu, len <= kQuadCopyMax)) {
+            if (len) quad_copy_bytes(gathered + o, in + so, len, q);
+        } else {
+#pragma unroll 1
+            for (int f = 0; f < 8; f++) {
+                const u64 fso = __shfl_sync(0xffffffffu, so, 4 * f), fo = __shfl_sync(0xffffffffu, o, 4 * f);
+                const uint32_t flen = __shfl_sync(0xffffffffu, len, 4 * f);
+                if (flen) warp_copy_bytes(gathered + fo, in + fso, flen, lane);
+            }
+        }
     }
 }
 

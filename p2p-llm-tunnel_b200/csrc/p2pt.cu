@@ -337,7 +337,7 @@ int32_t p2pt_frame_encode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t*
     if (n == 0) return P2PT_OK;
     if (!types || !sids || !pay_off || !out || !out_off) return set_err(ctx, P2PT_ERR_ARG, "frame_encode: null argument");
     DeviceGuard dg(ctx->device);
-    frame_encode_kernel<<<grid_for(ctx, n, 8, 16), 256, 0, (cudaStream_t)stream>>>(
+    frame_encode_kernel<<<grid_for(ctx, (n + 7) / 8, 8, 16), 256, 0, (cudaStream_t)stream>>>(
         n, types, sids, payload, (const u64*)pay_off, out, (const u64*)out_off);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
@@ -401,7 +401,7 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
                                                               (u64*)gathered_off, dst_off);
     count_launch(ctx, 1 + 3 * kSortPasses + 3);
     if (gathered) {
-        demux_gather_kernel<<<grid_for(ctx, n, 8, 16), 256, 0, st>>>(s.misc, perm, dst_off, desc, in, gathered,
+        demux_gather_kernel<<<grid_for(ctx, (n + 7) / 8, 8, 16), 256, 0, st>>>(n, s.misc, perm, dst_off, desc, in, gathered,
                                                                     gathered_cap, k_out, max_streams);
         count_launch(ctx);
     }
