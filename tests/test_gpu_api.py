@@ -127,3 +127,95 @@ def test_device_pointer_entry_points(ctx):
     assert np.array_equal(csr.cpu().numpy()[:kk + 1].astype(np.uint64), exp["csr"])
     assert np.array_equal(perm.cpu().numpy().astype(np.uint32), exp["perm"])
     assert np.array_equal(gathered.cpu().numpy(), exp["gathered"])
+
+
+def test_device_kernels_never_write_outside_their_items(ctx):
+    """Canary check (compute-sanitizer is not available on this pool): output slots are laid out with
+    gaps at odd offsets inside a buffer pre-filled with 0xCD; after the kernels ran every byte that
+    is not part of an item must still be 0xCD, and the items must match the oracle."""
+    import torch
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(99)
+    s = torch.cuda.current_stream().cuda_stream
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
+    keys = rng.integers(0, 256, (5, 16), dtype=np.uint8); ivs = rng.integers(0, 256, (5, 4), dtype=np.uint8)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    n = 700
+    lens = rng.integers(0, 600, n).astype(np.uint64); lens[:20] = np.arange(20)
+    raw_off = np.zeros(n + 1, np.uint64); np.cumsum(lens + np.uint64(13), out=raw_off[1:])
+    raw = rng.integers(0, 256, int(raw_off[-1]), dtype=np.uint8)
+    for i in range(n):
+        o = int(raw_off[i]); raw[o] = 23; raw[o + 1] = 0xFE; raw[o + 2] = 0xFD
+    session = rng.integers(0, 5, n).astype(np.uint32); nonce = rng.integers(0, 256, 8 * n, dtype=np.uint8)
+    slot = lens + np.uint64(37) + rng.integers(1, 40, n).astype(np.uint64)
+    rec_off = np.zeros(n + 1, np.uint64); np.cumsum(slot, out=rec_off[1:]); rec_off += np.uint64(7)
+    total = int(rec_off[-1]) + 64
+
+    def mask_of(off, item_len):
+        m = np.zeros(total, bool)
+        for i in range(n):
+            m[int(off[i]):int(off[i]) + int(item_len[i])] = True
+        return m
+
+    for g in (4, 8, 16, 32):
+        ctx.set_option("gcm_group_width", g)
+        rec = torch.full((total,), 0xCD, dtype=torch.uint8, device=dev)
+        status = torch.zeros(n, dtype=torch.uint8, device=dev)
+        ctx.call("p2pt_dtls_gcm_seal_batch_device", n, t(session), t(nonce), t(raw), t(raw_off), rec, t(rec_off), status, s)
+        torch.cuda.synchronize()
+        got = rec.cpu().numpy()
+        m = mask_of(rec_off, lens + np.uint64(37))
+        assert np.all(got[~m] == 0xCD), f"seal wrote outside its records (G={g})"
+        exp, _, _ = ob.dtls_seal(session, keys, ivs, nonce, raw, raw_off, rec_off)
+        assert np.array_equal(got[:int(rec_off[-1])][m[:int(rec_off[-1])]], exp[m[:int(rec_off[-1])]])
+        # open takes the record length from the input offsets, so its input is packed tight; its
+        # OUTPUT slots keep the gaps
+        tight_off = np.zeros(n + 1, np.uint64); np.cumsum(lens + np.uint64(37), out=tight_off[1:])
+        tight = np.concatenate([got[int(rec_off[i]):int(rec_off[i]) + int(lens[i]) + 37] for i in range(n)])
+        out = torch.full((total,), 0xCD, dtype=torch.uint8, device=dev)
+        olen = torch.zeros(n, dtype=torch.int32, device=dev)
+        ctx.call("p2pt_dtls_gcm_open_batch_device", n, t(session), t(tight), t(tight_off), out, t(rec_off), olen, status, s)
+        torch.cuda.synchronize()
+        assert int(status.sum()) == 0
+        go = out.cpu().numpy()
+        mo = mask_of(rec_off, lens + np.uint64(13))
+        assert np.all(go[~mo] == 0xCD), f"open wrote outside its records (G={g})"
+        for i in range(0, n, 7):
+            a = int(rec_off[i])
+            assert np.array_equal(go[a + 13:a + 13 + int(lens[i])], raw[int(raw_off[i]) + 13:int(raw_off[i + 1])])
+    ctx.set_option("gcm_group_width", 0)
+
+    # frame encode with gapped, unaligned slots (short and long payloads mixed)
+    plens = rng.integers(0, 900, n).astype(np.uint64); plens[::3] = rng.integers(0, 80, len(plens[::3]))
+    pay_off = np.zeros(n + 1, np.uint64); np.cumsum(plens, out=pay_off[1:])
+    payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+    fslot = plens + np.uint64(5) + rng.integers(1, 30, n).astype(np.uint64)
+    f_off = np.zeros(n + 1, np.uint64); np.cumsum(fslot, out=f_off[1:]); f_off += np.uint64(3)
+    total = int(f_off[-1]) + 64
+    types = np.full(n, 21, np.uint8); sids = rng.integers(1, 9, n).astype(np.uint32)
+    frames = torch.full((total,), 0xCD, dtype=torch.uint8, device=dev)
+    ctx.call("p2pt_frame_encode_batch_device", n, t(types), t(sids), t(payload), t(pay_off), frames, t(f_off), s)
+    torch.cuda.synchronize()
+    gf = frames.cpu().numpy()
+    mf = mask_of(f_off, plens + np.uint64(5))
+    assert np.all(gf[~mf] == 0xCD), "frame_encode wrote outside its frames"
+    expf, _ = ob.frame_encode(types, sids, payload, pay_off, f_off)
+    assert np.array_equal(gf[:int(f_off[-1])][mf[:int(f_off[-1])]], expf[mf[:int(f_off[-1])]])
+    # gather into a canary-filled buffer: exactly the body bytes, nothing after them
+    from p2p_llm_tunnel_b200._lib import DESC_DTYPE
+    tight_off = np.zeros(n + 1, np.uint64); np.cumsum(plens + np.uint64(5), out=tight_off[1:])
+    tight, _ = ob.frame_encode(types, sids, payload, pay_off)
+    desc = ob.frame_decode(tight, tight_off)
+    body = int(plens.sum())
+    gathered = torch.full((body + 256,), 0xCD, dtype=torch.uint8, device=dev)
+    sb = int(ctx.lib.p2pt_frame_demux_scratch_bytes(n))
+    scratch = torch.zeros(sb, dtype=torch.uint8, device=dev)
+    uniq = torch.zeros(n + 1, dtype=torch.int32, device=dev); csr = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+    goff = torch.zeros(n + 1, dtype=torch.int64, device=dev); perm = torch.zeros(n, dtype=torch.int32, device=dev)
+    k = torch.zeros(1, dtype=torch.int32, device=dev)
+    ctx.call("p2pt_frame_demux_batch_device", n, t(desc.view(np.uint8)), None, t(tight), n, uniq, None, csr, perm, k, gathered,
+             body, goff, scratch, sb, s)
+    torch.cuda.synchronize()
+    gg = gathered.cpu().numpy()
+    e = ob.frame_demux(desc, tight)
+    assert np.array_equal(gg[:body], e["gathered"]) and np.all(gg[body:] == 0xCD)
