@@ -61,7 +61,8 @@ class P2ptError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(_HERE, LIB_NAME)
+    # P2PT_LIB lets the tuning scripts load an alternative build of the same library
+    return os.environ.get("P2PT_LIB") or os.path.join(_HERE, LIB_NAME)
 
 
 _lib = None

@@ -240,7 +240,14 @@ struct GcmArgs {
     uint32_t m8, m16, m24;        // 1<<8, 1<<16, 1<<24 (see SmemLut)
 };
 
-constexpr int kGcmThreads = 1024;
+#ifndef P2PT_GCM_THREADS
+#define P2PT_GCM_THREADS 1024
+#endif
+#ifndef P2PT_GCM_UNROLL
+#define P2PT_GCM_UNROLL 1
+#endif
+constexpr int kGcmThreads = P2PT_GCM_THREADS;
+constexpr int kGcmUnroll = P2PT_GCM_UNROLL;
 constexpr uint32_t kGroupSlotBytes = 336;   // 11 x 16 B round keys + 9 x 16 B GHASH multiplier rows, padded
                                             // so that neighbouring groups' rows fall in different banks
 
@@ -428,6 +435,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
         uint32_t last_u = 0xffffffffu;
 
         const uint32_t rounds = (slots + G - 1) / G;
+#pragma unroll kGcmUnroll
         for (uint32_t t = 0; t < rounds; t++) {
             const uint32_t u = t * G + j;
             const int c = (int)u - 1;                        // body block index; -1 = J0/AAD slot

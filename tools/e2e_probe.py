@@ -14,7 +14,7 @@ sys.path.insert(0, ROOT)
 import p2p_llm_tunnel_b200 as p2pt  # noqa: E402
 from p2p_llm_tunnel_b200 import workload  # noqa: E402
 
-S, R, P, NB = 65536, 16, 1200, 8
+S, R, P, NB = 65536, 16, 1200, int(os.environ.get("NB", "8"))
 w = workload.pipeline_workload(S, R, P)
 keys, ivs = workload.sessions_keys(S)
 n = w["n"]; sub_n = n // NB; sub_streams = S * 4 // NB
@@ -81,12 +81,11 @@ for b in range(NB):
     open_(ctxs[0], b)
 assert all(int(k) == sub_streams for k in kks)
 gb = n * P / 1e9
-for name, ws in (("seal x1", [(seal, 0)]), ("seal x2", [(seal, 0), (seal, 1)]),
-                 ("open x2", [(open_, 0), (open_, 1)]), ("seal x2 + open x2", [(seal, 0), (seal, 1), (open_, 2), (open_, 3)][:2 + min(2, nctx - 2)] if nctx >= 4 else [(seal, 0), (open_, 1)])):
+NW = int(os.environ.get("NW", "2"))
+for name, ws in ((f"seal x{NW} + open x{NW}", [(seal, i) for i in range(NW)] + [(open_, NW + i) for i in range(NW)]),):
     t = run(ws)
-    both = "+" in name
-    print(f"{name:22s} {t * 1e3:8.2f} ms per {n} records{' (each direction)' if both else ''}  -> {gb / t:6.2f} GB/s payload per flow")
-
+    print(f"NB={NB} CHUNK_MB={os.environ.get('CHUNK_MB')} {name:22s} {t * 1e3:8.2f} ms per {n} records (each direction) -> {gb / t:6.2f} GB/s payload per flow")
+sys.exit(0)
 # raw DMA over the very buffers the calls use: payload up, records down, at the same time
 dev = torch.device("cuda:0")
 d_pay = torch.empty(n * P, dtype=torch.uint8, device=dev); d_rec = torch.empty(rec_bytes, dtype=torch.uint8, device=dev)
