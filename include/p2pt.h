@@ -50,6 +50,9 @@ extern "C" {
 #define P2PT_ST_NO_ROOM_FOR_NONCE 4  /* webrtc-dtls ErrNotEnoughRoomForNonce: len <= 13 + 8 */
 #define P2PT_ST_PASS_THROUGH      5  /* ChangeCipherSpec (type 20) record copied unmodified */
 #define P2PT_ST_BAD_HEADER        6  /* RecordLayerHeader::unmarshal failure: < 13 bytes or version */
+#define P2PT_ST_SCTP_BAD_CHECKSUM 7  /* webrtc-sctp ErrChecksumMismatch (CRC32c) */
+#define P2PT_ST_SCTP_MALFORMED    8  /* not a packet with exactly one DATA chunk of <= 1200 bytes */
+#define P2PT_ST_SCTP_INCOMPLETE   9  /* message: fragments missing between B and E in this batch */
 
 /* protocol.rs:9-12 */
 #define P2PT_MAX_FRAME_SIZE 65536u
@@ -60,6 +63,10 @@ extern "C" {
 #define P2PT_REC_NONCE      8u
 #define P2PT_REC_TAG        16u
 #define P2PT_REC_OVERHEAD   24u   /* sealed = raw + 8 + 16 */
+
+/* SCTP geometry (webrtc-sctp 0.10.0: INITIAL_MTU 1228 - 12 common header - 16 DATA chunk header) */
+#define P2PT_SCTP_MAX_PAYLOAD 1200u
+#define P2PT_SCTP_OVERHEAD    28u
 
 typedef struct p2pt_ctx p2pt_ctx;
 
@@ -73,6 +80,17 @@ typedef struct {
     uint8_t  status;     /* P2PT_ST_OK / TOO_SHORT / UNKNOWN_TYPE */
     uint8_t  pad[6];
 } p2pt_desc;             /* 24 bytes */
+
+/* One parsed SCTP DATA chunk (RFC 4960 3.3.1).  flags: bit0 E(nd), bit1 B(egin), bit2 U, bit3 I. */
+typedef struct {
+    uint32_t tsn;
+    uint16_t stream_id;
+    uint16_t ssn;
+    uint32_t ppid;
+    uint8_t  flags;
+    uint8_t  status;     /* P2PT_ST_OK / SCTP_BAD_CHECKSUM / SCTP_MALFORMED */
+    uint8_t  pad[2];
+} p2pt_sctp_chunk;       /* 16 bytes */
 
 /* ---- context ---------------------------------------------------------------------------- */
 int32_t     p2pt_abi_version(void);
@@ -167,6 +185,34 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
                                  uint64_t* csr, uint32_t* perm, uint32_t* k_out,
                                  uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off);
 
+/* ---- SCTP DATA chunks + CRC32c: the layer between the frame and the record.
+ *      webrtc-sctp 0.10.0 (un-vendored, Cargo.lock:2910-2911) cuts every data-channel message into
+ *      DATA chunks of <= 1200 bytes and checksums each packet with CRC32c (RFC 4960 3.1, 3.3.1, app. B).
+ *      Here: one DATA chunk per packet, fragments of one message get consecutive TSNs, B / E flags. */
+uint64_t p2pt_sctp_fragments(uint64_t msg_len);        /* max(1, ceil(len / 1200)) */
+uint64_t p2pt_sctp_packets_bytes(uint64_t msg_len);    /* bytes of all packets of one message, no DTLS header */
+/* messages -> packets, packed back to back into out.  Per message: ports, verification tag, stream id,
+ * stream sequence number, PPID (53 = binary), TSN of its first fragment.  If epoch != NULL every packet
+ * is preceded by a 13-byte DTLS record header (type 23, fe fd, epoch[i], seq48_first[i] + fragment,
+ * length), i.e. the output is directly the `raw` input of p2pt_dtls_gcm_seal_batch.
+ * pkt_off receives n_pkts + 1 byte offsets; pkt_cap = entries available in pkt_off. */
+int32_t p2pt_sctp_packetize_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg, const uint64_t* msg_off,
+                                  const uint16_t* src_port, const uint16_t* dst_port, const uint32_t* vtag,
+                                  const uint16_t* sid, const uint16_t* ssn, const uint32_t* ppid, const uint32_t* tsn0,
+                                  const uint16_t* epoch, const uint64_t* seq48_first,
+                                  uint8_t* out, uint64_t out_cap, uint64_t* pkt_off, uint64_t pkt_cap,
+                                  uint64_t* n_pkts_out);
+/* packets (each after `headroom` bytes, 13 when they come out of p2pt_dtls_gcm_open_batch) -> CRC check,
+ * chunk parse, and reassembly: fragments are ordered by (session, TSN) (TSNs must not wrap inside a
+ * batch, duplicates must have been dropped), messages = runs from a B to an E fragment, their payloads
+ * concatenated into msg with msg_off[n_msgs + 1] -- exactly the (buffer, offsets) input of
+ * p2pt_frame_decode_batch.  msg_first[m] = packet index of message m's first fragment (its info gives
+ * stream / ssn / ppid); msg_status[m] = OK or SCTP_INCOMPLETE.  info (n entries) is always filled. */
+int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const uint8_t* in, const uint64_t* in_off,
+                                          uint32_t headroom, const uint32_t* session, p2pt_sctp_chunk* info,
+                                          uint32_t max_msgs, uint8_t* msg, uint64_t msg_cap, uint64_t* msg_off,
+                                          uint32_t* msg_first, uint8_t* msg_status, uint32_t* n_msgs_out);
+
 /* ---- device-pointer variants: same arguments, all pointers are device pointers, `stream` is a
  *      cudaStream_t.  They enqueue on `stream` and return without synchronising. -------------- */
 int32_t p2pt_frame_encode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* types, const uint32_t* sids,
@@ -208,6 +254,23 @@ int32_t p2pt_frame_demux_batch_device_noalloc(p2pt_ctx* ctx, uint64_t n, const p
                                               uint64_t* csr, uint32_t* perm,
                                               uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
                                               uint64_t* gathered_off, void* stream);
+/* device forms of the SCTP calls.  packetize: the caller supplies the layout -- out_msg_off[i] = byte offset
+ * of message i's first packet (its packets follow back to back), pkt_first[n + 1] = running packet count;
+ * pkt_off[pkt_first[n] + 1] is written.  reassemble: scratch of p2pt_sctp_reassemble_scratch_bytes(n). */
+int32_t p2pt_sctp_packetize_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg, const uint64_t* msg_off,
+                                         const uint16_t* src_port, const uint16_t* dst_port, const uint32_t* vtag,
+                                         const uint16_t* sid, const uint16_t* ssn, const uint32_t* ppid, const uint32_t* tsn0,
+                                         const uint16_t* epoch, const uint64_t* seq48_first,
+                                         uint8_t* out, const uint64_t* out_msg_off, const uint64_t* pkt_first,
+                                         uint64_t* pkt_off, void* stream);
+int32_t p2pt_sctp_unpack_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const uint8_t* in, const uint64_t* in_off,
+                                      uint32_t headroom, p2pt_sctp_chunk* info, p2pt_desc* desc, void* stream);
+uint64_t p2pt_sctp_reassemble_scratch_bytes(uint64_t n_pkts);
+int32_t p2pt_sctp_reassemble_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const p2pt_sctp_chunk* info,
+                                          const p2pt_desc* desc, const uint32_t* session, const uint8_t* in,
+                                          uint32_t max_msgs, uint8_t* msg, uint64_t msg_cap, uint64_t* msg_off,
+                                          uint32_t* msg_first, uint8_t* msg_status, uint32_t* n_msgs_out,
+                                          void* scratch, uint64_t scratch_bytes, void* stream);
 int32_t p2pt_dtls_gcm_seal_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
                                         const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
                                         uint8_t* rec, const uint64_t* rec_off, uint8_t* status, void* stream);

@@ -417,3 +417,95 @@ void orc_dtls_open_batch(uint64_t n, const uint32_t* session,
         out_len[i] = (uint32_t)ol;
     }
 }
+
+/* ------------------------------------------------------------------------------------------ */
+/* SCTP DATA chunks + CRC32c.  webrtc-sctp 0.10.0 (un-vendored): packet.rs marshal / unmarshal,  */
+/* chunk_payload_data.rs, util.rs generate_packet_checksum.  Layout per RFC 4960 3.1 / 3.3.1.    */
+/* ------------------------------------------------------------------------------------------ */
+
+/* CRC32c (Castagnoli), bit-serial and reflected: polynomial 0x1EDC6F41 -> 0x82F63B78, init and
+ * final xor 0xFFFFFFFF (RFC 3720 12.1 / RFC 4960 appendix B). */
+uint32_t orc_crc32c(const uint8_t* p, size_t len) {
+    uint32_t crc = 0xFFFFFFFFu;
+    for (size_t i = 0; i < len; i++) {
+        crc ^= p[i];
+        for (int b = 0; b < 8; b++) crc = (crc >> 1) ^ (0x82F63B78u & (0u - (crc & 1u)));
+    }
+    return ~crc;
+}
+
+uint64_t orc_sctp_fragments(uint64_t msg_len) {
+    uint64_t k = (msg_len + ORC_SCTP_MAX_PAYLOAD - 1) / ORC_SCTP_MAX_PAYLOAD;
+    return k ? k : 1;
+}
+
+uint64_t orc_sctp_packets_bytes(uint64_t msg_len) {
+    uint64_t k = orc_sctp_fragments(msg_len);
+    uint64_t last = msg_len - (k - 1) * ORC_SCTP_MAX_PAYLOAD;
+    return (k - 1) * (28 + ORC_SCTP_MAX_PAYLOAD) + 28 + ((last + 3) & ~(uint64_t)3);
+}
+
+static void put16(uint8_t* p, uint32_t v) { p[0] = (uint8_t)(v >> 8); p[1] = (uint8_t)v; }
+static void put32(uint8_t* p, uint32_t v) { p[0] = (uint8_t)(v >> 24); p[1] = (uint8_t)(v >> 16); p[2] = (uint8_t)(v >> 8); p[3] = (uint8_t)v; }
+
+uint64_t orc_sctp_packetize(const uint8_t* msg, uint64_t len, uint16_t src_port, uint16_t dst_port, uint32_t vtag,
+                            uint16_t sid, uint16_t ssn, uint32_t ppid, uint32_t tsn0,
+                            int dtls_hdr, uint16_t epoch, uint64_t seq48_first, uint8_t* out) {
+    uint64_t k = orc_sctp_fragments(len), w = 0;
+    for (uint64_t f = 0; f < k; f++) {
+        uint64_t off = f * ORC_SCTP_MAX_PAYLOAD;
+        uint32_t fl = (uint32_t)(len - off < ORC_SCTP_MAX_PAYLOAD ? len - off : ORC_SCTP_MAX_PAYLOAD);
+        uint32_t padded = (fl + 3) & ~3u, plen = 28 + padded;
+        if (dtls_hdr) {
+            uint8_t* h = out + w;
+            uint64_t seq = seq48_first + f;
+            h[0] = 23; h[1] = 0xfe; h[2] = 0xfd; put16(h + 3, epoch);
+            for (int b = 0; b < 6; b++) h[5 + b] = (uint8_t)(seq >> (8 * (5 - b)));
+            put16(h + 11, plen);
+            w += 13;
+        }
+        uint8_t* p = out + w;
+        put16(p, src_port); put16(p + 2, dst_port); put32(p + 4, vtag);
+        p[8] = p[9] = p[10] = p[11] = 0;                                  /* checksum placeholder */
+        p[12] = 0;                                                        /* chunk type DATA */
+        p[13] = (uint8_t)((f == 0 ? 2 : 0) | (f == k - 1 ? 1 : 0));       /* B / E flags */
+        put16(p + 14, 16 + fl);                                           /* chunk length excludes padding */
+        put32(p + 16, tsn0 + (uint32_t)f);
+        put16(p + 20, sid); put16(p + 22, ssn); put32(p + 24, ppid);
+        if (fl) memcpy(p + 28, msg + off, fl);
+        for (uint32_t z = fl; z < padded; z++) p[28 + z] = 0;
+        uint32_t c = orc_crc32c(p, plen);
+        p[8] = (uint8_t)c; p[9] = (uint8_t)(c >> 8); p[10] = (uint8_t)(c >> 16); p[11] = (uint8_t)(c >> 24);   /* little-endian */
+        w += plen;
+    }
+    return w;
+}
+
+int orc_sctp_unpack(const uint8_t* pkt, uint64_t len, uint32_t headroom, orc_sctp_chunk* info,
+                    uint64_t* pay_off, uint32_t* pay_len) {
+    memset(info, 0, sizeof *info);
+    *pay_off = 0; *pay_len = 0;
+    if (len < (uint64_t)headroom + 12) { info->status = ORC_SCTP_MALFORMED; return info->status; }
+    const uint8_t* p = pkt + headroom;
+    uint64_t n = len - headroom;
+    /* checksum over the packet with the checksum field zeroed (verified first, like Packet::unmarshal) */
+    uint8_t* tmp = (uint8_t*)malloc(n);
+    memcpy(tmp, p, n);
+    tmp[8] = tmp[9] = tmp[10] = tmp[11] = 0;
+    uint32_t c = orc_crc32c(tmp, n);
+    free(tmp);
+    uint32_t theirs = (uint32_t)p[8] | ((uint32_t)p[9] << 8) | ((uint32_t)p[10] << 16) | ((uint32_t)p[11] << 24);
+    if (c != theirs) { info->status = ORC_SCTP_BAD_CHECKSUM; return info->status; }
+    if (n < 28 || p[12] != 0) { info->status = ORC_SCTP_MALFORMED; return info->status; }
+    uint32_t clen = ((uint32_t)p[14] << 8) | p[15];
+    if (clen < 16 || 12 + (uint64_t)((clen + 3) & ~3u) != n) { info->status = ORC_SCTP_MALFORMED; return info->status; }
+    info->flags = p[13];
+    info->tsn = ((uint32_t)p[16] << 24) | ((uint32_t)p[17] << 16) | ((uint32_t)p[18] << 8) | p[19];
+    info->stream_id = (uint16_t)(((uint32_t)p[20] << 8) | p[21]);
+    info->ssn = (uint16_t)(((uint32_t)p[22] << 8) | p[23]);
+    info->ppid = ((uint32_t)p[24] << 24) | ((uint32_t)p[25] << 16) | ((uint32_t)p[26] << 8) | p[27];
+    info->status = ORC_OK;
+    *pay_off = (uint64_t)headroom + 28;
+    *pay_len = clen - 16;
+    return ORC_OK;
+}

@@ -34,7 +34,9 @@ enum {
     ORC_AUTH_FAIL = 3,        /* aes-gcm decrypt_in_place Err */
     ORC_NO_ROOM_FOR_NONCE = 4,/* webrtc-dtls ErrNotEnoughRoomForNonce */
     ORC_PASS_THROUGH = 5,     /* ChangeCipherSpec record returned unmodified */
-    ORC_BAD_HEADER = 6        /* RecordLayerHeader::unmarshal failure (short / version) */
+    ORC_BAD_HEADER = 6,       /* RecordLayerHeader::unmarshal failure (short / version) */
+    ORC_SCTP_BAD_CHECKSUM = 7,/* webrtc-sctp ErrChecksumMismatch */
+    ORC_SCTP_MALFORMED = 8    /* shorter than the 12-byte common header, or not exactly one DATA chunk */
 };
 
 /* 24-byte frame descriptor, identical to p2pt_desc in include/p2pt.h */
@@ -90,6 +92,29 @@ void orc_dtls_open_batch(uint64_t n, const uint32_t* session,
                          const uint8_t* keys16, const uint8_t* ivs4,
                          const uint8_t* rec, const uint64_t* rec_off,
                          uint8_t* out, const uint64_t* out_off, uint32_t* out_len, uint8_t* status);
+
+/* ---- SCTP DATA-chunk packetise / unpack + CRC32c.  Restates webrtc-sctp 0.10.0
+ *      (UN-VENDORED, /root/reference/tunnel/Cargo.lock:2910-2911; CRC via crc 3.4.0, :420-421): RFC 4960
+ *      3.1 common header, 3.3.1 DATA chunk, appendix B checksum.  CRC32c itself is pinned by the RFC 3720
+ *      B.4 vectors; the packet layout is "parity unpinned" like the DTLS layout. ---- */
+#define ORC_SCTP_MAX_PAYLOAD 1200u   /* INITIAL_MTU 1228 - 12 common header - 16 DATA chunk header */
+typedef struct {
+    uint32_t tsn; uint16_t stream_id; uint16_t ssn; uint32_t ppid;
+    uint8_t flags;      /* bit0 E(nd), bit1 B(egin), bit2 U(nordered), bit3 I(mmediate) */
+    uint8_t status; uint8_t pad[2];
+} orc_sctp_chunk;
+uint32_t orc_crc32c(const uint8_t* p, size_t len);
+uint64_t orc_sctp_fragments(uint64_t msg_len);                 /* max(1, ceil(len / 1200)) */
+uint64_t orc_sctp_packets_bytes(uint64_t msg_len);             /* total bytes of the message's packets */
+/* message -> packets (one DATA chunk per packet, fragments of <= 1200 bytes, B/E flags, consecutive TSNs).
+ * If dtls_hdr != 0 every packet is preceded by a 13-byte DTLS record header (type 23, fe fd, epoch,
+ * seq48_first + fragment index, length = packet length).  Returns bytes written. */
+uint64_t orc_sctp_packetize(const uint8_t* msg, uint64_t len, uint16_t src_port, uint16_t dst_port, uint32_t vtag,
+                            uint16_t sid, uint16_t ssn, uint32_t ppid, uint32_t tsn0,
+                            int dtls_hdr, uint16_t epoch, uint64_t seq48_first, uint8_t* out);
+/* one packet (after `headroom` bytes) -> chunk info + payload slice; status OK / BAD_CHECKSUM / MALFORMED */
+int orc_sctp_unpack(const uint8_t* pkt, uint64_t len, uint32_t headroom, orc_sctp_chunk* info,
+                    uint64_t* pay_off, uint32_t* pay_len);
 
 #ifdef __cplusplus
 }

@@ -15,6 +15,10 @@ LIB_NAME = "libp2ptunnel_b200.so"
 # whole-call return codes / per-item status bytes (include/p2pt.h)
 OK, ERR_ARG, ERR_CUDA, ERR_CAPACITY, ERR_STATE = 0, -1, -2, -3, -4
 ST_OK, ST_TOO_SHORT, ST_UNKNOWN_TYPE, ST_AUTH_FAIL, ST_NO_ROOM_FOR_NONCE, ST_PASS_THROUGH, ST_BAD_HEADER = range(7)
+ST_SCTP_BAD_CHECKSUM, ST_SCTP_MALFORMED, ST_SCTP_INCOMPLETE = 7, 8, 9
+SCTP_CHUNK_DTYPE = np.dtype([("tsn", "<u4"), ("stream_id", "<u2"), ("ssn", "<u2"), ("ppid", "<u4"),
+                             ("flags", "u1"), ("status", "u1"), ("pad", "u1", (2,))])
+assert SCTP_CHUNK_DTYPE.itemsize == 16
 
 DESC_DTYPE = np.dtype([("pay_off", "<u8"), ("pay_len", "<u4"), ("stream_id", "<u4"),
                        ("msg_type", "u1"), ("status", "u1"), ("pad", "u1", (6,))])
@@ -40,6 +44,14 @@ SIGNATURES = {
     "p2pt_pipeline_seal": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_pipeline_open": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_pipeline_open_demux": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
+    "p2pt_sctp_fragments": (_u64, [_u64]),
+    "p2pt_sctp_packets_bytes": (_u64, [_u64]),
+    "p2pt_sctp_packetize_batch": (_i32, [_vp, _u64] + [_vp] * 11 + [_vp, _u64, _vp, _u64, _vp]),
+    "p2pt_sctp_unpack_reassemble_batch": (_i32, [_vp, _u64, _vp, _vp, _u32, _vp, _vp, _u32, _vp, _u64, _vp, _vp, _vp, _vp]),
+    "p2pt_sctp_packetize_batch_device": (_i32, [_vp, _u64] + [_vp] * 11 + [_vp, _vp, _vp, _vp, _vp]),
+    "p2pt_sctp_unpack_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u32, _vp, _vp, _vp]),
+    "p2pt_sctp_reassemble_scratch_bytes": (_u64, [_u64]),
+    "p2pt_sctp_reassemble_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _u32, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_frame_encode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_frame_decode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp]),
     "p2pt_frame_demux_scratch_bytes": (_u64, [_u64]),
@@ -298,3 +310,49 @@ class Context:
         return {"k": kk, "desc": desc, "out": out, "uniq_sid": uniq[:kk].copy(), "uniq_session": usess[:kk].copy(),
                 "csr": csr[:kk + 1].copy(), "perm": perm[:m].copy(), "gathered_off": goff[:kk + 1].copy(),
                 "gathered": gathered[:int(goff[kk])].copy()}
+
+    # ---- SCTP DATA chunks + CRC32c (host buffers) ------------------------------------------------------------
+    def sctp_packetize(self, msg, msg_off, src_port, dst_port, vtag, sid, ssn, ppid, tsn0, epoch=None, seq48_first=None):
+        """messages -> packets.  Returns (out bytes, pkt_off[n_pkts + 1]); with epoch/seq48_first every
+        packet carries a 13-byte DTLS record header in front (ready for dtls_seal)."""
+        msg = _as(msg, np.uint8); msg_off = _as(msg_off, np.uint64)
+        n = len(msg_off) - 1
+        a16 = lambda x: _as(np.broadcast_to(np.asarray(x), (n,)), np.uint16)
+        a32 = lambda x: _as(np.broadcast_to(np.asarray(x), (n,)), np.uint32)
+        src_port, dst_port, sid, ssn = a16(src_port), a16(dst_port), a16(sid), a16(ssn)
+        vtag, ppid, tsn0 = a32(vtag), a32(ppid), a32(tsn0)
+        lens = (msg_off[1:] - msg_off[:-1]).astype(np.int64)
+        frags = np.maximum(1, (lens + 1199) // 1200)
+        hdr = 0 if epoch is None else 13
+        last = lens - (frags - 1) * 1200
+        cap = int(((frags - 1) * 1228 + 28 + ((last + 3) & ~3) + hdr * frags).sum())
+        npk = int(frags.sum())
+        out = np.zeros(max(cap, 1), np.uint8)
+        pkt_off = np.zeros(npk + 1, np.uint64)
+        got = _u64(0)
+        ep = None if epoch is None else a16(epoch)
+        sq = None if epoch is None else _as(np.broadcast_to(np.asarray(seq48_first), (n,)), np.uint64)
+        self._check(self.lib.p2pt_sctp_packetize_batch(
+            self.h, n, msg.ctypes.data, msg_off.ctypes.data, src_port.ctypes.data, dst_port.ctypes.data, vtag.ctypes.data,
+            sid.ctypes.data, ssn.ctypes.data, ppid.ctypes.data, tsn0.ctypes.data, _ptr(ep), _ptr(sq),
+            out.ctypes.data, cap, pkt_off.ctypes.data, npk + 1, C.addressof(got)))
+        assert got.value == npk
+        return out[:cap], pkt_off
+
+    def sctp_unpack_reassemble(self, buf, in_off, headroom=0, session=None, max_msgs=None, msg_cap=None):
+        buf = _as(buf, np.uint8); in_off = _as(in_off, np.uint64)
+        n = len(in_off) - 1
+        if session is not None:
+            session = _as(session, np.uint32)
+        max_msgs = max(n, 1) if max_msgs is None else max_msgs
+        msg_cap = max(int(buf.size), 1) if msg_cap is None else msg_cap
+        info = np.zeros(n, SCTP_CHUNK_DTYPE)
+        msg = np.zeros(msg_cap, np.uint8); msg_off = np.zeros(max_msgs + 1, np.uint64)
+        first = np.zeros(max_msgs + 1, np.uint32); status = np.zeros(max_msgs + 1, np.uint8)
+        nm = _u32(0)
+        self._check(self.lib.p2pt_sctp_unpack_reassemble_batch(
+            self.h, n, buf.ctypes.data, in_off.ctypes.data, headroom, _ptr(session), info.ctypes.data, max_msgs,
+            msg.ctypes.data, msg_cap, msg_off.ctypes.data, first.ctypes.data, status.ctypes.data, C.addressof(nm)))
+        m = nm.value
+        return {"info": info, "n_msgs": m, "msg_off": msg_off[:m + 1].copy(), "msg": msg[:int(msg_off[m])].copy(),
+                "msg_first": first[:m].copy(), "msg_status": status[:m].copy()}

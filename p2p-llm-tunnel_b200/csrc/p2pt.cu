@@ -17,6 +17,7 @@
 #include "../../include/p2pt.h"
 #include "frame_kernels.cuh"
 #include "gcm_kernels.cuh"
+#include "sctp_kernels.cuh"
 
 using namespace p2pt;
 
@@ -104,6 +105,19 @@ static void build_te0(uint32_t te0[256]) {
         uint8_t s2 = gf8_mul_h(s, 2), s3 = (uint8_t)(s2 ^ s);
         te0[x] = (uint32_t)s2 | ((uint32_t)s << 8) | ((uint32_t)s << 16) | ((uint32_t)s3 << 24);
     }
+}
+
+// CRC32c slice-by-4 tables and x^(8k) mod P, from the polynomial (RFC 3720 12.1), reflected form
+static void build_crc_tables(uint32_t tab[4][256], uint32_t xpow[1280]) {
+    for (uint32_t i = 0; i < 256; i++) {
+        uint32_t c = i;
+        for (int b = 0; b < 8; b++) c = (c >> 1) ^ (0x82F63B78u & (0u - (c & 1u)));
+        tab[0][i] = c;
+    }
+    for (int k = 1; k < 4; k++)
+        for (uint32_t i = 0; i < 256; i++) tab[k][i] = (tab[k - 1][i] >> 8) ^ tab[0][tab[k - 1][i] & 0xff];
+    xpow[0] = 0x80000000u;                                   // the polynomial "1"
+    for (int k = 1; k < 1280; k++) xpow[k] = (xpow[k - 1] >> 8) ^ tab[0][xpow[k - 1] & 0xff];
 }
 
 __global__ void smem_base_probe_kernel(uint32_t* out) {
@@ -227,6 +241,12 @@ int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
     uint32_t te0[256];
     build_te0(te0);
     CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_te0, te0, sizeof te0));
+    {
+        static uint32_t ctab[4][256], cxp[1280];
+        build_crc_tables(ctab, cxp);
+        CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_tab, ctab, sizeof ctab));
+        CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_xpow, cxp, sizeof cxp));
+    }
     // where does dynamic shared memory start?  The T-tables must sit on a 64 KiB boundary.
     uint32_t* d_probe = nullptr;
     CUDA_TRY(nullptr, cudaMalloc(&d_probe, 4));
@@ -405,6 +425,116 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
                                                                     gathered_cap, k_out, max_streams);
         count_launch(ctx);
     }
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// SCTP DATA chunks + CRC32c
+// ---------------------------------------------------------------------------------------------------
+uint64_t p2pt_sctp_fragments(uint64_t msg_len) {
+    const uint64_t k = (msg_len + kSctpMaxPayload - 1) / kSctpMaxPayload;
+    return k ? k : 1;
+}
+uint64_t p2pt_sctp_packets_bytes(uint64_t msg_len) {
+    const uint64_t k = p2pt_sctp_fragments(msg_len), last = msg_len - (k - 1) * kSctpMaxPayload;
+    return (k - 1) * (uint64_t)kSctpMaxPacket + 28 + ((last + 3) & ~(uint64_t)3);
+}
+
+int32_t p2pt_sctp_packetize_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg, const uint64_t* msg_off,
+                                         const uint16_t* src_port, const uint16_t* dst_port, const uint32_t* vtag,
+                                         const uint16_t* sid, const uint16_t* ssn, const uint32_t* ppid, const uint32_t* tsn0,
+                                         const uint16_t* epoch, const uint64_t* seq48_first,
+                                         uint8_t* out, const uint64_t* out_msg_off, const uint64_t* pkt_first,
+                                         uint64_t* pkt_off, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!msg_off || !src_port || !dst_port || !vtag || !sid || !ssn || !ppid || !tsn0 || !out || !out_msg_off || !pkt_first || !pkt_off)
+        return set_err(ctx, P2PT_ERR_ARG, "sctp_packetize: null argument");
+    if ((epoch == nullptr) != (seq48_first == nullptr))
+        return set_err(ctx, P2PT_ERR_ARG, "sctp_packetize: epoch and seq48_first go together");
+    DeviceGuard dg(ctx->device);
+    SctpPacketizeArgs a;
+    a.n = n; a.msg = msg; a.msg_off = (const u64*)msg_off; a.src_port = src_port; a.dst_port = dst_port; a.vtag = vtag;
+    a.sid = sid; a.ssn = ssn; a.ppid = ppid; a.tsn0 = tsn0; a.epoch = epoch; a.seq48_first = (const u64*)seq48_first;
+    a.out = out; a.out_msg_off = (const u64*)out_msg_off; a.pkt_first = (const u64*)pkt_first; a.pkt_off = (u64*)pkt_off;
+    sctp_packetize_kernel<<<grid_for(ctx, n, kSctpWarps, 8), 32 * kSctpWarps, 0, (cudaStream_t)stream>>>(a);
+    count_launch(ctx);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+int32_t p2pt_sctp_unpack_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const uint8_t* in, const uint64_t* in_off,
+                                      uint32_t headroom, p2pt_sctp_chunk* info, p2pt_desc* desc, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n_pkts == 0) return P2PT_OK;
+    if (!in || !in_off || !info || !desc) return set_err(ctx, P2PT_ERR_ARG, "sctp_unpack: null argument");
+    DeviceGuard dg(ctx->device);
+    SctpUnpackArgs a;
+    a.n = n_pkts; a.in = in; a.in_off = (const u64*)in_off; a.headroom = headroom; a.info = info; a.desc = desc;
+    sctp_unpack_kernel<<<grid_for(ctx, n_pkts, kSctpWarps, 8), 32 * kSctpWarps, 0, (cudaStream_t)stream>>>(a);
+    count_launch(ctx);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+namespace {
+struct ReasmScratch {
+    uint8_t* demux; uint64_t demux_bytes;
+    uint32_t* uniq_tsn; uint32_t* uniq_sess; uint64_t* csr; uint64_t* goff; uint32_t* perm; uint32_t* k; uint32_t* blk;
+    uint64_t total;
+};
+ReasmScratch reasm_carve(void* base, uint64_t n) {
+    ReasmScratch r;
+    uint8_t* p = (uint8_t*)base;
+    const uint64_t nn = n ? n : 1;
+    r.demux = p; r.demux_bytes = demux_scratch_bytes(nn); p += align256(r.demux_bytes);
+    r.uniq_tsn = (uint32_t*)p; p += align256(4 * (nn + 1));
+    r.uniq_sess = (uint32_t*)p; p += align256(4 * (nn + 1));
+    r.csr = (uint64_t*)p; p += align256(8 * (nn + 1));
+    r.goff = (uint64_t*)p; p += align256(8 * (nn + 1));
+    r.perm = (uint32_t*)p; p += align256(4 * nn);
+    r.k = (uint32_t*)p; p += 256;
+    r.blk = (uint32_t*)p; p += align256(4 * (demux_scan_blocks(nn) + 2));
+    r.total = (uint64_t)(p - (uint8_t*)base);
+    return r;
+}
+}  // namespace
+
+uint64_t p2pt_sctp_reassemble_scratch_bytes(uint64_t n_pkts) { return reasm_carve(nullptr, n_pkts).total; }
+
+int32_t p2pt_sctp_reassemble_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const p2pt_sctp_chunk* info,
+                                          const p2pt_desc* desc, const uint32_t* session, const uint8_t* in,
+                                          uint32_t max_msgs, uint8_t* msg, uint64_t msg_cap, uint64_t* msg_off,
+                                          uint32_t* msg_first, uint8_t* msg_status, uint32_t* n_msgs_out,
+                                          void* scratch, uint64_t scratch_bytes, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!msg_off || !msg_first || !msg_status || !n_msgs_out) return set_err(ctx, P2PT_ERR_ARG, "sctp_reassemble: null output");
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_pkts == 0) {
+        CUDA_TRY(ctx, cudaMemsetAsync(n_msgs_out, 0, 4, st));
+        CUDA_TRY(ctx, cudaMemsetAsync(msg_off, 0, 8, st));
+        return P2PT_OK;
+    }
+    if (!info || !desc || !in || !msg || !scratch) return set_err(ctx, P2PT_ERR_ARG, "sctp_reassemble: null argument");
+    if (n_pkts > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "sctp_reassemble: n must fit in 32 bits");
+    if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "sctp_reassemble: scratch must be 256-byte aligned");
+    ReasmScratch r = reasm_carve(scratch, n_pkts);
+    if (scratch_bytes < r.total) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_reassemble: scratch too small");
+    // order the fragments by (session, TSN) and lay their payloads out back to back: the demux does
+    // exactly that with key = desc.stream_id (= TSN, set by the unpack kernel)
+    if (int32_t rc = p2pt_frame_demux_batch_device(ctx, n_pkts, desc, session, in, (uint32_t)n_pkts, r.uniq_tsn,
+                                                   session ? r.uniq_sess : nullptr, r.csr, r.perm, r.k, msg, msg_cap,
+                                                   r.goff, r.demux, r.demux_bytes, st)) return rc;
+    CUDA_TRY(ctx, cudaMemsetAsync(msg_status, 0, max_msgs, st));
+    const u64 nblk = demux_scan_blocks(n_pkts);
+    sctp_bounds_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(r.k, r.perm, (const u64*)r.csr, info, r.blk);
+    sctp_bounds_scan_kernel<<<1, kScanThreads, 0, st>>>(nblk, r.blk);
+    sctp_bounds_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(nblk, r.k, r.perm, (const u64*)r.csr, (const u64*)r.goff,
+                                                                   session ? r.uniq_sess : nullptr, info, r.blk, max_msgs,
+                                                                   (u64*)msg_off, msg_first, msg_status, n_msgs_out);
+    count_launch(ctx, 3);
     CUDA_TRY(ctx, cudaGetLastError());
     return P2PT_OK;
 }
@@ -827,6 +957,114 @@ int32_t p2pt_pipeline_open(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
     c.mode = kPipeOpen; c.n = n; c.session = session; c.in = rec; c.in_off = rec_off;
     c.out = out; c.out_off = out_off; c.desc = desc;
     return run_record_call(ctx, c, "pipeline_open");
+}
+
+int32_t p2pt_sctp_packetize_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg, const uint64_t* msg_off,
+                                  const uint16_t* src_port, const uint16_t* dst_port, const uint32_t* vtag,
+                                  const uint16_t* sid, const uint16_t* ssn, const uint32_t* ppid, const uint32_t* tsn0,
+                                  const uint16_t* epoch, const uint64_t* seq48_first,
+                                  uint8_t* out, uint64_t out_cap, uint64_t* pkt_off, uint64_t pkt_cap,
+                                  uint64_t* n_pkts_out) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!n_pkts_out || !pkt_off) return set_err(ctx, P2PT_ERR_ARG, "sctp_packetize: null output");
+    if (n == 0) { *n_pkts_out = 0; if (pkt_cap) pkt_off[0] = 0; return P2PT_OK; }
+    if (!msg_off || !src_port || !dst_port || !vtag || !sid || !ssn || !ppid || !tsn0 || !out)
+        return set_err(ctx, P2PT_ERR_ARG, "sctp_packetize: null argument");
+    if ((epoch == nullptr) != (seq48_first == nullptr)) return set_err(ctx, P2PT_ERR_ARG, "sctp_packetize: epoch and seq48_first go together");
+    if (!offsets_monotonic(msg_off, n)) return set_err(ctx, P2PT_ERR_ARG, "sctp_packetize: offsets must be non-decreasing");
+    const uint64_t hdr = epoch ? 13 : 0;
+    std::vector<uint64_t> first(n + 1), moff(n);
+    uint64_t pk = 0, bytes = 0;
+    for (uint64_t i = 0; i < n; i++) {
+        const uint64_t len = msg_off[i + 1] - msg_off[i], k = p2pt_sctp_fragments(len);
+        first[i] = pk; moff[i] = bytes;
+        pk += k; bytes += p2pt_sctp_packets_bytes(len) + hdr * k;
+    }
+    first[n] = pk;
+    *n_pkts_out = pk;
+    if (bytes > out_cap || pk + 1 > pkt_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_packetize: out_cap or pkt_cap too small");
+    const size_t mbytes = msg_off[n] - msg_off[0];
+    if (mbytes && !msg) return set_err(ctx, P2PT_ERR_ARG, "sctp_packetize: null msg");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = ctx->streams[0];
+    if (int32_t r = arena_reserve(ctx, pad256(mbytes) + 3 * pad256(8 * (n + 1)) + 4 * pad256(4 * n) + 4 * pad256(2 * n) +
+                                           pad256(8 * n) + pad256(bytes) + pad256(8 * (pk + 1)) + 16384)) return r;
+    uint8_t* d_msg = arena_take<uint8_t>(ctx, mbytes + 1);
+    uint64_t* d_moff = arena_take<uint64_t>(ctx, n + 1);
+    uint64_t* d_first = arena_take<uint64_t>(ctx, n + 1);
+    uint64_t* d_omoff = arena_take<uint64_t>(ctx, n + 1);
+    uint16_t* d_sp = arena_take<uint16_t>(ctx, n); uint16_t* d_dp = arena_take<uint16_t>(ctx, n);
+    uint16_t* d_sid = arena_take<uint16_t>(ctx, n); uint16_t* d_ssn = arena_take<uint16_t>(ctx, n);
+    uint32_t* d_vt = arena_take<uint32_t>(ctx, n); uint32_t* d_pp = arena_take<uint32_t>(ctx, n); uint32_t* d_tsn = arena_take<uint32_t>(ctx, n);
+    uint16_t* d_ep = arena_take<uint16_t>(ctx, n); uint64_t* d_sq = arena_take<uint64_t>(ctx, n);
+    uint8_t* d_out = arena_take<uint8_t>(ctx, bytes + 1);
+    uint64_t* d_poff = arena_take<uint64_t>(ctx, pk + 1);
+#define P2PT_UP(dst, src, cnt) CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, (cnt), cudaMemcpyHostToDevice, st))
+    if (mbytes) P2PT_UP(d_msg, msg + msg_off[0], mbytes);
+    P2PT_UP(d_moff, msg_off, 8 * (n + 1)); P2PT_UP(d_first, first.data(), 8 * (n + 1)); P2PT_UP(d_omoff, moff.data(), 8 * n);
+    P2PT_UP(d_sp, src_port, 2 * n); P2PT_UP(d_dp, dst_port, 2 * n); P2PT_UP(d_sid, sid, 2 * n); P2PT_UP(d_ssn, ssn, 2 * n);
+    P2PT_UP(d_vt, vtag, 4 * n); P2PT_UP(d_pp, ppid, 4 * n); P2PT_UP(d_tsn, tsn0, 4 * n);
+    if (epoch) { P2PT_UP(d_ep, epoch, 2 * n); P2PT_UP(d_sq, seq48_first, 8 * n); }
+#undef P2PT_UP
+    if (int32_t r = p2pt_sctp_packetize_batch_device(ctx, n, d_msg - msg_off[0], d_moff, d_sp, d_dp, d_vt, d_sid, d_ssn, d_pp, d_tsn,
+                                                     epoch ? d_ep : nullptr, epoch ? d_sq : nullptr, d_out, d_omoff, d_first, d_poff, st)) return r;
+    CUDA_TRY(ctx, cudaMemcpyAsync(out, d_out, bytes, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(pkt_off, d_poff, 8 * (pk + 1), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return P2PT_OK;
+}
+
+int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const uint8_t* in, const uint64_t* in_off,
+                                          uint32_t headroom, const uint32_t* session, p2pt_sctp_chunk* info,
+                                          uint32_t max_msgs, uint8_t* msg, uint64_t msg_cap, uint64_t* msg_off,
+                                          uint32_t* msg_first, uint8_t* msg_status, uint32_t* n_msgs_out) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!msg_off || !msg_first || !msg_status || !n_msgs_out || !info) return set_err(ctx, P2PT_ERR_ARG, "sctp_unpack_reassemble: null output");
+    if (n_pkts == 0) { *n_msgs_out = 0; msg_off[0] = 0; return P2PT_OK; }
+    if (!in || !in_off || !msg) return set_err(ctx, P2PT_ERR_ARG, "sctp_unpack_reassemble: null argument");
+    if (!offsets_monotonic(in_off, n_pkts)) return set_err(ctx, P2PT_ERR_ARG, "sctp_unpack_reassemble: offsets must be non-decreasing");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = ctx->streams[0];
+    const uint64_t n = n_pkts;
+    const size_t ibytes = in_off[n] - in_off[0];
+    const uint64_t sbytes = p2pt_sctp_reassemble_scratch_bytes(n);
+    if (int32_t r = arena_reserve(ctx, pad256(ibytes) + pad256(8 * (n + 1)) + pad256(4 * n) + pad256(16 * n) + pad256(24 * n) +
+                                           pad256(msg_cap) + pad256(8 * ((size_t)max_msgs + 1)) + pad256(4 * (size_t)max_msgs) +
+                                           pad256(max_msgs) + 256 + pad256(sbytes) + 16384)) return r;
+    uint8_t* d_in = arena_take<uint8_t>(ctx, ibytes + 1);
+    uint64_t* d_ioff = arena_take<uint64_t>(ctx, n + 1);
+    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
+    p2pt_sctp_chunk* d_info = arena_take<p2pt_sctp_chunk>(ctx, n);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
+    uint8_t* d_msg = arena_take<uint8_t>(ctx, msg_cap + 1);
+    uint64_t* d_moff = arena_take<uint64_t>(ctx, (size_t)max_msgs + 1);
+    uint32_t* d_mfirst = arena_take<uint32_t>(ctx, (size_t)max_msgs + 1);
+    uint8_t* d_mstat = arena_take<uint8_t>(ctx, (size_t)max_msgs + 1);
+    uint32_t* d_nm = arena_take<uint32_t>(ctx, 1);
+    uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in + in_off[0], ibytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_ioff, in_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
+    if (session) CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_sctp_unpack_batch_device(ctx, n, d_in - in_off[0], d_ioff, headroom, d_info, d_desc, st)) return r;
+    if (int32_t r = p2pt_sctp_reassemble_batch_device(ctx, n, d_info, d_desc, session ? d_sess : nullptr, d_in - in_off[0],
+                                                      max_msgs, d_msg, msg_cap, d_moff, d_mfirst, d_mstat, d_nm,
+                                                      d_scratch, sbytes, st)) return r;
+    uint32_t nm = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(info, d_info, 16 * n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    *n_msgs_out = nm;
+    if (nm > max_msgs) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_unpack_reassemble: more messages than max_msgs");
+    CUDA_TRY(ctx, cudaMemcpyAsync(msg_off, d_moff, 8 * ((size_t)nm + 1), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(msg_first, d_mfirst, 4 * (size_t)nm, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(msg_status, d_mstat, nm, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    if (msg_off[nm] > msg_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_unpack_reassemble: msg_cap too small");
+    if (msg_off[nm]) CUDA_TRY(ctx, cudaMemcpyAsync(msg, d_msg, msg_off[nm], cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return P2PT_OK;
 }
 
 int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,

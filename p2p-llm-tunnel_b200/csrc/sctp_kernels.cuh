@@ -1,0 +1,298 @@
+// sctp_kernels.cuh -- SCTP DATA-chunk packetise / unpack with CRC32c, and message reassembly, for
+// sm_100a.  This is the step that sits between the tunnel frame and the DTLS record in the
+// reference's stack: webrtc-data hands the frame to webrtc-sctp 0.10.0
+// (UN-VENDORED, /root/reference/tunnel/Cargo.lock:2910-2911), which cuts it into DATA chunks of at
+// most 1200 bytes, one per packet here, and checksums every packet with CRC32c (crc 3.4.0,
+// Cargo.lock:420-421).  Layout: RFC 4960 3.1 / 3.3.1 / appendix B.
+//
+// HBM-bound byte work again.  One warp per packet: the packet is staged in shared memory, every
+// lane runs a slice-by-4 table CRC over its own contiguous segment, the 32 partial remainders are
+// shifted to their place with a carry-less multiply by x^(8 * bytes after the segment) mod P and
+// XOR-reduced by shuffles, then the packet goes out as aligned words.
+#pragma once
+#include "common.cuh"
+#include "gcm_math.cuh"
+#include "frame_kernels.cuh"
+#include "../../include/p2pt.h"
+
+namespace p2pt {
+
+constexpr uint32_t kSctpMaxPayload = P2PT_SCTP_MAX_PAYLOAD;          // 1200
+constexpr uint32_t kSctpMaxPacket = 28 + kSctpMaxPayload;            // 1228
+constexpr int kSctpWarps = 8;                                        // warps (packets in flight) per block
+constexpr uint32_t kSctpBufBytes = 1280;                             // per-warp staging buffer
+constexpr uint32_t kSctpPktAt = 20;                                  // packet byte 0 sits at buffer byte 20 ->
+                                                                     // payload (packet byte 28) at 48, 16-aligned;
+                                                                     // an optional DTLS header occupies 7..19
+
+// slice-by-4 tables and x^(8k) mod P for k = 0..1279, reflected representation; filled by the host
+__device__ uint32_t g_crc_tab[4][256];
+__device__ uint32_t g_crc_xpow[1280];
+
+struct CrcSmem {
+    uint32_t tab[4][256];
+};
+
+__device__ __forceinline__ uint32_t crc_word(const CrcSmem& t, uint32_t crc, uint32_t w) {
+    const uint32_t x = crc ^ w;
+    return t.tab[3][x & 0xff] ^ t.tab[2][(x >> 8) & 0xff] ^ t.tab[1][(x >> 16) & 0xff] ^ t.tab[0][x >> 24];
+}
+
+// (a * b) mod P for reflected 32-bit residues: carry-less product (integer-multiply-with-holes,
+// gcm_math.cuh), realigned by one bit, then the upper 32 coefficients are folded with one table step.
+__device__ __forceinline__ uint32_t crc_mulmod(const CrcSmem& t, uint32_t a, uint32_t b) {
+    uint32_t bm[4] = {b & 0x11111111u, b & 0x22222222u, b & 0x44444444u, b & 0x88888888u};
+    const uint64_t p = clmul32(a, bm) << 1;
+    return crc_word(t, 0u, (uint32_t)p) ^ (uint32_t)(p >> 32);
+}
+
+// CRC32c of the staged packet (nwords 32-bit words at `words`, word 2 = checksum field counted as 0).
+// All 32 lanes call; every lane gets the result.
+__device__ __forceinline__ uint32_t warp_crc32c(const CrcSmem& t, const uint32_t* words, uint32_t nwords, int lane) {
+    const uint32_t segw = (nwords + 31) >> 5;
+    const uint32_t w0 = (uint32_t)lane * segw;
+    uint32_t w1 = w0 + segw;
+    if (w1 > nwords) w1 = nwords;
+    uint32_t c = 0;
+    for (uint32_t w = w0; w < w1; w++) {
+        uint32_t v = words[w];
+        if (w == 2) v = 0;
+        if (w == 0) v ^= 0xffffffffu;                   // the init value, folded into the first four bytes
+        c = crc_word(t, c, v);
+    }
+    uint32_t part = 0;
+    if (w0 < nwords) part = crc_mulmod(t, c, g_crc_xpow[(nwords - w1) * 4]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part ^= __shfl_xor_sync(0xffffffffu, part, o);
+    return ~part;
+}
+
+// smem byte stream [start, start + nbytes) of a 4-byte aligned buffer -> dst (any alignment):
+// aligned 32-bit stores built from two adjacent shared words, byte stores only at the two ends.
+__device__ __forceinline__ void smem_stream_to_global(const uint8_t* sbuf, uint32_t start, uint32_t nbytes,
+                                                      uint8_t* dst, int lane) {
+    uint32_t head = (uint32_t)((4 - ((uintptr_t)dst & 3)) & 3);
+    if (head > nbytes) head = nbytes;
+    if ((uint32_t)lane < head) dst[lane] = sbuf[start + lane];
+    const uint32_t body = nbytes - head, nfull = body >> 2;
+    const uint32_t so = start + head;                    // stream offset of the first aligned destination word
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(sbuf) + (so >> 2);
+    const unsigned sh = (so & 3) * 8;
+    uint32_t* dw = reinterpret_cast<uint32_t*>(dst + head);
+    for (uint32_t j = lane; j < nfull; j += 32) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
+    for (uint32_t b = (nfull << 2) + lane; b < body; b += 32) dst[head + b] = sbuf[so + b];
+}
+
+struct SctpPacketizeArgs {
+    u64 n;                                  // messages
+    const uint8_t* msg; const u64* msg_off;
+    const uint16_t* src_port; const uint16_t* dst_port; const uint32_t* vtag;
+    const uint16_t* sid; const uint16_t* ssn; const uint32_t* ppid; const uint32_t* tsn0;
+    const uint16_t* epoch; const u64* seq48_first;        // both null: bare packets; else DTLS header in front
+    uint8_t* out; const u64* out_msg_off;                 // byte offset of each message's first packet
+    const u64* pkt_first;                                 // index of each message's first packet (n + 1)
+    u64* pkt_off;                                         // out: byte offset of every packet (+ 1 terminator)
+};
+
+__global__ void __launch_bounds__(32 * kSctpWarps) sctp_packetize_kernel(const SctpPacketizeArgs a) {
+    __shared__ CrcSmem tabs;
+    __shared__ __align__(16) uint8_t bufs[kSctpWarps][kSctpBufBytes];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) (&tabs.tab[0][0])[i] = (&g_crc_tab[0][0])[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    uint8_t* buf = bufs[wib];
+    uint32_t* bw = reinterpret_cast<uint32_t*>(buf);
+    const bool dtls = a.epoch != nullptr;
+    const uint32_t hdr = dtls ? 13u : 0u;
+    const u64 warp = (u64)blockIdx.x * kSctpWarps + wib, nwarps = (u64)gridDim.x * kSctpWarps;
+    for (u64 i = warp; i < a.n; i += nwarps) {
+        const u64 mo = __ldg(a.msg_off + i), mlen = __ldg(a.msg_off + i + 1) - mo;
+        const uint8_t* m = a.msg + mo;
+        const u64 k = mlen ? (mlen + kSctpMaxPayload - 1) / kSctpMaxPayload : 1;
+        const u64 p0 = __ldg(a.pkt_first + i);
+        u64 oo = __ldg(a.out_msg_off + i);
+        const uint32_t sp = __ldg(a.src_port + i), dp = __ldg(a.dst_port + i), vt = __ldg(a.vtag + i);
+        const uint32_t sid = __ldg(a.sid + i), ssn = __ldg(a.ssn + i), pp = __ldg(a.ppid + i), t0 = __ldg(a.tsn0 + i);
+        for (u64 f = 0; f < k; f++) {
+            const u64 off = f * kSctpMaxPayload;
+            const uint32_t fl = (uint32_t)(mlen - off < kSctpMaxPayload ? mlen - off : kSctpMaxPayload);
+            const uint32_t padded = (fl + 3) & ~3u, plen = 28 + padded;
+            __syncwarp();
+            // ---- header words (packet bytes 0..27 -> buffer words 5..11), big-endian fields
+            if (lane < 7) {
+                uint32_t be;
+                const uint32_t flags = (f == 0 ? 2u : 0u) | (f == k - 1 ? 1u : 0u);
+                switch (lane) {
+                    case 0: be = (sp << 16) | dp; break;
+                    case 1: be = vt; break;
+                    case 2: be = 0; break;                                   // checksum, patched below
+                    case 3: be = (0u << 24) | (flags << 16) | (16 + fl); break;
+                    case 4: be = t0 + (uint32_t)f; break;
+                    case 5: be = (sid << 16) | ssn; break;
+                    default: be = pp; break;
+                }
+                bw[kSctpPktAt / 4 + lane] = bswap32(be);
+            }
+            if (dtls && lane < 13) {                                         // DTLS record header in front
+                const uint32_t ep = __ldg(a.epoch + i);
+                const u64 sq = __ldg(a.seq48_first + i) + f;
+                uint32_t b;
+                switch (lane) {
+                    case 0: b = 23; break; case 1: b = 0xfe; break; case 2: b = 0xfd; break;
+                    case 3: b = ep >> 8; break; case 4: b = ep; break;
+                    case 11: b = plen >> 8; break; case 12: b = plen; break;
+                    default: b = (uint32_t)(sq >> (8 * (10 - lane))); break;  // lanes 5..10: seq bytes 5..0
+                }
+                buf[kSctpPktAt - 13 + lane] = (uint8_t)b;
+            }
+            // ---- payload, zero padded, into the 16-byte aligned part of the buffer
+            for (uint32_t v = lane; v * 16 < padded; v += 32) {
+                const uint4 x = load16_bounded(m + off + 16 * v, m + off, m + off + fl);
+                *reinterpret_cast<uint4*>(buf + kSctpPktAt + 28 + 16 * v) = x;
+            }
+            __syncwarp();
+            const uint32_t crc = warp_crc32c(tabs, bw + kSctpPktAt / 4, plen >> 2, lane);
+            if (lane == 0) bw[kSctpPktAt / 4 + 2] = crc;                     // stored little-endian (webrtc-sctp put_u32_le)
+            __syncwarp();
+            smem_stream_to_global(buf, kSctpPktAt - hdr, plen + hdr, a.out + oo, lane);
+            if (lane == 0) a.pkt_off[p0 + f] = oo;
+            oo += plen + hdr;
+        }
+        if (lane == 0 && i == a.n - 1) a.pkt_off[p0 + k] = oo;               // terminator after the last packet
+    }
+}
+
+struct SctpUnpackArgs {
+    u64 n;                                   // packets
+    const uint8_t* in; const u64* in_off; uint32_t headroom;
+    p2pt_sctp_chunk* info; p2pt_desc* desc;
+};
+
+__global__ void __launch_bounds__(32 * kSctpWarps) sctp_unpack_kernel(const SctpUnpackArgs a) {
+    __shared__ CrcSmem tabs;
+    __shared__ __align__(16) uint8_t bufs[kSctpWarps][kSctpBufBytes];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) (&tabs.tab[0][0])[i] = (&g_crc_tab[0][0])[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    uint8_t* buf = bufs[wib];
+    const uint32_t* bw = reinterpret_cast<const uint32_t*>(buf);
+    const u64 warp = (u64)blockIdx.x * kSctpWarps + wib, nwarps = (u64)gridDim.x * kSctpWarps;
+    for (u64 i = warp; i < a.n; i += nwarps) {
+        const u64 io = __ldg(a.in_off + i), ilen = __ldg(a.in_off + i + 1) - io;
+        uint32_t st = P2PT_ST_OK;
+        uint32_t flags = 0, tsn = 0, sid = 0, ssn = 0, pp = 0, plen_pay = 0;
+        if (ilen < (u64)a.headroom + 12 || ilen - a.headroom > kSctpMaxPacket || ((ilen - a.headroom) & 3)) {
+            st = P2PT_ST_SCTP_MALFORMED;                                     // not a single-DATA-chunk packet we handle
+        } else {
+            const uint32_t n = (uint32_t)(ilen - a.headroom);
+            const uint8_t* p = a.in + io + a.headroom;
+            __syncwarp();
+            for (uint32_t v = lane; v * 16 < n; v += 32)
+                *reinterpret_cast<uint4*>(buf + 16 * v) = load16_bounded(p + 16 * v, p, p + n);
+            __syncwarp();
+            const uint32_t crc = warp_crc32c(tabs, bw, n >> 2, lane);
+            if (crc != bw[2]) st = P2PT_ST_SCTP_BAD_CHECKSUM;                // checked first, like Packet::unmarshal
+            else if (n < 28 || buf[12] != 0) st = P2PT_ST_SCTP_MALFORMED;
+            else {
+                const uint32_t w3 = bswap32(bw[3]);
+                const uint32_t clen = w3 & 0xffff;
+                if (clen < 16 || 12 + ((clen + 3) & ~3u) != n) st = P2PT_ST_SCTP_MALFORMED;
+                else {
+                    flags = (w3 >> 16) & 0xff; tsn = bswap32(bw[4]);
+                    const uint32_t w5 = bswap32(bw[5]);
+                    sid = w5 >> 16; ssn = w5 & 0xffff; pp = bswap32(bw[6]); plen_pay = clen - 16;
+                }
+            }
+        }
+        if (lane == 0) {
+            p2pt_sctp_chunk c;
+            c.tsn = tsn; c.stream_id = (uint16_t)sid; c.ssn = (uint16_t)ssn; c.ppid = pp;
+            c.flags = (uint8_t)flags; c.status = (uint8_t)st; c.pad[0] = c.pad[1] = 0;
+            a.info[i] = c;
+            // a descriptor p2pt_frame_demux_batch can order: key = TSN, "body" type so the gather takes it
+            p2pt_desc d;
+            d.pay_off = io + a.headroom + 28; d.pay_len = plen_pay; d.stream_id = tsn;
+            d.msg_type = 21; d.status = (uint8_t)st;
+            for (int q = 0; q < 6; q++) d.pad[q] = 0;
+            if (st != P2PT_ST_OK) { d.pay_off = io; d.pay_len = 0; }
+            a.desc[i] = d;
+        }
+    }
+}
+
+// ---- message bounds after the fragments were ordered by (session, TSN) with the demux ---------------
+// Sorted position s starts a message iff its fragment carries the B flag.  Exclusive scan of the B
+// flags numbers the messages; a message is complete when its fragments have consecutive TSNs in one
+// session and the last one carries E.
+__global__ void __launch_bounds__(kScanThreads) sctp_bounds_blocksum_kernel(
+    const uint32_t* __restrict__ k_ptr, const uint32_t* __restrict__ perm, const u64* __restrict__ csr,
+    const p2pt_sctp_chunk* __restrict__ info, uint32_t* __restrict__ blk) {
+    const u64 k = *k_ptr, s = (u64)blockIdx.x * kScanThreads + threadIdx.x;
+    HeadBytes v; v.heads = 0; v.bytes = 0;
+    if (s < k) v.heads = (info[perm[csr[s]]].flags & 2) ? 1u : 0u;
+    HeadBytes tot;
+    (void)block_scan_excl(v, tot);
+    if (threadIdx.x == 0) blk[blockIdx.x] = tot.heads;
+}
+
+__global__ void __launch_bounds__(kScanThreads) sctp_bounds_scan_kernel(u64 nblk, uint32_t* __restrict__ blk) {
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (u64 b0 = 0; b0 < nblk; b0 += kScanThreads) {
+        const u64 b = b0 + threadIdx.x;
+        HeadBytes v; v.heads = b < nblk ? blk[b] : 0; v.bytes = 0;
+        HeadBytes tot;
+        HeadBytes ex = block_scan_excl(v, tot);
+        const uint32_t c = carry;
+        if (b < nblk) blk[b] = c + ex.heads;
+        __syncthreads();
+        if (threadIdx.x == 0) carry = c + tot.heads;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) blk[nblk] = carry;
+}
+
+__global__ void __launch_bounds__(kScanThreads) sctp_bounds_emit_kernel(
+    u64 nblk, const uint32_t* __restrict__ k_ptr, const uint32_t* __restrict__ perm, const u64* __restrict__ csr,
+    const u64* __restrict__ gathered_off, const uint32_t* __restrict__ uniq_session,
+    const p2pt_sctp_chunk* __restrict__ info, const uint32_t* __restrict__ blk, uint32_t max_msgs,
+    u64* __restrict__ msg_off, uint32_t* __restrict__ msg_first, uint8_t* __restrict__ msg_status,
+    uint32_t* __restrict__ n_msgs_out) {
+    const u64 k = *k_ptr, s = (u64)blockIdx.x * kScanThreads + threadIdx.x;
+    HeadBytes v; v.heads = 0; v.bytes = 0;
+    p2pt_sctp_chunk me; me.flags = 0; me.tsn = 0;
+    if (s < k) { me = info[perm[csr[s]]]; v.heads = (me.flags & 2) ? 1u : 0u; }
+    HeadBytes tot;
+    HeadBytes ex = block_scan_excl(v, tot);
+    const uint32_t base = blk[blockIdx.x];
+    if (s < k) {
+        const uint32_t before = base + ex.heads;                 // messages that started before me
+        if (v.heads && before < max_msgs) { msg_off[before] = gathered_off[s]; msg_first[before] = perm[csr[s]]; }
+        // which message do I belong to, and is the chain to my successor intact?
+        const uint32_t mine = v.heads ? before : before - 1;     // before == 0 and no B: orphan fragment
+        bool bad = (!v.heads && before == 0);
+        if (!(me.flags & 1)) {                                    // not the end: successor must continue the message
+            if (s + 1 >= k) bad = true;
+            else {
+                const p2pt_sctp_chunk nx = info[perm[csr[s + 1]]];
+                const bool same_sess = !uniq_session || uniq_session[s + 1] == uniq_session[s];
+                if (!same_sess || nx.tsn != me.tsn + 1 || (nx.flags & 2)) bad = true;
+            }
+        } else if (s + 1 < k) {                                   // the end: successor must begin a new message
+            if (!(info[perm[csr[s + 1]]].flags & 2)) { /* successor is an orphan; it flags itself */ }
+        }
+        if (!v.heads && before > 0) {                             // continuation: predecessor must not have ended
+            const p2pt_sctp_chunk pv = info[perm[csr[s - 1]]];
+            if (pv.flags & 1) bad = true;
+        }
+        if (bad && before + (v.heads ? 1 : 0) > 0 && mine < max_msgs) msg_status[mine] = P2PT_ST_SCTP_INCOMPLETE;
+    }
+    if (s == 0) {
+        const uint32_t nm = blk[nblk];
+        *n_msgs_out = nm;
+        if (nm <= max_msgs) msg_off[nm] = gathered_off[k];
+    }
+}
+
+}  // namespace p2pt

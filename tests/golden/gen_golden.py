@@ -124,8 +124,21 @@ def dtls():
     return {"records": recs}
 
 
+def crc32c_vectors():
+    """RFC 3720 B.4 CRC32c examples (the polynomial SCTP uses, RFC 4960 appendix B)."""
+    return {"vectors": [
+        {"name": "ascii_123456789", "data": b"123456789".hex(), "crc": "e3069283"},
+        {"name": "32_zeros", "data": "00" * 32, "crc": "8a9136aa"},
+        {"name": "32_ones", "data": "ff" * 32, "crc": "62a8ab43"},
+        {"name": "32_incrementing", "data": bytes(range(32)).hex(), "crc": "46dd794e"},
+        {"name": "32_decrementing", "data": bytes(range(31, -1, -1)).hex(), "crc": "113fdb5c"},
+        {"name": "iscsi_read10_pdu", "data": "01c00000" + "00" * 12 + "14000000" + "00000400" + "00000014" + "00000018" + "28000000" + "00000000" + "02000000" + "00000000", "crc": "d9963a56"},
+    ]}
+
+
 if __name__ == "__main__":
-    for name, fn in (("frames_kat.json", frames), ("gcm_nist_kat.json", nist), ("dtls_records_kat.json", dtls)):
+    for name, fn in (("frames_kat.json", frames), ("gcm_nist_kat.json", nist), ("dtls_records_kat.json", dtls),
+                     ("crc32c_kat.json", crc32c_vectors)):
         with open(os.path.join(HERE, name), "w") as f:
             json.dump(fn(), f, indent=1)
         print("wrote", name)

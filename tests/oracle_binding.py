@@ -123,3 +123,55 @@ def pipeline_seal(w, keys, ivs):
     rec, _, status = dtls_seal(w["session"], keys, ivs, w["nonce8"], raw, raw_off, w.get("rec_off"))
     assert (status == 0).all()
     return rec
+
+
+SCTP_CHUNK_DTYPE = np.dtype([("tsn", "<u4"), ("stream_id", "<u2"), ("ssn", "<u2"), ("ppid", "<u4"),
+                             ("flags", "u1"), ("status", "u1"), ("pad", "u1", (2,))])
+
+
+def crc32c(data):
+    lib().orc_crc32c.restype = C.c_uint32
+    return lib().orc_crc32c(bytes(data), C.c_size_t(len(data)))
+
+
+def sctp_packetize(msgs, src_port, dst_port, vtag, sid, ssn, ppid, tsn0, epoch=None, seq48_first=None):
+    """list of byte strings -> (packet bytes, pkt_off) with the oracle; scalars broadcast per message"""
+    L = lib()
+    L.orc_sctp_packetize.restype = C.c_uint64
+    L.orc_sctp_packets_bytes.restype = C.c_uint64
+    L.orc_sctp_fragments.restype = C.c_uint64
+    n = len(msgs)
+    bc = lambda x: np.broadcast_to(np.asarray(x), (n,))
+    src_port, dst_port, vtag, sid, ssn, ppid, tsn0 = map(bc, (src_port, dst_port, vtag, sid, ssn, ppid, tsn0))
+    hdr = epoch is not None
+    if hdr:
+        epoch, seq48_first = bc(epoch), bc(seq48_first)
+    chunks, offs = [], [0]
+    for i, m in enumerate(msgs):
+        k = int(L.orc_sctp_fragments(C.c_uint64(len(m))))
+        cap = int(L.orc_sctp_packets_bytes(C.c_uint64(len(m)))) + (13 * k if hdr else 0)
+        out = C.create_string_buffer(cap)
+        w = L.orc_sctp_packetize(bytes(m), C.c_uint64(len(m)), C.c_uint16(int(src_port[i])), C.c_uint16(int(dst_port[i])),
+                                 C.c_uint32(int(vtag[i])), C.c_uint16(int(sid[i])), C.c_uint16(int(ssn[i])),
+                                 C.c_uint32(int(ppid[i])), C.c_uint32(int(tsn0[i])), C.c_int(1 if hdr else 0),
+                                 C.c_uint16(int(epoch[i]) if hdr else 0), C.c_uint64(int(seq48_first[i]) if hdr else 0), out)
+        assert w == cap
+        chunks.append(out.raw)
+        # per-packet offsets: all but the last fragment are 1228 (+13) bytes
+        for f in range(k):
+            ln = len(m) - 1200 * f
+            fl = min(max(ln, 0), 1200)
+            offs.append(offs[-1] + 28 + ((fl + 3) & ~3) + (13 if hdr else 0))
+    return np.frombuffer(b"".join(chunks), np.uint8), np.array(offs, np.uint64)
+
+
+def sctp_unpack(buf, in_off, headroom=0):
+    buf = _u8(buf); in_off = np.ascontiguousarray(in_off, np.uint64)
+    n = len(in_off) - 1
+    info = np.zeros(n, SCTP_CHUNK_DTYPE); po = np.zeros(n, np.uint64); pl = np.zeros(n, np.uint32)
+    for i in range(n):
+        a, b = int(in_off[i]), int(in_off[i + 1])
+        one = np.zeros(1, SCTP_CHUNK_DTYPE); o = C.c_uint64(0); ln = C.c_uint32(0)
+        lib().orc_sctp_unpack(C.c_void_p(buf.ctypes.data + a), C.c_uint64(b - a), C.c_uint32(headroom), _p(one), C.byref(o), C.byref(ln))
+        info[i] = one[0]; po[i] = a + o.value; pl[i] = ln.value
+    return info, po, pl

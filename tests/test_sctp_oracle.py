@@ -1,0 +1,51 @@
+"""CPU: the SCTP / CRC32c part of the oracle against RFC 3720 B.4 vectors and its own structure."""
+import json
+import os
+
+import numpy as np
+
+import oracle_binding as ob
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_crc32c_rfc3720_vectors():
+    for v in json.load(open(os.path.join(G, "crc32c_kat.json")))["vectors"]:
+        assert ob.crc32c(bytes.fromhex(v["data"])) == int(v["crc"], 16), v["name"]
+
+
+def test_packet_layout_and_roundtrip():
+    msgs = [b"", b"x", bytes(range(200)) * 6, bytes(1199), bytes([7]) * 1200, bytes([9]) * 1201, os.urandom(5000), os.urandom(65413)]
+    pk, off = ob.sctp_packetize(msgs, 5000, 5001, 0xDEADBEEF, 1, np.arange(len(msgs)), 53, 1000 + 100 * np.arange(len(msgs)))
+    info, po, pl = ob.sctp_unpack(pk, off)
+    assert not info["status"].any()
+    i = 0
+    for mi, m in enumerate(msgs):
+        k = max(1, -(-len(m) // 1200))
+        got = b""
+        for f in range(k):
+            a, b = int(off[i]), int(off[i + 1])
+            p = pk[a:b].tobytes()
+            assert p[:2] == (5000).to_bytes(2, "big") and p[2:4] == (5001).to_bytes(2, "big") and p[4:8] == bytes.fromhex("deadbeef")
+            assert p[12] == 0 and (b - a) % 4 == 0
+            assert info["flags"][i] == (2 if f == 0 else 0) | (1 if f == k - 1 else 0)
+            assert info["tsn"][i] == 1000 + 100 * mi + f and info["ssn"][i] == mi and info["stream_id"][i] == 1 and info["ppid"][i] == 53
+            assert int.from_bytes(p[14:16], "big") == 16 + pl[i]
+            assert p[28 + pl[i]:] == bytes(len(p) - 28 - pl[i])                       # zero padding
+            zeroed = p[:8] + bytes(4) + p[12:]
+            assert int.from_bytes(p[8:12], "little") == ob.crc32c(zeroed)            # checksum stored little-endian
+            got += pk[int(po[i]):int(po[i]) + int(pl[i])].tobytes()
+            i += 1
+        assert got == m
+    assert i == len(off) - 1
+
+
+def test_unpack_error_statuses_and_dtls_headroom():
+    pk, off = ob.sctp_packetize([b"hello sctp"], 1, 2, 3, 4, 5, 53, 77, epoch=1, seq48_first=9)
+    assert pk[0] == 23 and pk[1] == 0xFE and pk[2] == 0xFD and int.from_bytes(pk[5:11].tobytes(), "big") == 9
+    assert int.from_bytes(pk[11:13].tobytes(), "big") == len(pk) - 13
+    info, po, pl = ob.sctp_unpack(pk, off, headroom=13)
+    assert info["status"][0] == 0 and pk[int(po[0]):int(po[0]) + int(pl[0])].tobytes() == b"hello sctp"
+    bad = pk.copy(); bad[13 + 30] ^= 1
+    assert ob.sctp_unpack(bad, off, headroom=13)[0]["status"][0] == 7
+    assert ob.sctp_unpack(pk[:20], np.array([0, 20], np.uint64), headroom=13)[0]["status"][0] == 8
