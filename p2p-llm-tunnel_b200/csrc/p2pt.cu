@@ -458,7 +458,13 @@ int32_t p2pt_sctp_packetize_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_
     a.n = n; a.msg = msg; a.msg_off = (const u64*)msg_off; a.src_port = src_port; a.dst_port = dst_port; a.vtag = vtag;
     a.sid = sid; a.ssn = ssn; a.ppid = ppid; a.tsn0 = tsn0; a.epoch = epoch; a.seq48_first = (const u64*)seq48_first;
     a.out = out; a.out_msg_off = (const u64*)out_msg_off; a.pkt_first = (const u64*)pkt_first; a.pkt_off = (u64*)pkt_off;
-    sctp_packetize_kernel<<<grid_for(ctx, n, kSctpWarps, 8), 32 * kSctpWarps, 0, (cudaStream_t)stream>>>(a);
+    const uint32_t smem = sctp_smem_bytes(ctx->lut_slack);
+    static std::atomic<int> configured[16];
+    if (!configured[ctx->device & 15].load()) {
+        CUDA_TRY(ctx, cudaFuncSetAttribute(sctp_packetize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[ctx->device & 15].store(1);
+    }
+    sctp_packetize_kernel<<<grid_for(ctx, n, kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
     return P2PT_OK;
@@ -472,7 +478,13 @@ int32_t p2pt_sctp_unpack_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const uint
     DeviceGuard dg(ctx->device);
     SctpUnpackArgs a;
     a.n = n_pkts; a.in = in; a.in_off = (const u64*)in_off; a.headroom = headroom; a.info = info; a.desc = desc;
-    sctp_unpack_kernel<<<grid_for(ctx, n_pkts, kSctpWarps, 8), 32 * kSctpWarps, 0, (cudaStream_t)stream>>>(a);
+    const uint32_t smem = sctp_smem_bytes(ctx->lut_slack);
+    static std::atomic<int> configured[16];
+    if (!configured[ctx->device & 15].load()) {
+        CUDA_TRY(ctx, cudaFuncSetAttribute(sctp_unpack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[ctx->device & 15].store(1);
+    }
+    sctp_unpack_kernel<<<grid_for(ctx, n_pkts, kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
     return P2PT_OK;

@@ -19,52 +19,104 @@ namespace p2pt {
 
 constexpr uint32_t kSctpMaxPayload = P2PT_SCTP_MAX_PAYLOAD;          // 1200
 constexpr uint32_t kSctpMaxPacket = 28 + kSctpMaxPayload;            // 1228
-constexpr int kSctpWarps = 8;                                        // warps (packets in flight) per block
+constexpr int kSctpWarps = 32;                                       // warps (packets in flight) per block, 1 block per SM
 constexpr uint32_t kSctpBufBytes = 1280;                             // per-warp staging buffer
 constexpr uint32_t kSctpPktAt = 20;                                  // packet byte 0 sits at buffer byte 20 ->
                                                                      // payload (packet byte 28) at 48, 16-aligned;
                                                                      // an optional DTLS header occupies 7..19
+constexpr uint32_t kCrcLutBytes = 65536;                             // 256 rows x (T0 | T1) x 32 replicas x 4 B
+constexpr uint32_t kSctpStageBytes = kSctpWarps * kSctpBufBytes;
 
 // slice-by-4 tables and x^(8k) mod P for k = 0..1279, reflected representation; filled by the host
 __device__ uint32_t g_crc_tab[4][256];
 __device__ uint32_t g_crc_xpow[1280];
 
-struct CrcSmem {
-    uint32_t tab[4][256];
+// Shared-memory map, like the record kernel's: the CRC tables sit on a 64 KiB boundary of the shared
+// window so that one PRMT builds a lookup address (byte << 8 | lane << 2 | base); every table entry is
+// replicated 32x, lane l only touches bank l, so data-dependent lookups never conflict.  The staging
+// buffers live in the gap below the tables when it is large enough, else behind them.
+__host__ __device__ constexpr uint32_t sctp_smem_bytes(uint32_t slack) {
+    return slack + kCrcLutBytes + (slack >= kSctpStageBytes ? 0u : kSctpStageBytes);
+}
+
+struct CrcLut {
+    uint32_t lb;     // 64 KiB-aligned shared address of the tables + 4 * lane
+    template <int K, int T> __device__ __forceinline__ uint32_t look(uint32_t w) const {
+        const uint32_t idx = __byte_perm(w, lb, 0x7604 | (K << 4));
+        uint32_t v;
+        if (T == 0) asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(idx));
+        else        asm("ld.shared.u32 %0, [%1+128];" : "=r"(v) : "r"(idx));
+        return v;
+    }
 };
 
-__device__ __forceinline__ uint32_t crc_word(const CrcSmem& t, uint32_t crc, uint32_t w) {
+// one 32-bit word through the CRC register: two slice-by-2 steps (T1 = T0 advanced by one byte)
+__device__ __forceinline__ uint32_t crc_word(const CrcLut& t, uint32_t crc, uint32_t w) {
     const uint32_t x = crc ^ w;
-    return t.tab[3][x & 0xff] ^ t.tab[2][(x >> 8) & 0xff] ^ t.tab[1][(x >> 16) & 0xff] ^ t.tab[0][x >> 24];
+    const uint32_t c1 = t.look<0, 1>(x) ^ t.look<1, 0>(x) ^ (x >> 16);
+    return t.look<0, 1>(c1) ^ t.look<1, 0>(c1) ^ (c1 >> 16);
 }
 
 // (a * b) mod P for reflected 32-bit residues: carry-less product (integer-multiply-with-holes,
-// gcm_math.cuh), realigned by one bit, then the upper 32 coefficients are folded with one table step.
-__device__ __forceinline__ uint32_t crc_mulmod(const CrcSmem& t, uint32_t a, uint32_t b) {
+// gcm_math.cuh), realigned by one bit, then the upper 32 coefficients are folded with one word step.
+__device__ __forceinline__ uint32_t crc_mulmod(const CrcLut& t, uint32_t a, uint32_t b) {
     uint32_t bm[4] = {b & 0x11111111u, b & 0x22222222u, b & 0x44444444u, b & 0x88888888u};
     const uint64_t p = clmul32(a, bm) << 1;
     return crc_word(t, 0u, (uint32_t)p) ^ (uint32_t)(p >> 32);
 }
 
-// CRC32c of the staged packet (nwords 32-bit words at `words`, word 2 = checksum field counted as 0).
-// All 32 lanes call; every lane gets the result.
-__device__ __forceinline__ uint32_t warp_crc32c(const CrcSmem& t, const uint32_t* words, uint32_t nwords, int lane) {
-    const uint32_t segw = (nwords + 31) >> 5;
+// CRC32c of the staged packet (nwords 32-bit words at `words`; the caller has zeroed the checksum
+// field, word 2).  All 32 lanes call; every lane gets the result.  Lane l runs the register over its
+// own contiguous segment (lane 0 starts from the 0xFFFFFFFF init value, the others from 0), the
+// partial remainders are moved to their place by a multiply with x^(8 * bytes after the segment).
+__device__ __forceinline__ uint32_t warp_crc32c(const CrcLut& t, const uint32_t* words, uint32_t nwords, int lane) {
+    const uint32_t segw = (nwords + 31) >> 5;            // <= 10 for a 1228-byte packet
     const uint32_t w0 = (uint32_t)lane * segw;
     uint32_t w1 = w0 + segw;
     if (w1 > nwords) w1 = nwords;
-    uint32_t c = 0;
-    for (uint32_t w = w0; w < w1; w++) {
-        uint32_t v = words[w];
-        if (w == 2) v = 0;
-        if (w == 0) v ^= 0xffffffffu;                   // the init value, folded into the first four bytes
-        c = crc_word(t, c, v);
-    }
+    uint32_t c = lane == 0 ? 0xffffffffu : 0u;
+    const uint32_t* p = words + w0;
+    const int cnt = w0 < nwords ? (int)(w1 - w0) : 0;
+#pragma unroll
+    for (int i = 0; i < 10; i++)
+        if (i < cnt) c = crc_word(t, c, p[i]);
+    for (int i = 10; i < cnt; i++) c = crc_word(t, c, p[i]);
     uint32_t part = 0;
-    if (w0 < nwords) part = crc_mulmod(t, c, g_crc_xpow[(nwords - w1) * 4]);
+    if (cnt) part = crc_mulmod(t, c, g_crc_xpow[(nwords - w1) * 4]);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) part ^= __shfl_xor_sync(0xffffffffu, part, o);
     return ~part;
+}
+
+// 16 payload bytes at src + 16 v for staging: interior vectors take aligned loads (+ one funnel when
+// the source is not 16-byte aligned), the vectors that touch the item's end take the bounded path
+__device__ __forceinline__ uint4 stage_load16(const uint8_t* src, uint32_t v, uint32_t len) {
+    const unsigned sa = (unsigned)((uintptr_t)src & 15);
+    const uint8_t* p = src + 16 * (size_t)v;
+    if (16 * v + 32 <= len) {                             // the two covering aligned vectors are inside the item
+        const uint4 a = ldg128(p - sa);
+        if (!sa) return a;
+        return funnel16(a, ldg128(p - sa + 16), sa);
+    }
+    if (!sa && 16 * v + 16 <= len) return ldg128(p);
+    return load16_bounded(p, src, src + len);
+}
+
+// common prologue of the two packet kernels: fill the replicated tables, hand every warp its buffer
+__device__ __forceinline__ uint8_t* sctp_smem_setup(uint8_t* dyn_smem, CrcLut& lut) {
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(dyn_smem);
+    const uint32_t tbase = (sbase + 0xffffu) & ~0xffffu;
+    uint32_t* tabs = reinterpret_cast<uint32_t*>(dyn_smem + (tbase - sbase));
+    for (int idx = threadIdx.x; idx < 256 * 32; idx += blockDim.x) {
+        const int x = idx >> 5, l = idx & 31;
+        tabs[x * 64 + l] = g_crc_tab[0][x];
+        tabs[x * 64 + 32 + l] = g_crc_tab[1][x];
+    }
+    __syncthreads();
+    lut.lb = tbase + 4u * (threadIdx.x & 31);
+    const uint32_t slack = tbase - sbase;
+    uint8_t* stage = slack >= kSctpStageBytes ? dyn_smem : dyn_smem + slack + kCrcLutBytes;
+    return stage + (threadIdx.x >> 5) * kSctpBufBytes;
 }
 
 // smem byte stream [start, start + nbytes) of a 4-byte aligned buffer -> dst (any alignment):
@@ -94,13 +146,11 @@ struct SctpPacketizeArgs {
     u64* pkt_off;                                         // out: byte offset of every packet (+ 1 terminator)
 };
 
-__global__ void __launch_bounds__(32 * kSctpWarps) sctp_packetize_kernel(const SctpPacketizeArgs a) {
-    __shared__ CrcSmem tabs;
-    __shared__ __align__(16) uint8_t bufs[kSctpWarps][kSctpBufBytes];
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) (&tabs.tab[0][0])[i] = (&g_crc_tab[0][0])[i];
-    __syncthreads();
+__global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_packetize_kernel(const SctpPacketizeArgs a) {
+    extern __shared__ __align__(16) uint8_t sctp_dyn_smem[];
+    CrcLut tabs;
+    uint8_t* buf = sctp_smem_setup(sctp_dyn_smem, tabs);
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    uint8_t* buf = bufs[wib];
     uint32_t* bw = reinterpret_cast<uint32_t*>(buf);
     const bool dtls = a.epoch != nullptr;
     const uint32_t hdr = dtls ? 13u : 0u;
@@ -146,9 +196,10 @@ __global__ void __launch_bounds__(32 * kSctpWarps) sctp_packetize_kernel(const S
                 buf[kSctpPktAt - 13 + lane] = (uint8_t)b;
             }
             // ---- payload, zero padded, into the 16-byte aligned part of the buffer
-            for (uint32_t v = lane; v * 16 < padded; v += 32) {
-                const uint4 x = load16_bounded(m + off + 16 * v, m + off, m + off + fl);
-                *reinterpret_cast<uint4*>(buf + kSctpPktAt + 28 + 16 * v) = x;
+#pragma unroll
+            for (int it = 0; it < 3; it++) {                                  // 75 vectors for a full fragment
+                const uint32_t v = lane + 32 * it;
+                if (v * 16 < padded) *reinterpret_cast<uint4*>(buf + kSctpPktAt + 28 + 16 * v) = stage_load16(m + off, v, fl);
             }
             __syncwarp();
             const uint32_t crc = warp_crc32c(tabs, bw + kSctpPktAt / 4, plen >> 2, lane);
@@ -168,13 +219,11 @@ struct SctpUnpackArgs {
     p2pt_sctp_chunk* info; p2pt_desc* desc;
 };
 
-__global__ void __launch_bounds__(32 * kSctpWarps) sctp_unpack_kernel(const SctpUnpackArgs a) {
-    __shared__ CrcSmem tabs;
-    __shared__ __align__(16) uint8_t bufs[kSctpWarps][kSctpBufBytes];
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) (&tabs.tab[0][0])[i] = (&g_crc_tab[0][0])[i];
-    __syncthreads();
+__global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_unpack_kernel(const SctpUnpackArgs a) {
+    extern __shared__ __align__(16) uint8_t sctp_dyn_smem[];
+    CrcLut tabs;
+    uint8_t* buf = sctp_smem_setup(sctp_dyn_smem, tabs);
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    uint8_t* buf = bufs[wib];
     const uint32_t* bw = reinterpret_cast<const uint32_t*>(buf);
     const u64 warp = (u64)blockIdx.x * kSctpWarps + wib, nwarps = (u64)gridDim.x * kSctpWarps;
     for (u64 i = warp; i < a.n; i += nwarps) {
@@ -187,11 +236,18 @@ __global__ void __launch_bounds__(32 * kSctpWarps) sctp_unpack_kernel(const Sctp
             const uint32_t n = (uint32_t)(ilen - a.headroom);
             const uint8_t* p = a.in + io + a.headroom;
             __syncwarp();
-            for (uint32_t v = lane; v * 16 < n; v += 32)
-                *reinterpret_cast<uint4*>(buf + 16 * v) = load16_bounded(p + 16 * v, p, p + n);
+#pragma unroll
+            for (int it = 0; it < 3; it++) {
+                const uint32_t v = lane + 32 * it;
+                if (v * 16 < n) *reinterpret_cast<uint4*>(buf + 16 * v) = stage_load16(p, v, n);
+            }
+            __syncwarp();
+            const uint32_t theirs = bw[2];
+            __syncwarp();
+            if (lane == 0) reinterpret_cast<uint32_t*>(buf)[2] = 0;          // checksum field counts as zero
             __syncwarp();
             const uint32_t crc = warp_crc32c(tabs, bw, n >> 2, lane);
-            if (crc != bw[2]) st = P2PT_ST_SCTP_BAD_CHECKSUM;                // checked first, like Packet::unmarshal
+            if (crc != theirs) st = P2PT_ST_SCTP_BAD_CHECKSUM;               // checked first, like Packet::unmarshal
             else if (n < 28 || buf[12] != 0) st = P2PT_ST_SCTP_MALFORMED;
             else {
                 const uint32_t w3 = bswap32(bw[3]);

@@ -101,7 +101,49 @@ def records_config(n, L, n_sessions):
                      "alg_bytes_per_record": 2 * L + 74, "frac_of_hbm_peak": n * (2 * L + 74) / t_open / 1e6 / peak}}
 
 
+def sctp_config(n, L):
+    """n messages of L <= 1200 bytes -> n packets; packetise, then unpack + reassemble"""
+    w = workload.frames_workload(n, L)
+    msg_off = workload.fixed_offsets(n, L)
+    plen = 28 + ((L + 3) & ~3)
+    d_msg = t(w["payload"]); d_moff = t(msg_off)
+    z16 = torch.full((n,), 5000, dtype=torch.int16, device=dev); one16 = torch.ones(n, dtype=torch.int16, device=dev)
+    ssn = (torch.arange(n, device=dev) & 0x7FFF).to(torch.int16); v32 = torch.full((n,), 7, dtype=torch.int32, device=dev)
+    pp = torch.full((n,), 53, dtype=torch.int32, device=dev); tsn = torch.arange(n, dtype=torch.int32, device=dev)
+    out = torch.empty(n * plen, dtype=torch.uint8, device=dev)
+    omoff = t(workload.fixed_offsets(n, plen)[:-1].copy()); first = t(np.arange(n + 1, dtype=np.uint64))
+    pkt_off = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    pk = lambda: ctx.call("p2pt_sctp_packetize_batch_device", n, d_msg, d_moff, z16, z16, v32, one16, ssn, pp, tsn, None, None,
+                          out, omoff, first, pkt_off, s)
+    info = torch.empty(n * 16, dtype=torch.uint8, device=dev); desc = torch.empty(n * 24, dtype=torch.uint8, device=dev)
+    up = lambda: ctx.call("p2pt_sctp_unpack_batch_device", n, out, pkt_off, 0, info, desc, s)
+    sb = int(ctx.lib.p2pt_sctp_reassemble_scratch_bytes(n)); scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
+    msg = torch.empty(n * L, dtype=torch.uint8, device=dev); moff = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    mfirst = torch.empty(n, dtype=torch.int32, device=dev); mstat = torch.empty(n, dtype=torch.uint8, device=dev)
+    nm = torch.zeros(1, dtype=torch.int32, device=dev)
+    ra = lambda: ctx.call("p2pt_sctp_reassemble_batch_device", n, info, desc, None, out, n, msg, n * L, moff, mfirst, mstat, nm, scratch, sb, s)
+    t_pk = timeit(pk); t_up = timeit(up); t_ra = timeit(ra)
+    assert int(nm.item()) == n and int(mstat.sum()) == 0 and torch.equal(msg, d_msg)
+    hp = np.zeros(n * plen, np.uint8); hoff = workload.fixed_offsets(n, plen)
+    res = {}
+    for nt in (1, cores):
+        times = (C.c_double * 2)(); stats = (C.c_uint64 * 2)()
+        fast.cpufast_sctp(C.c_uint64(n), p(w["payload"]), p(msg_off), p(hp), p(hoff), C.c_int(nt), times, stats)
+        assert stats[0] == 0 and stats[1] == n * L
+        res[f"cpu_{nt}_threads"] = {"packetize_gbs_payload": n * L / times[0] / 1e9, "unpack_verify_gbs_payload": n * L / times[1] / 1e9}
+    ab_pk = L + plen + 50; ab_up = plen + 8 + 40
+    out_d = {"messages": n, "payload_bytes": L,
+             "packetize": {"ms": t_pk, "alg_bytes_per_packet": ab_pk, "hbm_gbs": n * ab_pk / t_pk / 1e6, "frac_of_hbm_peak": n * ab_pk / t_pk / 1e6 / peak,
+                           "payload_gbs": n * L / t_pk / 1e6, "packets_per_s": n / t_pk * 1e3},
+             "unpack_crc_verify": {"ms": t_up, "alg_bytes_per_packet": ab_up, "hbm_gbs": n * ab_up / t_up / 1e6, "frac_of_hbm_peak": n * ab_up / t_up / 1e6 / peak,
+                                   "payload_gbs": n * L / t_up / 1e6},
+             "reassemble_sort_gather": {"ms": t_ra, "payload_gbs": n * L / t_ra / 1e6}}
+    out_d.update(res)
+    return out_d
+
+
 res = {"hbm_peak_gbs": peak, "host_cores": cores,
+       "SCTP_1M_messages_1200B": sctp_config(1_000_000, 1200),
        "C2_1M_frames_1200B_4096_streams": codec_config(1_000_000, 1200, False),
        "C4_10M_frames_64B_sse": codec_config(10_000_000, 64, True),
        "C3_1M_records_1200B_1_session": records_config(1_000_000, 1200, 1),
