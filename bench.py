@@ -275,174 +275,185 @@ def run_gpu(args):
     demux_ms = float(np.mean([m[2].elapsed_time(m[3]) for m in marks]))
     value = world * payload_bytes / (dev_ms * 1e-3) / 1e9
 
-    # ---------------- end-to-end arm: host-pointer C ABI, pinned host buffers ----------------
-    # What a deployment does with one GPU: the batch is cut into sub-batches of whole sessions
-    # (sessions share nothing, so each sub-batch is an independent call), the provider side seals
-    # (serve.rs:269-276 + dc.send) while the consumer side opens + demuxes (rtc.rs:88 +
-    # proxy.rs:109-170).  Two seal workers and two open workers, each a host thread with its own
-    # p2pt_ctx, keep PCIe busy in both directions; every byte goes host -> device -> host inside the
-    # timed region, through the host-pointer C ABI only.
-    import queue
-    NB = 8                                   # sub-batches per step (8192 sessions = 131072 records each)
-    sub_n = n // NB
-    sub_streams = max_streams // NB
-    NW = 3                                   # workers (host thread + p2pt_ctx) per direction
-    ctxs = [ctx] + [p2pt.Context(local) for _ in range(2 * NW - 1)]
-    for c_ in ctxs[1:]:
-        c_.sessions_load(keys, ivs, keys, ivs)
-    for c_ in ctxs:
-        # with several calls in flight the overlap comes from the other workers; one large copy per
-        # direction per call is what PCIe moves fastest (measured: 48 GB/s vs 41 GB/s in 16 MiB pieces)
-        c_.set_option("chunk_bytes", 256 << 20)
+    def run_e2e():
+        # ---------------- end-to-end arm: host-pointer C ABI, pinned host buffers ----------------
+        # What a deployment does with one GPU: the batch is cut into sub-batches of whole sessions
+        # (sessions share nothing, so each sub-batch is an independent call), the provider side seals
+        # (serve.rs:269-276 + dc.send) while the consumer side opens + demuxes (rtc.rs:88 +
+        # proxy.rs:109-170).  Two seal workers and two open workers, each a host thread with its own
+        # p2pt_ctx, keep PCIe busy in both directions; every byte goes host -> device -> host inside the
+        # timed region, through the host-pointer C ABI only.
+        import queue
+        NB = 8                                   # sub-batches per step (8192 sessions = 131072 records each)
+        sub_n = n // NB
+        sub_streams = max_streams // NB
+        NW = 3                                   # workers (host thread + p2pt_ctx) per direction
+        ctxs = [ctx] + [p2pt.Context(local) for _ in range(2 * NW - 1)]
+        for c_ in ctxs[1:]:
+            c_.sessions_load(keys, ivs, keys, ivs)
+        for c_ in ctxs:
+            # with several calls in flight the overlap comes from the other workers; one large copy per
+            # direction per call is what PCIe moves fastest (measured: 48 GB/s vs 41 GB/s in 16 MiB pieces)
+            c_.set_option("chunk_bytes", 256 << 20)
 
-    def pinned(a):
-        return torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory()
-    h = {k: pinned(w[k]) for k in ("session", "epoch", "seq48", "nonce8", "types", "sids", "payload", "pay_off", "rec_off")}
-    esz = {"session": 4, "epoch": 2, "seq48": 8, "nonce8": 8, "types": 1, "sids": 4, "pay_off": 8, "rec_off": 8}
-    hp = {k: h[k].data_ptr() for k in h}
-    h_rec = [torch.empty(rec_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
-    h_status = torch.empty(n, dtype=torch.uint8).pin_memory()
-    h_desc = torch.empty(n * 24, dtype=torch.uint8).pin_memory()
-    h_uniq = torch.empty(NB * (sub_streams + 1) * 4, dtype=torch.uint8).pin_memory()
-    h_usess = torch.empty(NB * (sub_streams + 1) * 4, dtype=torch.uint8).pin_memory()
-    h_csr = torch.empty(NB * (sub_streams + 1) * 8, dtype=torch.uint8).pin_memory()
-    h_goff = torch.empty(NB * (sub_streams + 1) * 8, dtype=torch.uint8).pin_memory()
-    h_perm = torch.empty(n * 4, dtype=torch.uint8).pin_memory()
-    h_gath = torch.empty(payload_bytes, dtype=torch.uint8).pin_memory()
-    kks = (C.c_uint32 * NB)()
-    errs = []
+        def pinned(a):
+            return torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory()
+        h = {k: pinned(w[k]) for k in ("session", "epoch", "seq48", "nonce8", "types", "sids", "payload", "pay_off", "rec_off")}
+        esz = {"session": 4, "epoch": 2, "seq48": 8, "nonce8": 8, "types": 1, "sids": 4, "pay_off": 8, "rec_off": 8}
+        hp = {k: h[k].data_ptr() for k in h}
+        h_rec = [torch.empty(rec_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        h_status = torch.empty(n, dtype=torch.uint8).pin_memory()
+        h_desc = torch.empty(n * 24, dtype=torch.uint8).pin_memory()
+        h_uniq = torch.empty(NB * (sub_streams + 1) * 4, dtype=torch.uint8).pin_memory()
+        h_usess = torch.empty(NB * (sub_streams + 1) * 4, dtype=torch.uint8).pin_memory()
+        h_csr = torch.empty(NB * (sub_streams + 1) * 8, dtype=torch.uint8).pin_memory()
+        h_goff = torch.empty(NB * (sub_streams + 1) * 8, dtype=torch.uint8).pin_memory()
+        h_perm = torch.empty(n * 4, dtype=torch.uint8).pin_memory()
+        h_gath = torch.empty(payload_bytes, dtype=torch.uint8).pin_memory()
+        kks = (C.c_uint32 * NB)()
+        errs = []
 
-    def at(name, r0):
-        return hp[name] + r0 * esz[name]
+        def at(name, r0):
+            return hp[name] + r0 * esz[name]
 
-    def do_seal(c_, buf, b):
-        r0 = b * sub_n
-        c_.call("p2pt_pipeline_seal", sub_n, at("session", r0), at("epoch", r0), at("seq48", r0), at("nonce8", r0),
-                at("types", r0), at("sids", r0), hp["payload"], at("pay_off", r0), h_rec[buf].data_ptr(),
-                at("rec_off", r0), h_status.data_ptr() + r0)
+        def do_seal(c_, buf, b):
+            r0 = b * sub_n
+            c_.call("p2pt_pipeline_seal", sub_n, at("session", r0), at("epoch", r0), at("seq48", r0), at("nonce8", r0),
+                    at("types", r0), at("sids", r0), hp["payload"], at("pay_off", r0), h_rec[buf].data_ptr(),
+                    at("rec_off", r0), h_status.data_ptr() + r0)
 
-    def do_open(c_, buf, b):
-        r0 = b * sub_n
-        so = b * (sub_streams + 1)
-        c_.call("p2pt_pipeline_open_demux", sub_n, at("session", r0), h_rec[buf].data_ptr(), at("rec_off", r0), None,
-                h_desc.data_ptr() + 24 * r0, sub_streams, h_uniq.data_ptr() + 4 * so, h_usess.data_ptr() + 4 * so,
-                h_csr.data_ptr() + 8 * so, h_perm.data_ptr() + 4 * r0, C.addressof(kks) + 4 * b,
-                h_gath.data_ptr() + r0 * PAYLOAD, sub_n * PAYLOAD, h_goff.data_ptr() + 8 * so)
+        def do_open(c_, buf, b):
+            r0 = b * sub_n
+            so = b * (sub_streams + 1)
+            c_.call("p2pt_pipeline_open_demux", sub_n, at("session", r0), h_rec[buf].data_ptr(), at("rec_off", r0), None,
+                    h_desc.data_ptr() + 24 * r0, sub_streams, h_uniq.data_ptr() + 4 * so, h_usess.data_ptr() + 4 * so,
+                    h_csr.data_ptr() + 8 * so, h_perm.data_ptr() + 4 * r0, C.addressof(kks) + 4 * b,
+                    h_gath.data_ptr() + r0 * PAYLOAD, sub_n * PAYLOAD, h_goff.data_ptr() + 8 * so)
 
-    def e2e_run(steps):
-        """steps x NB sub-batches, each sealed then opened+demuxed; 2 seal + 2 open worker threads."""
-        jobs = steps * NB
-        sealed = [threading.Event() for _ in range(jobs)]
-        opened = [threading.Event() for _ in range(jobs)]
+        def e2e_run(steps):
+            """steps x NB sub-batches, each sealed then opened+demuxed; 2 seal + 2 open worker threads."""
+            jobs = steps * NB
+            sealed = [threading.Event() for _ in range(jobs)]
+            opened = [threading.Event() for _ in range(jobs)]
 
-        def seal_worker(i):
-            try:
-                for q in range(i, jobs, NW):
-                    if q >= 2 * NB:
-                        opened[q - 2 * NB].wait()          # the record buffer of two steps ago is free again
-                    do_seal(ctxs[i], (q // NB) & 1, q % NB)
-                    sealed[q].set()
-            except Exception as e:
-                errs.append(e)
-                for ev_ in sealed + opened:
-                    ev_.set()
+            def seal_worker(i):
+                try:
+                    for q in range(i, jobs, NW):
+                        if q >= 2 * NB:
+                            opened[q - 2 * NB].wait()          # the record buffer of two steps ago is free again
+                        do_seal(ctxs[i], (q // NB) & 1, q % NB)
+                        sealed[q].set()
+                except Exception as e:
+                    errs.append(e)
+                    for ev_ in sealed + opened:
+                        ev_.set()
 
-        def open_worker(i):
-            try:
-                for q in range(i, jobs, NW):
-                    sealed[q].wait()
-                    do_open(ctxs[NW + i], (q // NB) & 1, q % NB)
-                    opened[q].set()
-            except Exception as e:
-                errs.append(e)
-                for ev_ in sealed + opened:
-                    ev_.set()
-        ts = [threading.Thread(target=seal_worker, args=(i,)) for i in range(NW)] + \
-             [threading.Thread(target=open_worker, args=(i,)) for i in range(NW)]
-        for t_ in ts:
-            t_.start()
-        for t_ in ts:
-            t_.join()
-        if errs:
-            raise errs[0]
+            def open_worker(i):
+                try:
+                    for q in range(i, jobs, NW):
+                        sealed[q].wait()
+                        do_open(ctxs[NW + i], (q // NB) & 1, q % NB)
+                        opened[q].set()
+                except Exception as e:
+                    errs.append(e)
+                    for ev_ in sealed + opened:
+                        ev_.set()
+            ts = [threading.Thread(target=seal_worker, args=(i,)) for i in range(NW)] + \
+                 [threading.Thread(target=open_worker, args=(i,)) for i in range(NW)]
+            for t_ in ts:
+                t_.start()
+            for t_ in ts:
+                t_.join()
+            if errs:
+                raise errs[0]
 
-    e2e_steps = max(1, min(args.steps, 6))
-    e2e_run(2)
-    assert all(int(kks[b]) == sub_streams for b in range(NB)), list(kks)
-    assert int(h_status.sum()) == 0
-    assert np.array_equal(h_gath[: 4096 * PAYLOAD].numpy().reshape(4096, PAYLOAD), got), "e2e result differs"
-    tail = gathered[-4096 * PAYLOAD:].cpu().numpy()
-    assert np.array_equal(h_gath[-4096 * PAYLOAD:].numpy(), tail), "e2e result differs (tail)"
-    launches_e0 = sum(c_.launch_count() for c_ in ctxs)
-    barrier()
-    t0 = time.perf_counter()
-    e2e_run(e2e_steps)
-    torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
-    barrier()
-    launches_e2e = (sum(c_.launch_count() for c_ in ctxs) - launches_e0) // e2e_steps
-    # latency of ONE sub-batch through both calls with nothing else running, for reference
-    t0 = time.perf_counter(); do_seal(ctxs[0], 0, 0); t_seal = time.perf_counter() - t0
-    t0 = time.perf_counter(); do_open(ctxs[NW], 0, 0); t_open = time.perf_counter() - t0
-    meta = n * (4 + 2 + 8 + 8 + 1 + 4 + 8 + 8)
-    h2d = payload_bytes + meta + rec_bytes + n * (4 + 8)
-    d2h = rec_bytes + n + payload_bytes + n * 24 + n * 4 + NB * (sub_streams + 1) * (4 + 4 + 8 + 8)
-    e2e_val = world * payload_bytes / e2e_s / 1e9
-
-    # single small frame, batch of 1, host buffers: launch + copies dominate; the CPU wins this one
-    from p2p_llm_tunnel_b200.protocol import TunnelMessage
-    lat = {}
-    try:
-        sse = b'data: {"token": "hello"}\n\n' + b" " * 37          # 64-byte SSE chunk
-        m1 = TunnelMessage.res_body(99, sse)
-        for _ in range(5):
-            f1 = m1.encode(ctxs[-1]); TunnelMessage.decode(f1, ctxs[-1])
+        e2e_steps = max(1, min(args.steps, 6))
+        e2e_run(2)
+        assert all(int(kks[b]) == sub_streams for b in range(NB)), list(kks)
+        assert int(h_status.sum()) == 0
+        assert np.array_equal(h_gath[: 4096 * PAYLOAD].numpy().reshape(4096, PAYLOAD), got), "e2e result differs"
+        tail = gathered[-4096 * PAYLOAD:].cpu().numpy()
+        assert np.array_equal(h_gath[-4096 * PAYLOAD:].numpy(), tail), "e2e result differs (tail)"
+        launches_e0 = sum(c_.launch_count() for c_ in ctxs)
+        barrier()
         t0 = time.perf_counter()
-        for _ in range(50):
-            f1 = m1.encode(ctxs[-1])
-        lat["frame_encode_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
-        t0 = time.perf_counter()
-        for _ in range(50):
-            TunnelMessage.decode(f1, ctxs[-1])
-        lat["frame_decode_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
-        one = {k: w[k][:1].copy() for k in ("session", "epoch", "seq48", "types", "sids")}
-        one_pay = np.frombuffer(sse, np.uint8); one_off = np.array([0, 64], np.uint64)
-        for _ in range(3):
-            ctxs[-1].pipeline_seal(one["session"], one["epoch"], one["seq48"], w["nonce8"][:8], one["types"], one["sids"], one_pay, one_off)
-        t0 = time.perf_counter()
-        for _ in range(50):
-            r1 = ctxs[-1].pipeline_seal(one["session"], one["epoch"], one["seq48"], w["nonce8"][:8], one["types"], one["sids"], one_pay, one_off)
-        lat["pipeline_seal_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
-        lat["note"] = "wall clock per call through the Python binding, one 64-byte RES_BODY frame, host buffers"
-    except Exception as e:
-        lat = {"error": str(e)}
+        e2e_run(e2e_steps)
+        torch.cuda.synchronize()
+        e2e_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
+        barrier()
+        launches_e2e = (sum(c_.launch_count() for c_ in ctxs) - launches_e0) // e2e_steps
+        # latency of ONE sub-batch through both calls with nothing else running, for reference
+        t0 = time.perf_counter(); do_seal(ctxs[0], 0, 0); t_seal = time.perf_counter() - t0
+        t0 = time.perf_counter(); do_open(ctxs[NW], 0, 0); t_open = time.perf_counter() - t0
+        meta = n * (4 + 2 + 8 + 8 + 1 + 4 + 8 + 8)
+        h2d = payload_bytes + meta + rec_bytes + n * (4 + 8)
+        d2h = rec_bytes + n + payload_bytes + n * 24 + n * 4 + NB * (sub_streams + 1) * (4 + 4 + 8 + 8)
+        e2e_val = world * payload_bytes / e2e_s / 1e9
 
-    # PCIe as this box delivers it: pinned 1 GiB copies, each direction alone and both at once
-    pcie = None
-    try:
-        nb = 1 << 30
-        hp = torch.empty(nb, dtype=torch.uint8).pin_memory(); hq = torch.empty(nb, dtype=torch.uint8).pin_memory()
-        dp = torch.empty(nb, dtype=torch.uint8, device=dev); dq = torch.empty(nb, dtype=torch.uint8, device=dev)
-        s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+        # single small frame, batch of 1, host buffers: launch + copies dominate; the CPU wins this one
+        from p2p_llm_tunnel_b200.protocol import TunnelMessage
+        lat = {}
+        try:
+            sse = b'data: {"token": "hello"}\n\n' + b" " * 37          # 64-byte SSE chunk
+            m1 = TunnelMessage.res_body(99, sse)
+            for _ in range(5):
+                f1 = m1.encode(ctxs[-1]); TunnelMessage.decode(f1, ctxs[-1])
+            t0 = time.perf_counter()
+            for _ in range(50):
+                f1 = m1.encode(ctxs[-1])
+            lat["frame_encode_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
+            t0 = time.perf_counter()
+            for _ in range(50):
+                TunnelMessage.decode(f1, ctxs[-1])
+            lat["frame_decode_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
+            one = {k: w[k][:1].copy() for k in ("session", "epoch", "seq48", "types", "sids")}
+            one_pay = np.frombuffer(sse, np.uint8); one_off = np.array([0, 64], np.uint64)
+            for _ in range(3):
+                ctxs[-1].pipeline_seal(one["session"], one["epoch"], one["seq48"], w["nonce8"][:8], one["types"], one["sids"], one_pay, one_off)
+            t0 = time.perf_counter()
+            for _ in range(50):
+                r1 = ctxs[-1].pipeline_seal(one["session"], one["epoch"], one["seq48"], w["nonce8"][:8], one["types"], one["sids"], one_pay, one_off)
+            lat["pipeline_seal_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
+            lat["note"] = "wall clock per call through the Python binding, one 64-byte RES_BODY frame, host buffers"
+        except Exception as e:
+            lat = {"error": str(e)}
 
-        def timed(fn):
-            torch.cuda.synchronize(); t = time.perf_counter(); fn(); torch.cuda.synchronize(); return time.perf_counter() - t
+        # PCIe as this box delivers it: pinned 1 GiB copies, each direction alone and both at once
+        pcie = None
+        try:
+            nb = 1 << 30
+            hp = torch.empty(nb, dtype=torch.uint8).pin_memory(); hq = torch.empty(nb, dtype=torch.uint8).pin_memory()
+            dp = torch.empty(nb, dtype=torch.uint8, device=dev); dq = torch.empty(nb, dtype=torch.uint8, device=dev)
+            s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
 
-        def up():
-            with torch.cuda.stream(s1):
-                dp.copy_(hp, non_blocking=True)
+            def timed(fn):
+                torch.cuda.synchronize(); t = time.perf_counter(); fn(); torch.cuda.synchronize(); return time.perf_counter() - t
 
-        def down():
-            with torch.cuda.stream(s2):
-                hq.copy_(dq, non_blocking=True)
-        up(); down(); torch.cuda.synchronize()
-        t_up = min(timed(up) for _ in range(3)); t_dn = min(timed(down) for _ in range(3))
-        t_bi = min(timed(lambda: (up(), down())) for _ in range(3))
-        pcie = {"h2d_gbs": nb / t_up / 1e9, "d2h_gbs": nb / t_dn / 1e9, "bidir_each_gbs": nb / t_bi / 1e9,
-                "theoretical_gbs_per_dir": 63.0}
-        del hp, hq, dp, dq
-    except Exception as e:
-        pcie = {"error": str(e)}
+            def up():
+                with torch.cuda.stream(s1):
+                    dp.copy_(hp, non_blocking=True)
+
+            def down():
+                with torch.cuda.stream(s2):
+                    hq.copy_(dq, non_blocking=True)
+            up(); down(); torch.cuda.synchronize()
+            t_up = min(timed(up) for _ in range(3)); t_dn = min(timed(down) for _ in range(3))
+            t_bi = min(timed(lambda: (up(), down())) for _ in range(3))
+            pcie = {"h2d_gbs": nb / t_up / 1e9, "d2h_gbs": nb / t_dn / 1e9, "bidir_each_gbs": nb / t_bi / 1e9,
+                    "theoretical_gbs_per_dir": 63.0}
+            del hp, hq, dp, dq
+        except Exception as e:
+            pcie = {"error": str(e)}
+
+
+        return e2e_val, e2e_s, e2e_steps, launches_e2e, t_seal, t_open, h2d, d2h, pcie, lat, sub_n, NB
+
+    if args.no_e2e:
+        e2e_val = e2e_s = t_seal = t_open = None
+        e2e_steps = launches_e2e = h2d = d2h = sub_n = NB = 0
+        pcie = lat = None
+    else:
+        e2e_val, e2e_s, e2e_steps, launches_e2e, t_seal, t_open, h2d, d2h, pcie, lat, sub_n, NB = run_e2e()
 
     if rank != 0:
         if world > 1:
@@ -506,7 +517,7 @@ def run_gpu(args):
         "stages": stages,
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
-        "e2e": {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+        "e2e": None if args.no_e2e else {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_s * 1e3, "steps": e2e_steps, "launches_per_step": int(launches_e2e),
                 "one_subbatch_alone_ms": {"pipeline_seal": t_seal * 1e3, "pipeline_open_demux": t_open * 1e3,
                                           "records": sub_n},
@@ -532,6 +543,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end (host buffer) leg; for profiling runs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
