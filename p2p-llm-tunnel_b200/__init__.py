@@ -12,9 +12,10 @@ from .protocol import (  # noqa: F401
     demux_batch, chunk_body,
 )
 from .dtls import CryptoGcm  # noqa: F401
+from .reader import ProxyReader, ServeReassembler, StreamEvent  # noqa: F401
 
 __all__ = [
     "Context", "P2ptError", "lib_path", "load_library", "MessageType", "TunnelMessage",
     "MAX_BODY_CHUNK", "MAX_FRAME_SIZE", "encode_batch", "decode_batch", "demux_batch", "chunk_body",
-    "CryptoGcm",
+    "CryptoGcm", "ProxyReader", "ServeReassembler", "StreamEvent",
 ]
