@@ -150,7 +150,23 @@ __device__ __forceinline__ void quad_copy_bytes(uint8_t* dst, const uint8_t* src
         if (s) o = funnel16(a, ldg128(sa + 16 * v + 16), s);
         stg128(dst + 16 * v, o);
     }
-    for (uint32_t b = (nvec << 4) + q; b < len; b += 4) dst[b] = __ldg(src + b);
+    // tail (< 32 bytes): aligned 32-bit destination words, each from the two aligned source words
+    // that cover it (an aligned word that holds at least one byte of the item is always readable),
+    // then at most three single bytes
+    const uint32_t done = nvec << 4, rem = len - done;
+    const uint32_t nword = rem >> 2;
+    {
+        const uint8_t* sp = src + done;
+        const unsigned ws = (unsigned)((uintptr_t)sp & 3);
+        const uint32_t* sw = reinterpret_cast<const uint32_t*>(sp - ws);
+        uint32_t* dw = reinterpret_cast<uint32_t*>(dst + done);
+        for (uint32_t w = q; w < nword; w += 4) {
+            const uint32_t lo = __ldg(sw + w);
+            const uint32_t hi = ws ? __ldg(sw + w + 1) : 0u;
+            dw[w] = __funnelshift_r(lo, hi, ws * 8);
+        }
+    }
+    for (uint32_t b = done + (nword << 2) + q; b < len; b += 4) dst[b] = __ldg(src + b);
 }
 
 constexpr uint32_t kQuadCopyMax = 256;     // items up to this size take the 4-lane path

@@ -187,6 +187,15 @@ __device__ __forceinline__ bool demux_pass_trivial(const u64* misc, int pass) {
     return (((misc[1] & misc[2]) >> (8 * pass)) & 0xffu) == 0;
 }
 __device__ __forceinline__ u64 demux_valid_count(u64 n, const u64* misc) { return n - misc[3]; }
+// A trivial pass moves nothing: it leaves the data in the buffer it is in.  Which of the two
+// ping-pong buffers holds the input of `pass` (pass == kSortPasses: the final result) is the parity
+// of the number of real passes before it.
+__device__ __forceinline__ int demux_src_buffer(const u64* misc, int pass) {
+    int b = 0;
+    for (int p = 0; p < pass; p++) b ^= demux_pass_trivial(misc, p) ? 0 : 1;
+    return b;
+}
+struct DemuxBufs { u64* keys[2]; uint32_t* idx[2]; };
 
 __device__ __forceinline__ void demux_tile(u64 n, u64& lo, u64& hi) {
     const u64 per = (n + kSortBlocks - 1) / kSortBlocks;
@@ -198,9 +207,12 @@ __device__ __forceinline__ void demux_tile(u64 n, u64& lo, u64& hi) {
 }
 
 __global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
-    u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx, const p2pt_desc* __restrict__ desc,
+    u64 n, const DemuxBufs bufs, const p2pt_desc* __restrict__ desc,
     int pass, uint32_t* __restrict__ hist, const u64* __restrict__ misc) {
     if (demux_pass_trivial(misc, pass)) return;
+    const int sb = demux_src_buffer(misc, pass);
+    const u64* __restrict__ keys = bufs.keys[sb];
+    const uint32_t* __restrict__ idx = bufs.idx[sb];
     __shared__ uint32_t h[kRadix];
     h[threadIdx.x] = 0;
     __syncthreads();
@@ -248,16 +260,17 @@ __global__ void __launch_bounds__(32 * kRowScanWarps) demux_rowscan_kernel(uint3
 }
 
 __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
-    u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx,
-    u64* __restrict__ keys_out, uint32_t* __restrict__ idx_out, const p2pt_desc* __restrict__ desc,
+    u64 n, const DemuxBufs bufs, const p2pt_desc* __restrict__ desc,
     int pass, const uint32_t* __restrict__ hist, const u64* __restrict__ misc,
     const uint32_t* __restrict__ row_total) {
+    if (demux_pass_trivial(misc, pass)) return;          // nothing to move: the data stays where it is
+    const int sb = demux_src_buffer(misc, pass);
+    const u64* __restrict__ keys = bufs.keys[sb];
+    const uint32_t* __restrict__ idx = bufs.idx[sb];
+    u64* __restrict__ keys_out = bufs.keys[sb ^ 1];
+    uint32_t* __restrict__ idx_out = bufs.idx[sb ^ 1];
     u64 lo, hi;
     demux_tile(n, lo, hi);
-    if (demux_pass_trivial(misc, pass)) {
-        for (u64 i = lo + threadIdx.x; i < hi; i += kSortThreads) { keys_out[i] = keys[i]; idx_out[i] = idx[i]; }
-        return;
-    }
     static_assert(kSortThreads == kRadix, "one thread per digit");
     constexpr int W = kSortThreads / 32;
     __shared__ uint32_t base[kRadix];          // running output position per digit for this block
@@ -367,8 +380,11 @@ __device__ __forceinline__ HeadBytes block_scan_excl(HeadBytes v, HeadBytes& tot
 }
 
 __global__ void __launch_bounds__(kScanThreads) demux_blocksum_kernel(
-    u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx, const p2pt_desc* __restrict__ desc,
+    u64 n, const DemuxBufs bufs, const p2pt_desc* __restrict__ desc,
     const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes) {
+    const int fb = demux_src_buffer(misc, kSortPasses);
+    const u64* __restrict__ keys = bufs.keys[fb];
+    const uint32_t* __restrict__ idx = bufs.idx[fb];
     const u64 m = demux_valid_count(n, misc);
     const u64 j = (u64)blockIdx.x * kScanThreads + threadIdx.x;
     HeadBytes tot;
@@ -399,11 +415,15 @@ __global__ void __launch_bounds__(kScanThreads) demux_scan_blocksums_kernel(
 // Emit perm / uniq_sid / csr / gathered_off and per-frame gather destinations.
 // dst_off[j] (in scratch, reusing the other pair buffer as u64) = byte offset of frame perm[j] in gathered.
 __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
-    u64 n, const u64* __restrict__ keys, const uint32_t* __restrict__ idx, const p2pt_desc* __restrict__ desc,
+    u64 n, const DemuxBufs bufs, const p2pt_desc* __restrict__ desc,
     const u64* __restrict__ misc, const uint32_t* __restrict__ blk_heads, const u64* __restrict__ blk_bytes,
     u64 nblk, uint32_t max_streams, uint32_t* __restrict__ uniq_sid, uint32_t* __restrict__ uniq_session,
     u64* __restrict__ csr, uint32_t* __restrict__ perm, uint32_t* __restrict__ k_out,
-    u64* __restrict__ gathered_off, u64* __restrict__ dst_off) {
+    u64* __restrict__ gathered_off) {
+    const int fb = demux_src_buffer(misc, kSortPasses);
+    const u64* __restrict__ keys = bufs.keys[fb];
+    const uint32_t* __restrict__ idx = bufs.idx[fb];
+    u64* __restrict__ dst_off = bufs.keys[fb ^ 1];       // the idle key buffer holds per-frame gather offsets
     const u64 m = demux_valid_count(n, misc);
     const u64 j = (u64)blockIdx.x * kScanThreads + threadIdx.x;
     HeadBytes it = demux_item(j, m, keys, idx, desc);
@@ -438,11 +458,12 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
 // Gather: body frames only (serve.rs:120-124 extend_from_slice).  Same eight-items-per-warp
 // scheme as the encoder: four lanes per short frame, the whole warp per long one.
 __global__ void __launch_bounds__(256) demux_gather_kernel(
-    u64 n, const u64* __restrict__ misc, const uint32_t* __restrict__ perm, const u64* __restrict__ dst_off,
+    u64 n, const u64* __restrict__ misc, const uint32_t* __restrict__ perm, const DemuxBufs bufs,
     const p2pt_desc* __restrict__ desc, const uint8_t* __restrict__ in,
     uint8_t* __restrict__ gathered, u64 gathered_cap, const uint32_t* __restrict__ k_out, uint32_t max_streams) {
     const u64 m = demux_valid_count(n, misc);
     if (*k_out > max_streams) return;
+    const u64* __restrict__ dst_off = bufs.keys[demux_src_buffer(misc, kSortPasses) ^ 1];
     const int lane = threadIdx.x & 31, quad = lane >> 2, q = lane & 3;
     const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;

@@ -402,26 +402,22 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     DemuxScratch s = demux_carve(scratch, n);
     CUDA_TRY(ctx, cudaMemsetAsync(s.misc, 0, 32, st));
     demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc);
-    int cur = 0;
+    DemuxBufs bufs;
+    bufs.keys[0] = s.keys[0]; bufs.keys[1] = s.keys[1]; bufs.idx[0] = s.idx[0]; bufs.idx[1] = s.idx[1];
     for (int pass = 0; pass < kSortPasses; pass++) {
-        demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.keys[cur], s.idx[cur], desc, pass, s.hist, s.misc);
+        demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, desc, pass, s.hist, s.misc);
         demux_rowscan_kernel<<<kRadix / kRowScanWarps, 32 * kRowScanWarps, 0, st>>>(s.hist, pass, s.misc, s.row_total);
-        demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, s.keys[cur], s.idx[cur], s.keys[cur ^ 1],
-                                                                  s.idx[cur ^ 1], desc, pass, s.hist, s.misc, s.row_total);
-        cur ^= 1;
+        demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, desc, pass, s.hist, s.misc, s.row_total);
     }
-    const u64* skeys = s.keys[cur];
-    const uint32_t* sidx = s.idx[cur];
-    u64* dst_off = s.keys[cur ^ 1];                 // the idle key buffer holds per-frame gather offsets
     const u64 nblk = demux_scan_blocks(n);
-    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, skeys, sidx, desc, s.misc, s.blk_heads, s.blk_bytes);
+    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, desc, s.misc, s.blk_heads, s.blk_bytes);
     demux_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, s.blk_heads, s.blk_bytes);
-    demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, skeys, sidx, desc, s.misc, s.blk_heads, s.blk_bytes, nblk,
+    demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, desc, s.misc, s.blk_heads, s.blk_bytes, nblk,
                                                               max_streams, uniq_sid, uniq_session, (u64*)csr, perm, k_out,
-                                                              (u64*)gathered_off, dst_off);
+                                                              (u64*)gathered_off);
     count_launch(ctx, 1 + 3 * kSortPasses + 3);
     if (gathered) {
-        demux_gather_kernel<<<grid_for(ctx, (n + 7) / 8, 8, 16), 256, 0, st>>>(n, s.misc, perm, dst_off, desc, in, gathered,
+        demux_gather_kernel<<<grid_for(ctx, (n + 7) / 8, 8, 16), 256, 0, st>>>(n, s.misc, perm, bufs, desc, in, gathered,
                                                                     gathered_cap, k_out, max_streams);
         count_launch(ctx);
     }
