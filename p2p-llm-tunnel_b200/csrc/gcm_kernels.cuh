@@ -351,6 +351,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
             body0 = body_lo = ibase + 21; body_hi = ibase + 21 + L;
         }
         if (sidx >= a.n_sessions && st == P2PT_ST_OK) st = P2PT_ST_BAD_HEADER;
+        if (ilen > (1ull << 24) && st == P2PT_ST_OK) st = P2PT_ST_BAD_HEADER;     // far beyond any DTLS record; keeps 32-bit block math safe
 
         if (st != P2PT_ST_OK) {         // group-uniform early outs
             if (MODE == kOpen || MODE == kPipeOpen) {

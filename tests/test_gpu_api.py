@@ -219,3 +219,47 @@ def test_device_kernels_never_write_outside_their_items(ctx):
     gg = gathered.cpu().numpy()
     e = ob.frame_demux(desc, tight)
     assert np.array_equal(gg[:body], e["gathered"]) and np.all(gg[body:] == 0xCD)
+
+
+def test_error_codes_and_empty_batches(ctx):
+    """whole-call failures are negative return codes with a message; n = 0 is a no-op everywhere"""
+    import p2p_llm_tunnel_b200 as p2pt
+    z8 = np.zeros(0, np.uint8); z64 = np.zeros(1, np.uint64)
+    out, off = ctx.frame_encode(z8, np.zeros(0, np.uint32), z8, z64)
+    assert out.size == 0 and list(off) == [0]
+    assert ctx.frame_decode(z8, z64).size == 0
+    r = ctx.frame_demux(np.zeros(0, p2pt._lib.DESC_DTYPE), z8)
+    assert r["k"] == 0 and list(r["csr"]) == [0]
+    keys = np.zeros((1, 16), np.uint8); ivs = np.zeros((1, 4), np.uint8)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    rec, roff, st = ctx.dtls_seal(np.zeros(0, np.uint32), z8, z8, z64)
+    assert rec.size == 0 and st.size == 0
+    # non-monotonic offsets
+    with pytest.raises(p2pt.P2ptError) as e:
+        ctx.frame_decode(np.zeros(16, np.uint8), np.array([0, 10, 5], np.uint64))
+    assert e.value.code == -1 and "non-decreasing" in str(e.value)
+    # output slot too small
+    with pytest.raises(p2pt.P2ptError) as e:
+        ctx.dtls_seal([0], np.zeros(8, np.uint8), np.zeros(50, np.uint8), np.array([0, 50], np.uint64), np.array([0, 60], np.uint64))
+    assert e.value.code == -3
+    # seal before any session is loaded
+    fresh = p2pt.Context(0)
+    with pytest.raises(p2pt.P2ptError) as e:
+        fresh.dtls_seal([0], np.zeros(8, np.uint8), np.zeros(50, np.uint8), np.array([0, 50], np.uint64))
+    assert e.value.code == -4 and "sessions" in str(e.value)
+    with pytest.raises(p2pt.P2ptError):
+        fresh.set_option("no_such_option", 1)
+    assert fresh.get_info("sm_count") == 148 and fresh.get_info("nope") == -1
+    fresh.close()
+    # threads: two host-pointer calls on one ctx from two threads serialise and both succeed
+    import threading
+    res = []
+    def work(seed):
+        rng = np.random.default_rng(seed)
+        raw = np.zeros(13 + 500, np.uint8); raw[0] = 23; raw[1] = 0xFE; raw[2] = 0xFD; raw[13:] = rng.integers(0, 256, 500)
+        rec, _, st = ctx.dtls_seal([0], rng.integers(0, 256, 8, dtype=np.uint8), raw, np.array([0, 513], np.uint64))
+        out, _, olen, st2 = ctx.dtls_open([0], rec, np.array([0, 537], np.uint64))
+        res.append(bool(st[0] == 0 and st2[0] == 0 and np.array_equal(out[13:513], raw[13:])))
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(8)]
+    [t.start() for t in ts]; [t.join() for t in ts]
+    assert res == [True] * 8
