@@ -216,6 +216,24 @@ int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const 
                                           uint32_t max_msgs, uint8_t* msg, uint64_t msg_cap, uint64_t* msg_off,
                                           uint32_t* msg_first, uint8_t* msg_status, uint32_t* n_msgs_out);
 
+/* ---- DTLS record-layer bookkeeping (webrtc-dtls 0.10.0, un-vendored) ------------
+ * unpack_datagram: a UDP datagram carries one or more records back to back (13-byte header + length).
+ * rec_off[j] = byte offset of record j inside buf, rec_dgram[j] = its datagram; a record ends where the next
+ * one of the same datagram starts, or at the end of its datagram.  A datagram with a truncated record is
+ * dropped whole (dgram_status = BAD_HEADER), like ErrInvalidPacketLength in the reference.
+ * max_records sizes rec_off (max_records + 1 entries) and rec_dgram. */
+int32_t p2pt_dtls_datagram_split_batch(p2pt_ctx* ctx, uint64_t n_dgrams, const uint8_t* buf, const uint64_t* dgram_off,
+                                       uint64_t max_records, uint64_t* rec_off, uint32_t* rec_dgram,
+                                       uint8_t* dgram_status, uint32_t* n_records_out);
+/* Anti-replay sliding window (replaydetector SlidingWindowDetector, 64 entries), one state per session:
+ * latest / mask / started are arrays of n_sessions entries that the caller keeps between batches (host
+ * arrays here).  Records are judged in arrival order within their session: accept[i] = 1 if the record
+ * is neither older than the window nor a duplicate AND authentic[i] != 0 (authentic may be NULL = all);
+ * only accepted records advance the window, exactly as check() / accept() do around the AEAD open. */
+int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, const uint64_t* seq48,
+                                      const uint8_t* authentic, uint32_t n_sessions,
+                                      uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept);
+
 /* ---- device-pointer variants: same arguments, all pointers are device pointers, `stream` is a
  *      cudaStream_t.  They enqueue on `stream` and return without synchronising. -------------- */
 int32_t p2pt_frame_encode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* types, const uint32_t* sids,
@@ -274,6 +292,16 @@ int32_t p2pt_sctp_reassemble_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const 
                                           uint32_t max_msgs, uint8_t* msg, uint64_t msg_cap, uint64_t* msg_off,
                                           uint32_t* msg_first, uint8_t* msg_status, uint32_t* n_msgs_out,
                                           void* scratch, uint64_t scratch_bytes, void* stream);
+uint64_t p2pt_dtls_datagram_split_scratch_bytes(uint64_t n_dgrams);
+int32_t p2pt_dtls_datagram_split_batch_device(p2pt_ctx* ctx, uint64_t n_dgrams, const uint8_t* buf, const uint64_t* dgram_off,
+                                              uint64_t max_records, uint64_t* rec_off, uint32_t* rec_dgram,
+                                              uint8_t* dgram_status, uint32_t* n_records_out,
+                                              void* scratch, uint64_t scratch_bytes, void* stream);
+uint64_t p2pt_dtls_replay_filter_scratch_bytes(uint64_t n);
+int32_t p2pt_dtls_replay_filter_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, const uint64_t* seq48,
+                                             const uint8_t* authentic, uint32_t n_sessions,
+                                             uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept,
+                                             void* scratch, uint64_t scratch_bytes, void* stream);
 int32_t p2pt_dtls_gcm_seal_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
                                         const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
                                         uint8_t* rec, const uint64_t* rec_off, uint8_t* status, void* stream);

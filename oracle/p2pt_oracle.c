@@ -509,3 +509,52 @@ int orc_sctp_unpack(const uint8_t* pkt, uint64_t len, uint32_t headroom, orc_sct
     *pay_len = clen - 16;
     return ORC_OK;
 }
+
+/* ------------------------------------------------------------------------------------------ */
+/* DTLS record-layer bookkeeping: datagram -> records, anti-replay window. */
+/* webrtc-dtls 0.10.0 (un-vendored): record_layer/mod.rs unpack_datagram, and the replaydetector */
+/* crate's SlidingWindowDetector (window 64) used from conn.rs handle_incoming_packet.           */
+/* ------------------------------------------------------------------------------------------ */
+
+/* unpack_datagram: records are 13 + length bytes each; a datagram with a truncated record is
+ * rejected as a whole (ErrInvalidPacketLength).  Returns the number of records, or -1. */
+int64_t orc_dtls_datagram_split(const uint8_t* d, uint64_t len, uint64_t* rec_off /* cap entries */, uint64_t cap) {
+    uint64_t off = 0, k = 0;
+    while (off < len) {
+        if (len - off < 13) return -1;
+        uint64_t plen = 13 + (((uint64_t)d[off + 11] << 8) | d[off + 12]);
+        if (off + plen > len) return -1;
+        if (k < cap) rec_off[k] = off;
+        k++;
+        off += plen;
+    }
+    return (int64_t)k;
+}
+
+/* SlidingWindowDetector, one (latest, mask, started) triple per session; records are visited in
+ * arrival order.  check() happens before decryption, accept() only for records that authenticated
+ * (authentic[i] != 0).  accept_out[i] = 1 if the record is delivered. */
+void orc_replay_filter(uint64_t n, const uint32_t* session, const uint64_t* seq48, const uint8_t* authentic,
+                       uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept_out) {
+    const uint64_t WINDOW = 64, MAXSEQ = (1ull << 48) - 1;
+    for (uint64_t i = 0; i < n; i++) {
+        uint32_t s = session[i];
+        uint64_t q = seq48[i];
+        int ok = 1;
+        if (q > MAXSEQ) ok = 0;
+        else if (started[s] && q <= latest[s]) {
+            if (latest[s] >= WINDOW + q) ok = 0;                         /* too old */
+            else if ((mask[s] >> (latest[s] - q)) & 1) ok = 0;           /* duplicate */
+        }
+        if (ok && authentic[i]) {                                        /* accept() */
+            if (!started[s]) { started[s] = 1; latest[s] = q; mask[s] = 1; }
+            else if (q > latest[s]) {
+                uint64_t sh = q - latest[s];
+                mask[s] = sh >= 64 ? 0 : mask[s] << sh;
+                latest[s] = q;
+                mask[s] |= 1;
+            } else mask[s] |= 1ull << (latest[s] - q);
+            accept_out[i] = 1;
+        } else accept_out[i] = 0;
+    }
+}

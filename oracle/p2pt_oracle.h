@@ -116,6 +116,11 @@ uint64_t orc_sctp_packetize(const uint8_t* msg, uint64_t len, uint16_t src_port,
 int orc_sctp_unpack(const uint8_t* pkt, uint64_t len, uint32_t headroom, orc_sctp_chunk* info,
                     uint64_t* pay_off, uint32_t* pay_len);
 
+/* ---- DTLS record-layer bookkeeping (8(f) row 3; webrtc-dtls unpack_datagram, replaydetector) ---- */
+int64_t orc_dtls_datagram_split(const uint8_t* d, uint64_t len, uint64_t* rec_off, uint64_t cap);
+void orc_replay_filter(uint64_t n, const uint32_t* session, const uint64_t* seq48, const uint8_t* authentic,
+                       uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept_out);
+
 #ifdef __cplusplus
 }
 #endif

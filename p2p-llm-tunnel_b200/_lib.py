@@ -52,6 +52,12 @@ SIGNATURES = {
     "p2pt_sctp_unpack_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u32, _vp, _vp, _vp]),
     "p2pt_sctp_reassemble_scratch_bytes": (_u64, [_u64]),
     "p2pt_sctp_reassemble_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _u32, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
+    "p2pt_dtls_datagram_split_batch": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
+    "p2pt_dtls_replay_filter_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp]),
+    "p2pt_dtls_datagram_split_scratch_bytes": (_u64, [_u64]),
+    "p2pt_dtls_datagram_split_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
+    "p2pt_dtls_replay_filter_scratch_bytes": (_u64, [_u64]),
+    "p2pt_dtls_replay_filter_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_frame_encode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_frame_decode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp]),
     "p2pt_frame_demux_scratch_bytes": (_u64, [_u64]),
@@ -356,3 +362,29 @@ class Context:
         m = nm.value
         return {"info": info, "n_msgs": m, "msg_off": msg_off[:m + 1].copy(), "msg": msg[:int(msg_off[m])].copy(),
                 "msg_first": first[:m].copy(), "msg_status": status[:m].copy()}
+
+    # ---- DTLS record-layer bookkeeping -------------------------------------------------------------------------
+    def dtls_datagram_split(self, buf, dgram_off, max_records=None):
+        buf = _as(buf, np.uint8); dgram_off = _as(dgram_off, np.uint64)
+        n = len(dgram_off) - 1
+        max_records = max(int(buf.size // 13) + 1, 1) if max_records is None else max_records
+        rec_off = np.zeros(max_records + 1, np.uint64); rec_dgram = np.zeros(max_records + 1, np.uint32)
+        status = np.zeros(max(n, 1), np.uint8); nr = _u32(0)
+        self._check(self.lib.p2pt_dtls_datagram_split_batch(self.h, n, buf.ctypes.data, dgram_off.ctypes.data, max_records,
+                                                            rec_off.ctypes.data, rec_dgram.ctypes.data, status.ctypes.data,
+                                                            C.addressof(nr)))
+        k = nr.value
+        return rec_off[:k + 1].copy(), rec_dgram[:k].copy(), status[:n].copy()
+
+    def dtls_replay_filter(self, session, seq48, state, authentic=None):
+        """state = dict(latest=u64[S], mask=u64[S], started=u8[S]) updated in place; returns accept[n]"""
+        session = _as(session, np.uint32); seq48 = _as(seq48, np.uint64)
+        n = len(session)
+        accept = np.zeros(max(n, 1), np.uint8)
+        if authentic is not None:
+            authentic = _as(authentic, np.uint8)
+        S = len(state["latest"])
+        self._check(self.lib.p2pt_dtls_replay_filter_batch(self.h, n, session.ctypes.data, seq48.ctypes.data, _ptr(authentic), S,
+                                                           state["latest"].ctypes.data, state["mask"].ctypes.data,
+                                                           state["started"].ctypes.data, accept.ctypes.data))
+        return accept[:n]

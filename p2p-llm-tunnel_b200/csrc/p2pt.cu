@@ -18,6 +18,7 @@
 #include "frame_kernels.cuh"
 #include "gcm_kernels.cuh"
 #include "sctp_kernels.cuh"
+#include "dtls_state_kernels.cuh"
 
 using namespace p2pt;
 
@@ -1071,6 +1072,156 @@ int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const 
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     if (msg_off[nm] > msg_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_unpack_reassemble: msg_cap too small");
     if (msg_off[nm]) CUDA_TRY(ctx, cudaMemcpyAsync(msg, d_msg, msg_off[nm], cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return P2PT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// DTLS record-layer bookkeeping
+// ---------------------------------------------------------------------------------------------------
+uint64_t p2pt_dtls_datagram_split_scratch_bytes(uint64_t n) {
+    const uint64_t nn = n ? n : 1;
+    return align256(4 * nn) + align256(4 * (demux_scan_blocks(nn) + 2)) + 256;
+}
+
+int32_t p2pt_dtls_datagram_split_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* buf, const uint64_t* dgram_off,
+                                              uint64_t max_records, uint64_t* rec_off, uint32_t* rec_dgram,
+                                              uint8_t* dgram_status, uint32_t* n_records_out,
+                                              void* scratch, uint64_t scratch_bytes, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!rec_off || !rec_dgram || !n_records_out) return set_err(ctx, P2PT_ERR_ARG, "datagram_split: null output");
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) { CUDA_TRY(ctx, cudaMemsetAsync(n_records_out, 0, 4, st)); return P2PT_OK; }
+    if (!buf || !dgram_off || !dgram_status || !scratch) return set_err(ctx, P2PT_ERR_ARG, "datagram_split: null argument");
+    if (scratch_bytes < p2pt_dtls_datagram_split_scratch_bytes(n)) return set_err(ctx, P2PT_ERR_CAPACITY, "datagram_split: scratch too small");
+    uint32_t* count = (uint32_t*)scratch;
+    uint32_t* blk = (uint32_t*)((uint8_t*)scratch + align256(4 * n));
+    const u64 nblk = demux_scan_blocks(n);
+    dgram_count_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, buf, (const u64*)dgram_off, count, dgram_status, blk);
+    u32_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, blk);
+    dgram_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, nblk, buf, (const u64*)dgram_off, count, blk, max_records,
+                                                              (u64*)rec_off, rec_dgram, n_records_out);
+    count_launch(ctx, 3);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+namespace {
+struct ReplayScratch { p2pt_desc* desc; uint32_t* uniq; uint64_t* csr; uint32_t* perm; uint32_t* k; uint8_t* demux; uint64_t demux_bytes; uint64_t total; };
+ReplayScratch replay_carve(void* base, uint64_t n) {
+    ReplayScratch r;
+    uint8_t* p = (uint8_t*)base;
+    const uint64_t nn = n ? n : 1;
+    r.desc = (p2pt_desc*)p; p += align256(24 * nn);
+    r.uniq = (uint32_t*)p; p += align256(4 * (nn + 1));
+    r.csr = (uint64_t*)p; p += align256(8 * (nn + 1));
+    r.perm = (uint32_t*)p; p += align256(4 * nn);
+    r.k = (uint32_t*)p; p += 256;
+    r.demux = p; r.demux_bytes = demux_scratch_bytes(nn); p += align256(r.demux_bytes);
+    r.total = (uint64_t)(p - (uint8_t*)base);
+    return r;
+}
+}  // namespace
+
+uint64_t p2pt_dtls_replay_filter_scratch_bytes(uint64_t n) { return replay_carve(nullptr, n).total; }
+
+int32_t p2pt_dtls_replay_filter_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, const uint64_t* seq48,
+                                             const uint8_t* authentic, uint32_t n_sessions,
+                                             uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept,
+                                             void* scratch, uint64_t scratch_bytes, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !seq48 || !latest || !mask || !started || !accept || !scratch)
+        return set_err(ctx, P2PT_ERR_ARG, "replay_filter: null argument");
+    if (n > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "replay_filter: n must fit in 32 bits");
+    if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "replay_filter: scratch must be 256-byte aligned");
+    ReplayScratch r = replay_carve(scratch, n);
+    if (scratch_bytes < r.total) return set_err(ctx, P2PT_ERR_CAPACITY, "replay_filter: scratch too small");
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    replay_keys_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, session, r.desc);
+    // group the records by session, arrival order kept inside a session (the stable demux, key = session)
+    if (int32_t rc = p2pt_frame_demux_batch_device(ctx, n, r.desc, nullptr, nullptr, (uint32_t)n, r.uniq, nullptr, r.csr, r.perm,
+                                                   r.k, nullptr, 0, nullptr, r.demux, r.demux_bytes, st)) return rc;
+    replay_walk_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(r.k, r.uniq, (const u64*)r.csr, r.perm, (const u64*)seq48,
+                                                                authentic, n_sessions, (u64*)latest, (u64*)mask, started, accept);
+    count_launch(ctx, 2);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+int32_t p2pt_dtls_datagram_split_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* buf, const uint64_t* dgram_off,
+                                       uint64_t max_records, uint64_t* rec_off, uint32_t* rec_dgram,
+                                       uint8_t* dgram_status, uint32_t* n_records_out) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!rec_off || !rec_dgram || !n_records_out) return set_err(ctx, P2PT_ERR_ARG, "datagram_split: null output");
+    if (n == 0) { *n_records_out = 0; return P2PT_OK; }
+    if (!buf || !dgram_off || !dgram_status) return set_err(ctx, P2PT_ERR_ARG, "datagram_split: null argument");
+    if (!offsets_monotonic(dgram_off, n)) return set_err(ctx, P2PT_ERR_ARG, "datagram_split: offsets must be non-decreasing");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = ctx->streams[0];
+    const size_t bytes = dgram_off[n] - dgram_off[0];
+    const uint64_t sb = p2pt_dtls_datagram_split_scratch_bytes(n);
+    if (int32_t r = arena_reserve(ctx, pad256(bytes) + pad256(8 * (n + 1)) + pad256(8 * (max_records + 1)) + pad256(4 * max_records) +
+                                           pad256(n) + 256 + pad256(sb) + 8192)) return r;
+    uint8_t* d_buf = arena_take<uint8_t>(ctx, bytes + 1);
+    uint64_t* d_off = arena_take<uint64_t>(ctx, n + 1);
+    uint64_t* d_roff = arena_take<uint64_t>(ctx, max_records + 1);
+    uint32_t* d_rd = arena_take<uint32_t>(ctx, max_records + 1);
+    uint8_t* d_st = arena_take<uint8_t>(ctx, n);
+    uint32_t* d_n = arena_take<uint32_t>(ctx, 1);
+    uint8_t* d_scr = arena_take<uint8_t>(ctx, sb);
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_buf, buf + dgram_off[0], bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_off, dgram_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_dtls_datagram_split_batch_device(ctx, n, d_buf - dgram_off[0], d_off, max_records, d_roff, d_rd, d_st, d_n,
+                                                          d_scr, sb, st)) return r;
+    uint32_t total = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&total, d_n, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(dgram_status, d_st, n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    *n_records_out = total;
+    if (total > max_records) return set_err(ctx, P2PT_ERR_CAPACITY, "datagram_split: more records than max_records");
+    CUDA_TRY(ctx, cudaMemcpyAsync(rec_off, d_roff, 8 * ((size_t)total + 1), cudaMemcpyDeviceToHost, st));
+    if (total) CUDA_TRY(ctx, cudaMemcpyAsync(rec_dgram, d_rd, 4 * (size_t)total, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return P2PT_OK;
+}
+
+int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, const uint64_t* seq48,
+                                      const uint8_t* authentic, uint32_t n_sessions,
+                                      uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !seq48 || !latest || !mask || !started || !accept || !n_sessions)
+        return set_err(ctx, P2PT_ERR_ARG, "replay_filter: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = ctx->streams[0];
+    const uint64_t sb = p2pt_dtls_replay_filter_scratch_bytes(n);
+    const size_t S = n_sessions;
+    if (int32_t r = arena_reserve(ctx, pad256(4 * n) + pad256(8 * n) + 2 * pad256(n) + 2 * pad256(8 * S) + pad256(S) + pad256(sb) + 8192)) return r;
+    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
+    uint64_t* d_seq = arena_take<uint64_t>(ctx, n);
+    uint8_t* d_auth = arena_take<uint8_t>(ctx, n);
+    uint8_t* d_acc = arena_take<uint8_t>(ctx, n);
+    uint64_t* d_lat = arena_take<uint64_t>(ctx, S);
+    uint64_t* d_mask = arena_take<uint64_t>(ctx, S);
+    uint8_t* d_started = arena_take<uint8_t>(ctx, S);
+    uint8_t* d_scr = arena_take<uint8_t>(ctx, sb);
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_seq, seq48, 8 * n, cudaMemcpyHostToDevice, st));
+    if (authentic) CUDA_TRY(ctx, cudaMemcpyAsync(d_auth, authentic, n, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_lat, latest, 8 * S, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_mask, mask, 8 * S, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_started, started, S, cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_dtls_replay_filter_batch_device(ctx, n, d_sess, d_seq, authentic ? d_auth : nullptr, n_sessions,
+                                                         d_lat, d_mask, d_started, d_acc, d_scr, sb, st)) return r;
+    CUDA_TRY(ctx, cudaMemcpyAsync(accept, d_acc, n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(latest, d_lat, 8 * S, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(mask, d_mask, 8 * S, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(started, d_started, S, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     return P2PT_OK;
 }

@@ -175,3 +175,27 @@ def sctp_unpack(buf, in_off, headroom=0):
         lib().orc_sctp_unpack(C.c_void_p(buf.ctypes.data + a), C.c_uint64(b - a), C.c_uint32(headroom), _p(one), C.byref(o), C.byref(ln))
         info[i] = one[0]; po[i] = a + o.value; pl[i] = ln.value
     return info, po, pl
+
+
+def dtls_datagram_split(buf, dgram_off):
+    buf = _u8(buf); dgram_off = np.ascontiguousarray(dgram_off, np.uint64)
+    lib().orc_dtls_datagram_split.restype = C.c_int64
+    offs, dg, status = [], [], []
+    for i in range(len(dgram_off) - 1):
+        a, b = int(dgram_off[i]), int(dgram_off[i + 1])
+        tmp = np.zeros(max((b - a) // 13 + 1, 1), np.uint64)
+        k = lib().orc_dtls_datagram_split(C.c_void_p(buf.ctypes.data + a), C.c_uint64(b - a), _p(tmp), C.c_uint64(len(tmp)))
+        status.append(6 if k < 0 else 0)
+        for j in range(max(k, 0)):
+            offs.append(a + int(tmp[j])); dg.append(i)
+    return np.array(offs + [int(dgram_off[-1])], np.uint64), np.array(dg, np.uint32), np.array(status, np.uint8)
+
+
+def replay_filter(session, seq48, state, authentic=None):
+    session = np.ascontiguousarray(session, np.uint32); seq48 = np.ascontiguousarray(seq48, np.uint64)
+    n = len(session)
+    auth = np.ones(n, np.uint8) if authentic is None else np.ascontiguousarray(authentic, np.uint8)
+    accept = np.zeros(max(n, 1), np.uint8)
+    lib().orc_replay_filter(C.c_uint64(n), _p(session), _p(seq48), _p(auth), _p(state["latest"]), _p(state["mask"]),
+                            _p(state["started"]), _p(accept))
+    return accept[:n]

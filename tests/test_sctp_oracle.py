@@ -49,3 +49,24 @@ def test_unpack_error_statuses_and_dtls_headroom():
     bad = pk.copy(); bad[13 + 30] ^= 1
     assert ob.sctp_unpack(bad, off, headroom=13)[0]["status"][0] == 7
     assert ob.sctp_unpack(pk[:20], np.array([0, 20], np.uint64), headroom=13)[0]["status"][0] == 8
+
+
+def test_replay_window_oracle_semantics():
+    """SlidingWindowDetector (window 64): duplicates and records 64 or more behind the newest are dropped;
+    only authenticated records move the window."""
+    st = {"latest": np.zeros(1, np.uint64), "mask": np.zeros(1, np.uint64), "started": np.zeros(1, np.uint8)}
+    seqs = [0, 1, 1, 3, 2, 2, 100, 37, 36, 100, 99, 163, 100, 99, 164]
+    auth = [1, 1, 1, 1, 1, 1, 1,   1,  1,  1,   1,  0,   1,   1,  1]
+    got = ob.replay_filter(np.zeros(len(seqs), np.uint32), np.array(seqs, np.uint64), st, np.array(auth, np.uint8))
+    #        0  1  dup 3  2  dup 100 37(63 behind: ok) 36(64 behind: old) dup 99 163(not authentic) dup dup 164
+    assert list(got) == [1, 1, 0, 1, 1, 0, 1, 1, 0, 0, 1, 0, 0, 0, 1]
+    assert st["latest"][0] == 164
+
+
+def test_datagram_split_oracle():
+    r1 = bytes([23, 0xFE, 0xFD]) + bytes(8) + (5).to_bytes(2, "big") + b"hello"
+    r2 = bytes([22, 0xFE, 0xFD]) + bytes(8) + (0).to_bytes(2, "big")
+    buf = np.frombuffer(r1 + r2 + r1[:-1], np.uint8)
+    off = np.array([0, len(r1) + len(r2), len(buf)], np.uint64)
+    ro, rd, st = ob.dtls_datagram_split(buf, off)
+    assert list(st) == [0, 6] and list(rd) == [0, 0] and list(ro) == [0, len(r1), len(buf)]
