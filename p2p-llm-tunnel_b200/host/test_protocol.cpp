@@ -1,0 +1,143 @@
+// test_protocol.cpp -- the reference's own unit tests for the codec
+// (/root/reference/tunnel/src/protocol.rs:265-460), restated one for one against the C++ host mirror, plus the
+// DTLS record example of SURVEY.md App. A.2.  Needs a B200: every encode / decode runs on the GPU.
+// Build + run: tests/test_gpu_host_cpp.py (pytest -m gpu).
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+
+#include "p2pt_host.hpp"
+
+using namespace p2pt_host;
+using namespace p2pt_host::protocol;
+
+static int g_failed = 0, g_run = 0;
+#define CHECK(cond)                                                                      \
+    do { if (!(cond)) { std::printf("  CHECK failed: %s (%s:%d)\n", #cond, __FILE__, __LINE__); g_failed++; } } while (0)
+#define TEST(name) static void name(const Context& c); \
+    static struct name##_reg { name##_reg() { tests().push_back({#name, name}); } } name##_inst; \
+    static void name([[maybe_unused]] const Context& c)
+struct T { const char* n; void (*f)(const Context&); };
+static std::vector<T>& tests() { static std::vector<T> v; return v; }
+static Bytes B(const std::string& s) { return Bytes(s.begin(), s.end()); }
+static bool throws_with(const Context& c, const Bytes& b, const char* what) {
+    try { TunnelMessage::decode(c, b); } catch (const Error& e) { return std::string(e.what()).find(what) != std::string::npos; }
+    return false;
+}
+
+// --- Encode/Decode roundtrip tests (protocol.rs:271-388) ---
+TEST(test_roundtrip_hello) {
+    auto enc = TunnelMessage::hello(R"({"proto":"httptunnel","min_version":1,"max_version":1,"features":["sse"]})").encode(c);
+    auto d = TunnelMessage::decode(c, enc);
+    CHECK(d.msg_type == MessageType::Hello); CHECK(d.stream_id == 0);
+    CHECK(std::string(d.payload.begin(), d.payload.end()).find("\"proto\":\"httptunnel\"") != std::string::npos);
+}
+TEST(test_roundtrip_agree) {
+    auto d = TunnelMessage::decode(c, TunnelMessage::agree(R"({"version":1,"features":["sse"]})").encode(c));
+    CHECK(d.msg_type == MessageType::Agree);
+}
+TEST(test_roundtrip_req_headers) {
+    auto d = TunnelMessage::decode(c, TunnelMessage::req_headers(42, R"({"stream_id":42,"method":"POST","path":"/v1/chat/completions","headers":{}})").encode(c));
+    CHECK(d.msg_type == MessageType::ReqHeaders); CHECK(d.stream_id == 42);
+}
+TEST(test_roundtrip_req_body) {
+    auto body = B("hello world");
+    auto d = TunnelMessage::decode(c, TunnelMessage::req_body(7, body).encode(c));
+    CHECK(d.msg_type == MessageType::ReqBody); CHECK(d.stream_id == 7); CHECK(d.payload == body);
+}
+TEST(test_roundtrip_req_end) {
+    auto d = TunnelMessage::decode(c, TunnelMessage::req_end(7).encode(c));
+    CHECK(d.msg_type == MessageType::ReqEnd); CHECK(d.stream_id == 7); CHECK(d.payload.empty());
+}
+TEST(test_roundtrip_res_headers) {
+    auto d = TunnelMessage::decode(c, TunnelMessage::res_headers(99, R"({"stream_id":99,"status":200,"headers":{}})").encode(c));
+    CHECK(d.msg_type == MessageType::ResHeaders); CHECK(d.stream_id == 99);
+}
+TEST(test_roundtrip_res_body) {
+    auto data = B("data: {\"token\": \"hello\"}\n\n");
+    auto d = TunnelMessage::decode(c, TunnelMessage::res_body(99, data).encode(c));
+    CHECK(d.msg_type == MessageType::ResBody); CHECK(d.stream_id == 99); CHECK(d.payload == data);
+}
+TEST(test_roundtrip_res_end) {
+    auto d = TunnelMessage::decode(c, TunnelMessage::res_end(99).encode(c));
+    CHECK(d.msg_type == MessageType::ResEnd); CHECK(d.stream_id == 99); CHECK(d.payload.empty());
+}
+TEST(test_roundtrip_error) {
+    auto d = TunnelMessage::decode(c, TunnelMessage::error(5, "upstream timeout").encode(c));
+    CHECK(d.msg_type == MessageType::Error); CHECK(d.stream_id == 5); CHECK(d.payload == B("upstream timeout"));
+}
+// --- Negative: corrupt/truncated messages (protocol.rs:392-422) ---
+TEST(test_decode_empty) { CHECK(throws_with(c, {}, "too short")); }
+TEST(test_decode_too_short) { CHECK(throws_with(c, {1, 0, 0}, "too short")); }
+TEST(test_decode_unknown_type) { CHECK(throws_with(c, {255, 0, 0, 0, 0}, "unknown message type")); }
+TEST(test_decode_exactly_header_no_payload) {
+    auto m = TunnelMessage::decode(c, {12, 0, 0, 0, 0});
+    CHECK(m.msg_type == MessageType::ReqEnd); CHECK(m.stream_id == 0); CHECK(m.payload.empty());
+}
+// --- Boundary: edge cases (protocol.rs:426-460) ---
+TEST(test_zero_stream_id) { CHECK(TunnelMessage::decode(c, TunnelMessage::req_end(0).encode(c)).stream_id == 0); }
+TEST(test_max_stream_id) { CHECK(TunnelMessage::decode(c, TunnelMessage::req_end(UINT32_MAX).encode(c)).stream_id == UINT32_MAX); }
+TEST(test_large_payload) {
+    Bytes data(MAX_BODY_CHUNK, 0xAB);
+    auto enc = TunnelMessage::res_body(1, data).encode(c);
+    CHECK(enc.size() == 5 + MAX_BODY_CHUNK);
+    auto d = TunnelMessage::decode(c, enc);
+    CHECK(d.payload.size() == MAX_BODY_CHUNK); CHECK(d.payload == data);
+}
+TEST(test_empty_payload_body) {
+    auto d = TunnelMessage::decode(c, TunnelMessage::res_body(1, {}).encode(c));
+    CHECK(d.msg_type == MessageType::ResBody); CHECK(d.payload.empty());
+}
+// --- not in the reference's tests: wire bytes, from_u8, the chunker, the batched encoder ---
+TEST(test_wire_bytes_and_from_u8) {
+    auto enc = TunnelMessage::res_body(0x01020304, B("ab")).encode(c);
+    CHECK((enc == Bytes{21, 1, 2, 3, 4, 'a', 'b'}));
+    int valid = 0;
+    for (int v = 0; v < 256; v++) valid += from_u8((uint8_t)v).has_value();
+    CHECK(valid == 11); CHECK(!from_u8(0).has_value()); CHECK(from_u8(99).value() == MessageType::Error);
+}
+TEST(test_chunker_and_batch) {
+    Bytes body(2 * MAX_BODY_CHUNK + 100);
+    for (size_t i = 0; i < body.size(); i++) body[i] = (uint8_t)(i * 7);
+    auto msgs = chunk_body(9, body);
+    CHECK(msgs.size() == 3); CHECK(msgs[2].payload.size() == 100);
+    std::vector<uint64_t> off;
+    auto frames = encode_batch(c, msgs, off);
+    CHECK(off.back() == body.size() + 15);
+    Bytes f1(frames.begin() + (ptrdiff_t)off[1], frames.begin() + (ptrdiff_t)off[2]);
+    auto d = TunnelMessage::decode(c, f1);
+    CHECK(d.stream_id == 9); CHECK(d.payload == msgs[1].payload);
+}
+// --- DTLS record: the worked example of SURVEY.md App. A.2 (computed with OpenSSL via `cryptography`) ---
+TEST(test_crypto_gcm_known_record) {
+    uint8_t key[16], iv[4] = {1, 2, 3, 4}, nonce[8];
+    for (int i = 0; i < 16; i++) key[i] = (uint8_t)i;
+    for (int i = 0; i < 8; i++) nonce[i] = (uint8_t)i;
+    dtls::CryptoGcm gcm(c, key, iv, key, iv);
+    auto frame = TunnelMessage::res_body(99, B("data: {\"token\": \"hello\"}\n\n")).encode(c);
+    Bytes raw = {23, 0xfe, 0xfd, 0, 1, 0, 0, 0, 0, 0, 7, 0, (uint8_t)frame.size()};
+    raw.insert(raw.end(), frame.begin(), frame.end());
+    auto rec = gcm.encrypt(raw, nonce);
+    const char* expect = "17fefd00010000000000070037000102030405060738c4bc820b39df30be70dd0aa3eff22646ed80547c0e10efc21ea0e482efc15b2c93b3e5915c58f5e5dca8810d2964";
+    std::string hex;
+    for (uint8_t b : rec) { char t[3]; std::snprintf(t, 3, "%02x", b); hex += t; }
+    CHECK(hex == expect);
+    auto plain = gcm.decrypt(rec);
+    CHECK(plain.size() == raw.size()); CHECK(Bytes(plain.begin() + 13, plain.end()) == frame);
+    rec.back() ^= 1;
+    bool failed = false;
+    try { gcm.decrypt(rec); } catch (const dtls::ErrDecrypt&) { failed = true; }
+    CHECK(failed);
+    bool noroom = false;
+    try { gcm.decrypt(Bytes(rec.begin(), rec.begin() + 20)); } catch (const dtls::ErrNotEnoughRoomForNonce&) { noroom = true; }
+    CHECK(noroom);
+}
+
+int main() {
+    try {
+        Context c(0);
+        for (auto& t : tests()) { int before = g_failed; t.f(c); g_run++; std::printf("%s %s\n", g_failed == before ? "ok  " : "FAIL", t.n); }
+    } catch (const std::exception& e) { std::printf("fatal: %s\n", e.what()); return 2; }
+    std::printf("%d tests, %d failed checks\n", g_run, g_failed);
+    return g_failed ? 1 : 0;
+}

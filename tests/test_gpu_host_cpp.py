@@ -1,0 +1,24 @@
+"""The C++ host mirror (p2p-llm-tunnel_b200/host/p2pt_host.hpp): the reference's codec unit tests
+(/root/reference/tunnel/src/protocol.rs:265-460) restated in C++ run against it on the GPU; on a box
+without a GPU the same binary must fail loudly instead of computing anything on the CPU."""
+import subprocess
+
+import pytest
+
+
+@pytest.mark.gpu
+def test_reference_codec_tests_in_cpp(built):
+    r = subprocess.run([built.HOST_TEST], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    print(r.stdout)
+    assert r.returncode == 0, r.stdout
+    assert "20 tests, 0 failed checks" in r.stdout
+    for name in ("test_roundtrip_res_body", "test_decode_unknown_type", "test_large_payload", "test_crypto_gcm_known_record"):
+        assert f"ok   {name}" in r.stdout
+
+
+def test_cpp_host_mirror_has_no_cpu_fallback(built):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    r = subprocess.run([built.HOST_TEST], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert r.returncode == 2 and "no CUDA device" in r.stdout
