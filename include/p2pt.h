@@ -234,6 +234,15 @@ int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t*
                                       const uint8_t* authentic, uint32_t n_sessions,
                                       uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept);
 
+/* ---- SSE event scan over per-stream bodies.  body / body_off[k + 1] are the
+ *      gathered / gathered_off outputs of the demux.  An event ends after every "\n\n" inside one stream:
+ *      ev_csr[k + 1] = running event count per stream, ev_end[j] = byte offset (into body) just past event j;
+ *      done[s] = 1 if some event of stream s begins with `data: [DONE]\n\n`
+ *      (/root/reference/tmp/mock_llm.py:68-69).  max_events sizes ev_end. */
+int32_t p2pt_sse_scan_batch(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, const uint64_t* body_off,
+                            uint64_t max_events, uint64_t* ev_csr, uint64_t* ev_end, uint8_t* done,
+                            uint64_t* n_events_out);
+
 /* ---- device-pointer variants: same arguments, all pointers are device pointers, `stream` is a
  *      cudaStream_t.  They enqueue on `stream` and return without synchronising. -------------- */
 int32_t p2pt_frame_encode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* types, const uint32_t* sids,
@@ -302,6 +311,10 @@ int32_t p2pt_dtls_replay_filter_batch_device(p2pt_ctx* ctx, uint64_t n, const ui
                                              const uint8_t* authentic, uint32_t n_sessions,
                                              uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept,
                                              void* scratch, uint64_t scratch_bytes, void* stream);
+uint64_t p2pt_sse_scan_scratch_bytes(uint64_t k);
+int32_t p2pt_sse_scan_batch_device(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, const uint64_t* body_off,
+                                   uint64_t max_events, uint64_t* ev_csr, uint64_t* ev_end, uint8_t* done,
+                                   uint64_t* n_events_out, void* scratch, uint64_t scratch_bytes, void* stream);
 int32_t p2pt_dtls_gcm_seal_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
                                         const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
                                         uint8_t* rec, const uint64_t* rec_off, uint8_t* status, void* stream);

@@ -558,3 +558,32 @@ void orc_replay_filter(uint64_t n, const uint32_t* session, const uint64_t* seq4
         } else accept_out[i] = 0;
     }
 }
+
+/* ------------------------------------------------------------------------------------------ */
+/* SSE scan over reassembled response bodies.  The reference forwards SSE */
+/* bytes untouched (feature flag "sse", /root/reference/tunnel/src/protocol.rs:36,68); the event  */
+/* framing is the upstream's: `data: {...}\n\n` ... `data: [DONE]\n\n`                            */
+/* (/root/reference/tmp/mock_llm.py:54, :68-69).  An event ends after every pair of consecutive   */
+/* line feeds inside one stream; done[s] says whether an event `data: [DONE]` starts an event.   */
+/* ------------------------------------------------------------------------------------------ */
+uint64_t orc_sse_scan(uint64_t k, const uint8_t* body, const uint64_t* body_off,
+                      uint64_t* ev_csr /* k+1 */, uint64_t* ev_end /* cap */, uint64_t cap, uint8_t* done /* k */) {
+    static const char DONE[] = "data: [DONE]\n\n";
+    uint64_t total = 0;
+    for (uint64_t s = 0; s < k; s++) {
+        uint64_t a = body_off[s], b = body_off[s + 1];
+        ev_csr[s] = total;
+        done[s] = 0;
+        uint64_t start = a;                       /* start of the current event */
+        for (uint64_t i = a; i < b; i++) {
+            if (i == start && b - i >= 14 && memcmp(body + i, DONE, 14) == 0) done[s] = 1;
+            if (i > a && body[i] == '\n' && body[i - 1] == '\n') {
+                if (total < cap) ev_end[total] = i + 1;
+                total++;
+                start = i + 1;
+            }
+        }
+    }
+    ev_csr[k] = total;
+    return total;
+}

@@ -121,6 +121,10 @@ int64_t orc_dtls_datagram_split(const uint8_t* d, uint64_t len, uint64_t* rec_of
 void orc_replay_filter(uint64_t n, const uint32_t* session, const uint64_t* seq48, const uint8_t* authentic,
                        uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept_out);
 
+/* ---- SSE event scan over per-stream bodies (8(f) row 4) ---- */
+uint64_t orc_sse_scan(uint64_t k, const uint8_t* body, const uint64_t* body_off,
+                      uint64_t* ev_csr, uint64_t* ev_end, uint64_t cap, uint8_t* done);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,6 +58,9 @@ SIGNATURES = {
     "p2pt_dtls_datagram_split_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_dtls_replay_filter_scratch_bytes": (_u64, [_u64]),
     "p2pt_dtls_replay_filter_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
+    "p2pt_sse_scan_batch": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
+    "p2pt_sse_scan_scratch_bytes": (_u64, [_u64]),
+    "p2pt_sse_scan_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_frame_encode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_frame_decode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp]),
     "p2pt_frame_demux_scratch_bytes": (_u64, [_u64]),
@@ -388,3 +391,14 @@ class Context:
                                                            state["latest"].ctypes.data, state["mask"].ctypes.data,
                                                            state["started"].ctypes.data, accept.ctypes.data))
         return accept[:n]
+
+    def sse_scan(self, body, body_off, max_events=None):
+        """per-stream bodies -> (ev_csr[k + 1], ev_end[n_events], done[k])"""
+        body = _as(body, np.uint8); body_off = _as(body_off, np.uint64)
+        k = len(body_off) - 1
+        max_events = max(int(body.size // 2) + 1, 1) if max_events is None else max_events
+        ev_csr = np.zeros(k + 1, np.uint64); ev_end = np.zeros(max_events + 1, np.uint64)
+        done = np.zeros(max(k, 1), np.uint8); total = _u64(0)
+        self._check(self.lib.p2pt_sse_scan_batch(self.h, k, body.ctypes.data, body_off.ctypes.data, max_events,
+                                                 ev_csr.ctypes.data, ev_end.ctypes.data, done.ctypes.data, C.addressof(total)))
+        return ev_csr, ev_end[:total.value].copy(), done[:k].copy()

@@ -19,6 +19,7 @@
 #include "gcm_kernels.cuh"
 #include "sctp_kernels.cuh"
 #include "dtls_state_kernels.cuh"
+#include "sse_kernels.cuh"
 
 using namespace p2pt;
 
@@ -1072,6 +1073,75 @@ int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const 
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     if (msg_off[nm] > msg_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_unpack_reassemble: msg_cap too small");
     if (msg_off[nm]) CUDA_TRY(ctx, cudaMemcpyAsync(msg, d_msg, msg_off[nm], cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return P2PT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// SSE event scan
+// ---------------------------------------------------------------------------------------------------
+uint64_t p2pt_sse_scan_scratch_bytes(uint64_t k) { return align256(8 * (demux_scan_blocks(k ? k : 1) + 2)) + 256; }
+
+int32_t p2pt_sse_scan_batch_device(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, const uint64_t* body_off,
+                                   uint64_t max_events, uint64_t* ev_csr, uint64_t* ev_end, uint8_t* done,
+                                   uint64_t* n_events_out, void* scratch, uint64_t scratch_bytes, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!ev_csr || !n_events_out) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: null output");
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (k == 0) {
+        CUDA_TRY(ctx, cudaMemsetAsync(n_events_out, 0, 8, st));
+        CUDA_TRY(ctx, cudaMemsetAsync(ev_csr, 0, 8, st));
+        return P2PT_OK;
+    }
+    if (!body_off || !ev_end || !done || !scratch) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: null argument");
+    if (scratch_bytes < p2pt_sse_scan_scratch_bytes(k)) return set_err(ctx, P2PT_ERR_CAPACITY, "sse_scan: scratch too small");
+    u64* blk = (u64*)scratch;
+    const u64 nblk = demux_scan_blocks(k);
+    const unsigned grid = grid_for(ctx, k, 8, 16);
+    sse_scan_kernel<false><<<grid, 256, 0, st>>>(k, body, (const u64*)body_off, (u64*)ev_csr, nullptr, 0, nullptr);
+    u64_scan_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(k, (const u64*)ev_csr, blk);
+    u64_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, blk);
+    u64_scan_apply_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(k, nblk, (u64*)ev_csr, blk, (u64*)n_events_out);
+    sse_scan_kernel<true><<<grid, 256, 0, st>>>(k, body, (const u64*)body_off, (u64*)ev_csr, (u64*)ev_end, max_events, done);
+    count_launch(ctx, 5);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
+int32_t p2pt_sse_scan_batch(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, const uint64_t* body_off,
+                            uint64_t max_events, uint64_t* ev_csr, uint64_t* ev_end, uint8_t* done,
+                            uint64_t* n_events_out) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!ev_csr || !n_events_out) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: null output");
+    if (k == 0) { *n_events_out = 0; ev_csr[0] = 0; return P2PT_OK; }
+    if (!body_off || !ev_end || !done) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: null argument");
+    if (!offsets_monotonic(body_off, k)) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: offsets must be non-decreasing");
+    const size_t bytes = body_off[k] - body_off[0];
+    if (bytes && !body) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: null body");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = ctx->streams[0];
+    const uint64_t sb = p2pt_sse_scan_scratch_bytes(k);
+    if (int32_t r = arena_reserve(ctx, pad256(bytes) + 2 * pad256(8 * (k + 1)) + pad256(8 * (max_events + 1)) + pad256(k) + 256 + pad256(sb) + 8192)) return r;
+    uint8_t* d_body = arena_take<uint8_t>(ctx, bytes + 1);
+    uint64_t* d_off = arena_take<uint64_t>(ctx, k + 1);
+    uint64_t* d_csr = arena_take<uint64_t>(ctx, k + 1);
+    uint64_t* d_end = arena_take<uint64_t>(ctx, max_events + 1);
+    uint8_t* d_done = arena_take<uint8_t>(ctx, k);
+    uint64_t* d_n = arena_take<uint64_t>(ctx, 1);
+    uint8_t* d_scr = arena_take<uint8_t>(ctx, sb);
+    if (bytes) CUDA_TRY(ctx, cudaMemcpyAsync(d_body, body + body_off[0], bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_off, body_off, 8 * (k + 1), cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_sse_scan_batch_device(ctx, k, d_body - body_off[0], d_off, max_events, d_csr, d_end, d_done, d_n, d_scr, sb, st)) return r;
+    uint64_t total = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&total, d_n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ev_csr, d_csr, 8 * (k + 1), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(done, d_done, k, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    *n_events_out = total;
+    if (total > max_events) return set_err(ctx, P2PT_ERR_CAPACITY, "sse_scan: more events than max_events");
+    if (total) CUDA_TRY(ctx, cudaMemcpyAsync(ev_end, d_end, 8 * total, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     return P2PT_OK;
 }

@@ -1,0 +1,117 @@
+// sse_kernels.cuh -- SSE event scan over the per-stream bodies the demux gathered.
+// The tunnel forwards server-sent events untouched ("sse" feature, /root/reference/tunnel/src/protocol.rs:36,68);
+// the framing is the upstream's: `data: {...}\n\n` ... `data: [DONE]\n\n` (/root/reference/tmp/mock_llm.py:54,68-69).
+// One warp per stream walks the body in 512-byte rows (aligned 16-byte loads, bytes outside the stream read
+// as zero), marks every position that closes a "\n\n" pair, and either counts them (pass 1) or writes the
+// event end offsets in order (pass 2).  HBM-bound: every body byte is read once per pass.
+#pragma once
+#include "frame_kernels.cuh"
+
+namespace p2pt {
+
+// bit b of the result: byte b of v is '\n' and the byte before it (prev for b = 0) is '\n' too
+__device__ __forceinline__ uint32_t lf_pairs16(const uint4& v, uint32_t prev_byte) {
+    uint32_t m = 0;
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t p = prev_byte;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const uint32_t c = (w[i >> 2] >> (8 * (i & 3))) & 0xffu;
+        m |= (uint32_t)(c == 10u && p == 10u) << i;
+        p = c;
+    }
+    return m;
+}
+
+template <bool EMIT>
+__global__ void __launch_bounds__(256) sse_scan_kernel(u64 k, const uint8_t* __restrict__ body, const u64* __restrict__ body_off,
+                                                      u64* __restrict__ ev_csr, u64* __restrict__ ev_end, u64 cap,
+                                                      uint8_t* __restrict__ done) {
+    const int lane = threadIdx.x & 31;
+    const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
+    for (u64 s = warp; s < k; s += nwarps) {
+        const u64 a = __ldg(body_off + s), b = __ldg(body_off + s + 1);
+        const uint8_t* lo = body + a; const uint8_t* hi = body + b;
+        u64 count = 0;
+        const u64 out0 = EMIT ? ev_csr[s] : 0;
+        uint32_t carry = 0;                                   // last byte of the previous row (0 at the stream start)
+        bool is_done = false;
+        if (EMIT && lane == 0 && b - a >= 14) {               // an event starts at the stream start
+            const char* D = "data: [DONE]\n\n";
+            bool eq = true;
+            for (int q = 0; q < 14; q++) eq &= (__ldg(lo + q) == (uint8_t)D[q]);
+            is_done = eq;
+        }
+        for (u64 row = a; row < b; row += 512) {
+            const uint8_t* p = body + row + 16 * lane;
+            const uint4 v = (p < hi) ? load16_bounded(p, lo, hi) : make_uint4(0, 0, 0, 0);
+            uint32_t prev = __shfl_up_sync(0xffffffffu, v.w >> 24, 1);
+            if (lane == 0) prev = carry;
+            carry = __shfl_sync(0xffffffffu, v.w >> 24, 31);
+            const uint32_t m = lf_pairs16(v, prev);
+            const uint32_t c = __popc(m);
+            uint32_t incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+            if (EMIT) {
+                u64 slot = out0 + count + (incl - c);
+                uint32_t mm = m;
+                while (mm) {
+                    const int bit = __ffs(mm) - 1; mm &= mm - 1;
+                    const u64 end = row + 16 * lane + bit + 1;            // offset just past the second '\n'
+                    if (slot < cap) ev_end[slot] = end;
+                    slot++;
+                    if (b - end >= 14) {                                   // does the next event read `data: [DONE]`?
+                        const char* D = "data: [DONE]\n\n";
+                        bool eq = true;
+                        for (int q = 0; q < 14; q++) eq &= (__ldg(body + end + q) == (uint8_t)D[q]);
+                        is_done |= eq;
+                    }
+                }
+            }
+            count += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (!EMIT) { if (lane == 0) ev_csr[s] = count; }       // per-stream counts, scanned afterwards
+        else {
+            const bool any = __any_sync(0xffffffffu, is_done);
+            if (lane == 0) done[s] = any ? 1 : 0;
+        }
+    }
+}
+
+// exclusive scan of k u64 counts in place (k + 1 entries out): block sums -> single block scan -> add
+__global__ void __launch_bounds__(kScanThreads) u64_scan_blocksum_kernel(u64 k, const u64* __restrict__ v, u64* __restrict__ blk) {
+    const u64 i = (u64)blockIdx.x * kScanThreads + threadIdx.x;
+    HeadBytes x; x.heads = 0; x.bytes = i < k ? v[i] : 0;
+    HeadBytes tot;
+    (void)block_scan_excl(x, tot);
+    if (threadIdx.x == 0) blk[blockIdx.x] = tot.bytes;
+}
+__global__ void __launch_bounds__(kScanThreads) u64_scan_blocksums_kernel(u64 nblk, u64* __restrict__ blk) {
+    __shared__ u64 carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (u64 b0 = 0; b0 < nblk; b0 += kScanThreads) {
+        const u64 b = b0 + threadIdx.x;
+        HeadBytes x; x.heads = 0; x.bytes = b < nblk ? blk[b] : 0;
+        HeadBytes tot;
+        HeadBytes ex = block_scan_excl(x, tot);
+        const u64 c = carry;
+        if (b < nblk) blk[b] = c + ex.bytes;
+        __syncthreads();
+        if (threadIdx.x == 0) carry = c + tot.bytes;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) blk[nblk] = carry;
+}
+__global__ void __launch_bounds__(kScanThreads) u64_scan_apply_kernel(u64 k, u64 nblk, u64* __restrict__ v, const u64* __restrict__ blk,
+                                                                     u64* __restrict__ total_out) {
+    const u64 i = (u64)blockIdx.x * kScanThreads + threadIdx.x;
+    HeadBytes x; x.heads = 0; x.bytes = i < k ? v[i] : 0;
+    HeadBytes tot;
+    HeadBytes ex = block_scan_excl(x, tot);
+    if (i < k) v[i] = blk[blockIdx.x] + ex.bytes;
+    if (i == 0) { v[k] = blk[nblk]; *total_out = blk[nblk]; }
+}
+
+}  // namespace p2pt

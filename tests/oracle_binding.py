@@ -199,3 +199,13 @@ def replay_filter(session, seq48, state, authentic=None):
     lib().orc_replay_filter(C.c_uint64(n), _p(session), _p(seq48), _p(auth), _p(state["latest"]), _p(state["mask"]),
                             _p(state["started"]), _p(accept))
     return accept[:n]
+
+
+def sse_scan(body, body_off):
+    body = _u8(body); body_off = np.ascontiguousarray(body_off, np.uint64)
+    k = len(body_off) - 1
+    lib().orc_sse_scan.restype = C.c_uint64
+    cap = int(body.size // 2) + 1
+    ev_csr = np.zeros(k + 1, np.uint64); ev_end = np.zeros(cap, np.uint64); done = np.zeros(max(k, 1), np.uint8)
+    total = lib().orc_sse_scan(C.c_uint64(k), _p(body), _p(body_off), _p(ev_csr), _p(ev_end), C.c_uint64(cap), _p(done))
+    return ev_csr, ev_end[:total].copy(), done[:k].copy()

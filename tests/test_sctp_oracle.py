@@ -70,3 +70,12 @@ def test_datagram_split_oracle():
     off = np.array([0, len(r1) + len(r2), len(buf)], np.uint64)
     ro, rd, st = ob.dtls_datagram_split(buf, off)
     assert list(st) == [0, 6] and list(rd) == [0, 0] and list(ro) == [0, len(r1), len(buf)]
+
+
+def test_sse_scan_oracle():
+    streams = [b"data: a\n\ndata: b\n\n", b"", b"\n", b"data: [DONE]\n\n", b"x\n\n\ndata: [DONE]\n\nrest"]
+    body = np.frombuffer(b"".join(streams), np.uint8)
+    off = np.concatenate([[0], np.cumsum([len(s) for s in streams])]).astype(np.uint64)
+    csr, ends, done = ob.sse_scan(body, off)
+    assert list(csr) == [0, 2, 2, 2, 3, 6] and list(done) == [0, 0, 0, 1, 1]
+    assert list(ends[:2]) == [9, 18]
