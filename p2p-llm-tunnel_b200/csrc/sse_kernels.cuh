@@ -9,18 +9,17 @@
 
 namespace p2pt {
 
+// 4-bit mask of the bytes of w that equal '\n' (SWAR zero-byte test on w ^ 0x0a0a0a0a, exact per byte;
+// the multiply gathers the four flag bits into one nibble)
+__device__ __forceinline__ uint32_t lf_nibble(uint32_t w) {
+    const uint32_t x = w ^ 0x0a0a0a0au;
+    const uint32_t t = ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu);      // 0x80 in every byte that was '\n'
+    return ((t >> 7) * 0x01020408u) >> 24;                                          // bits 0..3 = bytes 0..3
+}
 // bit b of the result: byte b of v is '\n' and the byte before it (prev for b = 0) is '\n' too
 __device__ __forceinline__ uint32_t lf_pairs16(const uint4& v, uint32_t prev_byte) {
-    uint32_t m = 0;
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-    uint32_t p = prev_byte;
-#pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const uint32_t c = (w[i >> 2] >> (8 * (i & 3))) & 0xffu;
-        m |= (uint32_t)(c == 10u && p == 10u) << i;
-        p = c;
-    }
-    return m;
+    const uint32_t m = lf_nibble(v.x) | (lf_nibble(v.y) << 4) | (lf_nibble(v.z) << 8) | (lf_nibble(v.w) << 12);
+    return m & ((m << 1) | (prev_byte == 10u ? 1u : 0u)) & 0xffffu;
 }
 
 template <bool EMIT>

@@ -142,7 +142,51 @@ def sctp_config(n, L):
     return out_d
 
 
+def bookkeeping_config(n):
+    """8(f) rows 3 + 4: datagram split (2 records per datagram), replay window (65536 sessions), SSE scan"""
+    rng = np.random.default_rng(7)
+    plen = 600
+    rec = np.zeros((n, 13 + plen), np.uint8); rec[:, 0] = 23; rec[:, 1] = 0xFE; rec[:, 2] = 0xFD
+    rec[:, 11] = plen >> 8; rec[:, 12] = plen & 0xFF
+    d_buf = t(rec.reshape(-1)); nd = n // 2
+    d_off = t(workload.fixed_offsets(nd, 2 * (13 + plen)))
+    sb = int(ctx.lib.p2pt_dtls_datagram_split_scratch_bytes(nd)); scr = torch.empty(sb, dtype=torch.uint8, device=dev)
+    rec_off = torch.empty(n + 1, dtype=torch.int64, device=dev); rec_dg = torch.empty(n, dtype=torch.int32, device=dev)
+    dst = torch.empty(nd, dtype=torch.uint8, device=dev); nr = torch.zeros(1, dtype=torch.int32, device=dev)
+    split = lambda: ctx.call("p2pt_dtls_datagram_split_batch_device", nd, d_buf, d_off, n, rec_off, rec_dg, dst, nr, scr, sb, s)
+    t_split = timeit(split)
+    assert int(nr.item()) == n
+    S = 65536
+    session = t((np.arange(n, dtype=np.uint64) % S).astype(np.uint32)); seq = t((np.arange(n, dtype=np.uint64) // S))
+    lat = torch.zeros(S, dtype=torch.int64, device=dev); msk = torch.zeros(S, dtype=torch.int64, device=dev)
+    started = torch.zeros(S, dtype=torch.uint8, device=dev); acc = torch.empty(n, dtype=torch.uint8, device=dev)
+    sb2 = int(ctx.lib.p2pt_dtls_replay_filter_scratch_bytes(n)); scr2 = torch.empty(sb2, dtype=torch.uint8, device=dev)
+    def replay():
+        started.zero_()
+        ctx.call("p2pt_dtls_replay_filter_batch_device", n, session, seq, None, S, lat, msk, started, acc, scr2, sb2, s)
+    t_replay = timeit(replay)
+    assert int(acc.sum().item()) == n
+    # SSE scan over 4096 streams x ~293 KB of SSE text
+    k = 4096
+    one = (workload.SSE_TEMPLATE * 2300)[:292968]
+    body = t(np.frombuffer(one, np.uint8).repeat(1).reshape(1, -1).repeat(k, 0).reshape(-1)); boff = t(workload.fixed_offsets(k, len(one)))
+    nev = one.count(b"\n\n") * k
+    ev_csr = torch.empty(k + 1, dtype=torch.int64, device=dev); ev_end = torch.empty(nev + 1, dtype=torch.int64, device=dev)
+    done = torch.empty(k, dtype=torch.uint8, device=dev); tot = torch.zeros(1, dtype=torch.int64, device=dev)
+    sb3 = int(ctx.lib.p2pt_sse_scan_scratch_bytes(k)); scr3 = torch.empty(sb3, dtype=torch.uint8, device=dev)
+    sse = lambda: ctx.call("p2pt_sse_scan_batch_device", k, body, boff, nev, ev_csr, ev_end, done, tot, scr3, sb3, s)
+    t_sse = timeit(sse)
+    assert int(tot.item()) == nev
+    bb = k * len(one)
+    return {"datagram_split": {"ms": t_split, "records": n, "records_per_s": n / t_split * 1e3},
+            "replay_filter_65536_sessions": {"ms": t_replay, "records": n, "records_per_s": n / t_replay * 1e3},
+            "sse_scan": {"ms": t_sse, "body_bytes": bb, "events": nev, "hbm_gbs": 2 * bb / t_sse / 1e6,
+                         "frac_of_hbm_peak": 2 * bb / t_sse / 1e6 / peak, "body_gbs": bb / t_sse / 1e6,
+                         "note": "two passes (count, emit): algorithmic bytes = 2 x body"}}
+
+
 res = {"hbm_peak_gbs": peak, "host_cores": cores,
+       "bookkeeping_1M_records": bookkeeping_config(1_000_000),
        "SCTP_1M_messages_1200B": sctp_config(1_000_000, 1200),
        "C2_1M_frames_1200B_4096_streams": codec_config(1_000_000, 1200, False),
        "C4_10M_frames_64B_sse": codec_config(10_000_000, 64, True),
