@@ -147,7 +147,7 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
  * the explicit nonce the reference draws from rand::thread_rng(); it is an INPUT here so results
  * are reproducible.  session[i] indexes the table given to p2pt_sessions_load (local key / iv).
  * Needs rec_off[i+1] - rec_off[i] >= raw_len_i + 24.  status: OK or BAD_HEADER (raw_len < 13, session index
- * out of range, or an item above 16 MiB).  Bytes of an output slot beyond the item written into it are
+ * out of range, or an item above 1 000 000 bytes).  Bytes of an output slot beyond the item written into it are
  * unspecified after a host-pointer call (the whole slot range is copied back).  Do not call
  * p2pt_sessions_load while seal / open calls on the same ctx are in flight. */
 int32_t p2pt_dtls_gcm_seal_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,

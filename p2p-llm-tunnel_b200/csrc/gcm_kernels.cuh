@@ -100,15 +100,12 @@ struct SmemKeys {
     }
 };
 
-template <class Lut, class Keys>
-__device__ __forceinline__ void aes128_encrypt(const Lut& lut, const Keys& keys,
-                                               uint32_t& s0, uint32_t& s1, uint32_t& s2, uint32_t& s3) {
-    {
-        const uint4 k = keys.get(0);
-        s0 ^= k.x; s1 ^= k.y; s2 ^= k.z; s3 ^= k.w;
-    }
+// rounds FIRST..9 and the final round; the state enters as the input of round FIRST
+template <int FIRST, class Lut, class Keys>
+__device__ __forceinline__ void aes128_rounds(const Lut& lut, const Keys& keys,
+                                              uint32_t& s0, uint32_t& s1, uint32_t& s2, uint32_t& s3) {
 #pragma unroll
-    for (int r = 1; r < 10; r++) {
+    for (int r = FIRST; r < 10; r++) {
         const uint4 k = keys.get(r);
         uint32_t t0 = lut.template look<0, 0>(s0) ^ lut.template look<1, 1>(s1) ^ lut.template look<2, 2>(s2) ^ lut.template look<3, 3>(s3) ^ k.x;
         uint32_t t1 = lut.template look<0, 0>(s1) ^ lut.template look<1, 1>(s2) ^ lut.template look<2, 2>(s3) ^ lut.template look<3, 3>(s0) ^ k.y;
@@ -129,6 +126,42 @@ __device__ __forceinline__ void aes128_encrypt(const Lut& lut, const Keys& keys,
 #undef P2PT_LAST
     s0 = o0; s1 = o1; s2 = o2; s3 = o3;
 }
+
+template <class Lut, class Keys>
+__device__ __forceinline__ void aes128_encrypt(const Lut& lut, const Keys& keys,
+                                               uint32_t& s0, uint32_t& s1, uint32_t& s2, uint32_t& s3) {
+    const uint4 k = keys.get(0);
+    s0 ^= k.x; s1 ^= k.y; s2 ^= k.z; s3 ^= k.w;
+    aes128_rounds<1>(lut, keys, s0, s1, s2, s3);
+}
+
+// CTR blocks of one record differ only in the 32-bit counter, and for counters below 2^16 only in
+// two state bytes after the first AddRoundKey: of the 16 table lookups of round 1, 14 are the same
+// for every block of the record.  They are folded into four words once per record.
+struct CtrRound1 {
+    uint32_t c0, c1, c2, c3;     // round-1 outputs without the two counter-dependent lookups
+    uint32_t r3;                 // round key 0, word 3 (the counter word is XORed into it)
+    template <class Lut, class Keys>
+    __device__ __forceinline__ void prepare(const Lut& lut, const Keys& keys, uint32_t iv, uint32_t n0, uint32_t n1) {
+        const uint4 k0 = keys.get(0), k1 = keys.get(1);
+        const uint32_t s0 = iv ^ k0.x, s1 = n0 ^ k0.y, s2 = n1 ^ k0.z, s3 = k0.w;   // counter bytes 0, 1 are zero
+        r3 = k0.w;
+        c0 = lut.template look<0, 0>(s0) ^ lut.template look<1, 1>(s1) ^ lut.template look<2, 2>(s2) ^ k1.x;
+        c1 = lut.template look<0, 0>(s1) ^ lut.template look<1, 1>(s2) ^ lut.template look<3, 3>(s0) ^ k1.y;
+        c2 = lut.template look<0, 0>(s2) ^ lut.template look<1, 1>(s3) ^ lut.template look<2, 2>(s0) ^ lut.template look<3, 3>(s1) ^ k1.z;
+        c3 = lut.template look<0, 0>(s3) ^ lut.template look<1, 1>(s0) ^ lut.template look<2, 2>(s1) ^ lut.template look<3, 3>(s2) ^ k1.w;
+    }
+    // keystream block for counter ctr < 65536
+    template <class Lut, class Keys>
+    __device__ __forceinline__ void block(const Lut& lut, const Keys& keys, uint32_t ctr,
+                                          uint32_t& o0, uint32_t& o1, uint32_t& o2, uint32_t& o3) const {
+        const uint32_t s3 = bswap32(ctr) ^ r3;
+        o0 = c0 ^ lut.template look<3, 3>(s3);
+        o1 = c1 ^ lut.template look<2, 2>(s3);
+        o2 = c2; o3 = c3;
+        aes128_rounds<2>(lut, keys, o0, o1, o2, o3);
+    }
+};
 
 // GF(2^128) multiply with the prepared multiplier in shared memory (9 rows of 4 class masks):
 // same arithmetic as gf128_mul in gcm_math.cuh, one LDS.128 per 32x32 product instead of 36 registers.
@@ -351,7 +384,8 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
             body0 = body_lo = ibase + 21; body_hi = ibase + 21 + L;
         }
         if (sidx >= a.n_sessions && st == P2PT_ST_OK) st = P2PT_ST_BAD_HEADER;
-        if (ilen > (1ull << 24) && st == P2PT_ST_OK) st = P2PT_ST_BAD_HEADER;     // far beyond any DTLS record; keeps 32-bit block math safe
+        if (ilen > 1000000ull && st == P2PT_ST_OK) st = P2PT_ST_BAD_HEADER;       // far beyond any DTLS record (<= 2^16); keeps every
+                                                                                  // CTR counter below 2^16 (CtrRound1) and block math in 32 bits
 
         if (st != P2PT_ST_OK) {         // group-uniform early outs
             if (MODE == kOpen || MODE == kPipeOpen) {
@@ -428,6 +462,8 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
                  ((uint32_t)__ldg(ibase + 19) << 16) | ((uint32_t)__ldg(ibase + 20) << 24);
         }
         __syncwarp(gmask);                                   // key slot visible to the whole group
+        CtrRound1 r1;                                        // counters stay below 2^16: items are capped at 1 MB above
+        r1.prepare(lut, rkeys, ivw, n0, n1);
 
         U128 acc; acc.w[0] = acc.w[1] = acc.w[2] = acc.w[3] = 0;
         uint4 ej0 = make_uint4(0, 0, 0, 0);                  // E_K(J0), valid in group lane 0
@@ -443,8 +479,8 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
             const bool active = u < slots;
 
             // ---- AES-CTR keystream for counter c + 2 (J0 = counter 1)
-            uint32_t k0 = ivw, k1 = n0, k2 = n1, k3 = bswap32((uint32_t)(c + 2));
-            aes128_encrypt(lut, rkeys, k0, k1, k2, k3);
+            uint32_t k0, k1, k2, k3;
+            r1.block(lut, rkeys, (uint32_t)(c + 2), k0, k1, k2, k3);
 
             uint4 oblk = make_uint4(0, 0, 0, 0);             // bytes this lane contributes to the output stream
             U128 gin; gin.w[0] = gin.w[1] = gin.w[2] = gin.w[3] = 0;
