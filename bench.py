@@ -481,6 +481,20 @@ def run_gpu(args):
                 "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_record": dom_bytes,
                 "note": "AES-GCM without AES/CLMUL instructions is bound by the integer ALU / shared-memory LSU "
                         "pipes, not HBM; see DESIGN.md and profiles/ for pipe utilisation"}
+    # the pipe that actually binds this kernel: integer ALU (LOP3 / PRMT / SHF / IADD3), instruction counts from ncu
+    pipes = os.path.join(ROOT, "profiles", "record_kernel_pipes.json")
+    if os.path.exists(pipes):
+        try:
+            pj = json.load(open(pipes))
+            sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+            alu_winst = n * pj["lane_slots_per_record"] / 32.0 * pj["alu_pipe_inst_per_lane_slot"]
+            alu_peak = ctx.get_info("sm_count") * 4 * 0.5 * sm_hz
+            roofline["alu_pipe"] = {"bound": "integer ALU pipe", "achieved_warp_inst_per_s": alu_winst / (dom_ms * 1e-3),
+                                    "peak_warp_inst_per_s": alu_peak, "frac": alu_winst / (dom_ms * 1e-3) / alu_peak,
+                                    "alu_inst_per_16B_block": pj["alu_pipe_inst_per_lane_slot"], "ncu": pj["ncu"],
+                                    "source": pj["source"]}
+        except Exception as e:
+            roofline["alu_pipe"] = {"error": str(e)}
     prof = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(prof):
         try:
