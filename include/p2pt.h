@@ -104,7 +104,9 @@ void        p2pt_host_free(void* p);
 uint64_t    p2pt_launch_count(p2pt_ctx* ctx);
 /* tuning knobs.  "gcm_group_width": lanes that share one record in the seal/open kernels
  * (4, 8, 16 or 32; 0 = library default).  "chunk_bytes": size of the pieces in which host-pointer
- * calls overlap host->device copies, kernels and device->host copies (default 16 MiB). */
+ * calls overlap host->device copies, kernels and device->host copies (default 16 MiB).  "blocking_sync":
+ * 1 (default) = host-pointer calls sleep while they wait for the GPU, 0 = they spin (lowest latency for
+ * single small frames, but a spinning thread per call starves other workers on a busy host). */
 int32_t     p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value);
 /* read-only facts: "sm_count", "lut_slack", "gcm_group_width", "n_sessions", "gcm_threads"; -1 if unknown */
 int64_t     p2pt_ctx_get_info(p2pt_ctx* ctx, const char* name);

@@ -42,6 +42,8 @@ struct p2pt_ctx {
     int sm_count = 148;
     cudaStream_t streams[kStreams] = {};
     cudaEvent_t events[kStreams] = {};
+    cudaEvent_t sync_events[kStreams] = {};   // cudaEventBlockingSync: the host thread sleeps instead of spinning
+    bool blocking_sync = true;                // big host-pointer calls wait on sync_events (see wait_stream)
     std::mutex mu;                 // serialises host-pointer calls (they share the arena)
     std::mutex err_mu;
     std::string err;
@@ -125,6 +127,18 @@ static void build_crc_tables(uint32_t tab[4][256], uint32_t xpow[1280]) {
 __global__ void smem_base_probe_kernel(uint32_t* out) {
     extern __shared__ __align__(16) uint8_t dyn_smem[];
     *out = shared_addr(dyn_smem);
+}
+
+// Wait for one of the ctx's streams.  cudaStreamSynchronize spins on a CPU core; with several worker
+// threads per GPU and several GPUs per host that starves the threads that feed the copy engines, so by
+// default the wait is a blocking-sync event (the thread sleeps until the interrupt).
+static cudaError_t wait_stream(p2pt_ctx* ctx, cudaStream_t st) {
+    if (!ctx->blocking_sync) return cudaStreamSynchronize(st);
+    int idx = 0;
+    for (int i = 0; i < kStreams; i++) if (ctx->streams[i] == st) idx = i;
+    cudaError_t e = cudaEventRecord(ctx->sync_events[idx], st);
+    if (e != cudaSuccess) return e;
+    return cudaEventSynchronize(ctx->sync_events[idx]);
 }
 
 // ---- arena -----------------------------------------------------------------------------------------
@@ -235,7 +249,8 @@ int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
     ctx->sm_count = prop.multiProcessorCount;
     for (int i = 0; i < kStreams; i++) {
         if (cudaStreamCreateWithFlags(&ctx->streams[i], cudaStreamNonBlocking) != cudaSuccess ||
-            cudaEventCreateWithFlags(&ctx->events[i], cudaEventDisableTiming) != cudaSuccess) {
+            cudaEventCreateWithFlags(&ctx->events[i], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ctx->sync_events[i], cudaEventDisableTiming | cudaEventBlockingSync) != cudaSuccess) {
             delete ctx;
             return set_err(nullptr, P2PT_ERR_CUDA, "stream/event creation failed");
         }
@@ -274,6 +289,7 @@ int32_t p2pt_ctx_destroy(p2pt_ctx* ctx) {
         for (int i = 0; i < kStreams; i++) {
             if (ctx->streams[i]) cudaStreamDestroy(ctx->streams[i]);
             if (ctx->events[i]) cudaEventDestroy(ctx->events[i]);
+            if (ctx->sync_events[i]) cudaEventDestroy(ctx->sync_events[i]);
         }
         if (ctx->keys_local) cudaFree(ctx->keys_local);
         if (ctx->keys_remote) cudaFree(ctx->keys_remote);
@@ -310,6 +326,10 @@ int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
         ctx->gcm_g = (int)value;
         return P2PT_OK;
     }
+    if (strcmp(name, "blocking_sync") == 0) {
+        ctx->blocking_sync = value != 0;
+        return P2PT_OK;
+    }
     if (strcmp(name, "chunk_bytes") == 0) {
         if (value < (1 << 16)) return set_err(ctx, P2PT_ERR_ARG, "chunk_bytes must be at least 65536");
         ctx->chunk_bytes = (uint64_t)value;
@@ -341,7 +361,7 @@ int32_t p2pt_sessions_load(p2pt_ctx* ctx, uint32_t n, const uint8_t* local_keys1
         session_expand_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, dk, di, dir ? ctx->keys_remote : ctx->keys_local);
         count_launch(ctx);
         CUDA_TRY(ctx, cudaGetLastError());
-        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        CUDA_TRY(ctx, wait_stream(ctx, st));
     }
     cudaFree(dk);
     cudaFree(di);
@@ -723,7 +743,7 @@ int32_t p2pt_frame_encode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* types,
             CUDA_TRY(ctx, cudaMemcpyAsync(out + out_off[i], d_out + (out_off[i] - out_off[0]), len, cudaMemcpyDeviceToHost, st));
         }
     }
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     return P2PT_OK;
 }
 
@@ -745,7 +765,7 @@ int32_t p2pt_frame_decode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, co
     if (ibytes) CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in + in_off[0], ibytes, cudaMemcpyHostToDevice, st));
     if (int32_t r = p2pt_frame_decode_batch_device(ctx, n, d_in - in_off[0], d_io, d_desc, st)) return r;
     CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     return P2PT_OK;
 }
 
@@ -788,24 +808,24 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
                                                   gathered_off ? d_goff : nullptr, d_scratch, sbytes, st)) return r;
     uint32_t k = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&k, d_k, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     *k_out = k;
     if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: more streams than max_streams");
     CUDA_TRY(ctx, cudaMemcpyAsync(uniq_sid, d_uniq, 4 * (size_t)k, cudaMemcpyDeviceToHost, st));
     if (uniq_session) CUDA_TRY(ctx, cudaMemcpyAsync(uniq_session, d_usess, 4 * (size_t)k, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(csr, d_csr, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     const uint64_t m = csr[k];
     if (m) CUDA_TRY(ctx, cudaMemcpyAsync(perm, d_perm, 4 * m, cudaMemcpyDeviceToHost, st));
     if (gathered_off) {
         CUDA_TRY(ctx, cudaMemcpyAsync(gathered_off, d_goff, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        CUDA_TRY(ctx, wait_stream(ctx, st));
         if (gathered) {
             if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: gathered_cap too small");
             if (gathered_off[k]) CUDA_TRY(ctx, cudaMemcpyAsync(gathered, d_g, gathered_off[k], cudaMemcpyDeviceToHost, st));
         }
     }
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     return P2PT_OK;
 }
 
@@ -908,7 +928,7 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
         if (c.mode == kOpen) CUDA_TRY(ctx, cudaMemcpyAsync(c.out_len + r0, d_olen + r0, 4 * m, cudaMemcpyDeviceToHost, st));
         if (c.mode == kPipeOpen) CUDA_TRY(ctx, cudaMemcpyAsync(c.desc + r0, d_desc + r0, 24 * m, cudaMemcpyDeviceToHost, st));
     }
-    for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->streams[i]));
+    for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, wait_stream(ctx, ctx->streams[i]));
     // pipe-open descriptors are relative to the caller's `out`, which is how the kernel wrote them
     return P2PT_OK;
 }
@@ -1021,7 +1041,7 @@ int32_t p2pt_sctp_packetize_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg,
                                                      epoch ? d_ep : nullptr, epoch ? d_sq : nullptr, d_out, d_omoff, d_first, d_poff, st)) return r;
     CUDA_TRY(ctx, cudaMemcpyAsync(out, d_out, bytes, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(pkt_off, d_poff, 8 * (pk + 1), cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     return P2PT_OK;
 }
 
@@ -1064,16 +1084,16 @@ int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const 
     uint32_t nm = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(info, d_info, 16 * n, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     *n_msgs_out = nm;
     if (nm > max_msgs) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_unpack_reassemble: more messages than max_msgs");
     CUDA_TRY(ctx, cudaMemcpyAsync(msg_off, d_moff, 8 * ((size_t)nm + 1), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(msg_first, d_mfirst, 4 * (size_t)nm, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(msg_status, d_mstat, nm, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     if (msg_off[nm] > msg_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_unpack_reassemble: msg_cap too small");
     if (msg_off[nm]) CUDA_TRY(ctx, cudaMemcpyAsync(msg, d_msg, msg_off[nm], cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     return P2PT_OK;
 }
 
@@ -1138,11 +1158,11 @@ int32_t p2pt_sse_scan_batch(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, cons
     CUDA_TRY(ctx, cudaMemcpyAsync(&total, d_n, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(ev_csr, d_csr, 8 * (k + 1), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(done, d_done, k, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     *n_events_out = total;
     if (total > max_events) return set_err(ctx, P2PT_ERR_CAPACITY, "sse_scan: more events than max_events");
     if (total) CUDA_TRY(ctx, cudaMemcpyAsync(ev_end, d_end, 8 * total, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     return P2PT_OK;
 }
 
@@ -1250,12 +1270,12 @@ int32_t p2pt_dtls_datagram_split_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t*
     uint32_t total = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&total, d_n, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(dgram_status, d_st, n, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     *n_records_out = total;
     if (total > max_records) return set_err(ctx, P2PT_ERR_CAPACITY, "datagram_split: more records than max_records");
     CUDA_TRY(ctx, cudaMemcpyAsync(rec_off, d_roff, 8 * ((size_t)total + 1), cudaMemcpyDeviceToHost, st));
     if (total) CUDA_TRY(ctx, cudaMemcpyAsync(rec_dgram, d_rd, 4 * (size_t)total, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     return P2PT_OK;
 }
 
@@ -1292,7 +1312,7 @@ int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t*
     CUDA_TRY(ctx, cudaMemcpyAsync(latest, d_lat, 8 * S, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(mask, d_mask, 8 * S, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(started, d_started, S, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, wait_stream(ctx, st));
     return P2PT_OK;
 }
 
@@ -1368,14 +1388,14 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
                                                   gathered_off ? d_goff : nullptr, d_scratch, sbytes, s0)) return r;
     uint32_t k = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&k, d_k, 4, cudaMemcpyDeviceToHost, s0));
-    CUDA_TRY(ctx, cudaStreamSynchronize(s0));
+    CUDA_TRY(ctx, wait_stream(ctx, s0));
     *k_out = k;
     if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "pipeline_open_demux: more streams than max_streams");
     CUDA_TRY(ctx, cudaMemcpyAsync(uniq_sid, d_uniq, 4 * (size_t)k, cudaMemcpyDeviceToHost, s0));
     if (uniq_session) CUDA_TRY(ctx, cudaMemcpyAsync(uniq_session, d_usess, 4 * (size_t)k, cudaMemcpyDeviceToHost, s0));
     CUDA_TRY(ctx, cudaMemcpyAsync(csr, d_csr, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, s0));
     if (gathered_off) CUDA_TRY(ctx, cudaMemcpyAsync(gathered_off, d_goff, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, s0));
-    CUDA_TRY(ctx, cudaStreamSynchronize(s0));
+    CUDA_TRY(ctx, wait_stream(ctx, s0));
     const uint64_t m = csr[k];
     if (m) CUDA_TRY(ctx, cudaMemcpyAsync(perm, d_perm, 4 * m, cudaMemcpyDeviceToHost, s0));
     if (gathered) {
@@ -1392,7 +1412,7 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
             CUDA_TRY(ctx, cudaMemcpyAsync(gathered + o, d_g + o, len, cudaMemcpyDeviceToHost, ctx->streams[i]));
         }
     }
-    for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->streams[i]));
+    for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, wait_stream(ctx, ctx->streams[i]));
     return P2PT_OK;
 }
 
