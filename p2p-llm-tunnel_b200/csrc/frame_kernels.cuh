@@ -8,6 +8,7 @@
 // All of it is HBM-bound byte work: the kernels move aligned 16-byte vectors (common.cuh), size
 // their grids in multiples of the SM count, and never touch a tensor core.
 #pragma once
+#include <cooperative_groups.h>
 #include "common.cuh"
 #include "../../include/p2pt.h"
 
@@ -206,20 +207,22 @@ __device__ __forceinline__ void demux_tile(u64 n, u64& lo, u64& hi) {
     if (hi > n) hi = n;
 }
 
-__global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
-    u64 n, const DemuxBufs bufs, const p2pt_desc* __restrict__ desc,
-    int pass, uint32_t* __restrict__ hist, const u64* __restrict__ misc) {
-    if (demux_pass_trivial(misc, pass)) return;
+// The three phases of a sorting pass, as device functions so that they can run either as three
+// launches or inside one cooperative kernel (grid-wide syncs in between).  Everything another block
+// wrote (keys, indices, the histogram matrix, row totals) is read with __ldcg, i.e. from L2: inside a
+// single kernel an L1 line cached in an earlier pass would be stale.
+__device__ __forceinline__ void demux_hist_phase(u64 n, const DemuxBufs& bufs, const p2pt_desc* desc, int pass,
+                                                 uint32_t* hist, const u64* misc) {
     const int sb = demux_src_buffer(misc, pass);
-    const u64* __restrict__ keys = bufs.keys[sb];
-    const uint32_t* __restrict__ idx = bufs.idx[sb];
+    const u64* keys = bufs.keys[sb];
+    const uint32_t* idx = bufs.idx[sb];
     __shared__ uint32_t h[kRadix];
     h[threadIdx.x] = 0;
     __syncthreads();
     u64 lo, hi;
     demux_tile(n, lo, hi);
     for (u64 i = lo + threadIdx.x; i < hi; i += kSortThreads) {
-        const uint32_t d = demux_digit(keys[i], idx[i], pass, desc);
+        const uint32_t d = demux_digit(__ldcg(keys + i), __ldcg(idx + i), pass, desc);
         // warp-aggregated: one shared atomic per distinct digit in the warp
         const uint32_t peers = __match_any_sync(__activemask(), d);
         if ((__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&h[d], __popc(peers));
@@ -232,17 +235,13 @@ __global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
 // the row issued up front) and the row total.  The scan ACROSS rows is redone by every scatter
 // block in shared memory (256 values), which is cheaper than a serial single-block pass.
 constexpr int kRowScanWarps = 4;
-__global__ void __launch_bounds__(32 * kRowScanWarps) demux_rowscan_kernel(uint32_t* __restrict__ hist, int pass,
-                                                                          u64* __restrict__ misc,
-                                                                          uint32_t* __restrict__ row_total) {
-    if (demux_pass_trivial(misc, pass)) return;
+__device__ __forceinline__ void demux_rowscan_row(uint32_t* hist, int row, uint32_t* row_total) {
     constexpr int CH = (kSortBlocks + 31) / 32;
-    const int row = blockIdx.x * kRowScanWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (row >= kRadix) return;
+    const int lane = threadIdx.x & 31;
     uint32_t* r = hist + (u64)row * kSortBlocks;
     uint32_t v[CH];
 #pragma unroll
-    for (int i = 0; i < CH; i++) { const int b = 32 * i + lane; v[i] = b < kSortBlocks ? r[b] : 0u; }
+    for (int i = 0; i < CH; i++) { const int b = 32 * i + lane; v[i] = b < kSortBlocks ? __ldcg(r + b) : 0u; }
     uint32_t carry = 0;
 #pragma unroll
     for (int i = 0; i < CH; i++) {
@@ -259,16 +258,13 @@ __global__ void __launch_bounds__(32 * kRowScanWarps) demux_rowscan_kernel(uint3
     if (lane == 0) row_total[row] = carry;
 }
 
-__global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
-    u64 n, const DemuxBufs bufs, const p2pt_desc* __restrict__ desc,
-    int pass, const uint32_t* __restrict__ hist, const u64* __restrict__ misc,
-    const uint32_t* __restrict__ row_total) {
-    if (demux_pass_trivial(misc, pass)) return;          // nothing to move: the data stays where it is
+__device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs, const p2pt_desc* desc, int pass,
+                                                    const uint32_t* hist, const u64* misc, const uint32_t* row_total) {
     const int sb = demux_src_buffer(misc, pass);
-    const u64* __restrict__ keys = bufs.keys[sb];
-    const uint32_t* __restrict__ idx = bufs.idx[sb];
-    u64* __restrict__ keys_out = bufs.keys[sb ^ 1];
-    uint32_t* __restrict__ idx_out = bufs.idx[sb ^ 1];
+    const u64* keys = bufs.keys[sb];
+    const uint32_t* idx = bufs.idx[sb];
+    u64* keys_out = bufs.keys[sb ^ 1];
+    uint32_t* idx_out = bufs.idx[sb ^ 1];
     u64 lo, hi;
     demux_tile(n, lo, hi);
     static_assert(kSortThreads == kRadix, "one thread per digit");
@@ -279,7 +275,7 @@ __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     {
         // exclusive scan of the 256 row totals -> where each digit's output range starts
-        const uint32_t v = row_total[threadIdx.x];
+        const uint32_t v = __ldcg(row_total + threadIdx.x);
         uint32_t incl = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -291,7 +287,7 @@ __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
         uint32_t wbase = 0;
 #pragma unroll
         for (int w = 0; w < W; w++) wbase += (w < warp) ? wtot[w] : 0u;
-        base[threadIdx.x] = wbase + incl - v + hist[(u64)threadIdx.x * kSortBlocks + blockIdx.x];
+        base[threadIdx.x] = wbase + incl - v + __ldcg(hist + (u64)threadIdx.x * kSortBlocks + blockIdx.x);
     }
     for (u64 c0 = lo; c0 < hi; c0 += kSortThreads) {
 #pragma unroll
@@ -302,7 +298,7 @@ __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
         u64 key = 0;
         uint32_t ix = 0, d = 0, rank = 0;
         if (live) {
-            key = keys[i]; ix = idx[i];
+            key = __ldcg(keys + i); ix = __ldcg(idx + i);
             d = demux_digit(key, ix, pass, desc);
         }
         // rank among equal digits inside the warp, in lane (= arrival) order
@@ -326,6 +322,45 @@ __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
         __syncthreads();
         base[col] += run;
         __syncthreads();
+    }
+}
+
+// three launches per pass (fallback path) ...
+__global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
+    u64 n, const DemuxBufs bufs, const p2pt_desc* __restrict__ desc,
+    int pass, uint32_t* __restrict__ hist, const u64* __restrict__ misc) {
+    if (demux_pass_trivial(misc, pass)) return;
+    demux_hist_phase(n, bufs, desc, pass, hist, misc);
+}
+__global__ void __launch_bounds__(32 * kRowScanWarps) demux_rowscan_kernel(uint32_t* __restrict__ hist, int pass,
+                                                                          u64* __restrict__ misc,
+                                                                          uint32_t* __restrict__ row_total) {
+    if (demux_pass_trivial(misc, pass)) return;
+    const int row = blockIdx.x * kRowScanWarps + (threadIdx.x >> 5);
+    if (row < kRadix) demux_rowscan_row(hist, row, row_total);
+}
+__global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
+    u64 n, const DemuxBufs bufs, const p2pt_desc* __restrict__ desc,
+    int pass, const uint32_t* __restrict__ hist, const u64* __restrict__ misc,
+    const uint32_t* __restrict__ row_total) {
+    if (demux_pass_trivial(misc, pass)) return;          // nothing to move: the data stays where it is
+    demux_scatter_phase(n, bufs, desc, pass, hist, misc, row_total);
+}
+
+// ... or all passes in ONE cooperative launch: the nine passes are launch-latency bound at 1 M items
+// (27 launches of a few microseconds each), so the phases are separated by grid-wide syncs instead.
+__global__ void __launch_bounds__(kSortThreads) demux_sort_coop_kernel(
+    u64 n, const DemuxBufs bufs, const p2pt_desc* desc, uint32_t* hist, const u64* misc, uint32_t* row_total) {
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    for (int pass = 0; pass < kSortPasses; pass++) {
+        if (demux_pass_trivial(misc, pass)) continue;     // uniform over the whole grid
+        demux_hist_phase(n, bufs, desc, pass, hist, misc);
+        grid.sync();
+        const int row = blockIdx.x * (kSortThreads / 32) + (threadIdx.x >> 5);
+        if (row < kRadix) demux_rowscan_row(hist, row, row_total);
+        grid.sync();
+        demux_scatter_phase(n, bufs, desc, pass, hist, misc, row_total);
+        grid.sync();
     }
 }
 

@@ -44,6 +44,7 @@ struct p2pt_ctx {
     cudaEvent_t events[kStreams] = {};
     cudaEvent_t sync_events[kStreams] = {};   // cudaEventBlockingSync: the host thread sleeps instead of spinning
     bool blocking_sync = true;                // big host-pointer calls wait on sync_events (see wait_stream)
+    bool coop_sort = true;                    // demux sorting passes in one cooperative launch
     std::mutex mu;                 // serialises host-pointer calls (they share the arena)
     std::mutex err_mu;
     std::string err;
@@ -326,6 +327,10 @@ int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
         ctx->gcm_g = (int)value;
         return P2PT_OK;
     }
+    if (strcmp(name, "coop_sort") == 0) {
+        ctx->coop_sort = value != 0;
+        return P2PT_OK;
+    }
     if (strcmp(name, "blocking_sync") == 0) {
         ctx->blocking_sync = value != 0;
         return P2PT_OK;
@@ -426,10 +431,23 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc);
     DemuxBufs bufs;
     bufs.keys[0] = s.keys[0]; bufs.keys[1] = s.keys[1]; bufs.idx[0] = s.idx[0]; bufs.idx[1] = s.idx[1];
-    for (int pass = 0; pass < kSortPasses; pass++) {
-        demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, desc, pass, s.hist, s.misc);
-        demux_rowscan_kernel<<<kRadix / kRowScanWarps, 32 * kRowScanWarps, 0, st>>>(s.hist, pass, s.misc, s.row_total);
-        demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, desc, pass, s.hist, s.misc, s.row_total);
+    bool coop_done = false;
+    if (ctx->coop_sort) {
+        // all nine passes in one cooperative launch (grid-wide syncs between the phases)
+        u64 n_arg = n; const p2pt_desc* desc_arg = desc; uint32_t* hist_arg = s.hist; const u64* misc_arg = s.misc;
+        uint32_t* rt_arg = s.row_total;
+        void* args[] = {&n_arg, &bufs, &desc_arg, &hist_arg, &misc_arg, &rt_arg};
+        cudaError_t ce = cudaLaunchCooperativeKernel((void*)demux_sort_coop_kernel, dim3(kSortBlocks), dim3(kSortThreads), args, 0, st);
+        if (ce == cudaSuccess) { coop_done = true; count_launch(ctx); }
+        else { (void)cudaGetLastError(); ctx->coop_sort = false; }      // not supported here: fall back for good
+    }
+    if (!coop_done) {
+        for (int pass = 0; pass < kSortPasses; pass++) {
+            demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, desc, pass, s.hist, s.misc);
+            demux_rowscan_kernel<<<kRadix / kRowScanWarps, 32 * kRowScanWarps, 0, st>>>(s.hist, pass, s.misc, s.row_total);
+            demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, desc, pass, s.hist, s.misc, s.row_total);
+        }
+        count_launch(ctx, 3 * kSortPasses);
     }
     const u64 nblk = demux_scan_blocks(n);
     demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, desc, s.misc, s.blk_heads, s.blk_bytes);
@@ -437,7 +455,7 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, desc, s.misc, s.blk_heads, s.blk_bytes, nblk,
                                                               max_streams, uniq_sid, uniq_session, (u64*)csr, perm, k_out,
                                                               (u64*)gathered_off);
-    count_launch(ctx, 1 + 3 * kSortPasses + 3);
+    count_launch(ctx, 1 + 3);
     if (gathered) {
         demux_gather_kernel<<<grid_for(ctx, (n + 7) / 8, 8, 16), 256, 0, st>>>(n, s.misc, perm, bufs, desc, in, gathered,
                                                                     gathered_cap, k_out, max_streams);
