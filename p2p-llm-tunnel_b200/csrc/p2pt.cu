@@ -264,6 +264,15 @@ int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
         build_crc_tables(ctab, cxp);
         CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_tab, ctab, sizeof ctab));
         CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_xpow, cxp, sizeof cxp));
+        // contribution of the 0xFFFFFFFF init value to a packet of w words: the register 0xFFFFFFFF run
+        // through 4 w zero bytes (CRC is linear in its initial register)
+        static uint32_t cinit[kCrcSeg * 32 + 1];
+        uint32_t reg = 0xFFFFFFFFu;
+        for (int w = 0; w <= kCrcSeg * 32; w++) {
+            cinit[w] = reg;
+            for (int b = 0; b < 4; b++) reg = (reg >> 8) ^ ctab[0][reg & 0xff];
+        }
+        CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_init, cinit, sizeof cinit));
     }
     // where does dynamic shared memory start?  The T-tables must sit on a 64 KiB boundary.
     uint32_t* d_probe = nullptr;
