@@ -132,6 +132,20 @@ __device__ __forceinline__ void warp_copy_bytes(uint8_t* dst, const uint8_t* src
 // hundred bytes (SSE token chunks) a whole warp per item wastes 7/8 of every load; eight items per
 // warp keeps the lanes busy.  All four lanes of the quad must call.
 __device__ __forceinline__ void quad_copy_bytes(uint8_t* dst, const uint8_t* src, uint32_t len, int q) {
+    if ((((uintptr_t)dst | len) & 15) == 0) {
+        // Whole aligned destination vectors (the gather of 16-byte-multiple payloads): each one is built from
+        // the two aligned source vectors that cover it; one of those is read only if it holds item bytes.
+        const unsigned r = (unsigned)((uintptr_t)src & 15);
+        const uint8_t* sb = src - r;
+        const uint32_t nv = len >> 4;
+        for (uint32_t v = q; v < nv; v += 4) {
+            const uint4 a = ldg128(sb + 16 * v);
+            uint4 o = a;
+            if (r) o = funnel16(a, ldg128(sb + 16 * v + 16), r);      // r != 0: vector v + 1 holds item bytes [16 (v + 1) - r, ..)
+            stg128(dst + 16 * v, o);
+        }
+        return;
+    }
     uint32_t head = (uint32_t)((16 - ((uintptr_t)dst & 15)) & 15);
     if (head > len) head = len;
     for (uint32_t b = q; b < head; b += 4) dst[b] = __ldg(src + b);

@@ -56,6 +56,7 @@ struct p2pt_ctx {
     uint64_t chunk_bytes = 16u << 20;  // host-pointer calls move records in chunks of about this size
     uint32_t lut_slack = 0;        // bytes needed in front of the T-tables to reach 64 KiB alignment
     int gcm_g = 0;                 // forced group width (env P2PT_GCM_G), 0 = heuristic
+    int occ_encode = 4, occ_gather = 4;   // resident blocks per SM of the two copy kernels (set at create)
 };
 
 static std::string g_create_err;
@@ -213,6 +214,29 @@ static unsigned grid_for(p2pt_ctx* ctx, uint64_t items, unsigned per_block, unsi
     return (unsigned)g;
 }
 
+// Grid for a warp-per-tile grid-stride kernel: at most one resident wave (blocks_per_sm from the
+// occupancy query) and as many warps as give every warp the same number of tiles (within one), so that
+// no SM idles while the last blocks finish.
+static unsigned grid_balanced(p2pt_ctx* ctx, uint64_t tiles, unsigned warps_per_block, unsigned blocks_per_sm) {
+    if (tiles == 0) return 1;
+    const uint64_t cap_warps = (uint64_t)ctx->sm_count * blocks_per_sm * warps_per_block;
+    const uint64_t iters = (tiles + cap_warps - 1) / cap_warps;
+    const uint64_t warps = (tiles + iters - 1) / iters;
+    return (unsigned)((warps + warps_per_block - 1) / warps_per_block);
+}
+
+// Tile size of the two copy kernels (frame_encode_kernel, demux_gather_kernel) in rounds of 8 frames, and
+// their grid: 32-frame tiles on one balanced resident wave when every warp still gets >= 16 of them,
+// else 8-frame tiles on a grid the hardware scheduler balances.
+static int copy_tile_rounds(p2pt_ctx* ctx, uint64_t n, int blocks_per_sm) {
+    const uint64_t wave_warps = (uint64_t)ctx->sm_count * blocks_per_sm * 8;
+    return (n + 31) / 32 >= 16 * wave_warps ? 4 : 1;
+}
+static unsigned copy_grid(p2pt_ctx* ctx, uint64_t n, int rounds, int blocks_per_sm) {
+    if (rounds == 4) return grid_balanced(ctx, (n + 31) / 32, 8, blocks_per_sm);
+    return grid_for(ctx, (n + 7) / 8, 8, 16);
+}
+
 // ===================================================================================================
 extern "C" {
 
@@ -283,6 +307,10 @@ int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
     CUDA_TRY(nullptr, cudaStreamSynchronize(ctx->streams[0]));
     cudaFree(d_probe);
     ctx->lut_slack = (0x10000u - (sb & 0xffffu)) & 0xffffu;
+    CUDA_TRY(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_encode, frame_encode_kernel, 256, 0));
+    CUDA_TRY(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_gather, demux_gather_kernel, 256, 0));
+    if (ctx->occ_encode < 1) ctx->occ_encode = 1;
+    if (ctx->occ_gather < 1) ctx->occ_gather = 1;
     if (const char* g = getenv("P2PT_GCM_G")) {
         int v = atoi(g);
         if (v == 4 || v == 8 || v == 16 || v == 32) ctx->gcm_g = v;
@@ -393,8 +421,9 @@ int32_t p2pt_frame_encode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t*
     if (n == 0) return P2PT_OK;
     if (!types || !sids || !pay_off || !out || !out_off) return set_err(ctx, P2PT_ERR_ARG, "frame_encode: null argument");
     DeviceGuard dg(ctx->device);
-    frame_encode_kernel<<<grid_for(ctx, (n + 7) / 8, 8, 16), 256, 0, (cudaStream_t)stream>>>(
-        n, types, sids, payload, (const u64*)pay_off, out, (const u64*)out_off);
+    const int rounds = copy_tile_rounds(ctx, n, ctx->occ_encode);
+    frame_encode_kernel<<<copy_grid(ctx, n, rounds, ctx->occ_encode), 256, 0, (cudaStream_t)stream>>>(
+        n, types, sids, payload, (const u64*)pay_off, out, (const u64*)out_off, rounds);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
     return P2PT_OK;
@@ -437,13 +466,13 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: scratch must be 256-byte aligned");
     DemuxScratch s = demux_carve(scratch, n);
     CUDA_TRY(ctx, cudaMemsetAsync(s.misc, 0, 32, st));
-    demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc);
+    demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc, s.blen);
     DemuxBufs bufs;
     bufs.keys[0] = s.keys[0]; bufs.keys[1] = s.keys[1]; bufs.idx[0] = s.idx[0]; bufs.idx[1] = s.idx[1];
     bool coop_done = false;
     if (ctx->coop_sort) {
         // all nine passes in one cooperative launch (grid-wide syncs between the phases)
-        u64 n_arg = n; const p2pt_desc* desc_arg = desc; uint32_t* hist_arg = s.hist; const u64* misc_arg = s.misc;
+        u64 n_arg = n; const uint32_t* desc_arg = s.blen; uint32_t* hist_arg = s.hist; const u64* misc_arg = s.misc;
         uint32_t* rt_arg = s.row_total;
         void* args[] = {&n_arg, &bufs, &desc_arg, &hist_arg, &misc_arg, &rt_arg};
         cudaError_t ce = cudaLaunchCooperativeKernel((void*)demux_sort_coop_kernel, dim3(kSortBlocks), dim3(kSortThreads), args, 0, st);
@@ -452,22 +481,24 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     }
     if (!coop_done) {
         for (int pass = 0; pass < kSortPasses; pass++) {
-            demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, desc, pass, s.hist, s.misc);
+            demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc);
             demux_rowscan_kernel<<<kRadix / kRowScanWarps, 32 * kRowScanWarps, 0, st>>>(s.hist, pass, s.misc, s.row_total);
-            demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, desc, pass, s.hist, s.misc, s.row_total);
+            demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc, s.row_total);
         }
         count_launch(ctx, 3 * kSortPasses);
     }
-    const u64 nblk = demux_scan_blocks(n);
-    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, desc, s.misc, s.blk_heads, s.blk_bytes);
+    const u64 nblk = demux_emit_blocks(n);
+    const int dst_mode = !gathered ? 0 : gathered_cap <= 0xffffffffull ? 1 : 2;
+    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes);
     demux_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, s.blk_heads, s.blk_bytes);
-    demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, desc, s.misc, s.blk_heads, s.blk_bytes, nblk,
+    demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, nblk,
                                                               max_streams, uniq_sid, uniq_session, (u64*)csr, perm, k_out,
-                                                              (u64*)gathered_off);
+                                                              (u64*)gathered_off, dst_mode);
     count_launch(ctx, 1 + 3);
     if (gathered) {
-        demux_gather_kernel<<<grid_for(ctx, (n + 7) / 8, 8, 16), 256, 0, st>>>(n, s.misc, perm, bufs, desc, in, gathered,
-                                                                    gathered_cap, k_out, max_streams);
+        const int rounds = copy_tile_rounds(ctx, n, ctx->occ_gather);
+        demux_gather_kernel<<<copy_grid(ctx, n, rounds, ctx->occ_gather), 256, 0, st>>>(n, s.misc, bufs, desc, in, gathered,
+                                                                    gathered_cap, k_out, max_streams, dst_mode, rounds);
         count_launch(ctx);
     }
     CUDA_TRY(ctx, cudaGetLastError());

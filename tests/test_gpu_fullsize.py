@@ -109,6 +109,48 @@ def test_c4_ten_million_tiny_sse_frames(ctx):
     assert np.all(g[:, :6] == np.frombuffer(b"data: ", np.uint8))
 
 
+def test_large_ragged_batch_through_the_32_frame_tiles(ctx):
+    """Above ~2.4 M frames the encoder and the gather switch to 32-frame tiles (copy_tile_rounds in
+    p2pt.cu).  Ragged payloads of 0..40 bytes with a few long frames and a few undecodable ones, checked
+    byte for byte against a numpy construction of encode (protocol.rs:148-154) and of the stable
+    per-stream body concatenation (serve.rs:120-124)."""
+    rng = np.random.default_rng(0x5EED0006)
+    n = 2_600_000
+    lens = rng.integers(0, 41, n).astype(np.int64)
+    long_ix = rng.choice(n, 2000, replace=False)
+    lens[long_ix] = rng.integers(257, 3000, 2000)
+    types = np.full(n, 21, np.uint8)
+    types[rng.choice(n, 5000, replace=False)] = 22                  # ResEnd frames carry no body
+    bad_ix = rng.choice(n, 1000, replace=False)
+    types[bad_ix] = 0                                               # not a MessageType (protocol.rs:103-118)
+    sids = rng.integers(1, 3001, n).astype(np.uint32)
+    pay_off = np.zeros(n + 1, np.uint64); np.cumsum(lens, out=pay_off[1:])
+    payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+    frames, off = ctx.frame_encode(types, sids, payload, pay_off)
+    o = off[:-1].astype(np.int64)
+    assert np.array_equal(off.astype(np.int64), np.concatenate([[0], np.cumsum(lens + 5)]))
+    assert np.array_equal(frames[o], types)
+    be = sids.astype(">u4").view(np.uint8).reshape(n, 4)
+    for b in range(4):
+        assert np.array_equal(frames[o + 1 + b], be[:, b])
+    fidx = np.repeat(np.arange(n, dtype=np.int64), lens)            # frame of every payload byte
+    assert np.array_equal(frames[np.arange(len(payload), dtype=np.int64) + 5 * (fidx + 1)], payload)
+    del fidx
+    desc = ctx.frame_decode(frames, off)
+    bad = np.zeros(n, bool); bad[bad_ix] = True
+    assert np.array_equal(desc["status"] != 0, bad) and np.all(desc["status"][bad] == 2)
+    r = ctx.frame_demux(desc, frames, max_streams=3000)
+    assert r["k"] == 3000
+    good = np.flatnonzero(~bad)
+    order = good[np.argsort(sids[good], kind="stable")]
+    assert np.array_equal(r["perm"][: len(order)].astype(np.int64), order)
+    body = np.where(types[order] == 21, lens[order], 0)
+    starts = pay_off[:-1].astype(np.int64)[order]
+    excl = np.cumsum(body) - body
+    src = np.repeat(starts - excl, body) + np.arange(int(body.sum()), dtype=np.int64)
+    assert np.array_equal(r["gathered"], payload[src])
+
+
 def test_c5_slice_full_pipeline_multi_session(ctx):
     """configs[4] at 1/8 size (the full size runs in bench.py with its own correctness gate): 8192 sessions x
     16 records, encode->seal, open->decode->demux->gather keyed by (session, stream id)."""
