@@ -23,13 +23,19 @@ __device__ __forceinline__ bool msg_type_valid(uint32_t b) {
     return b == 99;
 }
 
+#ifndef P2PT_COPY_MIN_BLOCKS
+#define P2PT_COPY_MIN_BLOCKS 6      // resident 256-thread blocks per SM the two copy kernels are compiled for:
+                                    // 40 registers, 48 warps of loads in flight; measured 4 / 6 / 8 on 1 M x 1200 B:
+                                    // encode 0.55 / 0.52 / 0.53 ms, demux + gather 0.70 / 0.65 / 0.66 ms (8 spills)
+#endif
+
 // ---- encode: a warp takes a tile of 8 * rounds consecutive frames (rounds = 1 or 4).  Lane l loads the
 // metadata of frame l (coalesced) and writes its 5-byte header; the payload copies then run in rounds of
 // eight frames, four lanes per frame, when all of the tile are short (<= 256 B, the SSE token regime),
 // else frame after frame with all 32 lanes (aligned 16-byte vectors either way).  Tiles of 32 amortise
 // the metadata latency over four times the frames; the host picks them when the batch is large enough
 // that every warp still gets many tiles (copy_tile_rounds), else the last warps would run alone.
-__global__ void __launch_bounds__(256) frame_encode_kernel(
+__global__ void __launch_bounds__(256, P2PT_COPY_MIN_BLOCKS) frame_encode_kernel(
     u64 n, const uint8_t* __restrict__ types, const uint32_t* __restrict__ sids,
     const uint8_t* __restrict__ payload, const u64* __restrict__ pay_off,
     uint8_t* __restrict__ out, const u64* __restrict__ out_off, int rounds) {
@@ -600,7 +606,7 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
 // sector once, and the writes advance one front per stream, which L2 merges into whole lines.  Walking
 // the sorted order instead reads 69-byte frames and 24-byte descriptors at random (measured 4.7x read
 // amplification on 10 M x 64 B).
-__global__ void __launch_bounds__(256) demux_gather_kernel(
+__global__ void __launch_bounds__(256, P2PT_COPY_MIN_BLOCKS) demux_gather_kernel(
     u64 n, const u64* __restrict__ misc, const DemuxBufs bufs,
     const p2pt_desc* __restrict__ desc, const uint8_t* __restrict__ in,
     uint8_t* __restrict__ gathered, u64 gathered_cap, const uint32_t* __restrict__ k_out, uint32_t max_streams,

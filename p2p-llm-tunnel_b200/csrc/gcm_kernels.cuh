@@ -49,7 +49,8 @@ struct GlobalLut {   // setup kernels only (key expansion): plain global table
 // Measured on B200 (round 1): moving the byte-0 / byte-3 index arithmetic to the FMA pipe
 // (IMAD / IMAD.WIDE with run-time multipliers) took the ALU pipe from 630 to 550 instructions per
 // block but made the kernel 9 % SLOWER (3.89 -> 4.25 ms per 1 M records): the extra instructions
-// cost more issue slots than the ALU relief buys.  Kept behind a switch, off.
+// cost more issue slots than the ALU relief buys.  Moving only the byte-3 extraction (value 2: one PRMT ->
+// IMAD.WIDE + IMAD, a quarter of the look-ups) is still 3 % slower (3.74 -> 3.85 ms).  Kept behind a switch, off.
 #ifndef P2PT_FMA_EXTRACT
 #define P2PT_FMA_EXTRACT 0
 #endif
@@ -64,7 +65,7 @@ struct SmemLut {     // hot path: bank-replicated shared-memory tables
         // address = base | byte_K(w) << 8 | lane << 2
         uint32_t idx;
 #if P2PT_FMA_EXTRACT
-        if (K == 0) {            // ((w << 24) * 2^16 + (lb << 32)) >> 32 = (byte0 << 8) + lb, via IMAD + IMAD.WIDE
+        if (K == 0 && P2PT_FMA_EXTRACT == 1) {            // ((w << 24) * 2^16 + (lb << 32)) >> 32 = (byte0 << 8) + lb, via IMAD + IMAD.WIDE
             const uint32_t t = w * m24;
             const unsigned long long r = (unsigned long long)t * m16 + ((unsigned long long)lb << 32);
             idx = (uint32_t)(r >> 32);
