@@ -106,7 +106,12 @@ uint64_t    p2pt_launch_count(p2pt_ctx* ctx);
  * (4, 8, 16 or 32; 0 = library default).  "chunk_bytes": size of the pieces in which host-pointer
  * calls overlap host->device copies, kernels and device->host copies (default 16 MiB).  "blocking_sync":
  * 1 (default) = host-pointer calls sleep while they wait for the GPU, 0 = they spin (lowest latency for
- * single small frames, but a spinning thread per call starves other workers on a busy host). */
+ * single small frames, but a spinning thread per call starves other workers on a busy host).
+ * "small_call_bytes" (default 65536, 0 = off, at most 262144): p2pt_frame_encode_batch,
+ * p2pt_frame_decode_batch, the two dtls_gcm calls and p2pt_pipeline_seal / _open whose staged inputs and
+ * outputs fit this many bytes - the reference's per-frame call sites, batches of one or a few - run out
+ * of a mapped pinned buffer: one kernel launch and one (spinning) stream wait, no copies; about half the
+ * latency of the copy path for a single 64-byte frame. */
 int32_t     p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value);
 /* read-only facts: "sm_count", "lut_slack", "gcm_group_width", "n_sessions", "gcm_threads"; -1 if unknown */
 int64_t     p2pt_ctx_get_info(p2pt_ctx* ctx, const char* name);

@@ -57,6 +57,15 @@ struct p2pt_ctx {
     uint32_t lut_slack = 0;        // bytes needed in front of the T-tables to reach 64 KiB alignment
     int gcm_g = 0;                 // forced group width (env P2PT_GCM_G), 0 = heuristic
     int occ_encode = 4, occ_gather = 4;   // resident blocks per SM of the two copy kernels (set at create)
+    // Small host-pointer calls (the reference's per-frame encode / decode / seal / open call sites, batch of
+    // one or a few): inputs are staged into a mapped pinned buffer the kernel reads over PCIe and results
+    // come back the same way, so the call is one launch + one stream sync instead of up to eight copies.
+    uint8_t* zc_host = nullptr;    // host address of the mapped buffer
+    uint8_t* zc_dev = nullptr;     // device alias
+    size_t zc_cap = 0;
+    uint64_t small_call_bytes = 64u << 10;   // staging footprint up to which a call takes this path (0 = never)
+    struct PendingOut { void* dst; const void* src; size_t bytes; };
+    std::vector<PendingOut> zc_pending;
 };
 
 static std::string g_create_err;
@@ -163,6 +172,45 @@ static T* arena_take(p2pt_ctx* ctx, size_t count) {
     return p;
 }
 static size_t pad256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+// Staging for the inputs and outputs of one host-pointer call: the device arena + async copies, or,
+// when everything fits small_call_bytes, the mapped pinned buffer + plain memcpy (see p2pt_ctx).
+// Caller holds ctx->mu.
+struct IoStage {
+    p2pt_ctx* ctx;
+    bool zc = false;
+    size_t zc_used = 0;
+    int32_t reserve(size_t bytes) {
+        zc = ctx->zc_host && ctx->small_call_bytes && bytes <= ctx->small_call_bytes && bytes <= ctx->zc_cap;
+        ctx->zc_pending.clear();
+        return zc ? P2PT_OK : arena_reserve(ctx, bytes);
+    }
+    template <class T> T* take(size_t count) {
+        if (!zc) return arena_take<T>(ctx, count);
+        T* p = reinterpret_cast<T*>(ctx->zc_dev + zc_used);
+        zc_used += pad256(count * sizeof(T));
+        return p;
+    }
+    cudaError_t in(void* d, const void* h, size_t bytes, cudaStream_t st) {
+        if (!zc) return cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, st);
+        memcpy(ctx->zc_host + ((uint8_t*)d - ctx->zc_dev), h, bytes);
+        return cudaSuccess;
+    }
+    cudaError_t out(void* h, const void* d, size_t bytes, cudaStream_t st) {
+        if (!zc) return cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, st);
+        ctx->zc_pending.push_back({h, ctx->zc_host + ((const uint8_t*)d - ctx->zc_dev), bytes});
+        return cudaSuccess;
+    }
+    // wait for the call's work on st and deliver the staged results
+    cudaError_t finish(cudaStream_t st) {
+        if (!zc) return wait_stream(ctx, st);
+        cudaError_t e = cudaStreamSynchronize(st);        // a spin wait: these calls last microseconds
+        if (e != cudaSuccess) return e;
+        for (const auto& o : ctx->zc_pending) memcpy(o.dst, o.src, o.bytes);
+        ctx->zc_pending.clear();
+        return cudaSuccess;
+    }
+};
 
 // ---- launch helpers --------------------------------------------------------------------------------
 static inline void count_launch(p2pt_ctx* ctx, int k = 1) { ctx->launches.fetch_add((uint64_t)k, std::memory_order_relaxed); }
@@ -307,6 +355,18 @@ int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
     CUDA_TRY(nullptr, cudaStreamSynchronize(ctx->streams[0]));
     cudaFree(d_probe);
     ctx->lut_slack = (0x10000u - (sb & 0xffffu)) & 0xffffu;
+    {
+        void* h = nullptr; void* d = nullptr;
+        const size_t cap = 256u << 10;
+        if (cudaHostAlloc(&h, cap, cudaHostAllocMapped) == cudaSuccess) {
+            if (cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess) {
+                ctx->zc_host = (uint8_t*)h; ctx->zc_dev = (uint8_t*)d; ctx->zc_cap = cap;
+            } else {
+                cudaFreeHost(h);
+            }
+        }
+        (void)cudaGetLastError();      // without mapped memory the small-call path is simply off
+    }
     CUDA_TRY(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_encode, frame_encode_kernel, 256, 0));
     CUDA_TRY(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_gather, demux_gather_kernel, 256, 0));
     if (ctx->occ_encode < 1) ctx->occ_encode = 1;
@@ -332,6 +392,7 @@ int32_t p2pt_ctx_destroy(p2pt_ctx* ctx) {
         if (ctx->keys_local) cudaFree(ctx->keys_local);
         if (ctx->keys_remote) cudaFree(ctx->keys_remote);
         if (ctx->arena.base) cudaFree(ctx->arena.base);
+        if (ctx->zc_host) cudaFreeHost(ctx->zc_host);
     }
     delete ctx;
     return P2PT_OK;
@@ -370,6 +431,12 @@ int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
     }
     if (strcmp(name, "blocking_sync") == 0) {
         ctx->blocking_sync = value != 0;
+        return P2PT_OK;
+    }
+    if (strcmp(name, "small_call_bytes") == 0) {
+        if (value < 0 || (uint64_t)value > ctx->zc_cap) return set_err(ctx, P2PT_ERR_ARG, "small_call_bytes must be 0 .. 262144");
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        ctx->small_call_bytes = (uint64_t)value;
         return P2PT_OK;
     }
     if (strcmp(name, "chunk_bytes") == 0) {
@@ -776,32 +843,33 @@ int32_t p2pt_frame_encode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* types,
     cudaStream_t st = ctx->streams[0];
     const size_t pbytes = pay_off[n] - pay_off[0], obytes = out_off[n] - out_off[0];
     if (pbytes && !payload) return set_err(ctx, P2PT_ERR_ARG, "frame_encode: null payload");
-    if (int32_t r = arena_reserve(ctx, pad256(n) + pad256(4 * n) + 2 * pad256(8 * (n + 1)) + pad256(pbytes) + pad256(obytes) + 4096)) return r;
-    uint8_t* d_types = arena_take<uint8_t>(ctx, n);
-    uint32_t* d_sids = arena_take<uint32_t>(ctx, n);
-    uint64_t* d_po = arena_take<uint64_t>(ctx, n + 1);
-    uint64_t* d_oo = arena_take<uint64_t>(ctx, n + 1);
-    uint8_t* d_pay = arena_take<uint8_t>(ctx, pbytes + 1);
-    uint8_t* d_out = arena_take<uint8_t>(ctx, obytes + 1);
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_types, types, n, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_sids, sids, 4 * n, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_po, pay_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_oo, out_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
-    if (pbytes) CUDA_TRY(ctx, cudaMemcpyAsync(d_pay, payload + pay_off[0], pbytes, cudaMemcpyHostToDevice, st));
+    IoStage io{ctx};
+    if (int32_t r = io.reserve(pad256(n) + pad256(4 * n) + 2 * pad256(8 * (n + 1)) + pad256(pbytes + 1) + pad256(obytes + 1) + 4096)) return r;
+    uint8_t* d_types = io.take<uint8_t>(n);
+    uint32_t* d_sids = io.take<uint32_t>(n);
+    uint64_t* d_po = io.take<uint64_t>(n + 1);
+    uint64_t* d_oo = io.take<uint64_t>(n + 1);
+    uint8_t* d_pay = io.take<uint8_t>(pbytes + 1);
+    uint8_t* d_out = io.take<uint8_t>(obytes + 1);
+    CUDA_TRY(ctx, io.in(d_types, types, n, st));
+    CUDA_TRY(ctx, io.in(d_sids, sids, 4 * n, st));
+    CUDA_TRY(ctx, io.in(d_po, pay_off, 8 * (n + 1), st));
+    CUDA_TRY(ctx, io.in(d_oo, out_off, 8 * (n + 1), st));
+    if (pbytes) CUDA_TRY(ctx, io.in(d_pay, payload + pay_off[0], pbytes, st));
     if (int32_t r = p2pt_frame_encode_batch_device(ctx, n, d_types, d_sids, d_pay - pay_off[0], d_po,
                                                    d_out - out_off[0], d_oo, st)) return r;
     // only the bytes the frames cover are defined; gaps between slots keep the caller's contents
     bool dense = true;
     for (uint64_t i = 0; i < n && dense; i++) dense = (out_off[i + 1] - out_off[i] == 5 + (pay_off[i + 1] - pay_off[i]));
     if (dense) {
-        CUDA_TRY(ctx, cudaMemcpyAsync(out + out_off[0], d_out, obytes, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, io.out(out + out_off[0], d_out, obytes, st));
     } else {
         for (uint64_t i = 0; i < n; i++) {
             const size_t len = 5 + (pay_off[i + 1] - pay_off[i]);
-            CUDA_TRY(ctx, cudaMemcpyAsync(out + out_off[i], d_out + (out_off[i] - out_off[0]), len, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(ctx, io.out(out + out_off[i], d_out + (out_off[i] - out_off[0]), len, st));
         }
     }
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, io.finish(st));
     return P2PT_OK;
 }
 
@@ -815,15 +883,16 @@ int32_t p2pt_frame_decode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, co
     cudaStream_t st = ctx->streams[0];
     const size_t ibytes = in_off[n] - in_off[0];
     if (ibytes && !in) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: null input");
-    if (int32_t r = arena_reserve(ctx, pad256(8 * (n + 1)) + pad256(ibytes) + pad256(24 * n) + 4096)) return r;
-    uint64_t* d_io = arena_take<uint64_t>(ctx, n + 1);
-    uint8_t* d_in = arena_take<uint8_t>(ctx, ibytes + 1);
-    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_io, in_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
-    if (ibytes) CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in + in_off[0], ibytes, cudaMemcpyHostToDevice, st));
+    IoStage io{ctx};
+    if (int32_t r = io.reserve(pad256(8 * (n + 1)) + pad256(ibytes + 1) + pad256(24 * n) + 4096)) return r;
+    uint64_t* d_io = io.take<uint64_t>(n + 1);
+    uint8_t* d_in = io.take<uint8_t>(ibytes + 1);
+    p2pt_desc* d_desc = io.take<p2pt_desc>(n);
+    CUDA_TRY(ctx, io.in(d_io, in_off, 8 * (n + 1), st));
+    if (ibytes) CUDA_TRY(ctx, io.in(d_in, in + in_off[0], ibytes, st));
     if (int32_t r = p2pt_frame_decode_batch_device(ctx, n, d_in - in_off[0], d_io, d_desc, st)) return r;
-    CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, io.out(desc, d_desc, 24 * n, st));
+    CUDA_TRY(ctx, io.finish(st));
     return P2PT_OK;
 }
 
@@ -918,35 +987,36 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
     std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
     const size_t ibytes = c.in_off[n] - c.in_off[0], obytes = c.out_off[n] - c.out_off[0];
-    if (int32_t r = arena_reserve(ctx, pad256(4 * n) + pad256(8 * n) + 2 * pad256(8 * (n + 1)) + pad256(ibytes) +
-                                           pad256(obytes) + pad256(n) + pad256(4 * n) + pad256(2 * n) + pad256(8 * n) +
+    IoStage io{ctx};
+    if (int32_t r = io.reserve(pad256(4 * n) + pad256(8 * n) + 2 * pad256(8 * (n + 1)) + pad256(ibytes + 1) +
+                                           pad256(obytes + 1) + pad256(n) + pad256(4 * n) + pad256(2 * n) + pad256(8 * n) +
                                            pad256(n) + pad256(4 * n) + pad256(24 * n) + 16384)) return r;
-    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
-    uint8_t* d_nonce = arena_take<uint8_t>(ctx, 8 * n);
-    uint64_t* d_io = arena_take<uint64_t>(ctx, n + 1);
-    uint64_t* d_oo = arena_take<uint64_t>(ctx, n + 1);
-    uint8_t* d_in = arena_take<uint8_t>(ctx, ibytes + 1);
-    uint8_t* d_out = arena_take<uint8_t>(ctx, obytes + 1);
-    uint8_t* d_status = arena_take<uint8_t>(ctx, n);
-    uint32_t* d_olen = arena_take<uint32_t>(ctx, n);
-    uint16_t* d_epoch = arena_take<uint16_t>(ctx, n);
-    uint64_t* d_seq = arena_take<uint64_t>(ctx, n);
-    uint8_t* d_types = arena_take<uint8_t>(ctx, n);
-    uint32_t* d_sids = arena_take<uint32_t>(ctx, n);
-    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
+    uint32_t* d_sess = io.take<uint32_t>(n);
+    uint8_t* d_nonce = io.take<uint8_t>(8 * n);
+    uint64_t* d_io = io.take<uint64_t>(n + 1);
+    uint64_t* d_oo = io.take<uint64_t>(n + 1);
+    uint8_t* d_in = io.take<uint8_t>(ibytes + 1);
+    uint8_t* d_out = io.take<uint8_t>(obytes + 1);
+    uint8_t* d_status = io.take<uint8_t>(n);
+    uint32_t* d_olen = io.take<uint32_t>(n);
+    uint16_t* d_epoch = io.take<uint16_t>(n);
+    uint64_t* d_seq = io.take<uint64_t>(n);
+    uint8_t* d_types = io.take<uint8_t>(n);
+    uint32_t* d_sids = io.take<uint32_t>(n);
+    p2pt_desc* d_desc = io.take<p2pt_desc>(n);
 
     cudaStream_t s0 = ctx->streams[0];
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_io, c.in_off, 8 * (n + 1), cudaMemcpyHostToDevice, s0));
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_oo, c.out_off, 8 * (n + 1), cudaMemcpyHostToDevice, s0));
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, c.session, 4 * n, cudaMemcpyHostToDevice, s0));
-    if (seal) CUDA_TRY(ctx, cudaMemcpyAsync(d_nonce, c.nonce8, 8 * n, cudaMemcpyHostToDevice, s0));
+    CUDA_TRY(ctx, io.in(d_io, c.in_off, 8 * (n + 1), s0));
+    CUDA_TRY(ctx, io.in(d_oo, c.out_off, 8 * (n + 1), s0));
+    CUDA_TRY(ctx, io.in(d_sess, c.session, 4 * n, s0));
+    if (seal) CUDA_TRY(ctx, io.in(d_nonce, c.nonce8, 8 * n, s0));
     if (c.mode == kPipeSeal) {
-        CUDA_TRY(ctx, cudaMemcpyAsync(d_epoch, c.epoch, 2 * n, cudaMemcpyHostToDevice, s0));
-        CUDA_TRY(ctx, cudaMemcpyAsync(d_seq, c.seq48, 8 * n, cudaMemcpyHostToDevice, s0));
-        CUDA_TRY(ctx, cudaMemcpyAsync(d_types, c.types, n, cudaMemcpyHostToDevice, s0));
-        CUDA_TRY(ctx, cudaMemcpyAsync(d_sids, c.sids, 4 * n, cudaMemcpyHostToDevice, s0));
+        CUDA_TRY(ctx, io.in(d_epoch, c.epoch, 2 * n, s0));
+        CUDA_TRY(ctx, io.in(d_seq, c.seq48, 8 * n, s0));
+        CUDA_TRY(ctx, io.in(d_types, c.types, n, s0));
+        CUDA_TRY(ctx, io.in(d_sids, c.sids, 4 * n, s0));
     }
-    CUDA_TRY(ctx, cudaEventRecord(ctx->events[0], s0));
+    if (!io.zc) CUDA_TRY(ctx, cudaEventRecord(ctx->events[0], s0));     // the other streams wait for the metadata
 
     const int G = pick_group(ctx, n, ibytes);
     // chunk so that each chunk moves ~16 MiB of input
@@ -960,10 +1030,10 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
     for (uint64_t r0 = 0; r0 < n; r0 += chunk, si = (si + 1) % kStreams) {
         const uint64_t r1 = r0 + chunk < n ? r0 + chunk : n, m = r1 - r0;
         cudaStream_t st = ctx->streams[si];
-        if (si != 0 || r0 == 0) CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[0], 0));
+        if (!io.zc && (si != 0 || r0 == 0)) CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[0], 0));
         const size_t ib0 = c.in_off[r0] - c.in_off[0], ib1 = c.in_off[r1] - c.in_off[0];
         const size_t ob0 = c.out_off[r0] - c.out_off[0], ob1 = c.out_off[r1] - c.out_off[0];
-        if (ib1 > ib0) CUDA_TRY(ctx, cudaMemcpyAsync(d_in + ib0, c.in + c.in_off[r0], ib1 - ib0, cudaMemcpyHostToDevice, st));
+        if (ib1 > ib0) CUDA_TRY(ctx, io.in(d_in + ib0, c.in + c.in_off[r0], ib1 - ib0, st));
         GcmArgs a = {};
         a.n = m; a.session = d_sess + r0; a.n_sessions = ctx->n_sessions;
         a.keys = seal ? ctx->keys_local : ctx->keys_remote;
@@ -981,12 +1051,16 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
             default: r = launch_gcm<kPipeOpen>(ctx, a, G, st); break;
         }
         if (r) return r;
-        if (ob1 > ob0) CUDA_TRY(ctx, cudaMemcpyAsync(c.out + c.out_off[r0], d_out + ob0, ob1 - ob0, cudaMemcpyDeviceToHost, st));
-        if (c.status) CUDA_TRY(ctx, cudaMemcpyAsync(c.status + r0, d_status + r0, m, cudaMemcpyDeviceToHost, st));
-        if (c.mode == kOpen) CUDA_TRY(ctx, cudaMemcpyAsync(c.out_len + r0, d_olen + r0, 4 * m, cudaMemcpyDeviceToHost, st));
-        if (c.mode == kPipeOpen) CUDA_TRY(ctx, cudaMemcpyAsync(c.desc + r0, d_desc + r0, 24 * m, cudaMemcpyDeviceToHost, st));
+        if (ob1 > ob0) CUDA_TRY(ctx, io.out(c.out + c.out_off[r0], d_out + ob0, ob1 - ob0, st));
+        if (c.status) CUDA_TRY(ctx, io.out(c.status + r0, d_status + r0, m, st));
+        if (c.mode == kOpen) CUDA_TRY(ctx, io.out(c.out_len + r0, d_olen + r0, 4 * m, st));
+        if (c.mode == kPipeOpen) CUDA_TRY(ctx, io.out(c.desc + r0, d_desc + r0, 24 * m, st));
     }
-    for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, wait_stream(ctx, ctx->streams[i]));
+    if (io.zc) {
+        CUDA_TRY(ctx, io.finish(s0));                                    // a small call is one chunk on stream 0
+    } else {
+        for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, wait_stream(ctx, ctx->streams[i]));
+    }
     // pipe-open descriptors are relative to the caller's `out`, which is how the kernel wrote them
     return P2PT_OK;
 }

@@ -87,6 +87,59 @@ def test_crypto_gcm_mirror(ctx):
     assert a2.decrypt(r1) == a2.decrypt(r2) == r1[:13] + payload
 
 
+def test_small_calls_take_the_mapped_buffer_and_match_the_copy_path(ctx):
+    """Host-pointer calls whose staging fits `small_call_bytes` (default 64 KiB) run out of a mapped pinned
+    buffer - one launch, one sync, no copies; the option set to 0 forces the device-arena path.  Both must
+    give the same bytes for encode, decode, seal, open and the fused calls, ragged sizes included."""
+    from p2p_llm_tunnel_b200 import workload
+    from p2p_llm_tunnel_b200.dtls import record_header
+    rng = np.random.default_rng(0x5EED0007)
+    keys, ivs = workload.sessions_keys(8)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    for n in (1, 2, 17):
+        lens = rng.integers(0, 300, n).astype(np.uint64)
+        lens[0] = 64
+        pay_off = np.zeros(n + 1, np.uint64); np.cumsum(lens, out=pay_off[1:])
+        payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+        types = rng.choice(np.array([10, 11, 12, 20, 21, 22, 99], np.uint8), n)
+        sids = rng.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
+        session = rng.integers(0, 8, n).astype(np.uint32)
+        epoch = np.ones(n, np.uint16); seq = np.arange(n, dtype=np.uint64)
+        nonce = rng.integers(0, 256, 8 * n, dtype=np.uint8)
+        got = {}
+        for mode in (65536, 0):
+            ctx.set_option("small_call_bytes", mode)
+            frames, foff = ctx.frame_encode(types, sids, payload, pay_off)
+            desc = ctx.frame_decode(frames, foff)
+            rec, roff, st = ctx.pipeline_seal(session, epoch, seq, nonce, types, sids, payload, pay_off)
+            out, _, desc2 = ctx.pipeline_open(session, rec, roff)
+            raw_off = np.zeros(n + 1, np.uint64); np.cumsum(lens + np.uint64(13), out=raw_off[1:])
+            raw = np.concatenate([np.frombuffer(record_header(23, 1, i, int(lens[i])), np.uint8).tolist() +
+                                  payload[int(pay_off[i]):int(pay_off[i + 1])].tolist() for i in range(n)]).astype(np.uint8)
+            rec3, roff3, st3 = ctx.dtls_seal(session, nonce, raw, raw_off)
+            out3, _, olen3, st4 = ctx.dtls_open(session, rec3, roff3)
+            got[mode] = dict(frames=frames, desc=desc, rec=rec, st=st, out=out, desc2=desc2,
+                             rec3=rec3, st3=st3, out3=out3, olen3=olen3, st4=st4)
+        ctx.set_option("small_call_bytes", 65536)
+        for k in got[0]:
+            if k in ("out", "out3"):        # an opened record is 24 bytes shorter than its slot; the rest is undefined
+                ro = roff if k == "out" else roff3
+                for i in range(n):
+                    a, b = int(ro[i]), int(ro[i + 1]) - 24
+                    assert np.array_equal(got[0][k][a:b], got[65536][k][a:b]), (k, i)
+            else:
+                assert np.array_equal(got[0][k], got[65536][k]), k
+        assert not got[0]["st"].any() and not got[0]["st3"].any() and not got[0]["st4"].any()
+        assert not got[0]["desc2"]["status"].any() and np.array_equal(got[0]["desc2"]["stream_id"], sids)
+        for i in range(n):
+            a, L = int(got[0]["olen3"][i]), int(lens[i])
+            assert a == 13 + L
+            o = int(roff3[i])
+            assert np.array_equal(got[0]["out3"][o + 13:o + a], payload[int(pay_off[i]):int(pay_off[i + 1])])
+    with pytest.raises(Exception):
+        ctx.set_option("small_call_bytes", 1 << 30)
+
+
 def test_device_pointer_entry_points(ctx):
     import torch
     from p2p_llm_tunnel_b200 import workload
