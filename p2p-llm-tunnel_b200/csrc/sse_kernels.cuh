@@ -22,6 +22,35 @@ __device__ __forceinline__ uint32_t lf_pairs16(const uint4& v, uint32_t prev_byt
     return m & ((m << 1) | (prev_byte == 10u ? 1u : 0u)) & 0xffffu;
 }
 
+// keep bytes [lo, hi) of v, zero the others (0 <= lo <= hi <= 16); zero is not '\n'
+__device__ __forceinline__ uint4 keep_bytes16(const uint4& v, int lo, int hi) {
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int l = lo - 4 * k, h = hi - 4 * k;                        // range inside this word
+        const uint32_t ml = l <= 0 ? 0xffffffffu : l >= 4 ? 0u : (0xffffffffu << (8 * l));
+        const uint32_t mh = h >= 4 ? 0xffffffffu : h <= 0 ? 0u : (0xffffffffu >> (32 - 8 * h));
+        w[k] &= ml & mh;
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// does an event that starts at body + pos read `data: [DONE]\n\n`?  Byte 6 tells `data: [` from `data: {`,
+// so ordinary events cost one byte load.
+__device__ __forceinline__ bool sse_is_done_event(const uint8_t* __restrict__ body, u64 pos, u64 stream_end) {
+    if (stream_end - pos < 14 || __ldg(body + pos + 6) != (uint8_t)'[') return false;
+    const char* D = "data: [DONE]\n\n";
+    bool eq = true;
+    for (int q = 0; q < 14; q++) eq &= (__ldg(body + pos + q) == (uint8_t)D[q]);
+    return eq;
+}
+
+// One warp per stream; the stream is walked in groups of kSseRows rows of 512 bytes whose ALIGNED 16-byte
+// loads are all issued before the first is used (one vector per lane and row; a vector that sticks out of
+// the stream is masked, never byte-loaded).  The count pass only sums; the emit pass needs each lane's
+// exclusive event index, two rows share one 5-step shuffle scan (16-bit fields).
+constexpr int kSseRows = 4;
+
 template <bool EMIT>
 __global__ void __launch_bounds__(256) sse_scan_kernel(u64 k, const uint8_t* __restrict__ body, const u64* __restrict__ body_off,
                                                       u64* __restrict__ ev_csr, u64* __restrict__ ev_end, u64 cap,
@@ -31,47 +60,68 @@ __global__ void __launch_bounds__(256) sse_scan_kernel(u64 k, const uint8_t* __r
     for (u64 s = warp; s < k; s += nwarps) {
         const u64 a = __ldg(body_off + s), b = __ldg(body_off + s + 1);
         const uint8_t* lo = body + a; const uint8_t* hi = body + b;
+        const uint8_t* row0 = lo - ((uintptr_t)lo & 15);                  // aligned start of the first row
         u64 count = 0;
+        uint32_t lane_count = 0;
         const u64 out0 = EMIT ? ev_csr[s] : 0;
         uint32_t carry = 0;                                   // last byte of the previous row (0 at the stream start)
         bool is_done = false;
-        if (EMIT && lane == 0 && b - a >= 14) {               // an event starts at the stream start
-            const char* D = "data: [DONE]\n\n";
-            bool eq = true;
-            for (int q = 0; q < 14; q++) eq &= (__ldg(lo + q) == (uint8_t)D[q]);
-            is_done = eq;
-        }
-        for (u64 row = a; row < b; row += 512) {
-            const uint8_t* p = body + row + 16 * lane;
-            const uint4 v = (p < hi) ? load16_bounded(p, lo, hi) : make_uint4(0, 0, 0, 0);
-            uint32_t prev = __shfl_up_sync(0xffffffffu, v.w >> 24, 1);
-            if (lane == 0) prev = carry;
-            carry = __shfl_sync(0xffffffffu, v.w >> 24, 31);
-            const uint32_t m = lf_pairs16(v, prev);
-            const uint32_t c = __popc(m);
-            uint32_t incl = c;
+        if (EMIT && lane == 0) is_done = sse_is_done_event(body, a, b);   // an event starts at the stream start
+        for (const uint8_t* rp = row0; rp < hi; rp += 512 * kSseRows) {
+            uint4 v[kSseRows];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-            if (EMIT) {
-                u64 slot = out0 + count + (incl - c);
-                uint32_t mm = m;
-                while (mm) {
-                    const int bit = __ffs(mm) - 1; mm &= mm - 1;
-                    const u64 end = row + 16 * lane + bit + 1;            // offset just past the second '\n'
-                    if (slot < cap) ev_end[slot] = end;
-                    slot++;
-                    if (b - end >= 14) {                                   // does the next event read `data: [DONE]`?
-                        const char* D = "data: [DONE]\n\n";
-                        bool eq = true;
-                        for (int q = 0; q < 14; q++) eq &= (__ldg(body + end + q) == (uint8_t)D[q]);
-                        is_done |= eq;
+            for (int r = 0; r < kSseRows; r++) {
+                const uint8_t* p = rp + 512 * r + 16 * lane;
+                v[r] = (p < hi) ? ldg128(p) : make_uint4(0, 0, 0, 0);
+            }
+            uint32_t m[kSseRows], c[kSseRows];
+#pragma unroll
+            for (int r = 0; r < kSseRows; r++) {
+                const uint8_t* p = rp + 512 * r + 16 * lane;
+                if (p < hi && (p < lo || p + 16 > hi))
+                    v[r] = keep_bytes16(v[r], p < lo ? (int)(lo - p) : 0, p + 16 > hi ? (int)(hi - p) : 16);
+                uint32_t prev = __shfl_up_sync(0xffffffffu, v[r].w >> 24, 1);
+                if (lane == 0) prev = carry;
+                carry = __shfl_sync(0xffffffffu, v[r].w >> 24, 31);
+                m[r] = lf_pairs16(v[r], prev);
+                c[r] = __popc(m[r]);
+            }
+            if (!EMIT) {
+#pragma unroll
+                for (int r = 0; r < kSseRows; r++) lane_count += c[r];
+            } else {
+#pragma unroll
+                for (int r2 = 0; r2 < kSseRows; r2 += 2) {
+                    // a row holds at most 512 events, so two rows' inclusive scans fit 16-bit fields
+                    const uint32_t both = c[r2] | (c[r2 + 1] << 16);
+                    uint32_t incl = both;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+                    const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+#pragma unroll
+                    for (int e = 0; e < 2; e++) {
+                        const int r = r2 + e;
+                        const uint32_t inc_r = (incl >> (16 * e)) & 0xffffu;
+                        u64 slot = out0 + count + (inc_r - c[r]);
+                        uint32_t mm = m[r];
+                        const u64 pos0 = (u64)(rp + 512 * r + 16 * lane - body);
+                        while (mm) {
+                            const int bit = __ffs(mm) - 1; mm &= mm - 1;
+                            const u64 end = pos0 + bit + 1;                    // offset just past the second '\n'
+                            if (slot < cap) ev_end[slot] = end;
+                            slot++;
+                            is_done |= sse_is_done_event(body, end, b);        // does the next event read `data: [DONE]`?
+                        }
+                        count += (tot >> (16 * e)) & 0xffffu;
                     }
                 }
             }
-            count += __shfl_sync(0xffffffffu, incl, 31);
         }
-        if (!EMIT) { if (lane == 0) ev_csr[s] = count; }       // per-stream counts, scanned afterwards
-        else {
+        if (!EMIT) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) lane_count += __shfl_xor_sync(0xffffffffu, lane_count, o);
+            if (lane == 0) ev_csr[s] = lane_count;             // per-stream counts, scanned afterwards
+        } else {
             const bool any = __any_sync(0xffffffffu, is_done);
             if (lane == 0) done[s] = any ? 1 : 0;
         }

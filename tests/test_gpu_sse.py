@@ -32,12 +32,15 @@ def test_sse_scan_matches_oracle(ctx):
     streams[8] = b"data: [DONE]\n\n"                   # DONE right at the stream start
     streams[9] = b"prefix data: [DONE]\n\n"            # not at an event start: an event, but not done
     streams[10] = rng.integers(0, 256, 100000, dtype=np.uint8).tobytes()    # binary body
+    streams[11] = b"\n" * 5000                          # every byte but the first closes a pair: 512 events per row
+    streams[12] = b"a" * 511 + b"\n" + b"\n" + b"b" * 1535 + b"\n" + b"\n"     # pairs that straddle row / row-group ends
     body = np.frombuffer(b"".join(streams), np.uint8)
     off = np.concatenate([[0], np.cumsum([len(s) for s in streams])]).astype(np.uint64)
     csr, ends, done = ctx.sse_scan(body, off)
     ecsr, eends, edone = ob.sse_scan(body, off)
     assert np.array_equal(csr, ecsr) and np.array_equal(ends, eends) and np.array_equal(done, edone)
     assert done[8] == 1 and done[5] == 1 and done[6] == 0 and done[9] == 0 and csr[5] - csr[4] == 0
+    assert csr[12] - csr[11] == 4999 and csr[13] - csr[12] == 2
     # events reconstruct: first event of stream 0 parses as JSON
     if csr[1] > csr[0]:
         first = body[int(off[0]):int(ends[int(csr[0])])].tobytes()
