@@ -140,6 +140,44 @@ def test_small_calls_take_the_mapped_buffer_and_match_the_copy_path(ctx):
         ctx.set_option("small_call_bytes", 1 << 30)
 
 
+def test_option_paths_give_the_same_results(ctx):
+    """The non-default code paths behind p2pt_ctx_set_option: the three-launches-per-pass sort (coop_sort 0),
+    host-pointer record calls cut into many chunks over the ctx's four streams (chunk_bytes), and spinning
+    waits (blocking_sync 0) must all reproduce the default path's bytes."""
+    from p2p_llm_tunnel_b200 import workload
+    rng = np.random.default_rng(0x5EED0008)
+    S, n = 64, 20000
+    keys, ivs = workload.sessions_keys(S)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    lens = rng.integers(0, 400, n).astype(np.uint64)
+    pay_off = np.zeros(n + 1, np.uint64); np.cumsum(lens, out=pay_off[1:])
+    payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+    types = rng.choice(np.array([11, 21, 21, 21, 22, 99, 0], np.uint8), n)      # 0: undecodable after open
+    sids = rng.integers(1, 40, n).astype(np.uint32)
+    session = np.sort(rng.integers(0, S, n)).astype(np.uint32)
+    epoch = np.ones(n, np.uint16); seq = np.arange(n, dtype=np.uint64)
+    nonce = rng.integers(0, 256, 8 * n, dtype=np.uint8)
+
+    def run():
+        rec, roff, st = ctx.pipeline_seal(session, epoch, seq, nonce, types, sids, payload, pay_off)
+        out, _, desc = ctx.pipeline_open(session, rec, roff)
+        r = ctx.frame_demux(desc, out, session=session)
+        return dict(rec=rec, st=st, desc=desc, k=np.array([r["k"]]), uniq=r["uniq_sid"], usess=r["uniq_session"],
+                    csr=r["csr"], perm=r["perm"], gathered=r["gathered"], goff=r["gathered_off"])
+
+    base = run()
+    assert not base["st"].any() and (base["desc"]["status"] != 0).sum() == (types == 0).sum()
+    try:
+        for opt, val in (("coop_sort", 0), ("chunk_bytes", 65536), ("blocking_sync", 0)):
+            ctx.set_option(opt, val)
+            got = run()
+            for k2 in base:
+                assert np.array_equal(base[k2], got[k2]), (opt, k2)
+            ctx.set_option(opt, {"coop_sort": 1, "chunk_bytes": 16 << 20, "blocking_sync": 1}[opt])
+    finally:
+        ctx.set_option("coop_sort", 1); ctx.set_option("chunk_bytes", 16 << 20); ctx.set_option("blocking_sync", 1)
+
+
 def test_device_pointer_entry_points(ctx):
     import torch
     from p2p_llm_tunnel_b200 import workload
