@@ -313,14 +313,23 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
     demux_tile(n, lo, hi);
     static_assert(kSortThreads == kRadix, "one thread per digit");
     constexpr int W = kSortThreads / 32;
+    constexpr int kChunk = kSortThreads * kSortItems;
     // Chunks of W x 32 x kSortItems consecutive keys; warp w owns 32 x kSortItems consecutive ones and
-    // takes them in rounds of 32 (lane order = arrival order).  base and wcount are double-buffered by
-    // chunk parity, which saves the block-wide sync after the stores.
-    __shared__ uint32_t base[2][kRadix];       // running output position per digit for this block
-    __shared__ uint32_t wcount[2][W][kRadix];  // per-warp digit counts of the current chunk, then their prefix over warps
+    // takes them in rounds of 32 (lane order = arrival order).  The chunk is first sorted by digit into
+    // shared memory (position = start of the digit inside the chunk + keys of that digit in earlier
+    // warps + rank inside the warp), then written out in that order: neighbouring threads then store
+    // to neighbouring addresses inside a digit's run, whole sectors instead of one partial sector per key
+    // (measured on 10 M keys with 256 evenly used digits: 253 -> 159 us per pass).
+    __shared__ uint32_t wcount[W][kRadix];     // per-warp digit counts of the current chunk, then their prefix over warps
+    __shared__ uint32_t dstart[kRadix];        // first chunk-local position of each digit
+    __shared__ uint32_t gofs[kRadix];          // global position of a key = gofs[digit] + its chunk-local position
     __shared__ uint32_t wtot[W];
+    __shared__ u64 skey[kChunk];
+    __shared__ uint32_t sidx[kChunk];
+    __shared__ uint8_t sdig[kChunk];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int col = threadIdx.x;
+    uint32_t base;                             // running output position of digit `col` for this block
     {
         // exclusive scan of the 256 row totals -> where each digit's output range starts
         const uint32_t v = __ldcg(row_total + threadIdx.x);
@@ -335,12 +344,11 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
         uint32_t wbase = 0;
 #pragma unroll
         for (int w = 0; w < W; w++) wbase += (w < warp) ? wtot[w] : 0u;
-        base[0][col] = wbase + incl - v + __ldcg(hist + (u64)threadIdx.x * kSortBlocks + blockIdx.x);
+        base = wbase + incl - v + __ldcg(hist + (u64)threadIdx.x * kSortBlocks + blockIdx.x);
     }
-    int buf = 0;
-    for (u64 c0 = lo; c0 < hi; c0 += kSortThreads * kSortItems, buf ^= 1) {
+    for (u64 c0 = lo; c0 < hi; c0 += kChunk) {
 #pragma unroll
-        for (int w = 0; w < W; w++) wcount[buf][w][col] = 0;
+        for (int w = 0; w < W; w++) wcount[w][col] = 0;
         u64 key[kSortItems];
         uint32_t ix[kSortItems], d[kSortItems], rank[kSortItems];
         bool live[kSortItems];
@@ -357,7 +365,7 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
             if (live[r])
                 d[r] = pass < kKeyPasses ? (uint32_t)(key[r] >> (8 * pass)) & 0xffu : (__ldg(blen + ix[r]) == kNotDecodable ? 1u : 0u);
         }
-        __syncthreads();                                 // counters zeroed
+        __syncthreads();                                 // counters zeroed; the previous chunk's write-out is done
         // rank among equal digits inside the warp's 32 x kSortItems keys, in arrival order
 #pragma unroll
         for (int r = 0; r < kSortItems; r++) {
@@ -365,25 +373,51 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
             uint32_t peers = 0, before = 0;
             if (live[r]) {
                 peers = __match_any_sync(act, d[r]);
-                before = wcount[buf][warp][d[r]];
+                before = wcount[warp][d[r]];
                 rank[r] = before + __popc(peers & ((1u << lane) - 1));
             }
             __syncwarp();
-            if (live[r] && (peers >> lane) == 1u) wcount[buf][warp][d[r]] = before + __popc(peers);   // highest peer lane
+            if (live[r] && (peers >> lane) == 1u) wcount[warp][d[r]] = before + __popc(peers);   // highest peer lane
             __syncwarp();
         }
         __syncthreads();
-        // exclusive prefix over warps for this thread's digit column; next chunk's base
+        // exclusive prefix over warps for this thread's digit column, then over the digits
         uint32_t run = 0;
 #pragma unroll
-        for (int w = 0; w < W; w++) { const uint32_t t = wcount[buf][w][col]; wcount[buf][w][col] = run; run += t; }
-        base[buf ^ 1][col] = base[buf][col] + run;
+        for (int w = 0; w < W; w++) { const uint32_t t = wcount[w][col]; wcount[w][col] = run; run += t; }
+        uint32_t incl = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) wtot[warp] = incl;
+        __syncthreads();
+        {
+            uint32_t wbase = 0;
+#pragma unroll
+            for (int w = 0; w < W; w++) wbase += (w < warp) ? wtot[w] : 0u;
+            const uint32_t ds = wbase + incl - run;
+            dstart[col] = ds;
+            gofs[col] = base - ds;
+            base += run;
+        }
         __syncthreads();
 #pragma unroll
         for (int r = 0; r < kSortItems; r++) {
             if (live[r]) {
-                const uint32_t o = base[buf][d[r]] + wcount[buf][warp][d[r]] + rank[r];
-                keys_out[o] = key[r]; idx_out[o] = ix[r];
+                const uint32_t lp = dstart[d[r]] + wcount[warp][d[r]] + rank[r];
+                skey[lp] = key[r]; sidx[lp] = ix[r]; sdig[lp] = (uint8_t)d[r];
+            }
+        }
+        __syncthreads();
+        const uint32_t cnt = hi - c0 < (u64)kChunk ? (uint32_t)(hi - c0) : (uint32_t)kChunk;
+#pragma unroll
+        for (int r = 0; r < kSortItems; r++) {
+            const uint32_t t = r * kSortThreads + threadIdx.x;
+            if (t < cnt) {
+                const uint32_t o = gofs[sdig[t]] + t;
+                keys_out[o] = skey[t]; idx_out[o] = sidx[t];
             }
         }
     }

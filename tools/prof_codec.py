@@ -16,6 +16,8 @@ P = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
 dev = torch.device("cuda:0")
 ctx = p2pt.Context(0)
+if os.environ.get("COOP_SORT") is not None:
+    ctx.set_option("coop_sort", int(os.environ["COOP_SORT"]))
 w = workload.frames_workload(n, P, sse=(P == 64))
 t = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
 d = {k: t(w[k]) for k in ("types", "sids", "payload", "pay_off", "frame_off")}
