@@ -28,6 +28,8 @@ __global__ void __launch_bounds__(1024) probe(uint32_t* out, uint32_t seed, long
             if (OP == 0) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[c]) : "r"(k1), "r"(k2));
             if (OP == 1) asm volatile("prmt.b32 %0, %0, %1, 0x7604;" : "+r"(a[c]) : "r"(k1));
             if (OP == 2) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[c]) : "r"(k1), "r"(k2));
+            if (OP == 4) { uint32_t m; asm volatile("match.any.sync.b32 %0, %1, 0xffffffff;" : "=r"(m) : "r"(a[c] & 0xffu)); a[c] += m; }
+            if (OP == 5) { a[c] += __ballot_sync(0xffffffffu, a[c] & 1u); }
             if (OP == 3) {   // one LOP3 builds the address (row from the loaded value | base + 4 * lane), like the kernel's single PRMT
                 uint32_t ad;
                 asm volatile("lop3.b32 %0, %1, 0x1f80, %2, 0xea;" : "=r"(ad) : "r"(a[c]), "r"(lane_base));
@@ -67,10 +69,12 @@ int main() {
     float ms[4];
     const double lop3 = run<0>(sms, out, cyc, &ms[0]), prmt = run<1>(sms, out, cyc, &ms[1]);
     const double imadw = run<2>(sms, out, cyc, &ms[2]), lds = run<3>(sms, out, cyc, &ms[3]);
+    float ms2[2];
+    const double match = run<4>(sms, out, cyc, &ms2[0]), ballot = run<5>(sms, out, cyc, &ms2[1]);
     int clk_khz = 0; cudaDeviceGetAttribute(&clk_khz, cudaDevAttrClockRate, 0);
     printf("{\"device\": \"%s\", \"sms\": %d, \"max_sm_clock_mhz\": %.0f, \"warp_inst_per_clk_per_sm\": {\"lop3\": %.3f, \"prmt\": %.3f, "
-           "\"imad_wide\": %.3f, \"lds32\": %.3f}, \"kernel_ms\": {\"lop3\": %.3f, \"prmt\": %.3f, \"imad_wide\": %.3f, \"lds32\": %.3f}, "
+           "\"imad_wide\": %.3f, \"lds32\": %.3f, \"match_any_plus_iadd\": %.3f, \"ballot_plus_2alu\": %.3f}, \"kernel_ms\": {\"lop3\": %.3f, \"prmt\": %.3f, \"imad_wide\": %.3f, \"lds32\": %.3f}, "
            "\"note\": \"32 warps per SM, 8 independent chains per thread, clock64 around 4096 x 8 instructions; 1 CTA of 1024 threads per SM; lds32 = conflict-free LDS.32 with one LOP3 of address math each\"}\n",
-           p.name, sms, clk_khz / 1000.0, lop3, prmt, imadw, lds, ms[0], ms[1], ms[2], ms[3]);
+           p.name, sms, clk_khz / 1000.0, lop3, prmt, imadw, lds, match, ballot, ms[0], ms[1], ms[2], ms[3]);
     return cudaGetLastError() == cudaSuccess ? 0 : 1;
 }
