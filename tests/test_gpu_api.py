@@ -178,6 +178,55 @@ def test_option_paths_give_the_same_results(ctx):
         ctx.set_option("coop_sort", 1); ctx.set_option("chunk_bytes", 16 << 20); ctx.set_option("blocking_sync", 1)
 
 
+def test_gather_capacity_short_buffer_and_wide_offsets(ctx):
+    """p2pt_frame_demux_batch_device with a gather buffer that is too small: nothing is written past
+    gathered_cap (canary), gathered_off[k] still reports the bytes a full gather needs, and the frames that
+    fit are in place.  A gathered_cap >= 4 GiB switches the per-frame destinations to 64-bit words: same
+    bytes as the 32-bit path."""
+    import torch
+    rng = np.random.default_rng(0x5EED0009)
+    n = 5000
+    lens = rng.integers(0, 500, n).astype(np.uint64)
+    pay_off = np.zeros(n + 1, np.uint64); np.cumsum(lens, out=pay_off[1:])
+    payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+    types = np.full(n, 21, np.uint8)
+    sids = rng.integers(1, 30, n).astype(np.uint32)
+    frames, foff = ctx.frame_encode(types, sids, payload, pay_off)
+    desc = ctx.frame_decode(frames, foff)
+    full = ctx.frame_demux(desc, frames, max_streams=64)
+    total = int(full["gathered_off"][full["k"]])
+    assert total == int(pay_off[-1]) and len(full["gathered"]) == total
+    dev = torch.device("cuda:0")
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
+    d_desc, d_frames = t(desc), t(frames)
+    sb = int(ctx.lib.p2pt_frame_demux_scratch_bytes(n))
+    scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
+    uniq = torch.empty(65, dtype=torch.int32, device=dev); csr = torch.empty(65, dtype=torch.int64, device=dev)
+    goff = torch.empty(65, dtype=torch.int64, device=dev); perm = torch.empty(n, dtype=torch.int32, device=dev)
+    k = torch.zeros(1, dtype=torch.int32, device=dev)
+    s = torch.cuda.current_stream().cuda_stream
+    for cap, claim in ((total // 3, total // 3), (total, 1 << 33)):
+        gathered = torch.full((total + 4096,), 0xA5, dtype=torch.uint8, device=dev)
+        ctx.call("p2pt_frame_demux_batch_device", n, d_desc, None, d_frames, 64, uniq, None, csr, perm, k, gathered,
+                 claim, goff, scratch, sb, s)
+        torch.cuda.synchronize()
+        g = gathered.cpu().numpy(); go = goff.cpu().numpy()
+        assert int(k.item()) == full["k"] and int(go[full["k"]]) == total
+        assert np.all(g[cap:] == 0xA5)                                   # nothing past the capacity / the data
+        # every frame whose destination fits is there; a frame that does not fit is left out whole
+        order = np.argsort(sids, kind="stable")
+        dst = np.cumsum(lens[order]) - lens[order]
+        for j in rng.choice(n, 400, replace=False):
+            o, L = int(dst[j]), int(lens[order[j]])
+            src = payload[int(pay_off[order[j]]):int(pay_off[order[j] + 1])]
+            if o + L <= cap:
+                assert np.array_equal(g[o:o + L], src), j
+            else:
+                assert np.all(g[max(o, 0):o + L][max(cap - o, 0):] == 0xA5)
+        if cap == total:
+            assert np.array_equal(g[:total], full["gathered"])
+
+
 def test_device_pointer_entry_points(ctx):
     import torch
     from p2p_llm_tunnel_b200 import workload
