@@ -72,60 +72,61 @@ __device__ __forceinline__ void store_bytes(uint8_t* dst, const uint4& v, int fr
     }
 }
 
+#ifndef P2PT_COPY_BATCH
+#define P2PT_COPY_BATCH 3
+#endif
+constexpr int kCopyBatch = P2PT_COPY_BATCH;
+
+// funnel16 for a shift that is the same in every lane of the warp: the word part of the shift is a
+// (uniform) branch instead of twelve selects
+__device__ __forceinline__ uint4 funnel16_uniform(const uint4& a, const uint4& b, unsigned s) {
+    uint32_t w0, w1, w2, w3, w4;
+    switch (s >> 2) {
+        case 0:  w0 = a.x; w1 = a.y; w2 = a.z; w3 = a.w; w4 = b.x; break;
+        case 1:  w0 = a.y; w1 = a.z; w2 = a.w; w3 = b.x; w4 = b.y; break;
+        case 2:  w0 = a.z; w1 = a.w; w2 = b.x; w3 = b.y; w4 = b.z; break;
+        default: w0 = a.w; w1 = b.x; w2 = b.y; w3 = b.z; w4 = b.w; break;
+    }
+    const unsigned bs = (s & 3) * 8;
+    return make_uint4(__funnelshift_r(w0, w1, bs), __funnelshift_r(w1, w2, bs),
+                      __funnelshift_r(w2, w3, bs), __funnelshift_r(w3, w4, bs));
+}
+
 // Warp-cooperative copy of len bytes, any alignment on either side.  All 32 lanes must call.
-__device__ __forceinline__ void warp_copy_bytes(uint8_t* dst, const uint8_t* src, u64 len, int lane) {
+// Every lane builds whole ALIGNED destination vectors from the two aligned source vectors that cover
+// them (the second one is its neighbour's first and comes out of L1; an earlier version passed it
+// between lanes with eight shuffles and cost 365 instructions per 1200-byte frame, 65 % of the issue
+// slots).  Both source vectors of a whole destination vector hold bytes of the item, so nothing outside
+// the item's own 16-byte blocks is read; the < 16 bytes at either end are copied bytewise.
+__device__ __forceinline__ void warp_copy_bytes(uint8_t* dst, const uint8_t* src, uint32_t len, int lane) {
     if (len < 64) {
-        for (u64 i = lane; i < len; i += 32) dst[i] = __ldg(src + i);
+        for (uint32_t i = lane; i < len; i += 32) dst[i] = __ldg(src + i);
         return;
     }
-    const unsigned head = (unsigned)((16 - ((uintptr_t)dst & 15)) & 15);
-    if ((unsigned)lane < head) dst[lane] = __ldg(src + lane);
+    const uint32_t head = (uint32_t)((16 - ((uintptr_t)dst & 15)) & 15);
+    if ((uint32_t)lane < head) dst[lane] = __ldg(src + lane);
     uint8_t* d2 = dst + head;
     const uint8_t* s2 = src + head;
-    const u64 rem = len - head;
-    u64 nvec = rem >> 4;
+    const uint32_t rem = len - head, nvec = rem >> 4;
     const unsigned s = (unsigned)((uintptr_t)s2 & 15);
     const uint8_t* sa = s2 - s;
-    if (s) {
-        // the second aligned source vector of the last few destination vectors may run past the
-        // end of the source: leave those to the byte tail
-        const uint8_t* send = src + len;
-        u64 safe = (send >= sa + 32) ? (u64)((send - (sa + 32)) >> 4) + 1 : 0;
-        if (nvec > safe) nvec = safe;
-    }
-    // Each aligned source vector is loaded exactly once.  A lane keeps three vectors in flight
-    // (96 per warp pass); its right neighbour's vector comes by shuffle, the neighbour of lane 31
-    // is lane 0's vector of the next group.
-    const u64 nsrc = nvec + (s ? 1 : 0);
+    // kCopyBatch destination vectors per lane and pass, all loads issued before the first store
     const uint4 zero = make_uint4(0, 0, 0, 0);
-    for (u64 base = 0; base < nvec; base += 96) {
-        uint4 v[4];
+    for (uint32_t base = 0; base < nvec; base += 32 * kCopyBatch) {
+        uint4 a[kCopyBatch], b[kCopyBatch];
 #pragma unroll
-        for (int g = 0; g < 3; g++) {
-            const u64 idx = base + 32 * g + lane;
-            v[g] = idx < nsrc ? ldg128_stream(sa + 16 * idx) : zero;
-        }
-        {   // only lane 0's copy of the 4th group is ever used (as lane 31's neighbour in group 2)
-            const u64 idx = base + 96 + lane;
-            v[3] = (s && lane == 0 && idx < nsrc) ? ldg128_stream(sa + 16 * idx) : zero;
+        for (int g = 0; g < kCopyBatch; g++) {
+            const uint32_t j = base + 32 * g + lane;
+            a[g] = j < nvec ? ldg128(sa + 16 * j) : zero;
+            b[g] = (s && j < nvec) ? ldg128(sa + 16 * j + 16) : zero;
         }
 #pragma unroll
-        for (int g = 0; g < 3; g++) {
-            const u64 idx = base + 32 * g + lane;
-            uint4 out = v[g];
-            if (s) {
-                uint4 nb, n0;
-                nb.x = __shfl_down_sync(0xffffffffu, v[g].x, 1); n0.x = __shfl_sync(0xffffffffu, v[g + 1].x, 0);
-                nb.y = __shfl_down_sync(0xffffffffu, v[g].y, 1); n0.y = __shfl_sync(0xffffffffu, v[g + 1].y, 0);
-                nb.z = __shfl_down_sync(0xffffffffu, v[g].z, 1); n0.z = __shfl_sync(0xffffffffu, v[g + 1].z, 0);
-                nb.w = __shfl_down_sync(0xffffffffu, v[g].w, 1); n0.w = __shfl_sync(0xffffffffu, v[g + 1].w, 0);
-                if (lane == 31) nb = n0;
-                out = funnel16(v[g], nb, s);
-            }
-            if (idx < nvec) stg128(d2 + 16 * idx, out);
+        for (int g = 0; g < kCopyBatch; g++) {
+            const uint32_t j = base + 32 * g + lane;
+            if (j < nvec) stg128(d2 + 16 * j, s ? funnel16_uniform(a[g], b[g], s) : a[g]);
         }
     }
-    for (u64 i = (nvec << 4) + lane; i < rem; i += 32) d2[i] = __ldg(s2 + i);
+    for (uint32_t i = (nvec << 4) + lane; i < rem; i += 32) d2[i] = __ldg(s2 + i);
 }
 
 // Four lanes (q = 0..3) copy one short item (any alignment).  For frames of a few dozen to a few

@@ -23,10 +23,15 @@ __device__ __forceinline__ bool msg_type_valid(uint32_t b) {
     return b == 99;
 }
 
-#ifndef P2PT_COPY_MIN_BLOCKS
-#define P2PT_COPY_MIN_BLOCKS 6      // resident 256-thread blocks per SM the two copy kernels are compiled for:
-                                    // 40 registers, 48 warps of loads in flight; measured 4 / 6 / 8 on 1 M x 1200 B:
-                                    // encode 0.55 / 0.52 / 0.53 ms, demux + gather 0.70 / 0.65 / 0.66 ms (8 spills)
+// Resident 256-thread blocks per SM the two copy kernels are compiled for (register budget 64 K / (256 x blocks)).
+// Measured on 1 M x 1200 B with the two-loads-per-vector warp copy, three vectors in flight per lane:
+// encode 0.447 / 0.463 / 0.435 ms at 4 / 5 / 6 blocks; demux + gather 0.573 / 0.588 / 0.588 ms (the gather
+// spills at 40 registers).
+#ifndef P2PT_ENCODE_MIN_BLOCKS
+#define P2PT_ENCODE_MIN_BLOCKS 6
+#endif
+#ifndef P2PT_GATHER_MIN_BLOCKS
+#define P2PT_GATHER_MIN_BLOCKS 4
 #endif
 
 // ---- encode: a warp takes a tile of 8 * rounds consecutive frames (rounds = 1 or 4).  Lane l loads the
@@ -35,7 +40,7 @@ __device__ __forceinline__ bool msg_type_valid(uint32_t b) {
 // else frame after frame with all 32 lanes (aligned 16-byte vectors either way).  Tiles of 32 amortise
 // the metadata latency over four times the frames; the host picks them when the batch is large enough
 // that every warp still gets many tiles (copy_tile_rounds), else the last warps would run alone.
-__global__ void __launch_bounds__(256, P2PT_COPY_MIN_BLOCKS) frame_encode_kernel(
+__global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kernel(
     u64 n, const uint8_t* __restrict__ types, const uint32_t* __restrict__ sids,
     const uint8_t* __restrict__ payload, const u64* __restrict__ pay_off,
     uint8_t* __restrict__ out, const u64* __restrict__ out_off, int rounds) {
@@ -654,7 +659,7 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
 // sector once, and the writes advance one front per stream, which L2 merges into whole lines.  Walking
 // the sorted order instead reads 69-byte frames and 24-byte descriptors at random (measured 4.7x read
 // amplification on 10 M x 64 B).
-__global__ void __launch_bounds__(256, P2PT_COPY_MIN_BLOCKS) demux_gather_kernel(
+__global__ void __launch_bounds__(256, P2PT_GATHER_MIN_BLOCKS) demux_gather_kernel(
     u64 n, const u64* __restrict__ misc, const DemuxBufs bufs,
     const p2pt_desc* __restrict__ desc, const uint8_t* __restrict__ in,
     uint8_t* __restrict__ gathered, u64 gathered_cap, const uint32_t* __restrict__ k_out, uint32_t max_streams,
