@@ -441,9 +441,22 @@ def run_gpu(args):
             t_bi = min(timed(lambda: (up(), down())) for _ in range(3))
             pcie = {"h2d_gbs": nb / t_up / 1e9, "d2h_gbs": nb / t_dn / 1e9, "bidir_each_gbs": nb / t_bi / 1e9,
                     "theoretical_gbs_per_dir": 63.0}
-            del hp, hq, dp, dq
         except Exception as e:
             pcie = {"error": str(e)}
+        if world > 1:
+            # what one GPU gets while ALL ranks copy both ways at once: four back-to-back 1 GiB pairs after a
+            # barrier, slowest rank counts (the ceiling of the end-to-end arm at N GPUs)
+            ok = "error" not in pcie
+            barrier()
+            t_all = 0.0
+            if ok:
+                torch.cuda.synchronize(); t_ = time.perf_counter()
+                for _ in range(4):
+                    up(); down()
+                torch.cuda.synchronize(); t_all = time.perf_counter() - t_
+            t_all = max_over_ranks(t_all)
+            if ok and t_all > 0:
+                pcie["bidir_each_gbs_all_ranks_at_once"] = 4 * nb / t_all / 1e9
 
 
         return e2e_val, e2e_s, e2e_steps, launches_e2e, t_seal, t_open, h2d, d2h, pcie, lat, sub_n, NB
@@ -536,7 +549,9 @@ def run_gpu(args):
                 "one_subbatch_alone_ms": {"pipeline_seal": t_seal * 1e3, "pipeline_open_demux": t_open * 1e3,
                                           "records": sub_n},
                 "pcie": pcie,
-                "frac_of_pcie": (max(h2d, d2h) / e2e_s / 1e9) / pcie["bidir_each_gbs"] if pcie and "bidir_each_gbs" in pcie else None,
+                # against what PCIe delivered per direction with both directions busy (on every rank at once for N > 1)
+                "frac_of_pcie": (max(h2d, d2h) / e2e_s / 1e9) / pcie.get("bidir_each_gbs_all_ranks_at_once", pcie["bidir_each_gbs"])
+                if pcie and "bidir_each_gbs" in pcie else None,
                 "note": f"each step = the same {n}-record batch as {NB} sub-batches of whole sessions through "
                         "p2pt_pipeline_seal then p2pt_pipeline_open_demux (host pointers, pinned memory); 3 seal + 3 open "
                         "worker threads, one p2pt_ctx each; fill and drain of the worker pipeline are inside the timing; "
