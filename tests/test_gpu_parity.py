@@ -315,3 +315,55 @@ def test_pipeline_open_demux_one_call(ctx):
     # the reassembled bodies are the payloads in per-stream arrival order (minus the failed record)
     pay = w["payload"].reshape(w["n"], 700)
     assert np.array_equal(r["gathered"].reshape(-1, 700), pay[r["perm"]])
+
+
+def test_demux_fuzz_against_numpy(ctx):
+    """Randomised descriptor batches straight into p2pt_frame_demux_batch (no encode/decode in front):
+    sizes around the sort's chunk and tile edges, stream ids that use one to four key bytes, heavy skew,
+    optional sessions with their own high bits, undecodable frames, non-body types, empty bodies.  Expected
+    result from numpy: stable sort of the decodable frames by (session, stream id), per-stream body
+    concatenation (serve.rs:120-124)."""
+    from p2p_llm_tunnel_b200._lib import DESC_DTYPE
+    rng = np.random.default_rng(0x5EED000A)
+    sizes = [1, 2, 31, 255, 256, 257, 1023, 1024, 1025, 4095, 4096, 4097, 9999, 70000, 151553, 300000]
+    for case, n in enumerate(sizes * 2):
+        mode = case % 5
+        if mode == 0:   sid = rng.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)          # all four bytes vary
+        elif mode == 1: sid = rng.integers(1, 5, n).astype(np.uint32)                               # four streams
+        elif mode == 2: sid = np.where(rng.random(n) < 0.9, 7, rng.integers(0, 70000, n)).astype(np.uint32)   # 90 % one stream
+        elif mode == 3: sid = (rng.integers(0, 300, n) << 8).astype(np.uint32)                      # low byte constant
+        else:           sid = np.full(n, 0xDEADBEEF, np.uint32)                                     # a single stream
+        session = None
+        if case % 3 == 1:
+            session = (rng.integers(0, 50, n).astype(np.uint32) << 20) | rng.integers(0, 3, n).astype(np.uint32)
+        lens = rng.integers(0, 90, n).astype(np.uint32)
+        lens[rng.random(n) < 0.02] = 0
+        big = rng.random(n) < 0.002
+        lens[big] = rng.integers(257, 2000, int(big.sum()))
+        gap = rng.integers(0, 7, n)
+        pay_off = np.cumsum(np.concatenate([[3], (lens + gap)[:-1]])).astype(np.uint64)             # gaps and odd alignments
+        buf = rng.integers(0, 256, int(pay_off[-1] + lens[-1] + 16), dtype=np.uint8)
+        desc = np.zeros(n, DESC_DTYPE)
+        desc["pay_off"] = pay_off; desc["pay_len"] = lens; desc["stream_id"] = sid
+        desc["msg_type"] = rng.choice(np.array([11, 21, 21, 21, 20, 22, 99], np.uint8), n)
+        desc["status"] = np.where(rng.random(n) < 0.03, rng.integers(1, 3, n), 0).astype(np.uint8)
+        r = ctx.frame_demux(desc, buf, session=session)
+        ok = np.flatnonzero(desc["status"] == 0)
+        key = sid[ok].astype(np.uint64)
+        if session is not None:
+            key |= session[ok].astype(np.uint64) << np.uint64(32)
+        order = ok[np.argsort(key, kind="stable")]
+        skey = np.sort(key, kind="stable")
+        heads = np.flatnonzero(np.concatenate([[True], skey[1:] != skey[:-1]])) if len(ok) else np.zeros(0, np.int64)
+        assert r["k"] == len(heads), (case, n)
+        assert np.array_equal(r["perm"][: len(order)].astype(np.int64), order), (case, n)
+        assert np.array_equal(r["csr"][: r["k"] + 1].astype(np.int64), np.concatenate([heads, [len(ok)]])), (case, n)
+        assert np.array_equal(r["uniq_sid"], (skey[heads] & np.uint64(0xFFFFFFFF)).astype(np.uint32)), (case, n)
+        if session is not None:
+            assert np.array_equal(r["uniq_session"], (skey[heads] >> np.uint64(32)).astype(np.uint32)), (case, n)
+        body = np.where(np.isin(desc["msg_type"][order], (11, 21)), lens[order], 0).astype(np.int64)
+        excl = np.cumsum(body) - body
+        src = np.repeat(pay_off[order].astype(np.int64) - excl, body) + np.arange(int(body.sum()), dtype=np.int64)
+        assert np.array_equal(r["gathered"], buf[src]), (case, n)
+        assert np.array_equal(r["gathered_off"][: r["k"] + 1].astype(np.int64),
+                              np.concatenate([excl[heads] if len(heads) else [], [int(body.sum())]]).astype(np.int64)), (case, n)
