@@ -147,6 +147,10 @@ __device__ __forceinline__ void quad_copy_bytes(uint8_t* dst, const uint8_t* src
         }
         return;
     }
+    // General case: head bytes up to the first aligned destination vector, whole vectors, then words and
+    // bytes.  Two leaner-looking alternatives measured SLOWER on 10 M x 64 B frames at a 69-byte stride
+    // (encode 0.80 ms): aligned destination vectors with piecewise stores at both ends (0.89 ms), and
+    // aligned 32-bit destination words funnelled from two source words (0.88 ms, LSU-bound).
     uint32_t head = (uint32_t)((16 - ((uintptr_t)dst & 15)) & 15);
     if (head > len) head = len;
     for (uint32_t b = q; b < head; b += 4) dst[b] = __ldg(src + b);
