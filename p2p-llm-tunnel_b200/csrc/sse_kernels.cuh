@@ -49,7 +49,10 @@ __device__ __forceinline__ bool sse_is_done_event(const uint8_t* __restrict__ bo
 // loads are all issued before the first is used (one vector per lane and row; a vector that sticks out of
 // the stream is masked, never byte-loaded).  The count pass only sums; the emit pass needs each lane's
 // exclusive event index, two rows share one 5-step shuffle scan (16-bit fields).
-constexpr int kSseRows = 4;
+#ifndef P2PT_SSE_ROWS
+#define P2PT_SSE_ROWS 4          // measured per 1.2 GB of bodies: 2 rows 0.84 ms, 4 rows 0.79 ms, 8 rows 0.91 ms (80 registers)
+#endif
+constexpr int kSseRows = P2PT_SSE_ROWS;
 
 template <bool EMIT>
 __global__ void __launch_bounds__(256) sse_scan_kernel(u64 k, const uint8_t* __restrict__ body, const u64* __restrict__ body_off,

@@ -185,11 +185,15 @@ def bookkeeping_config(n):
                          "note": "two passes (count, emit): algorithmic bytes = 2 x body"}}
 
 
-res = {"hbm_peak_gbs": peak, "host_cores": cores,
-       "bookkeeping_1M_records": bookkeeping_config(1_000_000),
-       "SCTP_1M_messages_1200B": sctp_config(1_000_000, 1200),
-       "C2_1M_frames_1200B_4096_streams": codec_config(1_000_000, 1200, False),
-       "C4_10M_frames_64B_sse": codec_config(10_000_000, 64, True),
-       "C3_1M_records_1200B_1_session": records_config(1_000_000, 1200, 1),
-       "C3_1M_records_1200B_4096_sessions": records_config(1_000_000, 1200, 4096)}
+configs = {"bookkeeping_1M_records": lambda: bookkeeping_config(1_000_000),
+           "SCTP_1M_messages_1200B": lambda: sctp_config(1_000_000, 1200),
+           "C2_1M_frames_1200B_4096_streams": lambda: codec_config(1_000_000, 1200, False),
+           "C4_10M_frames_64B_sse": lambda: codec_config(10_000_000, 64, True),
+           "C3_1M_records_1200B_1_session": lambda: records_config(1_000_000, 1200, 1),
+           "C3_1M_records_1200B_4096_sessions": lambda: records_config(1_000_000, 1200, 4096)}
+only = os.environ.get("ONLY")                      # substring filter, e.g. ONLY=bookkeeping
+res = {"hbm_peak_gbs": peak, "host_cores": cores}
+for name, fn in configs.items():
+    if not only or only in name:
+        res[name] = fn()
 print(json.dumps(res, indent=1))
