@@ -214,7 +214,8 @@ int32_t p2pt_sctp_packetize_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg,
                                   uint64_t* n_pkts_out);
 /* packets (each after `headroom` bytes, 13 when they come out of p2pt_dtls_gcm_open_batch) -> CRC check,
  * chunk parse, and reassembly: fragments are ordered by (session, TSN) (TSNs must not wrap inside a
- * batch, duplicates must have been dropped), messages = runs from a B to an E fragment, their payloads
+ * batch); of several packets with the same (session, TSN) - retransmissions - only the first to arrive
+ * counts, as in webrtc-sctp's reassembly queue; messages = runs from a B to an E fragment, their payloads
  * concatenated into msg with msg_off[n_msgs + 1] -- exactly the (buffer, offsets) input of
  * p2pt_frame_decode_batch.  msg_first[m] = packet index of message m's first fragment (its info gives
  * stream / ssn / ppid); msg_status[m] = OK or SCTP_INCOMPLETE.  info (n entries) is always filled. */

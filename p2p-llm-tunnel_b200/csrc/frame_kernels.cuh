@@ -537,8 +537,11 @@ constexpr u64 demux_emit_blocks(u64 n) { return (n + (u64)kScanThreads * kDemuxI
 
 struct DemuxQuad { u64 key[kDemuxItems]; uint32_t ix[kDemuxItems]; HeadBytes it[kDemuxItems]; HeadBytes sum; };
 
+// first_only: only the first frame of every key contributes body bytes (the SCTP reassembly, where a second
+// packet with the same (session, TSN) is a retransmission to be dropped)
 __device__ __forceinline__ DemuxQuad demux_load_quad(u64 j, u64 m, u64 n, const u64* __restrict__ keys,
-                                                     const uint32_t* __restrict__ idx, const uint32_t* __restrict__ blen) {
+                                                     const uint32_t* __restrict__ idx, const uint32_t* __restrict__ blen,
+                                                     bool first_only) {
     DemuxQuad r;
     if (j + kDemuxItems <= n) {                          // arrays are 256-byte aligned, j is a multiple of 4
         const ulonglong2 k01 = *reinterpret_cast<const ulonglong2*>(keys + j);
@@ -562,7 +565,7 @@ __device__ __forceinline__ DemuxQuad demux_load_quad(u64 j, u64 m, u64 n, const 
         HeadBytes h; h.heads = 0; h.bytes = 0;
         if (j + e < m) {
             h.heads = (j + e == 0 || prev != r.key[e]) ? 1u : 0u;
-            h.bytes = blen[r.ix[e]];                     // the 4 n-byte array stays in L2; the 24-byte descriptors would not
+            h.bytes = (first_only && !h.heads) ? 0u : blen[r.ix[e]];   // the 4 n-byte array stays in L2; the 24-byte descriptors would not
         }
         prev = r.key[e];
         r.it[e] = h;
@@ -573,11 +576,11 @@ __device__ __forceinline__ DemuxQuad demux_load_quad(u64 j, u64 m, u64 n, const 
 
 __global__ void __launch_bounds__(kScanThreads) demux_blocksum_kernel(
     u64 n, const DemuxBufs bufs, const uint32_t* __restrict__ blen,
-    const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes) {
+    const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes, bool first_only) {
     const int fb = demux_src_buffer(misc, kSortPasses);
     const u64 m = demux_valid_count(n, misc);
     const u64 j = ((u64)blockIdx.x * kScanThreads + threadIdx.x) * kDemuxItems;
-    const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen);
+    const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen, first_only);
     HeadBytes tot;
     (void)block_scan_excl(qd.sum, tot);
     if (threadIdx.x == 0) { blk_heads[blockIdx.x] = tot.heads; blk_bytes[blockIdx.x] = tot.bytes; }
@@ -613,13 +616,13 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
     const u64* __restrict__ misc, const uint32_t* __restrict__ blk_heads, const u64* __restrict__ blk_bytes,
     u64 nblk, uint32_t max_streams, uint32_t* __restrict__ uniq_sid, uint32_t* __restrict__ uniq_session,
     u64* __restrict__ csr, uint32_t* __restrict__ perm, uint32_t* __restrict__ k_out,
-    u64* __restrict__ gathered_off, int dst_mode) {                  // 0 none, 1 = 32-bit, 2 = 64-bit offsets
+    u64* __restrict__ gathered_off, int dst_mode, bool first_only) {  // dst_mode: 0 none, 1 = 32-bit, 2 = 64-bit offsets
     const int fb = demux_src_buffer(misc, kSortPasses);
     u64* __restrict__ dst64 = bufs.keys[fb ^ 1];
     uint32_t* __restrict__ dst32 = reinterpret_cast<uint32_t*>(bufs.keys[fb ^ 1]);
     const u64 m = demux_valid_count(n, misc);
     const u64 j = ((u64)blockIdx.x * kScanThreads + threadIdx.x) * kDemuxItems;
-    const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen);
+    const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen, first_only);
     HeadBytes tot;
     HeadBytes ex = block_scan_excl(qd.sum, tot);
     uint32_t heads = blk_heads[blockIdx.x] + ex.heads;
@@ -629,8 +632,9 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
     for (int e = 0; e < kDemuxItems; e++) {
         if (j + e < m) {
             if (j + kDemuxItems > m) perm[j + e] = qd.ix[e];
-            if (dst_mode == 1) dst32[qd.ix[e]] = bytes > 0xffffffffull ? 0xffffffffu : (uint32_t)bytes;
-            else if (dst_mode == 2) dst64[qd.ix[e]] = bytes;
+            const bool skip = first_only && !qd.it[e].heads;      // all-ones = beyond any capacity: the gather leaves it out
+            if (dst_mode == 1) dst32[qd.ix[e]] = (skip || bytes > 0xffffffffull) ? 0xffffffffu : (uint32_t)bytes;
+            else if (dst_mode == 2) dst64[qd.ix[e]] = skip ? ~0ull : bytes;
             if (qd.it[e].heads) {
                 if (heads < max_streams) {
                     uniq_sid[heads] = (uint32_t)qd.key[e];
@@ -679,7 +683,7 @@ __global__ void __launch_bounds__(256, P2PT_GATHER_MIN_BLOCKS) demux_gather_kern
             const p2pt_desc d = desc[i];
             if (d.status == P2PT_ST_OK && (d.msg_type == 11 || d.msg_type == 21) && d.pay_len) {
                 o = dst_mode == 1 ? (u64)dst32[i] : dst64[i];      // a saturated 32-bit offset is beyond any 32-bit cap
-                if (o + d.pay_len <= gathered_cap) { len = d.pay_len; so = d.pay_off; }   // overflow: caller sees it in gathered_off[k]
+                if (o <= gathered_cap && d.pay_len <= gathered_cap - o) { len = d.pay_len; so = d.pay_off; }   // overflow: caller sees it in gathered_off[k]
             }
         }
         if (__all_sync(0xffffffffu, len <= kQuadCopyMax)) {

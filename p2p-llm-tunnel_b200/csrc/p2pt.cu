@@ -510,12 +510,16 @@ int32_t p2pt_frame_decode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t*
 
 uint64_t p2pt_frame_demux_scratch_bytes(uint64_t n) { return demux_scratch_bytes(n ? n : 1); }
 
-int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
-                                      const uint8_t* in,
-                                      uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
-                                      uint64_t* csr, uint32_t* perm,
-                                      uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
-                                      uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes, void* stream) {
+}  // extern "C"
+
+// first_only: see demux_load_quad (the SCTP reassembly drops retransmitted fragments this way)
+static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
+                                 const uint8_t* in,
+                                 uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                 uint64_t* csr, uint32_t* perm,
+                                 uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
+                                 uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes, void* stream,
+                                 bool first_only) {
     if (!ctx) return P2PT_ERR_ARG;
     if (!uniq_sid || !csr || !perm || !k_out) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null output");
     if (n > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: n must fit in 32 bits");
@@ -556,11 +560,11 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     }
     const u64 nblk = demux_emit_blocks(n);
     const int dst_mode = !gathered ? 0 : gathered_cap <= 0xffffffffull ? 1 : 2;
-    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes);
+    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, first_only);
     demux_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, s.blk_heads, s.blk_bytes);
     demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, nblk,
                                                               max_streams, uniq_sid, uniq_session, (u64*)csr, perm, k_out,
-                                                              (u64*)gathered_off, dst_mode);
+                                                              (u64*)gathered_off, dst_mode, first_only);
     count_launch(ctx, 1 + 3);
     if (gathered) {
         const int rounds = copy_tile_rounds(ctx, n, ctx->occ_gather);
@@ -570,6 +574,18 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
     }
     CUDA_TRY(ctx, cudaGetLastError());
     return P2PT_OK;
+}
+
+extern "C" {
+
+int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
+                                      const uint8_t* in,
+                                      uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                      uint64_t* csr, uint32_t* perm,
+                                      uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
+                                      uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes, void* stream) {
+    return demux_device_impl(ctx, n, desc, session, in, max_streams, uniq_sid, uniq_session, csr, perm, k_out, gathered,
+                             gathered_cap, gathered_off, scratch, scratch_bytes, stream, false);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -678,10 +694,12 @@ int32_t p2pt_sctp_reassemble_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const 
     ReasmScratch r = reasm_carve(scratch, n_pkts);
     if (scratch_bytes < r.total) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_reassemble: scratch too small");
     // order the fragments by (session, TSN) and lay their payloads out back to back: the demux does
-    // exactly that with key = desc.stream_id (= TSN, set by the unpack kernel)
-    if (int32_t rc = p2pt_frame_demux_batch_device(ctx, n_pkts, desc, session, in, (uint32_t)n_pkts, r.uniq_tsn,
-                                                   session ? r.uniq_sess : nullptr, r.csr, r.perm, r.k, msg, msg_cap,
-                                                   r.goff, r.demux, r.demux_bytes, st)) return rc;
+    // exactly that with key = desc.stream_id (= TSN, set by the unpack kernel).  first_only: a second packet
+    // with the same (session, TSN) is a retransmission; only the first to arrive contributes its payload
+    // (webrtc-sctp's reassembly queue ignores a chunk whose TSN it already holds)
+    if (int32_t rc = demux_device_impl(ctx, n_pkts, desc, session, in, (uint32_t)n_pkts, r.uniq_tsn,
+                                       session ? r.uniq_sess : nullptr, r.csr, r.perm, r.k, msg, msg_cap,
+                                       r.goff, r.demux, r.demux_bytes, st, true)) return rc;
     CUDA_TRY(ctx, cudaMemsetAsync(msg_status, 0, max_msgs, st));
     const u64 nblk = demux_scan_blocks(n_pkts);
     sctp_bounds_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(r.k, r.perm, (const u64*)r.csr, info, r.blk);

@@ -63,6 +63,44 @@ def test_unpack_reassemble_roundtrip_shuffled_multi_session(ctx):
     assert np.array_equal(r["info"]["ssn"][r["msg_first"]], np.concatenate([np.arange(40)] * S).astype(np.uint16))
 
 
+def test_retransmitted_packets_are_dropped(ctx):
+    """A second packet with the same (session, TSN) is a retransmission: webrtc-sctp's reassembly queue ignores
+    a chunk whose TSN it already holds.  Duplicates of first, middle and last fragments - anywhere in the
+    arrival order, in several sessions - must leave every message byte-identical and complete."""
+    rng = np.random.default_rng(34)
+    S = 5
+    per_sess = [_msgs(rng, 30, 0, 5000) for _ in range(S)]
+    pkts, sess = [], []
+    for s, msgs in enumerate(per_sess):
+        lens = np.array([len(m) for m in msgs])
+        frags = np.maximum(1, -(-lens // 1200))
+        tsn0 = 70000 * (s + 1) + np.concatenate([[0], np.cumsum(frags)[:-1]])
+        pk, off = ob.sctp_packetize(msgs, 10 + s, 20 + s, 99 + s, 1, np.arange(len(msgs)), 53, tsn0)
+        for i in range(len(off) - 1):
+            pkts.append(pk[int(off[i]):int(off[i + 1])].tobytes()); sess.append(s)
+    n0 = len(pkts)
+    dup = rng.choice(n0, n0 // 3, replace=False)                  # a third of the packets arrive twice ...
+    dup = np.concatenate([dup, dup[:20]])                          # ... and twenty of them three times
+    pkts += [pkts[i] for i in dup]; sess += [sess[i] for i in dup]
+    order = rng.permutation(len(pkts))
+    pkts = [pkts[i] for i in order]; sess = np.array(sess, np.uint32)[order]
+    buf, off = _pack(pkts)
+    r = ctx.sctp_unpack_reassemble(buf, off, session=sess)
+    assert not r["info"]["status"].any() and not r["msg_status"].any()
+    assert r["n_msgs"] == sum(len(m) for m in per_sess)
+    flat = [m for msgs in per_sess for m in msgs]
+    for i, m in enumerate(flat):
+        assert r["msg"][int(r["msg_off"][i]):int(r["msg_off"][i + 1])].tobytes() == m, i
+    assert int(r["msg_off"][r["n_msgs"]]) == sum(len(m) for m in flat)            # no duplicate bytes anywhere
+    # msg_first is the FIRST copy to arrive of each message's B fragment
+    first_b = {}
+    for pos in range(len(pkts)):
+        inf = r["info"][pos]
+        if inf["flags"] & 2:
+            first_b.setdefault((int(sess[pos]), int(inf["tsn"])), pos)
+    assert sorted(first_b.values()) == sorted(int(x) for x in r["msg_first"])
+
+
 def test_unpack_flags_bad_packets_and_incomplete_messages(ctx):
     rng = np.random.default_rng(33)
     msgs = [rng.integers(0, 256, 3000, dtype=np.uint8).tobytes() for _ in range(6)]     # 3 fragments each
