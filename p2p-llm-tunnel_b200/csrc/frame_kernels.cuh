@@ -656,6 +656,75 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
     }
 }
 
+// ---- small batches: the whole demux (all but the gather) in ONE block -------------------------------
+// Up to kSmallDemux frames: every thread ranks its frame by counting the decodable frames that sort in
+// front of it (key order, arrival order among equal keys) - n^2 / 1024 broadcast shared-memory reads per
+// thread - and the scan / emit step follows in the same kernel.  A reader loop that drains a few dozen
+// frames per wake-up pays two launches instead of six and no cooperative launch.
+constexpr int kSmallDemux = 1024;
+
+__global__ void __launch_bounds__(kSmallDemux) demux_small_kernel(
+    uint32_t n, const p2pt_desc* __restrict__ desc, const uint32_t* __restrict__ session,
+    uint32_t max_streams, uint32_t* __restrict__ uniq_sid, uint32_t* __restrict__ uniq_session,
+    u64* __restrict__ csr, uint32_t* __restrict__ perm, uint32_t* __restrict__ k_out,
+    u64* __restrict__ gathered_off, u64* __restrict__ dst_buf, int dst_mode, bool first_only) {
+    __shared__ u64 skey[kSmallDemux];
+    __shared__ uint8_t sok[kSmallDemux];
+    __shared__ u64 okey[kSmallDemux];
+    __shared__ uint32_t oidx[kSmallDemux], olen[kSmallDemux];
+    __shared__ uint32_t m_sh;
+    const uint32_t i = threadIdx.x;
+    u64 key = 0; bool ok = false; uint32_t bl = 0;
+    if (i < n) {
+        const p2pt_desc d = desc[i];
+        key = d.stream_id;
+        if (session) key |= (u64)session[i] << 32;
+        ok = d.status == P2PT_ST_OK;
+        bl = (d.msg_type == 11 || d.msg_type == 21) ? d.pay_len : 0u;
+    }
+    skey[i] = key; sok[i] = ok ? 1 : 0;
+    if (i == 0) m_sh = 0;
+    __syncthreads();
+    if (ok) {
+        uint32_t rank = 0;
+        for (uint32_t j = 0; j < n; j++) {
+            const u64 kj = skey[j];
+            rank += (sok[j] && (kj < key || (kj == key && j < i))) ? 1u : 0u;
+        }
+        okey[rank] = key; oidx[rank] = i; olen[rank] = bl;
+        atomicAdd(&m_sh, 1u);
+    }
+    __syncthreads();
+    const uint32_t m = m_sh, s = i;
+    HeadBytes it; it.heads = 0; it.bytes = 0;
+    if (s < m) {
+        it.heads = (s == 0 || okey[s - 1] != okey[s]) ? 1u : 0u;
+        it.bytes = (first_only && !it.heads) ? 0u : olen[s];
+    }
+    HeadBytes tot;
+    const HeadBytes ex = block_scan_excl(it, tot);
+    if (s < m) {
+        const uint32_t ix = oidx[s];
+        perm[s] = ix;
+        const bool skip = first_only && !it.heads;
+        if (dst_mode == 1) reinterpret_cast<uint32_t*>(dst_buf)[ix] = (skip || ex.bytes > 0xffffffffull) ? 0xffffffffu : (uint32_t)ex.bytes;
+        else if (dst_mode == 2) dst_buf[ix] = skip ? ~0ull : ex.bytes;
+        if (it.heads && ex.heads < max_streams) {
+            uniq_sid[ex.heads] = (uint32_t)okey[s];
+            if (uniq_session) uniq_session[ex.heads] = (uint32_t)(okey[s] >> 32);
+            csr[ex.heads] = s;
+            if (gathered_off) gathered_off[ex.heads] = ex.bytes;
+        }
+    }
+    if (i == 0) {
+        *k_out = tot.heads;
+        if (tot.heads <= max_streams) {
+            csr[tot.heads] = m;
+            if (gathered_off) gathered_off[tot.heads] = tot.bytes;
+        }
+    }
+}
+
 // Gather: body frames only (serve.rs:120-124 extend_from_slice).  Same 32-frames-per-warp scheme as
 // the encoder: four lanes per short frame, the whole warp per long one.
 // The frames are walked in ARRIVAL order and written to their place in the stream-grouped output

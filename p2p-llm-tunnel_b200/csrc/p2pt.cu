@@ -44,6 +44,8 @@ struct p2pt_ctx {
     cudaEvent_t events[kStreams] = {};
     cudaEvent_t sync_events[kStreams] = {};   // cudaEventBlockingSync: the host thread sleeps instead of spinning
     bool blocking_sync = true;                // big host-pointer calls wait on sync_events (see wait_stream)
+    bool small_demux = false;                 // batches of up to 1024 frames take the single-block demux kernel (off until verified on the GPU)
+    bool spin_this_call = false;              // set per host-pointer call (under mu): small calls spin instead of sleeping
     bool coop_sort = true;                    // demux sorting passes in one cooperative launch
     std::mutex mu;                 // serialises host-pointer calls (they share the arena)
     std::mutex err_mu;
@@ -144,7 +146,8 @@ __global__ void smem_base_probe_kernel(uint32_t* out) {
 // threads per GPU and several GPUs per host that starves the threads that feed the copy engines, so by
 // default the wait is a blocking-sync event (the thread sleeps until the interrupt).
 static cudaError_t wait_stream(p2pt_ctx* ctx, cudaStream_t st) {
-    if (!ctx->blocking_sync) return cudaStreamSynchronize(st);
+    // a sleeping wait costs a wake-up of 50-100 us; a call that stages a few MB has up to seven of them
+    if (!ctx->blocking_sync || ctx->spin_this_call) return cudaStreamSynchronize(st);
     int idx = 0;
     for (int i = 0; i < kStreams; i++) if (ctx->streams[i] == st) idx = i;
     cudaError_t e = cudaEventRecord(ctx->sync_events[idx], st);
@@ -152,9 +155,13 @@ static cudaError_t wait_stream(p2pt_ctx* ctx, cudaStream_t st) {
     return cudaEventSynchronize(ctx->sync_events[idx]);
 }
 
+// host-pointer calls that stage less than this wait by spinning: they finish in well under a millisecond
+constexpr size_t kSpinWaitBytes = 8u << 20;
+
 // ---- arena -----------------------------------------------------------------------------------------
 static int32_t arena_reserve(p2pt_ctx* ctx, size_t bytes) {
     ctx->arena.used = 0;
+    ctx->spin_this_call = bytes < kSpinWaitBytes;
     if (bytes <= ctx->arena.cap) return P2PT_OK;
     if (ctx->arena.base) cudaFree(ctx->arena.base);
     ctx->arena.base = nullptr;
@@ -429,6 +436,10 @@ int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
         ctx->coop_sort = value != 0;
         return P2PT_OK;
     }
+    if (strcmp(name, "small_demux") == 0) {
+        ctx->small_demux = value != 0;
+        return P2PT_OK;
+    }
     if (strcmp(name, "blocking_sync") == 0) {
         ctx->blocking_sync = value != 0;
         return P2PT_OK;
@@ -537,9 +548,25 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
     if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: scratch must be 256-byte aligned");
     DemuxScratch s = demux_carve(scratch, n);
     CUDA_TRY(ctx, cudaMemsetAsync(s.misc, 0, 32, st));
-    demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc, s.blen);
     DemuxBufs bufs;
     bufs.keys[0] = s.keys[0]; bufs.keys[1] = s.keys[1]; bufs.idx[0] = s.idx[0]; bufs.idx[1] = s.idx[1];
+    if (n <= (uint64_t)kSmallDemux && ctx->small_demux) {
+        // one block does init + sort + scan + emit; misc stays zero, so the gather finds the per-frame
+        // destinations in keys[1] exactly as after a sort without passes
+        const int dst_mode = !gathered ? 0 : gathered_cap <= 0xffffffffull ? 1 : 2;
+        demux_small_kernel<<<1, kSmallDemux, 0, st>>>((uint32_t)n, desc, session, max_streams, uniq_sid, uniq_session,
+                                                      (u64*)csr, perm, k_out, (u64*)gathered_off, s.keys[1], dst_mode, first_only);
+        count_launch(ctx);
+        if (gathered) {
+            const int rounds = copy_tile_rounds(ctx, n, ctx->occ_gather);
+            demux_gather_kernel<<<copy_grid(ctx, n, rounds, ctx->occ_gather), 256, 0, st>>>(n, s.misc, bufs, desc, in, gathered,
+                                                                        gathered_cap, k_out, max_streams, dst_mode, rounds);
+            count_launch(ctx);
+        }
+        CUDA_TRY(ctx, cudaGetLastError());
+        return P2PT_OK;
+    }
+    demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc, s.blen);
     bool coop_done = false;
     if (ctx->coop_sort) {
         // all nine passes in one cooperative launch (grid-wide syncs between the phases)
