@@ -111,7 +111,7 @@ uint64_t    p2pt_launch_count(p2pt_ctx* ctx);
  * p2pt_frame_decode_batch, the two dtls_gcm calls and p2pt_pipeline_seal / _open whose staged inputs and
  * outputs fit this many bytes - the reference's per-frame call sites, batches of one or a few - run out
  * of a mapped pinned buffer: one kernel launch and one (spinning) stream wait, no copies; about half the
- * latency of the copy path for a single 64-byte frame.  "small_demux" (default 0): demux calls of up to
+ * latency of the copy path for a single 64-byte frame.  "small_demux" (default 1): demux calls of up to
  * 1024 frames run init + sort + scan + emit in one single-block kernel (two launches with the gather
  * instead of six and a cooperative launch).  Host-pointer calls that stage less than 8 MiB always wait
  * by spinning, whatever "blocking_sync" says: a sleeping wait costs 50-100 us per wake-up. */

@@ -44,7 +44,7 @@ struct p2pt_ctx {
     cudaEvent_t events[kStreams] = {};
     cudaEvent_t sync_events[kStreams] = {};   // cudaEventBlockingSync: the host thread sleeps instead of spinning
     bool blocking_sync = true;                // big host-pointer calls wait on sync_events (see wait_stream)
-    bool small_demux = false;                 // batches of up to 1024 frames take the single-block demux kernel (off until verified on the GPU)
+    bool small_demux = true;                  // batches of up to 1024 frames take the single-block demux kernel
     bool spin_this_call = false;              // set per host-pointer call (under mu): small calls spin instead of sleeping
     bool coop_sort = true;                    // demux sorting passes in one cooperative launch
     std::mutex mu;                 // serialises host-pointer calls (they share the arena)

@@ -348,6 +348,12 @@ def test_demux_fuzz_against_numpy(ctx):
         desc["msg_type"] = rng.choice(np.array([11, 21, 21, 21, 20, 22, 99], np.uint8), n)
         desc["status"] = np.where(rng.random(n) < 0.03, rng.integers(1, 3, n), 0).astype(np.uint8)
         r = ctx.frame_demux(desc, buf, session=session)
+        if n <= 1024:           # the single-block kernel took it; the general path must agree
+            ctx.set_option("small_demux", 0)
+            r2 = ctx.frame_demux(desc, buf, session=session)
+            ctx.set_option("small_demux", 1)
+            for k2 in ("k", "perm", "csr", "uniq_sid", "gathered", "gathered_off"):
+                assert np.array_equal(r[k2], r2[k2]), (case, n, k2)
         ok = np.flatnonzero(desc["status"] == 0)
         key = sid[ok].astype(np.uint64)
         if session is not None:
