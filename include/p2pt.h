@@ -107,7 +107,7 @@ uint64_t    p2pt_launch_count(p2pt_ctx* ctx);
  * calls overlap host->device copies, kernels and device->host copies (default 16 MiB).  "blocking_sync":
  * 1 (default) = host-pointer calls sleep while they wait for the GPU, 0 = they spin (lowest latency for
  * single small frames, but a spinning thread per call starves other workers on a busy host).
- * "small_call_bytes" (default 65536, 0 = off, at most 262144): p2pt_frame_encode_batch,
+ * "small_call_bytes" (default 262144, 0 = off, at most 1048576): p2pt_frame_encode_batch,
  * p2pt_frame_decode_batch, the two dtls_gcm calls and p2pt_pipeline_seal / _open whose staged inputs and
  * outputs fit this many bytes - the reference's per-frame call sites, batches of one or a few - run out
  * of a mapped pinned buffer: one kernel launch and one (spinning) stream wait, no copies; about half the

@@ -65,7 +65,7 @@ struct p2pt_ctx {
     uint8_t* zc_host = nullptr;    // host address of the mapped buffer
     uint8_t* zc_dev = nullptr;     // device alias
     size_t zc_cap = 0;
-    uint64_t small_call_bytes = 64u << 10;   // staging footprint up to which a call takes this path (0 = never)
+    uint64_t small_call_bytes = 256u << 10;  // staging footprint up to which a call takes this path (0 = never)
     struct PendingOut { void* dst; const void* src; size_t bytes; };
     std::vector<PendingOut> zc_pending;
 };
@@ -223,9 +223,16 @@ struct IoStage {
 static inline void count_launch(p2pt_ctx* ctx, int k = 1) { ctx->launches.fetch_add((uint64_t)k, std::memory_order_relaxed); }
 
 static int pick_group(p2pt_ctx* ctx, uint64_t n, uint64_t body_bytes) {
-    (void)n; (void)body_bytes;
+    (void)body_bytes;
     if (ctx->gcm_g) return ctx->gcm_g;
-    return 4;      // measured on B200 at 1200-byte records: G=4 323 GB/s, 8: 313, 16: 290, 32: 213
+    // A full machine wants G = 4 (measured on B200 at 1200-byte records: G=4 323 GB/s, 8: 313, 16: 290, 32: 213).
+    // A batch too small to fill the 148 x 1024 lanes is latency-bound on one record's serial chain of slots
+    // (a 1200-byte record on 4 lanes: 20 rounds, ~40 us), so it gets the widest group that still fits.
+    const uint64_t lanes = (uint64_t)ctx->sm_count * kGcmThreads;
+    if (n * 32 <= lanes) return 32;
+    if (n * 16 <= lanes) return 16;
+    if (n * 8 <= lanes) return 8;
+    return 4;
 }
 
 template <int MODE>
@@ -364,7 +371,7 @@ int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
     ctx->lut_slack = (0x10000u - (sb & 0xffffu)) & 0xffffu;
     {
         void* h = nullptr; void* d = nullptr;
-        const size_t cap = 256u << 10;
+        const size_t cap = 1u << 20;
         if (cudaHostAlloc(&h, cap, cudaHostAllocMapped) == cudaSuccess) {
             if (cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess) {
                 ctx->zc_host = (uint8_t*)h; ctx->zc_dev = (uint8_t*)d; ctx->zc_cap = cap;
@@ -445,7 +452,7 @@ int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
         return P2PT_OK;
     }
     if (strcmp(name, "small_call_bytes") == 0) {
-        if (value < 0 || (uint64_t)value > ctx->zc_cap) return set_err(ctx, P2PT_ERR_ARG, "small_call_bytes must be 0 .. 262144");
+        if (value < 0 || (uint64_t)value > ctx->zc_cap) return set_err(ctx, P2PT_ERR_ARG, "small_call_bytes must be 0 .. 1048576");
         std::lock_guard<std::mutex> lk(ctx->mu);
         ctx->small_call_bytes = (uint64_t)value;
         return P2PT_OK;
@@ -1493,6 +1500,80 @@ int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t*
     return P2PT_OK;
 }
 
+}  // extern "C"
+
+// p2pt_pipeline_open_demux for a reader loop that drains a few frames per wake-up (n <= kSmallDemux and a
+// staging footprint within small_call_bytes): inputs go through the mapped pinned buffer, the three kernels
+// (open, single-block demux, gather) write the demux results straight back into it, only `desc` (and `out`
+// if asked for) take an asynchronous copy, and there is ONE stream wait.  Entries beyond k are never
+// copied to the caller, exactly like the general path.  *taken stays false if the call does not fit.
+static int32_t open_demux_small(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, const uint8_t* rec,
+                                const uint64_t* rec_off, uint8_t* out, p2pt_desc* desc, uint32_t max_streams,
+                                uint32_t* uniq_sid, uint32_t* uniq_session, uint64_t* csr, uint32_t* perm,
+                                uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off,
+                                bool* taken) {
+    *taken = false;
+    if (!ctx->small_demux || !ctx->zc_host || !ctx->small_call_bytes || n > (uint64_t)kSmallDemux) return P2PT_OK;
+    const size_t ibytes = rec_off[n] - rec_off[0];
+    const size_t ms1 = (size_t)(max_streams < n ? max_streams : n) + 1;
+    const size_t gcap = gathered ? (size_t)(gathered_cap < ibytes ? gathered_cap : ibytes) : 0;
+    const size_t foot = pad256(4 * n) + pad256(8 * (n + 1)) + pad256(ibytes + 1) + 2 * pad256(4 * ms1) + 2 * pad256(8 * ms1) +
+                        pad256(4 * n) + pad256(gcap + 1) + 256;
+    if (foot > ctx->small_call_bytes || foot > ctx->zc_cap) return P2PT_OK;
+    *taken = true;
+    const uint64_t sbytes = demux_scratch_bytes(n);
+    if (int32_t r = arena_reserve(ctx, pad256(ibytes + 1) + pad256(24 * n) + pad256(sbytes) + 4096)) return r;
+    uint8_t* d_out = arena_take<uint8_t>(ctx, ibytes + 1);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
+    uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
+    size_t used = 0;
+    auto zc = [&](size_t bytes) { uint8_t* p = ctx->zc_dev + used; used += pad256(bytes); return p; };
+    auto host_of = [&](const void* d) { return ctx->zc_host + ((const uint8_t*)d - ctx->zc_dev); };
+    uint32_t* z_sess = (uint32_t*)zc(4 * n);
+    uint64_t* z_io = (uint64_t*)zc(8 * (n + 1));
+    uint8_t* z_in = zc(ibytes + 1);
+    uint32_t* z_uniq = (uint32_t*)zc(4 * ms1);
+    uint32_t* z_usess = (uint32_t*)zc(4 * ms1);
+    uint64_t* z_csr = (uint64_t*)zc(8 * ms1);
+    uint64_t* z_goff = (uint64_t*)zc(8 * ms1);
+    uint32_t* z_perm = (uint32_t*)zc(4 * n);
+    uint8_t* z_g = zc(gcap + 1);
+    uint32_t* z_k = (uint32_t*)zc(4);
+    memcpy(host_of(z_sess), session, 4 * n);
+    memcpy(host_of(z_io), rec_off, 8 * (n + 1));
+    if (ibytes) memcpy(host_of(z_in), rec + rec_off[0], ibytes);
+    cudaStream_t st = ctx->streams[0];
+    GcmArgs a = {};
+    a.n = n; a.session = z_sess; a.n_sessions = ctx->n_sessions; a.keys = ctx->keys_remote;
+    a.in = z_in - rec_off[0]; a.in_off = (const u64*)z_io;
+    a.out = d_out - rec_off[0]; a.out_off = (const u64*)z_io;
+    a.desc = d_desc;
+    if (int32_t r = launch_gcm<kPipeOpen>(ctx, a, pick_group(ctx, n, ibytes), st)) return r;
+    CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, st));
+    if (out && ibytes) CUDA_TRY(ctx, cudaMemcpyAsync(out + rec_off[0], d_out, ibytes, cudaMemcpyDeviceToHost, st));
+    if (int32_t r = p2pt_frame_demux_batch_device(ctx, n, d_desc, z_sess, d_out - rec_off[0], max_streams, z_uniq,
+                                                  uniq_session ? z_usess : nullptr, z_csr, z_perm, z_k,
+                                                  gathered ? z_g : nullptr, gcap, gathered_off ? z_goff : nullptr,
+                                                  d_scratch, sbytes, st)) return r;
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const uint32_t k = *(const uint32_t*)host_of(z_k);
+    *k_out = k;
+    if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "pipeline_open_demux: more streams than max_streams");
+    memcpy(uniq_sid, host_of(z_uniq), 4 * (size_t)k);
+    if (uniq_session) memcpy(uniq_session, host_of(z_usess), 4 * (size_t)k);
+    memcpy(csr, host_of(z_csr), 8 * ((size_t)k + 1));
+    if (gathered_off) memcpy(gathered_off, host_of(z_goff), 8 * ((size_t)k + 1));
+    const uint64_t m = csr[k];
+    if (m) memcpy(perm, host_of(z_perm), 4 * m);
+    if (gathered) {
+        if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "pipeline_open_demux: gathered_cap too small");
+        memcpy(gathered, host_of(z_g), gathered_off[k]);
+    }
+    return P2PT_OK;
+}
+
+extern "C" {
+
 int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
                                  const uint8_t* rec, const uint64_t* rec_off,
                                  uint8_t* out, p2pt_desc* desc,
@@ -1509,6 +1590,12 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
     if (int32_t r = check_sessions(ctx)) return r;
     std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
+    {
+        bool taken = false;
+        const int32_t r = open_demux_small(ctx, n, session, rec, rec_off, out, desc, max_streams, uniq_sid, uniq_session, csr, perm,
+                                           k_out, gathered, gathered_cap, gathered_off, &taken);
+        if (taken) return r;
+    }
     const size_t ibytes = rec_off[n] - rec_off[0];
     const uint64_t sbytes = demux_scratch_bytes(n);
     const size_t gcap = gathered ? (size_t)gathered_cap : 0;

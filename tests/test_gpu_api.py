@@ -118,9 +118,12 @@ def test_small_calls_take_the_mapped_buffer_and_match_the_copy_path(ctx):
                                   payload[int(pay_off[i]):int(pay_off[i + 1])].tolist() for i in range(n)]).astype(np.uint8)
             rec3, roff3, st3 = ctx.dtls_seal(session, nonce, raw, raw_off)
             out3, _, olen3, st4 = ctx.dtls_open(session, rec3, roff3)
+            od = ctx.pipeline_open_demux(session, rec, roff, max_streams=n, gathered_cap=int(pay_off[-1]) + 8)
             got[mode] = dict(frames=frames, desc=desc, rec=rec, st=st, out=out, desc2=desc2,
-                             rec3=rec3, st3=st3, out3=out3, olen3=olen3, st4=st4)
-        ctx.set_option("small_call_bytes", 65536)
+                             rec3=rec3, st3=st3, out3=out3, olen3=olen3, st4=st4,
+                             od_k=np.array([od["k"]]), od_desc=od["desc"], od_uniq=od["uniq_sid"], od_usess=od["uniq_session"],
+                             od_csr=od["csr"], od_perm=od["perm"], od_g=od["gathered"], od_goff=od["gathered_off"])
+        ctx.set_option("small_call_bytes", 262144)
         for k in got[0]:
             if k in ("out", "out3"):        # an opened record is 24 bytes shorter than its slot; the rest is undefined
                 ro = roff if k == "out" else roff3

@@ -29,6 +29,10 @@ calls = {
     "pipeline_seal": lambda: lib.p2pt_pipeline_seal(h, 1, P(sess), P(ep), P(seq), P(nonce), P(types), P(sids), P(sse), P(pay_off), P(rec), P(r_off), P(st)),
     "pipeline_open": lambda: lib.p2pt_pipeline_open(h, 1, P(sess), P(rec), P(r_off), P(out), P(r_off), P(desc)),
 }
+uniq = np.zeros(2, np.uint32); usess = np.zeros(2, np.uint32); csr = np.zeros(2, np.uint64); goff = np.zeros(2, np.uint64)
+perm = np.zeros(1, np.uint32); kk = C.c_uint32(0); gath = np.zeros(64, np.uint8)
+calls["pipeline_open_demux"] = lambda: lib.p2pt_pipeline_open_demux(h, 1, P(sess), P(rec), P(r_off), None, P(desc), 1, P(uniq), P(usess),
+                                                                     P(csr), P(perm), C.byref(kk), P(gath), 64, P(goff))
 for mode in (65536, 0):
     ctx.set_option("small_call_bytes", mode)
     res = {}
