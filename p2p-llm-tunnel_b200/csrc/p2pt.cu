@@ -964,6 +964,54 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
     const uint64_t sbytes = demux_scratch_bytes(n);
     const size_t gcap = gathered ? (size_t)gathered_cap : 0;
     const size_t ib = gathered ? (size_t)in_bytes : 0;
+    if (ctx->small_demux && ctx->zc_host && ctx->small_call_bytes && n <= (uint64_t)kSmallDemux) {
+        // small batch: descriptors, frames and every result live in the mapped pinned buffer; two launches, one wait
+        const size_t ms1 = (size_t)(max_streams < n ? max_streams : n) + 1;
+        const size_t g2 = gcap < ib ? gcap : ib;                  // the bodies cannot be longer than the input
+        const size_t foot = pad256(24 * n) + pad256(4 * n) + pad256(ib + 1) + 2 * pad256(4 * ms1) + 2 * pad256(8 * ms1) +
+                            pad256(4 * n) + pad256(g2 + 1) + 256;
+        if (foot <= ctx->small_call_bytes && foot <= ctx->zc_cap) {
+            if (int32_t r = arena_reserve(ctx, pad256(sbytes) + 4096)) return r;
+            uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
+            size_t used = 0;
+            auto zc = [&](size_t bytes) { uint8_t* q = ctx->zc_dev + used; used += pad256(bytes); return q; };
+            auto host_of = [&](const void* d) { return ctx->zc_host + ((const uint8_t*)d - ctx->zc_dev); };
+            p2pt_desc* z_desc = (p2pt_desc*)zc(24 * n);
+            uint32_t* z_sess = (uint32_t*)zc(4 * n);
+            uint8_t* z_in = zc(ib + 1);
+            uint32_t* z_uniq = (uint32_t*)zc(4 * ms1);
+            uint32_t* z_usess = (uint32_t*)zc(4 * ms1);
+            uint64_t* z_csr = (uint64_t*)zc(8 * ms1);
+            uint64_t* z_goff = (uint64_t*)zc(8 * ms1);
+            uint32_t* z_perm = (uint32_t*)zc(4 * n);
+            uint8_t* z_g = zc(g2 + 1);
+            uint32_t* z_k = (uint32_t*)zc(4);
+            memcpy(host_of(z_desc), desc, 24 * n);
+            if (session) memcpy(host_of(z_sess), session, 4 * n);
+            if (ib) memcpy(host_of(z_in), in, ib);
+            if (int32_t r = p2pt_frame_demux_batch_device(ctx, n, z_desc, session ? z_sess : nullptr, z_in, max_streams, z_uniq,
+                                                          uniq_session ? z_usess : nullptr, z_csr, z_perm, z_k,
+                                                          gathered ? z_g : nullptr, g2, gathered_off ? z_goff : nullptr,
+                                                          d_scratch, sbytes, st)) return r;
+            CUDA_TRY(ctx, cudaStreamSynchronize(st));
+            const uint32_t k = *(const uint32_t*)host_of(z_k);
+            *k_out = k;
+            if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: more streams than max_streams");
+            memcpy(uniq_sid, host_of(z_uniq), 4 * (size_t)k);
+            if (uniq_session) memcpy(uniq_session, host_of(z_usess), 4 * (size_t)k);
+            memcpy(csr, host_of(z_csr), 8 * ((size_t)k + 1));
+            const uint64_t m = csr[k];
+            if (m) memcpy(perm, host_of(z_perm), 4 * m);
+            if (gathered_off) {
+                memcpy(gathered_off, host_of(z_goff), 8 * ((size_t)k + 1));
+                if (gathered) {
+                    if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: gathered_cap too small");
+                    if (gathered_off[k]) memcpy(gathered, host_of(z_g), gathered_off[k]);
+                }
+            }
+            return P2PT_OK;
+        }
+    }
     if (int32_t r = arena_reserve(ctx, pad256(24 * n) + pad256(4 * n) + pad256(ib) + 2 * pad256(4 * ((size_t)max_streams + 1)) +
                                            2 * pad256(8 * ((size_t)max_streams + 1)) + pad256(4 * n) + 256 +
                                            pad256(gcap) + pad256(sbytes) + 8192)) return r;

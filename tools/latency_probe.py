@@ -33,6 +33,9 @@ uniq = np.zeros(2, np.uint32); usess = np.zeros(2, np.uint32); csr = np.zeros(2,
 perm = np.zeros(1, np.uint32); kk = C.c_uint32(0); gath = np.zeros(64, np.uint8)
 calls["pipeline_open_demux"] = lambda: lib.p2pt_pipeline_open_demux(h, 1, P(sess), P(rec), P(r_off), None, P(desc), 1, P(uniq), P(usess),
                                                                      P(csr), P(perm), C.byref(kk), P(gath), 64, P(goff))
+desc_d = np.zeros(1, p2pt._lib.DESC_DTYPE); desc_d["pay_off"] = 5; desc_d["pay_len"] = 64; desc_d["stream_id"] = 99; desc_d["msg_type"] = 21
+calls["frame_demux"] = lambda: lib.p2pt_frame_demux_batch(h, 1, P(desc_d), None, P(frame), 69, 1, P(uniq), None, P(csr), P(perm), C.byref(kk),
+                                                           P(gath), 64, P(goff))
 for mode in (65536, 0):
     ctx.set_option("small_call_bytes", mode)
     res = {}
