@@ -414,6 +414,11 @@ def run_gpu(args):
             for _ in range(50):
                 r1 = ctxs[-1].pipeline_seal(one["session"], one["epoch"], one["seq48"], w["nonce8"][:8], one["types"], one["sids"], one_pay, one_off)
             lat["pipeline_seal_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
+            ctxs[-1].pipeline_open_demux(one["session"], r1[0], r1[1], max_streams=1, gathered_cap=64)
+            t0 = time.perf_counter()
+            for _ in range(50):
+                ctxs[-1].pipeline_open_demux(one["session"], r1[0], r1[1], max_streams=1, gathered_cap=64)
+            lat["pipeline_open_demux_batch1_us"] = (time.perf_counter() - t0) / 50 * 1e6
             lat["note"] = "wall clock per call through the Python binding, one 64-byte RES_BODY frame, host buffers"
         except Exception as e:
             lat = {"error": str(e)}
