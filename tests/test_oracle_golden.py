@@ -135,3 +135,33 @@ def test_demux_session_namespaces():
     r = ob.frame_demux(d, buf, np.array([1, 0, 1], np.uint32))
     assert list(r["uniq_session"]) == [0, 1] and list(r["uniq_sid"]) == [1, 1]
     assert list(r["perm"]) == [1, 0, 2] and r["gathered"].tobytes() == b"bac"
+
+
+def test_oracle_demux_against_numpy_randomised():
+    """The demux oracle itself, checked against an independent numpy statement of the same semantics (stable
+    order by (session, stream id) of the decodable frames, per-stream concatenation of body payloads,
+    serve.rs:120-124): the GPU parity tests lean on it."""
+    from p2p_llm_tunnel_b200._lib import DESC_DTYPE
+    rng = np.random.default_rng(0x5EED000B)
+    for case in range(12):
+        n = int(rng.integers(1, 3000))
+        sid = rng.integers(0, [5, 300, 2**32][case % 3], n, dtype=np.uint64).astype(np.uint32)
+        session = rng.integers(0, 4, n).astype(np.uint32) if case % 2 else None
+        lens = rng.integers(0, 60, n).astype(np.uint32)
+        pay_off = np.cumsum(np.concatenate([[2], (lens + rng.integers(0, 5, n))[:-1]])).astype(np.uint64)
+        buf = rng.integers(0, 256, int(pay_off[-1] + lens[-1] + 8), dtype=np.uint8)
+        desc = np.zeros(n, DESC_DTYPE)
+        desc["pay_off"] = pay_off; desc["pay_len"] = lens; desc["stream_id"] = sid
+        desc["msg_type"] = rng.choice(np.array([11, 21, 21, 20, 22, 99], np.uint8), n)
+        desc["status"] = np.where(rng.random(n) < 0.05, 1, 0).astype(np.uint8)
+        r = ob.frame_demux(desc, buf, session=session)
+        ok = np.flatnonzero(desc["status"] == 0)
+        key = sid[ok].astype(np.uint64)
+        if session is not None:
+            key |= session[ok].astype(np.uint64) << np.uint64(32)
+        order = ok[np.argsort(key, kind="stable")]
+        assert np.array_equal(np.asarray(r["perm"], np.int64)[: len(order)], order), case
+        body = np.where(np.isin(desc["msg_type"][order], (11, 21)), lens[order], 0).astype(np.int64)
+        excl = np.cumsum(body) - body
+        src = np.repeat(pay_off[order].astype(np.int64) - excl, body) + np.arange(int(body.sum()), dtype=np.int64)
+        assert np.array_equal(np.asarray(r["gathered"]), buf[src]), case
