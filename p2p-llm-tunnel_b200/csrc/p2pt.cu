@@ -180,6 +180,15 @@ static T* arena_take(p2pt_ctx* ctx, size_t count) {
 }
 static size_t pad256(size_t b) { return (b + 255) & ~(size_t)255; }
 
+// Carves device-visible pieces out of the ctx's mapped pinned buffer and maps them back to host addresses
+// (the small-batch paths of the demux calls; caller holds ctx->mu and has checked the footprint).
+struct ZcCarver {
+    p2pt_ctx* ctx;
+    size_t used = 0;
+    uint8_t* take(size_t bytes) { uint8_t* p = ctx->zc_dev + used; used += pad256(bytes); return p; }
+    uint8_t* host_of(const void* d) const { return ctx->zc_host + ((const uint8_t*)d - ctx->zc_dev); }
+};
+
 // Staging for the inputs and outputs of one host-pointer call: the device arena + async copies, or,
 // when everything fits small_call_bytes, the mapped pinned buffer + plain memcpy (see p2pt_ctx).
 // Caller holds ctx->mu.
@@ -973,9 +982,9 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
         if (foot <= ctx->small_call_bytes && foot <= ctx->zc_cap) {
             if (int32_t r = arena_reserve(ctx, pad256(sbytes) + 4096)) return r;
             uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
-            size_t used = 0;
-            auto zc = [&](size_t bytes) { uint8_t* q = ctx->zc_dev + used; used += pad256(bytes); return q; };
-            auto host_of = [&](const void* d) { return ctx->zc_host + ((const uint8_t*)d - ctx->zc_dev); };
+            ZcCarver zcv{ctx};
+            auto zc = [&](size_t bytes) { return zcv.take(bytes); };
+            auto host_of = [&](const void* d) { return zcv.host_of(d); };
             p2pt_desc* z_desc = (p2pt_desc*)zc(24 * n);
             uint32_t* z_sess = (uint32_t*)zc(4 * n);
             uint8_t* z_in = zc(ib + 1);
@@ -1574,9 +1583,9 @@ static int32_t open_demux_small(p2pt_ctx* ctx, uint64_t n, const uint32_t* sessi
     uint8_t* d_out = arena_take<uint8_t>(ctx, ibytes + 1);
     p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
     uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
-    size_t used = 0;
-    auto zc = [&](size_t bytes) { uint8_t* p = ctx->zc_dev + used; used += pad256(bytes); return p; };
-    auto host_of = [&](const void* d) { return ctx->zc_host + ((const uint8_t*)d - ctx->zc_dev); };
+    ZcCarver zcv{ctx};
+    auto zc = [&](size_t bytes) { return zcv.take(bytes); };
+    auto host_of = [&](const void* d) { return zcv.host_of(d); };
     uint32_t* z_sess = (uint32_t*)zc(4 * n);
     uint64_t* z_io = (uint64_t*)zc(8 * (n + 1));
     uint8_t* z_in = zc(ibytes + 1);
