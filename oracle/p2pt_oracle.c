@@ -517,11 +517,13 @@ int orc_sctp_unpack(const uint8_t* pkt, uint64_t len, uint32_t headroom, orc_sct
 /* ------------------------------------------------------------------------------------------ */
 
 /* unpack_datagram: records are 13 + length bytes each; a datagram with a truncated record is
- * rejected as a whole (ErrInvalidPacketLength).  Returns the number of records, or -1. */
+ * rejected as a whole (ErrInvalidPacketLength).  The remaining-bytes test is `<= header size` there, so a
+ * trailing header with nothing behind it (a zero-length record at the end) also drops the datagram.
+ * Returns the number of records, or -1. */
 int64_t orc_dtls_datagram_split(const uint8_t* d, uint64_t len, uint64_t* rec_off /* cap entries */, uint64_t cap) {
     uint64_t off = 0, k = 0;
     while (off < len) {
-        if (len - off < 13) return -1;
+        if (len - off <= 13) return -1;
         uint64_t plen = 13 + (((uint64_t)d[off + 11] << 8) | d[off + 12]);
         if (off + plen > len) return -1;
         if (k < cap) rec_off[k] = off;

@@ -16,7 +16,8 @@ __device__ __forceinline__ uint32_t dgram_walk(const uint8_t* d, u64 len, u64 ba
     u64 off = 0;
     uint32_t k = 0;
     while (off < len) {
-        if (len - off < 13) return 0xffffffffu;                        // ErrInvalidPacketLength: whole datagram dropped
+        // `<=`: unpack_datagram refuses a trailing bare 13-byte header (a record with no payload) too
+        if (len - off <= 13) return 0xffffffffu;                       // ErrInvalidPacketLength: whole datagram dropped
         const u64 plen = 13 + (((u64)__ldg(d + off + 11) << 8) | __ldg(d + off + 12));
         if (off + plen > len) return 0xffffffffu;
         if (rec_off && slot0 + k < cap) { rec_off[slot0 + k] = base + off; rec_dgram[slot0 + k] = dgram; }

@@ -1,0 +1,137 @@
+"""CPU: the oracle's DTLS record layout against wire records captured from OpenSSL's DTLS 1.2 stack
+(tests/golden/dtls_openssl_kat.json, made by tests/golden/gen_dtls_openssl.py).
+
+This is the pin for rows a15-a17 and (f)3: webrtc-dtls 0.10.0 (/root/reference/tunnel/Cargo.lock:2822-2825,
+reached at /root/reference/tunnel/src/serve.rs:274 and rtc.rs:88-92) is un-vendored, but it has to interoperate
+with exactly these records (TLS_ECDHE_ECDSA_WITH_AES_128_GCM_SHA256).  The keys in the fixture come from the
+key log + the TLS 1.2 PRF, not from this repository's code."""
+import json
+import os
+
+import numpy as np
+
+import oracle_binding as ob
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+h = bytes.fromhex
+
+
+def fixture():
+    with open(os.path.join(G, "dtls_openssl_kat.json")) as f:
+        return json.load(f)
+
+
+def write_keys(fx, direction):
+    side = "client" if direction == "c2s" else "server"
+    return (np.frombuffer(h(fx["keys"][side + "_write_key"]), np.uint8),
+            np.frombuffer(h(fx["keys"][side + "_write_iv"]), np.uint8))
+
+
+def raw_of(rec, plain):
+    """what CryptoGcm::encrypt is handed: the 13-byte header with the PLAINTEXT length, then the plaintext"""
+    return rec[:11] + len(plain).to_bytes(2, "big") + plain
+
+
+def test_fixture_shape():
+    fx = fixture()
+    assert fx["suite"] == "TLS_ECDHE_ECDSA_WITH_AES_128_GCM_SHA256"
+    recs = fx["records"]
+    assert {r["dir"] for r in recs} == {"c2s", "s2c"}
+    lens = {len(h(r["plain"])) for r in recs if r["type"] == 23}
+    assert {1, 15, 16, 17, 1200, 1205, 1228} <= lens              # block-edge sizes and the full-size record
+    assert {r["type"] for r in recs} == {22, 23}                   # Finished (handshake under GCM) + application data
+    assert any(d["n_records"] > 1 for d in fx["datagrams"])
+
+
+def test_oracle_opens_every_captured_record():
+    fx = fixture()
+    for r in fx["records"]:
+        key, iv = write_keys(fx, r["dir"])
+        rec, plain = h(r["rec"]), h(r["plain"])
+        out, _, olen, st = ob.dtls_open([0], key, iv, np.frombuffer(rec, np.uint8), [0, len(rec)])
+        assert st[0] == 0, (r["dir"], r["seq"])
+        assert int(olen[0]) == 13 + len(plain)
+        assert out[:13].tobytes() == rec[:13]                      # header left as it came (length not rewritten)
+        assert out[13:int(olen[0])].tobytes() == plain, (r["dir"], r["seq"])
+
+
+def test_oracle_reseals_to_the_captured_bytes():
+    fx = fixture()
+    for r in fx["records"]:
+        key, iv = write_keys(fx, r["dir"])
+        rec, plain = h(r["rec"]), h(r["plain"])
+        raw = raw_of(rec, plain)
+        got, _, st = ob.dtls_seal([0], key, iv, np.frombuffer(rec[13:21], np.uint8), np.frombuffer(raw, np.uint8), [0, len(raw)])
+        assert st[0] == 0 and got.tobytes() == rec, (r["dir"], r["seq"])
+
+
+def test_wrong_direction_key_or_touched_header_fails():
+    fx = fixture()
+    r = next(x for x in fx["records"] if x["type"] == 23 and len(h(x["plain"])) == 1205)
+    rec = h(r["rec"])
+    other = write_keys(fx, "s2c" if r["dir"] == "c2s" else "c2s")
+    _, _, _, st = ob.dtls_open([0], other[0], other[1], np.frombuffer(rec, np.uint8), [0, len(rec)])
+    assert st[0] == 3
+    key, iv = write_keys(fx, r["dir"])
+    # type, version, epoch, seq, nonce, ciphertext, tag.  Not the length field: CryptoGcm::decrypt takes the AAD
+    # length from the slice it was handed, and so does the oracle (the batch offsets, not bytes 11..13).
+    for pos in (0, 2, 4, 10, 13, 20, 21, len(rec) - 1):
+        t = bytearray(rec); t[pos] ^= 1
+        _, _, _, st = ob.dtls_open([0], key, iv, np.frombuffer(bytes(t), np.uint8), [0, len(t)])
+        assert st[0] in (3, 6), pos
+
+
+def test_datagram_split_on_captured_flights():
+    fx = fixture()
+    for d in fx["datagrams"]:
+        g = h(d["bytes"])
+        off, dg, st = ob.dtls_datagram_split(np.frombuffer(g, np.uint8), [0, len(g)])
+        assert st[0] == 0 and len(dg) == d["n_records"]
+        # every piece is a well-formed record: version fe fd / fe ff, length field = piece length - 13
+        for j in range(len(dg)):
+            p = g[int(off[j]):int(off[j + 1])]
+            assert p[1] == 0xFE and p[2] in (0xFD, 0xFF) and int.from_bytes(p[11:13], "big") == len(p) - 13
+
+
+def test_captured_flight_through_split_then_open():
+    """the server's last handshake flight: NewSessionTicket?, ChangeCipherSpec (epoch 0, passes through), Finished
+    (epoch 1, sealed): split, then open what is protected"""
+    fx = fixture()
+    seen_ccs = seen_fin = False
+    for d in fx["datagrams"]:
+        g = h(d["bytes"])
+        off, dg, _ = ob.dtls_datagram_split(np.frombuffer(g, np.uint8), [0, len(g)])
+        key, iv = write_keys(fx, d["dir"])
+        for j in range(len(dg)):
+            p = g[int(off[j]):int(off[j + 1])]
+            epoch = int.from_bytes(p[3:5], "big")
+            if p[0] == 20:
+                out, _, olen, st = ob.dtls_open([0], key, iv, np.frombuffer(p, np.uint8), [0, len(p)])
+                assert st[0] == 5 and out[:int(olen[0])].tobytes() == p
+                seen_ccs = True
+            elif epoch >= 1:
+                out, _, olen, st = ob.dtls_open([0], key, iv, np.frombuffer(p, np.uint8), [0, len(p)])
+                assert st[0] == 0
+                if p[0] == 22:
+                    assert out[13] == 20 and int(olen[0]) == 13 + 12 + 12   # Finished: handshake header + verify_data
+                    seen_fin = True
+    assert seen_ccs and seen_fin
+
+
+def test_application_records_carry_the_tunnel_frames():
+    """records -> open -> TunnelMessage::decode (protocol.rs:157-172): what proxy.rs:109-138 sees"""
+    fx = fixture()
+    key, iv = write_keys(fx, "s2c")
+    recs = [h(r["rec"]) for r in fx["records"] if r["dir"] == "s2c" and r["type"] == 23]
+    buf = np.frombuffer(b"".join(recs), np.uint8)
+    off = np.concatenate([[0], np.cumsum([len(r) for r in recs])]).astype(np.uint64)
+    out, _, olen, st = ob.dtls_open(np.zeros(len(recs), np.uint32), key, iv, buf, off)
+    assert (st == 0).all()
+    frames = [out[int(off[i]) + 13:int(off[i]) + int(olen[i])].tobytes() for i in range(len(recs))]
+    fbuf = np.frombuffer(b"".join(frames), np.uint8)
+    foff = np.concatenate([[0], np.cumsum([len(f) for f in frames])]).astype(np.uint64)
+    d = ob.frame_decode(fbuf, foff)
+    got = [(int(x["msg_type"]), int(x["stream_id"]), int(x["status"])) for x in d]
+    assert got[0] == (20, 42, 0) and got[1] == (21, 99, 0) and got[2] == (21, 42, 0)
+    assert got[5] == (22, 42, 0) and got[6] == (3, 0, 0)
+    assert frames[1][5:] == b'data: {"token": "hello"}\n\n'

@@ -151,11 +151,15 @@ def test_large_ragged_batch_through_the_32_frame_tiles(ctx):
     assert np.array_equal(r["gathered"], payload[src])
 
 
-def test_c5_slice_full_pipeline_multi_session(ctx):
-    """configs[4] at 1/8 size (the full size runs in bench.py with its own correctness gate): 8192 sessions x
-    16 records, encode->seal, open->decode->demux->gather keyed by (session, stream id)."""
+@pytest.mark.parametrize("S", [8192, 65536])
+def test_c5_full_pipeline_multi_session(ctx, S):
+    """configs[4] at 1/8 size and at full size (65 536 sessions x 16 records = 1 048 576 records x 1200 B):
+    encode->seal, open->decode->demux->gather keyed by (session, stream id).  The sealed bytes are checked on
+    sampled records against Python `cryptography` laid out as SURVEY.md App. A.2 (the layout itself is pinned by
+    tests/test_gpu_dtls_openssl.py), the rest by the round trip."""
+    from cryptography.hazmat.primitives.ciphers.aead import AESGCM
     from p2p_llm_tunnel_b200 import workload
-    S, R, P = 8192, 16, 1200
+    R, P = 16, 1200
     keys, ivs = workload.sessions_keys(S, seed_shift=5)
     ctx.sessions_load(keys, ivs, keys, ivs)
     w = workload.pipeline_workload(S, R, P, seed_shift=5)
@@ -163,6 +167,17 @@ def test_c5_slice_full_pipeline_multi_session(ctx):
     rec, rec_off, st = ctx.pipeline_seal(w["session"], w["epoch"], w["seq48"], w["nonce8"], w["types"], w["sids"],
                                          w["payload"], w["pay_off"], w["rec_off"])
     assert not st.any()
+    rng = np.random.default_rng(S)
+    for i in [0, 1, 15, 16, n // 2, n - 1] + [int(x) for x in rng.integers(0, n, 40)]:
+        s = int(w["session"][i])
+        frame = bytes([int(w["types"][i])]) + int(w["sids"][i]).to_bytes(4, "big") + \
+            w["payload"][int(w["pay_off"][i]):int(w["pay_off"][i + 1])].tobytes()
+        hdr = bytes([23, 0xFE, 0xFD]) + int(w["epoch"][i]).to_bytes(2, "big") + int(w["seq48"][i]).to_bytes(6, "big")
+        nonce = w["nonce8"][8 * i:8 * i + 8].tobytes()
+        aad = hdr[3:11] + hdr[0:3] + len(frame).to_bytes(2, "big")
+        exp = hdr + (len(frame) + 24).to_bytes(2, "big") + nonce + AESGCM(keys[s].tobytes()).encrypt(ivs[s].tobytes() + nonce, frame, aad)
+        a = int(rec_off[i])
+        assert rec[a:a + len(exp)].tobytes() == exp, i
     r = ctx.pipeline_open_demux(w["session"], rec, rec_off, max_streams=S * 4, gathered_cap=n * P)
     assert not r["desc"]["status"].any() and r["k"] == S * 4
     _check_demux_properties(r, w["sids"], n, w["session"])

@@ -65,11 +65,15 @@ def test_replay_window_oracle_semantics():
 
 def test_datagram_split_oracle():
     r1 = bytes([23, 0xFE, 0xFD]) + bytes(8) + (5).to_bytes(2, "big") + b"hello"
-    r2 = bytes([22, 0xFE, 0xFD]) + bytes(8) + (0).to_bytes(2, "big")
-    buf = np.frombuffer(r1 + r2 + r1[:-1], np.uint8)
-    off = np.array([0, len(r1) + len(r2), len(buf)], np.uint64)
+    r0 = bytes([22, 0xFE, 0xFD]) + bytes(8) + (0).to_bytes(2, "big")          # header only, zero-length record
+    # [r1 r0 r1] is fine; [r1 r1-truncated] and [r1 r0] (a bare header at the very end: unpack_datagram's
+    # `remaining <= 13` test) are dropped whole
+    dgrams = [r1 + r0 + r1, r1 + r1[:-1], r1 + r0]
+    buf = np.frombuffer(b"".join(dgrams), np.uint8)
+    off = np.concatenate([[0], np.cumsum([len(d) for d in dgrams])]).astype(np.uint64)
     ro, rd, st = ob.dtls_datagram_split(buf, off)
-    assert list(st) == [0, 6] and list(rd) == [0, 0] and list(ro) == [0, len(r1), len(buf)]
+    assert list(st) == [0, 6, 6] and list(rd) == [0, 0, 0]
+    assert list(ro) == [0, len(r1), len(r1) + len(r0), len(buf)]
 
 
 def test_sse_scan_oracle():

@@ -4,13 +4,18 @@ Some callers of this library are not allowed to allocate device memory while the
 task living inside a fixed device-memory budget because another tenant (an inference server) owns
 the rest of the GPU, or a per-connection loop that cannot take cudaMalloc's device-wide
 synchronisation.  For them the demux scratch is a static device array inside the library.  This test
-calls that entry point through the C ABI twice in a row (the second batch is smaller, so the array
-still holds stale data from the first) and requires the same bytes as the caller-scratch entry point
-produces, and checks that a batch beyond the stated maximum is refused.  It is collected last
-(file name) and needs nothing from the other tests, so it passes alone in a fresh process too.
+calls that entry point through the C ABI several times in a row (the second batch is smaller than the
+first, so the array still holds stale data) and requires the same bytes as the caller-scratch entry point
+produces AND as the CPU oracle produces, at the sizes where the library changes strategy (up to 1024
+frames a single-block kernel, above it the cooperative radix sort, and the stated maximum exactly),
+checks that the amount of free device memory is the same before and after the call, and that a
+batch beyond the stated maximum is refused.  It is collected last (file name) and needs nothing from
+the other tests, so it passes alone in a fresh process too.
 """
 import numpy as np
 import pytest
+
+import oracle_binding as ob
 
 pytestmark = pytest.mark.gpu
 
@@ -38,8 +43,13 @@ def _run(ctx, torch, entry, n, d_desc, d_sess, d_buf, gcap, scratch=None):
     args = [n, d_desc, d_sess, d_buf, ms, o["uniq"], o["usess"], o["csr"], o["perm"], o["k"], o["g"], gcap, o["goff"]]
     if scratch is not None:
         args += [scratch, scratch.numel()]
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info()
     ctx.call(entry, *args, s)
     torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info()
+    if scratch is None:
+        assert free_after == free_before, "the allocation-free entry point changed the free device memory"
     k = int(o["k"].item())
     m = int(o["csr"][k].item())
     return {"k": k, "uniq": o["uniq"][:k].cpu().numpy(), "usess": o["usess"][:k].cpu().numpy(),
@@ -51,11 +61,15 @@ def test_no_alloc_demux_matches_caller_scratch_entry_point(ctx):
     import torch
     dev = torch.device("cuda:0")
     rng = np.random.default_rng(2026)
-    for n, streams, sessions in ((40000, 300, 64), (7001, 5, 3)):      # two calls in a row, second one smaller
+    # calls in a row on the one shared array: large, smaller (stale data from the first still there), the
+    # single-block sizes (n <= 1024), one frame, and exactly the maximum
+    for n, streams, sessions in ((40000, 300, 64), (7001, 5, 3), (1024, 40, 4), (700, 9, 2), (1, 1, 1),
+                                 (MAX_FRAMES, 4096, 16), (1025, 1000, 1)):
         types, sids, payload, pay_off, session = _frames(rng, n, streams, sessions)
         buf, off = ctx.frame_encode(types, sids, payload, pay_off)
         buf = buf.copy()
-        buf[off[:-1][rng.random(n) < 0.01].astype(np.int64)] = 250       # a few undecodable frames
+        if n > 1:
+            buf[off[:-1][rng.random(n) < 0.01].astype(np.int64)] = 250   # a few undecodable frames
         desc = ctx.frame_decode(buf, off)
         d_desc = torch.from_numpy(desc.view(np.uint8).reshape(-1).copy()).to(dev)
         d_sess = torch.from_numpy(session.view(np.int32)).to(dev)
@@ -68,6 +82,11 @@ def test_no_alloc_demux_matches_caller_scratch_entry_point(ctx):
         assert got["k"] == ref["k"] and got["k"] > 0
         for key in ("uniq", "usess", "csr", "perm", "goff", "g"):
             assert np.array_equal(got[key], ref[key]), (n, key)         # bit-exact, like every other parity test
+        exp = ob.frame_demux(desc, buf, session)                        # and against the CPU oracle directly
+        assert got["k"] == exp["k"]
+        for key, okey in (("uniq", "uniq_sid"), ("usess", "uniq_session"), ("csr", "csr"), ("perm", "perm"),
+                          ("goff", "gathered_off"), ("g", "gathered")):
+            assert np.array_equal(got[key].astype(np.uint64), np.asarray(exp[okey]).astype(np.uint64)), (n, key)
 
 
 def test_no_alloc_demux_refuses_batches_beyond_its_maximum(ctx):
