@@ -12,6 +12,7 @@ no data-path collective -- sessions share no state).  One step = the full pipeli
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
@@ -83,6 +84,27 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+RECORD_KERNEL_SOURCES = ("gcm_kernels.cuh", "gcm_math.cuh", "common.cuh")
+
+
+def record_kernel_source_hash():
+    """hash of the sources of gcm_record_kernel: profiles/record_kernel_pipes.json and roofline_traffic.json are ncu
+    measurements of ONE build, tools/make_roofline_profile.py stamps them with this and bench.py ignores a stale file"""
+    h = hashlib.sha256()
+    for f in RECORD_KERNEL_SOURCES:
+        with open(os.path.join(ROOT, "p2p-llm-tunnel_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def bench_config():
+    """the `config` object of both arms (the driver compares them: same workload, same batch)"""
+    return {"workload": "C5 full frame+seal/open pipeline: 65536 sessions x 16 RES_BODY frames x 1200 B per GPU, "
+                        "sessions sharded by connection (global id = local*N + rank), no collective",
+            "records_per_step_per_gpu": SESSIONS * RECS, "payload_bytes": PAYLOAD, "streams_per_session": 4,
+            "l2_policy": "inputs (1.26 GB payload + 1.31 GB records per step) are larger than the 126 MB L2"}
+
+
 def make_workload(rank, world, sessions=SESSIONS):
     from p2p_llm_tunnel_b200 import workload
     w = workload.pipeline_workload(sessions, RECS, PAYLOAD, seed_shift=rank, session_base=rank, session_stride=world)
@@ -100,22 +122,60 @@ def load_cpufast():
     return lib
 
 
-def cpu_pipeline(lib, w, keys, ivs, rec, nthreads, reps=1):
-    """returns best (seal_s, open_s) over reps, and stats"""
+def cpu_pipeline(lib, w, keys, ivs, rec, nthreads, reps=1, backend=0, phases=3):
+    """returns best (seal_s, open_s) over reps, and stats; phases=5 times the open WITHOUT the per-stream map (AEAD +
+    frame decode only).  backend 0 = the RustCrypto-style port
+    (oracle/p2pt_cpu_fast.c), 1 = the same record layout around OpenSSL EVP_aes_128_gcm (oracle/p2pt_cpu_openssl.c)"""
     p = lambda a: C.c_void_p(a.ctypes.data)
-    times = (C.c_double * 2)(); stats = (C.c_uint64 * 4)()
+    times = (C.c_double * 3)(); stats = (C.c_uint64 * 4)()
     best = None
     for _ in range(reps):
-        rc = lib.cpufast_pipeline(C.c_uint64(w["n"]), p(w["session"]), p(keys), p(ivs), C.c_uint32(len(keys)),
-                                  p(w["epoch"]), p(w["seq48"]), p(w["nonce8"]), p(w["types"]), p(w["sids"]),
-                                  p(w["payload"]), p(w["pay_off"]), p(rec), p(w["rec_off"]), None,
-                                  C.c_int(nthreads), C.c_int(3), times, stats)
+        rc = lib.cpufast_pipeline_ex(C.c_uint64(w["n"]), p(w["session"]), p(keys), p(ivs), C.c_uint32(len(keys)),
+                                     p(w["epoch"]), p(w["seq48"]), p(w["nonce8"]), p(w["types"]), p(w["sids"]),
+                                     p(w["payload"]), p(w["pay_off"]), p(rec), p(w["rec_off"]), None,
+                                     C.c_int(nthreads), C.c_int(phases), times, stats, C.c_int(backend))
         if rc != 0:
-            raise RuntimeError("cpufast_pipeline failed")
-        t = (times[0], times[1])
+            raise RuntimeError(f"cpufast_pipeline_ex failed (backend {backend}, rc {rc})")
+        t = (times[0], times[1]) if phases == 3 else (times[0], times[2])
         if best is None or sum(t) < sum(best):
             best = t
     return best, [int(x) for x in stats]
+
+
+def slice_workload(w, sessions):
+    """the first `sessions` sessions of a pipeline workload (records of a session are consecutive)"""
+    m = sessions * RECS
+    sub = {k: (v[:m] if k not in ("nonce8", "payload", "pay_off", "rec_off") else v) for k, v in w.items() if k != "n"}
+    sub["nonce8"] = w["nonce8"][: 8 * m]; sub["pay_off"] = w["pay_off"][: m + 1]; sub["rec_off"] = w["rec_off"][: m + 1]
+    sub["n"] = m
+    return sub
+
+
+def openssl_baseline(lib, w, keys, ivs, rec, cores, check=None):
+    """the record layout around OpenSSL EVP_aes_128_gcm, all cores on the full batch and one thread on
+    1/16 of it.  Returns the `openssl_evp` object of cpu_baseline (None if libcrypto was not there at build time)."""
+    if not lib.cpuossl_available():
+        return None
+    payload_bytes = w["n"] * PAYLOAD
+    (ts, to), stats = cpu_pipeline(lib, w, keys, ivs, rec, cores, reps=2, backend=1)
+    assert stats[0] == 0 and stats[2] == payload_bytes, stats
+    if check is not None:
+        assert np.array_equal(rec[: 1 << 20], check), "OpenSSL baseline and GPU records differ"
+    (_, tn), _ = cpu_pipeline(lib, w, keys, ivs, rec, cores, reps=2, backend=1, phases=5)
+    w1 = slice_workload(w, SESSIONS // 16)
+    (ts1, to1), stats1 = cpu_pipeline(lib, w1, keys, ivs, rec, 1, reps=1, backend=1)
+    (_, tn1), _ = cpu_pipeline(lib, w1, keys, ivs, rec, 1, reps=1, backend=1, phases=5)
+    b1 = w1["n"] * PAYLOAD
+    return {"value": payload_bytes / (ts + to) / 1e9, "unit": "GB/s", "cores": cores, "kind": "port",
+            "seal_gbs": payload_bytes / ts / 1e9, "open_demux_gbs": payload_bytes / to / 1e9,
+            "open_only_gbs": payload_bytes / tn / 1e9,
+            "one_thread": {"value": b1 / (ts1 + to1) / 1e9, "seal_gbs": b1 / ts1 / 1e9, "open_demux_gbs": b1 / to1 / 1e9,
+                           "open_only_gbs": b1 / tn1 / 1e9, "sample": f"{w1['n']} records (1/16 of the batch)"},
+            "note": "open_only = AEAD open + frame decode without the per-stream HashMap<_, Vec<u8>> append (serve.rs:120-124), "
+                    "which is what limits open_demux on the CPU",
+            "sample": f"the full per-GPU batch ({w['n']} records x {PAYLOAD} B), best of 2, the oracle's record layout around "
+                      f"OpenSSL EVP_aes_128_gcm (one EVP context per worker, re-keyed per session, IV per record), "
+                      f"frame codec and per-stream map as in the port, {cores} host threads sharded by session"}
 
 
 def run_reference(args):
@@ -124,11 +184,11 @@ def run_reference(args):
         return
     lib = load_cpufast()
     cores = os.cpu_count() or 1
-    # bounded sample: 1/8 of the per-GPU batch (8192 sessions x 16 records x 1200 B = 157 MB payload)
-    sessions = SESSIONS // 8
+    # the same batch as the GPU arm's step: 65536 sessions x 16 records x 1200 B (1.26 GB payload) per step
+    sessions = SESSIONS
     w, keys, ivs = make_workload(0, 1, sessions)
     rec = np.zeros(int(w["rec_off"][-1]), np.uint8)
-    for _ in range(max(args.warmup, 1)):
+    for _ in range(max(min(args.warmup, 2), 1)):
         cpu_pipeline(lib, w, keys, ivs, rec, cores)
     t0 = time.perf_counter()
     tot_seal = tot_open = 0.0
@@ -140,18 +200,22 @@ def run_reference(args):
     step_s = wall / args.steps
     payload_bytes = w["n"] * PAYLOAD
     gbs = payload_bytes / step_s / 1e9
+    try:
+        ossl = openssl_baseline(lib, w, keys, ivs, rec, cores)
+    except Exception as e:
+        ossl = {"value": None, "error": str(e)}
     line = {
         "impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C5 full frame+seal/open pipeline, bounded sample", "sessions": sessions,
-                   "records_per_session": RECS, "payload_bytes": PAYLOAD, "records_per_step": w["n"]},
+        "config": bench_config(),
         "records_per_s": w["n"] / step_s,
         "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port",
-                         "sample": f"{sessions} sessions x {RECS} records x {PAYLOAD} B per step (1/8 of the GPU batch), "
+                         "sample": f"the full per-GPU batch every step ({sessions} sessions x {RECS} records x {PAYLOAD} B), "
                                    f"AES-NI + PCLMULQDQ C port of the RustCrypto path, {cores} threads sharded by session",
                          "seal_gbs": payload_bytes * args.steps / tot_seal / 1e9,
-                         "open_demux_gbs": payload_bytes * args.steps / tot_open / 1e9},
+                         "open_demux_gbs": payload_bytes * args.steps / tot_open / 1e9,
+                         "openssl_evp": ossl},
         "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -274,6 +338,21 @@ def run_gpu(args):
     open_ms = float(np.mean([m[1].elapsed_time(m[2]) for m in marks]))
     demux_ms = float(np.mean([m[2].elapsed_time(m[3]) for m in marks]))
     value = world * payload_bytes / (dev_ms * 1e-3) / 1e9
+
+    # ---------------- the other BASELINE.json configs, device-resident (C2, C3, C4, SCTP, bookkeeping) ----------------
+    configs = None
+    if world == 1 and not args.no_configs:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench_configs
+            sampler2 = ClockSampler(local)
+            sampler2.start()
+            configs = bench_configs.run_all(ctx, dev, with_cpu=False)
+            configs["clocks"] = sampler2.stop()
+            configs["launches"] = ctx.launch_count() - launches0 - launches
+        except Exception as e:
+            configs = {"error": str(e)}
+        ctx.sessions_load(keys, ivs, keys, ivs)      # the C3 configs loaded their own sessions
 
     def run_e2e():
         # ---------------- end-to-end arm: host-pointer C ABI, pinned host buffers ----------------
@@ -490,35 +569,46 @@ def run_gpu(args):
     seal_bytes = 2 * PAYLOAD + 86
     stages = {"seal_ms": seal_ms, "open_ms": open_ms, "demux_gather_ms": demux_ms,
               "seal_gbs_payload": payload_bytes / seal_ms / 1e6, "open_gbs_payload": payload_bytes / open_ms / 1e6,
-              "demux_gather_gbs_hbm": n * (2 * PAYLOAD + 41) / demux_ms / 1e6}
+              "demux_gather_gbs_hbm": n * (2 * PAYLOAD + 41) / demux_ms / 1e6,
+              "demux_gather_frac_of_hbm": n * (2 * PAYLOAD + 41) / demux_ms / 1e6 / peak}
     dom = "gcm_record_kernel<4,kPipeSeal>" if seal_ms >= open_ms else "gcm_record_kernel<4,kPipeOpen>"
     dom_ms = max(seal_ms, open_ms)
     dom_bytes = seal_bytes if seal_ms >= open_ms else (2 * PAYLOAD + 91)
     achieved = n * dom_bytes / dom_ms / 1e6
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_record": dom_bytes,
-                "note": "AES-GCM without AES/CLMUL instructions is bound by the integer ALU / shared-memory LSU "
-                        "pipes, not HBM; see DESIGN.md and profiles/ for pipe utilisation"}
-    # the pipe that actually binds this kernel: integer ALU (LOP3 / PRMT / SHF / IADD3), instruction counts from ncu
+    hbm = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+           "peak_source": peak_src, "algorithmic_bytes_per_record": dom_bytes}
+    # AES-GCM without AES / carry-less-multiply instructions is bound by the integer ALU pipe (LOP3 / PRMT / SHF /
+    # IADD3), not by HBM.  The instruction counts per 16-byte block come from ncu (tools/make_roofline_profile.py
+    # writes them, stamped with the hash of the kernel's sources); a file that describes another build is ignored
+    # and the line falls back to the HBM figure.
+    roofline = dict(hbm, kernel=dom, traffic=None)
+    src_hash = record_kernel_source_hash()
     pipes = os.path.join(ROOT, "profiles", "record_kernel_pipes.json")
-    if os.path.exists(pipes):
-        try:
-            pj = json.load(open(pipes))
+    try:
+        pj = json.load(open(pipes))
+        if pj.get("source_hash") != src_hash:
+            roofline["alu_pipe"] = {"stale": True, "note": f"{os.path.basename(pipes)} describes build {pj.get('source_hash')}, "
+                                                           f"this build is {src_hash}; re-run tools/make_roofline_profile.py"}
+        else:
+            which = "seal" if seal_ms >= open_ms else "open"
+            k = pj[which]
             sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
-            alu_winst = n * pj["lane_slots_per_record"] / 32.0 * pj["alu_pipe_inst_per_lane_slot"]
-            alu_peak = ctx.get_info("sm_count") * 4 * 0.5 * sm_hz
-            roofline["alu_pipe"] = {"bound": "integer ALU pipe", "achieved_warp_inst_per_s": alu_winst / (dom_ms * 1e-3),
-                                    "peak_warp_inst_per_s": alu_peak, "frac": alu_winst / (dom_ms * 1e-3) / alu_peak,
-                                    "alu_inst_per_16B_block": pj["alu_pipe_inst_per_lane_slot"], "ncu": pj["ncu"],
-                                    "source": pj["source"]}
-        except Exception as e:
-            roofline["alu_pipe"] = {"error": str(e)}
-    prof = os.path.join(ROOT, "profiles", "roofline_traffic.json")
-    if os.path.exists(prof):
-        try:
-            roofline["traffic"] = json.load(open(prof)).get("traffic_bytes_per_launch")
-        except Exception:
-            pass
+            alu_winst = n * k["lane_slots_per_record"] / 32.0 * k["alu_pipe_inst_per_lane_slot"]
+            alu_peak = ctx.get_info("sm_count") * pj["alu_warp_inst_per_clk_per_sm"] * sm_hz
+            a_ = alu_winst / (dom_ms * 1e-3)
+            roofline = {"bound": "alu", "kernel": dom, "achieved": a_ / 1e9, "peak": alu_peak / 1e9, "unit": "G warp-inst/s",
+                        "frac": a_ / alu_peak, "traffic": k.get("dram_bytes_per_launch"),
+                        "pipe": "integer ALU (LOP3 / PRMT / SHF / IADD3): %.0f of %.0f instructions per 16-byte block and lane"
+                                % (k["alu_pipe_inst_per_lane_slot"], k["total_inst_per_lane_slot"]),
+                        "peak_source": pj["alu_peak_source"], "sm_mhz_used": sm_hz / 1e6,
+                        "ncu": k.get("ncu"), "source": pj.get("source"), "source_hash": src_hash,
+                        "hbm": hbm,
+                        "note": "bound by the integer ALU pipe, not HBM (DESIGN.md 4); `hbm` is the secondary figure: algorithmic "
+                                "bytes per record x records / kernel time against the measured copy peak"}
+    except FileNotFoundError:
+        pass
+    except Exception as e:
+        roofline["alu_pipe"] = {"error": str(e)}
 
     cpu_baseline = None
     if world == 1 and not args.no_cpu:
@@ -534,6 +624,10 @@ def run_gpu(args):
                             "sample": f"the full per-GPU batch ({n} records x {PAYLOAD} B), best of 2, AES-NI + PCLMULQDQ "
                                       f"C port of the RustCrypto path on {cores} host threads sharded by session",
                             "seal_gbs": payload_bytes / ts / 1e9, "open_demux_gbs": payload_bytes / to / 1e9}
+            try:
+                cpu_baseline["openssl_evp"] = openssl_baseline(lib, hw, keys, ivs, crec, cores, check=rec[: 1 << 20].cpu().numpy())
+            except Exception as e:
+                cpu_baseline["openssl_evp"] = {"value": None, "error": str(e)}
         except Exception as e:  # the CPU arm must never take the GPU numbers down with it
             cpu_baseline = {"value": None, "unit": "GB/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e}"}
 
@@ -541,12 +635,10 @@ def run_gpu(args):
         "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": "C5 full frame+seal/open pipeline: 65536 sessions x 16 RES_BODY frames x 1200 B per GPU, "
-                               "sessions sharded by connection (global id = local*N + rank), no collective",
-                   "records_per_step_per_gpu": n, "payload_bytes": PAYLOAD, "streams_per_session": 4,
-                   "l2_policy": "inputs (1.26 GB payload + 1.31 GB records per step) are larger than the 126 MB L2"},
+        "config": bench_config(),
         "records_per_s": world * n / (dev_ms * 1e-3),
         "stages": stages,
+        "configs": configs,
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
         "e2e": None if args.no_e2e else {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -578,6 +670,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end (host buffer) leg; for profiling runs")
+    ap.add_argument("--no-configs", action="store_true", help="skip the device-resident C2 / C3 / C4 / SCTP stage timings")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

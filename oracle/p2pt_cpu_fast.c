@@ -225,13 +225,23 @@ static void map_free(stream_map* m) {
     free(m->slots);
 }
 
+/* second AEAD backend: OpenSSL EVP (p2pt_cpu_openssl.c) */
+int cpuossl_available(void);
+void* cpuossl_key_new(void);
+void cpuossl_key_free(void* p);
+void cpuossl_key_set_enc(void* p, const uint8_t key[16]);
+void cpuossl_key_set_dec(void* p, const uint8_t key[16]);
+int cpuossl_seal(void* p, const uint8_t iv4[4], const uint8_t nonce8[8], const uint8_t* raw, uint64_t raw_len, uint8_t* out);
+int cpuossl_open(void* p, const uint8_t iv4[4], const uint8_t* rec, uint64_t rec_len, uint8_t* out, uint64_t* out_len);
+
 /* ---- the threaded pipeline ---- */
 typedef struct {
     /* shared inputs */
     uint64_t n; const uint32_t* session; const uint8_t* keys16; const uint8_t* ivs4; uint32_t n_sessions;
     const uint16_t* epoch; const uint64_t* seq48; const uint8_t* nonce8; const uint8_t* types; const uint32_t* sids;
     const uint8_t* payload; const uint64_t* pay_off; uint8_t* rec; const uint64_t* rec_off; uint8_t* out;
-    int do_seal, do_open;
+    int do_seal, do_open, no_demux;
+    int backend;   /* 0 = the RustCrypto-style port above, 1 = OpenSSL EVP_aes_128_gcm */
     /* per thread */
     uint64_t r0, r1; uint64_t bad; uint64_t streams; uint64_t body_bytes; uint64_t checksum;
 } job;
@@ -240,10 +250,15 @@ static void* worker(void* arg) {
     job* j = (job*)arg;
     fast_key fk; uint32_t cur = 0xffffffffu;
     uint8_t* scratch = (uint8_t*)malloc(70000);
+    void* ok = j->backend ? cpuossl_key_new() : NULL;
     if (j->do_seal) {
         for (uint64_t i = j->r0; i < j->r1; i++) {
             uint32_t s = j->session[i];
-            if (s != cur) { fast_key_init(&fk, j->keys16 + 16 * (uint64_t)s); cur = s; }
+            if (s != cur) {
+                if (j->backend) cpuossl_key_set_enc(ok, j->keys16 + 16 * (uint64_t)s);
+                else fast_key_init(&fk, j->keys16 + 16 * (uint64_t)s);
+                cur = s;
+            }
             /* TunnelMessage::encode (protocol.rs:148-154) into raw = hdr13 || frame */
             uint64_t plen = j->pay_off[i + 1] - j->pay_off[i], flen = plen + 5;
             uint8_t* raw = scratch;
@@ -254,7 +269,9 @@ static void* worker(void* arg) {
             raw[14] = (uint8_t)(j->sids[i] >> 24); raw[15] = (uint8_t)(j->sids[i] >> 16);
             raw[16] = (uint8_t)(j->sids[i] >> 8); raw[17] = (uint8_t)j->sids[i];
             memcpy(raw + 18, j->payload + j->pay_off[i], plen);
-            if (fast_seal(&fk, j->ivs4 + 4 * (uint64_t)s, j->nonce8 + 8 * i, raw, 13 + flen, j->rec + j->rec_off[i])) j->bad++;
+            const int st = j->backend ? cpuossl_seal(ok, j->ivs4 + 4 * (uint64_t)s, j->nonce8 + 8 * i, raw, 13 + flen, j->rec + j->rec_off[i])
+                                      : fast_seal(&fk, j->ivs4 + 4 * (uint64_t)s, j->nonce8 + 8 * i, raw, 13 + flen, j->rec + j->rec_off[i]);
+            if (st) j->bad++;
         }
     }
     if (j->do_open) {
@@ -262,15 +279,21 @@ static void* worker(void* arg) {
         cur = 0xffffffffu;
         for (uint64_t i = j->r0; i < j->r1; i++) {
             uint32_t s = j->session[i];
-            if (s != cur) { fast_key_init(&fk, j->keys16 + 16 * (uint64_t)s); cur = s; }
+            if (s != cur) {
+                if (j->backend) cpuossl_key_set_dec(ok, j->keys16 + 16 * (uint64_t)s);
+                else fast_key_init(&fk, j->keys16 + 16 * (uint64_t)s);
+                cur = s;
+            }
             uint64_t olen = 0;
             uint8_t* o = j->out ? j->out + j->rec_off[i] : scratch;
-            int st = fast_open(&fk, j->ivs4 + 4 * (uint64_t)s, j->rec + j->rec_off[i], j->rec_off[i + 1] - j->rec_off[i], o, &olen);
+            int st = j->backend ? cpuossl_open(ok, j->ivs4 + 4 * (uint64_t)s, j->rec + j->rec_off[i], j->rec_off[i + 1] - j->rec_off[i], o, &olen)
+                                : fast_open(&fk, j->ivs4 + 4 * (uint64_t)s, j->rec + j->rec_off[i], j->rec_off[i + 1] - j->rec_off[i], o, &olen);
             if (st != ORC_OK) { j->bad++; continue; }
             /* TunnelMessage::decode (protocol.rs:157-172) + demux append (serve.rs:120-124) */
             uint64_t flen = olen - 13; const uint8_t* f = o + 13;
             if (flen < 5 || !orc_msg_type_valid(f[0])) { j->bad++; continue; }
             uint32_t sid = ((uint32_t)f[1] << 24) | ((uint32_t)f[2] << 16) | ((uint32_t)f[3] << 8) | f[4];
+            if (j->no_demux) { if (f[0] == 11 || f[0] == 21) j->body_bytes += flen - 5; continue; }
             stream_slot* sl = map_get(&m, ((uint64_t)s << 32) | sid);
             if (f[0] == 11 || f[0] == 21) map_append(sl, f + 5, flen - 5);
         }
@@ -283,6 +306,7 @@ static void* worker(void* arg) {
         map_free(&m);
     }
     free(scratch);
+    if (ok) cpuossl_key_free(ok);
     return NULL;
 }
 
@@ -293,13 +317,17 @@ static double now_s(void) {
 
 /* Runs encode->seal over all records, then open->decode->demux, on nthreads threads sharded by
  * contiguous record ranges cut at session boundaries.  times[0] = seal seconds, times[1] = open
- * seconds.  stats[0] = bad records, [1] = streams, [2] = body bytes reassembled, [3] = checksum. */
-int cpufast_pipeline(uint64_t n, const uint32_t* session, const uint8_t* keys16, const uint8_t* ivs4, uint32_t n_sessions,
-                     const uint16_t* epoch, const uint64_t* seq48, const uint8_t* nonce8,
-                     const uint8_t* types, const uint32_t* sids, const uint8_t* payload, const uint64_t* pay_off,
-                     uint8_t* rec, const uint64_t* rec_off, uint8_t* out, int nthreads, int phases,
-                     double* times, uint64_t* stats) {
-    if (!cpufast_supported()) return -1;
+ * seconds.  stats[0] = bad records, [1] = streams, [2] = body bytes reassembled, [3] = checksum.
+ * phases: bit 0 = seal, bit 1 = open + decode + demux append, bit 2 = open + decode WITHOUT the per-stream map
+ * (the AEAD alone; its seconds go to times[2], so only callers that set bit 2 need a third slot; stats then
+ * describe that last pass). */
+int cpufast_pipeline_ex(uint64_t n, const uint32_t* session, const uint8_t* keys16, const uint8_t* ivs4, uint32_t n_sessions,
+                        const uint16_t* epoch, const uint64_t* seq48, const uint8_t* nonce8,
+                        const uint8_t* types, const uint32_t* sids, const uint8_t* payload, const uint64_t* pay_off,
+                        uint8_t* rec, const uint64_t* rec_off, uint8_t* out, int nthreads, int phases,
+                        double* times, uint64_t* stats, int backend) {
+    if (backend == 0 && !cpufast_supported()) return -1;
+    if (backend == 1 && !cpuossl_available()) return -2;
     if (nthreads < 1) nthreads = 1;
     job* jobs = (job*)calloc((size_t)nthreads, sizeof(job));
     pthread_t* th = (pthread_t*)calloc((size_t)nthreads, sizeof(pthread_t));
@@ -311,14 +339,17 @@ int cpufast_pipeline(uint64_t n, const uint32_t* session, const uint8_t* keys16,
         jobs[t].n = n; jobs[t].session = session; jobs[t].keys16 = keys16; jobs[t].ivs4 = ivs4; jobs[t].n_sessions = n_sessions;
         jobs[t].epoch = epoch; jobs[t].seq48 = seq48; jobs[t].nonce8 = nonce8; jobs[t].types = types; jobs[t].sids = sids;
         jobs[t].payload = payload; jobs[t].pay_off = pay_off; jobs[t].rec = rec; jobs[t].rec_off = rec_off; jobs[t].out = out;
-        jobs[t].r0 = prev; jobs[t].r1 = end;
+        jobs[t].r0 = prev; jobs[t].r1 = end; jobs[t].backend = backend;
         prev = end;
     }
     memset(stats, 0, 4 * sizeof(uint64_t));
     times[0] = times[1] = 0;
-    for (int phase = 0; phase < 2; phase++) {
+    for (int phase = 0; phase < 3; phase++) {
         if (!(phases & (1 << phase))) continue;
-        for (int t = 0; t < nthreads; t++) { jobs[t].do_seal = (phase == 0); jobs[t].do_open = (phase == 1); }
+        for (int t = 0; t < nthreads; t++) {
+            jobs[t].do_seal = (phase == 0); jobs[t].do_open = (phase >= 1); jobs[t].no_demux = (phase == 2);
+            jobs[t].streams = jobs[t].body_bytes = jobs[t].checksum = 0;      /* bad records add up over the phases */
+        }
         double t0 = now_s();
         for (int t = 0; t < nthreads; t++) pthread_create(&th[t], NULL, worker, &jobs[t]);
         for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
@@ -329,6 +360,41 @@ int cpufast_pipeline(uint64_t n, const uint32_t* session, const uint8_t* keys16,
     }
     free(jobs); free(th);
     return 0;
+}
+
+int cpufast_pipeline(uint64_t n, const uint32_t* session, const uint8_t* keys16, const uint8_t* ivs4, uint32_t n_sessions,
+                     const uint16_t* epoch, const uint64_t* seq48, const uint8_t* nonce8,
+                     const uint8_t* types, const uint32_t* sids, const uint8_t* payload, const uint64_t* pay_off,
+                     uint8_t* rec, const uint64_t* rec_off, uint8_t* out, int nthreads, int phases,
+                     double* times, uint64_t* stats) {
+    return cpufast_pipeline_ex(n, session, keys16, ivs4, n_sessions, epoch, seq48, nonce8, types, sids, payload, pay_off,
+                               rec, rec_off, out, nthreads, phases, times, stats, 0);
+}
+
+/* batch seal / open through OpenSSL EVP (parity tests against the scalar oracle) */
+void cpuossl_seal_batch(uint64_t n, const uint32_t* session, const uint8_t* keys16, const uint8_t* ivs4,
+                        const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
+                        uint8_t* rec, const uint64_t* rec_off, uint8_t* status) {
+    void* k = cpuossl_key_new();
+    for (uint64_t i = 0; i < n; i++) {
+        cpuossl_key_set_enc(k, keys16 + 16 * (uint64_t)session[i]);
+        status[i] = (uint8_t)cpuossl_seal(k, ivs4 + 4 * (uint64_t)session[i], nonce8 + 8 * i, raw + raw_off[i],
+                                          raw_off[i + 1] - raw_off[i], rec + rec_off[i]);
+    }
+    cpuossl_key_free(k);
+}
+void cpuossl_open_batch(uint64_t n, const uint32_t* session, const uint8_t* keys16, const uint8_t* ivs4,
+                        const uint8_t* rec, const uint64_t* rec_off, uint8_t* out, const uint64_t* out_off,
+                        uint32_t* out_len, uint8_t* status) {
+    void* k = cpuossl_key_new();
+    for (uint64_t i = 0; i < n; i++) {
+        uint64_t ol = 0;
+        cpuossl_key_set_dec(k, keys16 + 16 * (uint64_t)session[i]);
+        status[i] = (uint8_t)cpuossl_open(k, ivs4 + 4 * (uint64_t)session[i], rec + rec_off[i],
+                                          rec_off[i + 1] - rec_off[i], out + out_off[i], &ol);
+        out_len[i] = (uint32_t)ol;
+    }
+    cpuossl_key_free(k);
 }
 
 /* plain batch seal / open with the fast path (for parity tests against the scalar oracle) */

@@ -70,3 +70,44 @@ def test_fast_pipeline_matches_oracle_and_counts_streams(fast):
     assert rc == 0
     assert np.array_equal(rec, ob.pipeline_seal(w, keys, ivs))
     assert stats[0] == 0 and stats[1] == 48 * 4 and stats[2] == n * 333
+
+
+def test_openssl_evp_baseline_matches_oracle(fast):
+    """the second timed baseline (oracle/p2pt_cpu_openssl.c: the record layout around EVP_aes_128_gcm) against
+    the scalar oracle, seal, open with tampering, and the threaded pipeline"""
+    if not fast.cpuossl_available():
+        pytest.skip("libcpufast.so was built without libcrypto")
+    rng = np.random.default_rng(10)
+    ns, n = 5, 600
+    keys = rng.integers(0, 256, (ns, 16), dtype=np.uint8); ivs = rng.integers(0, 256, (ns, 4), dtype=np.uint8)
+    lens = rng.integers(0, 1500, n).astype(np.uint64)
+    lens[:40] = np.arange(40)
+    raw_off = np.zeros(n + 1, np.uint64); np.cumsum(lens + np.uint64(13), out=raw_off[1:])
+    raw = rng.integers(0, 256, int(raw_off[-1]), dtype=np.uint8)
+    for i in range(n):
+        o = int(raw_off[i]); raw[o] = 23; raw[o + 1] = 0xFE; raw[o + 2] = 0xFD
+    session = rng.integers(0, ns, n).astype(np.uint32)
+    nonce = rng.integers(0, 256, 8 * n, dtype=np.uint8)
+    erec, rec_off, est = ob.dtls_seal(session, keys, ivs, nonce, raw, raw_off)
+    rec = np.zeros_like(erec); st = np.zeros(n, np.uint8)
+    fast.cpuossl_seal_batch(C.c_uint64(n), _p(session), _p(keys), _p(ivs), _p(nonce), _p(raw), _p(raw_off), _p(rec), _p(rec_off), _p(st))
+    assert np.array_equal(st, est) and np.array_equal(rec, erec)
+    bad = erec.copy()
+    for i in range(0, n, 13):
+        bad[int(rec_off[i]) + 21 + int(lens[i]) // 2] ^= 0x10
+    eout, _, eolen, est = ob.dtls_open(session, keys, ivs, bad, rec_off)
+    out = np.zeros_like(eout); olen = np.zeros(n, np.uint32)
+    fast.cpuossl_open_batch(C.c_uint64(n), _p(session), _p(keys), _p(ivs), _p(bad), _p(rec_off), _p(out), _p(rec_off), _p(olen), _p(st))
+    assert np.array_equal(st, est) and np.array_equal(olen, eolen) and np.array_equal(out, eout)
+
+    from p2p_llm_tunnel_b200 import workload
+    keys, ivs = workload.sessions_keys(48)
+    w = workload.pipeline_workload(48, 8, 333)
+    rec = np.zeros(int(w["rec_off"][-1]), np.uint8)
+    times = (C.c_double * 2)(); stats = (C.c_uint64 * 4)()
+    rc = fast.cpufast_pipeline_ex(C.c_uint64(w["n"]), _p(w["session"]), _p(keys), _p(ivs), 48, _p(w["epoch"]), _p(w["seq48"]),
+                                  _p(w["nonce8"]), _p(w["types"]), _p(w["sids"]), _p(w["payload"]), _p(w["pay_off"]),
+                                  _p(rec), _p(w["rec_off"]), None, 3, 3, times, stats, 1)
+    assert rc == 0
+    assert np.array_equal(rec, ob.pipeline_seal(w, keys, ivs))
+    assert stats[0] == 0 and stats[1] == 48 * 4 and stats[2] == w["n"] * 333

@@ -1,6 +1,7 @@
-"""Per-config, per-kernel device-resident timings for BASELINE.json configs C2 / C3 / C4 with the CPU
-port beside them.  Prints one JSON object; bench.py (C5) stays the headline.
-usage: python tools/bench_configs.py > profiles/rNN_configs.json"""
+"""Per-config, per-kernel device-resident timings for BASELINE.json configs C2 / C3 / C4, the SCTP layer and the
+bookkeeping kernels.  bench.py imports run_all() and puts the result into its JSON line as `configs` (GPU legs
+only); run as a script it also times the CPU port beside every stage and prints one JSON object.
+usage: python tools/bench_configs.py > profiles/rNN_configs.json        (ONLY=substring filters the configs)"""
 import ctypes as C
 import json
 import os
@@ -15,16 +16,24 @@ import __graft_entry__ as g  # noqa: E402
 import p2p_llm_tunnel_b200 as p2pt  # noqa: E402
 from p2p_llm_tunnel_b200 import workload  # noqa: E402
 
-dev = torch.device("cuda:0")
-ctx = p2pt.Context(0)
-pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
-peak = json.load(open(pk)).get("hbm_gbs", 6650.0) if os.path.exists(pk) else 6650.0
-g.build_oracle()
-fast = C.CDLL(g.CPUFAST_LIB)
+dev = ctx = fast = s = None
+peak = 6650.0
 cores = os.cpu_count() or 1
-s = torch.cuda.current_stream().cuda_stream
 t = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
 p = lambda a: C.c_void_p(a.ctypes.data)
+
+
+def setup(context, device, with_cpu):
+    """bind the module to a p2pt context / torch device; with_cpu loads the timed CPU port (oracle/libcpufast.so)"""
+    global dev, ctx, fast, s, peak
+    dev, ctx = device, context
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak = json.load(open(pk)).get("hbm_gbs", 6650.0) if os.path.exists(pk) else 6650.0
+    s = torch.cuda.current_stream().cuda_stream
+    fast = None
+    if with_cpu:
+        g.build_oracle()
+        fast = C.CDLL(g.CPUFAST_LIB)
 
 
 def timeit(fn, reps=5):
@@ -55,9 +64,9 @@ def codec_config(n, P, sse):
     t_enc, t_dec, t_dmx, t_dmg = timeit(enc), timeit(dec), timeit(dmx), timeit(dmg)
     assert int(k.item()) == 4096
     t_both = timeit(lambda: (dec(), dmg()))
-    hf = np.zeros(n * (P + 5), np.uint8)
+    hf = np.zeros(n * (P + 5), np.uint8) if fast else None
     res = {}
-    for nt in (1, cores):
+    for nt in ((1, cores) if fast else ()):
         times = (C.c_double * 2)(); stats = (C.c_uint64 * 3)()
         best = [1e9, 1e9]
         for _ in range(2):
@@ -67,7 +76,12 @@ def codec_config(n, P, sse):
         assert stats[0] == 0 and stats[2] == n * P
         res[f"cpu_{nt}_threads"] = {"encode_gbs_payload": n * P / best[0] / 1e9, "decode_demux_gbs_payload": n * P / best[1] / 1e9,
                                      "decode_demux_frames_per_s": n / best[1]}
-    assert np.array_equal(hf[: 1 << 20], frames[: 1 << 20].cpu().numpy())
+    if fast:
+        assert np.array_equal(hf[: 1 << 20], frames[: 1 << 20].cpu().numpy())
+    else:                                   # GPU-only run: check the encoder's output against numpy instead
+        f2 = frames[: 4096 * (P + 5)].cpu().numpy().reshape(4096, P + 5)
+        assert np.all(f2[:, 0] == 21) and np.array_equal(f2[:, 5:].reshape(-1), w["payload"][: 4096 * P])
+        assert np.array_equal(f2[:, 1:5].copy().view(">u4").reshape(-1), w["sids"][:4096])
     out = {
         "frames": n, "payload_bytes": P,
         "encode": {"ms": t_enc, "alg_bytes_per_frame": 2 * P + 26, "hbm_gbs": n * (2 * P + 26) / t_enc / 1e6,
@@ -124,9 +138,10 @@ def sctp_config(n, L):
     ra = lambda: ctx.call("p2pt_sctp_reassemble_batch_device", n, info, desc, None, out, n, msg, n * L, moff, mfirst, mstat, nm, scratch, sb, s)
     t_pk = timeit(pk); t_up = timeit(up); t_ra = timeit(ra)
     assert int(nm.item()) == n and int(mstat.sum()) == 0 and torch.equal(msg, d_msg)
-    hp = np.zeros(n * plen, np.uint8); hoff = workload.fixed_offsets(n, plen)
+    hp = np.zeros(n * plen, np.uint8) if fast else None
+    hoff = workload.fixed_offsets(n, plen)
     res = {}
-    for nt in (1, cores):
+    for nt in ((1, cores) if fast else ()):
         times = (C.c_double * 2)(); stats = (C.c_uint64 * 2)()
         fast.cpufast_sctp(C.c_uint64(n), p(w["payload"]), p(msg_off), p(hp), p(hoff), C.c_int(nt), times, stats)
         assert stats[0] == 0 and stats[1] == n * L
@@ -185,15 +200,25 @@ def bookkeeping_config(n):
                          "note": "two passes (count, emit): algorithmic bytes = 2 x body"}}
 
 
-configs = {"bookkeeping_1M_records": lambda: bookkeeping_config(1_000_000),
+CONFIGS = {"bookkeeping_1M_records": lambda: bookkeeping_config(1_000_000),
            "SCTP_1M_messages_1200B": lambda: sctp_config(1_000_000, 1200),
            "C2_1M_frames_1200B_4096_streams": lambda: codec_config(1_000_000, 1200, False),
            "C4_10M_frames_64B_sse": lambda: codec_config(10_000_000, 64, True),
            "C3_1M_records_1200B_1_session": lambda: records_config(1_000_000, 1200, 1),
            "C3_1M_records_1200B_4096_sessions": lambda: records_config(1_000_000, 1200, 4096)}
-only = os.environ.get("ONLY")                      # substring filter, e.g. ONLY=bookkeeping
-res = {"hbm_peak_gbs": peak, "host_cores": cores}
-for name, fn in configs.items():
-    if not only or only in name:
-        res[name] = fn()
-print(json.dumps(res, indent=1))
+
+
+def run_all(context, device, with_cpu=False, only=None):
+    """every config, device-resident, best of 5 with CUDA events on the launching stream; the caller must re-load its
+    own sessions afterwards (the C3 configs load theirs)"""
+    setup(context, device, with_cpu)
+    res = {"hbm_peak_gbs": peak, "host_cores": cores, "timing": "best of 5, CUDA events on the launching stream, inputs resident in HBM"}
+    for name, fn in CONFIGS.items():
+        if not only or only in name:
+            res[name] = fn()
+            torch.cuda.empty_cache()
+    return res
+
+
+if __name__ == "__main__":
+    print(json.dumps(run_all(p2pt.Context(0), torch.device("cuda:0"), with_cpu=True, only=os.environ.get("ONLY")), indent=1))
