@@ -360,20 +360,18 @@ def run_gpu(args):
         # (sessions share nothing, so each sub-batch is an independent call), the provider side seals
         # (serve.rs:269-276 + dc.send) while the consumer side opens + demuxes (rtc.rs:88 +
         # proxy.rs:109-170).  Two seal workers and two open workers, each a host thread with its own
-        # p2pt_ctx, keep PCIe busy in both directions; every byte goes host -> device -> host inside the
+        # call lane of the one p2pt_ctx, keep PCIe busy in both directions; every byte goes host -> device -> host inside the
         # timed region, through the host-pointer C ABI only.
         import queue
         NB = 8                                   # sub-batches per step (8192 sessions = 131072 records each)
         sub_n = n // NB
         sub_streams = max_streams // NB
         NW = 3                                   # workers (host thread + p2pt_ctx) per direction
-        ctxs = [ctx] + [p2pt.Context(local) for _ in range(2 * NW - 1)]
-        for c_ in ctxs[1:]:
-            c_.sessions_load(keys, ivs, keys, ivs)
-        for c_ in ctxs:
-            # with several calls in flight the overlap comes from the other workers; one large copy per
-            # direction per call is what PCIe moves fastest (measured: 48 GB/s vs 41 GB/s in 16 MiB pieces)
-            c_.set_option("chunk_bytes", 256 << 20)
+        # ONE context per GPU: its call lanes let all six workers be inside host-pointer calls at the same time
+        ctxs = [ctx] * (2 * NW)
+        # with several calls in flight the overlap comes from the other workers; one large copy per
+        # direction per call is what PCIe moves fastest (measured: 48 GB/s vs 41 GB/s in 16 MiB pieces)
+        ctx.set_option("chunk_bytes", 256 << 20)
 
         def pinned(a):
             return torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory()
@@ -453,14 +451,49 @@ def run_gpu(args):
         assert np.array_equal(h_gath[: 4096 * PAYLOAD].numpy().reshape(4096, PAYLOAD), got), "e2e result differs"
         tail = gathered[-4096 * PAYLOAD:].cpu().numpy()
         assert np.array_equal(h_gath[-4096 * PAYLOAD:].numpy(), tail), "e2e result differs (tail)"
-        launches_e0 = sum(c_.launch_count() for c_ in ctxs)
+        launches_e0 = ctx.launch_count()
         barrier()
         t0 = time.perf_counter()
         e2e_run(e2e_steps)
         torch.cuda.synchronize()
         e2e_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
         barrier()
-        launches_e2e = (sum(c_.launch_count() for c_ in ctxs) - launches_e0) // e2e_steps
+        launches_e2e = (ctx.launch_count() - launches_e0) // e2e_steps
+        # one side only, as a deployed box runs it (a provider seals, a consumer opens; the round trip above drags
+        # every payload byte over PCIe four times): all six workers on the same call, same sub-batches
+        def one_side(fn, steps):
+            jobs = steps * NB
+
+            def worker(i):
+                try:
+                    for q in range(i, jobs, 2 * NW):
+                        fn(ctx, (q // NB) & 1, q % NB)
+                except Exception as e:
+                    errs.append(e)
+            ts = [threading.Thread(target=worker, args=(i,)) for i in range(2 * NW)]
+            barrier()
+            t0_ = time.perf_counter()
+            for t_ in ts:
+                t_.start()
+            for t_ in ts:
+                t_.join()
+            torch.cuda.synchronize()
+            dt = max_over_ranks(time.perf_counter() - t0_) / steps
+            if errs:
+                raise errs[0]
+            return dt
+        one_side(do_seal, 1)
+        prov_s = one_side(do_seal, e2e_steps)
+        one_side(do_open, 1)
+        cons_s = one_side(do_open, e2e_steps)
+        sides = {"provider_only": {"value": world * payload_bytes / prov_s / 1e9, "unit": "GB/s", "ms_per_step": prov_s * 1e3,
+                                   "h2d_bytes_per_step": int(payload_bytes + n * (4 + 2 + 8 + 8 + 1 + 4 + 8 + 8)),
+                                   "d2h_bytes_per_step": int(rec_bytes + n),
+                                   "call": "p2pt_pipeline_seal (serve.rs:269-276 + dc.send): payload up, sealed records down"},
+                 "consumer_only": {"value": world * payload_bytes / cons_s / 1e9, "unit": "GB/s", "ms_per_step": cons_s * 1e3,
+                                   "h2d_bytes_per_step": int(rec_bytes + n * (4 + 8)),
+                                   "d2h_bytes_per_step": int(payload_bytes + n * 28 + NB * (sub_streams + 1) * 24),
+                                   "call": "p2pt_pipeline_open_demux (rtc.rs:88 + proxy.rs:109-170): records up, per-stream bodies down"}}
         # latency of ONE sub-batch through both calls with nothing else running, for reference
         t0 = time.perf_counter(); do_seal(ctxs[0], 0, 0); t_seal = time.perf_counter() - t0
         t0 = time.perf_counter(); do_open(ctxs[NW], 0, 0); t_open = time.perf_counter() - t0
@@ -543,14 +576,14 @@ def run_gpu(args):
                 pcie["bidir_each_gbs_all_ranks_at_once"] = 4 * nb / t_all / 1e9
 
 
-        return e2e_val, e2e_s, e2e_steps, launches_e2e, t_seal, t_open, h2d, d2h, pcie, lat, sub_n, NB
+        return e2e_val, e2e_s, e2e_steps, launches_e2e, t_seal, t_open, h2d, d2h, pcie, lat, sub_n, NB, sides
 
     if args.no_e2e:
         e2e_val = e2e_s = t_seal = t_open = None
         e2e_steps = launches_e2e = h2d = d2h = sub_n = NB = 0
-        pcie = lat = None
+        pcie = lat = sides = None
     else:
-        e2e_val, e2e_s, e2e_steps, launches_e2e, t_seal, t_open, h2d, d2h, pcie, lat, sub_n, NB = run_e2e()
+        e2e_val, e2e_s, e2e_steps, launches_e2e, t_seal, t_open, h2d, d2h, pcie, lat, sub_n, NB, sides = run_e2e()
 
     if rank != 0:
         if world > 1:
@@ -646,12 +679,13 @@ def run_gpu(args):
                 "one_subbatch_alone_ms": {"pipeline_seal": t_seal * 1e3, "pipeline_open_demux": t_open * 1e3,
                                           "records": sub_n},
                 "pcie": pcie,
+                "provider_only": sides["provider_only"], "consumer_only": sides["consumer_only"],
                 # against what PCIe delivered per direction with both directions busy (on every rank at once for N > 1)
                 "frac_of_pcie": (max(h2d, d2h) / e2e_s / 1e9) / pcie.get("bidir_each_gbs_all_ranks_at_once", pcie["bidir_each_gbs"])
                 if pcie and "bidir_each_gbs" in pcie else None,
                 "note": f"each step = the same {n}-record batch as {NB} sub-batches of whole sessions through "
                         "p2pt_pipeline_seal then p2pt_pipeline_open_demux (host pointers, pinned memory); 3 seal + 3 open "
-                        "worker threads, one p2pt_ctx each; fill and drain of the worker pipeline are inside the timing; "
+                        "worker threads on ONE p2pt_ctx (its call lanes); fill and drain of the worker pipeline are inside the timing; "
                         f"each step moves {h2d / 1e9:.2f} GB up and {d2h / 1e9:.2f} GB down over PCIe"},
         "gpu_launches": int(launches),
         "single_frame_latency": lat,

@@ -20,9 +20,11 @@
  *   - Entry points without a suffix take HOST pointers and do host->device copy, kernels,
  *     device->host copy, synchronously.  *_device entry points take DEVICE pointers plus a
  *     cudaStream_t (as void*) and only enqueue kernels; they allocate nothing.
- *   - Re-entrant: any thread may call on any ctx; host-pointer calls on one ctx serialise on the
- *     ctx's staging buffers.  One ctx per GPU.  There is no CPU fallback: without a CUDA device
- *     p2pt_ctx_create fails.
+ *   - Re-entrant: any thread may call on any ctx, and up to eight host-pointer calls run on one ctx at
+ *     the same time (each takes one of the ctx's call lanes - streams, staging arena, mapped buffer -
+ *     for its duration; a ninth caller waits for a lane).  This is the reference's calling pattern:
+ *     many tokio tasks encode and send over one connection (main.rs:18, serve.rs:131).  One ctx per
+ *     GPU.  There is no CPU fallback: without a CUDA device p2pt_ctx_create fails.
  */
 #ifndef P2PT_H
 #define P2PT_H
@@ -158,8 +160,9 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
  * are reproducible.  session[i] indexes the table given to p2pt_sessions_load (local key / iv).
  * Needs rec_off[i+1] - rec_off[i] >= raw_len_i + 24.  status: OK or BAD_HEADER (raw_len < 13, session index
  * out of range, or an item above 1 000 000 bytes).  Bytes of an output slot beyond the item written into it are
- * unspecified after a host-pointer call (the whole slot range is copied back).  Do not call
- * p2pt_sessions_load while seal / open calls on the same ctx are in flight. */
+ * ZERO after the call (seal, open and the fused forms alike: the kernel clears them, so nothing an earlier batch
+ * left in the staging memory can reach the caller), and so is the whole slot of an item that was refused.  Do
+ * not call p2pt_sessions_load while seal / open calls on the same ctx are in flight. */
 int32_t p2pt_dtls_gcm_seal_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session,
                                  const uint8_t* nonce8, const uint8_t* raw, const uint64_t* raw_off,
                                  uint8_t* rec, const uint64_t* rec_off, uint8_t* status);

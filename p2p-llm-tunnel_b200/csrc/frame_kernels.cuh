@@ -28,56 +28,206 @@ __device__ __forceinline__ bool msg_type_valid(uint32_t b) {
 // encode 0.447 / 0.463 / 0.435 ms at 4 / 5 / 6 blocks; demux + gather 0.573 / 0.588 / 0.588 ms (the gather
 // spills at 40 registers).
 #ifndef P2PT_ENCODE_MIN_BLOCKS
-#define P2PT_ENCODE_MIN_BLOCKS 6
+#define P2PT_ENCODE_MIN_BLOCKS 4
 #endif
 #ifndef P2PT_GATHER_MIN_BLOCKS
 #define P2PT_GATHER_MIN_BLOCKS 4
 #endif
 
-// ---- encode: a warp takes a tile of 8 * rounds consecutive frames (rounds = 1 or 4).  Lane l loads the
-// metadata of frame l (coalesced) and writes its 5-byte header; the payload copies then run in rounds of
-// eight frames, four lanes per frame, when all of the tile are short (<= 256 B, the SSE token regime),
-// else frame after frame with all 32 lanes (aligned 16-byte vectors either way).  Tiles of 32 amortise
-// the metadata latency over four times the frames; the host picks them when the batch is large enough
-// that every warp still gets many tiles (copy_tile_rounds), else the last warps would run alone.
+// ---- encode ----------------------------------------------------------------------------------------
+// Two regimes, chosen once per launch from the average output slot (two loads every thread makes):
+//
+//  * general (slots above kSmallFrameAvg bytes on average): a warp takes a tile of 8 * rounds consecutive frames
+//    (rounds = 1 or 4).  Lane l loads the metadata of frame l (coalesced) and writes its 5-byte header; the payload
+//    copies then run in rounds of eight frames, four lanes per frame, when all of the tile are short (<= 256 B),
+//    else frame after frame with all 32 lanes (aligned 16-byte vectors either way).  Tiles of 32 amortise the
+//    metadata latency over four times the frames; the host picks them when the batch is large enough that every
+//    warp still gets many tiles (copy_tile_rounds), else the last warps would run alone.
+//  * small frames (the SSE token regime, 10 M x 64 B): a 69-byte stride makes two of every five aligned
+//    destination vectors partial, and with frames written straight to global memory 13 of 32 lanes were live
+//    on average (0.30 of the HBM roofline).  Here a block takes kSmallTile consecutive frames at a time: their
+//    payload span is contiguous (offsets are back to back by construction) and comes into shared memory as whole
+//    aligned vectors; two lanes per frame then lay header + payload out in a second shared buffer at the
+//    frame's output position (32-bit shared-memory words, one funnel shift each, any alignment on both sides);
+//    and the output span - contiguous when the slots have no gaps - leaves as whole aligned 16-byte vectors.
+//    Only the two ends of a span are partial.  A tile whose slots have gaps or whose span does not fit the
+//    buffers takes the general path's four-lanes-per-frame copy.
+constexpr int kSmallTile = 128;                  // frames per block iteration in the small-frame regime
+constexpr uint32_t kSmallTileIn = 8192;          // payload span held in shared memory
+constexpr uint32_t kSmallTileOut = kSmallTileIn + 5 * kSmallTile;
+constexpr u64 kSmallFrameAvg = 128;              // average slot (bytes) up to which a launch runs in the small-frame regime
+
+// len bytes from shared src to shared dst, any alignment on either side, by `parts` cooperating lanes (part =
+// 0 .. parts - 1).  Whole destination words come from two source words and a funnel shift; each lane walks a
+// contiguous run of words so that consecutive words share a source word.
+__device__ __forceinline__ void smem_copy_unaligned(uint8_t* dst, const uint8_t* src, uint32_t len, int part, int parts) {
+    const uint32_t d0 = (uint32_t)((4 - ((uintptr_t)dst & 3)) & 3);               // bytes up to the first aligned dst word
+    if (len < d0 + 4) {                                                          // no whole word: bytes
+        for (uint32_t b = part; b < len; b += parts) dst[b] = src[b];
+        return;
+    }
+    const uint32_t nw = (len - d0) >> 2;                                         // whole destination words
+    if (part == 0) for (uint32_t b = 0; b < d0; b++) dst[b] = src[b];
+    if (part == parts - 1) for (uint32_t b = d0 + 4 * nw; b < len; b++) dst[b] = src[b];
+    const uint32_t per = (nw + parts - 1) / parts, w0 = per * part;
+    uint32_t w1 = w0 + per; if (w1 > nw) w1 = nw;
+    if (w0 >= w1) return;
+    uint32_t* dw = reinterpret_cast<uint32_t*>(dst + d0);
+    const uint8_t* s = src + d0 + 4 * w0;
+    const unsigned sh = (unsigned)((uintptr_t)s & 3) * 8;
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(s - ((uintptr_t)s & 3));
+    uint32_t lo = sw[0];
+    for (uint32_t k = 0; k < w1 - w0; k++) {
+        const uint32_t hi = sw[k + 1];          // for an aligned source the funnel ignores it; the buffers carry 32 spare bytes
+        dw[w0 + k] = __funnelshift_r(lo, hi, sh);
+        lo = hi;
+    }
+}
+
 __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kernel(
     u64 n, const uint8_t* __restrict__ types, const uint32_t* __restrict__ sids,
     const uint8_t* __restrict__ payload, const u64* __restrict__ pay_off,
     uint8_t* __restrict__ out, const u64* __restrict__ out_off, int rounds) {
     const int lane = threadIdx.x & 31, quad = lane >> 2, q = lane & 3;
-    const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
-    const int tile = 8 * rounds;
-    for (u64 i0 = warp * tile; i0 < n; i0 += nwarps * tile) {
-        const u64 i = i0 + lane;
-        u64 po = 0, oo = 0;
-        uint32_t len = 0;
-        bool live = lane < tile && i < n;
-        if (live) {
-            po = __ldg(pay_off + i); oo = __ldg(out_off + i);
-            const u64 l64 = __ldg(pay_off + i + 1) - po;
-            len = (uint32_t)l64;                       // payload lengths are 32-bit throughout (p2pt_desc.pay_len)
-            const uint32_t sid = __ldg(sids + i);      // header: [type][stream_id BE]
-            uint8_t* o = out + oo;
-            o[0] = __ldg(types + i);
-            o[1] = (uint8_t)(sid >> 24); o[2] = (uint8_t)(sid >> 16); o[3] = (uint8_t)(sid >> 8); o[4] = (uint8_t)sid;
-        }
-        if (__all_sync(0xffffffffu, len <= kQuadCopyMax)) {
+    if (__ldg(out_off + n) - __ldg(out_off) > n * kSmallFrameAvg) {
+        // ------------------------------------------------------------------ general regime
+        const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+        const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
+        const int tile = 8 * rounds;
+        for (u64 i0 = warp * tile; i0 < n; i0 += nwarps * tile) {
+            const u64 i = i0 + lane;
+            u64 po = 0, oo = 0;
+            uint32_t len = 0;
+            bool live = lane < tile && i < n;
+            if (live) {
+                po = __ldg(pay_off + i); oo = __ldg(out_off + i);
+                const u64 l64 = __ldg(pay_off + i + 1) - po;
+                len = (uint32_t)l64;                       // payload lengths are 32-bit throughout (p2pt_desc.pay_len)
+                const uint32_t sid = __ldg(sids + i);      // header: [type][stream_id BE]
+                uint8_t* o = out + oo;
+                o[0] = __ldg(types + i);
+                o[1] = (uint8_t)(sid >> 24); o[2] = (uint8_t)(sid >> 16); o[3] = (uint8_t)(sid >> 8); o[4] = (uint8_t)sid;
+            }
+            if (__all_sync(0xffffffffu, len <= kQuadCopyMax)) {
 #pragma unroll
-            for (int r = 0; r < 4; r++) {
-                if (r >= rounds) break;
-                const int f = 8 * r + quad;
-                const u64 fpo = __shfl_sync(0xffffffffu, po, f), foo = __shfl_sync(0xffffffffu, oo, f);
-                const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
-                if (flen) quad_copy_bytes(out + foo + 5, payload + fpo, flen, q);
+                for (int r = 0; r < 4; r++) {
+                    if (r >= rounds) break;
+                    const int f = 8 * r + quad;
+                    const u64 fpo = __shfl_sync(0xffffffffu, po, f), foo = __shfl_sync(0xffffffffu, oo, f);
+                    const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
+                    if (flen) quad_copy_bytes(out + foo + 5, payload + fpo, flen, q);
+                }
+            } else {
+#pragma unroll 1
+                for (int f = 0; f < tile; f++) {
+                    const u64 fpo = __shfl_sync(0xffffffffu, po, f), foo = __shfl_sync(0xffffffffu, oo, f);
+                    const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
+                    if (flen) warp_copy_bytes(out + foo + 5, payload + fpo, flen, lane);
+                }
+            }
+        }
+        return;
+    }
+    // ---------------------------------------------------------------------- small-frame regime
+    __shared__ __align__(16) uint8_t sin[kSmallTileIn + 32];
+    __shared__ __align__(16) uint8_t sout[kSmallTileOut + 32];
+    __shared__ u64 s_po[kSmallTile + 1], s_oo[kSmallTile + 1];
+    __shared__ uint32_t s_sid[kSmallTile];
+    __shared__ uint8_t s_type[kSmallTile];
+    const int t = threadIdx.x;
+    const u64 ntile = (n + kSmallTile - 1) / kSmallTile;
+    // Software pipeline over the block's tiles: the global loads of tile k + 1 (offsets, stream ids, types and, when
+    // the tile is dense, its payload span) are issued into registers before tile k is shuffled and flushed, so a
+    // tile costs one memory round trip and two barriers.
+    struct TileRegs {
+        u64 pb, pe, ob, oe;        // ends of the payload span and of the slot span (every thread loads them: broadcast)
+        u64 po, oo;                // offsets of frame t (t <= T)
+        uint32_t sid; uint8_t type;
+        uint4 v[3];                // this thread's aligned vectors of the payload span (<= 513 over 256 threads)
+        int T; bool dense;
+    };
+    auto load_tile = [&](u64 tile, TileRegs& r) {
+        const u64 i0 = tile * kSmallTile;
+        r.T = n - i0 < (u64)kSmallTile ? (int)(n - i0) : kSmallTile;
+        r.pb = __ldg(pay_off + i0); r.pe = __ldg(pay_off + i0 + r.T);
+        r.ob = __ldg(out_off + i0); r.oe = __ldg(out_off + i0 + r.T);
+        r.po = r.oo = 0; r.sid = 0; r.type = 0;
+        if (t <= r.T) { r.po = __ldg(pay_off + i0 + t); r.oo = __ldg(out_off + i0 + t); }
+        if (t < r.T) { r.sid = __ldg(sids + i0 + t); r.type = __ldg(types + i0 + t); }
+        r.dense = (r.oe - r.ob == (r.pe - r.pb) + 5ull * (u64)r.T) && (r.pe - r.pb <= kSmallTileIn);
+        if (r.dense) {
+            // whole aligned vectors (an aligned vector that holds one byte of the span lies in the same page as that
+            // byte, so the few bytes read beyond either end of the span are always mapped)
+            const uint8_t* gsrc = payload + r.pb;
+            const uint32_t ia = (uint32_t)((uintptr_t)gsrc & 15);
+            const uint32_t nvin = (ia + (uint32_t)(r.pe - r.pb) + 15) >> 4;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const uint32_t vi = t + 256 * k;
+                if (vi < nvin) r.v[k] = ldg128_stream(gsrc - ia + 16 * (size_t)vi);
+            }
+        }
+    };
+    TileRegs cur;
+    if (blockIdx.x < ntile) load_tile(blockIdx.x, cur);
+    for (u64 tile = blockIdx.x; tile < ntile; tile += gridDim.x) {
+        const int T = cur.T;
+        const u64 pb = cur.pb, ob = cur.ob;
+        const uint32_t ispan = (uint32_t)(cur.pe - cur.pb);
+        const u64 ospan = cur.oe - cur.ob;
+        const bool dense = cur.dense;
+        const uint32_t ia = (uint32_t)((uintptr_t)(payload + pb) & 15);
+        // registers -> shared memory (every thread is past the previous tile's shuffle: its second barrier)
+        if (t <= T) { s_po[t] = cur.po; s_oo[t] = cur.oo; }
+        if (t < T) { s_sid[t] = cur.sid; s_type[t] = cur.type; }
+        if (dense) {
+            const uint32_t nvin = (ia + ispan + 15) >> 4;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const uint32_t vi = t + 256 * k;
+                if (vi < nvin) *reinterpret_cast<uint4*>(sin + 16 * vi) = cur.v[k];
+            }
+        }
+        __syncthreads();                                               // tile in shared memory; previous flush behind everyone
+        if (tile + gridDim.x < ntile) load_tile(tile + gridDim.x, cur);   // next tile's loads fly during the rest
+        if (dense) {
+            uint8_t* gdst = out + ob;
+            const uint32_t oa = (uint32_t)((uintptr_t)gdst & 15);      // sout keeps the span's 16-byte phase
+            {
+                const int f = t >> 1, h = t & 1;                       // two lanes per frame
+                if (f < T) {
+                    const uint32_t po = (uint32_t)(s_po[f] - pb), len = (uint32_t)(s_po[f + 1] - s_po[f]);
+                    uint8_t* d = sout + oa + (uint32_t)(s_oo[f] - ob);
+                    if (h == 0) {                                      // header: [type][stream_id BE]
+                        const uint32_t sid = s_sid[f];
+                        d[0] = s_type[f];
+                        d[1] = (uint8_t)(sid >> 24); d[2] = (uint8_t)(sid >> 16); d[3] = (uint8_t)(sid >> 8); d[4] = (uint8_t)sid;
+                    }
+                    if (len) smem_copy_unaligned(d + 5, sin + ia + po, len, h, 2);
+                }
+            }
+            __syncthreads();
+            const uint32_t total = oa + (uint32_t)ospan;               // [oa, total) of sout is the span
+            uint8_t* g0 = gdst - oa;
+            for (uint32_t lo = 16u * t; lo < total; lo += 16u * 256u) {
+                const uint4 x = *reinterpret_cast<const uint4*>(sout + lo);
+                if (lo >= oa && lo + 16 <= total) stg128(g0 + lo, x);
+                else store_bytes(g0 + lo, x, lo < oa ? (int)(oa - lo) : 0, total - lo < 16u ? (int)(total - lo) : 16);
             }
         } else {
-#pragma unroll 1
-            for (int f = 0; f < tile; f++) {
-                const u64 fpo = __shfl_sync(0xffffffffu, po, f), foo = __shfl_sync(0xffffffffu, oo, f);
-                const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
-                if (flen) warp_copy_bytes(out + foo + 5, payload + fpo, flen, lane);
+            // slack between the slots, or a span beyond the buffers: four lanes per frame, straight to global memory
+            for (int f = t >> 2; f < T; f += 64) {
+                const u64 po = s_po[f];
+                const uint32_t len = (uint32_t)(s_po[f + 1] - po);
+                uint8_t* o = out + s_oo[f];
+                if ((t & 3) == 0) {
+                    const uint32_t sid = s_sid[f];
+                    o[0] = s_type[f];
+                    o[1] = (uint8_t)(sid >> 24); o[2] = (uint8_t)(sid >> 16); o[3] = (uint8_t)(sid >> 8); o[4] = (uint8_t)sid;
+                }
+                if (len) quad_copy_bytes(o + 5, payload + po, len, t & 3);
             }
+            __syncthreads();                                           // s_po / s_oo are rewritten for the next tile
         }
     }
 }
@@ -129,10 +279,17 @@ __global__ void __launch_bounds__(256) frame_decode_kernel(
 //
 // Scratch layout (p2pt_frame_demux_scratch_bytes): two key and two index arrays for ping-pong, the
 // [digit][block] histogram matrix, and the block sums of the final (stream count, body bytes) scan.
+//
+// Packed mode: without a session array the key is the 32-bit stream id, so key and frame index travel as
+// ONE 64-bit word (stream_id << 32 | index) and the index arrays are not touched at all: a sorting pass
+// moves 8 bytes per frame instead of 12 (the digit of key byte b is then byte 4 + b of the word).
 
 constexpr int kSortBlocks = 592;        // 4 x 148 SMs
 constexpr int kSortThreads = 256;
-constexpr int kSortItems = 4;           // keys per thread per chunk
+#ifndef P2PT_SORT_ITEMS
+#define P2PT_SORT_ITEMS 4
+#endif
+constexpr int kSortItems = P2PT_SORT_ITEMS;   // keys per thread per chunk
 constexpr int kRadix = 256;
 constexpr int kScanThreads = 1024;
 constexpr int kKeyPasses = 8;           // 8 key bytes, then the validity pass
@@ -183,9 +340,10 @@ inline DemuxScratch demux_carve(void* scratch, u64 n) {
 }
 
 // digit of element i of the pass's source buffers; the index array is only touched by the validity pass
-__device__ __forceinline__ uint32_t demux_digit(const u64* keys, const uint32_t* idx, u64 i, int pass, const uint32_t* blen) {
-    if (pass < kKeyPasses) return (uint32_t)(__ldcg(keys + i) >> (8 * pass)) & 0xffu;
-    return __ldg(blen + __ldcg(idx + i)) == kNotDecodable ? 1u : 0u;
+__device__ __forceinline__ uint32_t demux_digit(const u64* keys, const uint32_t* idx, u64 i, int pass, const uint32_t* blen, bool packed) {
+    if (pass < kKeyPasses) return (uint32_t)(__ldcg(keys + i) >> (8 * pass + (packed ? 32 : 0))) & 0xffu;
+    const uint32_t ix = packed ? (uint32_t)__ldcg(keys + i) : __ldcg(idx + i);
+    return __ldg(blen + ix) == kNotDecodable ? 1u : 0u;
 }
 
 __global__ void __launch_bounds__(256) demux_init_kernel(u64 n, const p2pt_desc* __restrict__ desc,
@@ -198,9 +356,13 @@ __global__ void __launch_bounds__(256) demux_init_kernel(u64 n, const p2pt_desc*
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const p2pt_desc d = desc[i];
         u64 k = d.stream_id;
-        if (session) k |= (u64)session[i] << 32;
-        keys[i] = k;
-        idx[i] = (uint32_t)i;
+        if (session) {
+            k |= (u64)session[i] << 32;
+            keys[i] = k;
+            idx[i] = (uint32_t)i;
+        } else {
+            keys[i] = (k << 32) | (u64)(uint32_t)i;      // packed mode
+        }
         vor |= k; vnor |= ~k;
         const bool ok = d.status == P2PT_ST_OK;
         bad += !ok;
@@ -253,7 +415,7 @@ __device__ __forceinline__ void demux_tile(u64 n, u64& lo, u64& hi) {
 // wrote (keys, indices, the histogram matrix, row totals) is read with __ldcg, i.e. from L2: inside a
 // single kernel an L1 line cached in an earlier pass would be stale.
 __device__ __forceinline__ void demux_hist_phase(u64 n, const DemuxBufs& bufs, const uint32_t* blen, int pass,
-                                                 uint32_t* hist, const u64* misc) {
+                                                 uint32_t* hist, const u64* misc, bool packed) {
     const int sb = demux_src_buffer(misc, pass);
     const u64* keys = bufs.keys[sb];
     const uint32_t* idx = bufs.idx[sb];
@@ -275,7 +437,7 @@ __device__ __forceinline__ void demux_hist_phase(u64 n, const DemuxBufs& bufs, c
         for (int r = 0; r < kSortItems; r++) {           // all loads first
             const u64 i = c0 + r * kSortThreads + threadIdx.x;
             live[r] = i < hi;
-            d[r] = live[r] ? demux_digit(keys, idx, i, pass, blen) : 0u;
+            d[r] = live[r] ? demux_digit(keys, idx, i, pass, blen, packed) : 0u;
         }
 #pragma unroll
         for (int r = 0; r < kSortItems; r++) {
@@ -322,7 +484,7 @@ __device__ __forceinline__ void demux_rowscan_row(uint32_t* hist, int row, uint3
 }
 
 __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs, const uint32_t* blen, int pass,
-                                                    const uint32_t* hist, const u64* misc, const uint32_t* row_total) {
+                                                    const uint32_t* hist, const u64* misc, const uint32_t* row_total, bool packed) {
     const int sb = demux_src_buffer(misc, pass);
     const u64* keys = bufs.keys[sb];
     const uint32_t* idx = bufs.idx[sb];
@@ -376,13 +538,14 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
             const u64 i = c0 + (u64)warp * (32 * kSortItems) + r * 32 + lane;
             live[r] = i < hi;
             key[r] = 0; ix[r] = 0;
-            if (live[r]) { key[r] = __ldcg(keys + i); ix[r] = __ldcg(idx + i); }
+            if (live[r]) { key[r] = __ldcg(keys + i); ix[r] = packed ? (uint32_t)key[r] : __ldcg(idx + i); }
         }
 #pragma unroll
         for (int r = 0; r < kSortItems; r++) {
             d[r] = 0;
             if (live[r])
-                d[r] = pass < kKeyPasses ? (uint32_t)(key[r] >> (8 * pass)) & 0xffu : (__ldg(blen + ix[r]) == kNotDecodable ? 1u : 0u);
+                d[r] = pass < kKeyPasses ? (uint32_t)(key[r] >> (8 * pass + (packed ? 32 : 0))) & 0xffu
+                                         : (__ldg(blen + ix[r]) == kNotDecodable ? 1u : 0u);
         }
         __syncthreads();                                 // counters zeroed; the previous chunk's write-out is done
         // rank among equal digits inside the warp's 32 x kSortItems keys, in arrival order
@@ -426,7 +589,8 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
         for (int r = 0; r < kSortItems; r++) {
             if (live[r]) {
                 const uint32_t lp = dstart[d[r]] + wcount[warp][d[r]] + rank[r];
-                skey[lp] = key[r]; sidx[lp] = ix[r]; sdig[lp] = (uint8_t)d[r];
+                skey[lp] = key[r]; sdig[lp] = (uint8_t)d[r];
+                if (!packed) sidx[lp] = ix[r];
             }
         }
         __syncthreads();
@@ -436,7 +600,8 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
             const uint32_t t = r * kSortThreads + threadIdx.x;
             if (t < cnt) {
                 const uint32_t o = gofs[sdig[t]] + t;
-                keys_out[o] = skey[t]; idx_out[o] = sidx[t];
+                keys_out[o] = skey[t];
+                if (!packed) idx_out[o] = sidx[t];
             }
         }
     }
@@ -445,9 +610,9 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
 // three launches per pass (fallback path) ...
 __global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
     u64 n, const DemuxBufs bufs, const uint32_t* __restrict__ blen,
-    int pass, uint32_t* __restrict__ hist, const u64* __restrict__ misc) {
+    int pass, uint32_t* __restrict__ hist, const u64* __restrict__ misc, bool packed) {
     if (demux_pass_trivial(misc, pass)) return;
-    demux_hist_phase(n, bufs, blen, pass, hist, misc);
+    demux_hist_phase(n, bufs, blen, pass, hist, misc, packed);
 }
 __global__ void __launch_bounds__(32 * kRowScanWarps) demux_rowscan_kernel(uint32_t* __restrict__ hist, int pass,
                                                                           u64* __restrict__ misc,
@@ -459,24 +624,24 @@ __global__ void __launch_bounds__(32 * kRowScanWarps) demux_rowscan_kernel(uint3
 __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
     u64 n, const DemuxBufs bufs, const uint32_t* __restrict__ blen,
     int pass, const uint32_t* __restrict__ hist, const u64* __restrict__ misc,
-    const uint32_t* __restrict__ row_total) {
+    const uint32_t* __restrict__ row_total, bool packed) {
     if (demux_pass_trivial(misc, pass)) return;          // nothing to move: the data stays where it is
-    demux_scatter_phase(n, bufs, blen, pass, hist, misc, row_total);
+    demux_scatter_phase(n, bufs, blen, pass, hist, misc, row_total, packed);
 }
 
 // ... or all passes in ONE cooperative launch: the nine passes are launch-latency bound at 1 M items
 // (27 launches of a few microseconds each), so the phases are separated by grid-wide syncs instead.
 __global__ void __launch_bounds__(kSortThreads) demux_sort_coop_kernel(
-    u64 n, const DemuxBufs bufs, const uint32_t* blen, uint32_t* hist, const u64* misc, uint32_t* row_total) {
+    u64 n, const DemuxBufs bufs, const uint32_t* blen, uint32_t* hist, const u64* misc, uint32_t* row_total, bool packed) {
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     for (int pass = 0; pass < kSortPasses; pass++) {
         if (demux_pass_trivial(misc, pass)) continue;     // uniform over the whole grid
-        demux_hist_phase(n, bufs, blen, pass, hist, misc);
+        demux_hist_phase(n, bufs, blen, pass, hist, misc, packed);
         grid.sync();
         const int row = blockIdx.x * (kSortThreads / 32) + (threadIdx.x >> 5);
         if (row < kRadix) demux_rowscan_row(hist, row, row_total);
         grid.sync();
-        demux_scatter_phase(n, bufs, blen, pass, hist, misc, row_total);
+        demux_scatter_phase(n, bufs, blen, pass, hist, misc, row_total, packed);
         grid.sync();
     }
 }
@@ -541,24 +706,30 @@ struct DemuxQuad { u64 key[kDemuxItems]; uint32_t ix[kDemuxItems]; HeadBytes it[
 // packet with the same (session, TSN) is a retransmission to be dropped)
 __device__ __forceinline__ DemuxQuad demux_load_quad(u64 j, u64 m, u64 n, const u64* __restrict__ keys,
                                                      const uint32_t* __restrict__ idx, const uint32_t* __restrict__ blen,
-                                                     bool first_only) {
+                                                     bool first_only, bool packed) {
     DemuxQuad r;
     if (j + kDemuxItems <= n) {                          // arrays are 256-byte aligned, j is a multiple of 4
         const ulonglong2 k01 = *reinterpret_cast<const ulonglong2*>(keys + j);
         const ulonglong2 k23 = *reinterpret_cast<const ulonglong2*>(keys + j + 2);
-        const uint4 x = *reinterpret_cast<const uint4*>(idx + j);
         r.key[0] = k01.x; r.key[1] = k01.y; r.key[2] = k23.x; r.key[3] = k23.y;
-        r.ix[0] = x.x; r.ix[1] = x.y; r.ix[2] = x.z; r.ix[3] = x.w;
+        if (!packed) {
+            const uint4 x = *reinterpret_cast<const uint4*>(idx + j);
+            r.ix[0] = x.x; r.ix[1] = x.y; r.ix[2] = x.z; r.ix[3] = x.w;
+        }
     } else {
 #pragma unroll
         for (int e = 0; e < kDemuxItems; e++) {
             r.key[e] = j + e < n ? keys[j + e] : 0;
-            r.ix[e] = j + e < n ? idx[j + e] : 0;
+            r.ix[e] = (!packed && j + e < n) ? idx[j + e] : 0;
         }
+    }
+    if (packed) {                                        // word = stream_id << 32 | frame index
+#pragma unroll
+        for (int e = 0; e < kDemuxItems; e++) { r.ix[e] = (uint32_t)r.key[e]; r.key[e] >>= 32; }
     }
     // the key before this thread's first one: the neighbour lane holds it, lane 0 reads it
     u64 prev = __shfl_up_sync(0xffffffffu, r.key[kDemuxItems - 1], 1);
-    if ((threadIdx.x & 31) == 0 && j > 0 && j < m) prev = keys[j - 1];
+    if ((threadIdx.x & 31) == 0 && j > 0 && j < m) prev = packed ? keys[j - 1] >> 32 : keys[j - 1];
     r.sum.heads = 0; r.sum.bytes = 0;
 #pragma unroll
     for (int e = 0; e < kDemuxItems; e++) {
@@ -576,11 +747,11 @@ __device__ __forceinline__ DemuxQuad demux_load_quad(u64 j, u64 m, u64 n, const 
 
 __global__ void __launch_bounds__(kScanThreads) demux_blocksum_kernel(
     u64 n, const DemuxBufs bufs, const uint32_t* __restrict__ blen,
-    const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes, bool first_only) {
+    const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes, bool first_only, bool packed) {
     const int fb = demux_src_buffer(misc, kSortPasses);
     const u64 m = demux_valid_count(n, misc);
     const u64 j = ((u64)blockIdx.x * kScanThreads + threadIdx.x) * kDemuxItems;
-    const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen, first_only);
+    const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen, first_only, packed);
     HeadBytes tot;
     (void)block_scan_excl(qd.sum, tot);
     if (threadIdx.x == 0) { blk_heads[blockIdx.x] = tot.heads; blk_bytes[blockIdx.x] = tot.bytes; }
@@ -616,13 +787,13 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
     const u64* __restrict__ misc, const uint32_t* __restrict__ blk_heads, const u64* __restrict__ blk_bytes,
     u64 nblk, uint32_t max_streams, uint32_t* __restrict__ uniq_sid, uint32_t* __restrict__ uniq_session,
     u64* __restrict__ csr, uint32_t* __restrict__ perm, uint32_t* __restrict__ k_out,
-    u64* __restrict__ gathered_off, int dst_mode, bool first_only) {  // dst_mode: 0 none, 1 = 32-bit, 2 = 64-bit offsets
+    u64* __restrict__ gathered_off, int dst_mode, bool first_only, bool packed) {  // dst_mode: 0 none, 1 = 32-bit, 2 = 64-bit offsets
     const int fb = demux_src_buffer(misc, kSortPasses);
     u64* __restrict__ dst64 = bufs.keys[fb ^ 1];
     uint32_t* __restrict__ dst32 = reinterpret_cast<uint32_t*>(bufs.keys[fb ^ 1]);
     const u64 m = demux_valid_count(n, misc);
     const u64 j = ((u64)blockIdx.x * kScanThreads + threadIdx.x) * kDemuxItems;
-    const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen, first_only);
+    const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen, first_only, packed);
     HeadBytes tot;
     HeadBytes ex = block_scan_excl(qd.sum, tot);
     uint32_t heads = blk_heads[blockIdx.x] + ex.heads;

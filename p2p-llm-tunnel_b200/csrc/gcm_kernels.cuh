@@ -152,6 +152,19 @@ struct CtrRound1 {
         c2 = lut.template look<0, 0>(s2) ^ lut.template look<1, 1>(s3) ^ lut.template look<2, 2>(s0) ^ lut.template look<3, 3>(s1) ^ k1.z;
         c3 = lut.template look<0, 0>(s3) ^ lut.template look<1, 1>(s0) ^ lut.template look<2, 2>(s1) ^ lut.template look<3, 3>(s2) ^ k1.w;
     }
+    // the same with the four words and round key 0 word 3 read back from the group's slot (P2PT_GCM_PARK)
+    template <class Lut, class Keys>
+    static __device__ __forceinline__ void block_parked(const Lut& lut, const Keys& keys, uint32_t slot, uint32_t ctr,
+                                                        uint32_t& o0, uint32_t& o1, uint32_t& o2, uint32_t& o3) {
+        uint32_t r3w, q0, q1, q2, q3;
+        asm volatile("ld.shared.u32 %0, [%1+12];" : "=r"(r3w) : "r"(slot));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+336];" : "=r"(q0), "=r"(q1), "=r"(q2), "=r"(q3) : "r"(slot));
+        const uint32_t s3 = bswap32(ctr) ^ r3w;
+        o0 = q0 ^ lut.template look<3, 3>(s3);
+        o1 = q1 ^ lut.template look<2, 2>(s3);
+        o2 = q2; o3 = q3;
+        aes128_rounds<2>(lut, keys, o0, o1, o2, o3);
+    }
     // keystream block for counter ctr < 65536
     template <class Lut, class Keys>
     __device__ __forceinline__ void block(const Lut& lut, const Keys& keys, uint32_t ctr,
@@ -280,10 +293,38 @@ struct GcmArgs {
 #ifndef P2PT_GCM_UNROLL
 #define P2PT_GCM_UNROLL 1
 #endif
+// P2PT_GCM_PIPELINE 1: the keystream block of round t + 1 is computed in round t, ahead of the GHASH multiply
+// of round t, so that the two chains (table look-ups + PRMT on one side, IMAD.WIDE + LOP3 on the other) sit
+// in one basic block and can be interleaved; costs four live registers across the loop.
+#ifndef P2PT_GCM_PIPELINE
+#define P2PT_GCM_PIPELINE 0
+#endif
+// P2PT_GCM_INTERIOR 1: rounds in which every lane of the group holds a complete interior block (five readable
+// source words, a complete successor block, a multiply to follow) are recognised by ONE group-uniform test on the
+// round index and skip the per-slot edge bookkeeping (fast-path range tests, active / last-slot tracking, tail
+// stores); the AES and GHASH code itself exists once.
+#ifndef P2PT_GCM_INTERIOR
+#define P2PT_GCM_INTERIOR 0
+#endif
+// P2PT_GCM_PARK 1: values that live for the whole record but are used once per block or once per record are
+// parked in the group's shared-memory slot instead of registers - the four round-1 words of the counter block
+// (one broadcast LDS.128 per block), round key 0 word 3 (already in the slot) and E_K(J0) (read once for the
+// tag) - and the three body pointers of the edge path are rebuilt there.  At the 64-register cap the compiler
+// otherwise spills and re-derives loop invariants inside the loop (64-bit range tests, the shared window
+// address from S2R).
+#ifndef P2PT_GCM_PARK
+#define P2PT_GCM_PARK 0
+#endif
 constexpr int kGcmThreads = P2PT_GCM_THREADS;
 constexpr int kGcmUnroll = P2PT_GCM_UNROLL;
+#if P2PT_GCM_PARK
+constexpr uint32_t kGroupSlotBytes = 368;   // 11 x 16 B round keys + 9 x 16 B GHASH multiplier rows + E_K(J0) at 320 +
+                                            // the four round-1 words at 336; 368 = 23 x 16 keeps neighbouring groups'
+                                            // rows in different banks
+#else
 constexpr uint32_t kGroupSlotBytes = 336;   // 11 x 16 B round keys + 9 x 16 B GHASH multiplier rows, padded
                                             // so that neighbouring groups' rows fall in different banks
+#endif
 
 // Shared-memory map of the record kernel.  The T-tables must start on a 64 KiB boundary of the
 // shared window (PRMT addressing) and the window itself starts a little above 0 (the first KiB is
@@ -355,16 +396,21 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
         const u64 ioff = __ldg(a.in_off + i);
         const u64 ilen = __ldg(a.in_off + i + 1) - ioff;
         const uint8_t* ibase = a.in + ioff;
-        uint8_t* obase = a.out + __ldg(a.out_off + i);
+        const u64 ooff = __ldg(a.out_off + i);
+        uint8_t* obase = a.out + ooff;
+        const u64 oslot = __ldg(a.out_off + i + 1) - ooff;      // bytes of the slot beyond the item are cleared below:
+                                                                // nothing stale from an earlier batch may reach the caller
         const uint32_t sidx = __ldg(a.session + i);
         const SessionKey* sk = a.keys + (sidx < a.n_sessions ? sidx : 0);
 
         uint32_t L;                     // plaintext / ciphertext length
         uint32_t st = P2PT_ST_OK;
         uint32_t hdr_type = 23, hdr_v0 = 0xfe, hdr_v1 = 0xfd;
-        const uint8_t* body_lo;         // input body bytes live in [body_lo, body_hi)
+        // input body bytes live in [body_lo, body_hi); body0 = address of input body byte 0 (may precede body_lo:
+        // pipe-seal).  All three follow from ibase, ilen and L (P2PT_BODY_* below), so the edge path can rebuild them.
+        const uint8_t* body_lo;
         const uint8_t* body_hi;
-        const uint8_t* body0;           // address of input body byte 0 (may precede body_lo: pipe-seal)
+        const uint8_t* body0;
         if (MODE == kSeal) {
             if (ilen < 13) st = P2PT_ST_BAD_HEADER;
             L = (uint32_t)(ilen - 13);
@@ -395,6 +441,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
                     for (u64 b = j; b < ilen; b += G) obase[b] = __ldg(ibase + b);
                     olen = (uint32_t)ilen;
                 }
+                for (u64 b = olen + j; b < oslot; b += G) obase[b] = 0;
                 if (j == 0) {
                     if (MODE == kOpen) a.out_len[i] = olen;
                     if (MODE == kPipeOpen) {
@@ -404,6 +451,9 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
                         a.desc[i] = d;
                     }
                 }
+            }
+            else {
+                for (u64 b = j; b < oslot; b += G) obase[b] = 0;
             }
             if (j == 0 && a.status) a.status[i] = (uint8_t)st;
             continue;
@@ -465,14 +515,38 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
         __syncwarp(gmask);                                   // key slot visible to the whole group
         CtrRound1 r1;                                        // counters stay below 2^16: items are capped at 1 MB above
         r1.prepare(lut, rkeys, ivw, n0, n1);
+#if P2PT_GCM_PARK
+        if (j == 0) sts128(slot + 336, r1.c0, r1.c1, r1.c2, r1.c3);
+        __syncwarp(gmask);
+#define P2PT_KS(ctr, a0, a1, a2, a3) CtrRound1::block_parked(lut, rkeys, slot, (ctr), a0, a1, a2, a3)
+#else
+#define P2PT_KS(ctr, a0, a1, a2, a3) r1.block(lut, rkeys, (ctr), a0, a1, a2, a3)
+#endif
 
         U128 acc; acc.w[0] = acc.w[1] = acc.w[2] = acc.w[3] = 0;
+#if !P2PT_GCM_PARK
         uint4 ej0 = make_uint4(0, 0, 0, 0);                  // E_K(J0), valid in group lane 0
+#endif
         uint32_t carry3 = 0;                                 // last word of lane G-1's block, previous round
         uint32_t fh0 = 0, fh1 = 0;                           // pipe-open: first 8 plaintext bytes (lane 1)
-        uint32_t last_u = 0xffffffffu;
-
         const uint32_t rounds = (slots + G - 1) / G;
+#if P2PT_GCM_INTERIOR
+        // rounds t_in_lo..t_in_hi: for every lane j, block c = tG + j - 1 lies in [max(c_fast_lo, 0), min(c_fast_hi,
+        // nfull - 2)] and slot u + G exists
+        int t_in_lo, t_in_hi;
+        {
+            const int lo = c_fast_lo > 0 ? c_fast_lo : 0;
+            int hi = c_fast_hi < (int)nfull - 2 ? c_fast_hi : (int)nfull - 2;
+            t_in_lo = (lo + 1 + G - 1) / G;
+            const int a_ = hi + 2 - G, b_ = (int)slots - 2 * G;
+            const int m_ = a_ < b_ ? a_ : b_;
+            t_in_hi = m_ >= 0 ? m_ / G : -1;
+        }
+#endif
+#if P2PT_GCM_PIPELINE
+        uint32_t nk0, nk1, nk2, nk3;                         // keystream of the coming round
+        P2PT_KS((uint32_t)(j + 1), nk0, nk1, nk2, nk3);
+#endif
 #pragma unroll kGcmUnroll
         for (uint32_t t = 0; t < rounds; t++) {
             const uint32_t u = t * G + j;
@@ -481,12 +555,23 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
 
             // ---- AES-CTR keystream for counter c + 2 (J0 = counter 1)
             uint32_t k0, k1, k2, k3;
-            r1.block(lut, rkeys, (uint32_t)(c + 2), k0, k1, k2, k3);
+#if P2PT_GCM_PIPELINE
+            k0 = nk0; k1 = nk1; k2 = nk2; k3 = nk3;
+#else
+            P2PT_KS((uint32_t)(c + 2), k0, k1, k2, k3);
+#endif
 
             uint4 oblk = make_uint4(0, 0, 0, 0);             // bytes this lane contributes to the output stream
             U128 gin; gin.w[0] = gin.w[1] = gin.w[2] = gin.w[3] = 0;
+#if P2PT_GCM_INTERIOR
+            const bool inner = ((int)t >= t_in_lo && (int)t <= t_in_hi);
+            const bool fast_in = inner || (c >= c_fast_lo && c <= c_fast_hi);
+            const bool full_blk = inner || (c >= 0 && (uint32_t)c < nfull);
+#else
+            const bool inner = false;
             const bool fast_in = (c >= c_fast_lo && c <= c_fast_hi);
             const bool full_blk = (c >= 0 && (uint32_t)c < nfull);
+#endif
             int ovalid_lo = 0, ovalid_hi = 0;                // valid byte range of oblk (edge slots)
 
             if (fast_in) {
@@ -510,7 +595,15 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
                     // -------- edge block: bounded byte loads, zero padding
                     const uint32_t pos = 16u * (uint32_t)c;
                     const uint32_t nb = (L - pos) < 16u ? (L - pos) : 16u;
+#if P2PT_GCM_PARK
+                    // rebuilt here (three adds on the rare path) rather than kept live across the loop
+                    const uint8_t* e_b0 = MODE == kSeal ? ibase + 13 : MODE == kPipeSeal ? ibase - 5 : ibase + 21;
+                    const uint8_t* e_lo = MODE == kPipeSeal ? ibase : e_b0;
+                    const uint8_t* e_hi = (MODE == kSeal || MODE == kPipeSeal) ? ibase + ilen : ibase + 21 + L;
+                    uint4 x = load16_bounded(e_b0 + pos, e_lo, e_hi);
+#else
                     uint4 x = load16_bounded(body0 + pos, body_lo, body_hi);
+#endif
                     if (MODE == kPipeSeal && c == 0) {       // synthesise [type][sid BE] in front of the payload
                         const uint32_t sid = __ldg(a.sids + i);
                         x.x = (uint32_t)__ldg(a.types + i) | ((sid >> 24) << 8) | (((sid >> 16) & 0xff) << 16) | (((sid >> 8) & 0xff) << 24);
@@ -523,7 +616,11 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
                     oblk = y; ovalid_hi = (int)nb;
                     if (MODE == kPipeOpen && c == 0) { fh0 = y.x; fh1 = y.y; }
                 } else if (is_j0) {
+#if P2PT_GCM_PARK
+                    sts128(slot + 320, k0, k1, k2, k3);      // E_K(J0): read back by every lane for the tag
+#else
                     ej0 = make_uint4(k0, k1, k2, k3);
+#endif
                     // AAD = epoch(2) seq(6) type ver(2) len(2); record header = type ver(2) epoch(2) seq(6) len(2)
                     uint32_t e_hi, s_w0, s_w1;               // header bytes 3..4, 5..8, 9..10 as BE numbers
                     if (MODE == kPipeSeal) {
@@ -565,12 +662,14 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
                 }
             }
 
+#if P2PT_GCM_PIPELINE
+            P2PT_KS((uint32_t)(c + 2 + G), nk0, nk1, nk2, nk3);      // next round's counter (unused after the last round)
+#endif
             // ---- GHASH: Horner in H^G; the lane's last block is multiplied after the loop
-            if (active) {
+            if (inner || active) {
                 acc.w[0] ^= gin.w[0]; acc.w[1] ^= gin.w[1]; acc.w[2] ^= gin.w[2]; acc.w[3] ^= gin.w[3];
-                last_u = u;
             }
-            if (u + G < slots) acc = gf128_mul_s(acc, gkey);
+            if (inner || u + G < slots) acc = gf128_mul_s(acc, gkey);
 
             // ---- output: the word that straddles into my block needs the previous block's last word
             uint32_t prev3 = __shfl_up_sync(gmask, oblk.w, 1, G);
@@ -585,7 +684,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
                 op[3] = __funnelshift_l(oblk.z, oblk.w, sh);
                 // my last `osh` bytes ride in the next block's first word; if there is no complete
                 // next block, store them here
-                if (osh && (uint32_t)(c + 1) >= nfull) store_bytes(ob0 + 16 * (size_t)c, oblk, 16 - (int)osh, 16);
+                if (!inner && osh && (uint32_t)(c + 1) >= nfull) store_bytes(ob0 + 16 * (size_t)c, oblk, 16 - (int)osh, 16);
             } else if (active && ovalid_hi > ovalid_lo) {
                 // edge slots (prefix block, partial last block): byte stores; the prefix's last `osh`
                 // bytes are covered by block 0's first word when block 0 is complete
@@ -597,6 +696,8 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
 
         // ------------------------------------------------------------------ finish GHASH
         {
+            // the lane's last slot is the largest u = tG + j below `slots`; a lane without any slot holds acc = 0
+            const uint32_t last_u = (uint32_t)j < slots ? ((slots - 1 - (uint32_t)j) / G) * G + (uint32_t)j : 0xffffffffu;
             const uint32_t fp = (last_u == 0xffffffffu) ? 1u : (slots - last_u);     // 1..G
             uint4 v = __ldg(reinterpret_cast<const uint4*>(sk->hpow[fp - 1]));
             U128 hf; hf.w[0] = v.x; hf.w[1] = v.y; hf.w[2] = v.z; hf.w[3] = v.w;
@@ -612,14 +713,25 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
             acc.w[3] ^= __shfl_xor_sync(gmask, acc.w[3], o, G);
         }
         uint4 tag;                                               // little-endian words, memory order
+#if P2PT_GCM_PARK
+        {
+            __syncwarp(gmask);
+            uint4 e;                                             // lane 0 of the group stored it in round 0
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+320];" : "=r"(e.x), "=r"(e.y), "=r"(e.z), "=r"(e.w) : "r"(slot) : "memory");
+            tag.x = bswap32(acc.w[3]) ^ e.x; tag.y = bswap32(acc.w[2]) ^ e.y;
+            tag.z = bswap32(acc.w[1]) ^ e.z; tag.w = bswap32(acc.w[0]) ^ e.w;
+        }
+#else
         tag.x = bswap32(acc.w[3]) ^ __shfl_sync(gmask, ej0.x, 0, G);
         tag.y = bswap32(acc.w[2]) ^ __shfl_sync(gmask, ej0.y, 0, G);
         tag.z = bswap32(acc.w[1]) ^ __shfl_sync(gmask, ej0.z, 0, G);
         tag.w = bswap32(acc.w[0]) ^ __shfl_sync(gmask, ej0.w, 0, G);
+#endif
 
         if (SEAL) {
             uint8_t* tp = ob0 + L;
             for (int b = j; b < 16; b += G) tp[b] = (uint8_t)(word_of(tag, b >> 2) >> (8 * (b & 3)));
+            for (u64 b = (u64)PREFIX + L + 16 + j; b < oslot; b += G) obase[b] = 0;
             if (j == 0 && a.status) a.status[i] = P2PT_ST_OK;
         } else {
             // constant-time style compare: OR of all byte differences, no early exit
@@ -630,9 +742,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
 #pragma unroll
             for (int o = G >> 1; o > 0; o >>= 1) diff |= __shfl_xor_sync(gmask, diff, o, G);
             const bool ok = (diff == 0);
-            if (!ok) {
-                for (u64 b = j; b < 13 + (u64)L; b += G) obase[b] = 0;
-            }
+            for (u64 b = (ok ? 13 + (u64)L : 0) + j; b < oslot; b += G) obase[b] = 0;     // a record that fails is cleared whole
             if (MODE == kOpen) {
                 if (j == 0) { a.out_len[i] = ok ? 13 + L : 0; a.status[i] = ok ? P2PT_ST_OK : P2PT_ST_AUTH_FAIL; }
             } else {

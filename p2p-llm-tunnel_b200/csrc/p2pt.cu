@@ -1,15 +1,19 @@
 // p2pt.cu -- the C ABI of libp2ptunnel_b200.so (include/p2pt.h): context, staging, launches.
 //
 // No CPU fallback lives here: every entry point either launches the sm_100a kernels or fails with
-// an error code.  Host-pointer entry points stage through a per-context device arena and a small
-// ring of streams so that host->device copies, kernels and device->host copies of successive
-// chunks overlap (PCIe Gen5 is what bounds these calls).
+// an error code.  Host-pointer entry points stage through a device arena and a small ring of streams
+// so that host->device copies, kernels and device->host copies of successive chunks overlap (PCIe
+// Gen5 is what bounds these calls).  A context owns kLanes such staging sets ("call lanes"): a call
+// takes a free lane for its duration, so several threads can be inside host-pointer calls on ONE
+// context at the same time - the reference encodes and sends from many tokio tasks over one
+// connection (/root/reference/tunnel/src/main.rs:18, serve.rs:131).
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <atomic>
+#include <condition_variable>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -37,37 +41,78 @@ struct Arena {
 
 }  // namespace
 
-struct p2pt_ctx {
-    int device = 0;
-    int sm_count = 148;
+// One staging set of a context: streams, events, a device arena that grows to the largest call it has seen,
+// and a mapped pinned buffer for small calls.  Owned by exactly one host-pointer call at a time.
+struct Lane {
     cudaStream_t streams[kStreams] = {};
     cudaEvent_t events[kStreams] = {};
     cudaEvent_t sync_events[kStreams] = {};   // cudaEventBlockingSync: the host thread sleeps instead of spinning
-    bool blocking_sync = true;                // big host-pointer calls wait on sync_events (see wait_stream)
-    bool small_demux = true;                  // batches of up to 1024 frames take the single-block demux kernel
-    bool spin_this_call = false;              // set per host-pointer call (under mu): small calls spin instead of sleeping
-    bool coop_sort = true;                    // demux sorting passes in one cooperative launch
-    std::mutex mu;                 // serialises host-pointer calls (they share the arena)
-    std::mutex err_mu;
-    std::string err;
-    SessionKey* keys_local = nullptr;
-    SessionKey* keys_remote = nullptr;
-    uint32_t n_sessions = 0;
     Arena arena;
-    std::atomic<uint64_t> launches{0};
-    uint64_t chunk_bytes = 16u << 20;  // host-pointer calls move records in chunks of about this size
-    uint32_t lut_slack = 0;        // bytes needed in front of the T-tables to reach 64 KiB alignment
-    int gcm_g = 0;                 // forced group width (env P2PT_GCM_G), 0 = heuristic
-    int occ_encode = 4, occ_gather = 4;   // resident blocks per SM of the two copy kernels (set at create)
+    bool spin_this_call = false;              // set per call: small calls spin instead of sleeping
     // Small host-pointer calls (the reference's per-frame encode / decode / seal / open call sites, batch of
     // one or a few): inputs are staged into a mapped pinned buffer the kernel reads over PCIe and results
     // come back the same way, so the call is one launch + one stream sync instead of up to eight copies.
     uint8_t* zc_host = nullptr;    // host address of the mapped buffer
     uint8_t* zc_dev = nullptr;     // device alias
     size_t zc_cap = 0;
-    uint64_t small_call_bytes = 256u << 10;  // staging footprint up to which a call takes this path (0 = never)
     struct PendingOut { void* dst; const void* src; size_t bytes; };
     std::vector<PendingOut> zc_pending;
+    bool busy = false;
+};
+
+constexpr int kLanes = 8;
+
+struct p2pt_ctx {
+    int device = 0;
+    int sm_count = 148;
+    Lane lanes[kLanes];
+    std::mutex pool_mu;            // guards Lane::busy
+    std::condition_variable pool_cv;
+    bool blocking_sync = true;                // big host-pointer calls wait on sync_events (see wait_stream)
+    bool small_demux = true;                  // batches of up to 1024 frames take the single-block demux kernel
+    bool coop_sort = true;                    // demux sorting passes in one cooperative launch
+    std::mutex err_mu;
+    std::string err;
+    SessionKey* keys_local = nullptr;
+    SessionKey* keys_remote = nullptr;
+    uint32_t n_sessions = 0;
+    std::atomic<uint64_t> launches{0};
+    uint64_t chunk_bytes = 16u << 20;  // host-pointer calls move records in chunks of about this size
+    uint32_t lut_slack = 0;        // bytes needed in front of the T-tables to reach 64 KiB alignment
+    int gcm_g = 0;                 // forced group width (env P2PT_GCM_G), 0 = heuristic
+    int occ_encode = 4, occ_gather = 4;   // resident blocks per SM of the two copy kernels (set at create)
+    size_t zc_cap = 0;             // size of every lane's mapped buffer (0: no mapped memory here, small-call path off)
+    uint64_t small_call_bytes = 256u << 10;  // staging footprint up to which a call takes the mapped-buffer path (0 = never)
+};
+
+// Takes a free lane of the context (lowest index first, so a single caller keeps reusing lane 0 and its
+// arena); blocks while all kLanes are in use.  If the call leaves early with an error, copies and kernels
+// it enqueued may still be running into the caller's buffers and the lane's arena: the guard waits for the
+// lane's streams before it gives the lane back, unless the call finished normally (dismiss()).
+struct LaneGuard {
+    p2pt_ctx* ctx;
+    Lane* lane = nullptr;
+    bool clean = false;
+    explicit LaneGuard(p2pt_ctx* c) : ctx(c) {
+        std::unique_lock<std::mutex> lk(c->pool_mu);
+        for (;;) {
+            for (int i = 0; i < kLanes; i++)
+                if (!c->lanes[i].busy) { lane = &c->lanes[i]; break; }
+            if (lane) break;
+            c->pool_cv.wait(lk);
+        }
+        lane->busy = true;
+    }
+    void dismiss() { clean = true; }
+    ~LaneGuard() {
+        if (!clean)
+            for (int i = 0; i < kStreams; i++) cudaStreamSynchronize(lane->streams[i]);
+        {
+            std::lock_guard<std::mutex> lk(ctx->pool_mu);
+            lane->busy = false;
+        }
+        ctx->pool_cv.notify_one();
+    }
 };
 
 static std::string g_create_err;
@@ -145,85 +190,86 @@ __global__ void smem_base_probe_kernel(uint32_t* out) {
 // Wait for one of the ctx's streams.  cudaStreamSynchronize spins on a CPU core; with several worker
 // threads per GPU and several GPUs per host that starves the threads that feed the copy engines, so by
 // default the wait is a blocking-sync event (the thread sleeps until the interrupt).
-static cudaError_t wait_stream(p2pt_ctx* ctx, cudaStream_t st) {
+static cudaError_t wait_stream(p2pt_ctx* ctx, Lane* L, cudaStream_t st) {
     // a sleeping wait costs a wake-up of 50-100 us; a call that stages a few MB has up to seven of them
-    if (!ctx->blocking_sync || ctx->spin_this_call) return cudaStreamSynchronize(st);
+    if (!ctx->blocking_sync || L->spin_this_call) return cudaStreamSynchronize(st);
     int idx = 0;
-    for (int i = 0; i < kStreams; i++) if (ctx->streams[i] == st) idx = i;
-    cudaError_t e = cudaEventRecord(ctx->sync_events[idx], st);
+    for (int i = 0; i < kStreams; i++) if (L->streams[i] == st) idx = i;
+    cudaError_t e = cudaEventRecord(L->sync_events[idx], st);
     if (e != cudaSuccess) return e;
-    return cudaEventSynchronize(ctx->sync_events[idx]);
+    return cudaEventSynchronize(L->sync_events[idx]);
 }
 
 // host-pointer calls that stage less than this wait by spinning: they finish in well under a millisecond
 constexpr size_t kSpinWaitBytes = 8u << 20;
 
 // ---- arena -----------------------------------------------------------------------------------------
-static int32_t arena_reserve(p2pt_ctx* ctx, size_t bytes) {
-    ctx->arena.used = 0;
-    ctx->spin_this_call = bytes < kSpinWaitBytes;
-    if (bytes <= ctx->arena.cap) return P2PT_OK;
-    if (ctx->arena.base) cudaFree(ctx->arena.base);
-    ctx->arena.base = nullptr;
-    ctx->arena.cap = 0;
+static int32_t arena_reserve(p2pt_ctx* ctx, Lane* L, size_t bytes) {
+    L->arena.used = 0;
+    L->spin_this_call = bytes < kSpinWaitBytes;
+    if (bytes <= L->arena.cap) return P2PT_OK;
+    if (L->arena.base) cudaFree(L->arena.base);
+    L->arena.base = nullptr;
+    L->arena.cap = 0;
     size_t want = bytes + bytes / 8 + (1u << 20);
-    CUDA_TRY(ctx, cudaMalloc(&ctx->arena.base, want));
-    ctx->arena.cap = want;
+    CUDA_TRY(ctx, cudaMalloc(&L->arena.base, want));
+    L->arena.cap = want;
     return P2PT_OK;
 }
 template <class T>
-static T* arena_take(p2pt_ctx* ctx, size_t count) {
+static T* arena_take(Lane* L, size_t count) {
     size_t bytes = (count * sizeof(T) + 255) & ~(size_t)255;
-    T* p = reinterpret_cast<T*>(ctx->arena.base + ctx->arena.used);
-    ctx->arena.used += bytes;
+    T* p = reinterpret_cast<T*>(L->arena.base + L->arena.used);
+    L->arena.used += bytes;
     return p;
 }
 static size_t pad256(size_t b) { return (b + 255) & ~(size_t)255; }
 
 // Carves device-visible pieces out of the ctx's mapped pinned buffer and maps them back to host addresses
-// (the small-batch paths of the demux calls; caller holds ctx->mu and has checked the footprint).
+// (the small-batch paths of the demux calls; the caller owns the lane and has checked the footprint).
 struct ZcCarver {
-    p2pt_ctx* ctx;
+    Lane* L;
     size_t used = 0;
-    uint8_t* take(size_t bytes) { uint8_t* p = ctx->zc_dev + used; used += pad256(bytes); return p; }
-    uint8_t* host_of(const void* d) const { return ctx->zc_host + ((const uint8_t*)d - ctx->zc_dev); }
+    uint8_t* take(size_t bytes) { uint8_t* p = L->zc_dev + used; used += pad256(bytes); return p; }
+    uint8_t* host_of(const void* d) const { return L->zc_host + ((const uint8_t*)d - L->zc_dev); }
 };
 
 // Staging for the inputs and outputs of one host-pointer call: the device arena + async copies, or,
 // when everything fits small_call_bytes, the mapped pinned buffer + plain memcpy (see p2pt_ctx).
-// Caller holds ctx->mu.
+// The caller owns the lane.
 struct IoStage {
     p2pt_ctx* ctx;
+    Lane* L;
     bool zc = false;
     size_t zc_used = 0;
     int32_t reserve(size_t bytes) {
-        zc = ctx->zc_host && ctx->small_call_bytes && bytes <= ctx->small_call_bytes && bytes <= ctx->zc_cap;
-        ctx->zc_pending.clear();
-        return zc ? P2PT_OK : arena_reserve(ctx, bytes);
+        zc = L->zc_host && ctx->small_call_bytes && bytes <= ctx->small_call_bytes && bytes <= L->zc_cap;
+        L->zc_pending.clear();
+        return zc ? P2PT_OK : arena_reserve(ctx, L, bytes);
     }
     template <class T> T* take(size_t count) {
-        if (!zc) return arena_take<T>(ctx, count);
-        T* p = reinterpret_cast<T*>(ctx->zc_dev + zc_used);
+        if (!zc) return arena_take<T>(L, count);
+        T* p = reinterpret_cast<T*>(L->zc_dev + zc_used);
         zc_used += pad256(count * sizeof(T));
         return p;
     }
     cudaError_t in(void* d, const void* h, size_t bytes, cudaStream_t st) {
         if (!zc) return cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, st);
-        memcpy(ctx->zc_host + ((uint8_t*)d - ctx->zc_dev), h, bytes);
+        memcpy(L->zc_host + ((uint8_t*)d - L->zc_dev), h, bytes);
         return cudaSuccess;
     }
     cudaError_t out(void* h, const void* d, size_t bytes, cudaStream_t st) {
         if (!zc) return cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, st);
-        ctx->zc_pending.push_back({h, ctx->zc_host + ((const uint8_t*)d - ctx->zc_dev), bytes});
+        L->zc_pending.push_back({h, L->zc_host + ((const uint8_t*)d - L->zc_dev), bytes});
         return cudaSuccess;
     }
     // wait for the call's work on st and deliver the staged results
     cudaError_t finish(cudaStream_t st) {
-        if (!zc) return wait_stream(ctx, st);
+        if (!zc) return wait_stream(ctx, L, st);
         cudaError_t e = cudaStreamSynchronize(st);        // a spin wait: these calls last microseconds
         if (e != cudaSuccess) return e;
-        for (const auto& o : ctx->zc_pending) memcpy(o.dst, o.src, o.bytes);
-        ctx->zc_pending.clear();
+        for (const auto& o : L->zc_pending) memcpy(o.dst, o.src, o.bytes);
+        L->zc_pending.clear();
         return cudaSuccess;
     }
 };
@@ -254,16 +300,9 @@ static int32_t launch_gcm(p2pt_ctx* ctx, const GcmArgs& a_in, int G, cudaStream_
     uint64_t grid = (a.n + groups_per_cta - 1) / groups_per_cta;
     if (grid > (uint64_t)ctx->sm_count) grid = ctx->sm_count;      // persistent: one CTA per SM
 #define P2PT_LAUNCH_G(GG)                                                                              \
-    case GG: {                                                                                         \
-        static std::atomic<int> configured[16];                                                        \
-        if (!configured[ctx->device & 15].load()) {                                                    \
-            CUDA_TRY(ctx, cudaFuncSetAttribute(gcm_record_kernel<GG, MODE>,                            \
-                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-            configured[ctx->device & 15].store(1);                                                     \
-        }                                                                                              \
+    case GG:                                                                                           \
         gcm_record_kernel<GG, MODE><<<(unsigned)grid, kGcmThreads, smem, st>>>(a);                     \
-        break;                                                                                         \
-    }
+        break;
     switch (G) {
         P2PT_LAUNCH_G(4)
         P2PT_LAUNCH_G(8)
@@ -326,69 +365,98 @@ const char* p2pt_last_error(p2pt_ctx* ctx) {
     return copy2.c_str();
 }
 
-int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
-    if (!out) return set_err(nullptr, P2PT_ERR_ARG, "out is null");
-    *out = nullptr;
-    int ndev = 0;
-    cudaError_t e = cudaGetDeviceCount(&ndev);
-    if (e != cudaSuccess || ndev == 0)
-        return set_err(nullptr, P2PT_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e) +
-                                                   " (libp2ptunnel_b200 has no CPU fallback)");
-    if (device < 0 || device >= ndev) return set_err(nullptr, P2PT_ERR_ARG, "device index out of range");
-    DeviceGuard dg(device);
-    cudaDeviceProp prop;
-    CUDA_TRY(nullptr, cudaGetDeviceProperties(&prop, device));
-    if (prop.major < 10)
-        return set_err(nullptr, P2PT_ERR_CUDA, "libp2ptunnel_b200 is built for sm_100a only");
-    p2pt_ctx* ctx = new p2pt_ctx();
-    ctx->device = device;
-    ctx->sm_count = prop.multiProcessorCount;
-    for (int i = 0; i < kStreams; i++) {
-        if (cudaStreamCreateWithFlags(&ctx->streams[i], cudaStreamNonBlocking) != cudaSuccess ||
-            cudaEventCreateWithFlags(&ctx->events[i], cudaEventDisableTiming) != cudaSuccess ||
-            cudaEventCreateWithFlags(&ctx->sync_events[i], cudaEventDisableTiming | cudaEventBlockingSync) != cudaSuccess) {
-            delete ctx;
-            return set_err(nullptr, P2PT_ERR_CUDA, "stream/event creation failed");
-        }
-    }
-    uint32_t te0[256];
-    build_te0(te0);
-    CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_te0, te0, sizeof te0));
-    {
-        static uint32_t ctab[4][256], cxp[1280];
+}  // extern "C" (reopened below)
+
+// Device-wide tables (g_te0, the CRC32c tables) are uploaded once per device, not once per context: kernels of
+// other contexts on the device may be reading them while a new context is being created.
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_tables_mu;
+bool g_tables_ready[kMaxDevices] = {};
+}  // namespace
+
+static int32_t upload_device_tables(int device) {
+    std::lock_guard<std::mutex> lk(g_tables_mu);
+    if (g_tables_ready[device]) return P2PT_OK;
+    static uint32_t te0[256], ctab[4][256], cxp[1280], cinit[kCrcSeg * 32 + 1];
+    static bool built = false;
+    if (!built) {
+        build_te0(te0);
         build_crc_tables(ctab, cxp);
-        CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_tab, ctab, sizeof ctab));
-        CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_xpow, cxp, sizeof cxp));
         // contribution of the 0xFFFFFFFF init value to a packet of w words: the register 0xFFFFFFFF run
         // through 4 w zero bytes (CRC is linear in its initial register)
-        static uint32_t cinit[kCrcSeg * 32 + 1];
         uint32_t reg = 0xFFFFFFFFu;
         for (int w = 0; w <= kCrcSeg * 32; w++) {
             cinit[w] = reg;
             for (int b = 0; b < 4; b++) reg = (reg >> 8) ^ ctab[0][reg & 0xff];
         }
-        CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_init, cinit, sizeof cinit));
+        built = true;
     }
+    CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_te0, te0, sizeof te0));
+    CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_tab, ctab, sizeof ctab));
+    CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_xpow, cxp, sizeof cxp));
+    CUDA_TRY(nullptr, cudaMemcpyToSymbol(g_crc_init, cinit, sizeof cinit));
+    CUDA_TRY(nullptr, cudaDeviceSynchronize());
+    g_tables_ready[device] = true;
+    return P2PT_OK;
+}
+
+// the record and SCTP kernels need more dynamic shared memory than the default limit; set once per context
+// (the attribute is per device and function, setting it again is harmless)
+template <int MODE>
+static cudaError_t configure_gcm_mode(uint32_t slack) {
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(gcm_record_kernel<4, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gcm_smem_bytes(4, slack))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(gcm_record_kernel<8, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gcm_smem_bytes(8, slack))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(gcm_record_kernel<16, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gcm_smem_bytes(16, slack))) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(gcm_record_kernel<32, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gcm_smem_bytes(32, slack));
+}
+
+static int32_t ctx_init(p2pt_ctx* ctx, int device, const cudaDeviceProp& prop) {
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    for (int l = 0; l < kLanes; l++) {
+        Lane& L = ctx->lanes[l];
+        for (int i = 0; i < kStreams; i++) {
+            CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&L.streams[i], cudaStreamNonBlocking));
+            CUDA_TRY(nullptr, cudaEventCreateWithFlags(&L.events[i], cudaEventDisableTiming));
+            CUDA_TRY(nullptr, cudaEventCreateWithFlags(&L.sync_events[i], cudaEventDisableTiming | cudaEventBlockingSync));
+        }
+    }
+    if (int32_t r = upload_device_tables(device)) return r;
     // where does dynamic shared memory start?  The T-tables must sit on a 64 KiB boundary.
     uint32_t* d_probe = nullptr;
     CUDA_TRY(nullptr, cudaMalloc(&d_probe, 4));
-    smem_base_probe_kernel<<<1, 32, 16, ctx->streams[0]>>>(d_probe);
+    cudaStream_t s0 = ctx->lanes[0].streams[0];
+    smem_base_probe_kernel<<<1, 32, 16, s0>>>(d_probe);
     uint32_t sb = 0;
-    CUDA_TRY(nullptr, cudaMemcpyAsync(&sb, d_probe, 4, cudaMemcpyDeviceToHost, ctx->streams[0]));
-    CUDA_TRY(nullptr, cudaStreamSynchronize(ctx->streams[0]));
+    cudaError_t e = cudaMemcpyAsync(&sb, d_probe, 4, cudaMemcpyDeviceToHost, s0);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s0);
     cudaFree(d_probe);
+    CUDA_TRY(nullptr, e);
     ctx->lut_slack = (0x10000u - (sb & 0xffffu)) & 0xffffu;
+    CUDA_TRY(nullptr, configure_gcm_mode<kSeal>(ctx->lut_slack));
+    CUDA_TRY(nullptr, configure_gcm_mode<kOpen>(ctx->lut_slack));
+    CUDA_TRY(nullptr, configure_gcm_mode<kPipeSeal>(ctx->lut_slack));
+    CUDA_TRY(nullptr, configure_gcm_mode<kPipeOpen>(ctx->lut_slack));
+    CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_packetize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_smem_bytes(ctx->lut_slack)));
+    CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_unpack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_smem_bytes(ctx->lut_slack)));
     {
-        void* h = nullptr; void* d = nullptr;
         const size_t cap = 1u << 20;
-        if (cudaHostAlloc(&h, cap, cudaHostAllocMapped) == cudaSuccess) {
-            if (cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess) {
-                ctx->zc_host = (uint8_t*)h; ctx->zc_dev = (uint8_t*)d; ctx->zc_cap = cap;
-            } else {
-                cudaFreeHost(h);
-            }
+        bool all = true;
+        for (int l = 0; l < kLanes && all; l++) {
+            void* h = nullptr; void* d = nullptr;
+            if (cudaHostAlloc(&h, cap, cudaHostAllocMapped) != cudaSuccess) { all = false; break; }
+            if (cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) { cudaFreeHost(h); all = false; break; }
+            ctx->lanes[l].zc_host = (uint8_t*)h; ctx->lanes[l].zc_dev = (uint8_t*)d; ctx->lanes[l].zc_cap = cap;
         }
         (void)cudaGetLastError();      // without mapped memory the small-call path is simply off
+        if (all) ctx->zc_cap = cap;
+        else
+            for (int l = 0; l < kLanes; l++) {
+                if (ctx->lanes[l].zc_host) cudaFreeHost(ctx->lanes[l].zc_host);
+                ctx->lanes[l].zc_host = ctx->lanes[l].zc_dev = nullptr; ctx->lanes[l].zc_cap = 0;
+            }
     }
     CUDA_TRY(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_encode, frame_encode_kernel, 256, 0));
     CUDA_TRY(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_gather, demux_gather_kernel, 256, 0));
@@ -397,6 +465,32 @@ int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
     if (const char* g = getenv("P2PT_GCM_G")) {
         int v = atoi(g);
         if (v == 4 || v == 8 || v == 16 || v == 32) ctx->gcm_g = v;
+    }
+    return P2PT_OK;
+}
+
+extern "C" {
+
+int32_t p2pt_ctx_create(int device, p2pt_ctx** out) {
+    if (!out) return set_err(nullptr, P2PT_ERR_ARG, "out is null");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return set_err(nullptr, P2PT_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                                                   " (libp2ptunnel_b200 has no CPU fallback)");
+    if (device < 0 || device >= ndev || device >= kMaxDevices) return set_err(nullptr, P2PT_ERR_ARG, "device index out of range");
+    DeviceGuard dg(device);
+    cudaDeviceProp prop;
+    CUDA_TRY(nullptr, cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return set_err(nullptr, P2PT_ERR_CUDA, "libp2ptunnel_b200 is built for sm_100a only");
+    p2pt_ctx* ctx = new p2pt_ctx();
+    const int32_t r = ctx_init(ctx, device, prop);
+    if (r != P2PT_OK) {                // whatever was created so far goes away with the context
+        ctx->device = device;
+        p2pt_ctx_destroy(ctx);
+        return r;
     }
     *out = ctx;
     return P2PT_OK;
@@ -407,15 +501,19 @@ int32_t p2pt_ctx_destroy(p2pt_ctx* ctx) {
     {
         DeviceGuard dg(ctx->device);
         cudaDeviceSynchronize();
-        for (int i = 0; i < kStreams; i++) {
-            if (ctx->streams[i]) cudaStreamDestroy(ctx->streams[i]);
-            if (ctx->events[i]) cudaEventDestroy(ctx->events[i]);
-            if (ctx->sync_events[i]) cudaEventDestroy(ctx->sync_events[i]);
+        for (int l = 0; l < kLanes; l++) {
+            Lane& L = ctx->lanes[l];
+            for (int i = 0; i < kStreams; i++) {
+                if (L.streams[i]) cudaStreamDestroy(L.streams[i]);
+                if (L.events[i]) cudaEventDestroy(L.events[i]);
+                if (L.sync_events[i]) cudaEventDestroy(L.sync_events[i]);
+            }
+            if (L.arena.base) cudaFree(L.arena.base);
+            if (L.zc_host) cudaFreeHost(L.zc_host);
         }
         if (ctx->keys_local) cudaFree(ctx->keys_local);
         if (ctx->keys_remote) cudaFree(ctx->keys_remote);
-        if (ctx->arena.base) cudaFree(ctx->arena.base);
-        if (ctx->zc_host) cudaFreeHost(ctx->zc_host);
+        (void)cudaGetLastError();
     }
     delete ctx;
     return P2PT_OK;
@@ -462,7 +560,6 @@ int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
     }
     if (strcmp(name, "small_call_bytes") == 0) {
         if (value < 0 || (uint64_t)value > ctx->zc_cap) return set_err(ctx, P2PT_ERR_ARG, "small_call_bytes must be 0 .. 1048576");
-        std::lock_guard<std::mutex> lk(ctx->mu);
         ctx->small_call_bytes = (uint64_t)value;
         return P2PT_OK;
     }
@@ -480,9 +577,10 @@ int32_t p2pt_sessions_load(p2pt_ctx* ctx, uint32_t n, const uint8_t* local_keys1
     if (!ctx) return P2PT_ERR_ARG;
     if (!n || !local_keys16 || !local_ivs4 || !remote_keys16 || !remote_ivs4)
         return set_err(ctx, P2PT_ERR_ARG, "sessions_load: null key material or n == 0");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
-    cudaStream_t st = ctx->streams[0];
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
     if (ctx->keys_local) { cudaFree(ctx->keys_local); ctx->keys_local = nullptr; }
     if (ctx->keys_remote) { cudaFree(ctx->keys_remote); ctx->keys_remote = nullptr; }
     ctx->n_sessions = 0;
@@ -497,11 +595,12 @@ int32_t p2pt_sessions_load(p2pt_ctx* ctx, uint32_t n, const uint8_t* local_keys1
         session_expand_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, dk, di, dir ? ctx->keys_remote : ctx->keys_local);
         count_launch(ctx);
         CUDA_TRY(ctx, cudaGetLastError());
-        CUDA_TRY(ctx, wait_stream(ctx, st));
+        CUDA_TRY(ctx, wait_stream(ctx, L, st));
     }
     cudaFree(dk);
     cudaFree(di);
     ctx->n_sessions = n;
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -582,32 +681,34 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         CUDA_TRY(ctx, cudaGetLastError());
         return P2PT_OK;
     }
+    const bool packed = (session == nullptr);          // key and frame index in one 64-bit word (frame_kernels.cuh)
     demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc, s.blen);
     bool coop_done = false;
     if (ctx->coop_sort) {
         // all nine passes in one cooperative launch (grid-wide syncs between the phases)
         u64 n_arg = n; const uint32_t* desc_arg = s.blen; uint32_t* hist_arg = s.hist; const u64* misc_arg = s.misc;
         uint32_t* rt_arg = s.row_total;
-        void* args[] = {&n_arg, &bufs, &desc_arg, &hist_arg, &misc_arg, &rt_arg};
+        bool packed_arg = packed;
+        void* args[] = {&n_arg, &bufs, &desc_arg, &hist_arg, &misc_arg, &rt_arg, &packed_arg};
         cudaError_t ce = cudaLaunchCooperativeKernel((void*)demux_sort_coop_kernel, dim3(kSortBlocks), dim3(kSortThreads), args, 0, st);
         if (ce == cudaSuccess) { coop_done = true; count_launch(ctx); }
         else { (void)cudaGetLastError(); ctx->coop_sort = false; }      // not supported here: fall back for good
     }
     if (!coop_done) {
         for (int pass = 0; pass < kSortPasses; pass++) {
-            demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc);
+            demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc, packed);
             demux_rowscan_kernel<<<kRadix / kRowScanWarps, 32 * kRowScanWarps, 0, st>>>(s.hist, pass, s.misc, s.row_total);
-            demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc, s.row_total);
+            demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc, s.row_total, packed);
         }
         count_launch(ctx, 3 * kSortPasses);
     }
     const u64 nblk = demux_emit_blocks(n);
     const int dst_mode = !gathered ? 0 : gathered_cap <= 0xffffffffull ? 1 : 2;
-    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, first_only);
+    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, first_only, packed);
     demux_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, s.blk_heads, s.blk_bytes);
     demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, nblk,
                                                               max_streams, uniq_sid, uniq_session, (u64*)csr, perm, k_out,
-                                                              (u64*)gathered_off, dst_mode, first_only);
+                                                              (u64*)gathered_off, dst_mode, first_only, packed);
     count_launch(ctx, 1 + 3);
     if (gathered) {
         const int rounds = copy_tile_rounds(ctx, n, ctx->occ_gather);
@@ -661,11 +762,6 @@ int32_t p2pt_sctp_packetize_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_
     a.sid = sid; a.ssn = ssn; a.ppid = ppid; a.tsn0 = tsn0; a.epoch = epoch; a.seq48_first = (const u64*)seq48_first;
     a.out = out; a.out_msg_off = (const u64*)out_msg_off; a.pkt_first = (const u64*)pkt_first; a.pkt_off = (u64*)pkt_off;
     const uint32_t smem = sctp_smem_bytes(ctx->lut_slack);
-    static std::atomic<int> configured[16];
-    if (!configured[ctx->device & 15].load()) {
-        CUDA_TRY(ctx, cudaFuncSetAttribute(sctp_packetize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured[ctx->device & 15].store(1);
-    }
     sctp_packetize_kernel<<<grid_for(ctx, n, kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
@@ -681,11 +777,6 @@ int32_t p2pt_sctp_unpack_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const uint
     SctpUnpackArgs a;
     a.n = n_pkts; a.in = in; a.in_off = (const u64*)in_off; a.headroom = headroom; a.info = info; a.desc = desc;
     const uint32_t smem = sctp_smem_bytes(ctx->lut_slack);
-    static std::atomic<int> configured[16];
-    if (!configured[ctx->device & 15].load()) {
-        CUDA_TRY(ctx, cudaFuncSetAttribute(sctp_unpack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured[ctx->device & 15].store(1);
-    }
     sctp_unpack_kernel<<<grid_for(ctx, n_pkts, kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
@@ -899,12 +990,13 @@ int32_t p2pt_frame_encode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* types,
     for (uint64_t i = 0; i < n; i++)
         if (out_off[i + 1] - out_off[i] < 5 + (pay_off[i + 1] - pay_off[i]))
             return set_err(ctx, P2PT_ERR_CAPACITY, "frame_encode: output slot smaller than 5 + payload");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
-    cudaStream_t st = ctx->streams[0];
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
     const size_t pbytes = pay_off[n] - pay_off[0], obytes = out_off[n] - out_off[0];
     if (pbytes && !payload) return set_err(ctx, P2PT_ERR_ARG, "frame_encode: null payload");
-    IoStage io{ctx};
+    IoStage io{ctx, L};
     if (int32_t r = io.reserve(pad256(n) + pad256(4 * n) + 2 * pad256(8 * (n + 1)) + pad256(pbytes + 1) + pad256(obytes + 1) + 4096)) return r;
     uint8_t* d_types = io.take<uint8_t>(n);
     uint32_t* d_sids = io.take<uint32_t>(n);
@@ -931,6 +1023,7 @@ int32_t p2pt_frame_encode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* types,
         }
     }
     CUDA_TRY(ctx, io.finish(st));
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -939,12 +1032,13 @@ int32_t p2pt_frame_decode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, co
     if (n == 0) return P2PT_OK;
     if (!in_off || !desc) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: null argument");
     if (!offsets_monotonic(in_off, n)) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: offsets must be non-decreasing");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
-    cudaStream_t st = ctx->streams[0];
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
     const size_t ibytes = in_off[n] - in_off[0];
     if (ibytes && !in) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: null input");
-    IoStage io{ctx};
+    IoStage io{ctx, L};
     if (int32_t r = io.reserve(pad256(8 * (n + 1)) + pad256(ibytes + 1) + pad256(24 * n) + 4096)) return r;
     uint64_t* d_io = io.take<uint64_t>(n + 1);
     uint8_t* d_in = io.take<uint8_t>(ibytes + 1);
@@ -954,6 +1048,7 @@ int32_t p2pt_frame_decode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, co
     if (int32_t r = p2pt_frame_decode_batch_device(ctx, n, d_in - in_off[0], d_io, d_desc, st)) return r;
     CUDA_TRY(ctx, io.out(desc, d_desc, 24 * n, st));
     CUDA_TRY(ctx, io.finish(st));
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -967,22 +1062,23 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
     if (n == 0) { *k_out = 0; csr[0] = 0; if (gathered_off) gathered_off[0] = 0; return P2PT_OK; }
     if (!desc) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null desc");
     if (gathered && (!in || !gathered_off)) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: gather needs in and gathered_off");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
-    cudaStream_t st = ctx->streams[0];
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
     const uint64_t sbytes = demux_scratch_bytes(n);
     const size_t gcap = gathered ? (size_t)gathered_cap : 0;
     const size_t ib = gathered ? (size_t)in_bytes : 0;
-    if (ctx->small_demux && ctx->zc_host && ctx->small_call_bytes && n <= (uint64_t)kSmallDemux) {
+    if (ctx->small_demux && L->zc_host && ctx->small_call_bytes && n <= (uint64_t)kSmallDemux) {
         // small batch: descriptors, frames and every result live in the mapped pinned buffer; two launches, one wait
         const size_t ms1 = (size_t)(max_streams < n ? max_streams : n) + 1;
         const size_t g2 = gcap < ib ? gcap : ib;                  // the bodies cannot be longer than the input
         const size_t foot = pad256(24 * n) + pad256(4 * n) + pad256(ib + 1) + 2 * pad256(4 * ms1) + 2 * pad256(8 * ms1) +
                             pad256(4 * n) + pad256(g2 + 1) + 256;
-        if (foot <= ctx->small_call_bytes && foot <= ctx->zc_cap) {
-            if (int32_t r = arena_reserve(ctx, pad256(sbytes) + 4096)) return r;
-            uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
-            ZcCarver zcv{ctx};
+        if (foot <= ctx->small_call_bytes && foot <= L->zc_cap) {
+            if (int32_t r = arena_reserve(ctx, L, pad256(sbytes) + 4096)) return r;
+            uint8_t* d_scratch = arena_take<uint8_t>(L, sbytes);
+            ZcCarver zcv{L};
             auto zc = [&](size_t bytes) { return zcv.take(bytes); };
             auto host_of = [&](const void* d) { return zcv.host_of(d); };
             p2pt_desc* z_desc = (p2pt_desc*)zc(24 * n);
@@ -1018,23 +1114,24 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
                     if (gathered_off[k]) memcpy(gathered, host_of(z_g), gathered_off[k]);
                 }
             }
+            lg.dismiss();
             return P2PT_OK;
         }
     }
-    if (int32_t r = arena_reserve(ctx, pad256(24 * n) + pad256(4 * n) + pad256(ib) + 2 * pad256(4 * ((size_t)max_streams + 1)) +
+    if (int32_t r = arena_reserve(ctx, L, pad256(24 * n) + pad256(4 * n) + pad256(ib) + 2 * pad256(4 * ((size_t)max_streams + 1)) +
                                            2 * pad256(8 * ((size_t)max_streams + 1)) + pad256(4 * n) + 256 +
                                            pad256(gcap) + pad256(sbytes) + 8192)) return r;
-    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
-    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
-    uint8_t* d_in = arena_take<uint8_t>(ctx, ib + 1);
-    uint32_t* d_uniq = arena_take<uint32_t>(ctx, max_streams + 1);
-    uint32_t* d_usess = arena_take<uint32_t>(ctx, max_streams + 1);
-    uint64_t* d_csr = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
-    uint64_t* d_goff = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
-    uint32_t* d_perm = arena_take<uint32_t>(ctx, n);
-    uint32_t* d_k = arena_take<uint32_t>(ctx, 1);
-    uint8_t* d_g = arena_take<uint8_t>(ctx, gcap + 1);
-    uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(L, n);
+    uint32_t* d_sess = arena_take<uint32_t>(L, n);
+    uint8_t* d_in = arena_take<uint8_t>(L, ib + 1);
+    uint32_t* d_uniq = arena_take<uint32_t>(L, max_streams + 1);
+    uint32_t* d_usess = arena_take<uint32_t>(L, max_streams + 1);
+    uint64_t* d_csr = arena_take<uint64_t>(L, (size_t)max_streams + 1);
+    uint64_t* d_goff = arena_take<uint64_t>(L, (size_t)max_streams + 1);
+    uint32_t* d_perm = arena_take<uint32_t>(L, n);
+    uint32_t* d_k = arena_take<uint32_t>(L, 1);
+    uint8_t* d_g = arena_take<uint8_t>(L, gcap + 1);
+    uint8_t* d_scratch = arena_take<uint8_t>(L, sbytes);
     CUDA_TRY(ctx, cudaMemcpyAsync(d_desc, desc, 24 * n, cudaMemcpyHostToDevice, st));
     if (session) CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, st));
     if (ib) CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in, ib, cudaMemcpyHostToDevice, st));
@@ -1044,24 +1141,25 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
                                                   gathered_off ? d_goff : nullptr, d_scratch, sbytes, st)) return r;
     uint32_t k = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&k, d_k, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
     *k_out = k;
     if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: more streams than max_streams");
     CUDA_TRY(ctx, cudaMemcpyAsync(uniq_sid, d_uniq, 4 * (size_t)k, cudaMemcpyDeviceToHost, st));
     if (uniq_session) CUDA_TRY(ctx, cudaMemcpyAsync(uniq_session, d_usess, 4 * (size_t)k, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(csr, d_csr, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
     const uint64_t m = csr[k];
     if (m) CUDA_TRY(ctx, cudaMemcpyAsync(perm, d_perm, 4 * m, cudaMemcpyDeviceToHost, st));
     if (gathered_off) {
         CUDA_TRY(ctx, cudaMemcpyAsync(gathered_off, d_goff, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(ctx, wait_stream(ctx, st));
+        CUDA_TRY(ctx, wait_stream(ctx, L, st));
         if (gathered) {
             if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: gathered_cap too small");
             if (gathered_off[k]) CUDA_TRY(ctx, cudaMemcpyAsync(gathered, d_g, gathered_off[k], cudaMemcpyDeviceToHost, st));
         }
     }
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -1093,10 +1191,11 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
         if (ol < need) return set_err(ctx, P2PT_ERR_CAPACITY, std::string(what) + ": output slot too small");
     }
     if (int32_t r = check_sessions(ctx)) return r;
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
     const size_t ibytes = c.in_off[n] - c.in_off[0], obytes = c.out_off[n] - c.out_off[0];
-    IoStage io{ctx};
+    IoStage io{ctx, L};
     if (int32_t r = io.reserve(pad256(4 * n) + pad256(8 * n) + 2 * pad256(8 * (n + 1)) + pad256(ibytes + 1) +
                                            pad256(obytes + 1) + pad256(n) + pad256(4 * n) + pad256(2 * n) + pad256(8 * n) +
                                            pad256(n) + pad256(4 * n) + pad256(24 * n) + 16384)) return r;
@@ -1114,7 +1213,7 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
     uint32_t* d_sids = io.take<uint32_t>(n);
     p2pt_desc* d_desc = io.take<p2pt_desc>(n);
 
-    cudaStream_t s0 = ctx->streams[0];
+    cudaStream_t s0 = L->streams[0];
     CUDA_TRY(ctx, io.in(d_io, c.in_off, 8 * (n + 1), s0));
     CUDA_TRY(ctx, io.in(d_oo, c.out_off, 8 * (n + 1), s0));
     CUDA_TRY(ctx, io.in(d_sess, c.session, 4 * n, s0));
@@ -1125,7 +1224,7 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
         CUDA_TRY(ctx, io.in(d_types, c.types, n, s0));
         CUDA_TRY(ctx, io.in(d_sids, c.sids, 4 * n, s0));
     }
-    if (!io.zc) CUDA_TRY(ctx, cudaEventRecord(ctx->events[0], s0));     // the other streams wait for the metadata
+    if (!io.zc) CUDA_TRY(ctx, cudaEventRecord(L->events[0], s0));     // the other streams wait for the metadata
 
     const int G = pick_group(ctx, n, ibytes);
     // chunk so that each chunk moves ~16 MiB of input
@@ -1138,8 +1237,8 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
     int si = 0;
     for (uint64_t r0 = 0; r0 < n; r0 += chunk, si = (si + 1) % kStreams) {
         const uint64_t r1 = r0 + chunk < n ? r0 + chunk : n, m = r1 - r0;
-        cudaStream_t st = ctx->streams[si];
-        if (!io.zc && (si != 0 || r0 == 0)) CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[0], 0));
+        cudaStream_t st = L->streams[si];
+        if (!io.zc && (si != 0 || r0 == 0)) CUDA_TRY(ctx, cudaStreamWaitEvent(st, L->events[0], 0));
         const size_t ib0 = c.in_off[r0] - c.in_off[0], ib1 = c.in_off[r1] - c.in_off[0];
         const size_t ob0 = c.out_off[r0] - c.out_off[0], ob1 = c.out_off[r1] - c.out_off[0];
         if (ib1 > ib0) CUDA_TRY(ctx, io.in(d_in + ib0, c.in + c.in_off[r0], ib1 - ib0, st));
@@ -1168,9 +1267,10 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
     if (io.zc) {
         CUDA_TRY(ctx, io.finish(s0));                                    // a small call is one chunk on stream 0
     } else {
-        for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, wait_stream(ctx, ctx->streams[i]));
+        for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, wait_stream(ctx, L, L->streams[i]));
     }
     // pipe-open descriptors are relative to the caller's `out`, which is how the kernel wrote them
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -1256,21 +1356,22 @@ int32_t p2pt_sctp_packetize_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg,
     if (bytes > out_cap || pk + 1 > pkt_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_packetize: out_cap or pkt_cap too small");
     const size_t mbytes = msg_off[n] - msg_off[0];
     if (mbytes && !msg) return set_err(ctx, P2PT_ERR_ARG, "sctp_packetize: null msg");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
-    cudaStream_t st = ctx->streams[0];
-    if (int32_t r = arena_reserve(ctx, pad256(mbytes) + 3 * pad256(8 * (n + 1)) + 4 * pad256(4 * n) + 4 * pad256(2 * n) +
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
+    if (int32_t r = arena_reserve(ctx, L, pad256(mbytes) + 3 * pad256(8 * (n + 1)) + 4 * pad256(4 * n) + 4 * pad256(2 * n) +
                                            pad256(8 * n) + pad256(bytes) + pad256(8 * (pk + 1)) + 16384)) return r;
-    uint8_t* d_msg = arena_take<uint8_t>(ctx, mbytes + 1);
-    uint64_t* d_moff = arena_take<uint64_t>(ctx, n + 1);
-    uint64_t* d_first = arena_take<uint64_t>(ctx, n + 1);
-    uint64_t* d_omoff = arena_take<uint64_t>(ctx, n + 1);
-    uint16_t* d_sp = arena_take<uint16_t>(ctx, n); uint16_t* d_dp = arena_take<uint16_t>(ctx, n);
-    uint16_t* d_sid = arena_take<uint16_t>(ctx, n); uint16_t* d_ssn = arena_take<uint16_t>(ctx, n);
-    uint32_t* d_vt = arena_take<uint32_t>(ctx, n); uint32_t* d_pp = arena_take<uint32_t>(ctx, n); uint32_t* d_tsn = arena_take<uint32_t>(ctx, n);
-    uint16_t* d_ep = arena_take<uint16_t>(ctx, n); uint64_t* d_sq = arena_take<uint64_t>(ctx, n);
-    uint8_t* d_out = arena_take<uint8_t>(ctx, bytes + 1);
-    uint64_t* d_poff = arena_take<uint64_t>(ctx, pk + 1);
+    uint8_t* d_msg = arena_take<uint8_t>(L, mbytes + 1);
+    uint64_t* d_moff = arena_take<uint64_t>(L, n + 1);
+    uint64_t* d_first = arena_take<uint64_t>(L, n + 1);
+    uint64_t* d_omoff = arena_take<uint64_t>(L, n + 1);
+    uint16_t* d_sp = arena_take<uint16_t>(L, n); uint16_t* d_dp = arena_take<uint16_t>(L, n);
+    uint16_t* d_sid = arena_take<uint16_t>(L, n); uint16_t* d_ssn = arena_take<uint16_t>(L, n);
+    uint32_t* d_vt = arena_take<uint32_t>(L, n); uint32_t* d_pp = arena_take<uint32_t>(L, n); uint32_t* d_tsn = arena_take<uint32_t>(L, n);
+    uint16_t* d_ep = arena_take<uint16_t>(L, n); uint64_t* d_sq = arena_take<uint64_t>(L, n);
+    uint8_t* d_out = arena_take<uint8_t>(L, bytes + 1);
+    uint64_t* d_poff = arena_take<uint64_t>(L, pk + 1);
 #define P2PT_UP(dst, src, cnt) CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, (cnt), cudaMemcpyHostToDevice, st))
     if (mbytes) P2PT_UP(d_msg, msg + msg_off[0], mbytes);
     P2PT_UP(d_moff, msg_off, 8 * (n + 1)); P2PT_UP(d_first, first.data(), 8 * (n + 1)); P2PT_UP(d_omoff, moff.data(), 8 * n);
@@ -1282,7 +1383,8 @@ int32_t p2pt_sctp_packetize_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg,
                                                      epoch ? d_ep : nullptr, epoch ? d_sq : nullptr, d_out, d_omoff, d_first, d_poff, st)) return r;
     CUDA_TRY(ctx, cudaMemcpyAsync(out, d_out, bytes, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(pkt_off, d_poff, 8 * (pk + 1), cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -1295,26 +1397,27 @@ int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const 
     if (n_pkts == 0) { *n_msgs_out = 0; msg_off[0] = 0; return P2PT_OK; }
     if (!in || !in_off || !msg) return set_err(ctx, P2PT_ERR_ARG, "sctp_unpack_reassemble: null argument");
     if (!offsets_monotonic(in_off, n_pkts)) return set_err(ctx, P2PT_ERR_ARG, "sctp_unpack_reassemble: offsets must be non-decreasing");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
-    cudaStream_t st = ctx->streams[0];
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
     const uint64_t n = n_pkts;
     const size_t ibytes = in_off[n] - in_off[0];
     const uint64_t sbytes = p2pt_sctp_reassemble_scratch_bytes(n);
-    if (int32_t r = arena_reserve(ctx, pad256(ibytes) + pad256(8 * (n + 1)) + pad256(4 * n) + pad256(16 * n) + pad256(24 * n) +
+    if (int32_t r = arena_reserve(ctx, L, pad256(ibytes) + pad256(8 * (n + 1)) + pad256(4 * n) + pad256(16 * n) + pad256(24 * n) +
                                            pad256(msg_cap) + pad256(8 * ((size_t)max_msgs + 1)) + pad256(4 * (size_t)max_msgs) +
                                            pad256(max_msgs) + 256 + pad256(sbytes) + 16384)) return r;
-    uint8_t* d_in = arena_take<uint8_t>(ctx, ibytes + 1);
-    uint64_t* d_ioff = arena_take<uint64_t>(ctx, n + 1);
-    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
-    p2pt_sctp_chunk* d_info = arena_take<p2pt_sctp_chunk>(ctx, n);
-    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
-    uint8_t* d_msg = arena_take<uint8_t>(ctx, msg_cap + 1);
-    uint64_t* d_moff = arena_take<uint64_t>(ctx, (size_t)max_msgs + 1);
-    uint32_t* d_mfirst = arena_take<uint32_t>(ctx, (size_t)max_msgs + 1);
-    uint8_t* d_mstat = arena_take<uint8_t>(ctx, (size_t)max_msgs + 1);
-    uint32_t* d_nm = arena_take<uint32_t>(ctx, 1);
-    uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
+    uint8_t* d_in = arena_take<uint8_t>(L, ibytes + 1);
+    uint64_t* d_ioff = arena_take<uint64_t>(L, n + 1);
+    uint32_t* d_sess = arena_take<uint32_t>(L, n);
+    p2pt_sctp_chunk* d_info = arena_take<p2pt_sctp_chunk>(L, n);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(L, n);
+    uint8_t* d_msg = arena_take<uint8_t>(L, msg_cap + 1);
+    uint64_t* d_moff = arena_take<uint64_t>(L, (size_t)max_msgs + 1);
+    uint32_t* d_mfirst = arena_take<uint32_t>(L, (size_t)max_msgs + 1);
+    uint8_t* d_mstat = arena_take<uint8_t>(L, (size_t)max_msgs + 1);
+    uint32_t* d_nm = arena_take<uint32_t>(L, 1);
+    uint8_t* d_scratch = arena_take<uint8_t>(L, sbytes);
     CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in + in_off[0], ibytes, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(d_ioff, in_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
     if (session) CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, st));
@@ -1325,16 +1428,17 @@ int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const 
     uint32_t nm = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&nm, d_nm, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(info, d_info, 16 * n, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
     *n_msgs_out = nm;
     if (nm > max_msgs) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_unpack_reassemble: more messages than max_msgs");
     CUDA_TRY(ctx, cudaMemcpyAsync(msg_off, d_moff, 8 * ((size_t)nm + 1), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(msg_first, d_mfirst, 4 * (size_t)nm, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(msg_status, d_mstat, nm, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
     if (msg_off[nm] > msg_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "sctp_unpack_reassemble: msg_cap too small");
     if (msg_off[nm]) CUDA_TRY(ctx, cudaMemcpyAsync(msg, d_msg, msg_off[nm], cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -1380,18 +1484,19 @@ int32_t p2pt_sse_scan_batch(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, cons
     if (!offsets_monotonic(body_off, k)) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: offsets must be non-decreasing");
     const size_t bytes = body_off[k] - body_off[0];
     if (bytes && !body) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: null body");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
-    cudaStream_t st = ctx->streams[0];
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
     const uint64_t sb = p2pt_sse_scan_scratch_bytes(k);
-    if (int32_t r = arena_reserve(ctx, pad256(bytes) + 2 * pad256(8 * (k + 1)) + pad256(8 * (max_events + 1)) + pad256(k) + 256 + pad256(sb) + 8192)) return r;
-    uint8_t* d_body = arena_take<uint8_t>(ctx, bytes + 1);
-    uint64_t* d_off = arena_take<uint64_t>(ctx, k + 1);
-    uint64_t* d_csr = arena_take<uint64_t>(ctx, k + 1);
-    uint64_t* d_end = arena_take<uint64_t>(ctx, max_events + 1);
-    uint8_t* d_done = arena_take<uint8_t>(ctx, k);
-    uint64_t* d_n = arena_take<uint64_t>(ctx, 1);
-    uint8_t* d_scr = arena_take<uint8_t>(ctx, sb);
+    if (int32_t r = arena_reserve(ctx, L, pad256(bytes) + 2 * pad256(8 * (k + 1)) + pad256(8 * (max_events + 1)) + pad256(k) + 256 + pad256(sb) + 8192)) return r;
+    uint8_t* d_body = arena_take<uint8_t>(L, bytes + 1);
+    uint64_t* d_off = arena_take<uint64_t>(L, k + 1);
+    uint64_t* d_csr = arena_take<uint64_t>(L, k + 1);
+    uint64_t* d_end = arena_take<uint64_t>(L, max_events + 1);
+    uint8_t* d_done = arena_take<uint8_t>(L, k);
+    uint64_t* d_n = arena_take<uint64_t>(L, 1);
+    uint8_t* d_scr = arena_take<uint8_t>(L, sb);
     if (bytes) CUDA_TRY(ctx, cudaMemcpyAsync(d_body, body + body_off[0], bytes, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(d_off, body_off, 8 * (k + 1), cudaMemcpyHostToDevice, st));
     if (int32_t r = p2pt_sse_scan_batch_device(ctx, k, d_body - body_off[0], d_off, max_events, d_csr, d_end, d_done, d_n, d_scr, sb, st)) return r;
@@ -1399,11 +1504,12 @@ int32_t p2pt_sse_scan_batch(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, cons
     CUDA_TRY(ctx, cudaMemcpyAsync(&total, d_n, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(ev_csr, d_csr, 8 * (k + 1), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(done, d_done, k, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
     *n_events_out = total;
     if (total > max_events) return set_err(ctx, P2PT_ERR_CAPACITY, "sse_scan: more events than max_events");
     if (total) CUDA_TRY(ctx, cudaMemcpyAsync(ev_end, d_end, 8 * total, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -1490,20 +1596,21 @@ int32_t p2pt_dtls_datagram_split_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t*
     if (n == 0) { *n_records_out = 0; return P2PT_OK; }
     if (!buf || !dgram_off || !dgram_status) return set_err(ctx, P2PT_ERR_ARG, "datagram_split: null argument");
     if (!offsets_monotonic(dgram_off, n)) return set_err(ctx, P2PT_ERR_ARG, "datagram_split: offsets must be non-decreasing");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
-    cudaStream_t st = ctx->streams[0];
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
     const size_t bytes = dgram_off[n] - dgram_off[0];
     const uint64_t sb = p2pt_dtls_datagram_split_scratch_bytes(n);
-    if (int32_t r = arena_reserve(ctx, pad256(bytes) + pad256(8 * (n + 1)) + pad256(8 * (max_records + 1)) + pad256(4 * max_records) +
+    if (int32_t r = arena_reserve(ctx, L, pad256(bytes) + pad256(8 * (n + 1)) + pad256(8 * (max_records + 1)) + pad256(4 * max_records) +
                                            pad256(n) + 256 + pad256(sb) + 8192)) return r;
-    uint8_t* d_buf = arena_take<uint8_t>(ctx, bytes + 1);
-    uint64_t* d_off = arena_take<uint64_t>(ctx, n + 1);
-    uint64_t* d_roff = arena_take<uint64_t>(ctx, max_records + 1);
-    uint32_t* d_rd = arena_take<uint32_t>(ctx, max_records + 1);
-    uint8_t* d_st = arena_take<uint8_t>(ctx, n);
-    uint32_t* d_n = arena_take<uint32_t>(ctx, 1);
-    uint8_t* d_scr = arena_take<uint8_t>(ctx, sb);
+    uint8_t* d_buf = arena_take<uint8_t>(L, bytes + 1);
+    uint64_t* d_off = arena_take<uint64_t>(L, n + 1);
+    uint64_t* d_roff = arena_take<uint64_t>(L, max_records + 1);
+    uint32_t* d_rd = arena_take<uint32_t>(L, max_records + 1);
+    uint8_t* d_st = arena_take<uint8_t>(L, n);
+    uint32_t* d_n = arena_take<uint32_t>(L, 1);
+    uint8_t* d_scr = arena_take<uint8_t>(L, sb);
     CUDA_TRY(ctx, cudaMemcpyAsync(d_buf, buf + dgram_off[0], bytes, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(d_off, dgram_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
     if (int32_t r = p2pt_dtls_datagram_split_batch_device(ctx, n, d_buf - dgram_off[0], d_off, max_records, d_roff, d_rd, d_st, d_n,
@@ -1511,12 +1618,13 @@ int32_t p2pt_dtls_datagram_split_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t*
     uint32_t total = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&total, d_n, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(dgram_status, d_st, n, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
     *n_records_out = total;
     if (total > max_records) return set_err(ctx, P2PT_ERR_CAPACITY, "datagram_split: more records than max_records");
     CUDA_TRY(ctx, cudaMemcpyAsync(rec_off, d_roff, 8 * ((size_t)total + 1), cudaMemcpyDeviceToHost, st));
     if (total) CUDA_TRY(ctx, cudaMemcpyAsync(rec_dgram, d_rd, 4 * (size_t)total, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -1527,20 +1635,21 @@ int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t*
     if (n == 0) return P2PT_OK;
     if (!session || !seq48 || !latest || !mask || !started || !accept || !n_sessions)
         return set_err(ctx, P2PT_ERR_ARG, "replay_filter: null argument");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
-    cudaStream_t st = ctx->streams[0];
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
     const uint64_t sb = p2pt_dtls_replay_filter_scratch_bytes(n);
     const size_t S = n_sessions;
-    if (int32_t r = arena_reserve(ctx, pad256(4 * n) + pad256(8 * n) + 2 * pad256(n) + 2 * pad256(8 * S) + pad256(S) + pad256(sb) + 8192)) return r;
-    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
-    uint64_t* d_seq = arena_take<uint64_t>(ctx, n);
-    uint8_t* d_auth = arena_take<uint8_t>(ctx, n);
-    uint8_t* d_acc = arena_take<uint8_t>(ctx, n);
-    uint64_t* d_lat = arena_take<uint64_t>(ctx, S);
-    uint64_t* d_mask = arena_take<uint64_t>(ctx, S);
-    uint8_t* d_started = arena_take<uint8_t>(ctx, S);
-    uint8_t* d_scr = arena_take<uint8_t>(ctx, sb);
+    if (int32_t r = arena_reserve(ctx, L, pad256(4 * n) + pad256(8 * n) + 2 * pad256(n) + 2 * pad256(8 * S) + pad256(S) + pad256(sb) + 8192)) return r;
+    uint32_t* d_sess = arena_take<uint32_t>(L, n);
+    uint64_t* d_seq = arena_take<uint64_t>(L, n);
+    uint8_t* d_auth = arena_take<uint8_t>(L, n);
+    uint8_t* d_acc = arena_take<uint8_t>(L, n);
+    uint64_t* d_lat = arena_take<uint64_t>(L, S);
+    uint64_t* d_mask = arena_take<uint64_t>(L, S);
+    uint8_t* d_started = arena_take<uint8_t>(L, S);
+    uint8_t* d_scr = arena_take<uint8_t>(L, sb);
     CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(d_seq, seq48, 8 * n, cudaMemcpyHostToDevice, st));
     if (authentic) CUDA_TRY(ctx, cudaMemcpyAsync(d_auth, authentic, n, cudaMemcpyHostToDevice, st));
@@ -1553,7 +1662,8 @@ int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t*
     CUDA_TRY(ctx, cudaMemcpyAsync(latest, d_lat, 8 * S, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(mask, d_mask, 8 * S, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(started, d_started, S, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, wait_stream(ctx, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    lg.dismiss();
     return P2PT_OK;
 }
 
@@ -1564,26 +1674,26 @@ int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t*
 // (open, single-block demux, gather) write the demux results straight back into it, only `desc` (and `out`
 // if asked for) take an asynchronous copy, and there is ONE stream wait.  Entries beyond k are never
 // copied to the caller, exactly like the general path.  *taken stays false if the call does not fit.
-static int32_t open_demux_small(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, const uint8_t* rec,
+static int32_t open_demux_small(p2pt_ctx* ctx, Lane* L, uint64_t n, const uint32_t* session, const uint8_t* rec,
                                 const uint64_t* rec_off, uint8_t* out, p2pt_desc* desc, uint32_t max_streams,
                                 uint32_t* uniq_sid, uint32_t* uniq_session, uint64_t* csr, uint32_t* perm,
                                 uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off,
                                 bool* taken) {
     *taken = false;
-    if (!ctx->small_demux || !ctx->zc_host || !ctx->small_call_bytes || n > (uint64_t)kSmallDemux) return P2PT_OK;
+    if (!ctx->small_demux || !L->zc_host || !ctx->small_call_bytes || n > (uint64_t)kSmallDemux) return P2PT_OK;
     const size_t ibytes = rec_off[n] - rec_off[0];
     const size_t ms1 = (size_t)(max_streams < n ? max_streams : n) + 1;
     const size_t gcap = gathered ? (size_t)(gathered_cap < ibytes ? gathered_cap : ibytes) : 0;
     const size_t foot = pad256(4 * n) + pad256(8 * (n + 1)) + pad256(ibytes + 1) + 2 * pad256(4 * ms1) + 2 * pad256(8 * ms1) +
                         pad256(4 * n) + pad256(gcap + 1) + 256;
-    if (foot > ctx->small_call_bytes || foot > ctx->zc_cap) return P2PT_OK;
+    if (foot > ctx->small_call_bytes || foot > L->zc_cap) return P2PT_OK;
     *taken = true;
     const uint64_t sbytes = demux_scratch_bytes(n);
-    if (int32_t r = arena_reserve(ctx, pad256(ibytes + 1) + pad256(24 * n) + pad256(sbytes) + 4096)) return r;
-    uint8_t* d_out = arena_take<uint8_t>(ctx, ibytes + 1);
-    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
-    uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
-    ZcCarver zcv{ctx};
+    if (int32_t r = arena_reserve(ctx, L, pad256(ibytes + 1) + pad256(24 * n) + pad256(sbytes) + 4096)) return r;
+    uint8_t* d_out = arena_take<uint8_t>(L, ibytes + 1);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(L, n);
+    uint8_t* d_scratch = arena_take<uint8_t>(L, sbytes);
+    ZcCarver zcv{L};
     auto zc = [&](size_t bytes) { return zcv.take(bytes); };
     auto host_of = [&](const void* d) { return zcv.host_of(d); };
     uint32_t* z_sess = (uint32_t*)zc(4 * n);
@@ -1599,7 +1709,7 @@ static int32_t open_demux_small(p2pt_ctx* ctx, uint64_t n, const uint32_t* sessi
     memcpy(host_of(z_sess), session, 4 * n);
     memcpy(host_of(z_io), rec_off, 8 * (n + 1));
     if (ibytes) memcpy(host_of(z_in), rec + rec_off[0], ibytes);
-    cudaStream_t st = ctx->streams[0];
+    cudaStream_t st = L->streams[0];
     GcmArgs a = {};
     a.n = n; a.session = z_sess; a.n_sessions = ctx->n_sessions; a.keys = ctx->keys_remote;
     a.in = z_in - rec_off[0]; a.in_off = (const u64*)z_io;
@@ -1645,38 +1755,39 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
     if (n > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: n must fit in 32 bits");
     if (!offsets_monotonic(rec_off, n)) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: offsets must be non-decreasing");
     if (int32_t r = check_sessions(ctx)) return r;
-    std::lock_guard<std::mutex> lk(ctx->mu);
     DeviceGuard dg(ctx->device);
+    LaneGuard lg(ctx);
+    Lane* L = lg.lane;
     {
         bool taken = false;
-        const int32_t r = open_demux_small(ctx, n, session, rec, rec_off, out, desc, max_streams, uniq_sid, uniq_session, csr, perm,
+        const int32_t r = open_demux_small(ctx, L, n, session, rec, rec_off, out, desc, max_streams, uniq_sid, uniq_session, csr, perm,
                                            k_out, gathered, gathered_cap, gathered_off, &taken);
-        if (taken) return r;
+        if (taken) { if (r == P2PT_OK) lg.dismiss(); return r; }
     }
     const size_t ibytes = rec_off[n] - rec_off[0];
     const uint64_t sbytes = demux_scratch_bytes(n);
     const size_t gcap = gathered ? (size_t)gathered_cap : 0;
-    if (int32_t r = arena_reserve(ctx, pad256(4 * n) + pad256(8 * (n + 1)) + 2 * pad256(ibytes) + pad256(24 * n) +
+    if (int32_t r = arena_reserve(ctx, L, pad256(4 * n) + pad256(8 * (n + 1)) + 2 * pad256(ibytes) + pad256(24 * n) +
                                            2 * pad256(4 * ((size_t)max_streams + 1)) + 2 * pad256(8 * ((size_t)max_streams + 1)) +
                                            pad256(4 * n) + 256 + pad256(gcap) + pad256(sbytes) + 16384)) return r;
-    uint32_t* d_sess = arena_take<uint32_t>(ctx, n);
-    uint64_t* d_io = arena_take<uint64_t>(ctx, n + 1);
-    uint8_t* d_in = arena_take<uint8_t>(ctx, ibytes + 1);
-    uint8_t* d_out = arena_take<uint8_t>(ctx, ibytes + 1);
-    p2pt_desc* d_desc = arena_take<p2pt_desc>(ctx, n);
-    uint32_t* d_uniq = arena_take<uint32_t>(ctx, (size_t)max_streams + 1);
-    uint32_t* d_usess = arena_take<uint32_t>(ctx, (size_t)max_streams + 1);
-    uint64_t* d_csr = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
-    uint64_t* d_goff = arena_take<uint64_t>(ctx, (size_t)max_streams + 1);
-    uint32_t* d_perm = arena_take<uint32_t>(ctx, n);
-    uint32_t* d_k = arena_take<uint32_t>(ctx, 1);
-    uint8_t* d_g = arena_take<uint8_t>(ctx, gcap + 1);
-    uint8_t* d_scratch = arena_take<uint8_t>(ctx, sbytes);
+    uint32_t* d_sess = arena_take<uint32_t>(L, n);
+    uint64_t* d_io = arena_take<uint64_t>(L, n + 1);
+    uint8_t* d_in = arena_take<uint8_t>(L, ibytes + 1);
+    uint8_t* d_out = arena_take<uint8_t>(L, ibytes + 1);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(L, n);
+    uint32_t* d_uniq = arena_take<uint32_t>(L, (size_t)max_streams + 1);
+    uint32_t* d_usess = arena_take<uint32_t>(L, (size_t)max_streams + 1);
+    uint64_t* d_csr = arena_take<uint64_t>(L, (size_t)max_streams + 1);
+    uint64_t* d_goff = arena_take<uint64_t>(L, (size_t)max_streams + 1);
+    uint32_t* d_perm = arena_take<uint32_t>(L, n);
+    uint32_t* d_k = arena_take<uint32_t>(L, 1);
+    uint8_t* d_g = arena_take<uint8_t>(L, gcap + 1);
+    uint8_t* d_scratch = arena_take<uint8_t>(L, sbytes);
 
-    cudaStream_t s0 = ctx->streams[0];
+    cudaStream_t s0 = L->streams[0];
     CUDA_TRY(ctx, cudaMemcpyAsync(d_io, rec_off, 8 * (n + 1), cudaMemcpyHostToDevice, s0));
     CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, s0));
-    CUDA_TRY(ctx, cudaEventRecord(ctx->events[0], s0));
+    CUDA_TRY(ctx, cudaEventRecord(L->events[0], s0));
     const int G = pick_group(ctx, n, ibytes);
     uint64_t chunk = n;
     if (ibytes > 2 * ctx->chunk_bytes) {
@@ -1686,8 +1797,8 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
     int si = 0;
     for (uint64_t r0 = 0; r0 < n; r0 += chunk, si = (si + 1) % kStreams) {
         const uint64_t r1 = r0 + chunk < n ? r0 + chunk : n;
-        cudaStream_t st = ctx->streams[si];
-        CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->events[0], 0));
+        cudaStream_t st = L->streams[si];
+        CUDA_TRY(ctx, cudaStreamWaitEvent(st, L->events[0], 0));
         const size_t b0 = rec_off[r0] - rec_off[0], b1 = rec_off[r1] - rec_off[0];
         if (b1 > b0) CUDA_TRY(ctx, cudaMemcpyAsync(d_in + b0, rec + rec_off[r0], b1 - b0, cudaMemcpyHostToDevice, st));
         GcmArgs a = {};
@@ -1699,8 +1810,8 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
         if (out && b1 > b0) CUDA_TRY(ctx, cudaMemcpyAsync(out + rec_off[r0], d_out + b0, b1 - b0, cudaMemcpyDeviceToHost, st));
     }
     for (int i = 1; i < kStreams; i++) {          // join the chunk streams into stream 0
-        CUDA_TRY(ctx, cudaEventRecord(ctx->events[i], ctx->streams[i]));
-        CUDA_TRY(ctx, cudaStreamWaitEvent(s0, ctx->events[i], 0));
+        CUDA_TRY(ctx, cudaEventRecord(L->events[i], L->streams[i]));
+        CUDA_TRY(ctx, cudaStreamWaitEvent(s0, L->events[i], 0));
     }
     CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, s0));
     if (int32_t r = p2pt_frame_demux_batch_device(ctx, n, d_desc, d_sess, d_out - rec_off[0], max_streams, d_uniq,
@@ -1709,14 +1820,14 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
                                                   gathered_off ? d_goff : nullptr, d_scratch, sbytes, s0)) return r;
     uint32_t k = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&k, d_k, 4, cudaMemcpyDeviceToHost, s0));
-    CUDA_TRY(ctx, wait_stream(ctx, s0));
+    CUDA_TRY(ctx, wait_stream(ctx, L, s0));
     *k_out = k;
     if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "pipeline_open_demux: more streams than max_streams");
     CUDA_TRY(ctx, cudaMemcpyAsync(uniq_sid, d_uniq, 4 * (size_t)k, cudaMemcpyDeviceToHost, s0));
     if (uniq_session) CUDA_TRY(ctx, cudaMemcpyAsync(uniq_session, d_usess, 4 * (size_t)k, cudaMemcpyDeviceToHost, s0));
     CUDA_TRY(ctx, cudaMemcpyAsync(csr, d_csr, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, s0));
     if (gathered_off) CUDA_TRY(ctx, cudaMemcpyAsync(gathered_off, d_goff, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, s0));
-    CUDA_TRY(ctx, wait_stream(ctx, s0));
+    CUDA_TRY(ctx, wait_stream(ctx, L, s0));
     const uint64_t m = csr[k];
     if (m) CUDA_TRY(ctx, cudaMemcpyAsync(perm, d_perm, 4 * m, cudaMemcpyDeviceToHost, s0));
     if (gathered) {
@@ -1724,16 +1835,17 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
         // split the big copy over the streams so both DMA engines stay busy
         const uint64_t total = gathered_off[k];
         const uint64_t piece = (total + kStreams - 1) / kStreams;
-        CUDA_TRY(ctx, cudaEventRecord(ctx->events[0], s0));
+        CUDA_TRY(ctx, cudaEventRecord(L->events[0], s0));
         for (int i = 0; i < kStreams && piece; i++) {
             const uint64_t o = (uint64_t)i * piece;
             if (o >= total) break;
             const uint64_t len = o + piece <= total ? piece : total - o;
-            CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->streams[i], ctx->events[0], 0));
-            CUDA_TRY(ctx, cudaMemcpyAsync(gathered + o, d_g + o, len, cudaMemcpyDeviceToHost, ctx->streams[i]));
+            CUDA_TRY(ctx, cudaStreamWaitEvent(L->streams[i], L->events[0], 0));
+            CUDA_TRY(ctx, cudaMemcpyAsync(gathered + o, d_g + o, len, cudaMemcpyDeviceToHost, L->streams[i]));
         }
     }
-    for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, wait_stream(ctx, ctx->streams[i]));
+    for (int i = 0; i < kStreams; i++) CUDA_TRY(ctx, wait_stream(ctx, L, L->streams[i]));
+    lg.dismiss();
     return P2PT_OK;
 }
 

@@ -274,8 +274,9 @@ def test_device_pointer_entry_points(ctx):
 
 def test_device_kernels_never_write_outside_their_items(ctx):
     """Canary check (compute-sanitizer is not available on this pool): output slots are laid out with
-    gaps at odd offsets inside a buffer pre-filled with 0xCD; after the kernels ran every byte that
-    is not part of an item must still be 0xCD, and the items must match the oracle."""
+    slack at odd offsets inside a buffer pre-filled with 0xCD; after the kernels ran every byte outside
+    the slots must still be 0xCD, the bytes of a slot behind its item must be zero (p2pt.h: nothing
+    stale may reach the caller), and the items must match the oracle."""
     import torch
     dev = torch.device("cuda:0")
     rng = np.random.default_rng(99)
@@ -308,7 +309,9 @@ def test_device_kernels_never_write_outside_their_items(ctx):
         torch.cuda.synchronize()
         got = rec.cpu().numpy()
         m = mask_of(rec_off, lens + np.uint64(37))
-        assert np.all(got[~m] == 0xCD), f"seal wrote outside its records (G={g})"
+        inside = np.zeros(total, bool); inside[int(rec_off[0]):int(rec_off[-1])] = True
+        assert np.all(got[~inside] == 0xCD), f"seal wrote outside its slots (G={g})"
+        assert not got[inside & ~m].any(), f"seal left stale bytes behind an item (G={g})"
         exp, _, _ = ob.dtls_seal(session, keys, ivs, nonce, raw, raw_off, rec_off)
         assert np.array_equal(got[:int(rec_off[-1])][m[:int(rec_off[-1])]], exp[m[:int(rec_off[-1])]])
         # open takes the record length from the input offsets, so its input is packed tight; its
@@ -322,7 +325,8 @@ def test_device_kernels_never_write_outside_their_items(ctx):
         assert int(status.sum()) == 0
         go = out.cpu().numpy()
         mo = mask_of(rec_off, lens + np.uint64(13))
-        assert np.all(go[~mo] == 0xCD), f"open wrote outside its records (G={g})"
+        assert np.all(go[~inside] == 0xCD), f"open wrote outside its slots (G={g})"
+        assert not go[inside & ~mo].any(), f"open left stale bytes behind an item (G={g})"
         for i in range(0, n, 7):
             a = int(rec_off[i])
             assert np.array_equal(go[a + 13:a + 13 + int(lens[i])], raw[int(raw_off[i]) + 13:int(raw_off[i + 1])])
@@ -344,6 +348,29 @@ def test_device_kernels_never_write_outside_their_items(ctx):
     assert np.all(gf[~mf] == 0xCD), "frame_encode wrote outside its frames"
     expf, _ = ob.frame_encode(types, sids, payload, pay_off, f_off)
     assert np.array_equal(gf[:int(f_off[-1])][mf[:int(f_off[-1])]], expf[mf[:int(f_off[-1])]])
+    # the small-frame regime of the encoder (average slot <= 128 bytes): dense slots go through shared memory in
+    # tiles of 128 frames, a tile with slack between its slots takes the four-lanes-per-frame copy
+    for gaps in (False, True):
+        n2 = 3000
+        pl2 = rng.integers(0, 110, n2).astype(np.uint64); pl2[:64] = np.arange(64); pl2[500:700] = 64
+        po2 = np.zeros(n2 + 1, np.uint64); np.cumsum(pl2, out=po2[1:])
+        pay2 = rng.integers(0, 256, int(po2[-1]), dtype=np.uint8)
+        sl2 = pl2 + np.uint64(5)
+        if gaps:
+            sl2[1000:1400] += rng.integers(1, 9, 400).astype(np.uint64)      # only some tiles have slack
+        fo2 = np.zeros(n2 + 1, np.uint64); np.cumsum(sl2, out=fo2[1:]); fo2 += np.uint64(11)
+        tot2 = int(fo2[-1]) + 64
+        ty2 = rng.choice(np.array([11, 21, 20, 22], np.uint8), n2); si2 = rng.integers(0, 2**32, n2, dtype=np.uint64).astype(np.uint32)
+        fr2 = torch.full((tot2,), 0xCD, dtype=torch.uint8, device=dev)
+        ctx.call("p2pt_frame_encode_batch_device", n2, t(ty2), t(si2), t(pay2), t(po2), fr2, t(fo2), s)
+        torch.cuda.synchronize()
+        g2 = fr2.cpu().numpy()
+        m2 = np.zeros(tot2, bool)
+        for i in range(n2):
+            m2[int(fo2[i]):int(fo2[i]) + int(pl2[i]) + 5] = True
+        assert np.all(g2[~m2] == 0xCD), f"small-frame encode wrote outside its frames (gaps={gaps})"
+        e2, _ = ob.frame_encode(ty2, si2, pay2, po2, fo2)
+        assert np.array_equal(g2[:int(fo2[-1])][m2[:int(fo2[-1])]], e2[m2[:int(fo2[-1])]]), gaps
     # gather into a canary-filled buffer: exactly the body bytes, nothing after them
     from p2p_llm_tunnel_b200._lib import DESC_DTYPE
     tight_off = np.zeros(n + 1, np.uint64); np.cumsum(plens + np.uint64(5), out=tight_off[1:])
