@@ -57,29 +57,42 @@ constexpr uint32_t kSmallTileIn = 8192;          // payload span held in shared 
 constexpr uint32_t kSmallTileOut = kSmallTileIn + 5 * kSmallTile;
 constexpr u64 kSmallFrameAvg = 128;              // average slot (bytes) up to which a launch runs in the small-frame regime
 
-// len bytes from shared src to shared dst, any alignment on either side, by `parts` cooperating lanes (part =
-// 0 .. parts - 1).  Whole destination words come from two source words and a funnel shift; each lane walks a
-// contiguous run of words so that consecutive words share a source word.
-__device__ __forceinline__ void smem_copy_unaligned(uint8_t* dst, const uint8_t* src, uint32_t len, int part, int parts) {
-    const uint32_t d0 = (uint32_t)((4 - ((uintptr_t)dst & 3)) & 3);               // bytes up to the first aligned dst word
+// The two shared buffers of the small-frame regime are PADDED by one word after every 16: logical word w lives at
+// physical word w + (w >> 4).  Frames of 64 bytes (the SSE chunk of BASELINE.json config #4) start 16 words apart,
+// so without the padding the lanes of a warp - each on its own frame - hit two banks; measured 67 % of the
+// shared-memory wavefronts were bank conflicts and the L1 pipe sat at 95 % of its peak.  With the padding
+// consecutive frames start 17 words apart.
+__device__ __forceinline__ uint32_t pad_word(uint32_t w) { return w + (w >> 4); }
+struct PaddedBuf {
+    uint32_t* w;                                       // physical words
+    __device__ __forceinline__ uint32_t& word(uint32_t i) const { return w[pad_word(i)]; }
+    __device__ __forceinline__ uint8_t& byte(uint32_t b) const { return reinterpret_cast<uint8_t*>(w)[4 * pad_word(b >> 2) + (b & 3)]; }
+};
+
+// len bytes from logical byte offset so of src to logical byte offset d of dst, any alignment on either side, by
+// `parts` cooperating lanes (part = 0 .. parts - 1).  Whole destination words come from two source words and a
+// funnel shift; each lane walks a contiguous run of words so that consecutive words share a source word.
+__device__ __forceinline__ void smem_copy_unaligned(const PaddedBuf& dst, uint32_t d, const PaddedBuf& src, uint32_t so,
+                                                    uint32_t len, int part, int parts) {
+    const uint32_t d0 = (4 - (d & 3)) & 3;                                       // bytes up to the first aligned dst word
     if (len < d0 + 4) {                                                          // no whole word: bytes
-        for (uint32_t b = part; b < len; b += parts) dst[b] = src[b];
+        for (uint32_t b = part; b < len; b += parts) dst.byte(d + b) = src.byte(so + b);
         return;
     }
     const uint32_t nw = (len - d0) >> 2;                                         // whole destination words
-    if (part == 0) for (uint32_t b = 0; b < d0; b++) dst[b] = src[b];
-    if (part == parts - 1) for (uint32_t b = d0 + 4 * nw; b < len; b++) dst[b] = src[b];
+    if (part == 0) for (uint32_t b = 0; b < d0; b++) dst.byte(d + b) = src.byte(so + b);
+    if (part == parts - 1) for (uint32_t b = d0 + 4 * nw; b < len; b++) dst.byte(d + b) = src.byte(so + b);
     const uint32_t per = (nw + parts - 1) / parts, w0 = per * part;
     uint32_t w1 = w0 + per; if (w1 > nw) w1 = nw;
     if (w0 >= w1) return;
-    uint32_t* dw = reinterpret_cast<uint32_t*>(dst + d0);
-    const uint8_t* s = src + d0 + 4 * w0;
-    const unsigned sh = (unsigned)((uintptr_t)s & 3) * 8;
-    const uint32_t* sw = reinterpret_cast<const uint32_t*>(s - ((uintptr_t)s & 3));
-    uint32_t lo = sw[0];
+    const uint32_t dw = (d + d0) >> 2;                                           // first whole destination word
+    const uint32_t sb = so + d0 + 4 * w0;                                        // source byte of destination word w0
+    const unsigned sh = (sb & 3) * 8;
+    const uint32_t sw = sb >> 2;
+    uint32_t lo = src.word(sw);
     for (uint32_t k = 0; k < w1 - w0; k++) {
-        const uint32_t hi = sw[k + 1];          // for an aligned source the funnel ignores it; the buffers carry 32 spare bytes
-        dw[w0 + k] = __funnelshift_r(lo, hi, sh);
+        const uint32_t hi = src.word(sw + k + 1);   // for an aligned source the funnel ignores it; the buffers carry spare words
+        dst.word(dw + w0 + k) = __funnelshift_r(lo, hi, sh);
         lo = hi;
     }
 }
@@ -129,8 +142,9 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
         return;
     }
     // ---------------------------------------------------------------------- small-frame regime
-    __shared__ __align__(16) uint8_t sin[kSmallTileIn + 32];
-    __shared__ __align__(16) uint8_t sout[kSmallTileOut + 32];
+    __shared__ __align__(16) uint32_t sin_w[(kSmallTileIn + 32) / 4 + (kSmallTileIn + 32) / 64 + 2];
+    __shared__ __align__(16) uint32_t sout_w[(kSmallTileOut + 32) / 4 + (kSmallTileOut + 32) / 64 + 2];
+    const PaddedBuf sin{sin_w}, sout{sout_w};
     __shared__ u64 s_po[kSmallTile + 1], s_oo[kSmallTile + 1];
     __shared__ uint32_t s_sid[kSmallTile];
     __shared__ uint8_t s_type[kSmallTile];
@@ -185,7 +199,10 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
 #pragma unroll
             for (int k = 0; k < 3; k++) {
                 const uint32_t vi = t + 256 * k;
-                if (vi < nvin) *reinterpret_cast<uint4*>(sin + 16 * vi) = cur.v[k];
+                if (vi < nvin) {                                       // words 4 vi .. 4 vi + 3 share one padding offset
+                    uint32_t* q4 = sin_w + 4 * vi + (vi >> 2);
+                    q4[0] = cur.v[k].x; q4[1] = cur.v[k].y; q4[2] = cur.v[k].z; q4[3] = cur.v[k].w;
+                }
             }
         }
         __syncthreads();                                               // tile in shared memory; previous flush behind everyone
@@ -197,20 +214,22 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
                 const int f = t >> 1, h = t & 1;                       // two lanes per frame
                 if (f < T) {
                     const uint32_t po = (uint32_t)(s_po[f] - pb), len = (uint32_t)(s_po[f + 1] - s_po[f]);
-                    uint8_t* d = sout + oa + (uint32_t)(s_oo[f] - ob);
+                    const uint32_t d = oa + (uint32_t)(s_oo[f] - ob);
                     if (h == 0) {                                      // header: [type][stream_id BE]
                         const uint32_t sid = s_sid[f];
-                        d[0] = s_type[f];
-                        d[1] = (uint8_t)(sid >> 24); d[2] = (uint8_t)(sid >> 16); d[3] = (uint8_t)(sid >> 8); d[4] = (uint8_t)sid;
+                        sout.byte(d) = s_type[f];
+                        sout.byte(d + 1) = (uint8_t)(sid >> 24); sout.byte(d + 2) = (uint8_t)(sid >> 16);
+                        sout.byte(d + 3) = (uint8_t)(sid >> 8); sout.byte(d + 4) = (uint8_t)sid;
                     }
-                    if (len) smem_copy_unaligned(d + 5, sin + ia + po, len, h, 2);
+                    if (len) smem_copy_unaligned(sout, d + 5, sin, ia + po, len, h, 2);
                 }
             }
             __syncthreads();
             const uint32_t total = oa + (uint32_t)ospan;               // [oa, total) of sout is the span
             uint8_t* g0 = gdst - oa;
             for (uint32_t lo = 16u * t; lo < total; lo += 16u * 256u) {
-                const uint4 x = *reinterpret_cast<const uint4*>(sout + lo);
+                const uint32_t* q4 = sout_w + (lo >> 2) + (lo >> 6);   // words lo / 4 .. + 3 share one padding offset
+                const uint4 x = make_uint4(q4[0], q4[1], q4[2], q4[3]);
                 if (lo >= oa && lo + 16 <= total) stg128(g0 + lo, x);
                 else store_bytes(g0 + lo, x, lo < oa ? (int)(oa - lo) : 0, total - lo < 16u ? (int)(total - lo) : 16);
             }
@@ -430,14 +449,32 @@ __device__ __forceinline__ void demux_hist_phase(u64 n, const DemuxBufs& bufs, c
     __syncthreads();
     u64 lo, hi;
     demux_tile(n, lo, hi);
+    // the key words of the next chunk are in flight while this one is ranked (the loop is latency-bound otherwise)
+    u64 nkey[kSortItems];
+#pragma unroll
+    for (int r = 0; r < kSortItems; r++) {
+        const u64 i = lo + r * kSortThreads + threadIdx.x;
+        nkey[r] = i < hi ? __ldcg(keys + i) : 0;
+    }
     for (u64 c0 = lo; c0 < hi; c0 += kSortThreads * kSortItems) {
         uint32_t d[kSortItems];
         bool live[kSortItems];
+        u64 key[kSortItems];
 #pragma unroll
-        for (int r = 0; r < kSortItems; r++) {           // all loads first
+        for (int r = 0; r < kSortItems; r++) {
+            key[r] = nkey[r];
+            const u64 i = c0 + kSortThreads * kSortItems + r * kSortThreads + threadIdx.x;
+            nkey[r] = i < hi ? __ldcg(keys + i) : 0;
+        }
+#pragma unroll
+        for (int r = 0; r < kSortItems; r++) {
             const u64 i = c0 + r * kSortThreads + threadIdx.x;
             live[r] = i < hi;
-            d[r] = live[r] ? demux_digit(keys, idx, i, pass, blen, packed) : 0u;
+            d[r] = 0;
+            if (live[r]) {
+                if (pass < kKeyPasses) d[r] = (uint32_t)(key[r] >> (8 * pass + (packed ? 32 : 0))) & 0xffu;
+                else d[r] = __ldg(blen + (packed ? (uint32_t)key[r] : __ldcg(idx + i))) == kNotDecodable ? 1u : 0u;
+            }
         }
 #pragma unroll
         for (int r = 0; r < kSortItems; r++) {
@@ -527,6 +564,12 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
         for (int w = 0; w < W; w++) wbase += (w < warp) ? wtot[w] : 0u;
         base = wbase + incl - v + __ldcg(hist + (u64)threadIdx.x * kSortBlocks + blockIdx.x);
     }
+    u64 nkey[kSortItems];                      // next chunk's key words, in flight while this chunk is ranked and written
+#pragma unroll
+    for (int r = 0; r < kSortItems; r++) {
+        const u64 i = lo + (u64)warp * (32 * kSortItems) + r * 32 + lane;
+        nkey[r] = i < hi ? __ldcg(keys + i) : 0;
+    }
     for (u64 c0 = lo; c0 < hi; c0 += kChunk) {
 #pragma unroll
         for (int w = 0; w < W; w++) wcount[w][col] = 0;
@@ -534,11 +577,14 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
         uint32_t ix[kSortItems], d[kSortItems], rank[kSortItems];
         bool live[kSortItems];
 #pragma unroll
-        for (int r = 0; r < kSortItems; r++) {           // all loads first
+        for (int r = 0; r < kSortItems; r++) {
             const u64 i = c0 + (u64)warp * (32 * kSortItems) + r * 32 + lane;
             live[r] = i < hi;
-            key[r] = 0; ix[r] = 0;
-            if (live[r]) { key[r] = __ldcg(keys + i); ix[r] = packed ? (uint32_t)key[r] : __ldcg(idx + i); }
+            key[r] = nkey[r];
+            ix[r] = 0;
+            if (live[r]) ix[r] = packed ? (uint32_t)key[r] : __ldcg(idx + i);
+            const u64 inext = i + kChunk;
+            nkey[r] = inext < hi ? __ldcg(keys + inext) : 0;
         }
 #pragma unroll
         for (int r = 0; r < kSortItems; r++) {
@@ -631,7 +677,7 @@ __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
 
 // ... or all passes in ONE cooperative launch: the nine passes are launch-latency bound at 1 M items
 // (27 launches of a few microseconds each), so the phases are separated by grid-wide syncs instead.
-__global__ void __launch_bounds__(kSortThreads) demux_sort_coop_kernel(
+__global__ void __launch_bounds__(kSortThreads, 4) demux_sort_coop_kernel(
     u64 n, const DemuxBufs bufs, const uint32_t* blen, uint32_t* hist, const u64* misc, uint32_t* row_total, bool packed) {
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     for (int pass = 0; pass < kSortPasses; pass++) {

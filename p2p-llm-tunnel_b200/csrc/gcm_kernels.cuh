@@ -313,7 +313,7 @@ struct GcmArgs {
 // otherwise spills and re-derives loop invariants inside the loop (64-bit range tests, the shared window
 // address from S2R).
 #ifndef P2PT_GCM_PARK
-#define P2PT_GCM_PARK 0
+#define P2PT_GCM_PARK 1
 #endif
 constexpr int kGcmThreads = P2PT_GCM_THREADS;
 constexpr int kGcmUnroll = P2PT_GCM_UNROLL;
