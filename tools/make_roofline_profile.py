@@ -56,32 +56,6 @@ def to_bytes(v, unit):
     return x * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}.get(unit, 1)
 
 
-def opcode_hist(rep, kernel_id):
-    rows = list(csv.reader(io.StringIO(ncu(rep, "--page", "source", "--csv", "--kernel-id", f"::{kernel_id}:"))))
-    hi = next(i for i, r in enumerate(rows) if "Source" in r and "Instructions Executed" in r)
-    hdr = rows[hi]
-    si, ei, ss = hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("# Samples")
-    stall_cols = [(j, c) for j, c in enumerate(hdr) if c.startswith("stall_") and "Not Issued" not in c]
-    agg, stalls, tot, stot = collections.Counter(), collections.Counter(), 0, 0
-    for r in rows[hi + 1:]:
-        try:
-            n = int(r[ei]); smp = int(r[ss])
-        except (ValueError, IndexError):
-            continue
-        op = r[si].strip().split()
-        if not op:
-            continue
-        o = op[1] if op[0].startswith("@") else op[0]
-        o = ".".join(o.split(".")[:2]) if o.startswith(("LD", "ST", "IMAD", "SHFL")) else o.split(".")[0]
-        agg[o] += n; tot += n; stot += smp
-        for j, c in stall_cols:
-            try:
-                stalls[c] += int(r[j])
-            except ValueError:
-                pass
-    return agg, tot, stalls, stot
-
-
 def main():
     rep, tag = sys.argv[1], sys.argv[2]
     raw = raw_page(rep)
@@ -97,9 +71,7 @@ def main():
         name = d["Kernel Name"][0]
         if "gcm_record_kernel" not in name:
             continue
-        which = "seal" if "<4, 2>" in name or "ELi2E" in name or ", 2>" in name else "open"
-        kid = d["ID"][0]
-        agg, tot, stalls, stot = opcode_hist(rep, name.split("(")[0].strip() if False else kid) if False else (None, None, None, None)
+        which = "seal" if ", 2>" in name else "open"
         text.append("-----")
         text.append(f"  Kernel Name = {name}")
         m = {}
@@ -121,15 +93,15 @@ def main():
                               "warps_active_pct": f("sm__warps_active.avg.pct_of_peak_sustained_active") / 100,
                               "local_loads_per_launch": f("sass__inst_executed_local_loads"),
                               "registers_per_thread": f("launch__registers_per_thread"),
-                              "duration_ms_under_ncu": f("gpu__time_duration.sum") * {"us": 1e-3, "ms": 1, "ns": 1e-6, "s": 1e3}.get(m["gpu__time_duration.sum"][1], 1)},
-                      "_id": kid}
+                              "duration_ms_under_ncu": f("gpu__time_duration.sum") * {"us": 1e-3, "ms": 1, "ns": 1e-6, "s": 1e3}.get(m["gpu__time_duration.sum"][1], 1)}}
     # instruction mix from the source page, one kernel at a time (launch order in the capture: seal, then open)
     for which in ("seal", "open"):
         if which not in out:
             continue
         k = out[which]
-        src = ncu(rep, "--page", "source", "--csv", "--print-kernel-base", "function", "--kernel-name", "regex:gcm_record", "--launch-skip",
-                  "0" if which == "seal" else "1", "--launch-count", "1")
+        src = ncu(rep, "--page", "source", "--csv", "--kernel-name", "regex:gcm_record", "--launch-skip", "0" if which == "seal" else "1",
+                  "--launch-count", "1")
+        assert ("(int)2>" if which == "seal" else "(int)3>") in src.split("\n", 1)[0], src.split("\n", 1)[0]
         rows = list(csv.reader(io.StringIO(src)))
         hi = next(i for i, r in enumerate(rows) if "Source" in r and "Instructions Executed" in r)
         hdr = rows[hi]
@@ -152,21 +124,26 @@ def main():
                     stalls[c] += int(r[j])
                 except ValueError:
                     pass
+        # the source page's counts come from its own replay passes and can be a whole multiple of the launch's
+        # smsp__inst_executed (2x in the r02 capture): the MIX is taken from it, the total from the raw page
+        scale = k["total_inst_per_lane_slot"] * WARP_SLOTS / tot
+        agg = collections.Counter({o: v * scale for o, v in agg.items()})
+        tot_src, tot = tot, tot * scale
         alu = sum(v for o, v in agg.items() if o in ALU)
         fma = sum(v for o, v in agg.items() if o.startswith("IMAD") or o in ("IMUL", "FFMA", "FMUL"))
         lds = sum(v for o, v in agg.items() if o.startswith("LDS"))
         k["alu_pipe_inst_per_lane_slot"] = alu / WARP_SLOTS
         k["fma_pipe_inst_per_lane_slot"] = fma / WARP_SLOTS
         k["lds_inst_per_lane_slot"] = lds / WARP_SLOTS
-        k["source_page_inst_per_lane_slot"] = tot / WARP_SLOTS
-        lines = [f"total warp instructions {tot}, per warp-slot {tot / WARP_SLOTS:.1f}; samples {stot}",
+        k["source_page_count_scale"] = scale
+        lines = [f"total warp instructions {tot:.0f} (smsp__inst_executed.sum; the source page counted {tot_src}, mix scaled by {scale:.3f}), "
+                 f"per warp-slot {tot / WARP_SLOTS:.1f}; samples {stot}",
                  f"ALU pipe {alu / WARP_SLOTS:.1f}, FMA pipe {fma / WARP_SLOTS:.1f}, LDS {lds / WARP_SLOTS:.1f} per warp-slot"]
         for o, v in agg.most_common(30):
-            lines.append(f"{o:14s} {v:12d} {v / tot * 100:5.1f}%  per-slot {v / WARP_SLOTS:7.1f}")
+            lines.append(f"{o:14s} {v:14.0f} {v / tot * 100:5.1f}%  per-slot {v / WARP_SLOTS:7.1f}")
         lines.append("stall samples: " + ", ".join(f"{c[6:]}={v / max(stot, 1) * 100:.1f}%" for c, v in stalls.most_common(9)))
         with open(os.path.join(ROOT, "profiles", f"{tag}_{which}_opcode_hist.txt"), "w") as fh:
             fh.write("\n".join(lines) + "\n")
-        k.pop("_id", None)
     with open(os.path.join(ROOT, "profiles", f"{tag}_ncu_record.txt"), "w") as fh:
         fh.write("\n".join(text) + "\n")
     with open(os.path.join(ROOT, "profiles", "record_kernel_pipes.json"), "w") as fh:
