@@ -363,15 +363,15 @@ def run_gpu(args):
         # call lane of the one p2pt_ctx, keep PCIe busy in both directions; every byte goes host -> device -> host inside the
         # timed region, through the host-pointer C ABI only.
         import queue
-        NB = 8                                   # sub-batches per step (8192 sessions = 131072 records each)
+        NB = env_int("P2PT_BENCH_NB", 8)          # sub-batches per step (8192 sessions = 131072 records each)
         sub_n = n // NB
         sub_streams = max_streams // NB
-        NW = 3                                   # workers (host thread + p2pt_ctx) per direction
+        NW = env_int("P2PT_BENCH_NW", 3)          # worker threads per direction (all on the one context)
         # ONE context per GPU: its call lanes let all six workers be inside host-pointer calls at the same time
         ctxs = [ctx] * (2 * NW)
         # with several calls in flight the overlap comes from the other workers; one large copy per
         # direction per call is what PCIe moves fastest (measured: 48 GB/s vs 41 GB/s in 16 MiB pieces)
-        ctx.set_option("chunk_bytes", 256 << 20)
+        ctx.set_option("chunk_bytes", env_int("P2PT_BENCH_CHUNK_MB", 256) << 20)
 
         def pinned(a):
             return torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory()

@@ -154,11 +154,11 @@ struct CtrRound1 {
     }
     // the same with the four words and round key 0 word 3 read back from the group's slot (P2PT_GCM_PARK)
     template <class Lut, class Keys>
-    static __device__ __forceinline__ void block_parked(const Lut& lut, const Keys& keys, uint32_t slot, uint32_t ctr,
+    static __device__ __forceinline__ void block_parked(const Lut& lut, const Keys& keys, uint32_t slot, uint32_t r1_off, uint32_t ctr,
                                                         uint32_t& o0, uint32_t& o1, uint32_t& o2, uint32_t& o3) {
         uint32_t r3w, q0, q1, q2, q3;
         asm volatile("ld.shared.u32 %0, [%1+12];" : "=r"(r3w) : "r"(slot));
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+336];" : "=r"(q0), "=r"(q1), "=r"(q2), "=r"(q3) : "r"(slot));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q0), "=r"(q1), "=r"(q2), "=r"(q3) : "r"(slot + r1_off));
         const uint32_t s3 = bswap32(ctr) ^ r3w;
         o0 = q0 ^ lut.template look<3, 3>(s3);
         o1 = q1 ^ lut.template look<2, 2>(s3);
@@ -179,9 +179,15 @@ struct CtrRound1 {
 
 // GF(2^128) multiply with the prepared multiplier in shared memory (9 rows of 4 class masks):
 // same arithmetic as gf128_mul in gcm_math.cuh, one LDS.128 per 32x32 product instead of 36 registers.
+// A prepared multiplier in the group's slot: nine rows of classes 0..3 (16 bytes each) and, with hole spacing 6,
+// nine rows of classes 4..5 (8 bytes each) behind them: one LDS.128 (+ one LDS.64) per 32x32 product.
+constexpr uint32_t kGkeyHiOff = 9 * 16;
+constexpr uint32_t kGkeyBytes = kGhashClasses == 4 ? 9 * 16 : 9 * 16 + 80;
 __device__ __forceinline__ uint64_t clmul32_s(uint32_t a, uint32_t key_addr, int row) {
-    uint32_t b[4];
+    uint32_t b[8];
     asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]) : "r"(key_addr + 16u * (uint32_t)row));
+    if (kGhashClasses == 6)
+        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b[4]), "=r"(b[5]) : "r"(key_addr + kGkeyHiOff + 8u * (uint32_t)row));
     return clmul32(a, b);
 }
 __device__ __forceinline__ void clmul64_s(uint32_t lo, uint32_t hi, uint32_t mid, uint32_t key_addr, int r,
@@ -288,7 +294,7 @@ struct GcmArgs {
 };
 
 #ifndef P2PT_GCM_THREADS
-#define P2PT_GCM_THREADS 1024
+#define P2PT_GCM_THREADS (P2PT_GHASH_SPACING == 6 ? 768 : 1024)     // the wider multiplier rows of spacing 6 need the room
 #endif
 #ifndef P2PT_GCM_UNROLL
 #define P2PT_GCM_UNROLL 1
@@ -318,9 +324,11 @@ struct GcmArgs {
 constexpr int kGcmThreads = P2PT_GCM_THREADS;
 constexpr int kGcmUnroll = P2PT_GCM_UNROLL;
 #if P2PT_GCM_PARK
-constexpr uint32_t kGroupSlotBytes = 368;   // 11 x 16 B round keys + 9 x 16 B GHASH multiplier rows + E_K(J0) at 320 +
-                                            // the four round-1 words at 336; 368 = 23 x 16 keeps neighbouring groups'
-                                            // rows in different banks
+// 11 x 16 B round keys, the GHASH multiplier rows, E_K(J0), the four round-1 words; an odd multiple of 16 bytes keeps
+// neighbouring groups' rows in different banks (368 = 23 x 16 with hole spacing 4, 432 = 27 x 16 with spacing 6)
+constexpr uint32_t kSlotEj0 = 176 + kGkeyBytes, kSlotR1 = kSlotEj0 + 16;
+constexpr uint32_t kGroupSlotBytes = ((kSlotR1 + 16) / 16) % 2 ? kSlotR1 + 16 : kSlotR1 + 32;
+static_assert((kGroupSlotBytes / 16) % 2 == 1, "slot stride must be an odd multiple of 16 bytes");
 #else
 constexpr uint32_t kGroupSlotBytes = 336;   // 11 x 16 B round keys + 9 x 16 B GHASH multiplier rows, padded
                                             // so that neighbouring groups' rows fall in different banks
@@ -497,8 +505,13 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
             o[6] = hv.x ^ hv.z; o[7] = hv.y ^ hv.w; o[8] = o[6] ^ o[7];
 #pragma unroll
             for (int q = 0; q < 9; q++) {
-                if ((q % G) == j)
-                    sts128(gkey + 16u * q, o[q] & 0x11111111u, o[q] & 0x22222222u, o[q] & 0x44444444u, o[q] & 0x88888888u);
+                if ((q % G) == j) {
+                    uint32_t cl[8];
+                    ghash_classes(o[q], cl);
+                    sts128(gkey + 16u * q, cl[0], cl[1], cl[2], cl[3]);
+                    if (kGhashClasses == 6)
+                        asm volatile("st.shared.v2.u32 [%0], {%1,%2};" :: "r"(gkey + kGkeyHiOff + 8u * q), "r"(cl[4]), "r"(cl[5]) : "memory");
+                }
             }
         }
         const uint32_t ivw = __ldg(&sk->iv);
@@ -516,9 +529,9 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
         CtrRound1 r1;                                        // counters stay below 2^16: items are capped at 1 MB above
         r1.prepare(lut, rkeys, ivw, n0, n1);
 #if P2PT_GCM_PARK
-        if (j == 0) sts128(slot + 336, r1.c0, r1.c1, r1.c2, r1.c3);
+        if (j == 0) sts128(slot + kSlotR1, r1.c0, r1.c1, r1.c2, r1.c3);
         __syncwarp(gmask);
-#define P2PT_KS(ctr, a0, a1, a2, a3) CtrRound1::block_parked(lut, rkeys, slot, (ctr), a0, a1, a2, a3)
+#define P2PT_KS(ctr, a0, a1, a2, a3) CtrRound1::block_parked(lut, rkeys, slot, kSlotR1, (ctr), a0, a1, a2, a3)
 #else
 #define P2PT_KS(ctr, a0, a1, a2, a3) r1.block(lut, rkeys, (ctr), a0, a1, a2, a3)
 #endif
@@ -617,7 +630,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
                     if (MODE == kPipeOpen && c == 0) { fh0 = y.x; fh1 = y.y; }
                 } else if (is_j0) {
 #if P2PT_GCM_PARK
-                    sts128(slot + 320, k0, k1, k2, k3);      // E_K(J0): read back by every lane for the tag
+                    sts128(slot + kSlotEj0, k0, k1, k2, k3);      // E_K(J0): read back by every lane for the tag
 #else
                     ej0 = make_uint4(k0, k1, k2, k3);
 #endif
@@ -717,7 +730,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
         {
             __syncwarp(gmask);
             uint4 e;                                             // lane 0 of the group stored it in round 0
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+320];" : "=r"(e.x), "=r"(e.y), "=r"(e.z), "=r"(e.w) : "r"(slot) : "memory");
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(e.x), "=r"(e.y), "=r"(e.z), "=r"(e.w) : "r"(slot + kSlotEj0) : "memory");
             tag.x = bswap32(acc.w[3]) ^ e.x; tag.y = bswap32(acc.w[2]) ^ e.y;
             tag.z = bswap32(acc.w[1]) ^ e.z; tag.w = bswap32(acc.w[0]) ^ e.w;
         }

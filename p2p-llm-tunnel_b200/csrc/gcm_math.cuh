@@ -1,7 +1,7 @@
 // gcm_math.cuh -- GF(2^128) arithmetic for GHASH without a carry-less multiply instruction.
 //
 // Everything here is __host__ __device__ so that the exact device arithmetic can be unit-tested on
-// the CPU (tests/test_gcm_math_host.py builds a tiny host harness around this header and compares
+// the CPU (tests/test_host_logic.py builds a tiny host harness around this header and compares
 // it with the oracle's SP 800-38D bitwise multiply).  It is NOT a CPU fallback: the library only
 // calls it from kernels.
 //
@@ -23,9 +23,33 @@ namespace p2pt {
 
 struct U128 { uint32_t w[4]; };   // w[0] = least-significant 32 bits of the BE integer
 
-// Multiplier prepared once per (session, power): the 9 Karatsuba operands of Y, each split into
-// the four "bit i mod 4" classes used by the integer-multiply-with-holes carry-less product.
-struct GhashKey { uint32_t m[9][4]; };
+// The carry-less 32x32 product is built from integer multiplies of operands that keep only every S-th bit
+// ("holes"): a product column then holds a COUNT of partial bits whose lowest bit is the XOR wanted, and the
+// count must not reach the next kept column S bits up.
+//   S = 4: 4 x 4 = 16 multiplies per product, a column of ONE multiply counts at most 8 (< 16), so the four
+//          multiplies that feed an output class have to be combined with XORs (LOP3, ALU pipe).
+//   S = 6: 6 x 6 = 36 multiplies, the six that feed an output class count at most 6+6+5+5+5+5 = 32 (< 64)
+//          TOGETHER, so they are simply accumulated by the multiply-add itself (IMAD.WIDE with a 64-bit addend, FMA
+//          pipe) and no XOR is needed: per product 16 ALU + 36 FMA instructions instead of 24 ALU + 16 FMA.  The
+//          record kernel is bound by the ALU pipe while the FMA pipe idles at 21 %, which is what this trades.
+#ifndef P2PT_GHASH_SPACING
+#define P2PT_GHASH_SPACING 4
+#endif
+constexpr int kGhashClasses = P2PT_GHASH_SPACING;
+static_assert(kGhashClasses == 4 || kGhashClasses == 6, "hole spacing 4 or 6");
+
+// the classes of a 32-bit operand: out[k] = bits of v at positions k, k + S, k + 2 S, ...
+P2PT_HD void ghash_classes(uint32_t v, uint32_t out[kGhashClasses]) {
+    if (kGhashClasses == 4) {
+        out[0] = v & 0x11111111u; out[1] = v & 0x22222222u; out[2] = v & 0x44444444u; out[3] = v & 0x88888888u;
+    } else {
+        out[0] = v & 0x41041041u; out[1] = v & 0x82082082u; out[2] = v & 0x04104104u;
+        out[3 % kGhashClasses] = v & 0x08208208u; out[4 % kGhashClasses] = v & 0x10410410u; out[5 % kGhashClasses] = v & 0x20820820u;
+    }
+}
+
+// Multiplier prepared once per (session, power): the 9 Karatsuba operands of Y, each split into its classes.
+struct GhashKey { uint32_t m[9][kGhashClasses]; };
 
 P2PT_HD void ghash_key_prepare(const U128& y, GhashKey& k) {
     uint32_t o[9];
@@ -33,25 +57,37 @@ P2PT_HD void ghash_key_prepare(const U128& y, GhashKey& k) {
     o[3] = y.w[2]; o[4] = y.w[3]; o[5] = y.w[2] ^ y.w[3];
     o[6] = y.w[0] ^ y.w[2]; o[7] = y.w[1] ^ y.w[3]; o[8] = o[6] ^ o[7];
 #pragma unroll
-    for (int i = 0; i < 9; i++) {
-        k.m[i][0] = o[i] & 0x11111111u;
-        k.m[i][1] = o[i] & 0x22222222u;
-        k.m[i][2] = o[i] & 0x44444444u;
-        k.m[i][3] = o[i] & 0x88888888u;
-    }
+    for (int i = 0; i < 9; i++) ghash_classes(o[i], k.m[i]);
 }
 
-// 32x32 -> 64 carry-less multiply from 16 integer multiplies.  Each operand class keeps every 4th
-// bit, so a product column sums at most 8 partial bits and never carries into the next kept
-// column (4 bits away); the kept column's low bit is the XOR we want.
-P2PT_HD uint64_t clmul32(uint32_t a, const uint32_t b[4]) {
-    const uint32_t a0 = a & 0x11111111u, a1 = a & 0x22222222u, a2 = a & 0x44444444u, a3 = a & 0x88888888u;
-    uint64_t z0 = ((uint64_t)a0 * b[0]) ^ ((uint64_t)a1 * b[3]) ^ ((uint64_t)a2 * b[2]) ^ ((uint64_t)a3 * b[1]);
-    uint64_t z1 = ((uint64_t)a0 * b[1]) ^ ((uint64_t)a1 * b[0]) ^ ((uint64_t)a2 * b[3]) ^ ((uint64_t)a3 * b[2]);
-    uint64_t z2 = ((uint64_t)a0 * b[2]) ^ ((uint64_t)a1 * b[1]) ^ ((uint64_t)a2 * b[0]) ^ ((uint64_t)a3 * b[3]);
-    uint64_t z3 = ((uint64_t)a0 * b[3]) ^ ((uint64_t)a1 * b[2]) ^ ((uint64_t)a2 * b[1]) ^ ((uint64_t)a3 * b[0]);
-    return (z0 & 0x1111111111111111ull) | (z1 & 0x2222222222222222ull) |
-           (z2 & 0x4444444444444444ull) | (z3 & 0x8888888888888888ull);
+// 32x32 -> 64 carry-less multiply, b given as its classes.
+P2PT_HD uint64_t clmul32(uint32_t a, const uint32_t b[kGhashClasses]) {
+    uint32_t ac[kGhashClasses];
+    ghash_classes(a, ac);
+    if (kGhashClasses == 4) {
+        // every operand class keeps every 4th bit: a column of one product sums at most 8 partial bits and never
+        // carries into the next kept column; the four products of an output class are XORed
+        const uint32_t a0 = ac[0], a1 = ac[1], a2 = ac[2], a3 = ac[3 % kGhashClasses];
+        uint64_t z0 = ((uint64_t)a0 * b[0]) ^ ((uint64_t)a1 * b[3 % kGhashClasses]) ^ ((uint64_t)a2 * b[2]) ^ ((uint64_t)a3 * b[1]);
+        uint64_t z1 = ((uint64_t)a0 * b[1]) ^ ((uint64_t)a1 * b[0]) ^ ((uint64_t)a2 * b[3 % kGhashClasses]) ^ ((uint64_t)a3 * b[2]);
+        uint64_t z2 = ((uint64_t)a0 * b[2]) ^ ((uint64_t)a1 * b[1]) ^ ((uint64_t)a2 * b[0]) ^ ((uint64_t)a3 * b[3 % kGhashClasses]);
+        uint64_t z3 = ((uint64_t)a0 * b[3 % kGhashClasses]) ^ ((uint64_t)a1 * b[2]) ^ ((uint64_t)a2 * b[1]) ^ ((uint64_t)a3 * b[0]);
+        return (z0 & 0x1111111111111111ull) | (z1 & 0x2222222222222222ull) |
+               (z2 & 0x4444444444444444ull) | (z3 & 0x8888888888888888ull);
+    } else {
+        // every 6th bit: the six products of output class k (a_i x b_(k-i)) are ADDED - a column counts at most 32
+        // partial bits, six bits wide - and the class's bit of the result is the lowest bit of its column
+        uint64_t r = 0;
+#pragma unroll
+        for (int k = kGhashClasses - 1; k >= 0; k--) {
+            uint64_t z = 0;
+#pragma unroll
+            for (int i = 0; i < kGhashClasses; i++) z += (uint64_t)ac[i] * b[(k - i + kGhashClasses) % kGhashClasses];
+            const uint64_t mk = 0x1041041041041041ull << k;        // bits k, k + 6, ... (< 64)
+            r = (z & mk) | (r & ~mk);                               // one bit-select per 32-bit half
+        }
+        return r;
+    }
 }
 
 // 64x64 -> 128 Karatsuba from three clmul32; operands (lo, hi, lo^hi) and key rows (r, r+1, r+2).

@@ -18,6 +18,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/p2pt.h"
 #include "frame_kernels.cuh"
 #include "gcm_kernels.cuh"
@@ -135,6 +137,14 @@ static int32_t set_err(p2pt_ctx* ctx, int32_t code, const std::string& msg) {
         if (e__ != cudaSuccess)                                                                 \
             return set_err(ctx, P2PT_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__)); \
     } while (0)
+
+// One NVTX range per host-pointer call, named after the entry point: what the reference's `tracing` spans are to
+// its tokio tasks (/root/reference/tunnel/src/main.rs:21-25) these are to a timeline profiler.  nvtx3 is
+// header-only and costs a few nanoseconds when no tool is attached.
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 struct DeviceGuard {
     int prev = -1;
@@ -579,6 +589,7 @@ int32_t p2pt_sessions_load(p2pt_ctx* ctx, uint32_t n, const uint8_t* local_keys1
         return set_err(ctx, P2PT_ERR_ARG, "sessions_load: null key material or n == 0");
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_sessions_load");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
     if (ctx->keys_local) { cudaFree(ctx->keys_local); ctx->keys_local = nullptr; }
@@ -992,6 +1003,7 @@ int32_t p2pt_frame_encode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* types,
             return set_err(ctx, P2PT_ERR_CAPACITY, "frame_encode: output slot smaller than 5 + payload");
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_frame_encode_batch");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
     const size_t pbytes = pay_off[n] - pay_off[0], obytes = out_off[n] - out_off[0];
@@ -1034,6 +1046,7 @@ int32_t p2pt_frame_decode_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, co
     if (!offsets_monotonic(in_off, n)) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: offsets must be non-decreasing");
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_frame_decode_batch");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
     const size_t ibytes = in_off[n] - in_off[0];
@@ -1064,6 +1077,7 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
     if (gathered && (!in || !gathered_off)) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: gather needs in and gathered_off");
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_frame_demux_batch");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
     const uint64_t sbytes = demux_scratch_bytes(n);
@@ -1193,6 +1207,7 @@ static int32_t run_record_call(p2pt_ctx* ctx, const RecordCall& c, const char* w
     if (int32_t r = check_sessions(ctx)) return r;
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_(what);
     Lane* L = lg.lane;
     const size_t ibytes = c.in_off[n] - c.in_off[0], obytes = c.out_off[n] - c.out_off[0];
     IoStage io{ctx, L};
@@ -1358,6 +1373,7 @@ int32_t p2pt_sctp_packetize_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg,
     if (mbytes && !msg) return set_err(ctx, P2PT_ERR_ARG, "sctp_packetize: null msg");
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_sctp_packetize_batch");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
     if (int32_t r = arena_reserve(ctx, L, pad256(mbytes) + 3 * pad256(8 * (n + 1)) + 4 * pad256(4 * n) + 4 * pad256(2 * n) +
@@ -1399,6 +1415,7 @@ int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const 
     if (!offsets_monotonic(in_off, n_pkts)) return set_err(ctx, P2PT_ERR_ARG, "sctp_unpack_reassemble: offsets must be non-decreasing");
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_sctp_unpack_reassemble_batch");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
     const uint64_t n = n_pkts;
@@ -1486,6 +1503,7 @@ int32_t p2pt_sse_scan_batch(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, cons
     if (bytes && !body) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: null body");
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_sse_scan_batch");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
     const uint64_t sb = p2pt_sse_scan_scratch_bytes(k);
@@ -1598,6 +1616,7 @@ int32_t p2pt_dtls_datagram_split_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t*
     if (!offsets_monotonic(dgram_off, n)) return set_err(ctx, P2PT_ERR_ARG, "datagram_split: offsets must be non-decreasing");
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_dtls_datagram_split_batch");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
     const size_t bytes = dgram_off[n] - dgram_off[0];
@@ -1637,6 +1656,7 @@ int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t*
         return set_err(ctx, P2PT_ERR_ARG, "replay_filter: null argument");
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_dtls_replay_filter_batch");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
     const uint64_t sb = p2pt_dtls_replay_filter_scratch_bytes(n);
@@ -1757,6 +1777,7 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
     if (int32_t r = check_sessions(ctx)) return r;
     DeviceGuard dg(ctx->device);
     LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_pipeline_open_demux");
     Lane* L = lg.lane;
     {
         bool taken = false;

@@ -60,7 +60,8 @@ __device__ __forceinline__ uint32_t crc_word(const CrcLut& t, uint32_t crc, uint
 // (a * b) mod P for reflected 32-bit residues: carry-less product (integer-multiply-with-holes,
 // gcm_math.cuh), realigned by one bit, then the upper 32 coefficients are folded with one word step.
 __device__ __forceinline__ uint32_t crc_mulmod(const CrcLut& t, uint32_t a, uint32_t b) {
-    uint32_t bm[4] = {b & 0x11111111u, b & 0x22222222u, b & 0x44444444u, b & 0x88888888u};
+    uint32_t bm[kGhashClasses];
+    ghash_classes(b, bm);
     const uint64_t p = clmul32(a, bm) << 1;
     return crc_word(t, 0u, (uint32_t)p) ^ (uint32_t)(p >> 32);
 }

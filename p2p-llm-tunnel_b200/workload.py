@@ -29,9 +29,10 @@ def fixed_offsets(n, size):
     return (np.arange(n + 1, dtype=np.uint64) * np.uint64(size))
 
 
-def frames_workload(n, payload_len, n_streams=4096, sse=False, seed_shift=0):
+def frames_workload(n, payload_len, n_streams=4096, sse=False, seed_shift=0, out_stride=None):
     """C2 / C4: n RES_BODY frames, payload_len bytes each, stream ids uniform over 1..=n_streams,
-    packed back to back.  Returns dict with the encoder inputs."""
+    packed back to back.  Returns dict with the encoder inputs.  out_stride (C2p: 1216 for 1200-byte
+    payloads) pads every output slot to that many bytes."""
     types = np.full(n, 21, np.uint8)
     sids = (splitmix64(SEED_SID + seed_shift, n) % _M(n_streams)).astype(np.uint32) + np.uint32(1)
     if sse:
@@ -40,7 +41,37 @@ def frames_workload(n, payload_len, n_streams=4096, sse=False, seed_shift=0):
     else:
         payload = rand_bytes(SEED_PAYLOAD + seed_shift, n * payload_len)
     return {"n": n, "types": types, "sids": sids, "payload": payload,
-            "pay_off": fixed_offsets(n, payload_len), "frame_off": fixed_offsets(n, payload_len + 5)}
+            "pay_off": fixed_offsets(n, payload_len), "frame_off": fixed_offsets(n, out_stride or payload_len + 5)}
+
+
+def lifecycle_workload(n_streams, bodies_per_stream, payload_len, corrupt_permille=1, seed_shift=0):
+    """C2x: every stream lives the way proxy.rs:118-153 sees it - one ResHeaders frame (JSON, the stream id inside),
+    `bodies_per_stream` ResBody frames, one ResEnd - and the streams are interleaved at random with each stream's own
+    order kept.  `corrupt_permille` of the frames are then damaged (half truncated below five bytes, half given a tag
+    that is no MessageType); which ones is in `corrupt`.  Ragged payloads (headers ~40 B, bodies payload_len, ends 0)."""
+    per = bodies_per_stream + 2
+    n = n_streams * per
+    # a random interleaving that keeps per-stream order: sort frames by a random key, then number the frames of
+    # each stream in the order they come out
+    key = splitmix64(SEED_SID + 0x200 + seed_shift, n)
+    sids = (np.arange(n, dtype=np.uint64) % _M(n_streams)).astype(np.uint32)[np.argsort(key, kind="stable")] + np.uint32(1)
+    order = np.argsort(sids, kind="stable")
+    pos = np.empty(n, np.int64)
+    pos[order] = np.tile(np.arange(per, dtype=np.int64), n_streams)           # index of the frame inside its stream
+    types = np.where(pos == 0, 20, np.where(pos == per - 1, 22, 21)).astype(np.uint8)
+    hdr = [b'{"stream_id":%d,"status":200,"headers":{}}' % s for s in range(1, n_streams + 1)]
+    hlen = np.array([len(h) for h in hdr], np.int64)
+    lens = np.where(types == 21, payload_len, 0).astype(np.int64)
+    is_h = types == 20
+    lens[is_h] = hlen[sids[is_h].astype(np.int64) - 1]
+    pay_off = np.zeros(n + 1, np.uint64); np.cumsum(lens, out=pay_off[1:])
+    payload = rand_bytes(SEED_PAYLOAD + 0x200 + seed_shift, int(pay_off[-1]))
+    for i in np.flatnonzero(is_h):
+        o = int(pay_off[i]); payload[o:o + int(lens[i])] = np.frombuffer(hdr[int(sids[i]) - 1], np.uint8)
+    frame_off = np.zeros(n + 1, np.uint64); np.cumsum(lens + 5, out=frame_off[1:])
+    corrupt = (splitmix64(SEED_CORRUPT + 0x200 + seed_shift, n) % _M(1000)) < _M(corrupt_permille)
+    return {"n": n, "types": types, "sids": sids, "payload": payload, "pay_off": pay_off, "frame_off": frame_off,
+            "pos": pos, "corrupt": corrupt, "per_stream": per}
 
 
 def sessions_keys(n_sessions, seed_shift=0):

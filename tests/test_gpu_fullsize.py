@@ -60,6 +60,80 @@ def test_c2x_corrupt_frames_are_skipped(ctx):
     assert np.array_equal(r["gathered"].reshape(-1, P), w["payload"].reshape(n, P)[r["perm"]])
 
 
+def test_c2p_padded_slots_keep_what_lies_between_the_frames(ctx):
+    """SURVEY.md 8(d) variant C2p: 1 M x 1200 B frames into 1216-byte slots (16-byte aligned frame starts); the
+    11 bytes of every slot behind its frame keep the caller's contents (frame_encode leaves gaps alone)."""
+    from p2p_llm_tunnel_b200 import workload
+    n, P, stride = 1_000_000, 1200, 1216
+    w = workload.frames_workload(n, P, out_stride=stride)
+    import ctypes as C
+    out = np.full(n * stride, 0x5A, np.uint8)
+    ctx._check(ctx.lib.p2pt_frame_encode_batch(ctx.h, n, w["types"].ctypes.data, w["sids"].ctypes.data, w["payload"].ctypes.data,
+                                               w["pay_off"].ctypes.data, out.ctypes.data, w["frame_off"].ctypes.data))
+    f2 = out.reshape(n, stride)
+    assert np.all(f2[:, 0] == 21) and np.array_equal(f2[:, 1:5].copy().view(">u4").reshape(-1), w["sids"])
+    assert np.array_equal(f2[:, 5:5 + P].reshape(-1), w["payload"]) and np.all(f2[:, 5 + P:] == 0x5A)
+
+
+def test_c2x_stream_lifecycles_with_corrupt_frames(ctx):
+    """SURVEY.md 8(d) variant C2x at full size: 4096 streams x (ResHeaders, 242 x ResBody, ResEnd) interleaved,
+    0.1 % of the frames damaged.  What proxy.rs:109-153 does frame by frame must come out of decode + demux:
+    damaged frames are skipped (warn! + continue), every stream's frames keep their order, the first surviving
+    frame of an undamaged stream is its ResHeaders, the last its ResEnd, and the gathered body is the
+    concatenation of its surviving ResBody payloads."""
+    from p2p_llm_tunnel_b200 import workload
+    S, K, P = 4096, 242, 1200
+    w = workload.lifecycle_workload(S, K, P)
+    n = w["n"]
+    frames, off = ctx.frame_encode(w["types"], w["sids"], w["payload"], w["pay_off"])
+    assert np.array_equal(off, w["frame_off"])
+    frames = frames.copy()
+    bad = np.flatnonzero(w["corrupt"])
+    assert 500 < len(bad) < 1500
+    in_off = off.copy()
+    starts = off[:-1].astype(np.int64)
+    frames[starts[bad[::2]]] = 0xEE                                   # a tag that is no MessageType
+    # truncation below five bytes: the frame keeps its first 3 bytes, the rest of its slot becomes a second,
+    # also undecodable "message" - the batch just has more items
+    cut = bad[1::2]
+    extra = np.sort(starts[cut] + 3).astype(np.uint64)
+    in_off = np.sort(np.concatenate([off, extra]))
+    desc = ctx.frame_decode(frames, in_off)
+    is_extra = np.isin(in_off[:-1], extra)
+    is_cut_head = np.isin(in_off[:-1], starts[cut].astype(np.uint64))
+    lens = (in_off[1:] - in_off[:-1]).astype(np.int64)
+    exp_status = np.zeros(len(desc), np.uint8)
+    exp_status[is_cut_head] = 1                                       # 3 bytes: too short
+    exp_status[is_extra & (lens < 5)] = 1
+    tail = is_extra & (lens >= 5)                                     # the cut-off remainder decodes as whatever its first byte says
+    ok_tags = np.isin(frames[in_off[:-1][tail].astype(np.int64)], (1, 2, 3, 4, 10, 11, 12, 20, 21, 22, 99))
+    exp_status[np.flatnonzero(tail)[~ok_tags]] = 2
+    orig = ~is_extra                                                  # items that are (what is left of) the original frames
+    bad_tag = np.zeros(n, bool); bad_tag[bad[::2]] = True
+    es = exp_status.copy(); es[np.flatnonzero(orig)[bad_tag]] = 2
+    assert np.array_equal(desc["status"], es)
+    r = ctx.frame_demux(desc, frames, max_streams=len(desc))
+    # streams 1..4096 are all there (the remainders of truncated frames may add a few stray ids)
+    sid_of = {int(s): i for i, s in enumerate(r["uniq_sid"])}
+    oidx = np.flatnonzero(orig)                                       # item index of original frame j
+    item_to_frame = np.full(len(desc), -1, np.int64); item_to_frame[oidx] = np.arange(n)
+    good = ~w["corrupt"]
+    for s in (1, 2, 77, 1000, 4095, 4096):
+        k = sid_of[s]
+        items = r["perm"][int(r["csr"][k]):int(r["csr"][k + 1])].astype(np.int64)
+        fr = item_to_frame[items]
+        fr = fr[fr >= 0]                                              # stray remainders carry random ids; ignore any that landed here
+        mine = np.flatnonzero((w["sids"] == s) & good)
+        assert np.array_equal(fr[np.isin(fr, mine)], mine)            # arrival order kept, damaged frames gone
+        if good[w["sids"] == s].all() and len(fr) == len(mine):
+            assert w["types"][fr[0]] == 20 and w["types"][fr[-1]] == 22
+            body = np.concatenate([w["payload"][int(w["pay_off"][j]):int(w["pay_off"][j + 1])] for j in mine if w["types"][j] == 21])
+            got = r["gathered"][int(r["gathered_off"][k]):int(r["gathered_off"][k + 1])]
+            assert np.array_equal(got, body)
+    total_body = int(((w["types"] == 21) & good).sum()) * P
+    assert int(r["gathered_off"][r["k"]]) >= total_body              # + whatever the stray remainders decoded to
+
+
 @pytest.mark.parametrize("n_sessions", [1, 4096])
 def test_c3_one_million_records_seal_open(ctx, n_sessions):
     """configs[2]: 1 M records x 1200 B, fixed keys / injected nonces; seal -> open round trip, sampled
