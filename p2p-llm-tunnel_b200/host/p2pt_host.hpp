@@ -7,11 +7,16 @@
 //       /root/reference/tunnel/src/protocol.rs:86-118, :139-262, limits :9-12
 //   dtls::CryptoGcm::{encrypt, decrypt}
 //       webrtc-dtls 0.10.0 crypto_gcm.rs (un-vendored, /root/reference/tunnel/Cargo.lock:2822-2824)
+//   reader::ProxyReader / reader::ServeReassembler -- the two per-frame reader loops in batched form
+//       /root/reference/tunnel/src/proxy.rs:105-172 (PendingResponses :23-24, StreamEvent :28-37)
+//       /root/reference/tunnel/src/serve.rs:82-156 (pending_requests :65)
 // Every encode / decode / encrypt / decrypt runs on the GPU (batch of one through the batch entry
 // points; encode_batch / decode_batch for real batches).  Nothing here computes on the CPU.
 #pragma once
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <optional>
 #include <stdexcept>
@@ -138,6 +143,174 @@ inline Bytes encode_batch(const Context& c, const std::vector<TunnelMessage>& ms
 }
 
 }  // namespace protocol
+
+// ---- batched reader / dispatcher ------------------------------------------------
+// The reference decodes one frame, takes a mutex, probes a HashMap and pushes one event, per frame.  Here a
+// whole batch is decoded and demultiplexed on the GPU (p2pt_frame_decode_batch + p2pt_frame_demux_batch) and
+// the host walks each stream's frames once, in arrival order: the same per-stream event sequences come out.
+namespace reader {
+
+using protocol::MessageType;
+
+struct StreamEvent {                                           // proxy.rs:28-37
+    enum Kind { Headers, Body, End, Error } kind;
+    Bytes value;                                               // headers JSON / body bytes / error text (lossy UTF-8 is the caller's)
+    bool operator==(const StreamEvent& o) const { return kind == o.kind && value == o.value; }
+};
+
+// The top-level unsigned integer field `key` of a JSON object (RequestHeaders / ResponseHeaders carry the stream
+// id there, protocol.rs:122-136; headers frames are routed by it, not by the frame header: proxy.rs:129,
+// serve.rs:113-118).  Nothing else of the JSON is interpreted here.
+inline std::optional<uint32_t> json_u32_field(const uint8_t* p, size_t n, const char* key) {
+    const size_t klen = std::strlen(key);
+    int depth = 0;
+    for (size_t i = 0; i < n; i++) {
+        const uint8_t ch = p[i];
+        if (ch == '"') {
+            size_t j = i + 1;
+            while (j < n && p[j] != '"') j += (p[j] == '\\') ? 2 : 1;
+            if (j >= n) return std::nullopt;                    // unterminated string: not JSON
+            if (depth == 1 && j - i - 1 == klen && std::memcmp(p + i + 1, key, klen) == 0) {
+                size_t q = j + 1;
+                while (q < n && (p[q] == ' ' || p[q] == '\t' || p[q] == '\n' || p[q] == '\r')) q++;
+                if (q < n && p[q] == ':') {
+                    q++;
+                    while (q < n && (p[q] == ' ' || p[q] == '\t' || p[q] == '\n' || p[q] == '\r')) q++;
+                    uint64_t v = 0; size_t digits = 0;
+                    while (q < n && p[q] >= '0' && p[q] <= '9' && digits < 11) { v = v * 10 + (p[q] - '0'); q++; digits++; }
+                    if (digits && v <= 0xffffffffull) return (uint32_t)v;
+                    return std::nullopt;
+                }
+            }
+            i = j;
+        } else if (ch == '{' || ch == '[') depth++;
+        else if (ch == '}' || ch == ']') depth--;
+    }
+    return std::nullopt;
+}
+inline bool json_looks_complete(const uint8_t* p, size_t n) {   // a whole object: what serde_json::from_slice needs at least
+    int depth = 0; bool any = false;
+    for (size_t i = 0; i < n; i++) {
+        if (p[i] == '"') { size_t j = i + 1; while (j < n && p[j] != '"') j += (p[j] == '\\') ? 2 : 1; if (j >= n) return false; i = j; }
+        else if (p[i] == '{') { depth++; any = true; }
+        else if (p[i] == '}') depth--;
+    }
+    return any && depth == 0;
+}
+
+// one decoded + demultiplexed batch, walked per target stream in arrival order
+struct Routed { uint64_t idx; uint8_t type; const uint8_t* data; size_t len; };
+
+inline std::map<int64_t, std::vector<Routed>> decode_demux(const Context& c, const std::vector<Bytes>& frames, uint8_t header_type,
+                                                           Bytes& buf, Bytes& gathered, size_t& decode_failures) {
+    const size_t n = frames.size();
+    std::vector<uint64_t> off(n + 1, 0);
+    for (size_t i = 0; i < n; i++) off[i + 1] = off[i] + frames[i].size();
+    buf.assign(off[n] + 1, 0);
+    for (size_t i = 0; i < n; i++) std::memcpy(buf.data() + off[i], frames[i].data(), frames[i].size());
+    std::vector<p2pt_desc> desc(n);
+    c.check(p2pt_frame_decode_batch(c.get(), n, buf.data(), off.data(), desc.data()));
+    for (const auto& d : desc) decode_failures += d.status != P2PT_ST_OK;          // warn! + continue
+    std::vector<uint32_t> uniq(n + 1), perm(n);
+    std::vector<uint64_t> csr(n + 1), goff(n + 1);
+    gathered.assign(off[n] + 1, 0);
+    uint32_t k = 0;
+    c.check(p2pt_frame_demux_batch(c.get(), n, desc.data(), nullptr, buf.data(), off[n], (uint32_t)n, uniq.data(), nullptr,
+                                   csr.data(), perm.data(), &k, gathered.data(), off[n], goff.data()));
+    std::map<int64_t, std::vector<Routed>> out;
+    for (uint32_t s = 0; s < k; s++) {
+        uint64_t cursor = goff[s];
+        for (uint64_t q = csr[s]; q < csr[s + 1]; q++) {
+            const p2pt_desc& d = desc[perm[q]];
+            Routed r{perm[q], d.msg_type, nullptr, d.pay_len};
+            if (d.msg_type == 11 || d.msg_type == 21) { r.data = gathered.data() + cursor; cursor += d.pay_len; }   // body: slice of the stream's gathered buffer
+            else r.data = buf.data() + d.pay_off;
+            int64_t target = uniq[s];
+            if (d.msg_type == header_type) {
+                auto sid = json_looks_complete(r.data, r.len) ? json_u32_field(r.data, r.len, "stream_id") : std::nullopt;
+                target = sid ? (int64_t)*sid : -1;               // unparsable headers
+            }
+            out[target].push_back(r);
+        }
+    }
+    for (auto& kv : out) std::sort(kv.second.begin(), kv.second.end(), [](const Routed& a, const Routed& b) { return a.idx < b.idx; });
+    return out;
+}
+
+// Consumer side: routes RES_* frames to per-stream event queues (proxy.rs:105-172).
+class ProxyReader {
+public:
+    explicit ProxyReader(const Context& c) : c_(c) {}
+    std::map<uint32_t, std::vector<StreamEvent>> pending, closed;   // pending = the mpsc senders; closed = finished streams' queues
+    size_t pongs_to_send = 0, decode_failures = 0;
+    void register_stream(uint32_t sid) { pending[sid]; }            // proxy.rs:266-270 pending.insert(stream_id, event_tx)
+    void feed(const std::vector<Bytes>& frames) {
+        if (frames.empty()) return;
+        Bytes buf, gathered;
+        auto per = decode_demux(c_, frames, (uint8_t)MessageType::ResHeaders, buf, gathered, decode_failures);
+        for (auto& kv : per) {
+            for (const Routed& r : kv.second) {
+                const auto t = (MessageType)r.type;
+                if (t == MessageType::Ping) { pongs_to_send++; continue; }                       // proxy.rs:154-162
+                if (kv.first < 0) continue;                                                       // failed to parse response headers
+                const uint32_t sid = (uint32_t)kv.first;
+                auto it = pending.find(sid);
+                if (it == pending.end()) continue;                                                // unknown stream: silently dropped (:135)
+                const Bytes v(r.data, r.data + r.len);
+                if (t == MessageType::ResHeaders) it->second.push_back({StreamEvent::Headers, v});
+                else if (t == MessageType::ResBody) it->second.push_back({StreamEvent::Body, v});
+                else if (t == MessageType::ResEnd || t == MessageType::Error) {                   // remove + terminal event (:139-153)
+                    it->second.push_back({t == MessageType::ResEnd ? StreamEvent::End : StreamEvent::Error, t == MessageType::ResEnd ? Bytes() : v});
+                    closed[sid] = std::move(it->second);
+                    pending.erase(it);
+                }
+                // Pong and everything else: ignored (:163-169)
+            }
+        }
+    }
+private:
+    const Context& c_;
+};
+
+// Provider side: REQ_HEADERS / REQ_BODY / REQ_END -> completed requests (serve.rs:82-156).
+class ServeReassembler {
+public:
+    struct Request { std::string headers_json; Bytes body; };
+    explicit ServeReassembler(const Context& c) : c_(c) {}
+    std::map<uint32_t, Request> pending_requests;                   // serve.rs:65
+    size_t pongs_to_send = 0, decode_failures = 0;
+    // the requests completed by this batch, in REQ_END arrival order
+    std::vector<Request> feed(const std::vector<Bytes>& frames) {
+        std::vector<std::pair<uint64_t, Request>> done;
+        if (frames.empty()) return {};
+        Bytes buf, gathered;
+        auto per = decode_demux(c_, frames, (uint8_t)MessageType::ReqHeaders, buf, gathered, decode_failures);
+        for (auto& kv : per) {
+            for (const Routed& r : kv.second) {
+                const auto t = (MessageType)r.type;
+                if (t == MessageType::Ping) { pongs_to_send++; continue; }
+                if (t == MessageType::ReqHeaders) {
+                    if (kv.first < 0) throw Error("invalid request headers JSON");               // serde `?` ends run_serve (serve.rs:113)
+                    pending_requests[(uint32_t)kv.first] = Request{std::string(r.data, r.data + r.len), {}};   // :112-119 insert
+                    continue;
+                }
+                if (kv.first < 0) continue;
+                auto it = pending_requests.find((uint32_t)kv.first);
+                if (it == pending_requests.end()) continue;                                       // body / end for an unknown request
+                if (t == MessageType::ReqBody) it->second.body.insert(it->second.body.end(), r.data, r.data + r.len);   // :120-124 extend_from_slice
+                else if (t == MessageType::ReqEnd) { done.push_back({r.idx, std::move(it->second)}); pending_requests.erase(it); }   // :125-139
+            }
+        }
+        std::sort(done.begin(), done.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+        std::vector<Request> out;
+        for (auto& d : done) out.push_back(std::move(d.second));
+        return out;
+    }
+private:
+    const Context& c_;
+};
+
+}  // namespace reader
 
 namespace dtls {
 

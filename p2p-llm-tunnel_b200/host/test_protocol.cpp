@@ -133,6 +133,119 @@ TEST(test_crypto_gcm_known_record) {
     CHECK(noroom);
 }
 
+// --- the two reader loops, batched (reader::ProxyReader = proxy.rs:109-170, reader::ServeReassembler = serve.rs:82-156),
+//     against the same loops written frame by frame the way the reference runs them ---
+static Bytes F(uint8_t t, uint32_t sid, const Bytes& p = {}) {
+    Bytes f = {t, (uint8_t)(sid >> 24), (uint8_t)(sid >> 16), (uint8_t)(sid >> 8), (uint8_t)sid};
+    f.insert(f.end(), p.begin(), p.end());
+    return f;
+}
+static uint32_t lcg(uint32_t& s) { s = s * 1664525u + 1013904223u; return s >> 8; }
+static bool valid_tag(uint8_t b) { return from_u8(b).has_value(); }
+
+TEST(test_proxy_reader_matches_the_per_frame_loop) {
+    using namespace p2pt_host::reader;
+    uint32_t seed = 5;
+    std::vector<std::vector<Bytes>> streams;
+    for (uint32_t sid = 1; sid <= 30; sid++) {
+        std::vector<Bytes> seq;
+        seq.push_back(F(20, sid, B("{\"stream_id\":" + std::to_string(sid) + ",\"status\":200,\"headers\":{\"stream_id\":\"7\"}}")));
+        const int nb = (int)(lcg(seed) % 9);
+        for (int b = 0; b < nb; b++) {
+            Bytes body(lcg(seed) % 300);
+            for (auto& x : body) x = (uint8_t)lcg(seed);
+            seq.push_back(F(21, sid, body));
+        }
+        seq.push_back(sid % 5 ? F(22, sid) : F(99, sid, B("upstream timeout")));
+        if (sid % 7 == 0) seq.push_back(F(21, sid, B("after the end")));            // dropped: stream already removed
+        streams.push_back(seq);
+    }
+    std::vector<Bytes> inter;                                                       // interleave, each stream's own order kept
+    std::vector<size_t> at(streams.size(), 0);
+    for (size_t left = 1; left;) {
+        left = 0;
+        const size_t j = lcg(seed) % streams.size();
+        if (at[j] < streams[j].size()) inter.push_back(streams[j][at[j]++]);
+        for (size_t q = 0; q < streams.size(); q++) left += at[q] < streams[q].size();
+    }
+    const std::vector<Bytes> extra = {F(3, 0), Bytes{250, 0, 0, 0, 1}, Bytes{0x15, 0}, F(4, 0), F(21, 9999, B("unknown stream")),
+                                      F(20, 3, B("{not json")), F(20, 77, B("{\"stream_id\":2,\"status\":404,\"headers\":{}}"))};
+    inter.insert(inter.begin() + 10, extra.begin(), extra.end());
+    // per-frame loop (proxy.rs:109-170)
+    std::map<uint32_t, std::vector<StreamEvent>> pending, closed;
+    size_t pongs = 0, fails = 0;
+    for (uint32_t s = 1; s <= 30; s++) if (s != 13) pending[s];
+    for (const Bytes& f : inter) {
+        if (f.size() < 5 || !valid_tag(f[0])) { fails++; continue; }
+        const uint8_t t = f[0];
+        uint32_t sid = ((uint32_t)f[1] << 24) | ((uint32_t)f[2] << 16) | ((uint32_t)f[3] << 8) | f[4];
+        const Bytes p(f.begin() + 5, f.end());
+        if (t == 20) {
+            if (!json_looks_complete(p.data(), p.size())) continue;
+            auto js = json_u32_field(p.data(), p.size(), "stream_id");
+            if (!js) continue;
+            auto it = pending.find(*js);
+            if (it != pending.end()) it->second.push_back({StreamEvent::Headers, p});
+        } else if (t == 21) { auto it = pending.find(sid); if (it != pending.end()) it->second.push_back({StreamEvent::Body, p}); }
+        else if (t == 22 || t == 99) {
+            auto it = pending.find(sid);
+            if (it != pending.end()) { it->second.push_back({t == 22 ? StreamEvent::End : StreamEvent::Error, t == 22 ? Bytes() : p}); closed[sid] = it->second; pending.erase(it); }
+        } else if (t == 3) pongs++;
+    }
+    ProxyReader rd(c);
+    for (uint32_t s = 1; s <= 30; s++) if (s != 13) rd.register_stream(s);
+    const size_t cut = inter.size() / 2;
+    rd.feed(std::vector<Bytes>(inter.begin(), inter.begin() + (ptrdiff_t)cut));     // two batches: state carries over
+    rd.feed(std::vector<Bytes>(inter.begin() + (ptrdiff_t)cut, inter.end()));
+    CHECK(rd.pongs_to_send == pongs); CHECK(pongs == 1); CHECK(rd.decode_failures == fails); CHECK(fails == 2);
+    CHECK(rd.pending == pending); CHECK(rd.closed == closed);
+    CHECK(closed.size() >= 28);
+}
+
+TEST(test_serve_reassembler_matches_the_per_frame_loop) {
+    using namespace p2pt_host::reader;
+    uint32_t seed = 6;
+    std::vector<std::vector<Bytes>> streams;
+    std::map<uint32_t, Bytes> bodies;
+    for (uint32_t sid = 1; sid <= 20; sid++) {
+        Bytes body(sid == 3 ? 2 * MAX_BODY_CHUNK + 777 : lcg(seed) % 2000);
+        for (auto& x : body) x = (uint8_t)lcg(seed);
+        bodies[sid] = body;
+        std::vector<Bytes> seq;
+        seq.push_back(F(10, sid, B("{\"stream_id\":" + std::to_string(sid) + ",\"method\":\"POST\",\"path\":\"/v1/x\",\"headers\":{}}")));
+        for (const auto& m : chunk_body(sid, body, false)) seq.push_back(F(11, sid, m.payload));
+        if (sid != 9) seq.push_back(F(12, sid));                                    // stream 9 stays pending
+        streams.push_back(seq);
+    }
+    std::vector<Bytes> inter;
+    std::vector<size_t> at(streams.size(), 0);
+    for (size_t left = 1; left;) {
+        left = 0;
+        const size_t j = lcg(seed) % streams.size();
+        if (at[j] < streams[j].size()) inter.push_back(streams[j][at[j]++]);
+        for (size_t q = 0; q < streams.size(); q++) left += at[q] < streams[q].size();
+    }
+    const std::vector<Bytes> extra = {F(11, 555, B("body for an unknown request")), F(3, 0), F(12, 556), Bytes{0, 1, 2}};
+    inter.insert(inter.begin() + 5, extra.begin(), extra.end());
+    std::vector<uint32_t> end_order;                                                // REQ_END arrival order
+    for (const Bytes& f : inter) if (f.size() >= 5 && f[0] == 12) { uint32_t sid = ((uint32_t)f[3] << 8) | f[4]; if (sid <= 20) end_order.push_back(sid); }
+    ServeReassembler rs(c);
+    std::vector<ServeReassembler::Request> done;
+    const size_t cut = inter.size() / 3;
+    for (int part = 0; part < 3; part++) {
+        auto a = inter.begin() + (ptrdiff_t)(part * cut), b = part == 2 ? inter.end() : inter.begin() + (ptrdiff_t)((part + 1) * cut);
+        for (auto& r : rs.feed(std::vector<Bytes>(a, b))) done.push_back(std::move(r));
+    }
+    CHECK(rs.pongs_to_send == 1); CHECK(rs.decode_failures == 1);
+    CHECK(done.size() == end_order.size()); CHECK(done.size() == 19);
+    for (size_t i = 0; i < done.size() && i < end_order.size(); i++) {
+        auto sid = json_u32_field((const uint8_t*)done[i].headers_json.data(), done[i].headers_json.size(), "stream_id");
+        CHECK(sid && *sid == end_order[i]);
+        CHECK(done[i].body == bodies[end_order[i]]);
+    }
+    CHECK(rs.pending_requests.size() == 1 && rs.pending_requests.count(9) == 1);
+}
+
 int main() {
     try {
         Context c(0);
