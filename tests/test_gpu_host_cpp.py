@@ -1,5 +1,6 @@
 """The C++ host mirror (p2p-llm-tunnel_b200/host/p2pt_host.hpp): the reference's codec unit tests
-(/root/reference/tunnel/src/protocol.rs:265-460) restated in C++ run against it on the GPU; on a box
+(/root/reference/tunnel/src/protocol.rs:265-460) restated in C++, and the two batched reader loops against their
+per-frame forms (proxy.rs:109-170, serve.rs:82-156), run against it on the GPU; on a box
 without a GPU the same binary must fail loudly instead of computing anything on the CPU."""
 import subprocess
 
@@ -11,8 +12,9 @@ def test_reference_codec_tests_in_cpp(built):
     r = subprocess.run([built.HOST_TEST], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     print(r.stdout)
     assert r.returncode == 0, r.stdout
-    assert "20 tests, 0 failed checks" in r.stdout
-    for name in ("test_roundtrip_res_body", "test_decode_unknown_type", "test_large_payload", "test_crypto_gcm_known_record"):
+    assert "22 tests, 0 failed checks" in r.stdout
+    for name in ("test_roundtrip_res_body", "test_decode_unknown_type", "test_large_payload", "test_crypto_gcm_known_record",
+                 "test_proxy_reader_matches_the_per_frame_loop", "test_serve_reassembler_matches_the_per_frame_loop"):
         assert f"ok   {name}" in r.stdout
 
 
