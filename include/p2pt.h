@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define P2PT_ABI_VERSION 1
+#define P2PT_ABI_VERSION 2
 
 /* whole-call return codes */
 #define P2PT_OK            0
@@ -219,14 +219,18 @@ int32_t p2pt_sctp_packetize_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg,
                                   uint8_t* out, uint64_t out_cap, uint64_t* pkt_off, uint64_t pkt_cap,
                                   uint64_t* n_pkts_out);
 /* packets (each after `headroom` bytes, 13 when they come out of p2pt_dtls_gcm_open_batch) -> CRC check,
- * chunk parse, and reassembly: fragments are ordered by (session, TSN) (TSNs must not wrap inside a
- * batch); of several packets with the same (session, TSN) - retransmissions - only the first to arrive
+ * chunk parse, and reassembly: fragments are ordered by (session, TSN).  TSNs are serial numbers modulo 2^32
+ * whose start the PEER chooses, so a message may straddle 0xFFFFFFFF -> 0: give tsn_base (n_pkts entries, the
+ * cumulative TSN ack point of each packet's association - what an SCTP stack always has at hand) and fragments
+ * are ordered by their distance from it, like webrtc-sctp's sna32 comparisons; with tsn_base == NULL raw TSNs
+ * are compared and must not wrap inside a batch.  Of several packets with the same (session, TSN) - retransmissions - only the first to arrive
  * counts, as in webrtc-sctp's reassembly queue; messages = runs from a B to an E fragment, their payloads
  * concatenated into msg with msg_off[n_msgs + 1] -- exactly the (buffer, offsets) input of
  * p2pt_frame_decode_batch.  msg_first[m] = packet index of message m's first fragment (its info gives
  * stream / ssn / ppid); msg_status[m] = OK or SCTP_INCOMPLETE.  info (n entries) is always filled. */
 int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const uint8_t* in, const uint64_t* in_off,
-                                          uint32_t headroom, const uint32_t* session, p2pt_sctp_chunk* info,
+                                          uint32_t headroom, const uint32_t* session, const uint32_t* tsn_base,
+                                          p2pt_sctp_chunk* info,
                                           uint32_t max_msgs, uint8_t* msg, uint64_t msg_cap, uint64_t* msg_off,
                                           uint32_t* msg_first, uint8_t* msg_status, uint32_t* n_msgs_out);
 
@@ -308,7 +312,8 @@ int32_t p2pt_sctp_packetize_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_
                                          uint8_t* out, const uint64_t* out_msg_off, const uint64_t* pkt_first,
                                          uint64_t* pkt_off, void* stream);
 int32_t p2pt_sctp_unpack_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const uint8_t* in, const uint64_t* in_off,
-                                      uint32_t headroom, p2pt_sctp_chunk* info, p2pt_desc* desc, void* stream);
+                                      uint32_t headroom, const uint32_t* tsn_base, p2pt_sctp_chunk* info, p2pt_desc* desc,
+                                      void* stream);
 uint64_t p2pt_sctp_reassemble_scratch_bytes(uint64_t n_pkts);
 int32_t p2pt_sctp_reassemble_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const p2pt_sctp_chunk* info,
                                           const p2pt_desc* desc, const uint32_t* session, const uint8_t* in,

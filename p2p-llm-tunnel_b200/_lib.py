@@ -47,9 +47,9 @@ SIGNATURES = {
     "p2pt_sctp_fragments": (_u64, [_u64]),
     "p2pt_sctp_packets_bytes": (_u64, [_u64]),
     "p2pt_sctp_packetize_batch": (_i32, [_vp, _u64] + [_vp] * 11 + [_vp, _u64, _vp, _u64, _vp]),
-    "p2pt_sctp_unpack_reassemble_batch": (_i32, [_vp, _u64, _vp, _vp, _u32, _vp, _vp, _u32, _vp, _u64, _vp, _vp, _vp, _vp]),
+    "p2pt_sctp_unpack_reassemble_batch": (_i32, [_vp, _u64, _vp, _vp, _u32, _vp, _vp, _vp, _u32, _vp, _u64, _vp, _vp, _vp, _vp]),
     "p2pt_sctp_packetize_batch_device": (_i32, [_vp, _u64] + [_vp] * 11 + [_vp, _vp, _vp, _vp, _vp]),
-    "p2pt_sctp_unpack_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u32, _vp, _vp, _vp]),
+    "p2pt_sctp_unpack_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u32, _vp, _vp, _vp, _vp]),
     "p2pt_sctp_reassemble_scratch_bytes": (_u64, [_u64]),
     "p2pt_sctp_reassemble_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _u32, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_dtls_datagram_split_batch": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
@@ -348,11 +348,13 @@ class Context:
         assert got.value == npk
         return out[:cap], pkt_off
 
-    def sctp_unpack_reassemble(self, buf, in_off, headroom=0, session=None, max_msgs=None, msg_cap=None):
+    def sctp_unpack_reassemble(self, buf, in_off, headroom=0, session=None, max_msgs=None, msg_cap=None, tsn_base=None):
         buf = _as(buf, np.uint8); in_off = _as(in_off, np.uint64)
         n = len(in_off) - 1
         if session is not None:
             session = _as(session, np.uint32)
+        if tsn_base is not None:
+            tsn_base = _as(np.broadcast_to(np.asarray(tsn_base, np.uint32), (n,)), np.uint32)
         max_msgs = max(n, 1) if max_msgs is None else max_msgs
         msg_cap = max(int(buf.size), 1) if msg_cap is None else msg_cap
         info = np.zeros(n, SCTP_CHUNK_DTYPE)
@@ -360,7 +362,7 @@ class Context:
         first = np.zeros(max_msgs + 1, np.uint32); status = np.zeros(max_msgs + 1, np.uint8)
         nm = _u32(0)
         self._check(self.lib.p2pt_sctp_unpack_reassemble_batch(
-            self.h, n, buf.ctypes.data, in_off.ctypes.data, headroom, _ptr(session), info.ctypes.data, max_msgs,
+            self.h, n, buf.ctypes.data, in_off.ctypes.data, headroom, _ptr(session), _ptr(tsn_base), info.ctypes.data, max_msgs,
             msg.ctypes.data, msg_cap, msg_off.ctypes.data, first.ctypes.data, status.ctypes.data, C.addressof(nm)))
         m = nm.value
         return {"info": info, "n_msgs": m, "msg_off": msg_off[:m + 1].copy(), "msg": msg[:int(msg_off[m])].copy(),

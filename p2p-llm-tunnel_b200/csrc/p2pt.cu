@@ -780,13 +780,15 @@ int32_t p2pt_sctp_packetize_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_
 }
 
 int32_t p2pt_sctp_unpack_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const uint8_t* in, const uint64_t* in_off,
-                                      uint32_t headroom, p2pt_sctp_chunk* info, p2pt_desc* desc, void* stream) {
+                                      uint32_t headroom, const uint32_t* tsn_base, p2pt_sctp_chunk* info, p2pt_desc* desc,
+                                      void* stream) {
     if (!ctx) return P2PT_ERR_ARG;
     if (n_pkts == 0) return P2PT_OK;
     if (!in || !in_off || !info || !desc) return set_err(ctx, P2PT_ERR_ARG, "sctp_unpack: null argument");
     DeviceGuard dg(ctx->device);
     SctpUnpackArgs a;
     a.n = n_pkts; a.in = in; a.in_off = (const u64*)in_off; a.headroom = headroom; a.info = info; a.desc = desc;
+    a.tsn_base = tsn_base;
     const uint32_t smem = sctp_smem_bytes(ctx->lut_slack);
     sctp_unpack_kernel<<<grid_for(ctx, n_pkts, kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
     count_launch(ctx);
@@ -1405,7 +1407,7 @@ int32_t p2pt_sctp_packetize_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* msg,
 }
 
 int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const uint8_t* in, const uint64_t* in_off,
-                                          uint32_t headroom, const uint32_t* session, p2pt_sctp_chunk* info,
+                                          uint32_t headroom, const uint32_t* session, const uint32_t* tsn_base, p2pt_sctp_chunk* info,
                                           uint32_t max_msgs, uint8_t* msg, uint64_t msg_cap, uint64_t* msg_off,
                                           uint32_t* msg_first, uint8_t* msg_status, uint32_t* n_msgs_out) {
     if (!ctx) return P2PT_ERR_ARG;
@@ -1421,12 +1423,13 @@ int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const 
     const uint64_t n = n_pkts;
     const size_t ibytes = in_off[n] - in_off[0];
     const uint64_t sbytes = p2pt_sctp_reassemble_scratch_bytes(n);
-    if (int32_t r = arena_reserve(ctx, L, pad256(ibytes) + pad256(8 * (n + 1)) + pad256(4 * n) + pad256(16 * n) + pad256(24 * n) +
+    if (int32_t r = arena_reserve(ctx, L, pad256(ibytes) + pad256(8 * (n + 1)) + 2 * pad256(4 * n) + pad256(16 * n) + pad256(24 * n) +
                                            pad256(msg_cap) + pad256(8 * ((size_t)max_msgs + 1)) + pad256(4 * (size_t)max_msgs) +
                                            pad256(max_msgs) + 256 + pad256(sbytes) + 16384)) return r;
     uint8_t* d_in = arena_take<uint8_t>(L, ibytes + 1);
     uint64_t* d_ioff = arena_take<uint64_t>(L, n + 1);
     uint32_t* d_sess = arena_take<uint32_t>(L, n);
+    uint32_t* d_base = arena_take<uint32_t>(L, n);
     p2pt_sctp_chunk* d_info = arena_take<p2pt_sctp_chunk>(L, n);
     p2pt_desc* d_desc = arena_take<p2pt_desc>(L, n);
     uint8_t* d_msg = arena_take<uint8_t>(L, msg_cap + 1);
@@ -1438,7 +1441,9 @@ int32_t p2pt_sctp_unpack_reassemble_batch(p2pt_ctx* ctx, uint64_t n_pkts, const 
     CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in + in_off[0], ibytes, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(d_ioff, in_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
     if (session) CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, st));
-    if (int32_t r = p2pt_sctp_unpack_batch_device(ctx, n, d_in - in_off[0], d_ioff, headroom, d_info, d_desc, st)) return r;
+    if (tsn_base) CUDA_TRY(ctx, cudaMemcpyAsync(d_base, tsn_base, 4 * n, cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_sctp_unpack_batch_device(ctx, n, d_in - in_off[0], d_ioff, headroom, tsn_base ? d_base : nullptr, d_info,
+                                                  d_desc, st)) return r;
     if (int32_t r = p2pt_sctp_reassemble_batch_device(ctx, n, d_info, d_desc, session ? d_sess : nullptr, d_in - in_off[0],
                                                       max_msgs, d_msg, msg_cap, d_moff, d_mfirst, d_mstat, d_nm,
                                                       d_scratch, sbytes, st)) return r;

@@ -246,6 +246,7 @@ struct SctpUnpackArgs {
     u64 n;                                   // packets
     const uint8_t* in; const u64* in_off; uint32_t headroom;
     p2pt_sctp_chunk* info; p2pt_desc* desc;
+    const uint32_t* tsn_base;                // nullable: per packet, the cumulative TSN ack point of its association
 };
 
 __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_unpack_kernel(const SctpUnpackArgs a) {
@@ -295,9 +296,12 @@ __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_unpack_kernel(const S
             c.tsn = tsn; c.stream_id = (uint16_t)sid; c.ssn = (uint16_t)ssn; c.ppid = pp;
             c.flags = (uint8_t)flags; c.status = (uint8_t)st; c.pad[0] = c.pad[1] = 0;
             a.info[i] = c;
-            // a descriptor p2pt_frame_demux_batch can order: key = TSN, "body" type so the gather takes it
+            // a descriptor p2pt_frame_demux_batch can order: key = TSN, "body" type so the gather takes it.  TSNs are
+            // serial numbers (RFC 4960 1.6: arithmetic modulo 2^32) and the peer picks where they start, so a message
+            // may straddle 0xFFFFFFFF -> 0: with tsn_base the key is the distance from the association's cumulative
+            // ack point, which orders any window of fewer than 2^32 TSNs correctly (webrtc-sctp compares with sna32)
             p2pt_desc d;
-            d.pay_off = io + a.headroom + 28; d.pay_len = plen_pay; d.stream_id = tsn;
+            d.pay_off = io + a.headroom + 28; d.pay_len = plen_pay; d.stream_id = a.tsn_base ? tsn - __ldg(a.tsn_base + i) : tsn;
             d.msg_type = 21; d.status = (uint8_t)st;
             for (int q = 0; q < 6; q++) d.pad[q] = 0;
             if (st != P2PT_ST_OK) { d.pay_off = io; d.pay_len = 0; }

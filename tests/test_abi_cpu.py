@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol(built):
     for s in declared_symbols():
         assert hasattr(lib, s), f"{s} declared in include/p2pt.h but not exported"
     lib.p2pt_abi_version.restype = C.c_int32
-    assert lib.p2pt_abi_version() == 1
+    assert lib.p2pt_abi_version() == 2
 
 
 def test_python_binding_covers_every_symbol(built):

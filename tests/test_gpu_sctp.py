@@ -101,6 +101,38 @@ def test_retransmitted_packets_are_dropped(ctx):
     assert sorted(first_b.values()) == sorted(int(x) for x in r["msg_first"])
 
 
+def test_tsn_wrap_around_inside_a_batch(ctx):
+    """TSNs are serial numbers modulo 2^32 and the PEER picks where they start: messages whose fragments straddle
+    0xFFFFFFFF -> 0 must reassemble like any other when the caller gives each packet's cumulative-ack base
+    (webrtc-sctp orders with sna32).  Two sessions, one wrapping, shuffled arrival, a few retransmissions."""
+    rng = np.random.default_rng(35)
+    starts = [0xFFFFFFFF - 6, 123456]                             # session 0 wraps after seven fragments: inside its 7th message
+    per_sess = [_msgs(rng, 12, 100, 6000) for _ in starts]
+    pkts, sess, base = [], [], []
+    for s, msgs in enumerate(per_sess):
+        lens = np.array([len(m) for m in msgs])
+        frags = np.maximum(1, -(-lens // 1200))
+        tsn0 = (starts[s] + np.concatenate([[0], np.cumsum(frags)[:-1]])) & 0xFFFFFFFF
+        pk, off = ob.sctp_packetize(msgs, 10 + s, 20 + s, 99 + s, 1, np.arange(len(msgs)), 53, tsn0)
+        for i in range(len(off) - 1):
+            pkts.append(pk[int(off[i]):int(off[i + 1])].tobytes()); sess.append(s); base.append((starts[s] - 1) & 0xFFFFFFFF)
+    assert sum(1 for p in pkts[:len(pkts) // 2] if int.from_bytes(p[16:20], "big") < 1000) > 0      # the wrap really happens
+    dup = rng.choice(len(pkts), 6, replace=False)
+    pkts += [pkts[i] for i in dup]; sess += [sess[i] for i in dup]; base += [base[i] for i in dup]
+    order = rng.permutation(len(pkts))
+    pkts = [pkts[i] for i in order]; sess = np.array(sess, np.uint32)[order]; base = np.array(base, np.uint32)[order]
+    buf, off = _pack(pkts)
+    r = ctx.sctp_unpack_reassemble(buf, off, session=sess, tsn_base=base)
+    assert not r["info"]["status"].any() and not r["msg_status"].any()
+    flat = [m for msgs in per_sess for m in msgs]
+    assert r["n_msgs"] == len(flat)
+    for i, m in enumerate(flat):
+        assert r["msg"][int(r["msg_off"][i]):int(r["msg_off"][i + 1])].tobytes() == m, i
+    # without the base the wrapping session's first message is cut in two: the documented limit of raw ordering
+    r2 = ctx.sctp_unpack_reassemble(buf, off, session=sess)
+    assert (r2["msg_status"] == 9).any()
+
+
 def test_unpack_flags_bad_packets_and_incomplete_messages(ctx):
     rng = np.random.default_rng(33)
     msgs = [rng.integers(0, 256, 3000, dtype=np.uint8).tobytes() for _ in range(6)]     # 3 fragments each

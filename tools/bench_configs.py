@@ -130,7 +130,7 @@ def sctp_config(n, L):
     pk = lambda: ctx.call("p2pt_sctp_packetize_batch_device", n, d_msg, d_moff, z16, z16, v32, one16, ssn, pp, tsn, None, None,
                           out, omoff, first, pkt_off, s)
     info = torch.empty(n * 16, dtype=torch.uint8, device=dev); desc = torch.empty(n * 24, dtype=torch.uint8, device=dev)
-    up = lambda: ctx.call("p2pt_sctp_unpack_batch_device", n, out, pkt_off, 0, info, desc, s)
+    up = lambda: ctx.call("p2pt_sctp_unpack_batch_device", n, out, pkt_off, 0, None, info, desc, s)
     sb = int(ctx.lib.p2pt_sctp_reassemble_scratch_bytes(n)); scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
     msg = torch.empty(n * L, dtype=torch.uint8, device=dev); moff = torch.empty(n + 1, dtype=torch.int64, device=dev)
     mfirst = torch.empty(n, dtype=torch.int32, device=dev); mstat = torch.empty(n, dtype=torch.uint8, device=dev)

@@ -19,6 +19,6 @@ pkt_off = torch.empty(n + 1, dtype=torch.int64, device=dev)
 info = torch.empty(n * 16, dtype=torch.uint8, device=dev); desc = torch.empty(n * 24, dtype=torch.uint8, device=dev)
 for _ in range(2):
     ctx.call("p2pt_sctp_packetize_batch_device", n, d_msg, d_moff, z16, z16, v32, one16, ssn, pp, tsn, None, None, out, omoff, first, pkt_off, s)
-    ctx.call("p2pt_sctp_unpack_batch_device", n, out, pkt_off, 0, info, desc, s)
+    ctx.call("p2pt_sctp_unpack_batch_device", n, out, pkt_off, 0, None, info, desc, s)
 torch.cuda.synchronize()
 print("ok")
