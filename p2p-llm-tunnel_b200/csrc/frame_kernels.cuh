@@ -949,46 +949,6 @@ __global__ void __launch_bounds__(kSmallDemux) demux_small_kernel(
 // sector once, and the writes advance one front per stream, which L2 merges into whole lines.  Walking
 // the sorted order instead reads 69-byte frames and 24-byte descriptors at random (measured 4.7x read
 // amplification on 10 M x 64 B).
-// len bytes from logical byte offset so of the padded shared buffer src to global dst (any alignment on either side),
-// by `parts` cooperating lanes.  Whole 16-byte destination vectors when dst and len allow (the gather of payloads whose
-// sizes are multiples of 16 into a stream that started aligned), else aligned 32-bit words, bytes only at the two ends.
-__device__ __forceinline__ void smem_to_global_unaligned(uint8_t* dst, const PaddedBuf& src, uint32_t so, uint32_t len,
-                                                         int part, int parts) {
-    if ((((uintptr_t)dst | len) & 15) == 0) {
-        const unsigned sh = (so & 3) * 8;
-        for (uint32_t v = part; v < (len >> 4); v += parts) {
-            const uint32_t sw = (so >> 2) + 4 * v;
-            const uint32_t w0 = src.word(sw), w1 = src.word(sw + 1), w2 = src.word(sw + 2), w3 = src.word(sw + 3), w4 = src.word(sw + 4);
-            stg128(dst + 16 * v, make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh),
-                                            __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh)));
-        }
-        return;
-    }
-    const uint32_t d0 = (uint32_t)((4 - ((uintptr_t)dst & 3)) & 3);
-    if (len < d0 + 4) {
-        for (uint32_t b = part; b < len; b += parts) dst[b] = src.byte(so + b);
-        return;
-    }
-    const uint32_t nw = (len - d0) >> 2;
-    if (part == 0) for (uint32_t b = 0; b < d0; b++) dst[b] = src.byte(so + b);
-    if (part == parts - 1) for (uint32_t b = d0 + 4 * nw; b < len; b++) dst[b] = src.byte(so + b);
-    const uint32_t per = (nw + parts - 1) / parts, w0 = per * part;
-    uint32_t w1 = w0 + per; if (w1 > nw) w1 = nw;
-    if (w0 >= w1) return;
-    uint32_t* dw = reinterpret_cast<uint32_t*>(dst + d0);
-    const uint32_t sb = so + d0 + 4 * w0;
-    const unsigned sh = (sb & 3) * 8;
-    const uint32_t sw = sb >> 2;
-    uint32_t lo = src.word(sw);
-    for (uint32_t k = 0; k < w1 - w0; k++) {
-        const uint32_t hi = src.word(sw + k + 1);
-        dw[w0 + k] = __funnelshift_r(lo, hi, sh);
-        lo = hi;
-    }
-}
-
-constexpr uint32_t kGatherTileIn = 9216;          // input span of a 128-frame tile held in shared memory (headers included)
-
 __global__ void __launch_bounds__(256, P2PT_GATHER_MIN_BLOCKS) demux_gather_kernel(
     u64 n, const u64* __restrict__ misc, const DemuxBufs bufs,
     const p2pt_desc* __restrict__ desc, const uint8_t* __restrict__ in,
@@ -998,124 +958,37 @@ __global__ void __launch_bounds__(256, P2PT_GATHER_MIN_BLOCKS) demux_gather_kern
     const u64* __restrict__ dst64 = bufs.keys[demux_src_buffer(misc, kSortPasses) ^ 1];
     const uint32_t* __restrict__ dst32 = reinterpret_cast<const uint32_t*>(dst64);
     const int lane = threadIdx.x & 31, quad = lane >> 2, q = lane & 3;
-    // Regime, as in the encoder: do the frames average at most kSmallFrameAvg bytes?  (Two descriptor loads every thread
-    // makes; the tiles below check their own span exactly.)
-    const u64 first_off = desc[0].pay_off, last_end = desc[n - 1].pay_off + desc[n - 1].pay_len;
-    if (!(last_end >= first_off && last_end - first_off <= n * kSmallFrameAvg)) {
-        // ------------------------------------------------------------------ general regime
-        const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-        const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
-        const int tile = 8 * rounds;                       // see frame_encode_kernel
-        for (u64 i0 = warp * tile; i0 < n; i0 += nwarps * tile) {
-            const u64 i = i0 + lane;                       // lane l holds the metadata of frame i0 + l
-            u64 so = 0, o = 0;
-            uint32_t len = 0;
-            if (lane < tile && i < n) {
-                const p2pt_desc d = desc[i];
-                if (d.status == P2PT_ST_OK && (d.msg_type == 11 || d.msg_type == 21) && d.pay_len) {
-                    o = dst_mode == 1 ? (u64)dst32[i] : dst64[i];      // a saturated 32-bit offset is beyond any 32-bit cap
-                    if (o <= gathered_cap && d.pay_len <= gathered_cap - o) { len = d.pay_len; so = d.pay_off; }   // overflow: caller sees it in gathered_off[k]
-                }
-            }
-            if (__all_sync(0xffffffffu, len <= kQuadCopyMax)) {
-#pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    if (r >= rounds) break;
-                    const int f = 8 * r + quad;
-                    const u64 fso = __shfl_sync(0xffffffffu, so, f), fo = __shfl_sync(0xffffffffu, o, f);
-                    const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
-                    if (flen) quad_copy_bytes(gathered + fo, in + fso, flen, q);
-                }
-            } else {
-#pragma unroll 1
-                for (int f = 0; f < tile; f++) {
-                    const u64 fso = __shfl_sync(0xffffffffu, so, f), fo = __shfl_sync(0xffffffffu, o, f);
-                    const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
-                    if (flen) warp_copy_bytes(gathered + fo, in + fso, flen, lane);
-                }
-            }
-        }
-        return;
-    }
-    // ---------------------------------------------------------------------- small-frame regime
-    // A block takes kSmallTile frames in arrival order at a time.  Their bytes lie front to back in the input, so the
-    // span from the first payload to the end of the last comes into (padded, double-buffered) shared memory as whole
-    // aligned vectors - one coalesced read of every DRAM sector, the next tile's loads in flight while this one is
-    // written out - and two lanes per frame then write the payload to its place in the stream-grouped output.
-    __shared__ __align__(16) uint32_t sin_w[2][(kGatherTileIn + 32) / 4 + (kGatherTileIn + 32) / 64 + 2];
-    __shared__ u64 s_dst[2][kSmallTile], s_src[2][kSmallTile];
-    __shared__ uint32_t s_len[2][kSmallTile];
-    __shared__ uint8_t s_mode[2][kSmallTile];                 // 0 nothing to copy, 1 from the staged span, 2 from global memory
-    const int t = threadIdx.x;
-    const u64 ntile = (n + kSmallTile - 1) / kSmallTile;
-    struct TileRegs {
-        u64 lo, hi;                // input span of the tile: first payload byte .. end of the last frame
-        u64 src, dst; uint32_t len;    // frame t: payload offset, destination, bytes to copy (0: nothing)
-        uint4 v[3];
-        int T; bool staged;
-    };
-    auto load_tile = [&](u64 tile, TileRegs& r) {
-        const u64 i0 = tile * kSmallTile;
-        r.T = n - i0 < (u64)kSmallTile ? (int)(n - i0) : kSmallTile;
-        const p2pt_desc dl = desc[i0 + r.T - 1];
-        r.lo = desc[i0].pay_off; r.hi = dl.pay_off + dl.pay_len;
-        r.src = 0; r.dst = 0; r.len = 0;
-        if (t < r.T) {
-            const p2pt_desc d = desc[i0 + t];
+    const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
+    const int tile = 8 * rounds;                       // see frame_encode_kernel
+    for (u64 i0 = warp * tile; i0 < n; i0 += nwarps * tile) {
+        const u64 i = i0 + lane;                       // lane l holds the metadata of frame i0 + l
+        u64 so = 0, o = 0;
+        uint32_t len = 0;
+        if (lane < tile && i < n) {
+            const p2pt_desc d = desc[i];
             if (d.status == P2PT_ST_OK && (d.msg_type == 11 || d.msg_type == 21) && d.pay_len) {
-                const u64 o = dst_mode == 1 ? (u64)dst32[i0 + t] : dst64[i0 + t];
-                if (o <= gathered_cap && d.pay_len <= gathered_cap - o) { r.len = d.pay_len; r.src = d.pay_off; r.dst = o; }
+                o = dst_mode == 1 ? (u64)dst32[i] : dst64[i];      // a saturated 32-bit offset is beyond any 32-bit cap
+                if (o <= gathered_cap && d.pay_len <= gathered_cap - o) { len = d.pay_len; so = d.pay_off; }   // overflow: caller sees it in gathered_off[k]
             }
         }
-        r.staged = r.hi >= r.lo && r.hi - r.lo <= kGatherTileIn;
-        if (r.staged) {
-            const uint8_t* gsrc = in + r.lo;
-            const uint32_t ia = (uint32_t)((uintptr_t)gsrc & 15);
-            const uint32_t nvin = (ia + (uint32_t)(r.hi - r.lo) + 15) >> 4;
+        if (__all_sync(0xffffffffu, len <= kQuadCopyMax)) {
 #pragma unroll
-            for (int k = 0; k < 3; k++) {
-                const uint32_t vi = t + 256 * k;
-                if (vi < nvin) r.v[k] = ldg128_stream(gsrc - ia + 16 * (size_t)vi);
+            for (int r = 0; r < 4; r++) {
+                if (r >= rounds) break;
+                const int f = 8 * r + quad;
+                const u64 fso = __shfl_sync(0xffffffffu, so, f), fo = __shfl_sync(0xffffffffu, o, f);
+                const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
+                if (flen) quad_copy_bytes(gathered + fo, in + fso, flen, q);
+            }
+        } else {
+#pragma unroll 1
+            for (int f = 0; f < tile; f++) {
+                const u64 fso = __shfl_sync(0xffffffffu, so, f), fo = __shfl_sync(0xffffffffu, o, f);
+                const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
+                if (flen) warp_copy_bytes(gathered + fo, in + fso, flen, lane);
             }
         }
-    };
-    TileRegs cur;
-    if (blockIdx.x < ntile) load_tile(blockIdx.x, cur);
-    int b = 0;
-    for (u64 tile = blockIdx.x; tile < ntile; tile += gridDim.x, b ^= 1) {
-        const int T = cur.T;
-        const u64 lo = cur.lo;
-        const uint32_t span = (uint32_t)(cur.hi - cur.lo);
-        const uint32_t ia = (uint32_t)((uintptr_t)(in + lo) & 15);
-        // a frame whose payload is not inside the staged span (a tile too large for the buffer, or descriptors that
-        // are not in input order) is copied from global memory, four lanes per frame
-        const bool inside = cur.staged && cur.src >= lo && cur.src + cur.len <= cur.hi;
-        if (t < T) {
-            s_dst[b][t] = cur.dst; s_src[b][t] = cur.src; s_len[b][t] = cur.len;
-            s_mode[b][t] = !cur.len ? 0 : inside ? 1 : 2;
-        }
-        const bool from_global = cur.len && !inside;
-        if (cur.staged) {
-            const uint32_t nvin = (ia + span + 15) >> 4;
-#pragma unroll
-            for (int k = 0; k < 3; k++) {
-                const uint32_t vi = t + 256 * k;
-                if (vi < nvin) {
-                    uint32_t* q4 = sin_w[b] + 4 * vi + (vi >> 2);
-                    q4[0] = cur.v[k].x; q4[1] = cur.v[k].y; q4[2] = cur.v[k].z; q4[3] = cur.v[k].w;
-                }
-            }
-        }
-        // tile b staged; buffer b ^ 1 is free again once every thread is past this barrier
-        const bool any_global = __syncthreads_or(from_global);
-        if (tile + gridDim.x < ntile) load_tile(tile + gridDim.x, cur);
-        const PaddedBuf sin{sin_w[b]};
-        const int f = t >> 1, h = t & 1;                      // two lanes per frame
-        if (f < T && s_mode[b][f] == 1)
-            smem_to_global_unaligned(gathered + s_dst[b][f], sin, ia + (uint32_t)(s_src[b][f] - lo), s_len[b][f], h, 2);
-        if (any_global)
-            for (int g = t >> 2; g < T; g += 64)
-                if (s_mode[b][g] == 2) quad_copy_bytes(gathered + s_dst[b][g], in + s_src[b][g], s_len[b][g], t & 3);
     }
 }
 
