@@ -299,8 +299,9 @@ class Context:
                                                 out.ctypes.data, out_off.ctypes.data, desc.ctypes.data))
         return out, out_off, desc
 
-    def pipeline_open_demux(self, session, rec, rec_off, max_streams, gathered_cap, want_out=False):
-        """open -> decode -> demux -> gather in one call; returns dict like frame_demux plus desc."""
+    def pipeline_open_demux(self, session, rec, rec_off, max_streams, gathered_cap, want_out=False, want_desc=True, want_perm=True):
+        """open -> decode -> demux -> gather in one call; returns dict like frame_demux plus desc.  want_desc / want_perm
+        = False passes NULL for them (they then come back zero-filled / empty)."""
         session = _as(session, np.uint32); rec = _as(rec, np.uint8); rec_off = _as(rec_off, np.uint64)
         n = len(session)
         desc = np.zeros(n, DESC_DTYPE)
@@ -311,13 +312,13 @@ class Context:
         k = _u32(0)
         self._check(self.lib.p2pt_pipeline_open_demux(
             self.h, n, session.ctypes.data, rec.ctypes.data, rec_off.ctypes.data,
-            out.ctypes.data if want_out else None, desc.ctypes.data, max_streams, uniq.ctypes.data,
-            usess.ctypes.data, csr.ctypes.data, perm.ctypes.data, C.addressof(k),
+            out.ctypes.data if want_out else None, desc.ctypes.data if want_desc else None, max_streams, uniq.ctypes.data,
+            usess.ctypes.data, csr.ctypes.data, perm.ctypes.data if want_perm else None, C.addressof(k),
             gathered.ctypes.data, gathered_cap, goff.ctypes.data))
         kk = k.value
         m = int(csr[kk])
         return {"k": kk, "desc": desc, "out": out, "uniq_sid": uniq[:kk].copy(), "uniq_session": usess[:kk].copy(),
-                "csr": csr[:kk + 1].copy(), "perm": perm[:m].copy(), "gathered_off": goff[:kk + 1].copy(),
+                "csr": csr[:kk + 1].copy(), "perm": perm[:m].copy() if want_perm else perm[:0], "gathered_off": goff[:kk + 1].copy(),
                 "gathered": gathered[:int(goff[kk])].copy()}
 
     # ---- SCTP DATA chunks + CRC32c (host buffers) ------------------------------------------------------------

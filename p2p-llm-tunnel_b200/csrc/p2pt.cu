@@ -1741,7 +1741,7 @@ static int32_t open_demux_small(p2pt_ctx* ctx, Lane* L, uint64_t n, const uint32
     a.out = d_out - rec_off[0]; a.out_off = (const u64*)z_io;
     a.desc = d_desc;
     if (int32_t r = launch_gcm<kPipeOpen>(ctx, a, pick_group(ctx, n, ibytes), st)) return r;
-    CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, st));
+    if (desc) CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, st));
     if (out && ibytes) CUDA_TRY(ctx, cudaMemcpyAsync(out + rec_off[0], d_out, ibytes, cudaMemcpyDeviceToHost, st));
     if (int32_t r = p2pt_frame_demux_batch_device(ctx, n, d_desc, z_sess, d_out - rec_off[0], max_streams, z_uniq,
                                                   uniq_session ? z_usess : nullptr, z_csr, z_perm, z_k,
@@ -1756,7 +1756,7 @@ static int32_t open_demux_small(p2pt_ctx* ctx, Lane* L, uint64_t n, const uint32
     memcpy(csr, host_of(z_csr), 8 * ((size_t)k + 1));
     if (gathered_off) memcpy(gathered_off, host_of(z_goff), 8 * ((size_t)k + 1));
     const uint64_t m = csr[k];
-    if (m) memcpy(perm, host_of(z_perm), 4 * m);
+    if (m && perm) memcpy(perm, host_of(z_perm), 4 * m);
     if (gathered) {
         if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "pipeline_open_demux: gathered_cap too small");
         memcpy(gathered, host_of(z_g), gathered_off[k]);
@@ -1773,9 +1773,9 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
                                  uint64_t* csr, uint32_t* perm, uint32_t* k_out,
                                  uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off) {
     if (!ctx) return P2PT_ERR_ARG;
-    if (!uniq_sid || !csr || !perm || !k_out) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: null output");
+    if (!uniq_sid || !csr || !k_out) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: null output");
     if (n == 0) { *k_out = 0; csr[0] = 0; if (gathered_off) gathered_off[0] = 0; return P2PT_OK; }
-    if (!session || !rec || !rec_off || !desc) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: null argument");
+    if (!session || !rec || !rec_off) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: null argument");
     if (gathered && !gathered_off) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: gather needs gathered_off");
     if (n > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: n must fit in 32 bits");
     if (!offsets_monotonic(rec_off, n)) return set_err(ctx, P2PT_ERR_ARG, "pipeline_open_demux: offsets must be non-decreasing");
@@ -1839,7 +1839,7 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
         CUDA_TRY(ctx, cudaEventRecord(L->events[i], L->streams[i]));
         CUDA_TRY(ctx, cudaStreamWaitEvent(s0, L->events[i], 0));
     }
-    CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, s0));
+    if (desc) CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, s0));       // desc / perm only when asked for
     if (int32_t r = p2pt_frame_demux_batch_device(ctx, n, d_desc, d_sess, d_out - rec_off[0], max_streams, d_uniq,
                                                   uniq_session ? d_usess : nullptr, d_csr, d_perm, d_k,
                                                   gathered ? d_g : nullptr, gathered_cap,
@@ -1855,7 +1855,7 @@ int32_t p2pt_pipeline_open_demux(p2pt_ctx* ctx, uint64_t n, const uint32_t* sess
     if (gathered_off) CUDA_TRY(ctx, cudaMemcpyAsync(gathered_off, d_goff, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, s0));
     CUDA_TRY(ctx, wait_stream(ctx, L, s0));
     const uint64_t m = csr[k];
-    if (m) CUDA_TRY(ctx, cudaMemcpyAsync(perm, d_perm, 4 * m, cudaMemcpyDeviceToHost, s0));
+    if (m && perm) CUDA_TRY(ctx, cudaMemcpyAsync(perm, d_perm, 4 * m, cudaMemcpyDeviceToHost, s0));
     if (gathered) {
         if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "pipeline_open_demux: gathered_cap too small");
         // split the big copy over the streams so both DMA engines stay busy

@@ -120,6 +120,11 @@ def test_slot_bytes_beyond_the_item_are_zero(ctx):
     assert not st.any()
     r2 = rec2.reshape(n, slot)
     assert np.array_equal(r2[:, :13 + L + 24].reshape(-1), rec) and not r2[:, 13 + L + 24:].any()
+    # the fused reader without desc / perm (a reader that only wants the per-stream bodies): same bodies
+    ra = ctx.pipeline_open_demux(session, rec, rec_off, max_streams=n, gathered_cap=int(rec.size))
+    rb = ctx.pipeline_open_demux(session, rec, rec_off, max_streams=n, gathered_cap=int(rec.size), want_desc=False, want_perm=False)
+    assert rb["k"] == ra["k"] and np.array_equal(rb["gathered"], ra["gathered"]) and np.array_equal(rb["csr"], ra["csr"])
+    assert not rb["desc"]["status"].any() and rb["perm"].size == 0
     # the fused reader with `out` requested
     w_off = np.arange(n + 1, dtype=np.uint64) * np.uint64(37 + L)
     r = ctx.pipeline_open_demux(session, rec, w_off, max_streams=n, gathered_cap=int(rec.size), want_out=True)
