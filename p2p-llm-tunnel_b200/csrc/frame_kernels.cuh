@@ -142,9 +142,12 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
         return;
     }
     // ---------------------------------------------------------------------- small-frame regime
-    __shared__ __align__(16) uint32_t sin_w[(kSmallTileIn + 32) / 4 + (kSmallTileIn + 32) / 64 + 2];
-    __shared__ __align__(16) uint32_t sout_w[(kSmallTileOut + 32) / 4 + (kSmallTileOut + 32) / 64 + 2];
-    const PaddedBuf sin{sin_w}, sout{sout_w};
+    // sin: the payload span behind kSinFront spare bytes, padded (pad_word); sout: the output span, plain words, all
+    // zero between tiles (boundary words are OR-ed together from the frames that share them)
+    constexpr uint32_t kSinFront = 16;
+    __shared__ __align__(16) uint32_t sin_w[(kSmallTileIn + 64) / 4 + (kSmallTileIn + 64) / 64 + 2];
+    __shared__ __align__(16) uint32_t sout_w[(kSmallTileOut + 32) / 4];
+    const PaddedBuf sin{sin_w};
     __shared__ u64 s_po[kSmallTile + 1], s_oo[kSmallTile + 1];
     __shared__ uint32_t s_sid[kSmallTile];
     __shared__ uint8_t s_type[kSmallTile];
@@ -184,6 +187,7 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
     };
     TileRegs cur;
     if (blockIdx.x < ntile) load_tile(blockIdx.x, cur);
+    for (uint32_t w = t; w < sizeof(sout_w) / 4; w += 256) sout_w[w] = 0;     // ordered before the first shuffle by the tile's barrier
     for (u64 tile = blockIdx.x; tile < ntile; tile += gridDim.x) {
         const int T = cur.T;
         const u64 pb = cur.pb, ob = cur.ob;
@@ -199,8 +203,8 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
 #pragma unroll
             for (int k = 0; k < 3; k++) {
                 const uint32_t vi = t + 256 * k;
-                if (vi < nvin) {                                       // words 4 vi .. 4 vi + 3 share one padding offset
-                    uint32_t* q4 = sin_w + 4 * vi + (vi >> 2);
+                if (vi < nvin) {                                       // four words that share one padding offset
+                    uint32_t* q4 = sin_w + pad_word(kSinFront / 4 + 4 * vi);
                     q4[0] = cur.v[k].x; q4[1] = cur.v[k].y; q4[2] = cur.v[k].z; q4[3] = cur.v[k].w;
                 }
             }
@@ -211,25 +215,62 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
             uint8_t* gdst = out + ob;
             const uint32_t oa = (uint32_t)((uintptr_t)gdst & 15);      // sout keeps the span's 16-byte phase
             {
-                const int f = t >> 1, h = t & 1;                       // two lanes per frame
+                // Two lanes per frame, one aligned output WORD at a time.  Words that lie wholly inside the payload are
+                // two source words and a funnel shift (the byte shift is the same for the whole frame); the at most three
+                // words at the head of the frame (header bytes, start of the payload) and the partial word at its end are
+                // built with byte masks and OR-ed in, because the neighbouring frame owns the other bytes of such a word.
+                const int f = t >> 1, h = t & 1;
                 if (f < T) {
                     const uint32_t po = (uint32_t)(s_po[f] - pb), len = (uint32_t)(s_po[f + 1] - s_po[f]);
-                    const uint32_t d = oa + (uint32_t)(s_oo[f] - ob);
-                    if (h == 0) {                                      // header: [type][stream_id BE]
-                        const uint32_t sid = s_sid[f];
-                        sout.byte(d) = s_type[f];
-                        sout.byte(d + 1) = (uint8_t)(sid >> 24); sout.byte(d + 2) = (uint8_t)(sid >> 16);
-                        sout.byte(d + 3) = (uint8_t)(sid >> 8); sout.byte(d + 4) = (uint8_t)sid;
+                    const uint32_t S = oa + (uint32_t)(s_oo[f] - ob), E = S + 5 + len;
+                    const int32_t delta = (int32_t)(kSinFront + ia + po) - (int32_t)(S + 5);   // source byte = output byte + delta
+                    const int32_t dq = delta >> 2;                                             // (4 w + delta) >> 2 = w + dq
+                    const unsigned sh = (unsigned)(delta & 3) * 8;
+                    const uint32_t wS = S >> 2, w_lo = (S + 8) >> 2, w_hi = E >> 2, wE = (E + 3) >> 2;
+                    if (w_hi > w_lo) {                                 // words wholly inside the payload: a contiguous run per lane
+                        const uint32_t per = (w_hi - w_lo + 1) >> 1, a = w_lo + h * per;
+                        const uint32_t b = a + per < w_hi ? a + per : w_hi;
+                        if (a < b) {
+                            uint32_t lo = sin.word((uint32_t)((int32_t)a + dq));
+                            for (uint32_t w = a; w < b; w++) {
+                                const uint32_t hi = sin.word((uint32_t)((int32_t)w + dq + 1));
+                                sout_w[w] = __funnelshift_r(lo, hi, sh);
+                                lo = hi;
+                            }
+                        }
                     }
-                    if (len) smem_copy_unaligned(sout, d + 5, sin, ia + po, len, h, 2);
+                    // edge words: lane 0 the head of the frame, lane 1 the partial word at its end
+                    const uint32_t he = w_lo < wE ? w_lo : wE;
+                    const uint32_t e0 = h == 0 ? wS : w_hi, e1 = h == 0 ? he : ((w_hi >= w_lo && 4 * w_hi < E) ? w_hi + 1 : w_hi);
+                    if (e0 < e1) {
+                        const uint32_t sid = s_sid[f];
+                        const u64 H = (u64)s_type[f] | ((u64)__byte_perm(sid, 0, 0x0123) << 8);     // [type][stream_id BE]
+                        for (uint32_t w = e0; w < e1; w++) {
+                            const int32_t rel = (int32_t)(4 * w) - (int32_t)S;             // position of the word's byte 0 in header || payload
+                            const uint32_t sa = (uint32_t)((int32_t)(4 * w) + delta);
+                            const uint32_t pw = __funnelshift_r(sin.word(sa >> 2), sin.word((sa >> 2) + 1), (sa & 3) * 8);
+                            const uint32_t hw = rel >= 5 ? 0u : rel >= 0 ? (uint32_t)(H >> (8 * rel)) : (uint32_t)(H << (8 * -rel));
+                            // bytes j of the word with lo <= rel + j < hi, as a mask
+                            auto bytes = [rel](int32_t lo, int32_t hi) -> uint32_t {
+                                int32_t j0 = lo - rel, j1 = hi - rel;
+                                j0 = j0 < 0 ? 0 : j0; j1 = j1 > 4 ? 4 : j1;
+                                if (j1 <= j0) return 0u;
+                                const uint32_t upto = j1 >= 4 ? 0xffffffffu : ((1u << (8 * j1)) - 1u);
+                                return upto & ~((1u << (8 * j0)) - 1u);
+                            };
+                            const uint32_t v = (hw & bytes(0, 5)) | (pw & bytes(5, 5 + (int32_t)len));
+                            atomicOr(&sout_w[w], v);
+                        }
+                    }
                 }
             }
             __syncthreads();
             const uint32_t total = oa + (uint32_t)ospan;               // [oa, total) of sout is the span
             uint8_t* g0 = gdst - oa;
             for (uint32_t lo = 16u * t; lo < total; lo += 16u * 256u) {
-                const uint32_t* q4 = sout_w + (lo >> 2) + (lo >> 6);   // words lo / 4 .. + 3 share one padding offset
-                const uint4 x = make_uint4(q4[0], q4[1], q4[2], q4[3]);
+                uint4* q4 = reinterpret_cast<uint4*>(sout_w + (lo >> 2));
+                const uint4 x = *q4;
+                *q4 = make_uint4(0, 0, 0, 0);                          // zero again for the next tile's OR-ed words
                 if (lo >= oa && lo + 16 <= total) stg128(g0 + lo, x);
                 else store_bytes(g0 + lo, x, lo < oa ? (int)(oa - lo) : 0, total - lo < 16u ? (int)(total - lo) : 16);
             }
