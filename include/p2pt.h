@@ -115,7 +115,8 @@ uint64_t    p2pt_launch_count(p2pt_ctx* ctx);
  * of a mapped pinned buffer: one kernel launch and one (spinning) stream wait, no copies; about half the
  * latency of the copy path for a single 64-byte frame.  "small_demux" (default 1): demux calls of up to
  * 1024 frames run init + sort + scan + emit in one single-block kernel (two launches with the gather
- * instead of six and a cooperative launch).  Host-pointer calls that stage less than 8 MiB always wait
+ * instead of six and a cooperative launch).  "direct_demux" (default 1): demux calls with max_streams <= 8192
+ * try the sort-free path first (see p2pt_frame_decode_demux_batch).  Host-pointer calls that stage less than 8 MiB always wait
  * by spinning, whatever "blocking_sync" says: a sleeping wait costs 50-100 us per wake-up. */
 int32_t     p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value);
 /* read-only facts: "sm_count", "lut_slack", "gcm_group_width", "n_sessions", "gcm_threads"; -1 if unknown */
@@ -152,6 +153,21 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
                                uint64_t* csr, uint32_t* perm,
                                uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
                                uint64_t* gathered_off);
+
+/* The reader loop in one call: decode + demux + body gather of frames that are already plaintext
+ * (proxy.rs:109-170: decode :109-116, HashMap probe per frame :118-153; serve.rs:82-156: decode :103-109,
+ * per-stream Vec<u8> append :112-139).  in / in_off as in p2pt_frame_decode_batch, everything else as in
+ * p2pt_frame_demux_batch.  desc (n entries) and perm are nullable: a reader that only wants the per-stream
+ * bodies never pays for 24-byte descriptors or the frame permutation.
+ * When max_streams <= 8192 the demux (here and in p2pt_frame_demux_batch) first tries a path without any
+ * sort - dense stream ids from a hash table, one ordered counting pass, one gather - and falls back to the
+ * sorting path on the device, without the host noticing, if the batch holds more distinct streams than that
+ * (k_out is exact either way).  Give max_streams honestly: a caller that passes n "to be safe" always sorts. */
+int32_t p2pt_frame_decode_demux_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, const uint64_t* in_off,
+                                      const uint32_t* session, p2pt_desc* desc,
+                                      uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                      uint64_t* csr, uint32_t* perm, uint32_t* k_out,
+                                      uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off);
 
 /* ---- DTLS 1.2 AES-128-GCM record layer ------------------------------------------------------ */
 /* CryptoGcm::encrypt(pkt_rlh, raw): raw_i = hdr13 || plaintext; rec_i = hdr13' || nonce8 ||
@@ -280,6 +296,15 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
                                       uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
                                       uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes,
                                       void* stream);
+/* device form of p2pt_frame_decode_demux_batch; scratch of p2pt_frame_decode_demux_scratch_bytes(n) bytes,
+ * 256-byte aligned (it also holds descriptors / perm for the sorting path when the caller passes NULL). */
+uint64_t p2pt_frame_decode_demux_scratch_bytes(uint64_t n);
+int32_t p2pt_frame_decode_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, const uint64_t* in_off,
+                                             const uint32_t* session, p2pt_desc* desc,
+                                             uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                             uint64_t* csr, uint32_t* perm, uint32_t* k_out,
+                                             uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off,
+                                             void* scratch, uint64_t scratch_bytes, void* stream);
 /* No counterpart in the reference (it has no device memory to manage).
  * Same work and same results as p2pt_frame_demux_batch_device, for callers that may not allocate
  * device memory while they run and have nowhere to take `scratch` from: for example a reader task
@@ -287,7 +312,7 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
  * GPU owns the rest of HBM, or a per-connection loop that cannot afford cudaMalloc / cudaFree
  * because those take the driver's allocator lock and synchronise the whole device, stalling every
  * other session's stream.  The scratch lives in a static device array inside the library
- * (about 8.0 MB, resident on every GPU that loads the library until the process exits), which
+ * (about 12.6 MB, resident on every GPU that loads the library until the process exits), which
  * bounds the batch: n <= P2PT_NOALLOC_MAX_FRAMES, larger batches are refused with
  * P2PT_ERR_CAPACITY.  The call itself performs no cudaMalloc / cudaFree and uses no allocating
  * library routine.

@@ -39,6 +39,9 @@ SIGNATURES = {
     "p2pt_frame_encode_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_frame_decode_batch": (_i32, [_vp, _u64, _vp, _vp, _vp]),
     "p2pt_frame_demux_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _u64, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
+    "p2pt_frame_decode_demux_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
+    "p2pt_frame_decode_demux_scratch_bytes": (_u64, [_u64]),
+    "p2pt_frame_decode_demux_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _u64, _vp]),
     "p2pt_dtls_gcm_seal_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_dtls_gcm_open_batch": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_pipeline_seal": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
@@ -231,6 +234,38 @@ class Context:
         kk = k.value
         m = int(csr[kk])
         res = {"k": kk, "uniq_sid": uniq[:kk].copy(), "csr": csr[:kk + 1].copy(), "perm": perm[:m].copy()}
+        if session is not None:
+            res["uniq_session"] = usess[:kk].copy()
+        if gather:
+            res["gathered_off"] = goff[:kk + 1].copy()
+            res["gathered"] = gathered[:int(goff[kk])].copy()
+        return res
+
+    def frame_decode_demux(self, buf, in_off, max_streams, gathered_cap=None, session=None, want_desc=False, want_perm=True):
+        """decode + demux + gather in one call (p2pt_frame_decode_demux_batch)"""
+        buf = _as(buf, np.uint8); in_off = _as(in_off, np.uint64)
+        n = len(in_off) - 1
+        if session is not None:
+            session = _as(session, np.uint32)
+        uniq = np.zeros(max_streams + 1, np.uint32); usess = np.zeros(max_streams + 1, np.uint32)
+        csr = np.zeros(max_streams + 1, np.uint64); goff = np.zeros(max_streams + 1, np.uint64)
+        perm = np.zeros(max(n, 1), np.uint32)
+        desc = np.zeros(max(n, 1), DESC_DTYPE)
+        gather = gathered_cap is not None
+        gathered = np.zeros(max(gathered_cap or 0, 1), np.uint8)
+        k = _u32(0)
+        self._check(self.lib.p2pt_frame_decode_demux_batch(
+            self.h, n, buf.ctypes.data, in_off.ctypes.data, _ptr(session), desc.ctypes.data if want_desc else None,
+            max_streams, uniq.ctypes.data, usess.ctypes.data if session is not None else None, csr.ctypes.data,
+            perm.ctypes.data if want_perm else None, C.addressof(k),
+            gathered.ctypes.data if gather else None, gathered_cap or 0, goff.ctypes.data if gather else None))
+        kk = k.value
+        m = int(csr[kk])
+        res = {"k": kk, "uniq_sid": uniq[:kk].copy(), "csr": csr[:kk + 1].copy()}
+        if want_perm:
+            res["perm"] = perm[:m].copy()
+        if want_desc:
+            res["desc"] = desc[:n]
         if session is not None:
             res["uniq_session"] = usess[:kk].copy()
         if gather:

@@ -294,7 +294,9 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
 
 // ---- decode: one thread per frame ----------------------------------------------------------------
 __global__ void __launch_bounds__(256) frame_decode_kernel(
-    u64 n, const uint8_t* __restrict__ in, const u64* __restrict__ in_off, p2pt_desc* __restrict__ desc) {
+    u64 n, const uint8_t* __restrict__ in, const u64* __restrict__ in_off, p2pt_desc* __restrict__ desc,
+    const uint32_t* run_flag) {
+    if (run_flag && *run_flag == 0) return;
     const u64 stride = (u64)gridDim.x * blockDim.x;
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const u64 o = __ldg(in_off + i), e = __ldg(in_off + i + 1);
@@ -371,7 +373,7 @@ __host__ __device__ constexpr u64 align256(u64 x) { return (x + 255) & ~(u64)255
 
 constexpr u64 demux_scan_blocks(u64 n) { return (n + kScanThreads - 1) / kScanThreads; }
 
-constexpr u64 demux_scratch_bytes(u64 n) {
+constexpr u64 demux_sort_scratch_bytes(u64 n) {
     u64 b = 0;
     b += 2 * align256(n * sizeof(u64));
     b += 2 * align256(n * sizeof(uint32_t));
@@ -409,7 +411,9 @@ __device__ __forceinline__ uint32_t demux_digit(const u64* keys, const uint32_t*
 __global__ void __launch_bounds__(256) demux_init_kernel(u64 n, const p2pt_desc* __restrict__ desc,
                                                          const uint32_t* __restrict__ session,
                                                          u64* __restrict__ keys, uint32_t* __restrict__ idx,
-                                                         u64* __restrict__ misc, uint32_t* __restrict__ blen) {
+                                                         u64* __restrict__ misc, uint32_t* __restrict__ blen,
+                                                         const uint32_t* run_flag) {
+    if (run_flag && *run_flag == 0) return;
     u64 vor = 0, vnor = 0;
     uint32_t bad = 0;
     const u64 stride = (u64)gridDim.x * blockDim.x;
@@ -455,6 +459,10 @@ __device__ __forceinline__ int demux_src_buffer(const u64* misc, int pass) {
     return b;
 }
 struct DemuxBufs { u64* keys[2]; uint32_t* idx[2]; };
+
+// run_flag (nullable): the kernels of the sorting path are also enqueued behind the direct path
+// (demux_direct_kernels.cuh) as its fallback; they then run only if that path raised its flag.
+__device__ __forceinline__ bool demux_skip(const uint32_t* run_flag) { return run_flag && *run_flag == 0; }
 
 __device__ __forceinline__ void demux_tile(u64 n, u64& lo, u64& hi) {
     const u64 per = (n + kSortBlocks - 1) / kSortBlocks;
@@ -697,29 +705,31 @@ __device__ __forceinline__ void demux_scatter_phase(u64 n, const DemuxBufs& bufs
 // three launches per pass (fallback path) ...
 __global__ void __launch_bounds__(kSortThreads) demux_hist_kernel(
     u64 n, const DemuxBufs bufs, const uint32_t* __restrict__ blen,
-    int pass, uint32_t* __restrict__ hist, const u64* __restrict__ misc, bool packed) {
-    if (demux_pass_trivial(misc, pass)) return;
+    int pass, uint32_t* __restrict__ hist, const u64* __restrict__ misc, bool packed, const uint32_t* run_flag) {
+    if (demux_skip(run_flag) || demux_pass_trivial(misc, pass)) return;
     demux_hist_phase(n, bufs, blen, pass, hist, misc, packed);
 }
 __global__ void __launch_bounds__(32 * kRowScanWarps) demux_rowscan_kernel(uint32_t* __restrict__ hist, int pass,
                                                                           u64* __restrict__ misc,
-                                                                          uint32_t* __restrict__ row_total) {
-    if (demux_pass_trivial(misc, pass)) return;
+                                                                          uint32_t* __restrict__ row_total, const uint32_t* run_flag) {
+    if (demux_skip(run_flag) || demux_pass_trivial(misc, pass)) return;
     const int row = blockIdx.x * kRowScanWarps + (threadIdx.x >> 5);
     if (row < kRadix) demux_rowscan_row(hist, row, row_total);
 }
 __global__ void __launch_bounds__(kSortThreads) demux_scatter_kernel(
     u64 n, const DemuxBufs bufs, const uint32_t* __restrict__ blen,
     int pass, const uint32_t* __restrict__ hist, const u64* __restrict__ misc,
-    const uint32_t* __restrict__ row_total, bool packed) {
-    if (demux_pass_trivial(misc, pass)) return;          // nothing to move: the data stays where it is
+    const uint32_t* __restrict__ row_total, bool packed, const uint32_t* run_flag) {
+    if (demux_skip(run_flag) || demux_pass_trivial(misc, pass)) return;          // nothing to move: the data stays where it is
     demux_scatter_phase(n, bufs, blen, pass, hist, misc, row_total, packed);
 }
 
 // ... or all passes in ONE cooperative launch: the nine passes are launch-latency bound at 1 M items
 // (27 launches of a few microseconds each), so the phases are separated by grid-wide syncs instead.
 __global__ void __launch_bounds__(kSortThreads, 4) demux_sort_coop_kernel(
-    u64 n, const DemuxBufs bufs, const uint32_t* blen, uint32_t* hist, const u64* misc, uint32_t* row_total, bool packed) {
+    u64 n, const DemuxBufs bufs, const uint32_t* blen, uint32_t* hist, const u64* misc, uint32_t* row_total, bool packed,
+    const uint32_t* run_flag) {
+    if (demux_skip(run_flag)) return;                     // uniform over the whole grid
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     for (int pass = 0; pass < kSortPasses; pass++) {
         if (demux_pass_trivial(misc, pass)) continue;     // uniform over the whole grid
@@ -834,7 +844,9 @@ __device__ __forceinline__ DemuxQuad demux_load_quad(u64 j, u64 m, u64 n, const 
 
 __global__ void __launch_bounds__(kScanThreads) demux_blocksum_kernel(
     u64 n, const DemuxBufs bufs, const uint32_t* __restrict__ blen,
-    const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes, bool first_only, bool packed) {
+    const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes, bool first_only, bool packed,
+    const uint32_t* run_flag) {
+    if (demux_skip(run_flag)) return;
     const int fb = demux_src_buffer(misc, kSortPasses);
     const u64 m = demux_valid_count(n, misc);
     const u64 j = ((u64)blockIdx.x * kScanThreads + threadIdx.x) * kDemuxItems;
@@ -846,7 +858,8 @@ __global__ void __launch_bounds__(kScanThreads) demux_blocksum_kernel(
 
 // single block: exclusive scan of the per-block sums, in place; element [nblk] receives the total
 __global__ void __launch_bounds__(kScanThreads) demux_scan_blocksums_kernel(
-    u64 nblk, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes) {
+    u64 nblk, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes, const uint32_t* run_flag) {
+    if (demux_skip(run_flag)) return;
     __shared__ uint32_t carry_h; __shared__ u64 carry_b;
     if (threadIdx.x == 0) { carry_h = 0; carry_b = 0; }
     __syncthreads();
@@ -874,7 +887,9 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
     const u64* __restrict__ misc, const uint32_t* __restrict__ blk_heads, const u64* __restrict__ blk_bytes,
     u64 nblk, uint32_t max_streams, uint32_t* __restrict__ uniq_sid, uint32_t* __restrict__ uniq_session,
     u64* __restrict__ csr, uint32_t* __restrict__ perm, uint32_t* __restrict__ k_out,
-    u64* __restrict__ gathered_off, int dst_mode, bool first_only, bool packed) {  // dst_mode: 0 none, 1 = 32-bit, 2 = 64-bit offsets
+    u64* __restrict__ gathered_off, int dst_mode, bool first_only, bool packed,    // dst_mode: 0 none, 1 = 32-bit, 2 = 64-bit offsets
+    const uint32_t* run_flag) {
+    if (demux_skip(run_flag)) return;
     const int fb = demux_src_buffer(misc, kSortPasses);
     u64* __restrict__ dst64 = bufs.keys[fb ^ 1];
     uint32_t* __restrict__ dst32 = reinterpret_cast<uint32_t*>(bufs.keys[fb ^ 1]);
@@ -994,7 +1009,8 @@ __global__ void __launch_bounds__(256, P2PT_GATHER_MIN_BLOCKS) demux_gather_kern
     u64 n, const u64* __restrict__ misc, const DemuxBufs bufs,
     const p2pt_desc* __restrict__ desc, const uint8_t* __restrict__ in,
     uint8_t* __restrict__ gathered, u64 gathered_cap, const uint32_t* __restrict__ k_out, uint32_t max_streams,
-    int dst_mode, int rounds) {
+    int dst_mode, int rounds, const uint32_t* run_flag) {
+    if (demux_skip(run_flag)) return;
     if (*k_out > max_streams) return;
     const u64* __restrict__ dst64 = bufs.keys[demux_src_buffer(misc, kSortPasses) ^ 1];
     const uint32_t* __restrict__ dst32 = reinterpret_cast<const uint32_t*>(dst64);

@@ -22,6 +22,7 @@
 
 #include "../../include/p2pt.h"
 #include "frame_kernels.cuh"
+#include "demux_direct_kernels.cuh"
 #include "gcm_kernels.cuh"
 #include "sctp_kernels.cuh"
 #include "dtls_state_kernels.cuh"
@@ -73,6 +74,7 @@ struct p2pt_ctx {
     bool blocking_sync = true;                // big host-pointer calls wait on sync_events (see wait_stream)
     bool small_demux = true;                  // batches of up to 1024 frames take the single-block demux kernel
     bool coop_sort = true;                    // demux sorting passes in one cooperative launch
+    bool direct_demux = true;                 // demux calls with max_streams <= 8192 try the sort-free path first
     std::mutex err_mu;
     std::string err;
     SessionKey* keys_local = nullptr;
@@ -451,6 +453,8 @@ static int32_t ctx_init(p2pt_ctx* ctx, int device, const cudaDeviceProp& prop) {
     CUDA_TRY(nullptr, configure_gcm_mode<kPipeOpen>(ctx->lut_slack));
     CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_packetize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_smem_bytes(ctx->lut_slack)));
     CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_unpack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_smem_bytes(ctx->lut_slack)));
+    CUDA_TRY(nullptr, cudaFuncSetAttribute(demux_direct_rank_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * kDirectIds));
+    CUDA_TRY(nullptr, cudaFuncSetAttribute(demux_direct_rank_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * kDirectIds));
     {
         const size_t cap = 1u << 20;
         bool all = true;
@@ -564,6 +568,10 @@ int32_t p2pt_ctx_set_option(p2pt_ctx* ctx, const char* name, int64_t value) {
         ctx->small_demux = value != 0;
         return P2PT_OK;
     }
+    if (strcmp(name, "direct_demux") == 0) {
+        ctx->direct_demux = value != 0;
+        return P2PT_OK;
+    }
     if (strcmp(name, "blocking_sync") == 0) {
         ctx->blocking_sync = value != 0;
         return P2PT_OK;
@@ -639,7 +647,7 @@ int32_t p2pt_frame_decode_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t*
     if (n == 0) return P2PT_OK;
     if (!in_off || !desc) return set_err(ctx, P2PT_ERR_ARG, "frame_decode: null argument");
     DeviceGuard dg(ctx->device);
-    frame_decode_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, (cudaStream_t)stream>>>(n, in, (const u64*)in_off, desc);
+    frame_decode_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, (cudaStream_t)stream>>>(n, in, (const u64*)in_off, desc, nullptr);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
     return P2PT_OK;
@@ -649,16 +657,27 @@ uint64_t p2pt_frame_demux_scratch_bytes(uint64_t n) { return demux_scratch_bytes
 
 }  // extern "C"
 
-// first_only: see demux_load_quad (the SCTP reassembly drops retransmitted fragments this way)
+// The demux behind every entry point.  first_only: see demux_load_quad (the SCTP reassembly drops retransmitted
+// fragments this way).  Fused form (in_off != NULL): the frames themselves are the input, `desc` is then where
+// descriptors go if anyone wants them (the caller's array, or scratch for the sorting path only).
+namespace {
+struct DemuxFused {
+    const uint64_t* in_off = nullptr;   // frame offsets: decode and demux in one call
+    p2pt_desc* desc_user = nullptr;     // descriptors the caller asked for (nullable)
+    p2pt_desc* desc_work = nullptr;     // where the sorting path decodes to (desc_user, or scratch)
+    uint32_t* perm_work = nullptr;      // the sorting path always writes perm: the caller's, or scratch
+};
+}  // namespace
+
 static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc, const uint32_t* session,
                                  const uint8_t* in,
                                  uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
                                  uint64_t* csr, uint32_t* perm,
                                  uint32_t* k_out, uint8_t* gathered, uint64_t gathered_cap,
                                  uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes, void* stream,
-                                 bool first_only) {
+                                 bool first_only, const DemuxFused* fused = nullptr) {
     if (!ctx) return P2PT_ERR_ARG;
-    if (!uniq_sid || !csr || !perm || !k_out) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null output");
+    if (!uniq_sid || !csr || (!perm && !fused) || !k_out) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null output");
     if (n > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: n must fit in 32 bits");
     if (gathered && (!gathered_off || !in)) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: gather needs in and gathered_off");
     DeviceGuard dg(ctx->device);
@@ -669,62 +688,98 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         if (gathered_off) CUDA_TRY(ctx, cudaMemsetAsync(gathered_off, 0, 8, st));
         return P2PT_OK;
     }
-    if (!desc || !scratch) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null desc or scratch");
+    if ((!desc && !fused) || !scratch) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: null desc or scratch");
     if (scratch_bytes < demux_scratch_bytes(n)) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: scratch too small");
     if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: scratch must be 256-byte aligned");
     DemuxScratch s = demux_carve(scratch, n);
     CUDA_TRY(ctx, cudaMemsetAsync(s.misc, 0, 32, st));
     DemuxBufs bufs;
     bufs.keys[0] = s.keys[0]; bufs.keys[1] = s.keys[1]; bufs.idx[0] = s.idx[0]; bufs.idx[1] = s.idx[1];
-    if (n <= (uint64_t)kSmallDemux && ctx->small_demux) {
+    const bool small = n <= (uint64_t)kSmallDemux && ctx->small_demux;
+    const int dst_mode = !gathered ? 0 : gathered_cap <= 0xffffffffull ? 1 : 2;
+    uint32_t* perm_sort = perm ? perm : fused->perm_work;       // the sorting path's perm (never NULL)
+
+    // ---- the direct path first (demux_direct_kernels.cuh): no sort when the caller expects few streams.  If the
+    //      batch turns out not to fit, it raises run_flag and the sorting path below - enqueued either way - runs.
+    const uint32_t* run_flag = nullptr;
+    if (ctx->direct_demux && !first_only && !small && max_streams <= (uint32_t)kDirectIds) {
+        const DirectScratch ds = direct_carve((uint8_t*)scratch + align256(demux_sort_scratch_bytes(n)), n, s);
+        CUDA_TRY(ctx, cudaMemsetAsync(ds.ctl, 0, kDirectZeroBytes, st));
+        DirectArgs a;
+        a.n = n; a.per = direct_per_block(n);
+        a.in = in; a.in_off = fused ? (const u64*)fused->in_off : nullptr;
+        a.desc_in = desc; a.desc_out = fused ? fused->desc_user : nullptr;
+        a.session = session; a.s = ds; a.want_rank = perm != nullptr;
+        const unsigned nb = (unsigned)direct_blocks(n);
+        if (fused) demux_direct_rank_kernel<true><<<nb, kDirectThreads, 8 * kDirectIds, st>>>(a);
+        else demux_direct_rank_kernel<false><<<nb, kDirectThreads, 8 * kDirectIds, st>>>(a);
+        demux_direct_streams_kernel<<<dim3(kDirectIds / kOrderT, 8), kOrderT, 0, st>>>(ds, (u64*)csr, k_out, (u64*)gathered_off);
+        demux_direct_prefix_kernel<<<kDirectIds / 32, 1024, 0, st>>>(ds, nb, max_streams, uniq_sid, uniq_session, (u64*)csr, (u64*)gathered_off);
+        count_launch(ctx, 3);
+        if (gathered || perm) {
+            const int rounds = copy_tile_rounds(ctx, n, ctx->occ_gather);
+            const unsigned grid = copy_grid(ctx, n, rounds, ctx->occ_gather);
+            if (fused) demux_direct_gather_kernel<true><<<grid, 256, 0, st>>>(a, gathered, gathered_cap, perm, k_out, max_streams, rounds);
+            else demux_direct_gather_kernel<false><<<grid, 256, 0, st>>>(a, gathered, gathered_cap, perm, k_out, max_streams, rounds);
+            count_launch(ctx);
+        }
+        CUDA_TRY(ctx, cudaGetLastError());
+        run_flag = ds.ctl;
+    }
+    if (fused) {
+        // the sorting path works on descriptors: decode first (after a direct attempt: only if that gave up)
+        frame_decode_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, in, (const u64*)fused->in_off, fused->desc_work, run_flag);
+        count_launch(ctx);
+        desc = fused->desc_work;
+    }
+    if (small) {
         // one block does init + sort + scan + emit; misc stays zero, so the gather finds the per-frame
         // destinations in keys[1] exactly as after a sort without passes
-        const int dst_mode = !gathered ? 0 : gathered_cap <= 0xffffffffull ? 1 : 2;
         demux_small_kernel<<<1, kSmallDemux, 0, st>>>((uint32_t)n, desc, session, max_streams, uniq_sid, uniq_session,
-                                                      (u64*)csr, perm, k_out, (u64*)gathered_off, s.keys[1], dst_mode, first_only);
+                                                      (u64*)csr, perm_sort, k_out, (u64*)gathered_off, s.keys[1], dst_mode, first_only);
         count_launch(ctx);
         if (gathered) {
             const int rounds = copy_tile_rounds(ctx, n, ctx->occ_gather);
             demux_gather_kernel<<<copy_grid(ctx, n, rounds, ctx->occ_gather), 256, 0, st>>>(n, s.misc, bufs, desc, in, gathered,
-                                                                        gathered_cap, k_out, max_streams, dst_mode, rounds);
+                                                                        gathered_cap, k_out, max_streams, dst_mode, rounds, nullptr);
             count_launch(ctx);
         }
         CUDA_TRY(ctx, cudaGetLastError());
         return P2PT_OK;
     }
     const bool packed = (session == nullptr);          // key and frame index in one 64-bit word (frame_kernels.cuh)
-    demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc, s.blen);
+    demux_init_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, desc, session, s.keys[0], s.idx[0], s.misc, s.blen, run_flag);
     bool coop_done = false;
     if (ctx->coop_sort) {
         // all nine passes in one cooperative launch (grid-wide syncs between the phases)
         u64 n_arg = n; const uint32_t* desc_arg = s.blen; uint32_t* hist_arg = s.hist; const u64* misc_arg = s.misc;
         uint32_t* rt_arg = s.row_total;
         bool packed_arg = packed;
-        void* args[] = {&n_arg, &bufs, &desc_arg, &hist_arg, &misc_arg, &rt_arg, &packed_arg};
+        const uint32_t* flag_arg = run_flag;
+        void* args[] = {&n_arg, &bufs, &desc_arg, &hist_arg, &misc_arg, &rt_arg, &packed_arg, &flag_arg};
         cudaError_t ce = cudaLaunchCooperativeKernel((void*)demux_sort_coop_kernel, dim3(kSortBlocks), dim3(kSortThreads), args, 0, st);
         if (ce == cudaSuccess) { coop_done = true; count_launch(ctx); }
         else { (void)cudaGetLastError(); ctx->coop_sort = false; }      // not supported here: fall back for good
     }
     if (!coop_done) {
         for (int pass = 0; pass < kSortPasses; pass++) {
-            demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc, packed);
-            demux_rowscan_kernel<<<kRadix / kRowScanWarps, 32 * kRowScanWarps, 0, st>>>(s.hist, pass, s.misc, s.row_total);
-            demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc, s.row_total, packed);
+            demux_hist_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc, packed, run_flag);
+            demux_rowscan_kernel<<<kRadix / kRowScanWarps, 32 * kRowScanWarps, 0, st>>>(s.hist, pass, s.misc, s.row_total, run_flag);
+            demux_scatter_kernel<<<kSortBlocks, kSortThreads, 0, st>>>(n, bufs, s.blen, pass, s.hist, s.misc, s.row_total, packed, run_flag);
         }
         count_launch(ctx, 3 * kSortPasses);
     }
     const u64 nblk = demux_emit_blocks(n);
-    const int dst_mode = !gathered ? 0 : gathered_cap <= 0xffffffffull ? 1 : 2;
-    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, first_only, packed);
-    demux_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, s.blk_heads, s.blk_bytes);
+    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, first_only, packed, run_flag);
+    demux_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, s.blk_heads, s.blk_bytes, run_flag);
     demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, nblk,
-                                                              max_streams, uniq_sid, uniq_session, (u64*)csr, perm, k_out,
-                                                              (u64*)gathered_off, dst_mode, first_only, packed);
+                                                              max_streams, uniq_sid, uniq_session, (u64*)csr, perm_sort, k_out,
+                                                              (u64*)gathered_off, dst_mode, first_only, packed, run_flag);
     count_launch(ctx, 1 + 3);
     if (gathered) {
         const int rounds = copy_tile_rounds(ctx, n, ctx->occ_gather);
         demux_gather_kernel<<<copy_grid(ctx, n, rounds, ctx->occ_gather), 256, 0, st>>>(n, s.misc, bufs, desc, in, gathered,
-                                                                    gathered_cap, k_out, max_streams, dst_mode, rounds);
+                                                                    gathered_cap, k_out, max_streams, dst_mode, rounds, run_flag);
         count_launch(ctx);
     }
     CUDA_TRY(ctx, cudaGetLastError());
@@ -741,6 +796,33 @@ int32_t p2pt_frame_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const p2pt_desc
                                       uint64_t* gathered_off, void* scratch, uint64_t scratch_bytes, void* stream) {
     return demux_device_impl(ctx, n, desc, session, in, max_streams, uniq_sid, uniq_session, csr, perm, k_out, gathered,
                              gathered_cap, gathered_off, scratch, scratch_bytes, stream, false);
+}
+
+uint64_t p2pt_frame_decode_demux_scratch_bytes(uint64_t n) {
+    const uint64_t nn = n ? n : 1;
+    return align256(demux_scratch_bytes(nn)) + align256(24 * nn) + align256(4 * nn);
+}
+
+int32_t p2pt_frame_decode_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, const uint64_t* in_off,
+                                             const uint32_t* session, p2pt_desc* desc,
+                                             uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                             uint64_t* csr, uint32_t* perm, uint32_t* k_out,
+                                             uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off,
+                                             void* scratch, uint64_t scratch_bytes, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n && (!in_off || !scratch)) return set_err(ctx, P2PT_ERR_ARG, "frame_decode_demux: null in_off or scratch");
+    if (n && scratch_bytes < p2pt_frame_decode_demux_scratch_bytes(n))
+        return set_err(ctx, P2PT_ERR_CAPACITY, "frame_decode_demux: scratch too small");
+    DemuxFused f;
+    const uint64_t nn = n ? n : 1;
+    f.in_off = in_off;
+    f.desc_user = desc;
+    uint8_t* p = (uint8_t*)scratch + align256(demux_scratch_bytes(nn));
+    f.desc_work = desc ? desc : (p2pt_desc*)p;
+    p += align256(24 * nn);
+    f.perm_work = perm ? perm : (uint32_t*)p;
+    return demux_device_impl(ctx, n, nullptr, session, in, max_streams, uniq_sid, uniq_session, csr, perm, k_out, gathered,
+                             gathered_cap, gathered_off, scratch, scratch_bytes, stream, false, &f);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -1173,6 +1255,74 @@ int32_t p2pt_frame_demux_batch(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* desc,
             if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: gathered_cap too small");
             if (gathered_off[k]) CUDA_TRY(ctx, cudaMemcpyAsync(gathered, d_g, gathered_off[k], cudaMemcpyDeviceToHost, st));
         }
+    }
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    lg.dismiss();
+    return P2PT_OK;
+}
+
+// The reader loop of proxy.rs:109-170 / serve.rs:82-156 on frames that are already plaintext: decode, demux and
+// body gather in one call.  Frames and offsets go up once; descriptors and perm come back only if asked for.
+int32_t p2pt_frame_decode_demux_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* in, const uint64_t* in_off,
+                                      const uint32_t* session, p2pt_desc* desc,
+                                      uint32_t max_streams, uint32_t* uniq_sid, uint32_t* uniq_session,
+                                      uint64_t* csr, uint32_t* perm, uint32_t* k_out,
+                                      uint8_t* gathered, uint64_t gathered_cap, uint64_t* gathered_off) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!uniq_sid || !csr || !k_out) return set_err(ctx, P2PT_ERR_ARG, "frame_decode_demux: null output");
+    if (n == 0) { *k_out = 0; csr[0] = 0; if (gathered_off) gathered_off[0] = 0; return P2PT_OK; }
+    if (!in_off) return set_err(ctx, P2PT_ERR_ARG, "frame_decode_demux: null in_off");
+    if (gathered && !gathered_off) return set_err(ctx, P2PT_ERR_ARG, "frame_decode_demux: gather needs gathered_off");
+    if (n > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "frame_decode_demux: n must fit in 32 bits");
+    if (!offsets_monotonic(in_off, n)) return set_err(ctx, P2PT_ERR_ARG, "frame_decode_demux: offsets must be non-decreasing");
+    const size_t ibytes = in_off[n] - in_off[0];
+    if (ibytes && !in) return set_err(ctx, P2PT_ERR_ARG, "frame_decode_demux: null input");
+    DeviceGuard dg(ctx->device);
+    LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_frame_decode_demux_batch");
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
+    const uint64_t sbytes = p2pt_frame_decode_demux_scratch_bytes(n);
+    const size_t gcap = gathered ? (size_t)gathered_cap : 0;
+    if (int32_t r = arena_reserve(ctx, L, pad256(8 * (n + 1)) + pad256(4 * n) + pad256(ibytes + 1) + pad256(24 * n) +
+                                           2 * pad256(4 * ((size_t)max_streams + 1)) + 2 * pad256(8 * ((size_t)max_streams + 1)) +
+                                           pad256(4 * n) + 256 + pad256(gcap + 1) + pad256(sbytes) + 8192)) return r;
+    uint64_t* d_io = arena_take<uint64_t>(L, n + 1);
+    uint32_t* d_sess = arena_take<uint32_t>(L, n);
+    uint8_t* d_in = arena_take<uint8_t>(L, ibytes + 1);
+    p2pt_desc* d_desc = arena_take<p2pt_desc>(L, n);
+    uint32_t* d_uniq = arena_take<uint32_t>(L, (size_t)max_streams + 1);
+    uint32_t* d_usess = arena_take<uint32_t>(L, (size_t)max_streams + 1);
+    uint64_t* d_csr = arena_take<uint64_t>(L, (size_t)max_streams + 1);
+    uint64_t* d_goff = arena_take<uint64_t>(L, (size_t)max_streams + 1);
+    uint32_t* d_perm = arena_take<uint32_t>(L, n);
+    uint32_t* d_k = arena_take<uint32_t>(L, 1);
+    uint8_t* d_g = arena_take<uint8_t>(L, gcap + 1);
+    uint8_t* d_scratch = arena_take<uint8_t>(L, sbytes);
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_io, in_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
+    if (session) CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, st));
+    if (ibytes) CUDA_TRY(ctx, cudaMemcpyAsync(d_in, in + in_off[0], ibytes, cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_frame_decode_demux_batch_device(ctx, n, d_in - in_off[0], d_io, session ? d_sess : nullptr,
+                                                         desc ? d_desc : nullptr, max_streams, d_uniq,
+                                                         uniq_session ? d_usess : nullptr, d_csr, perm ? d_perm : nullptr, d_k,
+                                                         gathered ? d_g : nullptr, gathered_cap,
+                                                         gathered_off ? d_goff : nullptr, d_scratch, sbytes, st)) return r;
+    if (desc) CUDA_TRY(ctx, cudaMemcpyAsync(desc, d_desc, 24 * n, cudaMemcpyDeviceToHost, st));
+    uint32_t k = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&k, d_k, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    *k_out = k;
+    if (k > max_streams) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_decode_demux: more streams than max_streams");
+    CUDA_TRY(ctx, cudaMemcpyAsync(uniq_sid, d_uniq, 4 * (size_t)k, cudaMemcpyDeviceToHost, st));
+    if (uniq_session) CUDA_TRY(ctx, cudaMemcpyAsync(uniq_session, d_usess, 4 * (size_t)k, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(csr, d_csr, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, st));
+    if (gathered_off) CUDA_TRY(ctx, cudaMemcpyAsync(gathered_off, d_goff, 8 * ((size_t)k + 1), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    const uint64_t m = csr[k];
+    if (m && perm) CUDA_TRY(ctx, cudaMemcpyAsync(perm, d_perm, 4 * m, cudaMemcpyDeviceToHost, st));
+    if (gathered) {
+        if (gathered_off[k] > gathered_cap) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_decode_demux: gathered_cap too small");
+        if (gathered_off[k]) CUDA_TRY(ctx, cudaMemcpyAsync(gathered, d_g, gathered_off[k], cudaMemcpyDeviceToHost, st));
     }
     CUDA_TRY(ctx, wait_stream(ctx, L, st));
     lg.dismiss();

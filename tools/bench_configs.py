@@ -61,9 +61,23 @@ def codec_config(n, P, sse):
     dec = lambda: ctx.call("p2pt_frame_decode_batch_device", n, frames, d["frame_off"], desc, s)
     dmx = lambda: ctx.call("p2pt_frame_demux_batch_device", n, desc, None, frames, ms, uniq, None, csr, perm, k, None, 0, None, scratch, sb, s)
     dmg = lambda: ctx.call("p2pt_frame_demux_batch_device", n, desc, None, frames, ms, uniq, None, csr, perm, k, gathered, n * P, goff, scratch, sb, s)
+    fsb = int(ctx.lib.p2pt_frame_decode_demux_scratch_bytes(n))
+    fscratch = torch.empty(fsb, dtype=torch.uint8, device=dev)
+    # the reader loop in one call: frames in, per-stream bodies out (no descriptors, no perm)
+    fused = lambda: ctx.call("p2pt_frame_decode_demux_batch_device", n, frames, d["frame_off"], None, None, ms, uniq, None, csr, None, k,
+                             gathered, n * P, goff, fscratch, fsb, s)
     t_enc, t_dec, t_dmx, t_dmg = timeit(enc), timeit(dec), timeit(dmx), timeit(dmg)
     assert int(k.item()) == 4096
     t_both = timeit(lambda: (dec(), dmg()))
+    g_ref = gathered.clone(); goff_ref = goff.clone()
+    gathered.zero_()
+    t_fused = timeit(fused)
+    assert int(k.item()) == 4096 and torch.equal(gathered, g_ref) and torch.equal(goff, goff_ref)
+    ctx.set_option("direct_demux", 0)                   # the sorting path on the same batch, for comparison
+    t_both_sort = timeit(lambda: (dec(), dmg()))
+    assert torch.equal(gathered, g_ref)
+    ctx.set_option("direct_demux", 1)
+    del g_ref
     hf = np.zeros(n * (P + 5), np.uint8) if fast else None
     res = {}
     for nt in ((1, cores) if fast else ()):
@@ -92,6 +106,11 @@ def codec_config(n, P, sse):
         "decode_demux_gather": {"ms": t_both, "alg_bytes_per_frame": 2 * P + 41, "hbm_gbs": n * (2 * P + 41) / t_both / 1e6,
                                 "frac_of_hbm_peak": n * (2 * P + 41) / t_both / 1e6 / peak, "frames_per_s": n / t_both * 1e3,
                                 "payload_gbs": n * P / t_both / 1e6},
+        "decode_demux_gather_sorting_path": {"ms": t_both_sort, "frac_of_hbm_peak": n * (2 * P + 41) / t_both_sort / 1e6 / peak},
+        "decode_demux_gather_one_call": {"ms": t_fused, "call": "p2pt_frame_decode_demux_batch_device, desc = perm = NULL",
+                                         "alg_bytes_per_frame": 2 * P + 41, "hbm_gbs": n * (2 * P + 41) / t_fused / 1e6,
+                                         "frac_of_hbm_peak": n * (2 * P + 41) / t_fused / 1e6 / peak, "frames_per_s": n / t_fused * 1e3,
+                                         "payload_gbs": n * P / t_fused / 1e6},
     }
     out.update(res)
     return out

@@ -30,6 +30,8 @@ uniq = torch.empty(ms + 1, dtype=torch.int32, device=dev); csr = torch.empty(ms 
 goff = torch.empty(ms + 1, dtype=torch.int64, device=dev); perm = torch.empty(n, dtype=torch.int32, device=dev)
 k = torch.zeros(1, dtype=torch.int32, device=dev); gathered = torch.empty(n * P, dtype=torch.uint8, device=dev)
 s = torch.cuda.current_stream().cuda_stream
+fsb = int(ctx.lib.p2pt_frame_decode_demux_scratch_bytes(n))
+fscratch = torch.empty(fsb, dtype=torch.uint8, device=dev)
 for _ in range(reps):
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     ev[0].record()
@@ -41,6 +43,12 @@ for _ in range(reps):
     ev[3].record()
     torch.cuda.synchronize()
     tt = [ev[i].elapsed_time(ev[i + 1]) for i in range(3)]
-    print(f"encode {tt[0]:.3f} ms  decode {tt[1]:.3f} ms  demux+gather {tt[2]:.3f} ms")
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    ctx.call("p2pt_frame_decode_demux_batch_device", n, frames, d["frame_off"], None, None, ms, uniq, None, csr, None, k,
+             gathered, n * P, goff, fscratch, fsb, s)
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"encode {tt[0]:.3f} ms  decode {tt[1]:.3f} ms  demux+gather {tt[2]:.3f} ms  decode+demux+gather in one call {e0.elapsed_time(e1):.3f} ms")
 assert int(k.item()) == ms
 print("prof codec ok", n, "frames")
