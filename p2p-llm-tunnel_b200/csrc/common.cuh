@@ -190,4 +190,5 @@ __device__ __forceinline__ void quad_copy_bytes(uint8_t* dst, const uint8_t* src
 
 constexpr uint32_t kQuadCopyMax = 256;     // items up to this size take the 4-lane path
 
+
 }  // namespace p2pt

@@ -111,10 +111,23 @@ __device__ __forceinline__ uint32_t ld_u32_volatile(const uint32_t* p) {
 __device__ __forceinline__ void st_u32_volatile(uint32_t* p, uint32_t v) {
     asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
+// two 32-bit multiplicative hashes (stream id, session), top bits: a handful of instructions instead of a 64-bit mixer
+#ifndef P2PT_DIRECT_HASHMIX
+#define P2PT_DIRECT_HASHMIX 0
+#endif
+#ifndef P2PT_DIRECT_TAGS
+#define P2PT_DIRECT_TAGS 0
+#endif
 __device__ __forceinline__ uint32_t direct_hash(u64 k) {
+#if P2PT_DIRECT_HASHMIX
     k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33;
     return (uint32_t)k & (kDirectSlots - 1);
+#else
+    const uint32_t h = (uint32_t)k * 0x9E3779B1u ^ (uint32_t)(k >> 32) * 0x85EBCA77u;
+    return h >> 17;                                        // the top bits of a multiplicative hash are the good ones
+#endif
 }
+static_assert(kDirectSlots == (1 << 15), "direct_hash returns 15 bits");
 // named-barrier hand-over of the counters from one warp to the next (ids 1 .. kDirectWarps; 0 is __syncthreads)
 __device__ __forceinline__ void turn_wait(int warp) { asm volatile("bar.sync %0, 64;" :: "r"(1 + warp) : "memory"); }
 __device__ __forceinline__ void turn_pass(int next_warp) { asm volatile("bar.arrive %0, 64;" :: "r"(1 + next_warp) : "memory"); }
@@ -199,6 +212,7 @@ template <bool FROM_FRAMES>
 __global__ void __launch_bounds__(kDirectThreads, 3) demux_direct_rank_kernel(const DirectArgs a) {
     extern __shared__ __align__(16) u64 bins[];         // per id: (frames << 32 | body bytes) of this block so far
     __shared__ uint32_t s_maxid;
+    __shared__ uint8_t tag[kDirectIds];                 // per id: a lane that holds it (duplicate test inside a round, below)
     for (int j = threadIdx.x; j < kDirectIds; j += kDirectThreads) bins[j] = 0;
     if (threadIdx.x == 0) s_maxid = 0;
     __syncthreads();
@@ -274,36 +288,50 @@ __global__ void __launch_bounds__(kDirectThreads, 3) demux_direct_rank_kernel(co
                 body[r] = (valid[r] && (type == 11 || type == 21)) ? d1.x : 0u;
             }
         }
-        // ---- groups of equal keys inside each round of 32; the lowest lane of a group resolves the id
-        uint32_t peers[R], id[R];
-        int leader[R];
-        bool need[R];
+        // ---- dense ids first (every decodable frame looks its key up), then the groups of equal ids inside each
+        //      round of 32 from thirteen ballots.  MATCH.ANY on the 64-bit keys was the bottleneck of this kernel:
+        //      its unit takes about 8 cycles per distinct value and warp, and SSE frames of 4096 interleaved
+        //      streams are all distinct (measured 260 us of MATCH unit time for 10 M frames); ballots cost the same
+        //      whatever the data.
+        uint32_t id[R];
 #pragma unroll
-        for (int r = 0; r < R; r++) {
-            // every lane takes part (no branch around MATCH, the four of them overlap); a frame that does not count
-            // gets a key of its own and is masked out of the groups afterwards
-            const u64 mk = valid[r] ? key[r] : (0xffffffffffffff00ull | (unsigned)lane);
-            const uint32_t vm = __ballot_sync(0xffffffffu, valid[r]);
-            const uint32_t mm = __match_any_sync(0xffffffffu, mk);
-            peers[r] = valid[r] ? (mm & vm) : 0u;
-            leader[r] = valid[r] ? __ffs(peers[r]) - 1 : lane;
-            need[r] = valid[r] && leader[r] == lane;
-            mybytes += body[r];
-        }
-        direct_lookup(need, key, id, a.s);
+        for (int r = 0; r < R; r++) mybytes += body[r];
+        direct_lookup(valid, key, id, a.s);
+        uint32_t peers[R];
         u64 pre[R];
         bool ok[R];
 #pragma unroll
         for (int r = 0; r < R; r++) {
-            id[r] = __shfl_sync(0xffffffffu, id[r], leader[r]);
             ok[r] = valid[r] && id[r] < (uint32_t)kDirectIds;
-            // body bytes of the group in front of this lane: only lanes of groups with several members matter
-            uint32_t pb = 0;
-            for (uint32_t m = __ballot_sync(0xffffffffu, (peers[r] & (peers[r] - 1)) != 0); m; m &= m - 1) {
-                const int src = __ffs(m) - 1;
-                const uint32_t v = __shfl_sync(0xffffffffu, body[r], src);
-                if (((peers[r] >> src) & 1u) && src < lane) pb += v;
+            // Do two lanes of this round hold the same id?  Usually not (4096 interleaved streams: one round in nine):
+            // every lane writes its number to the id's tag and reads it back; lanes that share an id read ONE value
+            // (one shared-memory instruction, one address), so at most one of them finds its own number.  Another warp
+            // writing the same tag in between can only make a lane see a foreign number - a needless slow path,
+            // never a missed duplicate.
+#if P2PT_DIRECT_TAGS
+            if (ok[r]) tag[id[r]] = (uint8_t)lane;
+            __syncwarp();
+            const bool mine = !ok[r] || tag[id[r]] == (uint8_t)lane;
+#else
+            const bool mine = false;
+#endif
+            uint32_t pm = 1u << lane, pb = 0;
+            if (!__all_sync(0xffffffffu, mine)) {
+                pm = __ballot_sync(0xffffffffu, ok[r]);
+#pragma unroll
+                for (int b = 0; b < 13; b++) {
+                    static_assert(kDirectIds <= (1 << 13), "thirteen id bits");
+                    const uint32_t bm = __ballot_sync(0xffffffffu, (id[r] >> b) & 1u);
+                    pm &= bm ^ (((id[r] >> b) & 1u) - 1u);        // lanes whose bit b equals mine
+                }
+                // body bytes of the group in front of this lane: only lanes of groups with several members matter
+                for (uint32_t m = __ballot_sync(0xffffffffu, ok[r] && (pm & (pm - 1)) != 0); m; m &= m - 1) {
+                    const int src = __ffs(m) - 1;
+                    const uint32_t v = __shfl_sync(0xffffffffu, body[r], src);
+                    if (((pm >> src) & 1u) && src < lane) pb += v;
+                }
             }
+            peers[r] = ok[r] ? pm : 0u;
             pre[r] = ((u64)__popc(peers[r] & lt) << 32) | pb;
             if (ok[r] && id[r] + 1 > maxid1) maxid1 = id[r] + 1;
         }
@@ -440,17 +468,27 @@ __global__ void __launch_bounds__(1024) demux_direct_prefix_kernel(
     }
 }
 
-// Frames in arrival order -> perm and the per-stream bodies.  Same tiles and copies as demux_gather_kernel.
+// Frames in arrival order -> perm and the per-stream bodies.  Same tiles and copies as demux_gather_kernel: lane l
+// holds the metadata of frame l of the tile; four lanes per short frame in rounds of eight frames, the whole warp
+// per long one.  When every frame of the tile is at most 64 bytes and lands on whole aligned vectors (bodies that
+// are multiples of 16 bytes - the fixed-size SSE chunk of BASELINE.json config #4) the four rounds issue all their
+// loads before the first store: taken one after the other each round waited for its own loads, and the kernel sat
+// at 81 % long-scoreboard stalls.  (A frame per LANE - all 32 in flight - measured ten times slower: 3.8 ms.)
 template <bool FROM_FRAMES>
-__global__ void __launch_bounds__(256, P2PT_GATHER_MIN_BLOCKS) demux_direct_gather_kernel(
-    const DirectArgs a, uint8_t* __restrict__ gathered, u64 gathered_cap, uint32_t* __restrict__ perm,
-    const uint32_t* __restrict__ k_out, uint32_t max_streams, int rounds) {
+#ifndef P2PT_DIRECT_GATHER_BLOCKS
+#define P2PT_DIRECT_GATHER_BLOCKS P2PT_GATHER_MIN_BLOCKS
+#endif
+__global__ void __launch_bounds__(256, P2PT_DIRECT_GATHER_BLOCKS) demux_direct_gather_kernel(
+    const DirectArgs a, const uint8_t* __restrict__ in, uint8_t* __restrict__ gathered, u64 gathered_cap,
+    uint32_t* __restrict__ perm, const uint32_t* __restrict__ k_out, uint32_t max_streams, int rounds) {
     if (a.s.ctl[0]) return;
     if (*k_out > max_streams) return;
     const int lane = threadIdx.x & 31, quad = lane >> 2, q = lane & 3;
     const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
     const int tile = 8 * rounds;
+    // (Keeping the metadata of the next two tiles in flight while a tile is copied - a two-stage software pipeline -
+    // measured slower: 293 .. 507 us instead of 313 on 10 M x 64 B, 736 instead of 437 us on 1 M x 1200 B.)
     for (u64 i0 = warp * tile; i0 < a.n; i0 += nwarps * tile) {
         const u64 i = i0 + lane;
         const u64* row = a.s.matrix + (i0 / a.per) * kDirectIds;      // the whole tile lies in one rank block's share
@@ -458,40 +496,63 @@ __global__ void __launch_bounds__(256, P2PT_GATHER_MIN_BLOCKS) demux_direct_gath
         uint32_t len = 0;
         if (lane < tile && i < a.n) {
             const uint32_t f = a.s.fid[i];
+            const uint32_t l = a.s.loc[i];
+            u64 po; uint32_t pl;
+            if (FROM_FRAMES) {
+                const u64 fo = __ldg(a.in_off + i);
+                po = fo + 5; pl = (uint32_t)(__ldg(a.in_off + i + 1) - fo - 5);
+            } else {
+                const uint2* d = reinterpret_cast<const uint2*>(a.desc_in + i);
+                const uint2 d0 = __ldg(d), d1 = __ldg(d + 1);
+                po = ((u64)d0.y << 32) | d0.x; pl = d1.x;
+            }
             if (f != kNoId) {
                 const u64 b = __ldg(row + f);
                 if (perm) perm[(b >> 32) + a.s.rank[i]] = (uint32_t)i;
-                const uint32_t l = a.s.loc[i];
                 if (gathered && l != kNoLoc) {
                     o = (b & 0xffffffffull) + l;
-                    u64 po; uint32_t pl;
-                    if (FROM_FRAMES) {
-                        const u64 fo = __ldg(a.in_off + i);
-                        po = fo + 5; pl = (uint32_t)(__ldg(a.in_off + i + 1) - fo - 5);
-                    } else {
-                        const uint2* d = reinterpret_cast<const uint2*>(a.desc_in + i);
-                        const uint2 d0 = __ldg(d), d1 = __ldg(d + 1);
-                        po = ((u64)d0.y << 32) | d0.x; pl = d1.x;
-                    }
                     if (o <= gathered_cap && pl <= gathered_cap - o) { len = pl; so = po; }   // overflow: caller sees it in gathered_off[k]
                 }
             }
         }
-        if (__all_sync(0xffffffffu, len <= kQuadCopyMax)) {
+        if (rounds == 4 && __all_sync(0xffffffffu, len <= 64 && (((uintptr_t)(gathered + o) | len) & 15) == 0)) {
+            uint4 va[4], vb[4];
+            uint8_t* dv[4];
+            unsigned sh[4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int f = 8 * r + quad;
+                const u64 fso = __shfl_sync(0xffffffffu, so, f), fo = __shfl_sync(0xffffffffu, o, f);
+                const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
+                const uint8_t* src = in + fso;
+                sh[r] = (unsigned)((uintptr_t)src & 15);
+                const uint8_t* sb = src - sh[r] + 16 * q;
+                dv[r] = nullptr;
+                va[r] = vb[r] = make_uint4(0, 0, 0, 0);
+                if (16u * q < flen) {                          // this lane's vector of the frame: bytes [16 q, 16 q + 16)
+                    dv[r] = gathered + fo + 16 * q;
+                    va[r] = ldg128(sb);
+                    if (sh[r]) vb[r] = ldg128(sb + 16);        // holds item bytes whenever the source is not aligned
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+                if (dv[r]) stg128(dv[r], sh[r] ? funnel16(va[r], vb[r], sh[r]) : va[r]);
+        } else if (__all_sync(0xffffffffu, len <= kQuadCopyMax)) {
 #pragma unroll
             for (int r = 0; r < 4; r++) {
                 if (r >= rounds) break;
                 const int f = 8 * r + quad;
                 const u64 fso = __shfl_sync(0xffffffffu, so, f), fo = __shfl_sync(0xffffffffu, o, f);
                 const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
-                if (flen) quad_copy_bytes(gathered + fo, a.in + fso, flen, q);
+                if (flen) quad_copy_bytes(gathered + fo, in + fso, flen, q);
             }
         } else {
 #pragma unroll 1
             for (int f = 0; f < tile; f++) {
                 const u64 fso = __shfl_sync(0xffffffffu, so, f), fo = __shfl_sync(0xffffffffu, o, f);
                 const uint32_t flen = __shfl_sync(0xffffffffu, len, f);
-                if (flen) warp_copy_bytes(gathered + fo, a.in + fso, flen, lane);
+                if (flen) warp_copy_bytes(gathered + fo, in + fso, flen, lane);
             }
         }
     }

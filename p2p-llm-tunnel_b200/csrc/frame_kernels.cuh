@@ -844,16 +844,21 @@ __device__ __forceinline__ DemuxQuad demux_load_quad(u64 j, u64 m, u64 n, const 
 
 __global__ void __launch_bounds__(kScanThreads) demux_blocksum_kernel(
     u64 n, const DemuxBufs bufs, const uint32_t* __restrict__ blen,
-    const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes, bool first_only, bool packed,
+    const u64* __restrict__ misc, uint32_t* __restrict__ blk_heads, u64* __restrict__ blk_bytes, u64 nblk, bool first_only, bool packed,
     const uint32_t* run_flag) {
     if (demux_skip(run_flag)) return;
     const int fb = demux_src_buffer(misc, kSortPasses);
     const u64 m = demux_valid_count(n, misc);
-    const u64 j = ((u64)blockIdx.x * kScanThreads + threadIdx.x) * kDemuxItems;
-    const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen, first_only, packed);
-    HeadBytes tot;
-    (void)block_scan_excl(qd.sum, tot);
-    if (threadIdx.x == 0) { blk_heads[blockIdx.x] = tot.heads; blk_bytes[blockIdx.x] = tot.bytes; }
+    // one step per scan block; as the direct path's fallback the grid is small (a launch of thousands of blocks
+    // that only look at the flag costs 10+ us) and every block takes several steps
+    for (u64 vb = blockIdx.x; vb < nblk; vb += gridDim.x) {
+        const u64 j = (vb * kScanThreads + threadIdx.x) * kDemuxItems;
+        const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen, first_only, packed);
+        HeadBytes tot;
+        (void)block_scan_excl(qd.sum, tot);
+        if (threadIdx.x == 0) { blk_heads[vb] = tot.heads; blk_bytes[vb] = tot.bytes; }
+        __syncthreads();
+    }
 }
 
 // single block: exclusive scan of the per-block sums, in place; element [nblk] receives the total
@@ -894,12 +899,13 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
     u64* __restrict__ dst64 = bufs.keys[fb ^ 1];
     uint32_t* __restrict__ dst32 = reinterpret_cast<uint32_t*>(bufs.keys[fb ^ 1]);
     const u64 m = demux_valid_count(n, misc);
-    const u64 j = ((u64)blockIdx.x * kScanThreads + threadIdx.x) * kDemuxItems;
+    for (u64 vb = blockIdx.x; vb < nblk; vb += gridDim.x) {       // see demux_blocksum_kernel
+    const u64 j = (vb * kScanThreads + threadIdx.x) * kDemuxItems;
     const DemuxQuad qd = demux_load_quad(j, m, n, bufs.keys[fb], bufs.idx[fb], blen, first_only, packed);
     HeadBytes tot;
     HeadBytes ex = block_scan_excl(qd.sum, tot);
-    uint32_t heads = blk_heads[blockIdx.x] + ex.heads;
-    u64 bytes = blk_bytes[blockIdx.x] + ex.bytes;
+    uint32_t heads = blk_heads[vb] + ex.heads;
+    u64 bytes = blk_bytes[vb] + ex.bytes;
     if (j + kDemuxItems <= m) *reinterpret_cast<uint4*>(perm + j) = make_uint4(qd.ix[0], qd.ix[1], qd.ix[2], qd.ix[3]);
 #pragma unroll
     for (int e = 0; e < kDemuxItems; e++) {
@@ -926,6 +932,8 @@ __global__ void __launch_bounds__(kScanThreads) demux_emit_kernel(
             csr[k] = m;
             if (gathered_off) gathered_off[k] = blk_bytes[nblk];
         }
+    }
+    __syncthreads();
     }
 }
 

@@ -84,7 +84,7 @@ struct p2pt_ctx {
     uint64_t chunk_bytes = 16u << 20;  // host-pointer calls move records in chunks of about this size
     uint32_t lut_slack = 0;        // bytes needed in front of the T-tables to reach 64 KiB alignment
     int gcm_g = 0;                 // forced group width (env P2PT_GCM_G), 0 = heuristic
-    int occ_encode = 4, occ_gather = 4;   // resident blocks per SM of the two copy kernels (set at create)
+    int occ_encode = 4, occ_gather = 4, occ_dgather = 4;   // resident blocks per SM of the copy kernels (set at create)
     size_t zc_cap = 0;             // size of every lane's mapped buffer (0: no mapped memory here, small-call path off)
     uint64_t small_call_bytes = 256u << 10;  // staging footprint up to which a call takes the mapped-buffer path (0 = never)
 };
@@ -476,6 +476,8 @@ static int32_t ctx_init(p2pt_ctx* ctx, int device, const cudaDeviceProp& prop) {
     CUDA_TRY(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_gather, demux_gather_kernel, 256, 0));
     if (ctx->occ_encode < 1) ctx->occ_encode = 1;
     if (ctx->occ_gather < 1) ctx->occ_gather = 1;
+    CUDA_TRY(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_dgather, demux_direct_gather_kernel<true>, 256, 0));
+    if (ctx->occ_dgather < 1) ctx->occ_dgather = 1;
     if (const char* g = getenv("P2PT_GCM_G")) {
         int v = atoi(g);
         if (v == 4 || v == 8 || v == 16 || v == 32) ctx->gcm_g = v;
@@ -717,10 +719,10 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         demux_direct_prefix_kernel<<<kDirectIds / 32, 1024, 0, st>>>(ds, nb, max_streams, uniq_sid, uniq_session, (u64*)csr, (u64*)gathered_off);
         count_launch(ctx, 3);
         if (gathered || perm) {
-            const int rounds = copy_tile_rounds(ctx, n, ctx->occ_gather);
-            const unsigned grid = copy_grid(ctx, n, rounds, ctx->occ_gather);
-            if (fused) demux_direct_gather_kernel<true><<<grid, 256, 0, st>>>(a, gathered, gathered_cap, perm, k_out, max_streams, rounds);
-            else demux_direct_gather_kernel<false><<<grid, 256, 0, st>>>(a, gathered, gathered_cap, perm, k_out, max_streams, rounds);
+            const int rounds = copy_tile_rounds(ctx, n, ctx->occ_dgather);
+            const unsigned grid = copy_grid(ctx, n, rounds, ctx->occ_dgather);
+            if (fused) demux_direct_gather_kernel<true><<<grid, 256, 0, st>>>(a, in, gathered, gathered_cap, perm, k_out, max_streams, rounds);
+            else demux_direct_gather_kernel<false><<<grid, 256, 0, st>>>(a, in, gathered, gathered_cap, perm, k_out, max_streams, rounds);
             count_launch(ctx);
         }
         CUDA_TRY(ctx, cudaGetLastError());
@@ -770,9 +772,10 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         count_launch(ctx, 3 * kSortPasses);
     }
     const u64 nblk = demux_emit_blocks(n);
-    demux_blocksum_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, first_only, packed, run_flag);
+    const unsigned scan_grid = run_flag && nblk > (u64)ctx->sm_count ? (unsigned)ctx->sm_count : (unsigned)nblk;
+    demux_blocksum_kernel<<<scan_grid, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, nblk, first_only, packed, run_flag);
     demux_scan_blocksums_kernel<<<1, kScanThreads, 0, st>>>(nblk, s.blk_heads, s.blk_bytes, run_flag);
-    demux_emit_kernel<<<(unsigned)nblk, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, nblk,
+    demux_emit_kernel<<<scan_grid, kScanThreads, 0, st>>>(n, bufs, s.blen, s.misc, s.blk_heads, s.blk_bytes, nblk,
                                                               max_streams, uniq_sid, uniq_session, (u64*)csr, perm_sort, k_out,
                                                               (u64*)gathered_off, dst_mode, first_only, packed, run_flag);
     count_launch(ctx, 1 + 3);
