@@ -112,20 +112,9 @@ __device__ __forceinline__ void st_u32_volatile(uint32_t* p, uint32_t v) {
     asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
 // two 32-bit multiplicative hashes (stream id, session), top bits: a handful of instructions instead of a 64-bit mixer
-#ifndef P2PT_DIRECT_HASHMIX
-#define P2PT_DIRECT_HASHMIX 0
-#endif
-#ifndef P2PT_DIRECT_TAGS
-#define P2PT_DIRECT_TAGS 0
-#endif
 __device__ __forceinline__ uint32_t direct_hash(u64 k) {
-#if P2PT_DIRECT_HASHMIX
-    k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33;
-    return (uint32_t)k & (kDirectSlots - 1);
-#else
     const uint32_t h = (uint32_t)k * 0x9E3779B1u ^ (uint32_t)(k >> 32) * 0x85EBCA77u;
     return h >> 17;                                        // the top bits of a multiplicative hash are the good ones
-#endif
 }
 static_assert(kDirectSlots == (1 << 15), "direct_hash returns 15 bits");
 // named-barrier hand-over of the counters from one warp to the next (ids 1 .. kDirectWarps; 0 is __syncthreads)
@@ -212,7 +201,6 @@ template <bool FROM_FRAMES>
 __global__ void __launch_bounds__(kDirectThreads, 3) demux_direct_rank_kernel(const DirectArgs a) {
     extern __shared__ __align__(16) u64 bins[];         // per id: (frames << 32 | body bytes) of this block so far
     __shared__ uint32_t s_maxid;
-    __shared__ uint8_t tag[kDirectIds];                 // per id: a lane that holds it (duplicate test inside a round, below)
     for (int j = threadIdx.x; j < kDirectIds; j += kDirectThreads) bins[j] = 0;
     if (threadIdx.x == 0) s_maxid = 0;
     __syncthreads();
@@ -303,33 +291,21 @@ __global__ void __launch_bounds__(kDirectThreads, 3) demux_direct_rank_kernel(co
 #pragma unroll
         for (int r = 0; r < R; r++) {
             ok[r] = valid[r] && id[r] < (uint32_t)kDirectIds;
-            // Do two lanes of this round hold the same id?  Usually not (4096 interleaved streams: one round in nine):
-            // every lane writes its number to the id's tag and reads it back; lanes that share an id read ONE value
-            // (one shared-memory instruction, one address), so at most one of them finds its own number.  Another warp
-            // writing the same tag in between can only make a lane see a foreign number - a needless slow path,
-            // never a missed duplicate.
-#if P2PT_DIRECT_TAGS
-            if (ok[r]) tag[id[r]] = (uint8_t)lane;
-            __syncwarp();
-            const bool mine = !ok[r] || tag[id[r]] == (uint8_t)lane;
-#else
-            const bool mine = false;
-#endif
-            uint32_t pm = 1u << lane, pb = 0;
-            if (!__all_sync(0xffffffffu, mine)) {
-                pm = __ballot_sync(0xffffffffu, ok[r]);
+            // (A cheaper test for "no two lanes share an id" - every lane writes its number to a per-id tag in shared
+            // memory and reads it back - measured slower: the 8 KiB of tags push the block over the 196 KiB shared-memory
+            // carve-out and L1 shrinks from 60 to 28 KiB: +73 us.  So did L2 prefetches of the next tile: no change.)
+            uint32_t pm = __ballot_sync(0xffffffffu, ok[r]), pb = 0;
 #pragma unroll
-                for (int b = 0; b < 13; b++) {
-                    static_assert(kDirectIds <= (1 << 13), "thirteen id bits");
-                    const uint32_t bm = __ballot_sync(0xffffffffu, (id[r] >> b) & 1u);
-                    pm &= bm ^ (((id[r] >> b) & 1u) - 1u);        // lanes whose bit b equals mine
-                }
-                // body bytes of the group in front of this lane: only lanes of groups with several members matter
-                for (uint32_t m = __ballot_sync(0xffffffffu, ok[r] && (pm & (pm - 1)) != 0); m; m &= m - 1) {
-                    const int src = __ffs(m) - 1;
-                    const uint32_t v = __shfl_sync(0xffffffffu, body[r], src);
-                    if (((pm >> src) & 1u) && src < lane) pb += v;
-                }
+            for (int b = 0; b < 13; b++) {
+                static_assert(kDirectIds <= (1 << 13), "thirteen id bits");
+                const uint32_t bm = __ballot_sync(0xffffffffu, (id[r] >> b) & 1u);
+                pm &= bm ^ (((id[r] >> b) & 1u) - 1u);            // lanes whose bit b equals mine
+            }
+            // body bytes of the group in front of this lane: only lanes of groups with several members matter
+            for (uint32_t m = __ballot_sync(0xffffffffu, ok[r] && (pm & (pm - 1)) != 0); m; m &= m - 1) {
+                const int src = __ffs(m) - 1;
+                const uint32_t v = __shfl_sync(0xffffffffu, body[r], src);
+                if (((pm >> src) & 1u) && src < lane) pb += v;
             }
             peers[r] = ok[r] ? pm : 0u;
             pre[r] = ((u64)__popc(peers[r] & lt) << 32) | pb;

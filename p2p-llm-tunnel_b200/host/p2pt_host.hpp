@@ -146,7 +146,7 @@ inline Bytes encode_batch(const Context& c, const std::vector<TunnelMessage>& ms
 
 // ---- batched reader / dispatcher ------------------------------------------------
 // The reference decodes one frame, takes a mutex, probes a HashMap and pushes one event, per frame.  Here a
-// whole batch is decoded and demultiplexed on the GPU (p2pt_frame_decode_batch + p2pt_frame_demux_batch) and
+// whole batch is decoded and demultiplexed on the GPU (p2pt_frame_decode_demux_batch) and
 // the host walks each stream's frames once, in arrival order: the same per-stream event sequences come out.
 namespace reader {
 
@@ -209,14 +209,14 @@ inline std::map<int64_t, std::vector<Routed>> decode_demux(const Context& c, con
     buf.assign(off[n] + 1, 0);
     for (size_t i = 0; i < n; i++) std::memcpy(buf.data() + off[i], frames[i].data(), frames[i].size());
     std::vector<p2pt_desc> desc(n);
-    c.check(p2pt_frame_decode_batch(c.get(), n, buf.data(), off.data(), desc.data()));
-    for (const auto& d : desc) decode_failures += d.status != P2PT_ST_OK;          // warn! + continue
     std::vector<uint32_t> uniq(n + 1), perm(n);
     std::vector<uint64_t> csr(n + 1), goff(n + 1);
     gathered.assign(off[n] + 1, 0);
     uint32_t k = 0;
-    c.check(p2pt_frame_demux_batch(c.get(), n, desc.data(), nullptr, buf.data(), off[n], (uint32_t)n, uniq.data(), nullptr,
-                                   csr.data(), perm.data(), &k, gathered.data(), off[n], goff.data()));
+    // decode + demux + body gather in ONE call (descriptors and perm wanted here: the host walks every frame)
+    c.check(p2pt_frame_decode_demux_batch(c.get(), n, buf.data(), off.data(), nullptr, desc.data(), (uint32_t)n, uniq.data(), nullptr,
+                                          csr.data(), perm.data(), &k, gathered.data(), off[n], goff.data()));
+    for (const auto& d : desc) decode_failures += d.status != P2PT_ST_OK;          // warn! + continue
     std::map<int64_t, std::vector<Routed>> out;
     for (uint32_t s = 0; s < k; s++) {
         uint64_t cursor = goff[s];

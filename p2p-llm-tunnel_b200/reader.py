@@ -4,8 +4,7 @@
   ServeReassembler /root/reference/tunnel/src/serve.rs:82-156   (pending_requests :65)
 
 The reference decodes one frame, takes a mutex, probes a HashMap and pushes one event, per frame.
-Here a whole batch is decoded and demultiplexed on the GPU (p2pt_frame_decode_batch +
-p2pt_frame_demux_batch) and the host walks each stream's frames once, in arrival order -- the same
+Here a whole batch is decoded and demultiplexed on the GPU (p2pt_frame_decode_demux_batch) and the host walks each stream's frames once, in arrival order -- the same
 per-stream event sequences come out.  Frames whose JSON stream id differs from their frame header
 (headers frames are routed by the JSON field, proxy.rs:129 / serve.rs:113-118) are merged back by
 arrival index so that even that corner behaves like the sequential loop.
@@ -27,9 +26,8 @@ class StreamEvent:                      # proxy.rs:28-37
 
 def _decode_demux(ctx, frames):
     buf, off = pack([bytes(f) for f in frames])
-    desc = ctx.frame_decode(buf, off)
-    r = ctx.frame_demux(desc, buf, max_streams=max(len(frames), 1))
-    return buf, desc, r
+    r = ctx.frame_decode_demux(buf, off, max_streams=max(len(frames), 1), gathered_cap=max(len(buf), 1), want_desc=True)
+    return buf, r["desc"], r
 
 
 def _per_target(desc, r, raw, header_type):

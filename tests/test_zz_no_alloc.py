@@ -7,7 +7,8 @@ synchronisation.  For them the demux scratch is a static device array inside the
 calls that entry point through the C ABI several times in a row (the second batch is smaller than the
 first, so the array still holds stale data) and requires the same bytes as the caller-scratch entry point
 produces AND as the CPU oracle produces, at the sizes where the library changes strategy (up to 1024
-frames a single-block kernel, above it the cooperative radix sort, and the stated maximum exactly),
+frames a single-block kernel; above it the sort-free path when the caller's max_streams is at most 8192,
+else the cooperative radix sort; and the stated maximum exactly),
 checks that the amount of free device memory is the same before and after the call, and that a
 batch beyond the stated maximum is refused.  It is collected last (file name) and needs nothing from
 the other tests, so it passes alone in a fresh process too.
@@ -32,9 +33,9 @@ def _frames(rng, n, n_streams, n_sessions):
     return types, sids, payload, pay_off, session
 
 
-def _run(ctx, torch, entry, n, d_desc, d_sess, d_buf, gcap, scratch=None):
+def _run(ctx, torch, entry, n, d_desc, d_sess, d_buf, gcap, scratch=None, ms=None):
     dev = d_desc.device
-    ms = n
+    ms = ms or n
     o = {"uniq": torch.zeros(ms + 1, dtype=torch.int32, device=dev), "usess": torch.zeros(ms + 1, dtype=torch.int32, device=dev),
          "csr": torch.zeros(ms + 1, dtype=torch.int64, device=dev), "perm": torch.zeros(n, dtype=torch.int32, device=dev),
          "k": torch.zeros(1, dtype=torch.int32, device=dev), "g": torch.zeros(max(gcap, 1), dtype=torch.uint8, device=dev),
@@ -63,8 +64,9 @@ def test_no_alloc_demux_matches_caller_scratch_entry_point(ctx):
     rng = np.random.default_rng(2026)
     # calls in a row on the one shared array: large, smaller (stale data from the first still there), the
     # single-block sizes (n <= 1024), one frame, and exactly the maximum
-    for n, streams, sessions in ((40000, 300, 64), (7001, 5, 3), (1024, 40, 4), (700, 9, 2), (1, 1, 1),
-                                 (MAX_FRAMES, 4096, 16), (1025, 1000, 1)):
+    for n, streams, sessions, ms in ((40000, 300, 64, None), (7001, 5, 3, None), (1024, 40, 4, None), (700, 9, 2, None),
+                                     (1, 1, 1, None), (MAX_FRAMES, 4096, 16, None), (1025, 1000, 1, None),
+                                     (MAX_FRAMES, 2000, 4, 8192), (100000, 300, 4, 1200)):
         types, sids, payload, pay_off, session = _frames(rng, n, streams, sessions)
         buf, off = ctx.frame_encode(types, sids, payload, pay_off)
         buf = buf.copy()
@@ -77,8 +79,8 @@ def test_no_alloc_demux_matches_caller_scratch_entry_point(ctx):
         gcap = int(payload.size)
         sb = int(ctx.lib.p2pt_frame_demux_scratch_bytes(n))
         scratch = torch.zeros(sb, dtype=torch.uint8, device=dev)
-        ref = _run(ctx, torch, "p2pt_frame_demux_batch_device", n, d_desc, d_sess, d_buf, gcap, scratch)
-        got = _run(ctx, torch, "p2pt_frame_demux_batch_device_noalloc", n, d_desc, d_sess, d_buf, gcap)
+        ref = _run(ctx, torch, "p2pt_frame_demux_batch_device", n, d_desc, d_sess, d_buf, gcap, scratch, ms)
+        got = _run(ctx, torch, "p2pt_frame_demux_batch_device_noalloc", n, d_desc, d_sess, d_buf, gcap, None, ms)
         assert got["k"] == ref["k"] and got["k"] > 0
         for key in ("uniq", "usess", "csr", "perm", "goff", "g"):
             assert np.array_equal(got[key], ref[key]), (n, key)         # bit-exact, like every other parity test
