@@ -5,10 +5,14 @@
 // most 1200 bytes, one per packet here, and checksums every packet with CRC32c (crc 3.4.0,
 // Cargo.lock:420-421).  Layout: RFC 4960 3.1 / 3.3.1 / appendix B.
 //
-// HBM-bound byte work again.  One warp per packet: the packet is staged in shared memory, every
-// lane runs a slice-by-4 table CRC over its own contiguous segment, the 32 partial remainders are
-// shifted to their place with a carry-less multiply by x^(8 * bytes after the segment) mod P and
-// XOR-reduced by shuffles, then the packet goes out as aligned words.
+// HBM-bound byte work again.  One warp per packet.  The packet (or the fragment a packet is built from)
+// comes into shared memory as whole ALIGNED 16-byte vectors by asynchronous copies (cp.async), double
+// buffered: the next packet's bytes are in flight while this one is checksummed, so a warp never waits
+// for global memory (the first version staged through registers and sat at 40 % long-scoreboard
+// stalls).  Every lane runs a table CRC over its own contiguous segment of the staged bytes - wherever
+// they lie: a packet that is not word-aligned in memory is read through a funnel shift - the 32 partial
+// remainders are shifted to their place with a carry-less multiply by x^(8 * bytes after the segment)
+// mod P and XOR-reduced by shuffles; the packetiser writes its output as aligned 16-byte vectors.
 #pragma once
 #include "common.cuh"
 #include "gcm_math.cuh"
@@ -20,12 +24,14 @@ namespace p2pt {
 constexpr uint32_t kSctpMaxPayload = P2PT_SCTP_MAX_PAYLOAD;          // 1200
 constexpr uint32_t kSctpMaxPacket = 28 + kSctpMaxPayload;            // 1228
 constexpr int kSctpWarps = 32;                                       // warps (packets in flight) per block, 1 block per SM
-constexpr uint32_t kSctpBufBytes = 1280;                             // per-warp staging buffer
-constexpr uint32_t kSctpPktAt = 20;                                  // packet byte 0 sits at buffer byte 20 ->
-                                                                     // payload (packet byte 28) at 48, 16-aligned;
-                                                                     // an optional DTLS header occupies 7..19
+// One staging buffer: kSctpFront bytes in front (zeros for the checksum's leading words; the packetiser builds its
+// headers there), then the raw aligned vectors (15 + 1228 + 15 bytes at most), then one spare vector (an unaligned
+// word read looks one word ahead).  Two buffers per warp.
+constexpr uint32_t kSctpFront = 96;
+constexpr uint32_t kSctpRawBytes = 1264;
+constexpr uint32_t kSctpBufBytes = kSctpFront + kSctpRawBytes + 16;
 constexpr uint32_t kCrcLutBytes = 65536;                             // 256 rows x (T0 | T1) x 32 replicas x 4 B
-constexpr uint32_t kSctpStageBytes = kSctpWarps * kSctpBufBytes;
+constexpr uint32_t kSctpStageBytes = 2 * kSctpWarps * kSctpBufBytes;
 
 // slice-by-4 tables and x^(8k) mod P for k = 0..1279, reflected representation; filled by the host
 __device__ uint32_t g_crc_tab[4][256];
@@ -34,10 +40,8 @@ __device__ uint32_t g_crc_xpow[1280];
 // Shared-memory map, like the record kernel's: the CRC tables sit on a 64 KiB boundary of the shared
 // window so that one PRMT builds a lookup address (byte << 8 | lane << 2 | base); every table entry is
 // replicated 32x, lane l only touches bank l, so data-dependent lookups never conflict.  The staging
-// buffers live in the gap below the tables when it is large enough, else behind them.
-__host__ __device__ constexpr uint32_t sctp_smem_bytes(uint32_t slack) {
-    return slack + kCrcLutBytes + (slack >= kSctpStageBytes ? 0u : kSctpStageBytes);
-}
+// buffers live behind the tables.
+__host__ __device__ constexpr uint32_t sctp_smem_bytes(uint32_t slack) { return slack + kCrcLutBytes + kSctpStageBytes; }
 
 struct CrcLut {
     uint32_t lb;     // 64 KiB-aligned shared address of the tables + 4 * lane
@@ -57,26 +61,105 @@ __device__ __forceinline__ uint32_t crc_word(const CrcLut& t, uint32_t crc, uint
     return t.look<0, 1>(c1) ^ t.look<1, 0>(c1) ^ (c1 >> 16);
 }
 
-// (a * b) mod P for reflected 32-bit residues: carry-less product (integer-multiply-with-holes,
-// gcm_math.cuh), realigned by one bit, then the upper 32 coefficients are folded with one word step.
-__device__ __forceinline__ uint32_t crc_mulmod(const CrcLut& t, uint32_t a, uint32_t b) {
-    uint32_t bm[kGhashClasses];
-    ghash_classes(b, bm);
+// (a * b) mod P for reflected 32-bit residues, b given as its pre-masked classes: carry-less product
+// (integer-multiply-with-holes, gcm_math.cuh), realigned by one bit, then the upper 32 coefficients are
+// folded with one word step.
+__device__ __forceinline__ uint32_t crc_mulmod(const CrcLut& t, uint32_t a, const uint32_t (&bm)[kGhashClasses]) {
     const uint64_t p = clmul32(a, bm) << 1;
     return crc_word(t, 0u, (uint32_t)p) ^ (uint32_t)(p >> 32);
 }
 
-// CRC32c of the staged packet (nwords <= 320 32-bit words at `words`; the caller has zeroed the checksum
-// field, word 2).  All 32 lanes call; every lane gets the result.
-// The segments are aligned to the END of the packet: lane l owns the kCrcSeg words that end
-// (31 - l) * kCrcSeg words before the end, so the shift x^(8 * bytes after) is a per-lane constant
-// (`xp`, loaded once per kernel), every lane runs exactly kCrcSeg steps (words before the packet
-// start read as zero, which leaves a zero register unchanged), and the 0xFFFFFFFF init value is
-// added by linearity from a table indexed by the packet length.
 constexpr int kCrcSeg = 10;                              // 32 lanes x 10 words = 1280 bytes >= the largest packet
 __device__ uint32_t g_crc_init[kCrcSeg * 32 + 1];        // init-value contribution for a packet of w words
 
-__device__ __forceinline__ uint32_t warp_crc32c(const CrcLut& t, const uint32_t* words, uint32_t nwords, int lane, uint32_t xp) {
+// CRC32c of a staged packet of nwords <= 320 words whose byte 0 lies at byte offset pkt0 of the buffer (any
+// alignment; ALIGNED = pkt0 is a multiple of 4, the usual case).  The checksum field must hold zero and the 40
+// bytes in front of the packet must be zero.  All 32 lanes call; every lane gets the result.
+// The segments are aligned to the END of the packet: lane l owns the kCrcSeg words that end
+// (31 - l) * kCrcSeg words before the end, so the shift x^(8 * bytes after) is a per-lane constant (its classes
+// `xpm`, computed once per kernel), every lane runs the same kCrcSeg steps without a bounds test (words before
+// the packet start read the zeros in front of it, which leave a zero register unchanged; a lane whose whole
+// segment lies before the packet skips them), and the 0xFFFFFFFF init value is added by linearity from a table
+// indexed by the packet length.
+template <bool ALIGNED>
+__device__ __forceinline__ uint32_t warp_crc32c(const CrcLut& t, const uint8_t* buf, uint32_t pkt0, uint32_t nwords, int lane,
+                                                const uint32_t (&xpm)[kGhashClasses]) {
+    const int first = (int)nwords - (32 - lane) * kCrcSeg;          // may be negative: leading zero words
+    uint32_t c = 0;
+    if (first > -kCrcSeg) {
+        const uint32_t* q = reinterpret_cast<const uint32_t*>(buf) + (int)(pkt0 >> 2) + first;
+        if (ALIGNED) {
+#pragma unroll
+            for (int i = 0; i < kCrcSeg; i++) c = crc_word(t, c, q[i]);
+        } else {
+            const unsigned sh = (pkt0 & 3) * 8;
+            uint32_t lo = q[0];
+#pragma unroll
+            for (int i = 0; i < kCrcSeg; i++) {
+                const uint32_t hi = q[i + 1];
+                c = crc_word(t, c, __funnelshift_r(lo, hi, sh));
+                lo = hi;
+            }
+        }
+    }
+    uint32_t part = crc_mulmod(t, c, xpm);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part ^= __shfl_xor_sync(0xffffffffu, part, o);
+    return ~(part ^ g_crc_init[nwords]);
+}
+
+// packet word i (32-bit, little-endian load) of a staged packet
+__device__ __forceinline__ uint32_t staged_word(const uint8_t* buf, uint32_t pkt0, int i) {
+    const uint32_t* q = reinterpret_cast<const uint32_t*>(buf) + (pkt0 >> 2) + i;
+    return __funnelshift_r(q[0], q[1], (pkt0 & 3) * 8);
+}
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// Start the copy of the aligned 16-byte vectors that cover [src, src + len) into the raw region of `buf`
+// (byte `src` lands at offset kSctpFront + (src & 15)).  An aligned vector that holds at least one byte of the
+// item is always readable, and no other vector is touched.  One commit group per call, also when len == 0.
+__device__ __forceinline__ void stage_async(uint8_t* buf, const uint8_t* src, uint32_t len, int lane) {
+    const uint32_t sa = (uint32_t)((uintptr_t)src & 15);
+    const uint32_t nvec = len ? (sa + len + 15) >> 4 : 0;
+#pragma unroll
+    for (int it = 0; it < 3; it++) {                                  // <= 79 vectors
+        const uint32_t v = lane + 32 * it;
+        if (v < nvec) cp_async16(buf + kSctpFront + 16 * v, src - sa + 16 * (size_t)v);
+    }
+    cp_async_commit();
+}
+
+// common prologue of the two packet kernels: fill the replicated tables, hand every warp its two buffers (fronts
+// zeroed), fetch the lane's constant CRC shift (see warp_crc32c)
+__device__ __forceinline__ uint8_t* sctp_smem_setup(uint8_t* dyn_smem, CrcLut& lut, uint32_t (&xpm)[kGhashClasses]) {
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(dyn_smem);
+    const uint32_t tbase = (sbase + 0xffffu) & ~0xffffu;
+    uint32_t* tabs = reinterpret_cast<uint32_t*>(dyn_smem + (tbase - sbase));
+    for (int idx = threadIdx.x; idx < 256 * 32; idx += blockDim.x) {
+        const int x = idx >> 5, l = idx & 31;
+        tabs[x * 64 + l] = g_crc_tab[0][x];
+        tabs[x * 64 + 32 + l] = g_crc_tab[1][x];
+    }
+    lut.lb = tbase + 4u * (threadIdx.x & 31);
+    ghash_classes(g_crc_xpow[(31 - (threadIdx.x & 31)) * kCrcSeg * 4], xpm);
+    uint8_t* mine = dyn_smem + (tbase - sbase) + kCrcLutBytes + (threadIdx.x >> 5) * (2 * kSctpBufBytes);
+    for (uint32_t w = threadIdx.x & 31; w < 2 * kSctpBufBytes / 4; w += 32) reinterpret_cast<uint32_t*>(mine)[w] = 0;
+    __syncthreads();
+    return mine;
+}
+
+// ---- the packetiser stages through registers (the asynchronous-copy form of it measured slower: 1.10 instead of
+//      0.93 ms per 1 M packets - byte-wise header and padding stores, and its message metadata still waits) ----
+constexpr uint32_t kSctpPktAt = 20;      // packet byte 0 sits at buffer byte 20 -> payload (packet byte 28) at 48, 16-aligned;
+                                         // an optional DTLS header occupies 7..19
+// CRC32c of a packet staged word-aligned at `words` (nwords <= 320; checksum field zeroed by the caller).  Same end-aligned
+// segments as warp_crc32c, with a bounds test per word instead of zeros in front.
+__device__ __forceinline__ uint32_t warp_crc32c_words(const CrcLut& t, const uint32_t* words, uint32_t nwords, int lane, const uint32_t (&xpm)[kGhashClasses]) {
     const int first = (int)nwords - (32 - lane) * kCrcSeg;          // may be negative: leading zero words
     uint32_t c = 0;
 #pragma unroll
@@ -85,7 +168,7 @@ __device__ __forceinline__ uint32_t warp_crc32c(const CrcLut& t, const uint32_t*
         const uint32_t v = wi >= 0 ? words[wi] : 0u;
         c = crc_word(t, c, v);
     }
-    uint32_t part = crc_mulmod(t, c, xp);
+    uint32_t part = crc_mulmod(t, c, xpm);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) part ^= __shfl_xor_sync(0xffffffffu, part, o);
     return ~(part ^ g_crc_init[nwords]);
@@ -123,25 +206,6 @@ __device__ __forceinline__ uint4 stage_load16(const uint8_t* src, uint32_t v, ui
     return r;
 }
 
-// common prologue of the two packet kernels: fill the replicated tables, hand every warp its buffer,
-// fetch the lane's constant CRC shift (see warp_crc32c)
-__device__ __forceinline__ uint8_t* sctp_smem_setup(uint8_t* dyn_smem, CrcLut& lut, uint32_t& xp) {
-    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(dyn_smem);
-    const uint32_t tbase = (sbase + 0xffffu) & ~0xffffu;
-    uint32_t* tabs = reinterpret_cast<uint32_t*>(dyn_smem + (tbase - sbase));
-    for (int idx = threadIdx.x; idx < 256 * 32; idx += blockDim.x) {
-        const int x = idx >> 5, l = idx & 31;
-        tabs[x * 64 + l] = g_crc_tab[0][x];
-        tabs[x * 64 + 32 + l] = g_crc_tab[1][x];
-    }
-    __syncthreads();
-    lut.lb = tbase + 4u * (threadIdx.x & 31);
-    xp = g_crc_xpow[(31 - (threadIdx.x & 31)) * kCrcSeg * 4];
-    const uint32_t slack = tbase - sbase;
-    uint8_t* stage = slack >= kSctpStageBytes ? dyn_smem : dyn_smem + slack + kCrcLutBytes;
-    return stage + (threadIdx.x >> 5) * kSctpBufBytes;
-}
-
 // smem byte stream [start, start + nbytes) of a 4-byte aligned buffer -> dst (any alignment):
 // aligned 32-bit stores built from two adjacent shared words, byte stores only at the two ends.
 __device__ __forceinline__ void smem_stream_to_global(const uint8_t* sbuf, uint32_t start, uint32_t nbytes,
@@ -177,8 +241,8 @@ struct SctpPacketizeArgs {
 __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_packetize_kernel(const SctpPacketizeArgs a) {
     extern __shared__ __align__(16) uint8_t sctp_dyn_smem[];
     CrcLut tabs;
-    uint32_t xp;
-    uint8_t* buf = sctp_smem_setup(sctp_dyn_smem, tabs, xp);
+    uint32_t xpm[kGhashClasses];
+    uint8_t* buf = sctp_smem_setup(sctp_dyn_smem, tabs, xpm);          // the first of the warp's two buffers is all it needs
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     uint32_t* bw = reinterpret_cast<uint32_t*>(buf);
     const bool dtls = a.epoch != nullptr;
@@ -231,7 +295,7 @@ __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_packetize_kernel(cons
                 if (v * 16 < padded) *reinterpret_cast<uint4*>(buf + kSctpPktAt + 28 + 16 * v) = stage_load16<true>(m + off, v, fl);
             }
             __syncwarp();
-            const uint32_t crc = warp_crc32c(tabs, bw + kSctpPktAt / 4, plen >> 2, lane, xp);
+            const uint32_t crc = warp_crc32c_words(tabs, bw + kSctpPktAt / 4, plen >> 2, lane, xpm);
             if (lane == 0) bw[kSctpPktAt / 4 + 2] = crc;                     // stored little-endian (webrtc-sctp put_u32_le)
             __syncwarp();
             smem_stream_to_global(buf, kSctpPktAt - hdr, plen + hdr, a.out + oo, lane);
@@ -252,61 +316,80 @@ struct SctpUnpackArgs {
 __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_unpack_kernel(const SctpUnpackArgs a) {
     extern __shared__ __align__(16) uint8_t sctp_dyn_smem[];
     CrcLut tabs;
-    uint32_t xp;
-    uint8_t* buf = sctp_smem_setup(sctp_dyn_smem, tabs, xp);
+    uint32_t xpm[kGhashClasses];
+    uint8_t* bufs = sctp_smem_setup(sctp_dyn_smem, tabs, xpm);
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const uint32_t* bw = reinterpret_cast<const uint32_t*>(buf);
     const u64 warp = (u64)blockIdx.x * kSctpWarps + wib, nwarps = (u64)gridDim.x * kSctpWarps;
+    // a packet we handle: headroom + 12 .. 1228 bytes, a multiple of 4 (else it is reported malformed and not staged)
+    auto sized = [&](u64 ilen) { return !(ilen < (u64)a.headroom + 12 || ilen - a.headroom > kSctpMaxPacket || ((ilen - a.headroom) & 3)); };
+    int cur = 0;
+    u64 io = 0, ilen = 0;
+    if (warp < a.n) {
+        io = __ldg(a.in_off + warp); ilen = __ldg(a.in_off + warp + 1) - io;
+        stage_async(bufs, a.in + io + a.headroom, sized(ilen) ? (uint32_t)(ilen - a.headroom) : 0u, lane);
+    }
     for (u64 i = warp; i < a.n; i += nwarps) {
-        const u64 io = __ldg(a.in_off + i), ilen = __ldg(a.in_off + i + 1) - io;
+        uint8_t* buf = bufs + cur * kSctpBufBytes;
+        const u64 inext = i + nwarps;
+        u64 io_n = 0, ilen_n = 0;
+        if (inext < a.n) {                                                   // the next packet's bytes fly while this one is checked
+            io_n = __ldg(a.in_off + inext); ilen_n = __ldg(a.in_off + inext + 1) - io_n;
+            stage_async(bufs + (cur ^ 1) * kSctpBufBytes, a.in + io_n + a.headroom, sized(ilen_n) ? (uint32_t)(ilen_n - a.headroom) : 0u, lane);
+        } else {
+            cp_async_commit();
+        }
+        cp_async_wait_all_but_one();
+        __syncwarp();
         uint32_t st = P2PT_ST_OK;
         uint32_t flags = 0, tsn = 0, sid = 0, ssn = 0, pp = 0, plen_pay = 0;
-        if (ilen < (u64)a.headroom + 12 || ilen - a.headroom > kSctpMaxPacket || ((ilen - a.headroom) & 3)) {
+        if (!sized(ilen)) {
             st = P2PT_ST_SCTP_MALFORMED;                                     // not a single-DATA-chunk packet we handle
         } else {
             const uint32_t n = (uint32_t)(ilen - a.headroom);
-            const uint8_t* p = a.in + io + a.headroom;
+            const uint32_t sa = (uint32_t)((uintptr_t)(a.in + io + a.headroom) & 15);
+            const uint32_t pkt0 = kSctpFront + sa;
+            if ((uint32_t)lane < sa) buf[kSctpFront + lane] = 0;             // bytes of the first vector in front of the packet
             __syncwarp();
-#pragma unroll
-            for (int it = 0; it < 3; it++) {
-                const uint32_t v = lane + 32 * it;
-                if (v * 16 < n) *reinterpret_cast<uint4*>(buf + 16 * v) = stage_load16<false>(p, v, n);
-            }
+            const uint32_t theirs = staged_word(buf, pkt0, 2);
             __syncwarp();
-            const uint32_t theirs = bw[2];
+            if (lane < 4) buf[pkt0 + 8 + lane] = 0;                          // checksum field counts as zero
             __syncwarp();
-            if (lane == 0) reinterpret_cast<uint32_t*>(buf)[2] = 0;          // checksum field counts as zero
-            __syncwarp();
-            const uint32_t crc = warp_crc32c(tabs, bw, n >> 2, lane, xp);
+            const uint32_t crc = (pkt0 & 3) ? warp_crc32c<false>(tabs, buf, pkt0, n >> 2, lane, xpm)
+                                            : warp_crc32c<true>(tabs, buf, pkt0, n >> 2, lane, xpm);
             if (crc != theirs) st = P2PT_ST_SCTP_BAD_CHECKSUM;               // checked first, like Packet::unmarshal
-            else if (n < 28 || buf[12] != 0) st = P2PT_ST_SCTP_MALFORMED;
+            else if (n < 28 || buf[pkt0 + 12] != 0) st = P2PT_ST_SCTP_MALFORMED;
             else {
-                const uint32_t w3 = bswap32(bw[3]);
+                const uint32_t w3 = bswap32(staged_word(buf, pkt0, 3));
                 const uint32_t clen = w3 & 0xffff;
                 if (clen < 16 || 12 + ((clen + 3) & ~3u) != n) st = P2PT_ST_SCTP_MALFORMED;
                 else {
-                    flags = (w3 >> 16) & 0xff; tsn = bswap32(bw[4]);
-                    const uint32_t w5 = bswap32(bw[5]);
-                    sid = w5 >> 16; ssn = w5 & 0xffff; pp = bswap32(bw[6]); plen_pay = clen - 16;
+                    flags = (w3 >> 16) & 0xff; tsn = bswap32(staged_word(buf, pkt0, 4));
+                    const uint32_t w5 = bswap32(staged_word(buf, pkt0, 5));
+                    sid = w5 >> 16; ssn = w5 & 0xffff; pp = bswap32(staged_word(buf, pkt0, 6)); plen_pay = clen - 16;
                 }
             }
         }
-        if (lane == 0) {
-            p2pt_sctp_chunk c;
-            c.tsn = tsn; c.stream_id = (uint16_t)sid; c.ssn = (uint16_t)ssn; c.ppid = pp;
-            c.flags = (uint8_t)flags; c.status = (uint8_t)st; c.pad[0] = c.pad[1] = 0;
-            a.info[i] = c;
-            // a descriptor p2pt_frame_demux_batch can order: key = TSN, "body" type so the gather takes it.  TSNs are
-            // serial numbers (RFC 4960 1.6: arithmetic modulo 2^32) and the peer picks where they start, so a message
-            // may straddle 0xFFFFFFFF -> 0: with tsn_base the key is the distance from the association's cumulative
-            // ack point, which orders any window of fewer than 2^32 TSNs correctly (webrtc-sctp compares with sna32)
-            p2pt_desc d;
-            d.pay_off = io + a.headroom + 28; d.pay_len = plen_pay; d.stream_id = a.tsn_base ? tsn - __ldg(a.tsn_base + i) : tsn;
-            d.msg_type = 21; d.status = (uint8_t)st;
-            for (int q = 0; q < 6; q++) d.pad[q] = 0;
-            if (st != P2PT_ST_OK) { d.pay_off = io; d.pay_len = 0; }
-            a.desc[i] = d;
+        // every lane holds the (warp-uniform) results: lanes 0..3 store the four words of the chunk info, lanes 4..6
+        // the three 8-byte words of a descriptor p2pt_frame_demux_batch can order: key = TSN, "body" type so the
+        // gather takes it.  TSNs are serial numbers (RFC 4960 1.6: arithmetic modulo 2^32) and the peer picks where
+        // they start, so a message may straddle 0xFFFFFFFF -> 0: with tsn_base the key is the distance from the
+        // association's cumulative ack point, which orders any window of fewer than 2^32 TSNs correctly (webrtc-sctp
+        // compares with sna32)
+        {
+            const uint32_t key = a.tsn_base ? tsn - __ldg(a.tsn_base + i) : tsn;
+            const u64 poff = st == P2PT_ST_OK ? io + a.headroom + 28 : io;
+            const uint32_t plen = st == P2PT_ST_OK ? plen_pay : 0u;
+            if (lane < 4) {
+                const uint32_t w = lane == 0 ? tsn : lane == 1 ? (sid & 0xffffu) | (ssn << 16) : lane == 2 ? pp : (flags & 0xffu) | (st << 8);
+                reinterpret_cast<uint32_t*>(a.info + i)[lane] = w;
+            } else if (lane < 7) {
+                const uint2 w = lane == 4 ? make_uint2((uint32_t)poff, (uint32_t)(poff >> 32)) : lane == 5 ? make_uint2(plen, key)
+                                          : make_uint2(21u | (st << 8), 0u);
+                reinterpret_cast<uint2*>(a.desc + i)[lane - 4] = w;
+            }
         }
+        __syncwarp();                                                        // the buffer is staged into again next round
+        cur ^= 1; io = io_n; ilen = ilen_n;
     }
 }
 
