@@ -29,7 +29,7 @@ struct SessionKey {
     uint32_t rk[44];        // FIPS-197 key schedule, little-endian words
     uint32_t iv;            // 4-byte implicit nonce (write IV), little-endian word
     uint32_t pad[3];
-    uint32_t hpow[32][4];   // H^1 .. H^32, U128 word order
+    uint32_t hpow[32][4];   // H^1 .. H^32, each times alpha^-1 (gf128_premul: the form gf128_mul_pre takes), U128 word order
 };
 static_assert(sizeof(SessionKey) == 704, "SessionKey layout");
 
@@ -198,22 +198,11 @@ __device__ __forceinline__ void clmul64_s(uint32_t lo, uint32_t hi, uint32_t mid
     out_lo = p ^ (m << 32);
     out_hi = q ^ (m >> 32);
 }
+// the multiplier rows in the slot come from a key power that was pre-multiplied by alpha^-1 (gf128_premul): no shift
 __device__ __forceinline__ U128 gf128_reduce(uint64_t pl, uint64_t ph, uint64_t ql, uint64_t qh, uint64_t rl, uint64_t rh) {
     rl ^= pl ^ ql;
     rh ^= ph ^ qh;
-    uint64_t v0 = pl, v1 = ph ^ rl, v2 = ql ^ rh, v3 = qh;
-    v3 = (v3 << 1) | (v2 >> 63);
-    v2 = (v2 << 1) | (v1 >> 63);
-    v1 = (v1 << 1) | (v0 >> 63);
-    v0 = (v0 << 1);
-    v2 ^= v0 ^ (v0 >> 1) ^ (v0 >> 2) ^ (v0 >> 7);
-    v1 ^= (v0 << 63) ^ (v0 << 62) ^ (v0 << 57);
-    v3 ^= v1 ^ (v1 >> 1) ^ (v1 >> 2) ^ (v1 >> 7);
-    v2 ^= (v1 << 63) ^ (v1 << 62) ^ (v1 << 57);
-    U128 z;
-    z.w[0] = (uint32_t)v2; z.w[1] = (uint32_t)(v2 >> 32);
-    z.w[2] = (uint32_t)v3; z.w[3] = (uint32_t)(v3 >> 32);
-    return z;
+    return gf128_fold<true>(pl, ph ^ rl, ql ^ rh, qh);
 }
 __device__ __forceinline__ U128 gf128_mul_s(const U128& x, uint32_t key_addr) {
     const uint32_t x0 = x.w[0], x1 = x.w[1], x2 = x.w[2], x3 = x.w[3];
@@ -265,7 +254,8 @@ __global__ void __launch_bounds__(128) session_expand_kernel(uint32_t n, const u
     ghash_key_prepare(H, hk);
     U128 p = H;
     for (int e = 0; e < 32; e++) {
-        sk->hpow[e][0] = p.w[0]; sk->hpow[e][1] = p.w[1]; sk->hpow[e][2] = p.w[2]; sk->hpow[e][3] = p.w[3];
+        const U128 pm = gf128_premul(p);
+        sk->hpow[e][0] = pm.w[0]; sk->hpow[e][1] = pm.w[1]; sk->hpow[e][2] = pm.w[2]; sk->hpow[e][3] = pm.w[3];
         p = gf128_mul(p, hk);
     }
 }
@@ -716,7 +706,7 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
             U128 hf; hf.w[0] = v.x; hf.w[1] = v.y; hf.w[2] = v.z; hf.w[3] = v.w;
             GhashKey kF;
             ghash_key_prepare(hf, kF);
-            acc = gf128_mul(acc, kF);                            // lanes that never ran hold 0
+            acc = gf128_mul_pre(acc, kF);                        // lanes that never ran hold 0
         }
 #pragma unroll
         for (int o = G >> 1; o > 0; o >>= 1) {
