@@ -165,6 +165,35 @@ struct CtrRound1 {
         o2 = q2; o3 = q3;
         aes128_rounds<2>(lut, keys, o0, o1, o2, o3);
     }
+    // Records of at most 254 blocks (4064 bytes: every DTLS record that fits a path MTU) only ever count in the LAST
+    // counter byte, so after round 1 a single state word depends on the counter and of the 16 look-ups of round 2 twelve
+    // are the same for every block of the record: they, round key 2 and the constant look-up of round 1 are folded into
+    // four words once per record (kept where round key 1 lay, which nobody reads after prepare()).  A block then costs
+    // 1 + 4 look-ups in rounds 1 and 2 instead of 2 + 16.
+    template <class Lut, class Keys>
+    __device__ __forceinline__ void fold_round2(const Lut& lut, const Keys& keys, uint32_t& q0, uint32_t& q1, uint32_t& q2, uint32_t& q3) const {
+        const uint4 k2 = keys.get(2);
+        const uint32_t v1 = c1 ^ lut.template look<2, 2>(r3), v2 = c2, v3 = c3;      // counter bytes 0..2 are zero
+        q0 = lut.template look<1, 1>(v1) ^ lut.template look<2, 2>(v2) ^ lut.template look<3, 3>(v3) ^ k2.x;
+        q1 = lut.template look<0, 0>(v1) ^ lut.template look<1, 1>(v2) ^ lut.template look<2, 2>(v3) ^ k2.y;
+        q2 = lut.template look<0, 0>(v2) ^ lut.template look<1, 1>(v3) ^ lut.template look<3, 3>(v1) ^ k2.z;
+        q3 = lut.template look<0, 0>(v3) ^ lut.template look<2, 2>(v1) ^ lut.template look<3, 3>(v2) ^ k2.w;
+    }
+    template <class Lut, class Keys>
+    static __device__ __forceinline__ void block_small(const Lut& lut, const Keys& keys, uint32_t slot, uint32_t r1_off, uint32_t ctr,
+                                                       uint32_t& o0, uint32_t& o1, uint32_t& o2, uint32_t& o3) {
+        uint32_t r3w, c0w, q0, q1, q2, q3;
+        asm volatile("ld.shared.u32 %0, [%1+12];" : "=r"(r3w) : "r"(slot));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c0w) : "r"(slot + r1_off));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4+16];" : "=r"(q0), "=r"(q1), "=r"(q2), "=r"(q3) : "r"(slot));
+        const uint32_t s3 = (ctr << 24) ^ r3w;                                        // bswap32(ctr) for ctr < 256
+        const uint32_t v0 = c0w ^ lut.template look<3, 3>(s3);
+        o0 = q0 ^ lut.template look<0, 0>(v0);
+        o1 = q1 ^ lut.template look<3, 3>(v0);
+        o2 = q2 ^ lut.template look<2, 2>(v0);
+        o3 = q3 ^ lut.template look<1, 1>(v0);
+        aes128_rounds<3>(lut, keys, o0, o1, o2, o3);
+    }
     // keystream block for counter ctr < 65536
     template <class Lut, class Keys>
     __device__ __forceinline__ void block(const Lut& lut, const Keys& keys, uint32_t ctr,
@@ -176,6 +205,10 @@ struct CtrRound1 {
         aes128_rounds<2>(lut, keys, o0, o1, o2, o3);
     }
 };
+
+// The keystream block of a record longer than 4064 bytes (its counters need two bytes), out of line: such records are
+// rare, and inlined beside block_small the second path cost the hot loop registers (spills at the 64-register cap).
+__device__ __noinline__ uint4 ctr_block_wide(uint32_t lut_lb, uint32_t slot, uint32_t r1_off, uint32_t ctr);
 
 // GF(2^128) multiply with the prepared multiplier in shared memory (9 rows of 4 class masks):
 // same arithmetic as gf128_mul in gcm_math.cuh, one LDS.128 per 32x32 product instead of 36 registers.
@@ -211,6 +244,14 @@ __device__ __forceinline__ U128 gf128_mul_s(const U128& x, uint32_t key_addr) {
     clmul64_s(x2, x3, x2 ^ x3, key_addr, 3, ql, qh);
     clmul64_s(x0 ^ x2, x1 ^ x3, x0 ^ x1 ^ x2 ^ x3, key_addr, 6, rl, rh);
     return gf128_reduce(pl, ph, ql, qh, rl, rh);
+}
+
+__device__ __noinline__ uint4 ctr_block_wide(uint32_t lut_lb, uint32_t slot, uint32_t r1_off, uint32_t ctr) {
+    SmemLut lut; lut.lb = lut_lb; lut.m8 = 1u << 8; lut.m16 = 1u << 16; lut.m24 = 1u << 24;
+    SmemKeys keys; keys.addr = slot;
+    uint4 o;
+    CtrRound1::block_parked(lut, keys, slot, r1_off, ctr, o.x, o.y, o.z, o.w);
+    return o;
 }
 
 // ---- session set-up: key schedule, H, H^1..H^32 (one thread per key) ------------------------------
@@ -519,9 +560,22 @@ __global__ void __launch_bounds__(kGcmThreads, 1) gcm_record_kernel(const GcmArg
         CtrRound1 r1;                                        // counters stay below 2^16: items are capped at 1 MB above
         r1.prepare(lut, rkeys, ivw, n0, n1);
 #if P2PT_GCM_PARK
-        if (j == 0) sts128(slot + kSlotR1, r1.c0, r1.c1, r1.c2, r1.c3);
+        const bool ctr_small = nc + 1 < 256;                 // every counter of the record (1 .. nc + 1) fits one byte
+        __syncwarp(gmask);                                   // everyone has read round keys 0 and 1
+        if (j == 0) {
+            sts128(slot + kSlotR1, r1.c0, r1.c1, r1.c2, r1.c3);
+            if (ctr_small) {
+                uint32_t q0, q1, q2, q3;
+                r1.fold_round2(lut, rkeys, q0, q1, q2, q3);
+                sts128(slot + 16, q0, q1, q2, q3);           // over round key 1
+            }
+        }
         __syncwarp(gmask);
-#define P2PT_KS(ctr, a0, a1, a2, a3) CtrRound1::block_parked(lut, rkeys, slot, kSlotR1, (ctr), a0, a1, a2, a3)
+#define P2PT_KS(ctr, a0, a1, a2, a3)                                                                   \
+    do {                                                                                               \
+        if (ctr_small) CtrRound1::block_small(lut, rkeys, slot, kSlotR1, (ctr), a0, a1, a2, a3);      \
+        else { const uint4 ks_ = ctr_block_wide(lut.lb, slot, kSlotR1, (ctr)); a0 = ks_.x; a1 = ks_.y; a2 = ks_.z; a3 = ks_.w; } \
+    } while (0)
 #else
 #define P2PT_KS(ctr, a0, a1, a2, a3) r1.block(lut, rkeys, (ctr), a0, a1, a2, a3)
 #endif
