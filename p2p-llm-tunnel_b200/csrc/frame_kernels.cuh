@@ -292,7 +292,7 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
     }
 }
 
-// ---- decode: one thread per frame ----------------------------------------------------------------
+// ---- decode: one thread per frame (offsets coalesced; the header itself is two aligned word loads) ------------
 __global__ void __launch_bounds__(256) frame_decode_kernel(
     u64 n, const uint8_t* __restrict__ in, const u64* __restrict__ in_off, p2pt_desc* __restrict__ desc,
     const uint32_t* run_flag) {
@@ -308,13 +308,17 @@ __global__ void __launch_bounds__(256) frame_decode_kernel(
             status = P2PT_ST_TOO_SHORT;
             if (len) type = __ldg(f);
         } else {
-            type = __ldg(f);
+            // the five header bytes lie inside the two aligned words that start at the frame's word: two loads, one
+            // funnel and one byte permute instead of five byte loads and four shifts
+            const unsigned sh = (unsigned)((uintptr_t)f & 3);
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(f - sh);
+            const u64 x = (((u64)__ldg(w + 1) << 32) | __ldg(w)) >> (8 * sh);
+            type = (uint32_t)x & 0xffu;
             if (!msg_type_valid(type)) {                // protocol.rs:161-163
                 status = P2PT_ST_UNKNOWN_TYPE;
             } else {
                 status = P2PT_ST_OK;
-                sid = ((uint32_t)__ldg(f + 1) << 24) | ((uint32_t)__ldg(f + 2) << 16) |
-                      ((uint32_t)__ldg(f + 3) << 8) | (uint32_t)__ldg(f + 4);    // :165 get_u32 (BE)
+                sid = __byte_perm((uint32_t)(x >> 8), 0, 0x0123);                // :165 get_u32 (BE)
                 poff = o + 5;
                 plen = (uint32_t)(len - 5);
             }
