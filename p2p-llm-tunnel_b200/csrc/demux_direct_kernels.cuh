@@ -11,11 +11,12 @@
 //            and keeps, per id, the running (frame count, body bytes) of ITS share in shared memory; a frame's
 //            position inside (block, id) is that running value when its turn comes.  The order inside a block is kept
 //            without block-wide barriers: warps take tiles of 128 consecutive frames, resolve ids and the prefix
-//            inside each group of 32 on their own (MATCH.ANY), and only the read-modify-write of the shared counters
-//            goes round the warps in turn, handed on through named barriers.
-//   streams  one block sorts the <= 8192 distinct keys (bitonic, shared memory), scans their totals and writes
-//            uniq_sid / uniq_session / csr / gathered_off.
-//   prefix   per id an exclusive scan of the per-block counters over the blocks, started at the stream's base.
+//            inside each group of 32 on their own (ballots on the id bits), and only the read-modify-write of the
+//            shared counters goes round the warps in turn, handed on through named barriers.
+//   streams  a key's stream number = the number of keys smaller than it, its base = the sum of their totals: all
+//            pairs of the <= 8192 distinct keys, spread over the machine (no sort of the keys either).
+//   prefix   per id an exclusive scan of the per-block counters over the blocks, started at the stream's base;
+//            writes uniq_sid / uniq_session / csr / gathered_off.
 //   gather   frames in arrival order (each DRAM sector read once): destination = matrix[block][id] + position.
 //
 // A batch that does not fit (more distinct keys than kDirectIds, 4 GiB or more of bodies, the one key the table
