@@ -28,11 +28,16 @@ namespace p2pt {
 
 constexpr int kDirectIds = 8192;                    // distinct (session, stream_id) keys the direct path can hold
 constexpr int kDirectSlots = 4 * kDirectIds;        // hash slots (load factor <= 0.25: most keys are found by the first probe)
-constexpr int kDirectWarps = 8;
+#ifndef P2PT_DIRECT_WARPS
+#define P2PT_DIRECT_WARPS 16
+#endif
+constexpr int kDirectWarps = P2PT_DIRECT_WARPS;     // 8 (three blocks per SM: 24 warps, 72 registers) or 16 (two blocks: 32 warps at
+                                                    // 60 registers, and 128 KiB of L1 left beside the counters): C4 rank 0.173 -> 0.153 ms
+constexpr int kDirectBlocksPerSm = kDirectWarps == 8 ? 3 : 2;
 constexpr int kDirectRounds = 4;                    // groups of 32 consecutive frames per warp and tile
 constexpr int kDirectThreads = 32 * kDirectWarps;
 constexpr int kDirectTile = kDirectThreads * kDirectRounds;      // 1024 frames per block iteration
-constexpr int kDirectMaxBlocks = 444;               // 3 resident blocks x 148 SMs
+constexpr int kDirectMaxBlocks = 148 * kDirectBlocksPerSm;      // every block resident
 constexpr uint32_t kNoLoc = 0xffffffffu;            // per-frame position: contributes nothing to the gather
 constexpr uint16_t kNoId = 0xffff;                  // per-frame id: not decodable
 constexpr uint32_t kDirectNone = 0xffffffffu;
@@ -119,8 +124,10 @@ __device__ __forceinline__ uint32_t direct_hash(u64 k) {
 }
 static_assert(kDirectSlots == (1 << 15), "direct_hash returns 15 bits");
 // named-barrier hand-over of the counters from one warp to the next (ids 1 .. kDirectWarps; 0 is __syncthreads)
-__device__ __forceinline__ void turn_wait(int warp) { asm volatile("bar.sync %0, 64;" :: "r"(1 + warp) : "memory"); }
-__device__ __forceinline__ void turn_pass(int next_warp) { asm volatile("bar.arrive %0, 64;" :: "r"(1 + next_warp) : "memory"); }
+// (with 16 warps all sixteen barriers are in use: id 0 is free between the kernel's first and last __syncthreads)
+constexpr int kTurnBase = kDirectWarps == 16 ? 0 : 1;
+__device__ __forceinline__ void turn_wait(int warp) { asm volatile("bar.sync %0, 64;" :: "r"(kTurnBase + warp) : "memory"); }
+__device__ __forceinline__ void turn_pass(int next_warp) { asm volatile("bar.arrive %0, 64;" :: "r"(kTurnBase + next_warp) : "memory"); }
 
 // One look at `slot` (its contents v just loaded) for `key`: 0 = resolved (id set), 1 = look at the same slot again
 // (its id is not published yet, or somebody took the slot in between), 2 = another key lives there, try the next slot.
@@ -199,7 +206,7 @@ __device__ __forceinline__ void direct_lookup(const bool (&need)[kDirectRounds],
 }
 
 template <bool FROM_FRAMES>
-__global__ void __launch_bounds__(kDirectThreads, 3) demux_direct_rank_kernel(const DirectArgs a) {
+__global__ void __launch_bounds__(kDirectThreads, kDirectBlocksPerSm) demux_direct_rank_kernel(const DirectArgs a) {
     extern __shared__ __align__(16) u64 bins[];         // per id: (frames << 32 | body bytes) of this block so far
     __shared__ uint32_t s_maxid;
     for (int j = threadIdx.x; j < kDirectIds; j += kDirectThreads) bins[j] = 0;

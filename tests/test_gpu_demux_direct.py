@@ -208,3 +208,24 @@ def test_fused_gather_into_a_buffer_that_is_too_small(ctx):
     o = exp["gathered_off"].astype(np.int64)
     first = exp["gathered"][: int(o[1])]
     assert np.array_equal(gh[: len(first)], first)
+
+
+def test_pipeline_open_demux_takes_the_direct_path(ctx):
+    """records -> open -> decode -> demux -> gather in one host call, with a stream bound the direct path accepts
+    (proxy.rs:109-170 from the DTLS records): same result as the oracle's open followed by its demux, one record tampered"""
+    from p2p_llm_tunnel_b200 import workload
+    keys, ivs = workload.sessions_keys(400, seed_shift=9)
+    ctx.sessions_load(keys, ivs, keys, ivs)
+    w = workload.pipeline_workload(400, 12, 200, seed_shift=9)
+    rec = ob.pipeline_seal(w, keys, ivs).copy()
+    rec[int(w["rec_off"][77]) + 40] ^= 4
+    r = ctx.pipeline_open_demux(w["session"], rec, w["rec_off"], max_streams=8192, gathered_cap=w["n"] * 200, want_out=True)
+    assert w["n"] > 1024 and list(np.nonzero(r["desc"]["status"])[0]) == [77]
+    exp = ob.frame_demux(r["desc"], r["out"], w["session"])
+    same(r, exp, KEYS + ("uniq_session",), "open+demux")
+    ctx.set_option("direct_demux", 0)
+    try:
+        r2 = ctx.pipeline_open_demux(w["session"], rec, w["rec_off"], max_streams=8192, gathered_cap=w["n"] * 200, want_out=True)
+    finally:
+        ctx.set_option("direct_demux", 1)
+    same(r, r2, KEYS + ("uniq_session",), "sorting path")
