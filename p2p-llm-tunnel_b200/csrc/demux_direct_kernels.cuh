@@ -364,9 +364,10 @@ __global__ void __launch_bounds__(kDirectThreads, kDirectBlocksPerSm) demux_dire
 // pairs, spread over the machine: 4096 keys are 256 blocks of 256 comparisons per thread - and add what they find
 // with atomics.  (A bitonic sort of the keys in one block took 63 us for 4096 keys; this takes a few.)
 constexpr int kOrderT = 256;
+constexpr int kOrderChunk = 128;           // keys a block compares its 256 keys against per step
 __global__ void __launch_bounds__(kOrderT) demux_direct_streams_kernel(
     const DirectScratch s, u64* __restrict__ csr, uint32_t* __restrict__ k_out, u64* __restrict__ gathered_off) {
-    __shared__ u64 ck[kOrderT], ct[kOrderT];
+    __shared__ u64 ck[kOrderChunk], ct[kOrderChunk];
     const uint32_t tid = threadIdx.x;
     const bool first_block = blockIdx.x == 0 && blockIdx.y == 0;
     const uint32_t nid = s.ctl[1];
@@ -380,22 +381,23 @@ __global__ void __launch_bounds__(kOrderT) demux_direct_streams_kernel(
         if (nid == 0) { csr[0] = 0; if (gathered_off) gathered_off[0] = 0; }
     }
     const uint32_t nb = (nid + kOrderT - 1) / kOrderT;
-    if (blockIdx.x >= nb || blockIdx.y >= nb) return;
+    if (blockIdx.x >= nb) return;
     const uint32_t id = blockIdx.x * kOrderT + tid;
     const u64 key = id < nid ? s.idkey[id] : 0ull;
     uint32_t cnt = 0;
     u64 sum = 0;                                                 // (frames << 32 | bytes) sums cannot carry: both totals fit 32 bits
-    for (uint32_t c = blockIdx.y; c < nb; c += gridDim.y) {
-        const uint32_t j0 = c * kOrderT;
+    const uint32_t nchunks = (nid + kOrderChunk - 1) / kOrderChunk;
+    for (uint32_t c = blockIdx.y; c < nchunks; c += gridDim.y) {
+        const uint32_t j0 = c * kOrderChunk;
         __syncthreads();
-        ck[tid] = j0 + tid < nid ? s.idkey[j0 + tid] : ~0ull;    // no real key is all ones (direct_lookup refuses it)
-        ct[tid] = j0 + tid < nid ? s.tot[j0 + tid] : 0ull;
+        if (tid < kOrderChunk) {
+            ck[tid] = j0 + tid < nid ? s.idkey[j0 + tid] : ~0ull;    // no real key is all ones (direct_lookup refuses it)
+            ct[tid] = j0 + tid < nid ? s.tot[j0 + tid] : 0ull;
+        }
         __syncthreads();
 #pragma unroll 16
-        for (int j = 0; j < kOrderT; j++) {
-            const bool less = ck[j] < key;
-            cnt += less ? 1u : 0u;
-            sum += less ? ct[j] : 0ull;
+        for (int j = 0; j < kOrderChunk; j++) {
+            if (ck[j] < key) { cnt++; sum += ct[j]; }              // two compares and three predicated adds per pair
         }
     }
     if (id < nid && cnt) { atomicAdd(s.ord + id, cnt); atomicAdd(s.base + id, sum); }

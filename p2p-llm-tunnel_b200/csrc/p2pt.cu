@@ -715,7 +715,7 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         const unsigned nb = (unsigned)direct_blocks(n);
         if (fused) demux_direct_rank_kernel<true><<<nb, kDirectThreads, 8 * kDirectIds, st>>>(a);
         else demux_direct_rank_kernel<false><<<nb, kDirectThreads, 8 * kDirectIds, st>>>(a);
-        demux_direct_streams_kernel<<<dim3(kDirectIds / kOrderT, 8), kOrderT, 0, st>>>(ds, (u64*)csr, k_out, (u64*)gathered_off);
+        demux_direct_streams_kernel<<<dim3(kDirectIds / kOrderT, 64), kOrderT, 0, st>>>(ds, (u64*)csr, k_out, (u64*)gathered_off);
         demux_direct_prefix_kernel<<<kDirectIds / 32, 1024, 0, st>>>(ds, nb, max_streams, uniq_sid, uniq_session, (u64*)csr, (u64*)gathered_off);
         count_launch(ctx, 3);
         if (gathered || perm) {
