@@ -65,10 +65,21 @@ struct Lane {
 
 constexpr int kLanes = 8;
 
+// A stream beside the caller's, with the two events that fork it off and join it back: the direct demux puts its
+// fallback (the sorting path's kernels, which only look at a flag when the direct path succeeded) there, so that
+// their launches overlap the direct path's gather instead of following it (seven empty launches: about 15 us).
+struct SideStream {
+    cudaStream_t st = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+constexpr int kSides = 8;
+
 struct p2pt_ctx {
     int device = 0;
     int sm_count = 148;
     Lane lanes[kLanes];
+    SideStream sides[kSides];
+    std::atomic<uint32_t> side_next{0};
     std::mutex pool_mu;            // guards Lane::busy
     std::condition_variable pool_cv;
     bool blocking_sync = true;                // big host-pointer calls wait on sync_events (see wait_stream)
@@ -435,6 +446,11 @@ static int32_t ctx_init(p2pt_ctx* ctx, int device, const cudaDeviceProp& prop) {
             CUDA_TRY(nullptr, cudaEventCreateWithFlags(&L.sync_events[i], cudaEventDisableTiming | cudaEventBlockingSync));
         }
     }
+    for (int i = 0; i < kSides; i++) {
+        CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->sides[i].st, cudaStreamNonBlocking));
+        CUDA_TRY(nullptr, cudaEventCreateWithFlags(&ctx->sides[i].fork, cudaEventDisableTiming));
+        CUDA_TRY(nullptr, cudaEventCreateWithFlags(&ctx->sides[i].join, cudaEventDisableTiming));
+    }
     if (int32_t r = upload_device_tables(device)) return r;
     // where does dynamic shared memory start?  The T-tables must sit on a 64 KiB boundary.
     uint32_t* d_probe = nullptr;
@@ -526,6 +542,11 @@ int32_t p2pt_ctx_destroy(p2pt_ctx* ctx) {
             }
             if (L.arena.base) cudaFree(L.arena.base);
             if (L.zc_host) cudaFreeHost(L.zc_host);
+        }
+        for (int i = 0; i < kSides; i++) {
+            if (ctx->sides[i].st) cudaStreamDestroy(ctx->sides[i].st);
+            if (ctx->sides[i].fork) cudaEventDestroy(ctx->sides[i].fork);
+            if (ctx->sides[i].join) cudaEventDestroy(ctx->sides[i].join);
         }
         if (ctx->keys_local) cudaFree(ctx->keys_local);
         if (ctx->keys_remote) cudaFree(ctx->keys_remote);
@@ -694,7 +715,6 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
     if (scratch_bytes < demux_scratch_bytes(n)) return set_err(ctx, P2PT_ERR_CAPACITY, "frame_demux: scratch too small");
     if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "frame_demux: scratch must be 256-byte aligned");
     DemuxScratch s = demux_carve(scratch, n);
-    CUDA_TRY(ctx, cudaMemsetAsync(s.misc, 0, 32, st));
     DemuxBufs bufs;
     bufs.keys[0] = s.keys[0]; bufs.keys[1] = s.keys[1]; bufs.idx[0] = s.idx[0]; bufs.idx[1] = s.idx[1];
     const bool small = n <= (uint64_t)kSmallDemux && ctx->small_demux;
@@ -704,6 +724,7 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
     // ---- the direct path first (demux_direct_kernels.cuh): no sort when the caller expects few streams.  If the
     //      batch turns out not to fit, it raises run_flag and the sorting path below - enqueued either way - runs.
     const uint32_t* run_flag = nullptr;
+    SideStream* side = nullptr;
     if (ctx->direct_demux && !first_only && !small && max_streams <= (uint32_t)kDirectIds) {
         const DirectScratch ds = direct_carve((uint8_t*)scratch + align256(demux_sort_scratch_bytes(n)), n, s);
         CUDA_TRY(ctx, cudaMemsetAsync(ds.ctl, 0, kDirectZeroBytes, st));
@@ -716,6 +737,9 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         if (fused) demux_direct_rank_kernel<true><<<nb, kDirectThreads, 8 * kDirectIds, st>>>(a);
         else demux_direct_rank_kernel<false><<<nb, kDirectThreads, 8 * kDirectIds, st>>>(a);
         demux_direct_streams_kernel<<<dim3(kDirectIds / kOrderT, 64), kOrderT, 0, st>>>(ds, (u64*)csr, k_out, (u64*)gathered_off);
+        // the flag is final now: from here the sorting path (as fallback) runs on a side stream, beside prefix + gather
+        side = &ctx->sides[ctx->side_next.fetch_add(1, std::memory_order_relaxed) % kSides];
+        CUDA_TRY(ctx, cudaEventRecord(side->fork, st));
         demux_direct_prefix_kernel<<<kDirectIds / 32, 1024, 0, st>>>(ds, nb, max_streams, uniq_sid, uniq_session, (u64*)csr, (u64*)gathered_off);
         count_launch(ctx, 3);
         if (gathered || perm) {
@@ -727,7 +751,11 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         }
         CUDA_TRY(ctx, cudaGetLastError());
         run_flag = ds.ctl;
+        CUDA_TRY(ctx, cudaStreamWaitEvent(side->st, side->fork, 0));
     }
+    cudaStream_t user_st = st;
+    if (side) st = side->st;                               // everything below is the fallback then
+    CUDA_TRY(ctx, cudaMemsetAsync(s.misc, 0, 32, st));     // the sorting path's control words
     if (fused) {
         // the sorting path works on descriptors: decode first (after a direct attempt: only if that gave up)
         frame_decode_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, in, (const u64*)fused->in_off, fused->desc_work, run_flag);
@@ -786,6 +814,10 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         count_launch(ctx);
     }
     CUDA_TRY(ctx, cudaGetLastError());
+    if (side) {                                            // join: the caller's stream continues when both paths are through
+        CUDA_TRY(ctx, cudaEventRecord(side->join, side->st));
+        CUDA_TRY(ctx, cudaStreamWaitEvent(user_st, side->join, 0));
+    }
     return P2PT_OK;
 }
 
