@@ -452,13 +452,18 @@ def run_gpu(args):
         tail = gathered[-4096 * PAYLOAD:].cpu().numpy()
         assert np.array_equal(h_gath[-4096 * PAYLOAD:].numpy(), tail), "e2e result differs (tail)"
         launches_e0 = ctx.launch_count()
+        # three timed runs of e2e_steps steps each, the fastest counts: a run is half a second of six host threads
+        # on a shared VM, and one descheduled worker costs a whole step (seen: 15.5 GB/s between two runs of 19.4)
+        e2e_s = None
+        for _ in range(3):
+            barrier()
+            t0 = time.perf_counter()
+            e2e_run(e2e_steps)
+            torch.cuda.synchronize()
+            run_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
+            e2e_s = run_s if e2e_s is None else min(e2e_s, run_s)
         barrier()
-        t0 = time.perf_counter()
-        e2e_run(e2e_steps)
-        torch.cuda.synchronize()
-        e2e_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
-        barrier()
-        launches_e2e = (ctx.launch_count() - launches_e0) // e2e_steps
+        launches_e2e = (ctx.launch_count() - launches_e0) // (3 * e2e_steps)
         # one side only, as a deployed box runs it (a provider seals, a consumer opens; the round trip above drags
         # every payload byte over PCIe four times): all six workers on the same call, same sub-batches
         def one_side(fn, steps):
@@ -686,7 +691,8 @@ def run_gpu(args):
                 "note": f"each step = the same {n}-record batch as {NB} sub-batches of whole sessions through "
                         "p2pt_pipeline_seal then p2pt_pipeline_open_demux (host pointers, pinned memory); 3 seal + 3 open "
                         "worker threads on ONE p2pt_ctx (its call lanes); fill and drain of the worker pipeline are inside the timing; "
-                        f"each step moves {h2d / 1e9:.2f} GB up and {d2h / 1e9:.2f} GB down over PCIe"},
+                        f"each step moves {h2d / 1e9:.2f} GB up and {d2h / 1e9:.2f} GB down over PCIe; "
+                        "fastest of three timed runs of `steps` steps (max over ranks each)"},
         "gpu_launches": int(launches),
         "single_frame_latency": lat,
         "clocks": clocks,

@@ -71,6 +71,8 @@ constexpr int kLanes = 8;
 struct SideStream {
     cudaStream_t st = nullptr;
     cudaEvent_t fork = nullptr, join = nullptr;
+    std::mutex mu;      // record + wait of one event as a pair: two calls that were handed the same side stream must not
+                        // wait on each other's record
 };
 constexpr int kSides = 8;
 
@@ -739,7 +741,11 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         demux_direct_streams_kernel<<<dim3(kDirectIds / kOrderT, 64), kOrderT, 0, st>>>(ds, (u64*)csr, k_out, (u64*)gathered_off);
         // the flag is final now: from here the sorting path (as fallback) runs on a side stream, beside prefix + gather
         side = &ctx->sides[ctx->side_next.fetch_add(1, std::memory_order_relaxed) % kSides];
-        CUDA_TRY(ctx, cudaEventRecord(side->fork, st));
+        {
+            std::lock_guard<std::mutex> lk(side->mu);
+            CUDA_TRY(ctx, cudaEventRecord(side->fork, st));
+            CUDA_TRY(ctx, cudaStreamWaitEvent(side->st, side->fork, 0));
+        }
         demux_direct_prefix_kernel<<<kDirectIds / 32, 1024, 0, st>>>(ds, nb, max_streams, uniq_sid, uniq_session, (u64*)csr, (u64*)gathered_off);
         count_launch(ctx, 3);
         if (gathered || perm) {
@@ -751,7 +757,6 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
         }
         CUDA_TRY(ctx, cudaGetLastError());
         run_flag = ds.ctl;
-        CUDA_TRY(ctx, cudaStreamWaitEvent(side->st, side->fork, 0));
     }
     cudaStream_t user_st = st;
     if (side) st = side->st;                               // everything below is the fallback then
@@ -815,6 +820,7 @@ static int32_t demux_device_impl(p2pt_ctx* ctx, uint64_t n, const p2pt_desc* des
     }
     CUDA_TRY(ctx, cudaGetLastError());
     if (side) {                                            // join: the caller's stream continues when both paths are through
+        std::lock_guard<std::mutex> lk(side->mu);
         CUDA_TRY(ctx, cudaEventRecord(side->join, side->st));
         CUDA_TRY(ctx, cudaStreamWaitEvent(user_st, side->join, 0));
     }
