@@ -9,17 +9,31 @@
 
 namespace p2pt {
 
-// 4-bit mask of the bytes of w that equal '\n' (SWAR zero-byte test on w ^ 0x0a0a0a0a, exact per byte;
-// the multiply gathers the four flag bits into one nibble)
-__device__ __forceinline__ uint32_t lf_nibble(uint32_t w) {
-    const uint32_t x = w ^ 0x0a0a0a0au;
-    const uint32_t t = ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu);      // 0x80 in every byte that was '\n'
-    return ((t >> 7) * 0x01020408u) >> 24;                                          // bits 0..3 = bytes 0..3
+// 0x80 in every byte b of the result whose byte in w is '\n' and whose predecessor (byte b - 1, the top byte of
+// prev_word for b = 0) is '\n' too - the byte that closes an event.  One funnel shift lines the predecessors up, one
+// LOP3 ORs the two differences from 0x0a, and an exact SWAR zero-byte test (no borrow between bytes) flags the bytes
+// where both vanish: five instructions per word (testing for '\n' first and pairing the flags afterwards took eight,
+// and the scan kernels were issue-bound at 68 / 135 instructions per 512-byte row).
+__device__ __forceinline__ uint32_t lf_pair_flags(uint32_t w, uint32_t prev_word) {
+    const uint32_t s = __funnelshift_l(prev_word, w, 8);                // bytes [prev.3, w.0, w.1, w.2]
+    const uint32_t z = (w ^ 0x0a0a0a0au) | (s ^ 0x0a0a0a0au);           // zero byte <=> both are '\n'
+    return ~(((z & 0x7f7f7f7fu) + 0x7f7f7f7fu) | z) & 0x80808080u;
 }
-// bit b of the result: byte b of v is '\n' and the byte before it (prev for b = 0) is '\n' too
-__device__ __forceinline__ uint32_t lf_pairs16(const uint4& v, uint32_t prev_byte) {
-    const uint32_t m = lf_nibble(v.x) | (lf_nibble(v.y) << 4) | (lf_nibble(v.z) << 8) | (lf_nibble(v.w) << 12);
-    return m & ((m << 1) | (prev_byte == 10u ? 1u : 0u)) & 0xffffu;
+struct PairFlags { uint32_t f[4]; };
+__device__ __forceinline__ PairFlags lf_pairs16(const uint4& v, uint32_t prev_word) {
+    PairFlags r;
+    r.f[0] = lf_pair_flags(v.x, prev_word); r.f[1] = lf_pair_flags(v.y, v.x);
+    r.f[2] = lf_pair_flags(v.z, v.y);       r.f[3] = lf_pair_flags(v.w, v.z);
+    return r;
+}
+__device__ __forceinline__ uint32_t pair_count(const PairFlags& p) { return __popc(p.f[0]) + __popc(p.f[1]) + __popc(p.f[2]) + __popc(p.f[3]); }
+// bit b = byte b of the vector closes an event (only lanes that hold an event pay for this: the multiply gathers the
+// four flag bits of a word into one nibble)
+__device__ __forceinline__ uint32_t pair_mask16(const PairFlags& p) {
+    uint32_t m = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) m |= (((p.f[k] >> 7) * 0x01020408u) >> 24) << (4 * k);
+    return m;
 }
 
 // keep bytes [lo, hi) of v, zero the others (0 <= lo <= hi <= 16); zero is not '\n'
@@ -69,7 +83,7 @@ __global__ void __launch_bounds__(256) sse_scan_kernel(u64 k, const uint8_t* __r
         u64 count = 0;
         uint32_t lane_count = 0;
         const u64 out0 = EMIT ? ev_csr[s] : 0;
-        uint32_t carry = 0;                                   // last byte of the previous row (0 at the stream start)
+        uint32_t carry = 0;                                   // last word of the previous row (0 at the stream start)
         bool is_done = false;
         if (EMIT && lane == 0) is_done = sse_is_done_event(body, a, b);   // an event starts at the stream start
         for (const uint8_t* rp = row0; rp < hi; rp += 512 * kSseRows) {
@@ -79,17 +93,18 @@ __global__ void __launch_bounds__(256) sse_scan_kernel(u64 k, const uint8_t* __r
                 const uint8_t* p = rp + 512 * r + 16 * lane;
                 v[r] = (p < hi) ? ldg128(p) : make_uint4(0, 0, 0, 0);
             }
-            uint32_t m[kSseRows], c[kSseRows];
+            PairFlags m[kSseRows];
+            uint32_t c[kSseRows];
 #pragma unroll
             for (int r = 0; r < kSseRows; r++) {
                 const uint8_t* p = rp + 512 * r + 16 * lane;
                 if (p < hi && (p < lo || p + 16 > hi))
                     v[r] = keep_bytes16(v[r], p < lo ? (int)(lo - p) : 0, p + 16 > hi ? (int)(hi - p) : 16);
-                uint32_t prev = __shfl_up_sync(0xffffffffu, v[r].w >> 24, 1);
+                uint32_t prev = __shfl_up_sync(0xffffffffu, v[r].w, 1);
                 if (lane == 0) prev = carry;
-                carry = __shfl_sync(0xffffffffu, v[r].w >> 24, 31);
+                carry = __shfl_sync(0xffffffffu, v[r].w, 31);
                 m[r] = lf_pairs16(v[r], prev);
-                c[r] = __popc(m[r]);
+                c[r] = pair_count(m[r]);
             }
             if (!EMIT) {
 #pragma unroll
@@ -108,7 +123,7 @@ __global__ void __launch_bounds__(256) sse_scan_kernel(u64 k, const uint8_t* __r
                         const int r = r2 + e;
                         const uint32_t inc_r = (incl >> (16 * e)) & 0xffffu;
                         u64 slot = out0 + count + (inc_r - c[r]);
-                        uint32_t mm = m[r];
+                        uint32_t mm = c[r] ? pair_mask16(m[r]) : 0u;
                         const u64 pos0 = (u64)(rp + 512 * r + 16 * lane - body);
                         while (mm) {
                             const int bit = __ffs(mm) - 1; mm &= mm - 1;

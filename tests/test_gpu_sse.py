@@ -74,3 +74,20 @@ def test_sse_scan_after_demux_gather(ctx):
         exp = [i + 2 for i in range(len(b) - 1) if b[i:i + 2] == b"\n\n"]
         got = (ends[int(csr[s]):int(csr[s + 1])] - r["gathered_off"][s]).tolist()
         assert got == exp, sid
+
+
+def test_sse_scan_fuzz_newline_runs(ctx):
+    """bodies of nothing but 'a' and '\\n' in random proportions, 700 streams of 0..3000 bytes back to back at every
+    alignment: pairs that straddle words, vectors, lanes, rows and row groups, runs of LFs, LFs that end one stream
+    and start the next (which must not pair)."""
+    rng = np.random.default_rng(53)
+    streams = []
+    for i in range(700):
+        n = int(rng.integers(0, 3000))
+        p = float(rng.choice([0.02, 0.2, 0.5, 0.9]))
+        streams.append(np.where(rng.random(n) < p, 10, 97).astype(np.uint8).tobytes())
+    body = np.frombuffer(b"".join(streams), np.uint8)
+    off = np.concatenate([[0], np.cumsum([len(s) for s in streams])]).astype(np.uint64)
+    csr, ends, done = ctx.sse_scan(body, off)
+    ecsr, eends, edone = ob.sse_scan(body, off)
+    assert np.array_equal(csr, ecsr) and np.array_equal(ends, eends) and np.array_equal(done, edone)
