@@ -161,6 +161,8 @@ def test_fused_decode_demux_matches_oracle(ctx, n, streams, max_streams):
     same(r, exp, ("uniq_sid", "csr", "gathered_off", "gathered"), "bodies only")
     r = ctx.frame_decode_demux(buf, off, max_streams)      # no gather
     same(r, exp, ("uniq_sid", "csr", "perm"), "no gather")
+    r = ctx.frame_decode_demux(buf, off, max_streams, want_perm=False)      # the stream table alone
+    same(r, exp, ("uniq_sid", "csr"), "table only")
 
 
 def test_fused_decode_demux_with_sessions_and_fallback(ctx):
