@@ -248,8 +248,13 @@ __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_packetize_kernel(cons
     const bool dtls = a.epoch != nullptr;
     const uint32_t hdr = dtls ? 13u : 0u;
     const u64 warp = (u64)blockIdx.x * kSctpWarps + wib, nwarps = (u64)gridDim.x * kSctpWarps;
+    // the warp's next message is pulled towards L2 while this one is packetised (its offset was fetched a round earlier,
+    // so nothing waits for it): the payload loads below then find their lines a cache level closer
+    u64 mo_next = warp + nwarps < a.n ? __ldg(a.msg_off + warp + nwarps) : 0;
     for (u64 i = warp; i < a.n; i += nwarps) {
         const u64 mo = __ldg(a.msg_off + i), mlen = __ldg(a.msg_off + i + 1) - mo;
+        if (i + nwarps < a.n && lane < 10) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.msg + mo_next + 128 * lane));
+        mo_next = i + 2 * nwarps < a.n ? __ldg(a.msg_off + i + 2 * nwarps) : 0;
         const uint8_t* m = a.msg + mo;
         const u64 k = mlen ? (mlen + kSctpMaxPayload - 1) / kSctpMaxPayload : 1;
         const u64 p0 = __ldg(a.pkt_first + i);
