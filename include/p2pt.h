@@ -21,7 +21,7 @@
  *     device->host copy, synchronously.  *_device entry points take DEVICE pointers plus a
  *     cudaStream_t (as void*) and only enqueue kernels; they allocate nothing.  Work is ordered on `stream`
  *     as usual; the demux calls may run part of it on a stream of the library's own that is forked off
- *     `stream` and joined back into it before the call returns (events only, also legal under stream capture).
+ *     `stream` and joined back into it before the call returns (two events; no host synchronisation).
  *   - Re-entrant: any thread may call on any ctx, and up to eight host-pointer calls run on one ctx at
  *     the same time (each takes one of the ctx's call lanes - streams, staging arena, mapped buffer -
  *     for its duration; a ninth caller waits for a lane).  This is the reference's calling pattern:
