@@ -109,6 +109,21 @@ __global__ void __launch_bounds__(256) sse_scan_kernel(u64 k, const uint8_t* __r
             if (!EMIT) {
 #pragma unroll
                 for (int r = 0; r < kSseRows; r++) lane_count += c[r];
+            } else if (!__any_sync(0xffffffffu, (c[0] | c[1] | c[2] | c[3]) > 1u)) {
+                // the usual case - no lane holds two events of a row (events are longer than 16 bytes): a lane's event
+                // index is a ballot and a popcount, no shuffle scan, and there is no loop over the lane's events
+                static_assert(kSseRows == 4, "four rows per group");
+#pragma unroll
+                for (int r = 0; r < kSseRows; r++) {
+                    const uint32_t bal = __ballot_sync(0xffffffffu, c[r] != 0);
+                    if (c[r]) {
+                        const u64 slot = out0 + count + __popc(bal & ((1u << lane) - 1u));
+                        const u64 end = (u64)(rp + 512 * r + 16 * lane - body) + __ffs(pair_mask16(m[r]));   // just past the second '\n'
+                        if (slot < cap) ev_end[slot] = end;
+                        is_done |= sse_is_done_event(body, end, b);            // does the next event read `data: [DONE]`?
+                    }
+                    count += __popc(bal);
+                }
             } else {
 #pragma unroll
                 for (int r2 = 0; r2 < kSseRows; r2 += 2) {
