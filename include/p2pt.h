@@ -314,7 +314,7 @@ int32_t p2pt_frame_decode_demux_batch_device(p2pt_ctx* ctx, uint64_t n, const ui
  * GPU owns the rest of HBM, or a per-connection loop that cannot afford cudaMalloc / cudaFree
  * because those take the driver's allocator lock and synchronise the whole device, stalling every
  * other session's stream.  The scratch lives in a static device array inside the library
- * (about 12.9 MB, resident on every GPU that loads the library until the process exits), which
+ * (about 10.8 MB, resident on every GPU that loads the library until the process exits), which
  * bounds the batch: n <= P2PT_NOALLOC_MAX_FRAMES, larger batches are refused with
  * P2PT_ERR_CAPACITY.  The call itself performs no cudaMalloc / cudaFree and uses no allocating
  * library routine.

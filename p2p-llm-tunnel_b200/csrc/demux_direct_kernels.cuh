@@ -36,7 +36,7 @@ constexpr int kDirectWarps = P2PT_DIRECT_WARPS;     // 8 (three blocks per SM: 2
 constexpr int kDirectBlocksPerSm = kDirectWarps == 8 ? 3 : 2;
 constexpr int kDirectRounds = 4;                    // groups of 32 consecutive frames per warp and tile
 constexpr int kDirectThreads = 32 * kDirectWarps;
-constexpr int kDirectTile = kDirectThreads * kDirectRounds;      // 1024 frames per block iteration
+constexpr int kDirectTile = kDirectThreads * kDirectRounds;      // frames per block iteration (2048 with 16 warps)
 constexpr int kDirectMaxBlocks = 148 * kDirectBlocksPerSm;      // every block resident
 constexpr uint32_t kNoLoc = 0xffffffffu;            // per-frame position: contributes nothing to the gather
 constexpr uint16_t kNoId = 0xffff;                  // per-frame id: not decodable
