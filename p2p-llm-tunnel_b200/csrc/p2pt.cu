@@ -470,7 +470,7 @@ static int32_t ctx_init(p2pt_ctx* ctx, int device, const cudaDeviceProp& prop) {
     CUDA_TRY(nullptr, configure_gcm_mode<kPipeSeal>(ctx->lut_slack));
     CUDA_TRY(nullptr, configure_gcm_mode<kPipeOpen>(ctx->lut_slack));
     CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_packetize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_smem_bytes(ctx->lut_slack)));
-    CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_unpack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_smem_bytes(ctx->lut_slack)));
+    CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_unpack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_unpack_smem_bytes(ctx->lut_slack)));
     CUDA_TRY(nullptr, cudaFuncSetAttribute(demux_direct_rank_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * kDirectIds));
     CUDA_TRY(nullptr, cudaFuncSetAttribute(demux_direct_rank_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * kDirectIds));
     {
@@ -912,8 +912,8 @@ int32_t p2pt_sctp_unpack_batch_device(p2pt_ctx* ctx, uint64_t n_pkts, const uint
     SctpUnpackArgs a;
     a.n = n_pkts; a.in = in; a.in_off = (const u64*)in_off; a.headroom = headroom; a.info = info; a.desc = desc;
     a.tsn_base = tsn_base;
-    const uint32_t smem = sctp_smem_bytes(ctx->lut_slack);
-    sctp_unpack_kernel<<<grid_for(ctx, n_pkts, kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
+    const uint32_t smem = sctp_unpack_smem_bytes(ctx->lut_slack);
+    sctp_unpack_kernel<<<grid_for(ctx, (n_pkts + 1) / 2, kUnpackWarps, 1), 32 * kUnpackWarps, smem, (cudaStream_t)stream>>>(a);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
     return P2PT_OK;

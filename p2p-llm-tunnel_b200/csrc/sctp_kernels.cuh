@@ -318,82 +318,155 @@ struct SctpUnpackArgs {
     const uint32_t* tsn_base;                // nullable: per packet, the cumulative TSN ack point of its association
 };
 
-__global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_unpack_kernel(const SctpUnpackArgs a) {
+// The unpack kernel gives a packet to HALF a warp: everything that is not the CRC itself - offsets, geometry, staging,
+// fix-ups, header parse, the stores of info / desc - is warp-wide instruction stream whatever the number of lanes that
+// need it (it was 290 of the 492 warp instructions per packet with a warp per packet), so two packets per warp halve it
+// per packet; a lane's CRC segment doubles to 20 words, which costs the same per packet.  24 warps per block: their
+// 96 staging buffers (two packets x double buffering) fill the gap below the tables first.
+constexpr int kUnpackWarps = 24;
+constexpr int kCrcSegHalf = 20;                                       // 16 lanes x 20 words = 1280 bytes
+constexpr uint32_t kUnpackBufs = kUnpackWarps * 4;
+__host__ __device__ constexpr uint32_t sctp_unpack_smem_bytes(uint32_t slack) {
+    const uint32_t low = slack / kSctpBufBytes;
+    return slack + kCrcLutBytes + (kUnpackBufs > low ? (kUnpackBufs - low) * kSctpBufBytes : 0u);
+}
+
+// warp_crc32c for a packet held by 16 lanes (hl = lane & 15): same end-aligned segments, 20 words each
+template <bool ALIGNED>
+__device__ __forceinline__ uint32_t half_crc32c(const CrcLut& t, const uint8_t* buf, uint32_t pkt0, uint32_t nwords, int hl,
+                                                uint32_t hmask, const uint32_t (&xpm)[kGhashClasses]) {
+    const int first = (int)nwords - (16 - hl) * kCrcSegHalf;
+    uint32_t c = 0;
+    if (first > -kCrcSegHalf) {
+        // words before the packet start: zeros lie in front of it, but only kSctpFront bytes of them - clamp
+        const uint32_t* q0 = reinterpret_cast<const uint32_t*>(buf) + (int)(pkt0 >> 2);
+        const int lo = first < -(int)(kSctpFront / 4 - 4) ? -(int)(kSctpFront / 4 - 4) : first;      // still all zeros in front
+        const uint32_t* q = q0 + lo;
+        const int steps = first + kCrcSegHalf - lo;                   // <= 20; the skipped leading words are zero
+        if (ALIGNED) {
+#pragma unroll 5
+            for (int i = 0; i < steps; i++) c = crc_word(t, c, q[i]);
+        } else {
+            const unsigned sh = (pkt0 & 3) * 8;
+            uint32_t lo_w = q[0];
+#pragma unroll 5
+            for (int i = 0; i < steps; i++) {
+                const uint32_t hi_w = q[i + 1];
+                c = crc_word(t, c, __funnelshift_r(lo_w, hi_w, sh));
+                lo_w = hi_w;
+            }
+        }
+    }
+    uint32_t part = crc_mulmod(t, c, xpm);
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) part ^= __shfl_xor_sync(hmask, part, o, 16);     // the other half may be elsewhere
+    return ~(part ^ g_crc_init[nwords]);
+}
+
+__global__ void __launch_bounds__(32 * kUnpackWarps, 1) sctp_unpack_kernel(const SctpUnpackArgs a) {
     extern __shared__ __align__(16) uint8_t sctp_dyn_smem[];
-    CrcLut tabs;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, half = lane >> 4, hl = lane & 15;
+    // ---- tables on their 64 KiB boundary, staging buffers below them first
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sctp_dyn_smem);
+    const uint32_t tbase = (sbase + 0xffffu) & ~0xffffu;
+    {
+        uint32_t* tabs = reinterpret_cast<uint32_t*>(sctp_dyn_smem + (tbase - sbase));
+        for (int idx = threadIdx.x; idx < 256 * 32; idx += blockDim.x) {
+            const int x = idx >> 5, l = idx & 31;
+            tabs[x * 64 + l] = g_crc_tab[0][x];
+            tabs[x * 64 + 32 + l] = g_crc_tab[1][x];
+        }
+    }
+    CrcLut tabs; tabs.lb = tbase + 4u * (uint32_t)lane;
     uint32_t xpm[kGhashClasses];
-    uint8_t* bufs = sctp_smem_setup(sctp_dyn_smem, tabs, xpm);
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const u64 warp = (u64)blockIdx.x * kSctpWarps + wib, nwarps = (u64)gridDim.x * kSctpWarps;
+    ghash_classes(g_crc_xpow[(15 - hl) * kCrcSegHalf * 4], xpm);
+    const uint32_t n_low = (tbase - sbase) / kSctpBufBytes;
+    auto buffer = [&](uint32_t q) -> uint8_t* {
+        return q < n_low ? sctp_dyn_smem + q * kSctpBufBytes : sctp_dyn_smem + (tbase - sbase) + kCrcLutBytes + (q - n_low) * kSctpBufBytes;
+    };
+    uint8_t* const buf_a = buffer(wib * 4 + half * 2);
+    uint8_t* const buf_b = buffer(wib * 4 + half * 2 + 1);
+    for (uint32_t w = hl; w < kSctpBufBytes / 4; w += 16) { reinterpret_cast<uint32_t*>(buf_a)[w] = 0; reinterpret_cast<uint32_t*>(buf_b)[w] = 0; }
+    const uint32_t hmask = 0xffffu << (16 * half);
+    __syncthreads();
+
+    const u64 pairs = (a.n + 1) / 2;
+    const u64 warp = (u64)blockIdx.x * kUnpackWarps + wib, nwarps = (u64)gridDim.x * kUnpackWarps;
     // a packet we handle: headroom + 12 .. 1228 bytes, a multiple of 4 (else it is reported malformed and not staged)
     auto sized = [&](u64 ilen) { return !(ilen < (u64)a.headroom + 12 || ilen - a.headroom > kSctpMaxPacket || ((ilen - a.headroom) & 3)); };
-    int cur = 0;
-    u64 io = 0, ilen = 0;
-    if (warp < a.n) {
-        io = __ldg(a.in_off + warp); ilen = __ldg(a.in_off + warp + 1) - io;
-        stage_async(bufs, a.in + io + a.headroom, sized(ilen) ? (uint32_t)(ilen - a.headroom) : 0u, lane);
-    }
-    for (u64 i = warp; i < a.n; i += nwarps) {
-        uint8_t* buf = bufs + cur * kSctpBufBytes;
-        const u64 inext = i + nwarps;
-        u64 io_n = 0, ilen_n = 0;
-        if (inext < a.n) {                                                   // the next packet's bytes fly while this one is checked
-            io_n = __ldg(a.in_off + inext); ilen_n = __ldg(a.in_off + inext + 1) - io_n;
-            stage_async(bufs + (cur ^ 1) * kSctpBufBytes, a.in + io_n + a.headroom, sized(ilen_n) ? (uint32_t)(ilen_n - a.headroom) : 0u, lane);
-        } else {
-            cp_async_commit();
+    auto stage_half = [&](uint8_t* buf, u64 i, u64& io, u64& ilen) {      // start the copy of packet i (this half's)
+        io = 0; ilen = 0;
+        if (i < a.n) { io = __ldg(a.in_off + i); ilen = __ldg(a.in_off + i + 1) - io; }
+        const uint8_t* src = a.in + io + a.headroom;
+        const uint32_t len = (i < a.n && sized(ilen)) ? (uint32_t)(ilen - a.headroom) : 0u;
+        const uint32_t sa = (uint32_t)((uintptr_t)src & 15);
+        const uint32_t nvec = len ? (sa + len + 15) >> 4 : 0;
+#pragma unroll
+        for (int it = 0; it < 5; it++) {                                  // <= 79 vectors over 16 lanes
+            const uint32_t v = hl + 16 * it;
+            if (v < nvec) cp_async16(buf + kSctpFront + 16 * v, src - sa + 16 * (size_t)v);
         }
+        cp_async_commit();
+    };
+    int cur = 0;
+    u64 io, ilen;
+    stage_half(buf_a, 2 * warp + half, io, ilen);
+    for (u64 pp = warp; pp < pairs; pp += nwarps) {
+        const u64 i = 2 * pp + half;
+        uint8_t* buf = cur ? buf_b : buf_a;
+        u64 io_n, ilen_n;
+        stage_half(cur ? buf_a : buf_b, 2 * (pp + nwarps) + half, io_n, ilen_n);   // the next pair flies while this one is checked
         cp_async_wait_all_but_one();
         __syncwarp();
         uint32_t st = P2PT_ST_OK;
-        uint32_t flags = 0, tsn = 0, sid = 0, ssn = 0, pp = 0, plen_pay = 0;
-        if (!sized(ilen)) {
-            st = P2PT_ST_SCTP_MALFORMED;                                     // not a single-DATA-chunk packet we handle
-        } else {
-            const uint32_t n = (uint32_t)(ilen - a.headroom);
-            const uint32_t sa = (uint32_t)((uintptr_t)(a.in + io + a.headroom) & 15);
-            const uint32_t pkt0 = kSctpFront + sa;
-            if ((uint32_t)lane < sa) buf[kSctpFront + lane] = 0;             // bytes of the first vector in front of the packet
-            __syncwarp();
-            const uint32_t theirs = staged_word(buf, pkt0, 2);
-            __syncwarp();
-            if (lane < 4) buf[pkt0 + 8 + lane] = 0;                          // checksum field counts as zero
-            __syncwarp();
-            const uint32_t crc = (pkt0 & 3) ? warp_crc32c<false>(tabs, buf, pkt0, n >> 2, lane, xpm)
-                                            : warp_crc32c<true>(tabs, buf, pkt0, n >> 2, lane, xpm);
-            if (crc != theirs) st = P2PT_ST_SCTP_BAD_CHECKSUM;               // checked first, like Packet::unmarshal
-            else if (n < 28 || buf[pkt0 + 12] != 0) st = P2PT_ST_SCTP_MALFORMED;
-            else {
-                const uint32_t w3 = bswap32(staged_word(buf, pkt0, 3));
-                const uint32_t clen = w3 & 0xffff;
-                if (clen < 16 || 12 + ((clen + 3) & ~3u) != n) st = P2PT_ST_SCTP_MALFORMED;
+        uint32_t flags = 0, tsn = 0, sid = 0, ssn = 0, pp_id = 0, plen_pay = 0;
+        if (i < a.n) {
+            if (!sized(ilen)) {
+                st = P2PT_ST_SCTP_MALFORMED;                                 // not a single-DATA-chunk packet we handle
+            } else {
+                const uint32_t n = (uint32_t)(ilen - a.headroom);
+                const uint32_t sa = (uint32_t)((uintptr_t)(a.in + io + a.headroom) & 15);
+                const uint32_t pkt0 = kSctpFront + sa;
+                if ((uint32_t)hl < sa) buf[kSctpFront + hl] = 0;             // bytes of the first vector in front of the packet
+                __syncwarp(hmask);
+                const uint32_t theirs = staged_word(buf, pkt0, 2);
+                __syncwarp(hmask);
+                if (hl < 4) buf[pkt0 + 8 + hl] = 0;                          // checksum field counts as zero
+                __syncwarp(hmask);
+                const uint32_t crc = (pkt0 & 3) ? half_crc32c<false>(tabs, buf, pkt0, n >> 2, hl, hmask, xpm)
+                                                : half_crc32c<true>(tabs, buf, pkt0, n >> 2, hl, hmask, xpm);
+                if (crc != theirs) st = P2PT_ST_SCTP_BAD_CHECKSUM;           // checked first, like Packet::unmarshal
+                else if (n < 28 || buf[pkt0 + 12] != 0) st = P2PT_ST_SCTP_MALFORMED;
                 else {
-                    flags = (w3 >> 16) & 0xff; tsn = bswap32(staged_word(buf, pkt0, 4));
-                    const uint32_t w5 = bswap32(staged_word(buf, pkt0, 5));
-                    sid = w5 >> 16; ssn = w5 & 0xffff; pp = bswap32(staged_word(buf, pkt0, 6)); plen_pay = clen - 16;
+                    const uint32_t w3 = bswap32(staged_word(buf, pkt0, 3));
+                    const uint32_t clen = w3 & 0xffff;
+                    if (clen < 16 || 12 + ((clen + 3) & ~3u) != n) st = P2PT_ST_SCTP_MALFORMED;
+                    else {
+                        flags = (w3 >> 16) & 0xff; tsn = bswap32(staged_word(buf, pkt0, 4));
+                        const uint32_t w5 = bswap32(staged_word(buf, pkt0, 5));
+                        sid = w5 >> 16; ssn = w5 & 0xffff; pp_id = bswap32(staged_word(buf, pkt0, 6)); plen_pay = clen - 16;
+                    }
                 }
             }
-        }
-        // every lane holds the (warp-uniform) results: lanes 0..3 store the four words of the chunk info, lanes 4..6
-        // the three 8-byte words of a descriptor p2pt_frame_demux_batch can order: key = TSN, "body" type so the
-        // gather takes it.  TSNs are serial numbers (RFC 4960 1.6: arithmetic modulo 2^32) and the peer picks where
-        // they start, so a message may straddle 0xFFFFFFFF -> 0: with tsn_base the key is the distance from the
-        // association's cumulative ack point, which orders any window of fewer than 2^32 TSNs correctly (webrtc-sctp
-        // compares with sna32)
-        {
+            // every lane of the half holds the results: lanes 0..3 store the four words of the chunk info, lanes 4..6 the
+            // three 8-byte words of a descriptor p2pt_frame_demux_batch can order: key = TSN, "body" type so the gather
+            // takes it.  TSNs are serial numbers (RFC 4960 1.6: arithmetic modulo 2^32) and the peer picks where they
+            // start, so a message may straddle 0xFFFFFFFF -> 0: with tsn_base the key is the distance from the
+            // association's cumulative ack point, which orders any window of fewer than 2^32 TSNs correctly (webrtc-sctp
+            // compares with sna32)
             const uint32_t key = a.tsn_base ? tsn - __ldg(a.tsn_base + i) : tsn;
             const u64 poff = st == P2PT_ST_OK ? io + a.headroom + 28 : io;
             const uint32_t plen = st == P2PT_ST_OK ? plen_pay : 0u;
-            if (lane < 4) {
-                const uint32_t w = lane == 0 ? tsn : lane == 1 ? (sid & 0xffffu) | (ssn << 16) : lane == 2 ? pp : (flags & 0xffu) | (st << 8);
-                reinterpret_cast<uint32_t*>(a.info + i)[lane] = w;
-            } else if (lane < 7) {
-                const uint2 w = lane == 4 ? make_uint2((uint32_t)poff, (uint32_t)(poff >> 32)) : lane == 5 ? make_uint2(plen, key)
-                                          : make_uint2(21u | (st << 8), 0u);
-                reinterpret_cast<uint2*>(a.desc + i)[lane - 4] = w;
+            if (hl < 4) {
+                const uint32_t w = hl == 0 ? tsn : hl == 1 ? (sid & 0xffffu) | (ssn << 16) : hl == 2 ? pp_id : (flags & 0xffu) | (st << 8);
+                reinterpret_cast<uint32_t*>(a.info + i)[hl] = w;
+            } else if (hl < 7) {
+                const uint2 w = hl == 4 ? make_uint2((uint32_t)poff, (uint32_t)(poff >> 32)) : hl == 5 ? make_uint2(plen, key)
+                                        : make_uint2(21u | (st << 8), 0u);
+                reinterpret_cast<uint2*>(a.desc + i)[hl - 4] = w;
             }
         }
-        __syncwarp();                                                        // the buffer is staged into again next round
+        __syncwarp();                                                        // the buffers are staged into again next round
         cur ^= 1; io = io_n; ilen = ilen_n;
     }
 }
