@@ -896,7 +896,7 @@ int32_t p2pt_sctp_packetize_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_
     a.sid = sid; a.ssn = ssn; a.ppid = ppid; a.tsn0 = tsn0; a.epoch = epoch; a.seq48_first = (const u64*)seq48_first;
     a.out = out; a.out_msg_off = (const u64*)out_msg_off; a.pkt_first = (const u64*)pkt_first; a.pkt_off = (u64*)pkt_off;
     const uint32_t smem = sctp_smem_bytes(ctx->lut_slack);
-    sctp_packetize_kernel<<<grid_for(ctx, n, kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
+    sctp_packetize_kernel<<<grid_for(ctx, (n + 1) / 2, kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
     return P2PT_OK;

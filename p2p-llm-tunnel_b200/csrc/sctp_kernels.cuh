@@ -238,76 +238,131 @@ struct SctpPacketizeArgs {
     u64* pkt_off;                                         // out: byte offset of every packet (+ 1 terminator)
 };
 
+// A message per HALF warp, like the unpack kernel's packet per half warp (see there): the per-message and per-packet
+// bookkeeping is warp-wide instruction stream, two messages per warp halve it per packet.
+constexpr int kCrcSegHalfWords = 20;                                  // 16 lanes x 20 words = 1280 bytes
+__device__ __forceinline__ uint32_t half_crc32c_words(const CrcLut& t, const uint32_t* words, uint32_t nwords, int hl, uint32_t hmask,
+                                                      const uint32_t (&xpm)[kGhashClasses]) {
+    const int first = (int)nwords - (16 - hl) * kCrcSegHalfWords;   // may be negative: leading zero words
+    uint32_t c = 0;
+#pragma unroll 5
+    for (int i = 0; i < kCrcSegHalfWords; i++) {
+        const int wi = first + i;
+        const uint32_t v = wi >= 0 ? words[wi] : 0u;
+        c = crc_word(t, c, v);
+    }
+    uint32_t part = crc_mulmod(t, c, xpm);
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) part ^= __shfl_xor_sync(hmask, part, o, 16);
+    return ~(part ^ g_crc_init[nwords]);
+}
+// smem_stream_to_global by 16 lanes
+__device__ __forceinline__ void half_stream_to_global(const uint8_t* sbuf, uint32_t start, uint32_t nbytes, uint8_t* dst, int hl) {
+    uint32_t head = (uint32_t)((4 - ((uintptr_t)dst & 3)) & 3);
+    if (head > nbytes) head = nbytes;
+    if ((uint32_t)hl < head) dst[hl] = sbuf[start + hl];
+    const uint32_t body = nbytes - head, nfull = body >> 2;
+    const uint32_t so = start + head;                    // stream offset of the first aligned destination word
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(sbuf) + (so >> 2);
+    const unsigned sh = (so & 3) * 8;
+    uint32_t* dw = reinterpret_cast<uint32_t*>(dst + head);
+#pragma unroll 5
+    for (int it = 0; it < 20; it++) {
+        const uint32_t j = hl + 16 * it;
+        if (j < nfull) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
+    }
+    for (uint32_t j = hl + 320; j < nfull; j += 16) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
+    for (uint32_t b = (nfull << 2) + hl; b < body; b += 16) dst[head + b] = sbuf[so + b];
+}
+
 __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_packetize_kernel(const SctpPacketizeArgs a) {
     extern __shared__ __align__(16) uint8_t sctp_dyn_smem[];
     CrcLut tabs;
     uint32_t xpm[kGhashClasses];
-    uint8_t* buf = sctp_smem_setup(sctp_dyn_smem, tabs, xpm);          // the first of the warp's two buffers is all it needs
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    uint8_t* bufs = sctp_smem_setup(sctp_dyn_smem, tabs, xpm);         // two buffers per warp: one per half here
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, half = lane >> 4, hl = lane & 15;
+    const uint32_t hmask = 0xffffu << (16 * half);
+    ghash_classes(g_crc_xpow[(15 - hl) * kCrcSegHalfWords * 4], xpm);   // the shift of a 20-word segment
+    uint8_t* buf = bufs + half * kSctpBufBytes;
     uint32_t* bw = reinterpret_cast<uint32_t*>(buf);
     const bool dtls = a.epoch != nullptr;
     const uint32_t hdr = dtls ? 13u : 0u;
     const u64 warp = (u64)blockIdx.x * kSctpWarps + wib, nwarps = (u64)gridDim.x * kSctpWarps;
-    // the warp's next message is pulled towards L2 while this one is packetised (its offset was fetched a round earlier,
-    // so nothing waits for it): the payload loads below then find their lines a cache level closer
-    u64 mo_next = warp + nwarps < a.n ? __ldg(a.msg_off + warp + nwarps) : 0;
-    for (u64 i = warp; i < a.n; i += nwarps) {
-        const u64 mo = __ldg(a.msg_off + i), mlen = __ldg(a.msg_off + i + 1) - mo;
-        if (i + nwarps < a.n && lane < 10) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.msg + mo_next + 128 * lane));
-        mo_next = i + 2 * nwarps < a.n ? __ldg(a.msg_off + i + 2 * nwarps) : 0;
-        const uint8_t* m = a.msg + mo;
-        const u64 k = mlen ? (mlen + kSctpMaxPayload - 1) / kSctpMaxPayload : 1;
-        const u64 p0 = __ldg(a.pkt_first + i);
-        u64 oo = __ldg(a.out_msg_off + i);
-        const uint32_t sp = __ldg(a.src_port + i), dp = __ldg(a.dst_port + i), vt = __ldg(a.vtag + i);
-        const uint32_t sid = __ldg(a.sid + i), ssn = __ldg(a.ssn + i), pp = __ldg(a.ppid + i), t0 = __ldg(a.tsn0 + i);
-        for (u64 f = 0; f < k; f++) {
-            const u64 off = f * kSctpMaxPayload;
-            const uint32_t fl = (uint32_t)(mlen - off < kSctpMaxPayload ? mlen - off : kSctpMaxPayload);
-            const uint32_t padded = (fl + 3) & ~3u, plen = 28 + padded;
-            __syncwarp();
-            // ---- header words (packet bytes 0..27 -> buffer words 5..11), big-endian fields
-            if (lane < 7) {
-                uint32_t be;
-                const uint32_t flags = (f == 0 ? 2u : 0u) | (f == k - 1 ? 1u : 0u);
-                switch (lane) {
-                    case 0: be = (sp << 16) | dp; break;
-                    case 1: be = vt; break;
-                    case 2: be = 0; break;                                   // checksum, patched below
-                    case 3: be = (0u << 24) | (flags << 16) | (16 + fl); break;
-                    case 4: be = t0 + (uint32_t)f; break;
-                    case 5: be = (sid << 16) | ssn; break;
-                    default: be = pp; break;
-                }
-                bw[kSctpPktAt / 4 + lane] = bswap32(be);
-            }
-            if (dtls && lane < 13) {                                         // DTLS record header in front
-                const uint32_t ep = __ldg(a.epoch + i);
-                const u64 sq = __ldg(a.seq48_first + i) + f;
-                uint32_t b;
-                switch (lane) {
-                    case 0: b = 23; break; case 1: b = 0xfe; break; case 2: b = 0xfd; break;
-                    case 3: b = ep >> 8; break; case 4: b = ep; break;
-                    case 11: b = plen >> 8; break; case 12: b = plen; break;
-                    default: b = (uint32_t)(sq >> (8 * (10 - lane))); break;  // lanes 5..10: seq bytes 5..0
-                }
-                buf[kSctpPktAt - 13 + lane] = (uint8_t)b;
-            }
-            // ---- payload, zero padded, into the 16-byte aligned part of the buffer
-#pragma unroll
-            for (int it = 0; it < 3; it++) {                                  // 75 vectors for a full fragment
-                const uint32_t v = lane + 32 * it;
-                if (v * 16 < padded) *reinterpret_cast<uint4*>(buf + kSctpPktAt + 28 + 16 * v) = stage_load16<true>(m + off, v, fl);
-            }
-            __syncwarp();
-            const uint32_t crc = warp_crc32c_words(tabs, bw + kSctpPktAt / 4, plen >> 2, lane, xpm);
-            if (lane == 0) bw[kSctpPktAt / 4 + 2] = crc;                     // stored little-endian (webrtc-sctp put_u32_le)
-            __syncwarp();
-            smem_stream_to_global(buf, kSctpPktAt - hdr, plen + hdr, a.out + oo, lane);
-            if (lane == 0) a.pkt_off[p0 + f] = oo;
-            oo += plen + hdr;
+    const u64 pairs = (a.n + 1) / 2;
+    // this half's next message is pulled towards L2 while the current one is packetised (its offset was fetched a round
+    // earlier, so nothing waits for it): the payload loads below then find their lines a cache level closer
+    u64 mo_next = 2 * (warp + nwarps) + half < a.n ? __ldg(a.msg_off + 2 * (warp + nwarps) + half) : 0;
+    for (u64 pp = warp; pp < pairs; pp += nwarps) {
+        const u64 i = 2 * pp + half;
+        const bool have = i < a.n;
+        u64 mo = 0, mlen = 0, p0 = 0, oo = 0;
+        uint32_t sp = 0, dp = 0, vt = 0, sid = 0, ssn = 0, ppid = 0, t0 = 0, k = 0;
+        if (have) {
+            mo = __ldg(a.msg_off + i); mlen = __ldg(a.msg_off + i + 1) - mo;
+            k = mlen == 0 ? 1u : mlen < 0xfffff000ull ? ((uint32_t)mlen + kSctpMaxPayload - 1) / kSctpMaxPayload
+                                                      : (uint32_t)((mlen + kSctpMaxPayload - 1) / kSctpMaxPayload);
+            p0 = __ldg(a.pkt_first + i); oo = __ldg(a.out_msg_off + i);
+            sp = __ldg(a.src_port + i); dp = __ldg(a.dst_port + i); vt = __ldg(a.vtag + i);
+            sid = __ldg(a.sid + i); ssn = __ldg(a.ssn + i); ppid = __ldg(a.ppid + i); t0 = __ldg(a.tsn0 + i);
         }
-        if (lane == 0 && i == a.n - 1) a.pkt_off[p0 + k] = oo;               // terminator after the last packet
+        {
+            const u64 inx = 2 * (pp + nwarps) + half;
+            if (inx < a.n && hl < 10) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.msg + mo_next + 128 * hl));
+            const u64 inn = 2 * (pp + 2 * nwarps) + half;
+            mo_next = inn < a.n ? __ldg(a.msg_off + inn) : 0;
+        }
+        const uint8_t* m = a.msg + mo;
+        const uint32_t k_other = __shfl_xor_sync(0xffffffffu, k, 16);
+        const uint32_t kmax = k > k_other ? k : k_other;
+        for (uint32_t f = 0; f < kmax; f++) {
+            if (f < k) {                                                         // the same for all 16 lanes of the half
+                const u64 off = (u64)f * kSctpMaxPayload;
+                const uint32_t fl = (uint32_t)(mlen - off < kSctpMaxPayload ? mlen - off : kSctpMaxPayload);
+                const uint32_t padded = (fl + 3) & ~3u, plen = 28 + padded;
+                __syncwarp(hmask);
+                // ---- header words (packet bytes 0..27 -> buffer words 5..11), big-endian fields
+                if (hl < 7) {
+                    uint32_t be;
+                    const uint32_t flags = (f == 0 ? 2u : 0u) | (f == k - 1 ? 1u : 0u);
+                    switch (hl) {
+                        case 0: be = (sp << 16) | dp; break;
+                        case 1: be = vt; break;
+                        case 2: be = 0; break;                                   // checksum, patched below
+                        case 3: be = (0u << 24) | (flags << 16) | (16 + fl); break;
+                        case 4: be = t0 + f; break;
+                        case 5: be = (sid << 16) | ssn; break;
+                        default: be = ppid; break;
+                    }
+                    bw[kSctpPktAt / 4 + hl] = bswap32(be);
+                }
+                if (dtls && hl < 13) {                                           // DTLS record header in front
+                    const uint32_t ep = __ldg(a.epoch + i);
+                    const u64 sq = __ldg(a.seq48_first + i) + f;
+                    uint32_t b;
+                    switch (hl) {
+                        case 0: b = 23; break; case 1: b = 0xfe; break; case 2: b = 0xfd; break;
+                        case 3: b = ep >> 8; break; case 4: b = ep; break;
+                        case 11: b = plen >> 8; break; case 12: b = plen; break;
+                        default: b = (uint32_t)(sq >> (8 * (10 - hl))); break;    // lanes 5..10: seq bytes 5..0
+                    }
+                    buf[kSctpPktAt - 13 + hl] = (uint8_t)b;
+                }
+                // ---- payload, zero padded, into the 16-byte aligned part of the buffer
+#pragma unroll
+                for (int it = 0; it < 5; it++) {                                  // 75 vectors for a full fragment
+                    const uint32_t v = hl + 16 * it;
+                    if (v * 16 < padded) *reinterpret_cast<uint4*>(buf + kSctpPktAt + 28 + 16 * v) = stage_load16<true>(m + off, v, fl);
+                }
+                __syncwarp(hmask);
+                const uint32_t crc = half_crc32c_words(tabs, bw + kSctpPktAt / 4, plen >> 2, hl, hmask, xpm);
+                if (hl == 0) bw[kSctpPktAt / 4 + 2] = crc;                       // stored little-endian (webrtc-sctp put_u32_le)
+                __syncwarp(hmask);
+                half_stream_to_global(buf, kSctpPktAt - hdr, plen + hdr, a.out + oo, hl);
+                if (hl == 0) a.pkt_off[p0 + f] = oo;
+                oo += plen + hdr;
+            }
+        }
+        if (have && hl == 0 && i == a.n - 1) a.pkt_off[p0 + k] = oo;             // terminator after the last packet
     }
 }
 
