@@ -469,7 +469,7 @@ static int32_t ctx_init(p2pt_ctx* ctx, int device, const cudaDeviceProp& prop) {
     CUDA_TRY(nullptr, configure_gcm_mode<kOpen>(ctx->lut_slack));
     CUDA_TRY(nullptr, configure_gcm_mode<kPipeSeal>(ctx->lut_slack));
     CUDA_TRY(nullptr, configure_gcm_mode<kPipeOpen>(ctx->lut_slack));
-    CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_packetize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_smem_bytes(ctx->lut_slack)));
+    CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_packetize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_packetize_smem_bytes(ctx->lut_slack)));
     CUDA_TRY(nullptr, cudaFuncSetAttribute(sctp_unpack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sctp_unpack_smem_bytes(ctx->lut_slack)));
     CUDA_TRY(nullptr, cudaFuncSetAttribute(demux_direct_rank_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * kDirectIds));
     CUDA_TRY(nullptr, cudaFuncSetAttribute(demux_direct_rank_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * kDirectIds));
@@ -895,8 +895,8 @@ int32_t p2pt_sctp_packetize_batch_device(p2pt_ctx* ctx, uint64_t n, const uint8_
     a.n = n; a.msg = msg; a.msg_off = (const u64*)msg_off; a.src_port = src_port; a.dst_port = dst_port; a.vtag = vtag;
     a.sid = sid; a.ssn = ssn; a.ppid = ppid; a.tsn0 = tsn0; a.epoch = epoch; a.seq48_first = (const u64*)seq48_first;
     a.out = out; a.out_msg_off = (const u64*)out_msg_off; a.pkt_first = (const u64*)pkt_first; a.pkt_off = (u64*)pkt_off;
-    const uint32_t smem = sctp_smem_bytes(ctx->lut_slack);
-    sctp_packetize_kernel<<<grid_for(ctx, (n + 1) / 2, kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
+    const uint32_t smem = sctp_packetize_smem_bytes(ctx->lut_slack);
+    sctp_packetize_kernel<<<grid_for(ctx, (n + 32 / kPkLanes - 1) / (32 / kPkLanes), kSctpWarps, 1), 32 * kSctpWarps, smem, (cudaStream_t)stream>>>(a);
     count_launch(ctx);
     CUDA_TRY(ctx, cudaGetLastError());
     return P2PT_OK;

@@ -5,14 +5,15 @@
 // most 1200 bytes, one per packet here, and checksums every packet with CRC32c (crc 3.4.0,
 // Cargo.lock:420-421).  Layout: RFC 4960 3.1 / 3.3.1 / appendix B.
 //
-// HBM-bound byte work again.  One warp per packet.  The packet (or the fragment a packet is built from)
-// comes into shared memory as whole ALIGNED 16-byte vectors by asynchronous copies (cp.async), double
-// buffered: the next packet's bytes are in flight while this one is checksummed, so a warp never waits
-// for global memory (the first version staged through registers and sat at 40 % long-scoreboard
-// stalls).  Every lane runs a table CRC over its own contiguous segment of the staged bytes - wherever
-// they lie: a packet that is not word-aligned in memory is read through a funnel shift - the 32 partial
-// remainders are shifted to their place with a carry-less multiply by x^(8 * bytes after the segment)
-// mod P and XOR-reduced by shuffles; the packetiser writes its output as aligned 16-byte vectors.
+// HBM-bound byte work again, and instruction-bound in practice.  HALF a warp per packet (unpack) or per message
+// (packetise): what is not the CRC - offsets, geometry, staging, header work, stores - is warp-wide instruction
+// stream whatever the number of lanes that need it, so two items per warp halve it per packet.  Unpack: the packet
+// comes into shared memory as whole ALIGNED 16-byte vectors by asynchronous copies (cp.async), double buffered - the
+// next packet's bytes are in flight while this one is checksummed - and is read where it lies (a packet that is not
+// word-aligned in memory goes through a funnel shift).  Packetise: the fragment is staged through registers into a
+// 16-byte aligned position behind the header words.  Either way every lane runs a table CRC over its own contiguous
+// 20-word segment, the 16 partial remainders are shifted to their place with a carry-less multiply by
+// x^(8 * bytes after the segment) mod P and XOR-reduced by shuffles.
 #pragma once
 #include "common.cuh"
 #include "gcm_math.cuh"
@@ -26,12 +27,11 @@ constexpr uint32_t kSctpMaxPacket = 28 + kSctpMaxPayload;            // 1228
 constexpr int kSctpWarps = 32;                                       // warps (packets in flight) per block, 1 block per SM
 // One staging buffer: kSctpFront bytes in front (zeros for the checksum's leading words; the packetiser builds its
 // headers there), then the raw aligned vectors (15 + 1228 + 15 bytes at most), then one spare vector (an unaligned
-// word read looks one word ahead).  Two buffers per warp.
+// word read looks one word ahead).  The unpack kernel's buffers (two per half warp: double buffering).
 constexpr uint32_t kSctpFront = 96;
 constexpr uint32_t kSctpRawBytes = 1264;
 constexpr uint32_t kSctpBufBytes = kSctpFront + kSctpRawBytes + 16;
 constexpr uint32_t kCrcLutBytes = 65536;                             // 256 rows x (T0 | T1) x 32 replicas x 4 B
-constexpr uint32_t kSctpStageBytes = 2 * kSctpWarps * kSctpBufBytes;
 
 // slice-by-4 tables and x^(8k) mod P for k = 0..1279, reflected representation; filled by the host
 __device__ uint32_t g_crc_tab[4][256];
@@ -40,9 +40,7 @@ __device__ uint32_t g_crc_xpow[1280];
 // Shared-memory map, like the record kernel's: the CRC tables sit on a 64 KiB boundary of the shared
 // window so that one PRMT builds a lookup address (byte << 8 | lane << 2 | base); every table entry is
 // replicated 32x, lane l only touches bank l, so data-dependent lookups never conflict.  The staging
-// buffers live behind the tables.
-__host__ __device__ constexpr uint32_t sctp_smem_bytes(uint32_t slack) { return slack + kCrcLutBytes + kSctpStageBytes; }
-
+// buffers fill the gap below the tables first and continue behind them (sctp_*_smem_bytes below).
 struct CrcLut {
     uint32_t lb;     // 64 KiB-aligned shared address of the tables + 4 * lane
     template <int K, int T> __device__ __forceinline__ uint32_t look(uint32_t w) const {
@@ -69,44 +67,8 @@ __device__ __forceinline__ uint32_t crc_mulmod(const CrcLut& t, uint32_t a, cons
     return crc_word(t, 0u, (uint32_t)p) ^ (uint32_t)(p >> 32);
 }
 
-constexpr int kCrcSeg = 10;                              // 32 lanes x 10 words = 1280 bytes >= the largest packet
+constexpr int kCrcSeg = 10;                              // g_crc_init covers packets of up to 32 x 10 words = 1280 bytes
 __device__ uint32_t g_crc_init[kCrcSeg * 32 + 1];        // init-value contribution for a packet of w words
-
-// CRC32c of a staged packet of nwords <= 320 words whose byte 0 lies at byte offset pkt0 of the buffer (any
-// alignment; ALIGNED = pkt0 is a multiple of 4, the usual case).  The checksum field must hold zero and the 40
-// bytes in front of the packet must be zero.  All 32 lanes call; every lane gets the result.
-// The segments are aligned to the END of the packet: lane l owns the kCrcSeg words that end
-// (31 - l) * kCrcSeg words before the end, so the shift x^(8 * bytes after) is a per-lane constant (its classes
-// `xpm`, computed once per kernel), every lane runs the same kCrcSeg steps without a bounds test (words before
-// the packet start read the zeros in front of it, which leave a zero register unchanged; a lane whose whole
-// segment lies before the packet skips them), and the 0xFFFFFFFF init value is added by linearity from a table
-// indexed by the packet length.
-template <bool ALIGNED>
-__device__ __forceinline__ uint32_t warp_crc32c(const CrcLut& t, const uint8_t* buf, uint32_t pkt0, uint32_t nwords, int lane,
-                                                const uint32_t (&xpm)[kGhashClasses]) {
-    const int first = (int)nwords - (32 - lane) * kCrcSeg;          // may be negative: leading zero words
-    uint32_t c = 0;
-    if (first > -kCrcSeg) {
-        const uint32_t* q = reinterpret_cast<const uint32_t*>(buf) + (int)(pkt0 >> 2) + first;
-        if (ALIGNED) {
-#pragma unroll
-            for (int i = 0; i < kCrcSeg; i++) c = crc_word(t, c, q[i]);
-        } else {
-            const unsigned sh = (pkt0 & 3) * 8;
-            uint32_t lo = q[0];
-#pragma unroll
-            for (int i = 0; i < kCrcSeg; i++) {
-                const uint32_t hi = q[i + 1];
-                c = crc_word(t, c, __funnelshift_r(lo, hi, sh));
-                lo = hi;
-            }
-        }
-    }
-    uint32_t part = crc_mulmod(t, c, xpm);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) part ^= __shfl_xor_sync(0xffffffffu, part, o);
-    return ~(part ^ g_crc_init[nwords]);
-}
 
 // packet word i (32-bit, little-endian load) of a staged packet
 __device__ __forceinline__ uint32_t staged_word(const uint8_t* buf, uint32_t pkt0, int i) {
@@ -120,60 +82,10 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
-// Start the copy of the aligned 16-byte vectors that cover [src, src + len) into the raw region of `buf`
-// (byte `src` lands at offset kSctpFront + (src & 15)).  An aligned vector that holds at least one byte of the
-// item is always readable, and no other vector is touched.  One commit group per call, also when len == 0.
-__device__ __forceinline__ void stage_async(uint8_t* buf, const uint8_t* src, uint32_t len, int lane) {
-    const uint32_t sa = (uint32_t)((uintptr_t)src & 15);
-    const uint32_t nvec = len ? (sa + len + 15) >> 4 : 0;
-#pragma unroll
-    for (int it = 0; it < 3; it++) {                                  // <= 79 vectors
-        const uint32_t v = lane + 32 * it;
-        if (v < nvec) cp_async16(buf + kSctpFront + 16 * v, src - sa + 16 * (size_t)v);
-    }
-    cp_async_commit();
-}
-
-// common prologue of the two packet kernels: fill the replicated tables, hand every warp its two buffers (fronts
-// zeroed), fetch the lane's constant CRC shift (see warp_crc32c)
-__device__ __forceinline__ uint8_t* sctp_smem_setup(uint8_t* dyn_smem, CrcLut& lut, uint32_t (&xpm)[kGhashClasses]) {
-    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(dyn_smem);
-    const uint32_t tbase = (sbase + 0xffffu) & ~0xffffu;
-    uint32_t* tabs = reinterpret_cast<uint32_t*>(dyn_smem + (tbase - sbase));
-    for (int idx = threadIdx.x; idx < 256 * 32; idx += blockDim.x) {
-        const int x = idx >> 5, l = idx & 31;
-        tabs[x * 64 + l] = g_crc_tab[0][x];
-        tabs[x * 64 + 32 + l] = g_crc_tab[1][x];
-    }
-    lut.lb = tbase + 4u * (threadIdx.x & 31);
-    ghash_classes(g_crc_xpow[(31 - (threadIdx.x & 31)) * kCrcSeg * 4], xpm);
-    uint8_t* mine = dyn_smem + (tbase - sbase) + kCrcLutBytes + (threadIdx.x >> 5) * (2 * kSctpBufBytes);
-    for (uint32_t w = threadIdx.x & 31; w < 2 * kSctpBufBytes / 4; w += 32) reinterpret_cast<uint32_t*>(mine)[w] = 0;
-    __syncthreads();
-    return mine;
-}
-
 // ---- the packetiser stages through registers (the asynchronous-copy form of it measured slower: 1.10 instead of
 //      0.93 ms per 1 M packets - byte-wise header and padding stores, and its message metadata still waits) ----
 constexpr uint32_t kSctpPktAt = 20;      // packet byte 0 sits at buffer byte 20 -> payload (packet byte 28) at 48, 16-aligned;
                                          // an optional DTLS header occupies 7..19
-// CRC32c of a packet staged word-aligned at `words` (nwords <= 320; checksum field zeroed by the caller).  Same end-aligned
-// segments as warp_crc32c, with a bounds test per word instead of zeros in front.
-__device__ __forceinline__ uint32_t warp_crc32c_words(const CrcLut& t, const uint32_t* words, uint32_t nwords, int lane, const uint32_t (&xpm)[kGhashClasses]) {
-    const int first = (int)nwords - (32 - lane) * kCrcSeg;          // may be negative: leading zero words
-    uint32_t c = 0;
-#pragma unroll
-    for (int i = 0; i < kCrcSeg; i++) {
-        const int wi = first + i;
-        const uint32_t v = wi >= 0 ? words[wi] : 0u;
-        c = crc_word(t, c, v);
-    }
-    uint32_t part = crc_mulmod(t, c, xpm);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) part ^= __shfl_xor_sync(0xffffffffu, part, o);
-    return ~(part ^ g_crc_init[nwords]);
-}
-
 // 16 payload bytes at src + 16 v for staging, built from the two ALIGNED source vectors that cover them
 // (one funnel when the source is not 16-byte aligned).  An aligned vector is read only if it holds at
 // least one byte of the item, so nothing outside the item's own 16-byte blocks is touched; with ZERO_TAIL
@@ -206,27 +118,6 @@ __device__ __forceinline__ uint4 stage_load16(const uint8_t* src, uint32_t v, ui
     return r;
 }
 
-// smem byte stream [start, start + nbytes) of a 4-byte aligned buffer -> dst (any alignment):
-// aligned 32-bit stores built from two adjacent shared words, byte stores only at the two ends.
-__device__ __forceinline__ void smem_stream_to_global(const uint8_t* sbuf, uint32_t start, uint32_t nbytes,
-                                                      uint8_t* dst, int lane) {
-    uint32_t head = (uint32_t)((4 - ((uintptr_t)dst & 3)) & 3);
-    if (head > nbytes) head = nbytes;
-    if ((uint32_t)lane < head) dst[lane] = sbuf[start + lane];
-    const uint32_t body = nbytes - head, nfull = body >> 2;
-    const uint32_t so = start + head;                    // stream offset of the first aligned destination word
-    const uint32_t* sw = reinterpret_cast<const uint32_t*>(sbuf) + (so >> 2);
-    const unsigned sh = (so & 3) * 8;
-    uint32_t* dw = reinterpret_cast<uint32_t*>(dst + head);
-#pragma unroll
-    for (int it = 0; it < 10; it++) {
-        const uint32_t j = lane + 32 * it;
-        if (j < nfull) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
-    }
-    for (uint32_t j = lane + 320; j < nfull; j += 32) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
-    for (uint32_t b = (nfull << 2) + lane; b < body; b += 32) dst[head + b] = sbuf[so + b];
-}
-
 struct SctpPacketizeArgs {
     u64 n;                                  // messages
     const uint8_t* msg; const u64* msg_off;
@@ -238,62 +129,96 @@ struct SctpPacketizeArgs {
     u64* pkt_off;                                         // out: byte offset of every packet (+ 1 terminator)
 };
 
-// A message per HALF warp, like the unpack kernel's packet per half warp (see there): the per-message and per-packet
-// bookkeeping is warp-wide instruction stream, two messages per warp halve it per packet.
-constexpr int kCrcSegHalfWords = 20;                                  // 16 lanes x 20 words = 1280 bytes
-__device__ __forceinline__ uint32_t half_crc32c_words(const CrcLut& t, const uint32_t* words, uint32_t nwords, int hl, uint32_t hmask,
-                                                      const uint32_t (&xpm)[kGhashClasses]) {
-    const int first = (int)nwords - (16 - hl) * kCrcSegHalfWords;   // may be negative: leading zero words
+// A message per GROUP of kPkLanes lanes (half or quarter of a warp), like the unpack kernel's packet per half warp (see
+// there): the per-message and per-packet bookkeeping is warp-wide instruction stream, several messages per warp divide
+// it per packet; a lane's CRC segment grows to 320 / kPkLanes words at the same cost per packet.  One staging buffer per
+// group; they fill the gap below the tables first.  Measured per 1 M packets: a warp per message 0.915 ms, half a warp
+// 0.767 ms, a quarter 0.804 ms (40-word CRC chains per lane, ten staging vectors per lane: the serial part grows).
+#ifndef P2PT_SCTP_PK_LANES
+#define P2PT_SCTP_PK_LANES 16
+#endif
+constexpr int kPkLanes = P2PT_SCTP_PK_LANES;
+static_assert(kPkLanes == 8 || kPkLanes == 16, "a message per quarter or half warp");
+constexpr int kPkSegWords = 320 / kPkLanes;                            // kPkLanes x kPkSegWords words = 1280 bytes
+constexpr uint32_t kPkBufBytes = 1296;                                // packet at byte 20 + 1228 + slack, a multiple of 16
+constexpr uint32_t kPkBufs = kSctpWarps * (32 / kPkLanes);
+__host__ __device__ constexpr uint32_t sctp_packetize_smem_bytes(uint32_t slack) {
+    const uint32_t low = slack / kPkBufBytes;
+    return slack + kCrcLutBytes + (kPkBufs > low ? (kPkBufs - low) * kPkBufBytes : 0u);
+}
+// CRC32c of a packet staged word-aligned at `words` (nwords <= 320; checksum field zeroed by the caller), by the kPkLanes
+// lanes of a group; every lane of the group gets the result.  The segments are aligned to the END of the packet: lane l
+// owns the kPkSegWords words that end (kPkLanes - 1 - l) segments before the end, so the shift x^(8 * bytes after) is a
+// per-lane constant (its classes `xpm`, computed once per kernel) and every lane runs the same number of steps; words
+// before the packet start count as zero (they leave a zero register unchanged), and the 0xFFFFFFFF init value is added
+// by linearity from a table indexed by the packet length.
+__device__ __forceinline__ uint32_t group_crc32c_words(const CrcLut& t, const uint32_t* words, uint32_t nwords, int gl, uint32_t gmask,
+                                                       const uint32_t (&xpm)[kGhashClasses]) {
+    const int first = (int)nwords - (kPkLanes - gl) * kPkSegWords;   // may be negative: leading zero words
     uint32_t c = 0;
 #pragma unroll 5
-    for (int i = 0; i < kCrcSegHalfWords; i++) {
+    for (int i = 0; i < kPkSegWords; i++) {
         const int wi = first + i;
         const uint32_t v = wi >= 0 ? words[wi] : 0u;
         c = crc_word(t, c, v);
     }
     uint32_t part = crc_mulmod(t, c, xpm);
 #pragma unroll
-    for (int o = 8; o > 0; o >>= 1) part ^= __shfl_xor_sync(hmask, part, o, 16);
+    for (int o = kPkLanes / 2; o > 0; o >>= 1) part ^= __shfl_xor_sync(gmask, part, o, kPkLanes);
     return ~(part ^ g_crc_init[nwords]);
 }
-// smem_stream_to_global by 16 lanes
-__device__ __forceinline__ void half_stream_to_global(const uint8_t* sbuf, uint32_t start, uint32_t nbytes, uint8_t* dst, int hl) {
+// smem byte stream [start, start + nbytes) of a 4-byte aligned buffer -> dst (any alignment) by the kPkLanes lanes of a
+// group: aligned 32-bit stores built from two adjacent shared words, byte stores only at the two ends
+__device__ __forceinline__ void group_stream_to_global(const uint8_t* sbuf, uint32_t start, uint32_t nbytes, uint8_t* dst, int gl) {
     uint32_t head = (uint32_t)((4 - ((uintptr_t)dst & 3)) & 3);
     if (head > nbytes) head = nbytes;
-    if ((uint32_t)hl < head) dst[hl] = sbuf[start + hl];
+    if ((uint32_t)gl < head) dst[gl] = sbuf[start + gl];
     const uint32_t body = nbytes - head, nfull = body >> 2;
     const uint32_t so = start + head;                    // stream offset of the first aligned destination word
     const uint32_t* sw = reinterpret_cast<const uint32_t*>(sbuf) + (so >> 2);
     const unsigned sh = (so & 3) * 8;
     uint32_t* dw = reinterpret_cast<uint32_t*>(dst + head);
 #pragma unroll 5
-    for (int it = 0; it < 20; it++) {
-        const uint32_t j = hl + 16 * it;
+    for (int it = 0; it < kPkSegWords; it++) {
+        const uint32_t j = gl + kPkLanes * it;
         if (j < nfull) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
     }
-    for (uint32_t j = hl + 320; j < nfull; j += 16) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
-    for (uint32_t b = (nfull << 2) + hl; b < body; b += 16) dst[head + b] = sbuf[so + b];
+    for (uint32_t j = gl + 320; j < nfull; j += kPkLanes) dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
+    for (uint32_t b = (nfull << 2) + gl; b < body; b += kPkLanes) dst[head + b] = sbuf[so + b];
 }
 
 __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_packetize_kernel(const SctpPacketizeArgs a) {
     extern __shared__ __align__(16) uint8_t sctp_dyn_smem[];
-    CrcLut tabs;
+    constexpr int GPW = 32 / kPkLanes;                                   // groups (messages in flight) per warp
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, grp = lane / kPkLanes, gl = lane % kPkLanes;
+    const uint32_t gmask = (kPkLanes == 16 ? 0xffffu : 0xffu) << (kPkLanes * grp);
+    // ---- tables on their 64 KiB boundary, staging buffers below them first
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sctp_dyn_smem);
+    const uint32_t tbase = (sbase + 0xffffu) & ~0xffffu;
+    {
+        uint32_t* tb = reinterpret_cast<uint32_t*>(sctp_dyn_smem + (tbase - sbase));
+        for (int idx = threadIdx.x; idx < 256 * 32; idx += blockDim.x) {
+            const int x = idx >> 5, l = idx & 31;
+            tb[x * 64 + l] = g_crc_tab[0][x];
+            tb[x * 64 + 32 + l] = g_crc_tab[1][x];
+        }
+    }
+    __syncthreads();
+    CrcLut tabs; tabs.lb = tbase + 4u * (uint32_t)lane;
     uint32_t xpm[kGhashClasses];
-    uint8_t* bufs = sctp_smem_setup(sctp_dyn_smem, tabs, xpm);         // two buffers per warp: one per half here
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, half = lane >> 4, hl = lane & 15;
-    const uint32_t hmask = 0xffffu << (16 * half);
-    ghash_classes(g_crc_xpow[(15 - hl) * kCrcSegHalfWords * 4], xpm);   // the shift of a 20-word segment
-    uint8_t* buf = bufs + half * kSctpBufBytes;
+    ghash_classes(g_crc_xpow[(kPkLanes - 1 - gl) * kPkSegWords * 4], xpm);   // the shift of this lane's segment
+    const uint32_t n_low = (tbase - sbase) / kPkBufBytes, q = (uint32_t)(wib * GPW + grp);
+    uint8_t* buf = q < n_low ? sctp_dyn_smem + q * kPkBufBytes : sctp_dyn_smem + (tbase - sbase) + kCrcLutBytes + (q - n_low) * kPkBufBytes;
     uint32_t* bw = reinterpret_cast<uint32_t*>(buf);
     const bool dtls = a.epoch != nullptr;
     const uint32_t hdr = dtls ? 13u : 0u;
     const u64 warp = (u64)blockIdx.x * kSctpWarps + wib, nwarps = (u64)gridDim.x * kSctpWarps;
-    const u64 pairs = (a.n + 1) / 2;
-    // this half's next message is pulled towards L2 while the current one is packetised (its offset was fetched a round
+    const u64 bundles = (a.n + GPW - 1) / GPW;                           // GPW consecutive messages per warp and step
+    // this group's next message is pulled towards L2 while the current one is packetised (its offset was fetched a round
     // earlier, so nothing waits for it): the payload loads below then find their lines a cache level closer
-    u64 mo_next = 2 * (warp + nwarps) + half < a.n ? __ldg(a.msg_off + 2 * (warp + nwarps) + half) : 0;
-    for (u64 pp = warp; pp < pairs; pp += nwarps) {
-        const u64 i = 2 * pp + half;
+    u64 mo_next = GPW * (warp + nwarps) + grp < a.n ? __ldg(a.msg_off + GPW * (warp + nwarps) + grp) : 0;
+    for (u64 pp = warp; pp < bundles; pp += nwarps) {
+        const u64 i = GPW * pp + grp;
         const bool have = i < a.n;
         u64 mo = 0, mlen = 0, p0 = 0, oo = 0;
         uint32_t sp = 0, dp = 0, vt = 0, sid = 0, ssn = 0, ppid = 0, t0 = 0, k = 0;
@@ -306,25 +231,26 @@ __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_packetize_kernel(cons
             sid = __ldg(a.sid + i); ssn = __ldg(a.ssn + i); ppid = __ldg(a.ppid + i); t0 = __ldg(a.tsn0 + i);
         }
         {
-            const u64 inx = 2 * (pp + nwarps) + half;
-            if (inx < a.n && hl < 10) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.msg + mo_next + 128 * hl));
-            const u64 inn = 2 * (pp + 2 * nwarps) + half;
+            const u64 inx = GPW * (pp + nwarps) + grp;
+            if (inx < a.n) for (int l = gl; l < 10; l += kPkLanes) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.msg + mo_next + 128 * l));
+            const u64 inn = GPW * (pp + 2 * nwarps) + grp;
             mo_next = inn < a.n ? __ldg(a.msg_off + inn) : 0;
         }
         const uint8_t* m = a.msg + mo;
-        const uint32_t k_other = __shfl_xor_sync(0xffffffffu, k, 16);
-        const uint32_t kmax = k > k_other ? k : k_other;
+        uint32_t kmax = k;
+#pragma unroll
+        for (int o = kPkLanes; o < 32; o <<= 1) { const uint32_t ko = __shfl_xor_sync(0xffffffffu, kmax, o); kmax = ko > kmax ? ko : kmax; }
         for (uint32_t f = 0; f < kmax; f++) {
-            if (f < k) {                                                         // the same for all 16 lanes of the half
+            if (f < k) {                                                         // the same for all lanes of the group
                 const u64 off = (u64)f * kSctpMaxPayload;
                 const uint32_t fl = (uint32_t)(mlen - off < kSctpMaxPayload ? mlen - off : kSctpMaxPayload);
                 const uint32_t padded = (fl + 3) & ~3u, plen = 28 + padded;
-                __syncwarp(hmask);
+                __syncwarp(gmask);
                 // ---- header words (packet bytes 0..27 -> buffer words 5..11), big-endian fields
-                if (hl < 7) {
+                if (gl < 7) {
                     uint32_t be;
                     const uint32_t flags = (f == 0 ? 2u : 0u) | (f == k - 1 ? 1u : 0u);
-                    switch (hl) {
+                    switch (gl) {
                         case 0: be = (sp << 16) | dp; break;
                         case 1: be = vt; break;
                         case 2: be = 0; break;                                   // checksum, patched below
@@ -333,36 +259,38 @@ __global__ void __launch_bounds__(32 * kSctpWarps, 1) sctp_packetize_kernel(cons
                         case 5: be = (sid << 16) | ssn; break;
                         default: be = ppid; break;
                     }
-                    bw[kSctpPktAt / 4 + hl] = bswap32(be);
+                    bw[kSctpPktAt / 4 + gl] = bswap32(be);
                 }
-                if (dtls && hl < 13) {                                           // DTLS record header in front
+                if (dtls) {                                                      // DTLS record header in front
                     const uint32_t ep = __ldg(a.epoch + i);
                     const u64 sq = __ldg(a.seq48_first + i) + f;
-                    uint32_t b;
-                    switch (hl) {
-                        case 0: b = 23; break; case 1: b = 0xfe; break; case 2: b = 0xfd; break;
-                        case 3: b = ep >> 8; break; case 4: b = ep; break;
-                        case 11: b = plen >> 8; break; case 12: b = plen; break;
-                        default: b = (uint32_t)(sq >> (8 * (10 - hl))); break;    // lanes 5..10: seq bytes 5..0
+                    for (int h = gl; h < 13; h += kPkLanes) {
+                        uint32_t b;
+                        switch (h) {
+                            case 0: b = 23; break; case 1: b = 0xfe; break; case 2: b = 0xfd; break;
+                            case 3: b = ep >> 8; break; case 4: b = ep; break;
+                            case 11: b = plen >> 8; break; case 12: b = plen; break;
+                            default: b = (uint32_t)(sq >> (8 * (10 - h))); break;  // bytes 5..10: seq bytes 5..0
+                        }
+                        buf[kSctpPktAt - 13 + h] = (uint8_t)b;
                     }
-                    buf[kSctpPktAt - 13 + hl] = (uint8_t)b;
                 }
                 // ---- payload, zero padded, into the 16-byte aligned part of the buffer
-#pragma unroll
-                for (int it = 0; it < 5; it++) {                                  // 75 vectors for a full fragment
-                    const uint32_t v = hl + 16 * it;
+#pragma unroll 5
+                for (int it = 0; it < 80 / kPkLanes; it++) {                      // 75 vectors for a full fragment
+                    const uint32_t v = gl + kPkLanes * it;
                     if (v * 16 < padded) *reinterpret_cast<uint4*>(buf + kSctpPktAt + 28 + 16 * v) = stage_load16<true>(m + off, v, fl);
                 }
-                __syncwarp(hmask);
-                const uint32_t crc = half_crc32c_words(tabs, bw + kSctpPktAt / 4, plen >> 2, hl, hmask, xpm);
-                if (hl == 0) bw[kSctpPktAt / 4 + 2] = crc;                       // stored little-endian (webrtc-sctp put_u32_le)
-                __syncwarp(hmask);
-                half_stream_to_global(buf, kSctpPktAt - hdr, plen + hdr, a.out + oo, hl);
-                if (hl == 0) a.pkt_off[p0 + f] = oo;
+                __syncwarp(gmask);
+                const uint32_t crc = group_crc32c_words(tabs, bw + kSctpPktAt / 4, plen >> 2, gl, gmask, xpm);
+                if (gl == 0) bw[kSctpPktAt / 4 + 2] = crc;                       // stored little-endian (webrtc-sctp put_u32_le)
+                __syncwarp(gmask);
+                group_stream_to_global(buf, kSctpPktAt - hdr, plen + hdr, a.out + oo, gl);
+                if (gl == 0) a.pkt_off[p0 + f] = oo;
                 oo += plen + hdr;
             }
         }
-        if (have && hl == 0 && i == a.n - 1) a.pkt_off[p0 + k] = oo;             // terminator after the last packet
+        if (have && gl == 0 && i == a.n - 1) a.pkt_off[p0 + k] = oo;             // terminator after the last packet
     }
 }
 
@@ -386,7 +314,8 @@ __host__ __device__ constexpr uint32_t sctp_unpack_smem_bytes(uint32_t slack) {
     return slack + kCrcLutBytes + (kUnpackBufs > low ? (kUnpackBufs - low) * kSctpBufBytes : 0u);
 }
 
-// warp_crc32c for a packet held by 16 lanes (hl = lane & 15): same end-aligned segments, 20 words each
+// The same for a packet that lies anywhere in its staging buffer (byte 0 at offset pkt0; ALIGNED = a multiple of 4), held by
+// 16 lanes (hl = lane & 15), 20 words each: the bytes in front of the packet are zero, so there is no bounds test per word
 template <bool ALIGNED>
 __device__ __forceinline__ uint32_t half_crc32c(const CrcLut& t, const uint8_t* buf, uint32_t pkt0, uint32_t nwords, int hl,
                                                 uint32_t hmask, const uint32_t (&xpm)[kGhashClasses]) {
