@@ -30,7 +30,7 @@ constexpr int kSctpWarps = 32;                                       // warps (p
 // word read looks one word ahead).  The unpack kernel's buffers (two per half warp: double buffering).
 constexpr uint32_t kSctpFront = 96;
 constexpr uint32_t kSctpRawBytes = 1264;
-constexpr uint32_t kSctpBufBytes = kSctpFront + kSctpRawBytes + 16;
+constexpr uint32_t kSctpBufBytes = kSctpFront + kSctpRawBytes + 16;        // (padding it to 16 mod 32 words like kPkBufBytes: no gain here)
 constexpr uint32_t kCrcLutBytes = 65536;                             // 256 rows x (T0 | T1) x 32 replicas x 4 B
 
 // slice-by-4 tables and x^(8k) mod P for k = 0..1279, reflected representation; filled by the host
@@ -140,7 +140,8 @@ struct SctpPacketizeArgs {
 constexpr int kPkLanes = P2PT_SCTP_PK_LANES;
 static_assert(kPkLanes == 8 || kPkLanes == 16, "a message per quarter or half warp");
 constexpr int kPkSegWords = 320 / kPkLanes;                            // kPkLanes x kPkSegWords words = 1280 bytes
-constexpr uint32_t kPkBufBytes = 1296;                                // packet at byte 20 + 1228 + slack, a multiple of 16
+constexpr uint32_t kPkBufBytes = 1344;                                // packet at byte 20 + 1228 + slack; 336 words = 16 mod 32: the two
+                                                                      // halves of a warp, each in its own buffer, use disjoint banks
 constexpr uint32_t kPkBufs = kSctpWarps * (32 / kPkLanes);
 __host__ __device__ constexpr uint32_t sctp_packetize_smem_bytes(uint32_t slack) {
     const uint32_t low = slack / kPkBufBytes;
