@@ -28,8 +28,8 @@ constexpr int kSctpWarps = 32;                                       // warps (p
 // One staging buffer: kSctpFront bytes in front (zeros for the checksum's leading words; the packetiser builds its
 // headers there), then the raw aligned vectors (15 + 1228 + 15 bytes at most), then one spare vector (an unaligned
 // word read looks one word ahead).  The unpack kernel's buffers (two per half warp: double buffering).
-constexpr uint32_t kSctpFront = 96;
-constexpr uint32_t kSctpRawBytes = 1264;
+constexpr uint32_t kSctpFront = 48;
+constexpr uint32_t kSctpRawBytes = 1248;
 constexpr uint32_t kSctpBufBytes = kSctpFront + kSctpRawBytes + 16;        // (padding it to 16 mod 32 words like kPkBufBytes: no gain here)
 constexpr uint32_t kCrcLutBytes = 65536;                             // 256 rows x (T0 | T1) x 32 replicas x 4 B
 
@@ -305,9 +305,10 @@ struct SctpUnpackArgs {
 // The unpack kernel gives a packet to HALF a warp: everything that is not the CRC itself - offsets, geometry, staging,
 // fix-ups, header parse, the stores of info / desc - is warp-wide instruction stream whatever the number of lanes that
 // need it (it was 290 of the 492 warp instructions per packet with a warp per packet), so two packets per warp halve it
-// per packet; a lane's CRC segment doubles to 20 words, which costs the same per packet.  24 warps per block: their
-// 96 staging buffers (two packets x double buffering) fill the gap below the tables first.
-constexpr int kUnpackWarps = 24;
+// per packet; a lane's CRC segment doubles to 20 words, which costs the same per packet.  30 warps per block: their
+// 120 staging buffers (two packets x double buffering, 1312 bytes each) fill the gap below the tables first (24 warps
+// with 1376-byte buffers: 0.507 ms per 1 M packets, 30 warps: 0.478 ms; 32 would need 16 bytes more than an SM has).
+constexpr int kUnpackWarps = 30;
 constexpr int kCrcSegHalf = 20;                                       // 16 lanes x 20 words = 1280 bytes
 constexpr uint32_t kUnpackBufs = kUnpackWarps * 4;
 __host__ __device__ constexpr uint32_t sctp_unpack_smem_bytes(uint32_t slack) {
