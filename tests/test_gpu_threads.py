@@ -129,3 +129,50 @@ def test_slot_bytes_beyond_the_item_are_zero(ctx):
     w_off = np.arange(n + 1, dtype=np.uint64) * np.uint64(37 + L)
     r = ctx.pipeline_open_demux(session, rec, w_off, max_streams=n, gathered_cap=int(rec.size), want_out=True)
     assert not r["out"].reshape(n, 37 + L)[:, 13 + L:].any()
+
+
+def test_eight_threads_demux_on_one_context_share_the_side_streams(ctx):
+    """p2pt_frame_decode_demux_batch from eight threads at once on ONE context: every call takes the sort-free path
+    (max_streams <= 8192), whose on-device fallback is enqueued on one of the context's eight side streams - handed out
+    round-robin, so concurrent calls share them.  Results must equal the oracle's for every thread and repetition, also
+    for the batch that overflows the direct path and comes out of the fallback (capacity error with the exact count)."""
+    import p2p_llm_tunnel_b200 as p2pt
+    from test_gpu_parity import make_frames
+    NT, REPS = 8, 6
+    rng = np.random.default_rng(0x7EA0)
+    work = []
+    for i in range(NT):
+        n = int(rng.integers(3000, 40000))
+        buf, off = make_frames(rng, n, int(rng.integers(1, 3000)), corrupt=0.02)
+        d = ob.frame_decode(buf, off)
+        work.append((buf, off, ob.frame_demux(d, buf)))
+    # one thread's batch has more streams than the direct path holds
+    big_buf, big_off = make_frames(rng, 60000, 20000, corrupt=0)
+    big_k = ob.frame_demux(ob.frame_decode(big_buf, big_off), big_buf)["k"]
+    assert big_k > 8192
+    errs = []
+
+    def run(i):
+        try:
+            buf, off, exp = work[i]
+            for rep in range(REPS):
+                if i == 3 and rep % 2:
+                    try:
+                        ctx.frame_decode_demux(big_buf, big_off, 8192, gathered_cap=len(big_buf))
+                        raise AssertionError("expected a capacity error")
+                    except p2pt.P2ptError as e:
+                        assert e.code == -3
+                    continue
+                r = ctx.frame_decode_demux(buf, off, 8192, gathered_cap=int(exp["gathered_off"][-1]))
+                assert r["k"] == exp["k"]
+                for key in ("uniq_sid", "csr", "perm", "gathered_off", "gathered"):
+                    assert np.array_equal(r[key], exp[key]), (i, rep, key)
+        except Exception as e:       # noqa: BLE001
+            errs.append((i, e))
+
+    ts = [threading.Thread(target=run, args=(i,)) for i in range(NT)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
