@@ -28,7 +28,7 @@ constexpr int kSctpWarps = 32;                                       // warps (p
 // One staging buffer: kSctpFront bytes in front (zeros for the checksum's leading words; the packetiser builds its
 // headers there), then the raw aligned vectors (15 + 1228 + 15 bytes at most), then one spare vector (an unaligned
 // word read looks one word ahead).  The unpack kernel's buffers (two per half warp: double buffering).
-constexpr uint32_t kSctpFront = 80;
+constexpr uint32_t kSctpFront = 48;
 constexpr uint32_t kSctpRawBytes = 1248;
 constexpr uint32_t kSctpBufBytes = kSctpFront + kSctpRawBytes + 16;        // (padding it to 16 mod 32 words like kPkBufBytes: no gain here)
 constexpr uint32_t kCrcLutBytes = 65536;                             // 256 rows x (T0 | T1) x 32 replicas x 4 B
@@ -316,39 +316,34 @@ __host__ __device__ constexpr uint32_t sctp_unpack_smem_bytes(uint32_t slack) {
     return slack + kCrcLutBytes + (kUnpackBufs > low ? (kUnpackBufs - low) * kSctpBufBytes : 0u);
 }
 
-// CRC32c of a packet that lies anywhere in its staging buffer (byte 0 at offset pkt0; ALIGNED = a multiple of 4), held by
-// 16 lanes (hl = lane & 15), 20 words each, end-aligned: a lane whose segment lies wholly in front of the packet has
-// nothing to do, every other lane starts at most 19 words in front of it, where kSctpFront bytes of zeros lie - no bounds
-// test and no trip count per lane.  The 20 words run as TWO chains of 10 (a CRC step is two dependent table rounds, and
-// the two packets of a warp share one instruction stream, so a single chain leaves the warp waiting on shared memory);
-// the chains meet in the carry-less product: c_front * x^(segment offset + 10 words) + c_back * x^(segment offset),
-// reduced once.
+// The same for a packet that lies anywhere in its staging buffer (byte 0 at offset pkt0; ALIGNED = a multiple of 4), held by
+// 16 lanes (hl = lane & 15), 20 words each: the bytes in front of the packet are zero, so there is no bounds test per word
 template <bool ALIGNED>
 __device__ __forceinline__ uint32_t half_crc32c(const CrcLut& t, const uint8_t* buf, uint32_t pkt0, uint32_t nwords, int hl,
-                                                uint32_t hmask, const uint32_t (&xpm_front)[kGhashClasses],
-                                                const uint32_t (&xpm_back)[kGhashClasses]) {
-    constexpr int kChain = kCrcSegHalf / 2;
+                                                uint32_t hmask, const uint32_t (&xpm)[kGhashClasses]) {
     const int first = (int)nwords - (16 - hl) * kCrcSegHalf;
-    uint32_t cf = 0, cb = 0;
+    uint32_t c = 0;
     if (first > -kCrcSegHalf) {
-        const uint32_t* q = reinterpret_cast<const uint32_t*>(buf) + (int)(pkt0 >> 2) + first;
+        // words before the packet start: zeros lie in front of it, but only kSctpFront bytes of them - clamp
+        const uint32_t* q0 = reinterpret_cast<const uint32_t*>(buf) + (int)(pkt0 >> 2);
+        const int lo = first < -(int)(kSctpFront / 4 - 4) ? -(int)(kSctpFront / 4 - 4) : first;      // still all zeros in front
+        const uint32_t* q = q0 + lo;
+        const int steps = first + kCrcSegHalf - lo;                   // <= 20; the skipped leading words are zero
         if (ALIGNED) {
-#pragma unroll
-            for (int i = 0; i < kChain; i++) { cf = crc_word(t, cf, q[i]); cb = crc_word(t, cb, q[kChain + i]); }
+#pragma unroll 5
+            for (int i = 0; i < steps; i++) c = crc_word(t, c, q[i]);
         } else {
             const unsigned sh = (pkt0 & 3) * 8;
-            uint32_t lf = q[0], lb = q[kChain];
-#pragma unroll
-            for (int i = 0; i < kChain; i++) {
-                const uint32_t hf = q[i + 1], hb = q[kChain + i + 1];
-                cf = crc_word(t, cf, __funnelshift_r(lf, hf, sh));
-                cb = crc_word(t, cb, __funnelshift_r(lb, hb, sh));
-                lf = hf; lb = hb;
+            uint32_t lo_w = q[0];
+#pragma unroll 5
+            for (int i = 0; i < steps; i++) {
+                const uint32_t hi_w = q[i + 1];
+                c = crc_word(t, c, __funnelshift_r(lo_w, hi_w, sh));
+                lo_w = hi_w;
             }
         }
     }
-    const uint64_t p = (clmul32(cf, xpm_front) ^ clmul32(cb, xpm_back)) << 1;
-    uint32_t part = crc_word(t, 0u, (uint32_t)p) ^ (uint32_t)(p >> 32);
+    uint32_t part = crc_mulmod(t, c, xpm);
 #pragma unroll
     for (int o = 8; o > 0; o >>= 1) part ^= __shfl_xor_sync(hmask, part, o, 16);     // the other half may be elsewhere
     return ~(part ^ g_crc_init[nwords]);
@@ -369,9 +364,8 @@ __global__ void __launch_bounds__(32 * kUnpackWarps, 1) sctp_unpack_kernel(const
         }
     }
     CrcLut tabs; tabs.lb = tbase + 4u * (uint32_t)lane;
-    uint32_t xpm_front[kGhashClasses], xpm_back[kGhashClasses];        // x^(8 x bytes behind the chain's last word)
-    ghash_classes(g_crc_xpow[((15 - hl) * kCrcSegHalf + kCrcSegHalf / 2) * 4], xpm_front);
-    ghash_classes(g_crc_xpow[(15 - hl) * kCrcSegHalf * 4], xpm_back);
+    uint32_t xpm[kGhashClasses];
+    ghash_classes(g_crc_xpow[(15 - hl) * kCrcSegHalf * 4], xpm);
     const uint32_t n_low = (tbase - sbase) / kSctpBufBytes;
     auto buffer = [&](uint32_t q) -> uint8_t* {
         return q < n_low ? sctp_dyn_smem + q * kSctpBufBytes : sctp_dyn_smem + (tbase - sbase) + kCrcLutBytes + (q - n_low) * kSctpBufBytes;
@@ -384,19 +378,13 @@ __global__ void __launch_bounds__(32 * kUnpackWarps, 1) sctp_unpack_kernel(const
 
     const u64 pairs = (a.n + 1) / 2;
     const u64 warp = (u64)blockIdx.x * kUnpackWarps + wib, nwarps = (u64)gridDim.x * kUnpackWarps;
-    // a packet we handle: headroom + 12 .. 1228 bytes, a multiple of 4 (else it is reported malformed and not staged).
-    // fetch: where packet i lies and its length behind the headroom (0 = none of ours); the offsets are read TWO rounds
-    // ahead of their packet's check, so the copy that needs them a round later does not wait for them
-    auto fetch = [&](u64 i, u64& io, uint32_t& len) {
-        io = 0; len = 0;
-        if (i < a.n) {
-            io = __ldg(a.in_off + i);
-            const u64 ilen = __ldg(a.in_off + i + 1) - io;
-            if (!(ilen < (u64)a.headroom + 12 || ilen - a.headroom > kSctpMaxPacket || ((ilen - a.headroom) & 3))) len = (uint32_t)(ilen - a.headroom);
-        }
-    };
-    auto stage_half = [&](uint8_t* buf, u64 io, uint32_t len) {           // start the copy of this half's packet
+    // a packet we handle: headroom + 12 .. 1228 bytes, a multiple of 4 (else it is reported malformed and not staged)
+    auto sized = [&](u64 ilen) { return !(ilen < (u64)a.headroom + 12 || ilen - a.headroom > kSctpMaxPacket || ((ilen - a.headroom) & 3)); };
+    auto stage_half = [&](uint8_t* buf, u64 i, u64& io, u64& ilen) {      // start the copy of packet i (this half's)
+        io = 0; ilen = 0;
+        if (i < a.n) { io = __ldg(a.in_off + i); ilen = __ldg(a.in_off + i + 1) - io; }
         const uint8_t* src = a.in + io + a.headroom;
+        const uint32_t len = (i < a.n && sized(ilen)) ? (uint32_t)(ilen - a.headroom) : 0u;
         const uint32_t sa = (uint32_t)((uintptr_t)src & 15);
         const uint32_t nvec = len ? (sa + len + 15) >> 4 : 0;
 #pragma unroll
@@ -407,27 +395,22 @@ __global__ void __launch_bounds__(32 * kUnpackWarps, 1) sctp_unpack_kernel(const
         cp_async_commit();
     };
     int cur = 0;
-    u64 io, io_n;
-    uint32_t len, len_n;
-    fetch(2 * warp + half, io, len);
-    fetch(2 * (warp + nwarps) + half, io_n, len_n);
-    stage_half(buf_a, io, len);
+    u64 io, ilen;
+    stage_half(buf_a, 2 * warp + half, io, ilen);
     for (u64 pp = warp; pp < pairs; pp += nwarps) {
         const u64 i = 2 * pp + half;
         uint8_t* buf = cur ? buf_b : buf_a;
-        u64 io_nn;
-        uint32_t len_nn;
-        fetch(2 * (pp + 2 * nwarps) + half, io_nn, len_nn);
-        stage_half(cur ? buf_a : buf_b, io_n, len_n);                        // the next pair flies while this one is checked
+        u64 io_n, ilen_n;
+        stage_half(cur ? buf_a : buf_b, 2 * (pp + nwarps) + half, io_n, ilen_n);   // the next pair flies while this one is checked
         cp_async_wait_all_but_one();
         __syncwarp();
         uint32_t st = P2PT_ST_OK;
         uint32_t flags = 0, tsn = 0, sid = 0, ssn = 0, pp_id = 0, plen_pay = 0;
         if (i < a.n) {
-            if (!len) {
+            if (!sized(ilen)) {
                 st = P2PT_ST_SCTP_MALFORMED;                                 // not a single-DATA-chunk packet we handle
             } else {
-                const uint32_t n = len;
+                const uint32_t n = (uint32_t)(ilen - a.headroom);
                 const uint32_t sa = (uint32_t)((uintptr_t)(a.in + io + a.headroom) & 15);
                 const uint32_t pkt0 = kSctpFront + sa;
                 if ((uint32_t)hl < sa) buf[kSctpFront + hl] = 0;             // bytes of the first vector in front of the packet
@@ -436,8 +419,8 @@ __global__ void __launch_bounds__(32 * kUnpackWarps, 1) sctp_unpack_kernel(const
                 __syncwarp(hmask);
                 if (hl < 4) buf[pkt0 + 8 + hl] = 0;                          // checksum field counts as zero
                 __syncwarp(hmask);
-                const uint32_t crc = (pkt0 & 3) ? half_crc32c<false>(tabs, buf, pkt0, n >> 2, hl, hmask, xpm_front, xpm_back)
-                                                : half_crc32c<true>(tabs, buf, pkt0, n >> 2, hl, hmask, xpm_front, xpm_back);
+                const uint32_t crc = (pkt0 & 3) ? half_crc32c<false>(tabs, buf, pkt0, n >> 2, hl, hmask, xpm)
+                                                : half_crc32c<true>(tabs, buf, pkt0, n >> 2, hl, hmask, xpm);
                 if (crc != theirs) st = P2PT_ST_SCTP_BAD_CHECKSUM;           // checked first, like Packet::unmarshal
                 else if (n < 28 || buf[pkt0 + 12] != 0) st = P2PT_ST_SCTP_MALFORMED;
                 else {
@@ -470,7 +453,7 @@ __global__ void __launch_bounds__(32 * kUnpackWarps, 1) sctp_unpack_kernel(const
             }
         }
         __syncwarp();                                                        // the buffers are staged into again next round
-        cur ^= 1; io = io_n; len = len_n; io_n = io_nn; len_n = len_nn;
+        cur ^= 1; io = io_n; ilen = ilen_n;
     }
 }
 
