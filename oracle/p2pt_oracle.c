@@ -1,7 +1,7 @@
 /*
  * p2pt_oracle.c -- CPU oracle (plain C, scalar, no intrinsics).  TEST INFRASTRUCTURE ONLY:
  * see the header comment in p2pt_oracle.h for who may use it and for the parity-pinning status
- * ("parity unpinned" for the DTLS record layout; codec and AES-GCM arithmetic are pinned).
+ * (codec, AES-GCM arithmetic, DTLS record layout and replay window are pinned; the SCTP packet layout is "parity unpinned").
  *
  * Every function cites the reference file:line (or the standard, where the arithmetic lives in an
  * un-vendored crate) it restates.  Nothing here is copied from the reference: the codec is 20

@@ -11,11 +11,17 @@
  *     (/root/reference/tunnel/src/protocol.rs:392-460, :271-388) -> tests/golden/frames_kat.json.
  *   - AES-128-GCM arithmetic: pinned by FIPS-197 App. B / C.1 and the GCM spec test cases 1-4,
  *     and cross-checked against Python `cryptography` (OpenSSL) on every golden record.
- *   - DTLS record LAYOUT (nonce / AAD / header length fix-up): "parity unpinned" against the
- *     reference, because it lives in the un-vendored crate webrtc-dtls 0.10.0
- *     (/root/reference/tunnel/Cargo.lock:2822-2824) whose source is not under /root/reference and
- *     no reference test touches it.  The layout is restated from RFC 6347 4.1 / RFC 5288 3 as that
- *     crate implements them and is isolated in orc_dtls_aad()/orc_dtls_seal()/orc_dtls_open().
+ *   - DTLS record LAYOUT (nonce / AAD / header length fix-up): it lives in the un-vendored crate
+ *     webrtc-dtls 0.10.0 (/root/reference/tunnel/Cargo.lock:2822-2824), whose source is not under
+ *     /root/reference and which no reference test touches.  Restated from RFC 6347 4.1 / RFC 5288 3 in
+ *     orc_dtls_aad()/orc_dtls_seal()/orc_dtls_open() and PINNED to wire records captured from OpenSSL's
+ *     DTLS 1.2 stack (tests/golden/gen_dtls_openssl.py -> dtls_openssl_kat.json,
+ *     tests/test_dtls_openssl_pin.py): what that crate has to interoperate with.
+ *   - anti-replay window: PINNED the same way, to what a live `openssl s_server -dtls1_2` accepted of a
+ *     scripted sequence of replayed / reordered / stale / forged records
+ *     (tests/golden/gen_replay_openssl.py -> replay_openssl_kat.json).
+ *   - SCTP packet layout: "parity unpinned" (un-vendored webrtc-sctp 0.10.0, no SCTP stack in this image);
+ *     CRC32c itself is pinned by the RFC 3720 B.4 vectors.
  */
 #ifndef P2PT_ORACLE_H
 #define P2PT_ORACLE_H
@@ -96,7 +102,7 @@ void orc_dtls_open_batch(uint64_t n, const uint32_t* session,
 /* ---- SCTP DATA-chunk packetise / unpack + CRC32c.  Restates webrtc-sctp 0.10.0
  *      (UN-VENDORED, /root/reference/tunnel/Cargo.lock:2910-2911; CRC via crc 3.4.0, :420-421): RFC 4960
  *      3.1 common header, 3.3.1 DATA chunk, appendix B checksum.  CRC32c itself is pinned by the RFC 3720
- *      B.4 vectors; the packet layout is "parity unpinned" like the DTLS layout. ---- */
+ *      B.4 vectors; the packet layout is "parity unpinned". ---- */
 #define ORC_SCTP_MAX_PAYLOAD 1200u   /* INITIAL_MTU 1228 - 12 common header - 16 DATA chunk header */
 typedef struct {
     uint32_t tsn; uint16_t stream_id; uint16_t ssn; uint32_t ppid;

@@ -135,3 +135,44 @@ def test_application_records_carry_the_tunnel_frames():
     assert got[0] == (20, 42, 0) and got[1] == (21, 99, 0) and got[2] == (21, 42, 0)
     assert got[5] == (22, 42, 0) and got[6] == (3, 0, 0)
     assert frames[1][5:] == b'data: {"token": "hello"}\n\n'
+
+
+# ---- the anti-replay window, against what a live OpenSSL DTLS 1.2 server accepted (tests/golden/replay_openssl_kat.json,
+#      made by tests/golden/gen_replay_openssl.py: held records delivered with duplicates, reordering, jumps of more than
+#      64, records 63 and 64 behind the newest, forged copies) ----
+
+def replay_fixture():
+    with open(os.path.join(G, "replay_openssl_kat.json")) as f:
+        fx = json.load(f)
+    a = fx["arrivals"]
+    return (fx, np.array([x["seq"] for x in a], np.uint64), np.array([x["authentic"] for x in a], np.uint8),
+            np.array([x["accepted"] for x in a], np.uint8))
+
+
+def fresh_window(sessions=1):
+    return {"latest": np.zeros(sessions, np.uint64), "mask": np.zeros(sessions, np.uint64), "started": np.zeros(sessions, np.uint8)}
+
+
+def test_replay_fixture_shape():
+    fx, seq, auth, acc = replay_fixture()
+    assert fx["window"] == 64 and len(seq) > 100
+    assert 0 < acc.sum() < len(acc) and (auth == 0).sum() >= 2
+    assert not acc[auth == 0].any()                                  # nothing forged was delivered
+    newest = np.maximum.accumulate(np.where(acc == 1, seq, 0))
+    behind = newest.astype(np.int64) - seq.astype(np.int64)
+    assert (behind[acc == 1] <= 63).all()                            # nothing 64 or more behind the newest got through ...
+    assert 63 in set(behind[acc == 1].tolist())                      # ... the edge itself did ...
+    assert 64 in set(behind[(acc == 0) & (auth == 1)].tolist())      # ... and one step beyond it did not
+
+
+def test_oracle_window_decides_like_openssl():
+    fx, seq, auth, acc = replay_fixture()
+    st = fresh_window()
+    assert list(ob.replay_filter(np.zeros(1, np.uint32), np.zeros(1, np.uint64), st)) == [1]     # seq 0: the client's Finished
+    got = ob.replay_filter(np.zeros(len(seq), np.uint32), seq, st, auth)
+    assert np.array_equal(got, acc), np.nonzero(got != acc)[0]
+    # the same arrivals one record per call: the state carried between calls is all there is
+    st = fresh_window()
+    ob.replay_filter(np.zeros(1, np.uint32), np.zeros(1, np.uint64), st)
+    one = [int(ob.replay_filter(np.zeros(1, np.uint32), seq[i:i + 1], st, auth[i:i + 1])[0]) for i in range(len(seq))]
+    assert one == acc.tolist()

@@ -122,3 +122,27 @@ def test_datagram_split_then_open_on_captured_flights(ctx):
     want = [h(r["plain"]) for r in fx["records"]]
     got = [out[int(poff[i]) + 13:int(poff[i]) + int(olen[i])].tobytes() for i in prot]
     assert got == want
+
+
+def test_replay_window_decides_like_openssl(ctx):
+    """p2pt_dtls_replay_filter_batch on the arrivals a live OpenSSL DTLS 1.2 server judged (replay_openssl_kat.json): in one
+    batch, cut into batches of every size from 1 to 9, and with the same arrivals interleaved on 37 sessions."""
+    from test_dtls_openssl_pin import fresh_window, replay_fixture
+    fx, seq, auth, acc = replay_fixture()
+    n = len(seq)
+    zero = np.zeros(1, np.uint64)
+    st = fresh_window()
+    assert list(ctx.dtls_replay_filter(np.zeros(1, np.uint32), zero, st)) == [1]
+    assert np.array_equal(ctx.dtls_replay_filter(np.zeros(n, np.uint32), seq, st, auth), acc)
+    for step in range(1, 10):
+        st = fresh_window()
+        ctx.dtls_replay_filter(np.zeros(1, np.uint32), zero, st)
+        got = np.concatenate([ctx.dtls_replay_filter(np.zeros(len(seq[i:i + step]), np.uint32), seq[i:i + step], st, auth[i:i + step])
+                              for i in range(0, n, step)])
+        assert np.array_equal(got, acc), step
+    S = 37
+    st = fresh_window(S)
+    ctx.dtls_replay_filter(np.arange(S, dtype=np.uint32), np.zeros(S, np.uint64), st)
+    sess = np.tile(np.arange(S, dtype=np.uint32), n)                 # arrival i of every session, then arrival i + 1 ...
+    got = ctx.dtls_replay_filter(sess, np.repeat(seq, S), st, np.repeat(auth, S))
+    assert np.array_equal(got.reshape(n, S), np.repeat(acc, S).reshape(n, S))
