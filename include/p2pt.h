@@ -271,6 +271,15 @@ int32_t p2pt_dtls_datagram_split_batch(p2pt_ctx* ctx, uint64_t n_dgrams, const u
 int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, const uint64_t* seq48,
                                       const uint8_t* authentic, uint32_t n_sessions,
                                       uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept);
+/* Sequence numbers of outgoing records (webrtc-dtls 0.10.0 conn.rs, the write path, un-vendored: every record takes
+ * its epoch's counter with fetch_add(1); more than 2^48 - 1 is ErrSequenceNumberOverflow).  next_seq[s] is the number
+ * the next record of session s gets; the caller keeps the array (n_sessions entries, host array here) between batches
+ * and restarts a session at 0 when its epoch changes.  seq48[i] = next_seq[session[i]] + the number of records of the
+ * same session in front of record i in this batch, ok[i] = 1; afterwards every next_seq[s] has advanced by the
+ * session's records.  ok[i] = 0 and seq48[i] = 0 for a record whose number would pass 2^48 - 1 or whose session index is
+ * not below n_sessions: it must not be sealed.  The result feeds the seq48 argument of the seal calls. */
+int32_t p2pt_dtls_seq_assign_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, uint32_t n_sessions,
+                                   uint64_t* next_seq, uint64_t* seq48, uint8_t* ok);
 
 /* ---- SSE event scan over per-stream bodies.  body / body_off[k + 1] are the
  *      gathered / gathered_off outputs of the demux.  An event ends after every "\n\n" inside one stream:
@@ -354,6 +363,10 @@ int32_t p2pt_dtls_datagram_split_batch_device(p2pt_ctx* ctx, uint64_t n_dgrams, 
                                               uint64_t max_records, uint64_t* rec_off, uint32_t* rec_dgram,
                                               uint8_t* dgram_status, uint32_t* n_records_out,
                                               void* scratch, uint64_t scratch_bytes, void* stream);
+uint64_t p2pt_dtls_seq_assign_scratch_bytes(uint64_t n);
+int32_t p2pt_dtls_seq_assign_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, uint32_t n_sessions,
+                                          uint64_t* next_seq, uint64_t* seq48, uint8_t* ok,
+                                          void* scratch, uint64_t scratch_bytes, void* stream);
 uint64_t p2pt_dtls_replay_filter_scratch_bytes(uint64_t n);
 int32_t p2pt_dtls_replay_filter_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, const uint64_t* seq48,
                                              const uint8_t* authentic, uint32_t n_sessions,

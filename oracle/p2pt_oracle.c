@@ -561,6 +561,21 @@ void orc_replay_filter(uint64_t n, const uint32_t* session, const uint64_t* seq4
     }
 }
 
+/* Sequence numbers of outgoing records: webrtc-dtls 0.10.0 conn.rs (un-vendored) takes the epoch's counter with
+ * fetch_add(1) for every record it marshals and fails with ErrSequenceNumberOverflow beyond 2^48 - 1.  Records are
+ * visited in batch order; ok[i] = 0 (seq 0) for a record that cannot be numbered. */
+void orc_dtls_seq_assign(uint64_t n, const uint32_t* session, uint32_t n_sessions, uint64_t* next_seq,
+                         uint64_t* seq48, uint8_t* ok) {
+    const uint64_t MAXSEQ = (1ull << 48) - 1;
+    for (uint64_t i = 0; i < n; i++) {
+        uint32_t s = session[i];
+        seq48[i] = 0; ok[i] = 0;
+        if (s >= n_sessions || next_seq[s] > MAXSEQ) continue;
+        seq48[i] = next_seq[s]++;
+        ok[i] = 1;
+    }
+}
+
 /* ------------------------------------------------------------------------------------------ */
 /* SSE scan over reassembled response bodies.  The reference forwards SSE */
 /* bytes untouched (feature flag "sse", /root/reference/tunnel/src/protocol.rs:36,68); the event  */

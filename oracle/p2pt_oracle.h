@@ -126,6 +126,8 @@ int orc_sctp_unpack(const uint8_t* pkt, uint64_t len, uint32_t headroom, orc_sct
 int64_t orc_dtls_datagram_split(const uint8_t* d, uint64_t len, uint64_t* rec_off, uint64_t cap);
 void orc_replay_filter(uint64_t n, const uint32_t* session, const uint64_t* seq48, const uint8_t* authentic,
                        uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept_out);
+void orc_dtls_seq_assign(uint64_t n, const uint32_t* session, uint32_t n_sessions, uint64_t* next_seq,
+                         uint64_t* seq48, uint8_t* ok);
 
 /* ---- SSE event scan over per-stream bodies (8(f) row 4) ---- */
 uint64_t orc_sse_scan(uint64_t k, const uint8_t* body, const uint64_t* body_off,

@@ -61,6 +61,9 @@ SIGNATURES = {
     "p2pt_dtls_datagram_split_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_dtls_replay_filter_scratch_bytes": (_u64, [_u64]),
     "p2pt_dtls_replay_filter_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
+    "p2pt_dtls_seq_assign_batch": (_i32, [_vp, _u64, _vp, _u32, _vp, _vp, _vp]),
+    "p2pt_dtls_seq_assign_scratch_bytes": (_u64, [_u64]),
+    "p2pt_dtls_seq_assign_batch_device": (_i32, [_vp, _u64, _vp, _u32, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_sse_scan_batch": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
     "p2pt_sse_scan_scratch_bytes": (_u64, [_u64]),
     "p2pt_sse_scan_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
@@ -429,6 +432,16 @@ class Context:
                                                            state["latest"].ctypes.data, state["mask"].ctypes.data,
                                                            state["started"].ctypes.data, accept.ctypes.data))
         return accept[:n]
+
+    def dtls_seq_assign(self, session, next_seq):
+        """next_seq = u64[S], the number each session's next record gets, advanced in place; returns (seq48[n], ok[n])"""
+        session = _as(session, np.uint32)
+        n = len(session)
+        seq48 = np.zeros(max(n, 1), np.uint64); ok = np.zeros(max(n, 1), np.uint8)
+        assert next_seq.dtype == np.uint64 and next_seq.flags.c_contiguous
+        self._check(self.lib.p2pt_dtls_seq_assign_batch(self.h, n, session.ctypes.data, len(next_seq), next_seq.ctypes.data,
+                                                        seq48.ctypes.data, ok.ctypes.data))
+        return seq48[:n], ok[:n]
 
     def sse_scan(self, body, body_off, max_events=None):
         """per-stream bodies -> (ev_csr[k + 1], ev_end[n_events], done[k])"""

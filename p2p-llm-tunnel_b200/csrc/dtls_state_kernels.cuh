@@ -3,12 +3,16 @@
 //   * anti-replay sliding window   replaydetector SlidingWindowDetector, window 64, as driven by
 //                                  webrtc-dtls conn.rs handle_incoming_packet: check() before the
 //                                  record is opened, accept() only once it authenticated
+//   * sequence numbers of outgoing records: every record takes its epoch's counter with fetch_add(1)
+//                                  (webrtc-dtls conn.rs, the write path), 48 bits, overflow is an error
 // Small integer kernels: one thread per datagram / per session walks its few items exactly like the
 // reference does; the parallelism is across datagrams and across sessions.
 #pragma once
 #include "frame_kernels.cuh"
 
 namespace p2pt {
+
+constexpr u64 kSeq48Max = (1ull << 48) - 1;
 
 // ---- datagram split -----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t dgram_walk(const uint8_t* d, u64 len, u64 base, u64* rec_off, uint32_t* rec_dgram,
@@ -116,7 +120,7 @@ __global__ void __launch_bounds__(256) replay_walk_kernel(const uint32_t* __rest
         for (u64 j = csr[g]; j < csr[g + 1]; j++) {
             const uint32_t i = perm[j];
             const u64 q = seq48[i];
-            bool ok = known && q <= ((1ull << 48) - 1);
+            bool ok = known && q <= kSeq48Max;
             if (ok && st && q <= lat) {
                 if (lat >= 64 + q) ok = false;                          // older than the window
                 else if ((m >> (lat - q)) & 1) ok = false;              // already seen
@@ -129,6 +133,48 @@ __global__ void __launch_bounds__(256) replay_walk_kernel(const uint32_t* __rest
             } else accept[i] = 0;
         }
         if (known) { latest[s] = lat; mask[s] = m; started[s] = st ? 1 : 0; }
+    }
+}
+
+// ---- sequence numbers of outgoing records ---------------------------------------------------------------
+// The records were grouped by session with the stable demux (arrival order kept inside a session): the record at
+// sorted position j of group g is the (j - csr[g])-th of its session in this batch.  One thread per position; its group
+// by binary search over csr (k + 1 entries, L2-resident).
+__global__ void __launch_bounds__(256) seq_assign_kernel(u64 n, const uint32_t* __restrict__ k_ptr, const uint32_t* __restrict__ uniq_session,
+                                                        const u64* __restrict__ csr, const uint32_t* __restrict__ perm,
+                                                        uint32_t n_sessions, const u64* __restrict__ next_seq,
+                                                        u64* __restrict__ seq48, uint8_t* __restrict__ ok) {
+    const uint32_t k = *k_ptr;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) {
+        uint32_t lo = 0, hi = k;                                         // csr[lo] <= j < csr[hi]
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (csr[mid] <= j) lo = mid; else hi = mid;
+        }
+        const uint32_t s = uniq_session[lo], i = perm[j];
+        u64 q = 0;
+        bool good = s < n_sessions;
+        if (good) {
+            const u64 base = next_seq[s], r = j - csr[lo];
+            good = base <= kSeq48Max && r <= kSeq48Max - base;           // ErrSequenceNumberOverflow beyond 2^48 - 1
+            if (good) q = base + r;
+        }
+        seq48[i] = q;
+        ok[i] = good ? 1 : 0;
+    }
+}
+
+// after the numbers are out: every session's counter advances by its records, saturating one past the last number
+__global__ void __launch_bounds__(256) seq_advance_kernel(const uint32_t* __restrict__ k_ptr, const uint32_t* __restrict__ uniq_session,
+                                                         const u64* __restrict__ csr, uint32_t n_sessions, u64* __restrict__ next_seq) {
+    const uint32_t k = *k_ptr;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 g = (u64)blockIdx.x * blockDim.x + threadIdx.x; g < k; g += stride) {
+        const uint32_t s = uniq_session[g];
+        if (s >= n_sessions) continue;
+        const u64 base = next_seq[s], cnt = csr[g + 1] - csr[g];
+        next_seq[s] = (base > kSeq48Max || cnt > kSeq48Max + 1 - base) ? kSeq48Max + 1 : base + cnt;
     }
 }
 

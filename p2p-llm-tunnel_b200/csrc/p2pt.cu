@@ -1802,6 +1802,32 @@ int32_t p2pt_dtls_replay_filter_batch_device(p2pt_ctx* ctx, uint64_t n, const ui
     return P2PT_OK;
 }
 
+uint64_t p2pt_dtls_seq_assign_scratch_bytes(uint64_t n) { return replay_carve(nullptr, n).total; }
+
+int32_t p2pt_dtls_seq_assign_batch_device(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, uint32_t n_sessions,
+                                          uint64_t* next_seq, uint64_t* seq48, uint8_t* ok,
+                                          void* scratch, uint64_t scratch_bytes, void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !next_seq || !seq48 || !ok || !scratch) return set_err(ctx, P2PT_ERR_ARG, "seq_assign: null argument");
+    if (n > 0xffffffffull) return set_err(ctx, P2PT_ERR_ARG, "seq_assign: n must fit in 32 bits");
+    if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "seq_assign: scratch must be 256-byte aligned");
+    ReplayScratch r = replay_carve(scratch, n);
+    if (scratch_bytes < r.total) return set_err(ctx, P2PT_ERR_CAPACITY, "seq_assign: scratch too small");
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    replay_keys_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, session, r.desc);
+    // the records of a session in arrival order (the stable demux, key = session)
+    if (int32_t rc = p2pt_frame_demux_batch_device(ctx, n, r.desc, nullptr, nullptr, (uint32_t)n, r.uniq, nullptr, r.csr, r.perm,
+                                                   r.k, nullptr, 0, nullptr, r.demux, r.demux_bytes, st)) return rc;
+    seq_assign_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(n, r.k, r.uniq, (const u64*)r.csr, r.perm, n_sessions,
+                                                                (const u64*)next_seq, (u64*)seq48, ok);
+    seq_advance_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, st>>>(r.k, r.uniq, (const u64*)r.csr, n_sessions, (u64*)next_seq);
+    count_launch(ctx, 3);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
 int32_t p2pt_dtls_datagram_split_batch(p2pt_ctx* ctx, uint64_t n, const uint8_t* buf, const uint64_t* dgram_off,
                                        uint64_t max_records, uint64_t* rec_off, uint32_t* rec_dgram,
                                        uint8_t* dgram_status, uint32_t* n_records_out) {
@@ -1878,6 +1904,35 @@ int32_t p2pt_dtls_replay_filter_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t*
     CUDA_TRY(ctx, cudaMemcpyAsync(latest, d_lat, 8 * S, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(mask, d_mask, 8 * S, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(started, d_started, S, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, wait_stream(ctx, L, st));
+    lg.dismiss();
+    return P2PT_OK;
+}
+
+int32_t p2pt_dtls_seq_assign_batch(p2pt_ctx* ctx, uint64_t n, const uint32_t* session, uint32_t n_sessions,
+                                   uint64_t* next_seq, uint64_t* seq48, uint8_t* ok) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (n == 0) return P2PT_OK;
+    if (!session || !next_seq || !seq48 || !ok || !n_sessions) return set_err(ctx, P2PT_ERR_ARG, "seq_assign: null argument");
+    DeviceGuard dg(ctx->device);
+    LaneGuard lg(ctx);
+    NvtxRange nvtx_("p2pt_dtls_seq_assign_batch");
+    Lane* L = lg.lane;
+    cudaStream_t st = L->streams[0];
+    const uint64_t sb = p2pt_dtls_seq_assign_scratch_bytes(n);
+    const size_t S = n_sessions;
+    if (int32_t r = arena_reserve(ctx, L, pad256(4 * n) + pad256(8 * n) + pad256(n) + pad256(8 * S) + pad256(sb) + 8192)) return r;
+    uint32_t* d_sess = arena_take<uint32_t>(L, n);
+    uint64_t* d_seq = arena_take<uint64_t>(L, n);
+    uint8_t* d_ok = arena_take<uint8_t>(L, n);
+    uint64_t* d_next = arena_take<uint64_t>(L, S);
+    uint8_t* d_scr = arena_take<uint8_t>(L, sb);
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_sess, session, 4 * n, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_next, next_seq, 8 * S, cudaMemcpyHostToDevice, st));
+    if (int32_t r = p2pt_dtls_seq_assign_batch_device(ctx, n, d_sess, n_sessions, d_next, d_seq, d_ok, d_scr, sb, st)) return r;
+    CUDA_TRY(ctx, cudaMemcpyAsync(seq48, d_seq, 8 * n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ok, d_ok, n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(next_seq, d_next, 8 * S, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, wait_stream(ctx, L, st));
     lg.dismiss();
     return P2PT_OK;

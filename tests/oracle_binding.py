@@ -201,6 +201,15 @@ def replay_filter(session, seq48, state, authentic=None):
     return accept[:n]
 
 
+def seq_assign(session, next_seq):
+    """next_seq (u64[S]) advanced in place; returns (seq48[n], ok[n])"""
+    session = np.ascontiguousarray(session, np.uint32)
+    n = len(session)
+    seq48 = np.zeros(max(n, 1), np.uint64); ok = np.zeros(max(n, 1), np.uint8)
+    lib().orc_dtls_seq_assign(C.c_uint64(n), _p(session), C.c_uint32(len(next_seq)), _p(next_seq), _p(seq48), _p(ok))
+    return seq48[:n], ok[:n]
+
+
 def sse_scan(body, body_off):
     body = _u8(body); body_off = np.ascontiguousarray(body_off, np.uint64)
     k = len(body_off) - 1

@@ -176,3 +176,41 @@ def test_oracle_window_decides_like_openssl():
     ob.replay_filter(np.zeros(1, np.uint32), np.zeros(1, np.uint64), st)
     one = [int(ob.replay_filter(np.zeros(1, np.uint32), seq[i:i + 1], st, auth[i:i + 1])[0]) for i in range(len(seq))]
     assert one == acc.tolist()
+
+
+def test_sequence_numbers_of_captured_records_are_what_the_oracle_assigns():
+    """Every protected record OpenSSL wrote carries the next number of its (direction, epoch), from 0, in write order:
+    the rule orc_dtls_seq_assign restates (webrtc-dtls conn.rs fetch_add per record).  Both directions as two sessions."""
+    fx = fixture()
+    recs = [r for r in fx["records"] if r["epoch"] == 1]
+    sess = np.array([0 if r["dir"] == "c2s" else 1 for r in recs], np.uint32)
+    nxt = np.zeros(2, np.uint64)
+    seq, ok = ob.seq_assign(sess, nxt)
+    assert ok.all() and seq.tolist() == [r["seq"] for r in recs]
+    assert nxt.tolist() == [int((sess == 0).sum()), int((sess == 1).sum())]
+    # and the replay capture: the client's application records are numbered 1..N behind its Finished (0)
+    rfx, rseq, _, _ = replay_fixture()
+    nxt = np.zeros(1, np.uint64)
+    seq, ok = ob.seq_assign(np.zeros(int(rseq.max()) + 1, np.uint32), nxt)
+    assert set(rseq.tolist()) <= set(seq.tolist()) and seq[0] == 0
+
+
+def test_seq_assign_oracle_semantics():
+    rng = np.random.default_rng(11)
+    S, n = 9, 5000
+    sess = rng.integers(0, S + 2, n).astype(np.uint32)               # S, S + 1: not a session of the table
+    nxt = rng.integers(0, 1000, S).astype(np.uint64)
+    nxt[3] = (1 << 48) - 3                                           # three numbers left
+    start = nxt.copy()
+    seq, ok = ob.seq_assign(sess, nxt)
+    for s in range(S + 2):
+        idx = np.nonzero(sess == s)[0]
+        if s >= S:
+            assert not ok[idx].any() and not seq[idx].any()
+            continue
+        want = int(start[s]) + np.arange(len(idx))
+        good = want <= (1 << 48) - 1
+        assert np.array_equal(ok[idx], good.astype(np.uint8))
+        assert np.array_equal(seq[idx][good], want[good].astype(np.uint64)) and not seq[idx][~good].any()
+        assert int(nxt[s]) == min(int(start[s]) + len(idx), 1 << 48)
+    assert (~ok[sess == 3].astype(bool)).sum() == (sess == 3).sum() - 3
