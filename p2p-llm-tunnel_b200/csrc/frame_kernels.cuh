@@ -162,6 +162,7 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
         uint32_t sid; uint8_t type;
         uint4 v[3];                // this thread's aligned vectors of the payload span (<= 513 over 256 threads)
         int T; bool dense;
+        bool tiny;                 // frame t has fewer than 3 payload bytes (see the whole-word shuffle below)
     };
     auto load_tile = [&](u64 tile, TileRegs& r) {
         const u64 i0 = tile * kSmallTile;
@@ -169,8 +170,9 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
         r.pb = __ldg(pay_off + i0); r.pe = __ldg(pay_off + i0 + r.T);
         r.ob = __ldg(out_off + i0); r.oe = __ldg(out_off + i0 + r.T);
         r.po = r.oo = 0; r.sid = 0; r.type = 0;
+        r.tiny = false;
         if (t <= r.T) { r.po = __ldg(pay_off + i0 + t); r.oo = __ldg(out_off + i0 + t); }
-        if (t < r.T) { r.sid = __ldg(sids + i0 + t); r.type = __ldg(types + i0 + t); }
+        if (t < r.T) { r.sid = __ldg(sids + i0 + t); r.type = __ldg(types + i0 + t); r.tiny = __ldg(pay_off + i0 + t + 1) - r.po < 3; }
         r.dense = (r.oe - r.ob == (r.pe - r.pb) + 5ull * (u64)r.T) && (r.pe - r.pb <= kSmallTileIn);
         if (r.dense) {
             // whole aligned vectors (an aligned vector that holds one byte of the span lies in the same page as that
@@ -186,6 +188,8 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
         }
     };
     TileRegs cur;
+    cur.tiny = false;
+    bool sout_dirty = false;                           // block-uniform: sout holds words of a whole-word tile
     if (blockIdx.x < ntile) load_tile(blockIdx.x, cur);
     for (uint32_t w = t; w < sizeof(sout_w) / 4; w += 256) sout_w[w] = 0;     // ordered before the first shuffle by the tile's barrier
     for (u64 tile = blockIdx.x; tile < ntile; tile += gridDim.x) {
@@ -209,12 +213,59 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
                 }
             }
         }
-        __syncthreads();                                               // tile in shared memory; previous flush behind everyone
+        const bool whole = !__syncthreads_or(cur.tiny);                // tile in shared memory; previous flush behind everyone
         if (tile + gridDim.x < ntile) load_tile(tile + gridDim.x, cur);   // next tile's loads fly during the rest
         if (dense) {
             uint8_t* gdst = out + ob;
             const uint32_t oa = (uint32_t)((uintptr_t)gdst & 15);      // sout keeps the span's 16-byte phase
-            {
+            if (whole) {
+                // Every payload of the tile has at least 3 bytes (an SSE chunk, any body frame): then every aligned output
+                // WORD has one owner and is written whole - no byte masks, no OR-ing, no zeroed buffer.  Frame f owns the
+                // words from the one its first byte lies in up to, not including, the one the next frame starts in.  The
+                // bytes in front of the frame in its first word are the last payload bytes of frame f - 1, and those lie
+                // right in front of this frame's payload in the input span (payloads are back to back): the output is
+                // the input with five bytes inserted per frame.  So the first two words are funnel shifts of
+                // (4 bytes before the payload | header | 4 bytes of payload), and every word after them lies wholly
+                // inside the payload.  Two lanes per frame: one head word and half of the payload words each.  (The
+                // bytes in front of the tile's first frame and behind its last are not stored by the flush.)
+                sout_dirty = true;
+                const int f = t >> 1, h = t & 1;
+                if (f < T) {
+                    const uint32_t po = (uint32_t)(s_po[f] - pb);
+                    const uint32_t S = oa + (uint32_t)(s_oo[f] - ob), E = oa + (uint32_t)(s_oo[f + 1] - ob);
+                    const uint32_t P0 = kSinFront + ia + po;                                   // payload start in sin
+                    const uint32_t wS = S >> 2, wE = f == T - 1 ? (E + 3) >> 2 : E >> 2;
+                    {
+                        const uint32_t base = P0 - 4, bw = (base >> 2) + h;
+                        const uint32_t v = __funnelshift_r(sin.word(bw), sin.word(bw + 1), (base & 3) * 8);   // h = 0: the 4 bytes before the payload, 1: its first 4
+                        const uint32_t sidbe = __byte_perm(s_sid[f], 0, 0x0123);
+                        const uint32_t hlo = (uint32_t)s_type[f] | (sidbe << 8);               // [type][stream_id BE bytes 0..2]
+                        const uint32_t lo = h ? hlo : v, hi = h ? ((sidbe >> 24) | (v << 8)) : hlo;
+                        sout_w[wS + h] = __funnelshift_rc(lo, hi, 32 - 8 * (S & 3));
+                    }
+                    const uint32_t w0 = wS + 2;
+                    if (wE > w0) {
+                        const int32_t delta = (int32_t)P0 - (int32_t)(S + 5);                  // source byte = output byte + delta
+                        const int32_t dq = delta >> 2;
+                        const unsigned sh = (unsigned)(delta & 3) * 8;
+                        const uint32_t per = (wE - w0 + 1) >> 1, a = w0 + h * per;
+                        const uint32_t b = a + per < wE ? a + per : wE;
+                        if (a < b) {
+                            uint32_t lo = sin.word((uint32_t)((int32_t)a + dq));
+                            for (uint32_t w = a; w < b; w++) {
+                                const uint32_t hi = sin.word((uint32_t)((int32_t)w + dq + 1));
+                                sout_w[w] = __funnelshift_r(lo, hi, sh);
+                                lo = hi;
+                            }
+                        }
+                    }
+                }
+            } else {
+                if (sout_dirty) {                                      // the whole-word shuffle leaves its words behind
+                    for (uint32_t w = t; w < sizeof(sout_w) / 4; w += 256) sout_w[w] = 0;
+                    __syncthreads();
+                    sout_dirty = false;
+                }
                 // Two lanes per frame, one aligned output WORD at a time.  Words that lie wholly inside the payload are
                 // two source words and a funnel shift (the byte shift is the same for the whole frame); the at most three
                 // words at the head of the frame (header bytes, start of the payload) and the partial word at its end are
@@ -270,7 +321,7 @@ __global__ void __launch_bounds__(256, P2PT_ENCODE_MIN_BLOCKS) frame_encode_kern
             for (uint32_t lo = 16u * t; lo < total; lo += 16u * 256u) {
                 uint4* q4 = reinterpret_cast<uint4*>(sout_w + (lo >> 2));
                 const uint4 x = *q4;
-                *q4 = make_uint4(0, 0, 0, 0);                          // zero again for the next tile's OR-ed words
+                if (!whole) *q4 = make_uint4(0, 0, 0, 0);              // zero again for the next tile's OR-ed words
                 if (lo >= oa && lo + 16 <= total) stg128(g0 + lo, x);
                 else store_bytes(g0 + lo, x, lo < oa ? (int)(oa - lo) : 0, total - lo < 16u ? (int)(total - lo) : 16);
             }

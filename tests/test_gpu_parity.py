@@ -70,6 +70,32 @@ def test_frame_encode_with_gaps_and_unaligned_slots(ctx):
         assert np.array_equal(got[a:b], exp[a:b]), i
 
 
+@pytest.mark.parametrize("lo,hi", [(3, 4), (3, 12), (64, 65), (3, 130), (60, 70)])
+@pytest.mark.parametrize("shift", [0, 1, 2, 3, 7, 13])
+def test_small_frames_whole_word_tiles(ctx, lo, hi, shift):
+    """The small-frame encoder's whole-word shuffle (every payload of a 128-frame tile >= 3 bytes): all byte phases of the
+    payload span and of the output span, the shortest frames it takes (3 bytes: two words), tiles with a shorter payload
+    in between (they take the OR-ing shuffle, whose buffer has to be cleared again), a ragged last tile."""
+    rng = np.random.default_rng(1000 * lo + 10 * hi + shift)
+    n = 128 * 23 + 57
+    lens = rng.integers(lo, hi, n).astype(np.uint64)
+    for tile in (3, 4, 9, 22):                                        # tiles that fall back
+        lens[128 * tile + int(rng.integers(0, 128))] = int(rng.integers(0, 3))
+    lens[-1] = 3
+    pay_off = np.zeros(n + 1, np.uint64); np.cumsum(lens, out=pay_off[1:])
+    pay_off += np.uint64(shift)                                       # payload span starts at any byte phase
+    payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
+    types = VALID[rng.integers(0, len(VALID), n)]
+    sids = rng.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
+    out_off = np.zeros(n + 1, np.uint64); np.cumsum(lens + np.uint64(5), out=out_off[1:])
+    out_off += np.uint64((5 * shift + 1) % 16)
+    got, _ = ctx.frame_encode(types, sids, payload, pay_off, out_off)
+    exp, _ = ob.frame_encode(types, sids, payload, pay_off, out_off)
+    a = int(out_off[0])
+    assert np.array_equal(got[a:], exp[a:])
+    assert not got[:a].any()                                          # nothing in front of the first slot
+
+
 def make_frames(rng, n, n_streams, corrupt=0.02, lo=0, hi=200):
     lens, pay_off = ragged(rng, n, lo, hi)
     payload = rng.integers(0, 256, int(pay_off[-1]), dtype=np.uint8)
