@@ -56,3 +56,24 @@ def test_product_does_not_reference_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "liboracle" not in text and "p2pt_oracle" not in text and "oracle_binding" not in text, f
+
+
+def test_header_is_plain_c_and_links_from_c(built, tmp_path):
+    """include/p2pt.h through a C99 compiler with -pedantic -Werror (what cgo / bindgen / a Rust `extern "C"` block see), and a
+    C program linked against the library calling the entry points that need no device."""
+    import subprocess
+    import p2p_llm_tunnel_b200 as p2pt
+    src = tmp_path / "c_abi.c"
+    src.write_text('#include "p2pt.h"\n#include <stdio.h>\n'
+                   'int main(void) {\n'
+                   '    p2pt_desc d; p2pt_sctp_chunk c; (void)d; (void)c;\n'
+                   '    if (sizeof(p2pt_desc) != 24 || sizeof(p2pt_sctp_chunk) != 16) return 2;\n'
+                   '    printf("%d %llu %llu %llu\\n", (int)p2pt_abi_version(), (unsigned long long)p2pt_sctp_fragments(65413),\n'
+                   '           (unsigned long long)p2pt_sctp_packets_bytes(1200), (unsigned long long)p2pt_frame_demux_scratch_bytes(1000));\n'
+                   '    return 0;\n}\n')
+    libdir = os.path.dirname(p2pt.lib_path())
+    exe = tmp_path / "c_abi"
+    subprocess.check_call(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"), str(src),
+                           "-o", str(exe), "-L", libdir, "-lp2ptunnel_b200", "-Wl,-rpath," + libdir])
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()
+    assert int(out[0]) >= 2 and out[1] == "55" and out[2] == "1228" and int(out[3]) > 0
