@@ -372,6 +372,14 @@ int32_t p2pt_dtls_replay_filter_batch_device(p2pt_ctx* ctx, uint64_t n, const ui
                                              const uint8_t* authentic, uint32_t n_sessions,
                                              uint64_t* latest, uint64_t* mask, uint8_t* started, uint8_t* accept,
                                              void* scratch, uint64_t scratch_bytes, void* stream);
+/* The same scan in ONE pass over the bodies (the call above reads them twice: count, then emit): the caller says how
+ * many body bytes there are at most (body_bytes >= body_off[k] - body_off[0], e.g. the gathered_cap it gave the demux) -
+ * the tile states of the scan need scratch in proportion to it, and body_off lives on the device.  Same outputs. */
+uint64_t p2pt_sse_scan_onepass_scratch_bytes(uint64_t k, uint64_t body_bytes);
+int32_t p2pt_sse_scan_onepass_batch_device(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, const uint64_t* body_off,
+                                           uint64_t body_bytes, uint64_t max_events, uint64_t* ev_csr, uint64_t* ev_end,
+                                           uint8_t* done, uint64_t* n_events_out, void* scratch, uint64_t scratch_bytes,
+                                           void* stream);
 uint64_t p2pt_sse_scan_scratch_bytes(uint64_t k);
 int32_t p2pt_sse_scan_batch_device(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, const uint64_t* body_off,
                                    uint64_t max_events, uint64_t* ev_csr, uint64_t* ev_end, uint8_t* done,

@@ -66,6 +66,8 @@ SIGNATURES = {
     "p2pt_dtls_seq_assign_batch_device": (_i32, [_vp, _u64, _vp, _u32, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_sse_scan_batch": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp]),
     "p2pt_sse_scan_scratch_bytes": (_u64, [_u64]),
+    "p2pt_sse_scan_onepass_scratch_bytes": (_u64, [_u64, _u64]),
+    "p2pt_sse_scan_onepass_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_sse_scan_batch_device": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "p2pt_frame_encode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "p2pt_frame_decode_batch_device": (_i32, [_vp, _u64, _vp, _vp, _vp, _vp]),

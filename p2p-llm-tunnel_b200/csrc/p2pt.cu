@@ -1687,6 +1687,68 @@ int32_t p2pt_sse_scan_batch_device(p2pt_ctx* ctx, uint64_t k, const uint8_t* bod
     return P2PT_OK;
 }
 
+namespace {
+struct SseOnepassScratch { u64* state; u64* gstate; u64* gfinal; unsigned long long* ticket; uint32_t* tile_first; uint64_t zero_bytes; uint64_t total; };
+SseOnepassScratch sse_onepass_carve(void* base, uint64_t ntiles) {
+    SseOnepassScratch r;
+    uint8_t* p = (uint8_t*)base;
+    r.ticket = (unsigned long long*)p; p += 256;
+    r.state = (u64*)p; p += align256(8 * ntiles);
+    r.gstate = (u64*)p; p += align256(8 * (ntiles / 32 + 1));
+    r.gfinal = (u64*)p; p += align256(8 * (ntiles / 32 + 1));
+    r.zero_bytes = (uint64_t)(p - (uint8_t*)base);          // ticket + tile states: cleared per call
+    r.tile_first = (uint32_t*)p; p += align256(4 * ntiles);
+    r.total = (uint64_t)(p - (uint8_t*)base);
+    return r;
+}
+}  // namespace
+
+uint64_t p2pt_sse_scan_onepass_scratch_bytes(uint64_t k, uint64_t body_bytes) {
+    (void)k;
+    return sse_onepass_carve(nullptr, sse_onepass_tiles(body_bytes)).total;
+}
+
+int32_t p2pt_sse_scan_onepass_batch_device(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, const uint64_t* body_off,
+                                           uint64_t body_bytes, uint64_t max_events, uint64_t* ev_csr, uint64_t* ev_end,
+                                           uint8_t* done, uint64_t* n_events_out, void* scratch, uint64_t scratch_bytes,
+                                           void* stream) {
+    if (!ctx) return P2PT_ERR_ARG;
+    if (!ev_csr || !n_events_out) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: null output");
+    DeviceGuard dg(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (k == 0) {
+        CUDA_TRY(ctx, cudaMemsetAsync(n_events_out, 0, 8, st));
+        CUDA_TRY(ctx, cudaMemsetAsync(ev_csr, 0, 8, st));
+        return P2PT_OK;
+    }
+    if (!body_off || !ev_end || !done || !scratch) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: null argument");
+    if (k > 0xfffffffeull) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: k must fit in 32 bits");
+    if (((uintptr_t)scratch & 255) != 0) return set_err(ctx, P2PT_ERR_ARG, "sse_scan: scratch must be 256-byte aligned");
+    const u64 ntiles = sse_onepass_tiles(body_bytes);
+    SseOnepassScratch r = sse_onepass_carve(scratch, ntiles);
+    if (scratch_bytes < r.total) return set_err(ctx, P2PT_ERR_CAPACITY, "sse_scan: scratch too small");
+    SseOnepassArgs a;
+    a.k = k; a.body = body; a.body_off = (const u64*)body_off; a.ntiles = ntiles;
+    a.ev_csr = (u64*)ev_csr; a.ev_end = (u64*)ev_end; a.cap = max_events; a.done = done; a.n_events_out = (u64*)n_events_out;
+    a.state = r.state; a.gstate = r.gstate; a.gfinal = r.gfinal; a.ticket = r.ticket; a.tile_first = r.tile_first;
+    CUDA_TRY(ctx, cudaMemsetAsync(scratch, 0, r.zero_bytes, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(r.tile_first, 0xff, 4 * ntiles, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(done, 0, k, st));
+    sse_tile_first_kernel<<<grid_for(ctx, k + 1, 256, 8), 256, 0, st>>>(a);
+    static std::atomic<int> occ{0};                      // resident blocks per SM (the same on every B200)
+    int per_sm = occ.load();
+    if (!per_sm) {
+        CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sse_onepass_kernel, 256, 0));
+        if (per_sm < 1) per_sm = 1;
+        occ.store(per_sm);
+    }
+    const u64 resident = (u64)ctx->sm_count * (u64)per_sm;   // persistent: tiles are handed out by ticket
+    sse_onepass_kernel<<<(unsigned)(ntiles < resident ? ntiles : resident), 256, 0, st>>>(a);
+    count_launch(ctx, 2);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return P2PT_OK;
+}
+
 int32_t p2pt_sse_scan_batch(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, const uint64_t* body_off,
                             uint64_t max_events, uint64_t* ev_csr, uint64_t* ev_end, uint8_t* done,
                             uint64_t* n_events_out) {
@@ -1702,7 +1764,7 @@ int32_t p2pt_sse_scan_batch(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, cons
     NvtxRange nvtx_("p2pt_sse_scan_batch");
     Lane* L = lg.lane;
     cudaStream_t st = L->streams[0];
-    const uint64_t sb = p2pt_sse_scan_scratch_bytes(k);
+    const uint64_t sb = p2pt_sse_scan_onepass_scratch_bytes(k, bytes);
     if (int32_t r = arena_reserve(ctx, L, pad256(bytes) + 2 * pad256(8 * (k + 1)) + pad256(8 * (max_events + 1)) + pad256(k) + 256 + pad256(sb) + 8192)) return r;
     uint8_t* d_body = arena_take<uint8_t>(L, bytes + 1);
     uint64_t* d_off = arena_take<uint64_t>(L, k + 1);
@@ -1713,7 +1775,7 @@ int32_t p2pt_sse_scan_batch(p2pt_ctx* ctx, uint64_t k, const uint8_t* body, cons
     uint8_t* d_scr = arena_take<uint8_t>(L, sb);
     if (bytes) CUDA_TRY(ctx, cudaMemcpyAsync(d_body, body + body_off[0], bytes, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(d_off, body_off, 8 * (k + 1), cudaMemcpyHostToDevice, st));
-    if (int32_t r = p2pt_sse_scan_batch_device(ctx, k, d_body - body_off[0], d_off, max_events, d_csr, d_end, d_done, d_n, d_scr, sb, st)) return r;
+    if (int32_t r = p2pt_sse_scan_onepass_batch_device(ctx, k, d_body - body_off[0], d_off, bytes, max_events, d_csr, d_end, d_done, d_n, d_scr, sb, st)) return r;
     uint64_t total = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&total, d_n, 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(ev_csr, d_csr, 8 * (k + 1), cudaMemcpyDeviceToHost, st));

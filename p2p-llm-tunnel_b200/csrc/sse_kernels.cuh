@@ -163,6 +163,257 @@ __global__ void __launch_bounds__(256) sse_scan_kernel(u64 k, const uint8_t* __r
     }
 }
 
+// ---- one pass ---------------------------------------------------------------------------------------------------
+// The two-pass scan above reads every body byte twice (count per stream, scan the counts, emit).  The order of ev_end
+// is simply the byte order of the bodies (streams lie back to back, body_off is monotone), so the whole thing is ONE
+// stream compaction over the byte range with a decoupled look-back: blocks take 16 KiB tiles in ticket order, flag the
+// bytes that close an event, publish the tile's count, sum the counts of the tiles in front (waiting only for tiles
+// whose ticket is lower - those are held by blocks that are already running, and every block publishes its count
+// before it waits), and write the tile's event ends at the running index.  A '\n' pair must not reach across a stream
+// boundary: the stream starts that lie in a tile are marked in a bitmap and their flags cleared; the same streams get
+// their ev_csr (events in front of their first byte) from the tile.  Which streams start in a tile comes from a small
+// pre-pass (sse_tile_first_kernel).  The body is read once.
+#ifndef P2PT_SSE_UNROLL
+#define P2PT_SSE_UNROLL 4      // vectors in flight per thread in the flag phase
+#endif
+constexpr int kSseUnroll = P2PT_SSE_UNROLL;
+constexpr uint32_t kSseTileBytes = 65536;                                // per block and ticket: what is in flight per SM has to cover
+constexpr int kSseTileVecs = kSseTileBytes / 16;                         // the latencies of a tile (look-back, offsets): 16 KiB tiles
+constexpr int kSseVecsPerThread = kSseTileVecs / 256;                    // measured 1.26 ms per 1.2 GB, twice the two-pass scan
+__host__ __device__ inline u64 sse_onepass_tiles(u64 body_bytes) { return (body_bytes + 15) / kSseTileBytes + 1; }
+
+struct SseOnepassArgs {
+    u64 k; const uint8_t* body; const u64* body_off; u64 ntiles;
+    u64* ev_csr; u64* ev_end; u64 cap; uint8_t* done; u64* n_events_out;
+    u64* state;                 // [ntiles] count << 2 | (1 = the tile's own count, 2 = count of all tiles up to it); zeroed
+    u64* gstate;                // [ntiles / 32 + 1] per group of 32 tiles: sum of the counts published so far << 8 | how many; zeroed
+    u64* gfinal;                // [ntiles / 32 + 1] count of all tiles up to the group's last one << 1 | 1 once known; zeroed
+    unsigned long long* ticket; // zeroed
+    uint32_t* tile_first;       // [ntiles] lowest stream index (0 .. k) whose first byte lies in the tile; 0xffffffff = none
+};
+
+__global__ void __launch_bounds__(256) sse_tile_first_kernel(const SseOnepassArgs a) {
+    const u64 b0 = __ldg(a.body_off);
+    const uint32_t lead = (uint32_t)((uintptr_t)(a.body + b0) & 15);
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 s = (u64)blockIdx.x * blockDim.x + threadIdx.x; s <= a.k; s += stride) {
+        u64 t = (__ldg(a.body_off + s) - b0 + lead) / kSseTileBytes;
+        if (t >= a.ntiles) t = a.ntiles - 1;
+        atomicMin(a.tile_first + t, (uint32_t)s);
+    }
+}
+
+__device__ __forceinline__ u64 ld_relaxed_u64(const u64* p) {
+    u64 v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u64(u64* p, u64 v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+
+// first index u in [0, k] with body_off[u] > pos (k + 1 if none)
+__device__ __forceinline__ u64 sse_upper_bound(const u64* __restrict__ body_off, u64 k, u64 pos) {
+    u64 lo = 0, hi = k + 1;
+    while (lo < hi) { const u64 mid = (lo + hi) >> 1; if (__ldg(body_off + mid) <= pos) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+
+__global__ void __launch_bounds__(256) sse_onepass_kernel(const SseOnepassArgs a) {
+    __shared__ __align__(16) uint16_t s_m16[kSseTileVecs];       // per vector: bit b = byte b closes an event
+    __shared__ __align__(16) uint16_t s_pre[kSseTileVecs];       // events of the tile in front of the vector (<= 65535 per tile)
+    __shared__ __align__(16) uint32_t s_start[kSseTileVecs / 2]; // bit per byte of the tile: a stream starts here
+    __shared__ uint32_t s_wsum[8];
+    __shared__ u64 s_base;
+    __shared__ unsigned long long s_tile;
+    const int t = threadIdx.x, lane = t & 31, wib = t >> 5;
+    const u64 b0 = __ldg(a.body_off), b1 = __ldg(a.body_off + a.k);
+    const uint8_t* lo = a.body + b0; const uint8_t* hi = a.body + b1;
+    const uint32_t lead = (uint32_t)((uintptr_t)lo & 15);
+    const uint8_t* base0 = lo - lead;                  // aligned start of tile 0
+    const uint16_t* s_start16 = reinterpret_cast<const uint16_t*>(s_start);
+    for (;;) {
+        if (t == 0) s_tile = atomicAdd(a.ticket, 1ull);
+#pragma unroll
+        for (int q = 0; q < kSseTileVecs / 2 / 256; q++) s_start[t + 256 * q] = 0;
+        __syncthreads();
+        const u64 tile = s_tile;
+        if (tile >= a.ntiles) return;
+        const uint8_t* tp = base0 + tile * kSseTileBytes;
+        const u64 rel0 = tile * kSseTileBytes;         // distance of the tile's first byte from base0
+        const bool last_tile = tile == a.ntiles - 1;
+        const uint32_t fs = a.tile_first[tile];        // needed further down: in flight meanwhile
+        // ---- flags of every vector (bytes outside the bodies count as zero); a vector's predecessor byte is its left
+        //      neighbour's last one: the lane to the left holds it, lane 0 reads it
+        if (tp > lo && tp + kSseTileBytes <= hi) {
+            // a tile inside the bodies (all but the first and the last): no range tests
+#pragma unroll 1
+            for (int j0 = 0; j0 < kSseVecsPerThread; j0 += kSseUnroll) {
+                uint4 v[kSseUnroll];
+                const uint8_t* p0 = tp + 16 * (t + 256 * j0);
+#pragma unroll
+                for (int u = 0; u < kSseUnroll; u++) v[u] = ldg128(p0 + 4096 * u);
+#pragma unroll
+                for (int u = 0; u < kSseUnroll; u++) {
+                    uint32_t prev = __shfl_up_sync(0xffffffffu, v[u].w, 1);
+                    if (lane == 0) prev = (uint32_t)__ldg(p0 + 4096 * u - 1) << 24;
+                    const PairFlags f = lf_pairs16(v[u], prev);
+                    s_m16[t + 256 * (j0 + u)] = (f.f[0] | f.f[1] | f.f[2] | f.f[3]) ? (uint16_t)pair_mask16(f) : (uint16_t)0;
+                }
+            }
+        } else {
+#pragma unroll 1
+            for (int j = 0; j < kSseVecsPerThread; j++) {
+                const int vi = t + 256 * j;
+                const uint8_t* p = tp + 16 * vi;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (p < hi && p + 16 > lo) {
+                    v = ldg128(p);
+                    if (p < lo || p + 16 > hi) v = keep_bytes16(v, p < lo ? (int)(lo - p) : 0, p + 16 > hi ? (int)(hi - p) : 16);
+                }
+                uint32_t prev = __shfl_up_sync(0xffffffffu, v.w, 1);
+                if (lane == 0) prev = (p > lo && p <= hi) ? ((uint32_t)__ldg(p - 1) << 24) : 0u;
+                const PairFlags f = lf_pairs16(v, prev);
+                s_m16[vi] = (f.f[0] | f.f[1] | f.f[2] | f.f[3]) ? (uint16_t)pair_mask16(f) : (uint16_t)0;
+            }
+        }
+        // ---- the streams whose first byte lies in this tile: a pair must not reach across it
+        if (fs != 0xffffffffu) {
+            for (u64 s = (u64)fs + t; s <= a.k; s += 256) {
+                const u64 r = __ldg(a.body_off + s) - b0 + lead - rel0;
+                if (r >= kSseTileBytes) break;          // later tiles (offsets are monotone); behind the last tile there is no byte
+                atomicOr(&s_start[r >> 5], 1u << (r & 31));
+            }
+        }
+        __syncthreads();
+        // ---- thread t owns vectors 16 t .. 16 t + 15 from here on: clear the stream starts, count, prefix
+        uint32_t mine = 0;
+        uint32_t cw[kSseVecsPerThread / 2];                                // bit b of word i: byte 32 i + b of this thread's 256 closes an event
+        {
+            uint4* mq = reinterpret_cast<uint4*>(s_m16 + kSseVecsPerThread * t);
+            const uint4* sq = reinterpret_cast<const uint4*>(s_start16 + kSseVecsPerThread * t);
+#pragma unroll
+            for (int h = 0; h < kSseVecsPerThread / 8; h++) {
+                uint4 mm = mq[h];
+                const uint4 ss = sq[h];
+                mm.x &= ~ss.x; mm.y &= ~ss.y; mm.z &= ~ss.z; mm.w &= ~ss.w;
+                if (fs != 0xffffffffu) mq[h] = mm;                         // the streams that start here look their counts up below
+                cw[4 * h] = mm.x; cw[4 * h + 1] = mm.y; cw[4 * h + 2] = mm.z; cw[4 * h + 3] = mm.w;
+                mine += __popc(mm.x) + __popc(mm.y) + __popc(mm.z) + __popc(mm.w);
+            }
+        }
+        uint32_t incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t x = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += x; }
+        if (lane == 31) s_wsum[wib] = incl;
+        __syncthreads();
+        uint32_t wbase = 0, agg = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) { const uint32_t x = s_wsum[w]; if (w < wib) wbase += x; agg += x; }
+        const uint32_t tpre = wbase + incl - mine;     // events of the tile in front of this thread's vectors
+        if (fs != 0xffffffffu) {                       // the streams that start here look their counts up below
+            uint32_t run = tpre;
+#pragma unroll
+            for (int q = 0; q < kSseVecsPerThread; q++) {
+                s_pre[kSseVecsPerThread * t + q] = (uint16_t)run;
+                run += __popc((uint32_t)s_m16[kSseVecsPerThread * t + q]);
+            }
+        }
+        // ---- look-back by warp 0: the count of all tiles in front.  All resident blocks (up to 1184) reach this point at
+        //      about the same time, so the nearest tile with a FINAL count lies about that far back: walking the tile
+        //      states 32 at a time took ~30 us per tile (most of the kernel), 256 at a time flooded L2 with polling.  So
+        //      tiles also add their count to their GROUP of 32 (sum and number of tiles in one 64-bit word, one atomic),
+        //      and the last tile of a group publishes the final count at the group's end: a walk is the tiles of the own
+        //      group in front (one step) and then whole groups, 32 of them = 1024 tiles per step.
+        if (wib == 0) {
+            u64 base = 0;
+            const u64 g = tile >> 5;
+            const int r = (int)(tile & 31);
+            if (lane == 0) {
+                st_release_u64(a.state + tile, ((u64)agg << 2) | 1u);
+                atomicAdd(reinterpret_cast<unsigned long long*>(a.gstate + g), ((unsigned long long)agg << 8) | 1ull);
+            }
+            bool found = false;
+            if (r > 0) {                                                    // tiles tile - 1 .. tile - r of this group
+                for (;;) {
+                    const u64 st = lane < r ? ld_relaxed_u64(a.state + tile - 1 - lane) : 0ull;
+                    const uint32_t flag = (uint32_t)(st & 3u);
+                    const uint32_t fin = __ballot_sync(0xffffffffu, lane < r && flag == 2u);
+                    const int first_fin = fin ? __ffs(fin) - 1 : r;        // nearest tile with a final count (r: none)
+                    if (__ballot_sync(0xffffffffu, lane < r && lane <= first_fin && flag == 0u)) { __nanosleep(64); continue; }
+                    u64 part = (lane < r && lane <= first_fin) ? (st >> 2) : 0ull;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+                    base += part;
+                    found = first_fin < r;
+                    break;
+                }
+            }
+            if (!found && g > 0) {                                          // whole groups g - 1, g - 2, ...
+                long long jg = (long long)g - 1;
+                for (;;) {
+                    const long long idx = jg - lane;
+                    const u64 gf = idx >= 0 ? ld_relaxed_u64(a.gfinal + idx) : 1ull;   // in front of group 0: nothing, final
+                    const u64 gs = idx >= 0 ? ld_relaxed_u64(a.gstate + idx) : 32ull;
+                    const uint32_t fin = __ballot_sync(0xffffffffu, (gf & 1ull) != 0);
+                    const int first_fin = fin ? __ffs(fin) - 1 : 32;
+                    const bool sums = lane < first_fin;                     // groups in front of the nearest final one: whole sums
+                    if (__ballot_sync(0xffffffffu, sums && (gs & 0xffull) != 32ull)) { __nanosleep(64); continue; }
+                    u64 part = sums ? (gs >> 8) : (lane == first_fin ? (gf >> 1) : 0ull);
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+                    base += part;
+                    if (first_fin < 32) break;
+                    jg -= 32;
+                }
+            }
+            if (lane == 0) {
+                st_release_u64(a.state + tile, ((base + agg) << 2) | 2u);
+                if (r == 31) st_release_u64(a.gfinal + g, ((base + agg) << 1) | 1u);
+                s_base = base;
+            }
+        }
+        __syncthreads();
+        const u64 base = s_base;
+        // ---- emit the event ends of this thread's vectors, in order
+        if (mine) {
+            u64 slot = base + tpre;
+            const u64 pos0 = (u64)(tp - a.body) + 16u * (uint32_t)(kSseVecsPerThread * t);
+#pragma unroll
+            for (int i = 0; i < kSseVecsPerThread / 2; i++) {
+                uint32_t mm = cw[i];
+                while (mm) {
+                    const int bit = __ffs(mm) - 1; mm &= mm - 1;
+                    const u64 end = pos0 + 32 * i + bit + 1;                   // offset just past the second '\n'
+                    if (slot < a.cap) a.ev_end[slot] = end;
+                    slot++;
+                    // does the next event read `data: [DONE]`?  Byte 6 tells `data: [` from `data: {`; only a full match looks
+                    // for the stream it lies in (it has to end inside that stream)
+                    if (b1 - end >= 14 && __ldg(a.body + end + 6) == (uint8_t)'[' && sse_is_done_event(a.body, end, b1)) {
+                        const u64 s = sse_upper_bound(a.body_off, a.k, end) - 1;
+                        if (s < a.k && __ldg(a.body_off + s + 1) - end >= 14) a.done[s] = 1;
+                    }
+                }
+            }
+        }
+        // ---- the streams that start in this tile: events in front of them, and an event starts at their first byte
+        if (fs != 0xffffffffu) {
+            for (u64 s = (u64)fs + t; s <= a.k; s += 256) {
+                const u64 so = __ldg(a.body_off + s);
+                const u64 r = so - b0 + lead - rel0;
+                if (r >= kSseTileBytes && !last_tile) break;               // the last tile also takes what lies behind it (nothing there)
+                const uint32_t vi = (uint32_t)(r >> 4);
+                const u64 before = r >= kSseTileBytes ? (u64)agg
+                                                      : (u64)s_pre[vi] + __popc((uint32_t)s_m16[vi] & ((1u << (r & 15)) - 1u));
+                a.ev_csr[s] = base + before;
+                if (s < a.k && sse_is_done_event(a.body, so, __ldg(a.body_off + s + 1))) a.done[s] = 1;
+            }
+        }
+        if (last_tile && t == 0) *a.n_events_out = base + agg;
+        __syncthreads();                                                      // shared arrays are rewritten for the next tile
+    }
+}
+
 // exclusive scan of k u64 counts in place (k + 1 entries out): block sums -> single block scan -> add
 __global__ void __launch_bounds__(kScanThreads) u64_scan_blocksum_kernel(u64 k, const u64* __restrict__ v, u64* __restrict__ blk) {
     const u64 i = (u64)blockIdx.x * kScanThreads + threadIdx.x;

@@ -91,3 +91,87 @@ def test_sse_scan_fuzz_newline_runs(ctx):
     csr, ends, done = ctx.sse_scan(body, off)
     ecsr, eends, edone = ob.sse_scan(body, off)
     assert np.array_equal(csr, ecsr) and np.array_equal(ends, eends) and np.array_equal(done, edone)
+
+
+def _device_scan(ctx, body, off, onepass, body_bytes=None, cap=None, lead=0):
+    """the device-pointer entry points on torch buffers; `lead` shifts the body inside its allocation (byte phase)"""
+    import torch
+    dev = torch.device("cuda:0")
+    k = len(off) - 1
+    span = int(off[-1] - off[0])
+    d_store = torch.zeros(lead + len(body) + 64, dtype=torch.uint8, device=dev)
+    d_store[lead:lead + len(body)] = torch.from_numpy(np.array(body, dtype=np.uint8)).to(dev)
+    d_body = d_store[lead:]
+    d_off = torch.from_numpy(np.ascontiguousarray(off).view(np.int64)).to(dev)
+    cap = (len(body) // 2 + 1) if cap is None else cap
+    ev_csr = torch.full((k + 1,), -1, dtype=torch.int64, device=dev); ev_end = torch.full((cap + 1,), -1, dtype=torch.int64, device=dev)
+    done = torch.full((max(k, 1),), 7, dtype=torch.uint8, device=dev); tot = torch.full((1,), -1, dtype=torch.int64, device=dev)
+    s = torch.cuda.current_stream().cuda_stream
+    if onepass:
+        bb = span if body_bytes is None else body_bytes
+        sb = int(ctx.lib.p2pt_sse_scan_onepass_scratch_bytes(k, bb))
+        scr = torch.full((sb,), 0x5A, dtype=torch.uint8, device=dev)          # the call has to clear what it needs itself
+        ctx.call("p2pt_sse_scan_onepass_batch_device", k, d_body, d_off, bb, cap, ev_csr, ev_end, done, tot, scr, sb, s)
+    else:
+        sb = int(ctx.lib.p2pt_sse_scan_scratch_bytes(k)); scr = torch.empty(sb, dtype=torch.uint8, device=dev)
+        ctx.call("p2pt_sse_scan_batch_device", k, d_body, d_off, cap, ev_csr, ev_end, done, tot, scr, sb, s)
+    torch.cuda.synchronize()
+    n = int(tot.item())
+    return ev_csr.cpu().numpy().view(np.uint64), ev_end.cpu().numpy().view(np.uint64)[:min(n, cap)], done.cpu().numpy()[:k], n, ev_end.cpu().numpy()
+
+
+@pytest.mark.parametrize("lead", [0, 1, 7, 15])
+def test_one_pass_scan_over_many_tiles(ctx, lead):
+    """p2pt_sse_scan_onepass_batch_device against the oracle and against the two-pass entry point: 3 MB of bodies (about 190
+    tiles of 16 KiB), streams from empty to several tiles long, runs of line feeds across tile edges, streams that start
+    exactly at a tile edge, a first stream that does not start at offset 0, every byte phase of the allocation, a byte
+    bound larger than the span, a scratch buffer full of garbage."""
+    rng = np.random.default_rng(900 + lead)
+    streams = []
+    total = 0
+    while total < 3_000_000:
+        kind = rng.random()
+        if kind < 0.15:
+            n = 0
+        elif kind < 0.5:
+            n = int(rng.integers(1, 40))
+        elif kind < 0.9:
+            n = int(rng.integers(40, 6000))
+        else:
+            n = int(rng.integers(6000, 70000))
+        p = float(rng.choice([0.0, 0.03, 0.3, 0.97]))
+        b = np.where(rng.random(n) < p, 10, 97).astype(np.uint8)
+        if n > 40 and rng.random() < 0.3:
+            at = int(rng.integers(0, n - 20)); b[at:at + 14] = np.frombuffer(b"data: [DONE]\n\n", np.uint8)
+            if at >= 2 and rng.random() < 0.7:
+                b[at - 2:at] = 10                                      # ... at an event start
+        if rng.random() < 0.1 and n >= 14:
+            b[:14] = np.frombuffer(b"data: [DONE]\n\n", np.uint8)      # DONE right at the stream start
+        streams.append(b.tobytes()); total += n
+    pre = 37                                                            # bytes in front of the first stream that belong to nobody
+    body = np.frombuffer(b"\n" * pre + b"".join(streams), np.uint8)
+    off = (np.concatenate([[0], np.cumsum([len(x) for x in streams])]) + pre).astype(np.uint64)
+    # some streams start exactly where a tile starts (tile 0 starts at the 16-byte line of the first stream's first byte)
+    ecsr, eends, edone = ob.sse_scan(body, off)
+    for bound in (None, int(off[-1] - off[0]) + 100_000):
+        csr, ends, done, n, _ = _device_scan(ctx, body, off, True, body_bytes=bound, lead=lead)
+        assert n == len(eends) and np.array_equal(csr, ecsr) and np.array_equal(ends, eends) and np.array_equal(done, edone)
+    csr2, ends2, done2, n2, _ = _device_scan(ctx, body, off, False, lead=lead)
+    assert n2 == n and np.array_equal(csr2, ecsr) and np.array_equal(ends2, eends) and np.array_equal(done2, edone)
+    assert edone.sum() > 5 and len(eends) > 10000
+
+
+def test_one_pass_scan_edges(ctx):
+    """no bytes at all; one stream of one byte; only empty streams; thousands of streams inside one tile; an event buffer that is
+    too small (the total is still reported, nothing is written behind the buffer)."""
+    for streams in ([b""], [b"\n"], [b""] * 50, [b"\n\n"] * 5000, [b"a\n\n", b"", b"\n", b"\n\n\n"]):
+        body = np.frombuffer(b"".join(streams) + b"\n\n", np.uint8)     # two bytes behind the last stream: nobody's
+        off = np.concatenate([[0], np.cumsum([len(x) for x in streams])]).astype(np.uint64)
+        ecsr, eends, edone = ob.sse_scan(body, off)
+        csr, ends, done, n, _ = _device_scan(ctx, body, off, True)
+        assert n == len(eends) and np.array_equal(csr, ecsr) and np.array_equal(ends, eends) and np.array_equal(done, edone), streams[:3]
+    streams = [b"x\n\n" * 3000]
+    body = np.frombuffer(streams[0], np.uint8); off = np.array([0, len(body)], np.uint64)
+    csr, ends, done, n, raw = _device_scan(ctx, body, off, True, cap=100)
+    assert n == 3000 and len(ends) == 100 and ends.tolist() == [3 * (i + 1) for i in range(100)]
+    assert raw[100] == -1                                               # the slot behind the buffer is untouched

@@ -12,11 +12,17 @@ body = t(np.frombuffer(one, np.uint8).reshape(1, -1).repeat(k, 0).reshape(-1)); 
 nev = one.count(b"\n\n") * k
 ev_csr = torch.empty(k + 1, dtype=torch.int64, device=dev); ev_end = torch.empty(nev + 1, dtype=torch.int64, device=dev)
 done = torch.empty(k, dtype=torch.uint8, device=dev); tot = torch.zeros(1, dtype=torch.int64, device=dev)
-sb = int(ctx.lib.p2pt_sse_scan_scratch_bytes(k)); scr = torch.empty(sb, dtype=torch.uint8, device=dev)
+two_pass = os.environ.get("TWO_PASS") is not None            # the older entry point that reads the bodies twice
+bb = k * len(one)
+sb = int(ctx.lib.p2pt_sse_scan_scratch_bytes(k) if two_pass else ctx.lib.p2pt_sse_scan_onepass_scratch_bytes(k, bb))
+scr = torch.empty(sb, dtype=torch.uint8, device=dev)
 for _ in range(int(sys.argv[1]) if len(sys.argv) > 1 else 3):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    ctx.call("p2pt_sse_scan_batch_device", k, body, boff, nev, ev_csr, ev_end, done, tot, scr, sb, s)
+    if two_pass:
+        ctx.call("p2pt_sse_scan_batch_device", k, body, boff, nev, ev_csr, ev_end, done, tot, scr, sb, s)
+    else:
+        ctx.call("p2pt_sse_scan_onepass_batch_device", k, body, boff, bb, nev, ev_csr, ev_end, done, tot, scr, sb, s)
     e1.record(); torch.cuda.synchronize()
     print(f"sse scan {e0.elapsed_time(e1):.3f} ms for {k * len(one) / 1e9:.2f} GB, {nev} events")
 assert int(tot.item()) == nev
