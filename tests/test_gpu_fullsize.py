@@ -165,11 +165,13 @@ def test_c3_one_million_records_seal_open(ctx, n_sessions):
     assert not out2[bad, :13 + L].any()                                     # failed records are zeroed
 
 
-def test_c4_ten_million_tiny_sse_frames(ctx):
-    """configs[3]: 10 M RES_BODY frames x 64 B (SSE chunk template), 4096 stream ids."""
+@pytest.mark.parametrize("sse", [True, False])
+def test_c4_ten_million_tiny_sse_frames(ctx, sse):
+    """configs[3]: 10 M RES_BODY frames x 64 B, 4096 stream ids; payload bytes from the SSE chunk template and the
+    uniform-random variant of SURVEY.md 8(d)."""
     from p2p_llm_tunnel_b200 import workload
     n, P = 10_000_000, 64
-    w = workload.frames_workload(n, P, sse=True)
+    w = workload.frames_workload(n, P, sse=sse)
     frames, off = ctx.frame_encode(w["types"], w["sids"], w["payload"], w["pay_off"])
     f2 = frames.reshape(n, P + 5)
     assert np.all(f2[:, 0] == 21) and np.array_equal(f2[:, 5:].reshape(-1), w["payload"])
@@ -180,7 +182,12 @@ def test_c4_ten_million_tiny_sse_frames(ctx):
     _check_demux_properties(r, w["sids"], n)
     assert int(r["gathered"].astype(np.uint64).sum()) == int(w["payload"].astype(np.uint64).sum())
     g = r["gathered"].reshape(n, P)
-    assert np.all(g[:, :6] == np.frombuffer(b"data: ", np.uint8))
+    if sse:
+        assert np.all(g[:, :6] == np.frombuffer(b"data: ", np.uint8))
+    # the fused call (decode + demux + gather, no descriptors) on the same frames
+    r2 = ctx.frame_decode_demux(frames, off, 4096, gathered_cap=n * P, want_desc=False)
+    for key in ("uniq_sid", "csr", "gathered_off", "gathered"):
+        assert np.array_equal(r2[key], r[key]), key
 
 
 def test_large_ragged_batch_through_the_32_frame_tiles(ctx):
