@@ -251,12 +251,16 @@ __global__ void __launch_bounds__(256) sse_onepass_kernel(const SseOnepassArgs a
             for (int j0 = 0; j0 < kSseVecsPerThread; j0 += kSseUnroll) {
                 uint4 v[kSseUnroll];
                 const uint8_t* p0 = tp + 16 * (t + 256 * j0);
+                uint32_t pb[kSseUnroll];                                   // lane 0: the byte in front of its vector
 #pragma unroll
-                for (int u = 0; u < kSseUnroll; u++) v[u] = ldg128(p0 + 4096 * u);
+                for (int u = 0; u < kSseUnroll; u++) {                     // all loads of the group before the first use
+                    v[u] = ldg128(p0 + 4096 * u);
+                    pb[u] = lane == 0 ? (uint32_t)__ldg(p0 + 4096 * u - 1) : 0u;
+                }
 #pragma unroll
                 for (int u = 0; u < kSseUnroll; u++) {
                     uint32_t prev = __shfl_up_sync(0xffffffffu, v[u].w, 1);
-                    if (lane == 0) prev = (uint32_t)__ldg(p0 + 4096 * u - 1) << 24;
+                    if (lane == 0) prev = pb[u] << 24;
                     const PairFlags f = lf_pairs16(v[u], prev);
                     s_m16[t + 256 * (j0 + u)] = (f.f[0] | f.f[1] | f.f[2] | f.f[3]) ? (uint16_t)pair_mask16(f) : (uint16_t)0;
                 }
