@@ -355,5 +355,81 @@ private:
     const Context& c_;
 };
 
+// ---- record-layer bookkeeping (webrtc-dtls 0.10.0 conn / record layer, un-vendored) ----
+
+// unpack_datagram for a batch: the records of every datagram, back to back; a datagram with a truncated record (or a
+// trailing bare header) is dropped whole.
+struct Unpacked { std::vector<uint64_t> rec_off; std::vector<uint32_t> rec_dgram; std::vector<uint8_t> dgram_status; };
+inline Unpacked unpack_datagrams(const Context& c, const Bytes& buf, const std::vector<uint64_t>& dgram_off) {
+    Unpacked u;
+    const uint64_t n = dgram_off.empty() ? 0 : dgram_off.size() - 1;
+    const uint64_t cap = buf.size() / RECORD_LAYER_HEADER_SIZE + 1;
+    u.rec_off.assign(cap + 1, 0); u.rec_dgram.assign(cap, 0); u.dgram_status.assign(n ? n : 1, 0);
+    uint32_t k = 0;
+    const uint8_t dummy = 0;
+    c.check(p2pt_dtls_datagram_split_batch(c.get(), n, buf.empty() ? &dummy : buf.data(), dgram_off.data(), cap, u.rec_off.data(),
+                                           u.rec_dgram.data(), u.dgram_status.data(), &k));
+    u.rec_off.resize(k + 1); u.rec_dgram.resize(k); u.dgram_status.resize(n);
+    return u;
+}
+
+// replaydetector::SlidingWindowDetector (window 64) for every session of a connection table: check() before the record is
+// opened, accept() only for records that authenticated - a batch at a time, in arrival order per session.
+class ReplayDetector {
+public:
+    ReplayDetector(const Context& c, size_t n_sessions) : c_(c), latest_(n_sessions, 0), mask_(n_sessions, 0), started_(n_sessions, 0) {}
+    std::vector<uint8_t> filter(const std::vector<uint32_t>& session, const std::vector<uint64_t>& seq48,
+                                const std::vector<uint8_t>* authentic = nullptr) {
+        std::vector<uint8_t> accept(session.size() ? session.size() : 1, 0);
+        c_.check(p2pt_dtls_replay_filter_batch(c_.get(), session.size(), session.data(), seq48.data(),
+                                               authentic ? authentic->data() : nullptr, (uint32_t)latest_.size(), latest_.data(),
+                                               mask_.data(), started_.data(), accept.data()));
+        accept.resize(session.size());
+        return accept;
+    }
+    uint64_t latest(size_t s) const { return latest_[s]; }
+private:
+    const Context& c_;
+    std::vector<uint64_t> latest_, mask_;
+    std::vector<uint8_t> started_;
+};
+
+// the write path's sequence numbers: every record takes its session's (epoch's) counter, fetch_add(1); more than 2^48 - 1
+// is ErrSequenceNumberOverflow (ok[i] = 0 here)
+class SequenceNumbers {
+public:
+    SequenceNumbers(const Context& c, size_t n_sessions) : c_(c), next_(n_sessions, 0) {}
+    std::vector<uint64_t> assign(const std::vector<uint32_t>& session, std::vector<uint8_t>* ok_out = nullptr) {
+        std::vector<uint64_t> seq(session.size() ? session.size() : 1, 0);
+        std::vector<uint8_t> ok(seq.size(), 0);
+        c_.check(p2pt_dtls_seq_assign_batch(c_.get(), session.size(), session.data(), (uint32_t)next_.size(), next_.data(), seq.data(), ok.data()));
+        seq.resize(session.size()); ok.resize(session.size());
+        if (ok_out) *ok_out = std::move(ok);
+        return seq;
+    }
+    void restart(size_t s) { next_[s] = 0; }                    // a new epoch
+    uint64_t next(size_t s) const { return next_[s]; }
+private:
+    const Context& c_;
+    std::vector<uint64_t> next_;
+};
+
 }  // namespace dtls
+
+// ---- SSE event scan over per-stream bodies (upstream framing of tmp/mock_llm.py:54, :68-69) ----
+namespace sse {
+struct Events { std::vector<uint64_t> ev_csr, ev_end; std::vector<uint8_t> done; };
+inline Events scan(const Context& c, const Bytes& body, const std::vector<uint64_t>& body_off) {
+    Events e;
+    const uint64_t k = body_off.empty() ? 0 : body_off.size() - 1;
+    const uint64_t cap = body.size() / 2 + 1;
+    e.ev_csr.assign(k + 1, 0); e.ev_end.assign(cap, 0); e.done.assign(k ? k : 1, 0);
+    uint64_t total = 0;
+    const uint8_t dummy = 0;
+    c.check(p2pt_sse_scan_batch(c.get(), k, body.empty() ? &dummy : body.data(), body_off.data(), cap, e.ev_csr.data(), e.ev_end.data(),
+                                e.done.data(), &total));
+    e.ev_end.resize(total); e.done.resize(k);
+    return e;
+}
+}  // namespace sse
 }  // namespace p2pt_host

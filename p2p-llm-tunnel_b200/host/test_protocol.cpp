@@ -246,6 +246,84 @@ TEST(test_serve_reassembler_matches_the_per_frame_loop) {
     CHECK(rs.pending_requests.size() == 1 && rs.pending_requests.count(9) == 1);
 }
 
+// --- record-layer bookkeeping and the SSE scan against scalar restatements written here (not the oracle: this file is
+//     product-side) ---
+TEST(test_replay_detector_matches_the_sliding_window) {
+    // the window as replaydetector keeps it: latest, a 64-bit mask of seen numbers behind it
+    struct Win { bool started = false; uint64_t latest = 0, mask = 0;
+                 bool check(uint64_t q) const { if (!started || q > latest) return true; if (latest - q >= 64) return false; return !((mask >> (latest - q)) & 1); }
+                 void accept(uint64_t q) { if (!started) { started = true; latest = q; mask = 1; }
+                                           else if (q > latest) { uint64_t sh = q - latest; mask = sh >= 64 ? 0 : mask << sh; mask |= 1; latest = q; }
+                                           else mask |= 1ull << (latest - q); } };
+    const size_t S = 5;
+    std::vector<Win> ref(S);
+    dtls::ReplayDetector det(c, S);
+    uint64_t x = 88172645463325252ull;
+    auto rnd = [&]() { x ^= x << 13; x ^= x >> 7; x ^= x << 17; return x; };
+    std::vector<uint64_t> nxt(S, 0);
+    for (int batch = 0; batch < 3; batch++) {
+        std::vector<uint32_t> sess; std::vector<uint64_t> seq; std::vector<uint8_t> auth, want;
+        for (int i = 0; i < 4000; i++) {
+            const uint32_t s = (uint32_t)(rnd() % S);
+            const uint64_t r = rnd() % 100;
+            uint64_t q;
+            if (r < 60) q = nxt[s]++;
+            else if (r < 85) { const uint64_t back = rnd() % 80; q = nxt[s] > back ? nxt[s] - back : 0; }
+            else { nxt[s] += rnd() % 90; q = nxt[s]++; }
+            const uint8_t a = (rnd() % 25) != 0;
+            sess.push_back(s); seq.push_back(q); auth.push_back(a);
+            const bool ok = ref[s].check(q) && a;
+            if (ok) ref[s].accept(q);
+            want.push_back(ok);
+        }
+        CHECK(det.filter(sess, seq, &auth) == want);
+        for (size_t s = 0; s < S; s++) CHECK(det.latest(s) == ref[s].latest);
+    }
+}
+TEST(test_sequence_numbers_count_per_session) {
+    dtls::SequenceNumbers sn(c, 4);
+    const std::vector<uint32_t> sess = {2, 0, 2, 2, 1, 0, 7, 2};
+    std::vector<uint8_t> ok;
+    auto seq = sn.assign(sess, &ok);
+    CHECK((seq == std::vector<uint64_t>{0, 0, 1, 2, 0, 1, 0, 3}));
+    CHECK((ok == std::vector<uint8_t>{1, 1, 1, 1, 1, 1, 0, 1}));                     // session 7 is not in the table
+    seq = sn.assign({2, 2, 3});
+    CHECK((seq == std::vector<uint64_t>{4, 5, 0}));
+    CHECK(sn.next(2) == 6 && sn.next(0) == 2 && sn.next(3) == 1);
+    sn.restart(2);
+    CHECK(sn.assign({2})[0] == 0);
+}
+TEST(test_unpack_datagrams_and_drop_the_truncated_one) {
+    auto rec = [](uint8_t type, size_t len) { Bytes r = {type, 0xfe, 0xfd, 0, 1, 0, 0, 0, 0, 0, 9, (uint8_t)(len >> 8), (uint8_t)len}; r.resize(13 + len, 0x5a); return r; };
+    Bytes buf; std::vector<uint64_t> off = {0};
+    auto dgram = [&](std::initializer_list<Bytes> recs, size_t cut = 0) { for (auto& r : recs) buf.insert(buf.end(), r.begin(), r.end()); buf.resize(buf.size() - cut); off.push_back(buf.size()); };
+    dgram({rec(22, 40), rec(20, 1), rec(22, 64)});
+    dgram({rec(23, 1200)});
+    dgram({rec(23, 100), rec(23, 50)}, 7);                                          // the second record is cut short
+    dgram({rec(23, 10), rec(23, 0)});                                               // a trailing bare header: dropped as well
+    auto u = dtls::unpack_datagrams(c, buf, off);
+    CHECK((u.dgram_status == std::vector<uint8_t>{0, 0, P2PT_ST_BAD_HEADER, P2PT_ST_BAD_HEADER}));
+    CHECK((u.rec_dgram == std::vector<uint32_t>{0, 0, 0, 1}));
+    CHECK(u.rec_off.size() == 5 && u.rec_off[0] == 0 && u.rec_off[1] == 53 && u.rec_off[2] == 67 && u.rec_off[3] == off[1]);
+}
+TEST(test_sse_scan_finds_the_events_of_every_stream) {
+    const std::vector<std::string> streams = {"data: {\"a\":1}\n\ndata: {\"b\":2}\n\ndata: [DONE]\n\n", "", "\n", "data: {\"c\":3}\n\ntail without an end",
+                                              "data: [DONE]\n\n", "x data: [DONE]\n\n"};
+    Bytes body; std::vector<uint64_t> off = {0};
+    for (auto& s : streams) { body.insert(body.end(), s.begin(), s.end()); off.push_back(body.size()); }
+    auto e = sse::scan(c, body, off);
+    std::vector<uint64_t> want_csr = {0}, want_end; std::vector<uint8_t> want_done;
+    for (size_t s = 0; s < streams.size(); s++) {
+        const std::string& t = streams[s];
+        bool done = t.compare(0, 14, "data: [DONE]\n\n") == 0;
+        for (size_t i = 1; i < t.size(); i++)
+            if (t[i] == '\n' && t[i - 1] == '\n') { want_end.push_back(off[s] + i + 1); done |= t.compare(i + 1, 14, "data: [DONE]\n\n") == 0; }
+        want_csr.push_back(want_end.size()); want_done.push_back(done);
+    }
+    CHECK(e.ev_csr == want_csr); CHECK(e.ev_end == want_end); CHECK(e.done == want_done);
+    CHECK((want_done == std::vector<uint8_t>{1, 0, 0, 0, 1, 0}));
+}
+
 int main() {
     try {
         Context c(0);

@@ -12,9 +12,11 @@ def test_reference_codec_tests_in_cpp(built):
     r = subprocess.run([built.HOST_TEST], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     print(r.stdout)
     assert r.returncode == 0, r.stdout
-    assert "22 tests, 0 failed checks" in r.stdout
+    assert "26 tests, 0 failed checks" in r.stdout
     for name in ("test_roundtrip_res_body", "test_decode_unknown_type", "test_large_payload", "test_crypto_gcm_known_record",
-                 "test_proxy_reader_matches_the_per_frame_loop", "test_serve_reassembler_matches_the_per_frame_loop"):
+                 "test_proxy_reader_matches_the_per_frame_loop", "test_serve_reassembler_matches_the_per_frame_loop",
+                 "test_replay_detector_matches_the_sliding_window", "test_sequence_numbers_count_per_session",
+                 "test_unpack_datagrams_and_drop_the_truncated_one", "test_sse_scan_finds_the_events_of_every_stream"):
         assert f"ok   {name}" in r.stdout
 
 
