@@ -79,3 +79,58 @@ int main(){ srand(7); int bad=0;
                            "-o", str(exe)])
     out = subprocess.check_output([str(exe)]).decode()
     assert "bad=0" in out
+
+
+def test_cpp_reader_routes_headers_like_a_json_parser(tmp_path):
+    """The C++ reader mirror routes REQ_HEADERS / RES_HEADERS frames by the `stream_id` INSIDE their JSON payload
+    (proxy.rs:129, serve.rs:113-118 parse the payload with serde_json), with a scanner that interprets nothing else of the
+    JSON.  Host-only logic: compiled for the CPU and compared with Python's json module on well-formed and broken
+    payloads."""
+    import json
+    cases = [
+        '{"stream_id":42,"status":200,"headers":{}}',
+        '{ "stream_id" : 7 , "method":"POST"}',
+        '{"headers":{"stream_id":9},"stream_id":3}',                       # the nested one is not it
+        '{"note":"\\"stream_id\\":99","stream_id":5}',                     # inside a string, with escaped quotes
+        '{"a":[{"stream_id":1}],"stream_id":4294967295}',                  # u32::MAX
+        '{"stream_id":4294967296}',                                        # does not fit u32: serde fails
+        '{"stream_id":-1}', '{"stream_id":"12"}', '{"stream_id":null}', '{"status":200}',
+        '{"stream_id":12', '{"stream_id":12}}', '', 'not json', '{"stream_id":1,"s":"unterminated}',
+        '{"k":"\\\\","stream_id":8}',                                      # a string that ends in a backslash pair
+        '{"stream_id":\n\t17}',
+    ]
+    want = []
+    for c in cases:
+        try:
+            v = json.loads(c)
+            sid = v.get("stream_id") if isinstance(v, dict) else None
+            ok = isinstance(sid, int) and not isinstance(sid, bool) and 0 <= sid <= 0xFFFFFFFF
+            want.append(sid if ok else -1)
+        except ValueError:
+            want.append(-1)
+    src = tmp_path / "j.cpp"
+    src.write_text(r'''
+#include "p2pt_host.hpp"
+#include <cstdio>
+#include <iostream>
+#include <string>
+int main() {
+    std::string line;
+    while (std::getline(std::cin, line, '\x1e')) {
+        const uint8_t* p = (const uint8_t*)line.data();
+        auto sid = p2pt_host::reader::json_looks_complete(p, line.size()) ? p2pt_host::reader::json_u32_field(p, line.size(), "stream_id")
+                                                                          : std::nullopt;
+        std::printf("%lld\n", sid ? (long long)*sid : -1LL);
+    }
+    return 0;
+}
+''')
+    import p2p_llm_tunnel_b200 as p2pt
+    libdir = os.path.dirname(p2pt.lib_path())
+    exe = tmp_path / "j"
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "p2p-llm-tunnel_b200", "host"),
+                           str(src), "-o", str(exe), "-L", libdir, "-lp2ptunnel_b200", "-Wl,-rpath," + libdir])
+    out = subprocess.run([str(exe)], input="\x1e".join(cases).encode(), capture_output=True, check=True).stdout.decode().split()
+    got = [int(x) for x in out]
+    # an empty last case yields no record from getline: compare what came out, then the count
+    assert got == want[:len(got)] and len(got) >= len(cases) - 1, list(zip(cases, want, got))
