@@ -134,3 +134,38 @@ int main() {
     got = [int(x) for x in out]
     # an empty last case yields no record from getline: compare what came out, then the count
     assert got == want[:len(got)] and len(got) >= len(cases) - 1, list(zip(cases, want, got))
+
+
+def test_committed_bench_lines_carry_the_contract():
+    """profiles/r02_bench_final.json and r02_reference_final.json (the lines `bench.py` printed on the B200 box) have every
+    key the measurement contract names, with consistent values."""
+    import json
+    line = json.load(open(os.path.join(ROOT, "profiles", "r02_bench_final.json")))
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+                "dtype", "data", "config", "roofline", "cpu_baseline", "e2e", "gpu_launches", "clocks", "configs"):
+        assert key in line, key
+    assert line["unit"] == "GB/s" and line["higher_is_better"] is True and line["scaling"] == "weak" and line["dtype"] == "u8"
+    assert line["vs_baseline"] is None and line["data"] == "synthetic" and "workload" in line["config"] and line["warmup"] >= 3
+    assert line["gpu_launches"] > 0 and line["n_gpus"] == 1
+    rf = line["roofline"]
+    for key in ("bound", "achieved", "peak", "unit", "frac", "traffic"):
+        assert key in rf, key
+    assert abs(rf["frac"] - rf["achieved"] / rf["peak"]) < 1e-9 and 0.5 < rf["frac"] < 1.0
+    assert rf["hbm"]["bound"] == "hbm" and abs(rf["hbm"]["frac"] - rf["hbm"]["achieved"] / rf["hbm"]["peak"]) < 1e-9
+    cb = line["cpu_baseline"]
+    for key in ("value", "unit", "cores", "kind", "sample"):
+        assert key in cb, key
+    assert cb["kind"] in ("port", "reference") and cb["cores"] >= 1 and "openssl_evp" in cb
+    e2e = line["e2e"]
+    for key in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step"):
+        assert key in e2e, key
+    assert e2e["h2d_bytes_per_step"] > 2e9 and e2e["d2h_bytes_per_step"] > 2e9 and 0 < e2e["value"] < line["value"]
+    ck = line["clocks"]
+    assert ck["sm_mhz"] > 0.9 * ck["sm_max_mhz"] and not set(ck["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
+    # value = payload bytes of the batch / step time
+    n = line["config"]["records_per_step_per_gpu"] * line["config"]["payload_bytes"]
+    assert abs(line["value"] - n / line["ms_per_step"] / 1e6) < 0.01 * line["value"]
+    ref = json.load(open(os.path.join(ROOT, "profiles", "r02_reference_final.json")))
+    assert ref["impl"] == "reference" and ref["metric"] == line["metric"] and ref["unit"] == line["unit"] and ref["config"] == line["config"]
+    assert ref["e2e"]["h2d_bytes_per_step"] == 0 and ref["e2e"]["d2h_bytes_per_step"] == 0 and ref["e2e"]["value"] == ref["value"]
+    assert ref["cpu_baseline"]["value"] == ref["value"] and ref["cpu_baseline"]["kind"] in ("port", "reference")
